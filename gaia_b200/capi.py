@@ -1,0 +1,382 @@
+"""ctypes binding of the C ABI declared in include/gaia_b200.h (libgaia_b200.so).
+
+This is the reference-side binding a maintainer would use from Python; the C++ host adapter
+(gaia_b200/host/VBDPhysicsB200.h) binds the same symbols.  There is no CPU fallback: if the
+shared library (built in-tree by __graft_entry__.build()) is missing, loading raises.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libgaia_b200.so")
+
+c_f3 = C.c_float * 3
+
+
+class PhysicsParams(C.Structure):
+    """gaia_physics_params (BasePhysicsParams + VBDPhysicsParameters of the reference)."""
+    _fields_ = [
+        ("gravity", c_f3), ("timeStep", C.c_float), ("numSubsteps", C.c_int32), ("iterations", C.c_int32),
+        ("usePlaneGround", C.c_int32), ("useBowlGround", C.c_int32), ("checkAndUpdateWorldBounds", C.c_int32),
+        ("worldBoundsMin", c_f3), ("worldBoundsMax", c_f3), ("boundaryFrictionDynamic", C.c_float),
+        ("dcdTetMeshSceneBVHRebuildSteps", C.c_int32), ("dcdSurfaceSceneBVHRebuildSteps", C.c_int32),
+        ("ccdBVHRebuildSteps", C.c_int32),
+        ("stepSize", C.c_float), ("stepSizeGD", C.c_float), ("associateGravityWithInertia", C.c_int32),
+        ("collisionStiffness", C.c_float), ("intermediateCollisionIterations", C.c_int32),
+        ("boundaryCollisionStiffness", C.c_float), ("boundaryFrictionEpsV", C.c_float),
+        ("frictionStartIter", C.c_int32), ("useAccelerator", C.c_int32), ("acceleratorRho", C.c_float),
+        ("collisionOffHeight", C.c_float),
+    ]
+
+
+class CollisionParams(C.Structure):
+    """gaia_collision_params (CollisionDetectionParamters of the reference)."""
+    _fields_ = [
+        ("allowCCD", C.c_int32), ("allowDCD", C.c_int32), ("checkFeasibleRegion", C.c_int32),
+        ("checkTetTraverse", C.c_int32), ("handleSelfCollision", C.c_int32),
+        ("stopTraversingAfterPassingQueryPoint", C.c_int32), ("tetrahedralTraverseForNonSelfIntersection", C.c_int32),
+        ("useStaticTraverse", C.c_int32), ("loopLessTraverse", C.c_int32), ("shiftQueryPointToCenter", C.c_int32),
+        ("centerShiftLevel", C.c_float), ("maxNumberOfBVHQuery", C.c_int32), ("feasibleRegionEpsilon", C.c_float),
+        ("rayTriIntersectionEPSILON", C.c_float), ("maxSearchDistanceMultiplier", C.c_float),
+    ]
+
+
+class ObjectParams(C.Structure):
+    """gaia_object_params (ObjectParams + ObjectParamsVBD + ObjectParametersVBDNeoHookean)."""
+    _fields_ = [
+        ("scale", c_f3), ("rotation", c_f3), ("translation", c_f3), ("initialVelocity", c_f3),
+        ("density", C.c_float), ("hasNoGravZone", C.c_int32), ("noGravZoneThreshold", C.c_float),
+        ("maxVelocityMagnitude", C.c_float), ("frameToAppear", C.c_int32),
+        ("frictionDynamic", C.c_float), ("frictionEpsV", C.c_float), ("exponentialVelDamping", C.c_float),
+        ("constantVelDamping", C.c_float), ("initializationType", C.c_int32), ("initRatio_g", C.c_float),
+        ("miu", C.c_float), ("lmbd", C.c_float), ("dampingHydrostatic", C.c_float), ("dampingDeviatoric", C.c_float),
+    ]
+
+
+class Contact(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("queryMesh", "queryVertex", "hitMesh", "hitTet", "hitFace", "fromCCD",
+                                         "shortestPathFound", "closestPointType")]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ("timeCsmpInitialStep", "timeCsmpMaterialSolve", "timeCsmpUpdateVelocity",
+                                          "timeCsmpUpdatingBVHDCD", "timeCsmpColDetectDCD", "timeCsmpUpdatingBVHCCD",
+                                          "timeCsmpColDetectCCD", "timeCsmpFrame")] + \
+               [(n, C.c_int64) for n in ("vertexSolves", "colourSweeps", "substeps", "frames", "kernelLaunches",
+                                         "algorithmicBytes", "numContactsDCD", "numContactsCCD")]
+
+
+CONTACT_DTYPE = np.dtype([(n, np.int32) for n, _ in Contact._fields_])
+
+
+def default_physics_params(**kw):
+    p = PhysicsParams()
+    p.gravity = c_f3(0, -10, 0); p.timeStep = 0.01666666666666666666; p.numSubsteps = 20; p.iterations = 1
+    p.usePlaneGround = 1; p.useBowlGround = 0; p.checkAndUpdateWorldBounds = 0
+    p.worldBoundsMin = c_f3(-1e7, -1e7, -1e7); p.worldBoundsMax = c_f3(1e7, 1e7, 1e7)
+    p.boundaryFrictionDynamic = 0.1
+    p.dcdTetMeshSceneBVHRebuildSteps = 16; p.dcdSurfaceSceneBVHRebuildSteps = 3; p.ccdBVHRebuildSteps = 7
+    p.stepSize = 1.0; p.stepSizeGD = 1e-3; p.associateGravityWithInertia = 1
+    p.collisionStiffness = 1e5; p.intermediateCollisionIterations = -1
+    p.boundaryCollisionStiffness = 1e5; p.boundaryFrictionEpsV = 1.0; p.frictionStartIter = 0
+    p.useAccelerator = 0; p.acceleratorRho = 0.93; p.collisionOffHeight = 1e7
+    _apply(p, kw)
+    return p
+
+
+def default_collision_params(**kw):
+    c = CollisionParams()
+    c.allowCCD = 1; c.allowDCD = 1; c.checkFeasibleRegion = 1; c.checkTetTraverse = 1; c.handleSelfCollision = 1
+    c.stopTraversingAfterPassingQueryPoint = 1; c.tetrahedralTraverseForNonSelfIntersection = 1
+    c.useStaticTraverse = 1; c.loopLessTraverse = 0; c.shiftQueryPointToCenter = 1; c.centerShiftLevel = 0.01
+    c.maxNumberOfBVHQuery = 500; c.feasibleRegionEpsilon = 1e-2; c.rayTriIntersectionEPSILON = 1e-10
+    c.maxSearchDistanceMultiplier = 1.8
+    _apply(c, kw)
+    return c
+
+
+def default_object_params(**kw):
+    o = ObjectParams()
+    o.scale = c_f3(1, 1, 1); o.rotation = c_f3(0, 0, 0); o.translation = c_f3(0, 0, 0); o.initialVelocity = c_f3(0, 0, 0)
+    o.density = 1.0; o.hasNoGravZone = 0; o.noGravZoneThreshold = 0.0; o.maxVelocityMagnitude = -1.0
+    o.frameToAppear = -1; o.frictionDynamic = 0.1; o.frictionEpsV = 0.01; o.exponentialVelDamping = 1.0
+    o.constantVelDamping = 0.0; o.initializationType = 0; o.initRatio_g = 0.5
+    o.miu = 1e4; o.lmbd = 1e5; o.dampingHydrostatic = 0.0; o.dampingDeviatoric = 0.0
+    _apply(o, kw)
+    return o
+
+
+def _apply(st, kw):
+    names = {n for n, _ in st._fields_}
+    for k, v in kw.items():
+        if k not in names:
+            raise KeyError(f"{type(st).__name__} has no field {k!r}")
+        if isinstance(v, (list, tuple, np.ndarray)):
+            setattr(st, k, c_f3(*[float(x) for x in v]))
+        else:
+            setattr(st, k, v)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+class GaiaError(RuntimeError):
+    pass
+
+
+def bind_scene_api(lib, prefix):
+    """Declare argtypes for the functions shared by the product ABI and the oracle's shadow ABI."""
+    P = C.c_void_p
+    FP, IP = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    sig = {
+        "add_tet_mesh": ([P, C.c_int32, C.c_int32, FP, IP, C.POINTER(ObjectParams), C.c_int32, IP, IP, C.c_int32, IP], C.c_int),
+        "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
+        "frame_id": ([P], C.c_int), "num_meshes": ([P], C.c_int),
+        "mesh_sizes": ([P, C.c_int, IP, IP, IP, IP], C.c_int),
+        "get_positions": ([P, C.c_int, FP], C.c_int), "get_prev_positions": ([P, C.c_int, FP], C.c_int),
+        "get_velocities": ([P, C.c_int, FP], C.c_int), "get_inertia": ([P, C.c_int, FP], C.c_int),
+        "set_state": ([P, C.c_int, FP, FP], C.c_int), "get_surface_positions": ([P, C.c_int, FP], C.c_int),
+        "get_world_bounds": ([P, FP, FP], C.c_int), "num_parallel_groups": ([P], C.c_int),
+        "get_parallel_group": ([P, C.c_int, IP, IP], C.c_int),
+        "get_surface_vertex_ids": ([P, C.c_int, IP], C.c_int), "get_surface_faces": ([P, C.c_int, IP], C.c_int),
+        "get_vertex_masses": ([P, C.c_int, FP], C.c_int),
+        "detect_collisions": ([P, C.c_int, C.c_int], C.c_int),
+        "get_contacts": ([P, C.POINTER(Contact), C.c_int64, C.POINTER(C.c_int64)], C.c_int),
+        "enable_mesh": ([P, C.c_int, C.c_int, C.c_int], C.c_int),
+        "get_stats": ([P, C.POINTER(Stats)], C.c_int), "reset_stats": ([P], C.c_int),
+    }
+    for name, (args, res) in sig.items():
+        fn = getattr(lib, prefix + name)
+        fn.argtypes = args
+        fn.restype = res
+
+
+class SceneBase:
+    """Calls shared by the product (`gaia_b200_*`) and the oracle shadow ABI (`oracle_*`)."""
+    _lib = None
+    _prefix = ""
+    h = None
+
+    def _call(self, name, *args):
+        rc = getattr(self._lib, self._prefix + name)(self.h, *args)
+        if rc < 0:
+            raise GaiaError(f"{self._prefix}{name} failed: {rc} {self.last_error()}")
+        return rc
+
+    def last_error(self):
+        return ""
+
+    def add_tet_mesh(self, xyz, tets, obj, colors, fixed=()):
+        xyz = _f32(xyz).reshape(-1, 3); tets = _i32(tets).reshape(-1, 4)
+        offs = np.zeros(len(colors) + 1, np.int32)
+        offs[1:] = np.cumsum([len(c) for c in colors])
+        cv = _i32(np.concatenate([np.asarray(c, np.int32) for c in colors]) if len(colors) else np.zeros(0, np.int32))
+        fx = _i32(np.asarray(fixed, np.int32))
+        return self._call("add_tet_mesh", xyz.shape[0], tets.shape[0], _fp(xyz), _ip(tets), C.byref(obj),
+                          len(colors), _ip(offs), _ip(cv), len(fx), _ip(fx))
+
+    def finalize(self):
+        self._call("finalize")
+
+    def run_frames(self, n=1):
+        self._call("run_frames", n)
+
+    def run_iterations(self, n=1):
+        self._call("run_iterations", n)
+
+    @property
+    def frame_id(self):
+        return self._call("frame_id")
+
+    @property
+    def num_meshes(self):
+        return self._call("num_meshes")
+
+    def mesh_sizes(self, mesh):
+        v = [C.c_int32() for _ in range(4)]
+        self._call("mesh_sizes", mesh, *[C.byref(x) for x in v])
+        return tuple(x.value for x in v)
+
+    def _getv(self, name, mesh, n):
+        out = np.empty((n, 3), np.float32)
+        self._call(name, mesh, _fp(out))
+        return out
+
+    def positions(self, mesh):
+        return self._getv("get_positions", mesh, self.mesh_sizes(mesh)[0])
+
+    def prev_positions(self, mesh):
+        return self._getv("get_prev_positions", mesh, self.mesh_sizes(mesh)[0])
+
+    def velocities(self, mesh):
+        return self._getv("get_velocities", mesh, self.mesh_sizes(mesh)[0])
+
+    def inertia(self, mesh):
+        return self._getv("get_inertia", mesh, self.mesh_sizes(mesh)[0])
+
+    def surface_positions(self, mesh):
+        return self._getv("get_surface_positions", mesh, self.mesh_sizes(mesh)[2])
+
+    def set_state(self, mesh, pos=None, vel=None):
+        p = _f32(pos) if pos is not None else None
+        v = _f32(vel) if vel is not None else None
+        self._call("set_state", mesh, _fp(p) if p is not None else None, _fp(v) if v is not None else None)
+
+    def world_bounds(self):
+        mn = np.empty(3, np.float32); mx = np.empty(3, np.float32)
+        self._call("get_world_bounds", _fp(mn), _fp(mx))
+        return mn, mx
+
+    def parallel_groups(self):
+        out = []
+        for g in range(self._call("num_parallel_groups")):
+            n = C.c_int32()
+            self._call("get_parallel_group", g, None, C.byref(n))
+            a = np.empty(2 * n.value, np.int32)
+            self._call("get_parallel_group", g, _ip(a), C.byref(n))
+            out.append(a.reshape(-1, 2))
+        return out
+
+    def surface_vertex_ids(self, mesh):
+        a = np.empty(self.mesh_sizes(mesh)[2], np.int32)
+        self._call("get_surface_vertex_ids", mesh, _ip(a))
+        return a
+
+    def surface_faces(self, mesh):
+        a = np.empty((self.mesh_sizes(mesh)[3], 3), np.int32)
+        self._call("get_surface_faces", mesh, _ip(a))
+        return a
+
+    def vertex_masses(self, mesh):
+        a = np.empty(self.mesh_sizes(mesh)[0], np.float32)
+        self._call("get_vertex_masses", mesh, _fp(a))
+        return a
+
+    def detect_collisions(self, dcd=True, ccd=True):
+        self._call("detect_collisions", int(dcd), int(ccd))
+
+    def contacts(self):
+        n = C.c_int64()
+        self._call("get_contacts", None, 0, C.byref(n))
+        arr = np.zeros(max(n.value, 1), CONTACT_DTYPE)
+        self._call("get_contacts", arr.ctypes.data_as(C.POINTER(Contact)), n.value, C.byref(n))
+        return arr[: n.value]
+
+    def enable_mesh(self, mesh, collide=True, solve=True):
+        self._call("enable_mesh", mesh, int(collide), int(solve))
+
+    def stats(self):
+        s = Stats()
+        self._call("get_stats", C.byref(s))
+        return {n: getattr(s, n) for n, _ in Stats._fields_}
+
+    def reset_stats(self):
+        self._call("reset_stats")
+
+
+_lib = None
+
+
+def load_library(path=None):
+    """Load libgaia_b200.so; raises if the CUDA extension has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise GaiaError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.gaia_b200_abi_version.restype = C.c_int
+    lib.gaia_b200_last_error.restype = C.c_char_p
+    lib.gaia_b200_last_error.argtypes = [C.c_void_p]
+    lib.gaia_b200_create.argtypes = [C.POINTER(PhysicsParams), C.POINTER(CollisionParams), C.c_int, C.POINTER(C.c_void_p)]
+    lib.gaia_b200_create.restype = C.c_int
+    lib.gaia_b200_destroy.argtypes = [C.c_void_p]
+    lib.gaia_b200_destroy.restype = None
+    bind_scene_api(lib, "gaia_b200_")
+    P = C.c_void_p
+    FP, IP = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    lib.gaia_b200_synchronize.argtypes = [P]
+    lib.gaia_b200_total_vertices.argtypes = [P]; lib.gaia_b200_total_vertices.restype = C.c_int64
+    lib.gaia_b200_get_all_positions.argtypes = [P, FP]
+    lib.gaia_b200_set_all_state.argtypes = [P, FP, FP]
+    lib.gaia_b200_get_bvh_leaf_order.argtypes = [P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)]
+    lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
+    lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
+    for f in ("default_physics_params", "default_collision_params", "default_object_params"):
+        getattr(lib, "gaia_b200_" + f).restype = None
+    _lib = lib
+    return lib
+
+
+class Scene(SceneBase):
+    """A VBD scene on one B200 (mirror of VBDPhysics: initialize -> runStep loop)."""
+    _prefix = "gaia_b200_"
+
+    def __init__(self, phys=None, col=None, device=0):
+        self._lib = load_library()
+        phys = phys or default_physics_params(); col = col or default_collision_params()
+        h = C.c_void_p()
+        rc = self._lib.gaia_b200_create(C.byref(phys), C.byref(col), device, C.byref(h))
+        if rc < 0:
+            raise GaiaError(f"gaia_b200_create failed: {rc} {self._lib.gaia_b200_last_error(None).decode()}")
+        self.h = h
+
+    def last_error(self):
+        return self._lib.gaia_b200_last_error(self.h).decode()
+
+    def close(self):
+        if self.h is not None:
+            self._lib.gaia_b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self._call("synchronize")
+
+    @property
+    def total_vertices(self):
+        return self._lib.gaia_b200_total_vertices(self.h)
+
+    def all_positions(self, out=None):
+        if out is None:
+            out = np.empty((self.total_vertices, 3), np.float32)
+        self._call("get_all_positions", _fp(out))
+        return out
+
+    def set_all_state(self, pos, vel):
+        self._call("set_all_state", _fp(pos), _fp(vel))
+
+    def bvh_leaf_order(self, which):
+        n = C.c_int64()
+        self._call("get_bvh_leaf_order", which, None, 0, C.byref(n))
+        a = np.empty(n.value, np.int32)
+        self._call("get_bvh_leaf_order", which, _ip(a), n.value, C.byref(n))
+        return a
+
+    def set_profiling(self, on=True):
+        self._call("set_profiling", int(on))
+
+    @property
+    def cuda_stream(self):
+        return self._lib.gaia_b200_cuda_stream(self.h)

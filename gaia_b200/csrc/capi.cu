@@ -1,0 +1,305 @@
+// C ABI of libgaia_b200.so (include/gaia_b200.h): argument checking, error text, call ordering.
+// No CPU path exists behind these entry points: create() fails without a CUDA device.
+#include "scene_impl.h"
+#include <cmath>
+#include <cstring>
+#include <string>
+
+using namespace gb;
+
+struct gaia_handle { Scene s; };
+
+static thread_local std::string g_createErr;
+
+static int fail(Scene& s, int code, const std::string& msg) { s.err = msg; return code; }
+static int cuda_fail(Scene& s, cudaError_t e) { s.err = std::string("CUDA: ") + cudaGetErrorString(e); return GAIA_ERR_CUDA; }
+#define REQUIRE(h) if (!(h)) return GAIA_ERR_INVALID_ARG
+#define FINALIZED(h) if (!(h)->s.finalized) return fail((h)->s, GAIA_ERR_STATE, "scene not finalized")
+
+extern "C" {
+
+int gaia_b200_abi_version(void) { return GAIA_B200_ABI_VERSION; }
+const char* gaia_b200_last_error(const gaia_handle* h) { return h ? h->s.err.c_str() : g_createErr.c_str(); }
+
+void gaia_b200_default_physics_params(gaia_physics_params* p) {
+    std::memset(p, 0, sizeof(*p));
+    p->gravity[1] = -10.f; p->timeStep = 0.01666666666666666666f; p->numSubsteps = 20; p->iterations = 1;
+    p->usePlaneGround = 1;
+    for (int d = 0; d < 3; d++) { p->worldBoundsMin[d] = -1e7f; p->worldBoundsMax[d] = 1e7f; }
+    p->boundaryFrictionDynamic = 0.1f;
+    p->dcdTetMeshSceneBVHRebuildSteps = 16; p->dcdSurfaceSceneBVHRebuildSteps = 3; p->ccdBVHRebuildSteps = 7;
+    p->stepSize = 1.0f; p->stepSizeGD = 1e-3f; p->associateGravityWithInertia = 1;
+    p->collisionStiffness = 1e5f; p->intermediateCollisionIterations = -1;
+    p->boundaryCollisionStiffness = 1e5f; p->boundaryFrictionEpsV = 1.0f; p->frictionStartIter = 0;
+    p->useAccelerator = 0; p->acceleratorRho = 0.93f; p->collisionOffHeight = 1e7f;
+}
+void gaia_b200_default_collision_params(gaia_collision_params* c) {
+    std::memset(c, 0, sizeof(*c));
+    c->allowCCD = 1; c->allowDCD = 1; c->checkFeasibleRegion = 1; c->checkTetTraverse = 1; c->handleSelfCollision = 1;
+    c->stopTraversingAfterPassingQueryPoint = 1; c->tetrahedralTraverseForNonSelfIntersection = 1; c->useStaticTraverse = 1;
+    c->shiftQueryPointToCenter = 1; c->centerShiftLevel = 0.01f; c->maxNumberOfBVHQuery = 500;
+    c->feasibleRegionEpsilon = 1e-2f; c->rayTriIntersectionEPSILON = 1e-10f; c->maxSearchDistanceMultiplier = 1.8f;
+}
+void gaia_b200_default_object_params(gaia_object_params* o) {
+    std::memset(o, 0, sizeof(*o));
+    for (int d = 0; d < 3; d++) o->scale[d] = 1.f;
+    o->density = 1.f; o->maxVelocityMagnitude = -1.f; o->frameToAppear = -1;
+    o->frictionDynamic = 0.1f; o->frictionEpsV = 0.01f; o->exponentialVelDamping = 1.0f; o->initRatio_g = 0.5f;
+    o->miu = 1e4f; o->lmbd = 1e5f;
+}
+
+int gaia_b200_create(const gaia_physics_params* phys, const gaia_collision_params* col, int device, gaia_handle** out) {
+    if (!phys || !col || !out) { g_createErr = "null argument"; return GAIA_ERR_INVALID_ARG; }
+    *out = nullptr;
+    int nDev = 0;
+    cudaError_t e = cudaGetDeviceCount(&nDev);
+    if (e != cudaSuccess || nDev <= 0) {
+        g_createErr = std::string("no CUDA device available (") + cudaGetErrorString(e) + "); gaia_b200 has no CPU path";
+        return GAIA_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= nDev) { g_createErr = "device ordinal out of range"; return GAIA_ERR_INVALID_ARG; }
+    if (phys->useBowlGround) { g_createErr = "useBowlGround is outside the hot path (CPU-only feature of the reference)"; return GAIA_ERR_UNSUPPORTED; }
+    if (phys->numSubsteps <= 0 || phys->iterations < 0 || !(phys->timeStep > 0)) { g_createErr = "bad step parameters"; return GAIA_ERR_INVALID_ARG; }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_createErr = cudaGetErrorString(e); return GAIA_ERR_CUDA; }
+    gaia_handle* h = new gaia_handle();
+    Scene& s = h->s;
+    s.phys = *phys; s.col = *col; s.device = device;
+    s.dt = s.phys.timeStep / s.phys.numSubsteps;                 // BasePhysicFramework::timeStepEqualize
+    s.dtSqrReciprocal = 1.f / (s.dt * s.dt);
+    std::memset(&s.stats, 0, sizeof(s.stats));
+    *out = h;
+    return GAIA_OK;
+}
+
+void gaia_b200_destroy(gaia_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->s.device);
+    if (h->s.stream) cudaStreamSynchronize(h->s.stream);
+    delete h;
+}
+
+int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params* obj,
+                           int32_t nColors, const int32_t* color_offsets, const int32_t* color_verts, int32_t nFixed, const int32_t* fixedPoints) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (s.finalized) return fail(s, GAIA_ERR_STATE, "add_tet_mesh after finalize");
+    if (nV <= 0 || nT <= 0 || !xyz || !tets || !obj || nColors <= 0 || !color_offsets || !color_verts || nFixed < 0 || (nFixed && !fixedPoints))
+        return fail(s, GAIA_ERR_INVALID_ARG, "add_tet_mesh: bad argument");
+    if (s.meshes.size() >= (1u << 24) - 1) return fail(s, GAIA_ERR_INVALID_ARG, "too many meshes");
+    if (obj->initializationType == 5) return fail(s, GAIA_ERR_UNSUPPORTED, "initializationType 5 (symplectic Euler) is not on the hot path");
+    for (int64_t i = 0; i < 4 * (int64_t)nT; i++) if (tets[i] < 0 || tets[i] >= nV) return fail(s, GAIA_ERR_INVALID_ARG, "tet index out of range");
+    for (int i = 0; i < nFixed; i++) if (fixedPoints[i] < 0 || fixedPoints[i] >= nV) return fail(s, GAIA_ERR_INVALID_ARG, "fixed point out of range");
+    s.meshes.emplace_back();
+    HostMesh& m = s.meshes.back();
+    m.id = (int)s.meshes.size() - 1;
+    gaia_object_params o = *obj;
+    o.exponentialVelDamping = std::pow(o.exponentialVelDamping, s.dt);   // VBDPhysics::timeStepEqualize
+    o.constantVelDamping = o.constantVelDamping * s.dt;
+    host_mesh_init(m, nV, nT, xyz, tets, o, nColors, color_offsets, color_verts, nFixed, fixedPoints);
+    return m.id;
+}
+
+int gaia_b200_finalize(gaia_handle* h) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (s.finalized) return fail(s, GAIA_ERR_STATE, "already finalized");
+    if (s.meshes.empty()) return fail(s, GAIA_ERR_STATE, "no meshes");
+    cudaSetDevice(s.device);
+    if (!host_finalize(s)) return GAIA_ERR_INVALID_ARG;
+    cudaError_t e = device_upload(s);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    e = collision_init(s);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    s.finalized = true;
+    return GAIA_OK;
+}
+
+static void enable_models(Scene& s) {   // VBDPhysics::enableModels (VBDPhysics.cpp:685-709): frameToAppear <= frameId
+    for (auto& m : s.meshes)
+        if (m.obj.frameToAppear <= s.frameId && (!m.activeForCollision || !m.activeForMaterialSolve)) {
+            m.activeForCollision = true; m.activeForMaterialSolve = true; s.meshParamsDirty = true;
+        }
+}
+
+int gaia_b200_run_frames(gaia_handle* h, int32_t nFrames) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    cudaSetDevice(s.device);
+    for (int f = 0; f < nFrames; f++) {
+        enable_models(s);
+        cudaError_t e = run_substeps(s, s.phys.numSubsteps);
+        if (e != cudaSuccess) return cuda_fail(s, e);
+        ++s.frameId;
+    }
+    return GAIA_OK;
+}
+
+int gaia_b200_run_iterations(gaia_handle* h, int32_t nIters) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    cudaSetDevice(s.device);
+    enable_models(s);
+    cudaError_t e = run_iterations_only(s, nIters);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    return GAIA_OK;
+}
+
+int gaia_b200_synchronize(gaia_handle* h) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    cudaSetDevice(s.device);
+    cudaError_t e = cudaStreamSynchronize(s.stream);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    return check_device_errors(s);
+}
+int gaia_b200_frame_id(const gaia_handle* h) { return h ? h->s.frameId : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_num_meshes(const gaia_handle* h) { return h ? (int)h->s.meshes.size() : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_mesh_sizes(const gaia_handle* h, int mesh, int32_t* nV, int32_t* nT, int32_t* nSurfV, int32_t* nSurfF) {
+    REQUIRE(h);
+    if (mesh < 0 || mesh >= (int)h->s.meshes.size()) return GAIA_ERR_INVALID_ARG;
+    const HostMesh& m = h->s.meshes[mesh];
+    if (nV) *nV = m.nV; if (nT) *nT = m.nT; if (nSurfV) *nSurfV = m.nSurfV(); if (nSurfF) *nSurfF = m.nSurfF();
+    return GAIA_OK;
+}
+
+static int get_field(gaia_handle* h, int mesh, const float4* buf, float* xyz) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (mesh < 0 || mesh >= (int)s.meshes.size() || !xyz) return fail(s, GAIA_ERR_INVALID_ARG, "bad mesh id / null output");
+    cudaSetDevice(s.device);
+    cudaError_t e = gather_to_host(s, buf, s.meshes[mesh].vertBase, s.meshes[mesh].nV, xyz);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    return check_device_errors(s);
+}
+int gaia_b200_get_positions(gaia_handle* h, int mesh, float* xyz) { return get_field(h, mesh, h ? h->s.pos.p : nullptr, xyz); }
+int gaia_b200_get_prev_positions(gaia_handle* h, int mesh, float* xyz) { return get_field(h, mesh, h ? h->s.prev.p : nullptr, xyz); }
+int gaia_b200_get_velocities(gaia_handle* h, int mesh, float* xyz) { return get_field(h, mesh, h ? h->s.vel.p : nullptr, xyz); }
+int gaia_b200_get_inertia(gaia_handle* h, int mesh, float* xyz) { return get_field(h, mesh, h ? h->s.inertia.p : nullptr, xyz); }
+
+int gaia_b200_set_state(gaia_handle* h, int mesh, const float* pos, const float* vel) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (mesh < 0 || mesh >= (int)s.meshes.size()) return fail(s, GAIA_ERR_INVALID_ARG, "bad mesh id");
+    cudaSetDevice(s.device);
+    const HostMesh& m = s.meshes[mesh];
+    cudaError_t e;
+    if (pos && (e = scatter_from_host(s, s.pos.p, m.vertBase, m.nV, pos, false)) != cudaSuccess) return cuda_fail(s, e);
+    if (vel && (e = scatter_from_host(s, s.vel.p, m.vertBase, m.nV, vel, false)) != cudaSuccess) return cuda_fail(s, e);
+    return GAIA_OK;
+}
+
+int gaia_b200_get_surface_positions(gaia_handle* h, int mesh, float* xyz) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (mesh < 0 || mesh >= (int)s.meshes.size() || !xyz) return fail(s, GAIA_ERR_INVALID_ARG, "bad mesh id / null output");
+    const HostMesh& m = s.meshes[mesh];
+    std::vector<float> all(3 * (size_t)m.nV);
+    int rc = gaia_b200_get_positions(h, mesh, all.data());
+    if (rc < 0) return rc;
+    for (int i = 0; i < m.nSurfV(); i++) std::memcpy(xyz + 3 * (size_t)i, &all[3 * (size_t)m.surfaceVIds[i]], 12);
+    return GAIA_OK;
+}
+
+int64_t gaia_b200_total_vertices(const gaia_handle* h) { return h ? h->s.nVerts : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_get_all_positions(gaia_handle* h, float* xyz) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (!xyz) return fail(s, GAIA_ERR_INVALID_ARG, "null output");
+    cudaSetDevice(s.device);
+    cudaError_t e = gather_to_host(s, s.pos.p, 0, s.nVerts, xyz);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    return check_device_errors(s);
+}
+int gaia_b200_set_all_state(gaia_handle* h, const float* pos, const float* vel) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    cudaSetDevice(s.device);
+    cudaError_t e;
+    if (pos && (e = scatter_from_host(s, s.pos.p, 0, s.nVerts, pos, false)) != cudaSuccess) return cuda_fail(s, e);
+    if (vel && (e = scatter_from_host(s, s.vel.p, 0, s.nVerts, vel, false)) != cudaSuccess) return cuda_fail(s, e);
+    return GAIA_OK;
+}
+
+int gaia_b200_get_world_bounds(const gaia_handle* h, float* mn, float* mx) {
+    REQUIRE(h);
+    for (int d = 0; d < 3; d++) { mn[d] = h->s.phys.worldBoundsMin[d]; mx[d] = h->s.phys.worldBoundsMax[d]; }
+    return GAIA_OK;
+}
+int gaia_b200_num_parallel_groups(const gaia_handle* h) { return h ? (int)h->s.groups.size() : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_get_parallel_group(const gaia_handle* h, int group, int32_t* out, int32_t* nPairs) {
+    REQUIRE(h);
+    if (group < 0 || group >= (int)h->s.groups.size() || !nPairs) return GAIA_ERR_INVALID_ARG;
+    const auto& g = h->s.groups[group];
+    *nPairs = (int32_t)g.size() / 2;
+    if (out) std::memcpy(out, g.data(), g.size() * sizeof(int32_t));
+    return GAIA_OK;
+}
+#define MESH_ARRAY_GETTER(name, field, T)                                                  \
+    int name(const gaia_handle* h, int mesh, T* out) {                                     \
+        REQUIRE(h);                                                                        \
+        if (mesh < 0 || mesh >= (int)h->s.meshes.size() || !out) return GAIA_ERR_INVALID_ARG; \
+        const auto& v = h->s.meshes[mesh].field;                                           \
+        std::memcpy(out, v.data(), v.size() * sizeof(T));                                  \
+        return GAIA_OK;                                                                    \
+    }
+MESH_ARRAY_GETTER(gaia_b200_get_surface_vertex_ids, surfaceVIds, int32_t)
+MESH_ARRAY_GETTER(gaia_b200_get_surface_faces, surfFaces, int32_t)
+MESH_ARRAY_GETTER(gaia_b200_get_vertex_masses, mass, float)
+
+int gaia_b200_detect_collisions(gaia_handle* h, int doDCD, int doCCD) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    cudaSetDevice(s.device);
+    sync_mesh_params(s);
+    const gaia_collision_params saved = s.col;
+    s.col.allowDCD = saved.allowDCD && doDCD; s.col.allowCCD = saved.allowCCD && doCCD;
+    s.substep = 0;
+    cudaError_t e = collision_dcd(s, false);
+    if (e == cudaSuccess) e = collision_ccd(s);
+    if (e == cudaSuccess) e = collision_prepare(s);
+    s.col = saved;
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    return check_device_errors(s);
+}
+int gaia_b200_get_contacts(gaia_handle* h, gaia_contact* out, int64_t capacity, int64_t* n) {
+    REQUIRE(h); FINALIZED(h);
+    if (!n) return GAIA_ERR_INVALID_ARG;
+    cudaSetDevice(h->s.device);
+    *n = collision_fetch_contacts(h->s, out, capacity);
+    return *n < 0 ? GAIA_ERR_CUDA : GAIA_OK;
+}
+int gaia_b200_get_bvh_leaf_order(gaia_handle* h, int which, int32_t* out, int64_t capacity, int64_t* n) {
+    REQUIRE(h); FINALIZED(h);
+    if (!n) return GAIA_ERR_INVALID_ARG;
+    cudaSetDevice(h->s.device);
+    *n = collision_leaf_order(h->s, which, out, capacity);
+    return *n < 0 ? GAIA_ERR_INVALID_ARG : GAIA_OK;
+}
+
+int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int activeForMaterialSolve) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (mesh < 0 || mesh >= (int)s.meshes.size()) return fail(s, GAIA_ERR_INVALID_ARG, "bad mesh id");
+    s.meshes[mesh].activeForCollision = activeForCollision != 0;
+    s.meshes[mesh].activeForMaterialSolve = activeForMaterialSolve != 0;
+    s.meshParamsDirty = true;
+    return GAIA_OK;
+}
+
+int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out) {
+    REQUIRE(h);
+    if (!out) return GAIA_ERR_INVALID_ARG;
+    *out = h->s.stats;
+    if (h->s.profiling) out->timeCsmpMaterialSolve = h->s.solveKernelMs;
+    return GAIA_OK;
+}
+int gaia_b200_reset_stats(gaia_handle* h) {
+    REQUIRE(h);
+    std::memset(&h->s.stats, 0, sizeof(gaia_stats));
+    h->s.solveKernelMs = 0.0; h->s.solveKernelLaunches = 0;
+    return GAIA_OK;
+}
+int gaia_b200_set_profiling(gaia_handle* h, int enabled) { REQUIRE(h); h->s.profiling = enabled != 0; return GAIA_OK; }
+void* gaia_b200_cuda_stream(gaia_handle* h) { return h ? (void*)h->s.stream : nullptr; }
+
+}  // extern "C"

@@ -1,0 +1,308 @@
+// Host-side mesh preparation of libgaia_b200.so: everything VBDPhysics::initialize does before the first step,
+// re-derived for a colour-sorted SoA device layout.
+//   transform / rest volume / lumped mass      TetMeshFEM::initialize, M/TetMesh/TetMeshFEM.cpp:369-429
+//   surface vertex / face orderings            MeshFrame2 basetmesh.h:1881-1930, SurfaceMeshStatic.h:15-55,
+//                                              TriMesh/BaseMesh.h:1484-1530; TetMeshTopology::initialize TetMeshFEM.cpp:136-221
+//   colour sort + group merge                  TetMeshFEM.cpp:122-133, M/VBD/VBDPhysics.cpp:99-122, 236-274
+//   world box update                           BasePhysicFramework::updateWorldBox, BasePhysicsFramework.cpp:73-98
+#include "scene_impl.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+namespace gb {
+
+static const int kFaceOf[4][3] = {{1, 2, 3}, {2, 0, 3}, {0, 1, 3}, {1, 0, 2}};   // face i is opposite vertex i
+
+// ---- float helpers written to round exactly like the reference's Eigen expressions (no FMA: -ffp-contract=off)
+static void rodrigues(const float rot[3], float R[9] /*row-major*/) {
+    const float ang = std::sqrt(rot[0] * rot[0] + rot[1] * rot[1] + rot[2] * rot[2]);
+    const float ax[3] = {rot[0] / ang, rot[1] / ang, rot[2] / ang};
+    const float s = std::sin(ang), c = std::cos(ang);
+    const float sx = s * ax[0], sy = s * ax[1], sz = s * ax[2];
+    const float cx = (1.f - c) * ax[0], cy = (1.f - c) * ax[1], cz = (1.f - c) * ax[2];
+    float t;
+    t = cx * ax[1]; R[1] = t - sz; R[3] = t + sz;
+    t = cx * ax[2]; R[2] = t + sy; R[6] = t - sy;
+    t = cy * ax[2]; R[5] = t - sx; R[7] = t + sx;
+    R[0] = cx * ax[0] + c; R[4] = cy * ax[1] + c; R[8] = cz * ax[2] + c;
+}
+
+static inline float det3_cols(const float a[3], const float b[3], const float c[3]) {
+    // Eigen bruteforce_det3 on the matrix with columns a,b,c
+    auto h = [&](const float* p, const float* q, const float* r) { return p[0] * (q[1] * r[2] - r[1] * q[2]); };
+    return h(a, b, c) - h(b, a, c) + h(c, a, b);
+}
+
+static void surface_topology(HostMesh& m) {
+    const int nV = m.nV, nT = m.nT;
+    // bucket the 4*nT half-faces by their smallest vertex, then match duplicates inside each bucket
+    struct Half { int32_t lo, mid, hi, tet, face; };
+    std::vector<int32_t> bucketOff(nV + 1, 0);
+    std::vector<Half> halves(4 * (size_t)nT);
+    for (int t = 0; t < nT; t++)
+        for (int i = 0; i < 4; i++) {
+            int32_t k0 = m.tets[4 * t + kFaceOf[i][0]], k1 = m.tets[4 * t + kFaceOf[i][1]], k2 = m.tets[4 * t + kFaceOf[i][2]];
+            if (k0 > k1) std::swap(k0, k1);
+            if (k1 > k2) std::swap(k1, k2);
+            if (k0 > k1) std::swap(k0, k1);
+            halves[4 * (size_t)t + i] = {k0, k1, k2, t, i};
+            bucketOff[k0 + 1]++;
+        }
+    for (int v = 0; v < nV; v++) bucketOff[v + 1] += bucketOff[v];
+    std::vector<int32_t> slot(halves.size());
+    {
+        std::vector<int32_t> cur(bucketOff.begin(), bucketOff.end() - 1);
+        for (size_t q = 0; q < halves.size(); q++) slot[cur[halves[q].lo]++] = (int32_t)q;
+    }
+    m.tetNbrTets.assign(4 * (size_t)nT, -1);
+    for (int v = 0; v < nV; v++)
+        for (int x = bucketOff[v]; x < bucketOff[v + 1]; x++) {
+            const Half& A = halves[slot[x]];
+            if (m.tetNbrTets[4 * (size_t)A.tet + A.face] != -1) continue;
+            for (int y = x + 1; y < bucketOff[v + 1]; y++) {
+                const Half& B = halves[slot[y]];
+                if (A.mid == B.mid && A.hi == B.hi) {
+                    m.tetNbrTets[4 * (size_t)A.tet + A.face] = B.tet;
+                    m.tetNbrTets[4 * (size_t)B.tet + B.face] = A.tet;
+                    break;
+                }
+            }
+        }
+    // boundary half-faces in creation order; face vertices rotate to (p2,p0,p1) (trimesh createFace + FHEIterator)
+    std::vector<uint8_t> onSurface(nV, 0);
+    for (int t = 0; t < nT; t++)
+        for (int i = 0; i < 4; i++) {
+            if (m.tetNbrTets[4 * (size_t)t + i] != -1) continue;
+            const int32_t p0 = m.tets[4 * t + kFaceOf[i][0]], p1 = m.tets[4 * t + kFaceOf[i][1]], p2 = m.tets[4 * t + kFaceOf[i][2]];
+            m.surfFaces.insert(m.surfFaces.end(), {p2, p0, p1});
+            m.surfFaceTet.push_back(t);
+            m.surfFaceIdAtTet.push_back(i);
+            onSurface[p0] = onSurface[p1] = onSurface[p2] = 1;
+        }
+    m.tetVertToSurf.assign(nV, -1);
+    for (int v = 0; v < nV; v++)
+        if (onSurface[v]) { m.tetVertToSurf[v] = (int32_t)m.surfaceVIds.size(); m.surfaceVIds.push_back(v); }
+    const int nF = m.nSurfF();
+    // neighbour face across edge k = face that owns the opposite directed edge; sort packed directed edges
+    std::vector<std::pair<uint64_t, int32_t>> edges(3 * (size_t)nF);
+    for (int f = 0; f < nF; f++)
+        for (int k = 0; k < 3; k++) {
+            const uint64_t a = (uint32_t)m.surfFaces[3 * f + k], b = (uint32_t)m.surfFaces[3 * f + (k + 1) % 3];
+            edges[3 * (size_t)f + k] = {(a << 32) | b, f};
+        }
+    std::sort(edges.begin(), edges.end());
+    m.surfFace3Nbr.assign(3 * (size_t)nF, -1);
+    for (int f = 0; f < nF; f++)
+        for (int k = 0; k < 3; k++) {
+            const uint64_t a = (uint32_t)m.surfFaces[3 * f + k], b = (uint32_t)m.surfFaces[3 * f + (k + 1) % 3];
+            const uint64_t key = (b << 32) | a;
+            auto it = std::lower_bound(edges.begin(), edges.end(), std::make_pair(key, (int32_t)-1));
+            // several faces may own the same directed edge on non-manifold input: the last one created wins
+            // (BaseMesh.h:1497-1511 overwrites he_sym)
+            int32_t found = -1;
+            for (; it != edges.end() && it->first == key; ++it) found = it->second;
+            m.surfFace3Nbr[3 * f + k] = found;
+        }
+    // neighbour surface vertices per surface vertex (ascending ids), CSR
+    std::vector<std::vector<int32_t>> nb(m.nSurfV());
+    for (int f = 0; f < nF; f++)
+        for (int k = 0; k < 3; k++) {
+            auto& L = nb[m.tetVertToSurf[m.surfFaces[3 * f + k]]];
+            L.push_back(m.surfFaces[3 * f + (k + 1) % 3]);
+            L.push_back(m.surfFaces[3 * f + (k + 2) % 3]);
+        }
+    m.surfNbrOff.assign(m.nSurfV() + 1, 0);
+    for (int sv = 0; sv < m.nSurfV(); sv++) {
+        auto& L = nb[sv];
+        std::sort(L.begin(), L.end());
+        L.erase(std::unique(L.begin(), L.end()), L.end());
+        m.surfNbrOff[sv + 1] = m.surfNbrOff[sv] + (int32_t)L.size();
+        m.surfNbrVerts.insert(m.surfNbrVerts.end(), L.begin(), L.end());
+    }
+}
+
+void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
+                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed) {
+    m.nV = nV; m.nT = nT; m.obj = obj;
+    m.tets.assign(tets, tets + 4 * (size_t)nT);
+    m.pos0.assign(xyz, xyz + 3 * (size_t)nV);
+    const float rn2 = obj.rotation[0] * obj.rotation[0] + obj.rotation[1] * obj.rotation[1] + obj.rotation[2] * obj.rotation[2];
+    if (std::sqrt(rn2) > 0) {
+        float R[9];
+        rodrigues(obj.rotation, R);
+        for (int v = 0; v < nV; v++) {
+            float* p = &m.pos0[3 * (size_t)v];
+            const float x = p[0], y = p[1], z = p[2];
+            p[0] = R[0] * x + R[1] * y + R[2] * z;
+            p[1] = R[3] * x + R[4] * y + R[5] * z;
+            p[2] = R[6] * x + R[7] * y + R[8] * z;
+        }
+    }
+    for (int v = 0; v < nV; v++)
+        for (int d = 0; d < 3; d++) {
+            float& c = m.pos0[3 * (size_t)v + d];
+            c *= obj.scale[d];
+            c += obj.translation[d];
+        }
+    m.restVol.resize(nT);
+    m.mass.assign(nV, 0.f);
+    for (int t = 0; t < nT; t++) {
+        const float* x0 = &m.pos0[3 * (size_t)m.tets[4 * t]];
+        float e[3][3];
+        for (int c = 0; c < 3; c++) {
+            const float* xc = &m.pos0[3 * (size_t)m.tets[4 * t + c + 1]];
+            for (int d = 0; d < 3; d++) e[c][d] = xc[d] - x0[d];
+        }
+        const float vol = det3_cols(e[0], e[1], e[2]) / 6;
+        m.restVol[t] = vol;
+        for (int k = 0; k < 4; k++) {
+            float& mv = m.mass[m.tets[4 * t + k]];
+            mv = (float)((double)mv + 0.25 * (double)vol * (double)obj.density);
+        }
+    }
+    m.fixedMask.assign(nV, 0);
+    m.fixedPoints.assign(fixed, fixed + nFixed);
+    for (int i = 0; i < nFixed; i++) m.fixedMask[fixed[i]] = 1;
+    for (int c = 0; c < nColors; c++) m.colors.emplace_back(colorVerts + colorOffsets[c], colorVerts + colorOffsets[c + 1]);
+    // size-descending; ties keep file order (documented rule: stable sort)
+    std::stable_sort(m.colors.begin(), m.colors.end(),
+                     [](const std::vector<int32_t>& a, const std::vector<int32_t>& b) { return a.size() > b.size(); });
+    surface_topology(m);
+    if (obj.frameToAppear > 0) { m.activeForCollision = false; m.activeForMaterialSolve = false; }
+}
+
+// Merge per-mesh colours into global groups, assign sorted ids, build incidence streams. Returns false on bad input.
+bool host_finalize(Scene& s) {
+    auto& M = s.meshes;
+    if (s.phys.checkAndUpdateWorldBounds) {
+        for (auto& m : M)
+            for (int d = 0; d < 3; d++) {
+                if (!m.nV) continue;
+                float mn = m.pos0[d], mx = m.pos0[d];
+                for (int v = 1; v < m.nV; v++) { mn = std::min(mn, m.pos0[3 * (size_t)v + d]); mx = std::max(mx, m.pos0[3 * (size_t)v + d]); }
+                if (s.phys.worldBoundsMin[d] > mn) s.phys.worldBoundsMin[d] = mn;
+                if (s.phys.worldBoundsMax[d] < mx) s.phys.worldBoundsMax[d] = mx;
+            }
+    }
+    size_t nGroups = 0;
+    for (auto& m : M) nGroups = std::max(nGroups, m.colors.size());
+    s.groups.assign(nGroups, {});
+    for (size_t im = 0; im < M.size(); im++) {
+        HostMesh& m = M[im];
+        m.groupOfVertex.assign(m.nV, -1);
+        std::vector<int> free_(m.colors.size());
+        std::iota(free_.begin(), free_.end(), 0);
+        for (auto& colour : m.colors) {
+            size_t pick = 0;
+            for (size_t i = 1; i < free_.size(); i++)
+                if (s.groups[free_[i]].size() < s.groups[free_[pick]].size()) pick = i;   // first smallest
+            const int g = free_[pick];
+            free_.erase(free_.begin() + pick);
+            for (int32_t v : colour) {
+                if (v < 0 || v >= m.nV) { s.err = "colouring references a vertex out of range"; return false; }
+                if (m.groupOfVertex[v] != -1) { s.err = "vertex coloured twice"; return false; }
+                s.groups[g].push_back((int32_t)im); s.groups[g].push_back(v);
+                m.groupOfVertex[v] = g;
+            }
+        }
+        for (int v = 0; v < m.nV; v++)
+            if (m.groupOfVertex[v] == -1) { s.err = "vertex without a colour"; return false; }
+    }
+    // bases and sorted ids
+    int64_t vb = 0, tb = 0, svb = 0, sfb = 0;
+    for (auto& m : M) {
+        m.vertBase = vb; m.tetBase = tb; m.surfVBase = svb; m.surfFBase = sfb;
+        vb += m.nV; tb += m.nT; svb += m.nSurfV(); sfb += m.nSurfF();
+        m.sortedId.assign(m.nV, -1);
+    }
+    s.nVerts = vb; s.nTets = tb; s.nSurfVerts = svb; s.nSurfFaces = sfb;
+    if (vb >= (int64_t)1 << 31 || 4 * tb >= (int64_t)1 << 31) { s.err = "scene too large for 32-bit indices"; return false; }
+    s.groupStart.assign(nGroups + 1, 0);
+    s.sortedToOrig.resize(vb);
+    {
+        int32_t sid = 0;
+        for (size_t g = 0; g < nGroups; g++) {
+            s.groupStart[g] = sid;
+            const auto& G = s.groups[g];
+            for (size_t i = 0; i < G.size(); i += 2) {
+                HostMesh& m = M[G[i]];
+                m.sortedId[G[i + 1]] = sid;
+                s.sortedToOrig[sid] = (int32_t)(m.vertBase + G[i + 1]);
+                sid++;
+            }
+        }
+        s.groupStart[nGroups] = sid;
+    }
+    // incidence streams: per sorted vertex, incident tets in ascending tet id (MeshFrame2 order). Each record is the
+    // tet re-ordered by an EVEN permutation that puts the owning vertex first: (x, a, b, c).
+    static const int kEven[4][4] = {{0, 1, 2, 3}, {1, 0, 3, 2}, {2, 0, 1, 3}, {3, 0, 2, 1}};
+    s.h_incOff.assign(vb + 1, 0);
+    for (auto& m : M)
+        for (int t = 0; t < m.nT; t++)
+            for (int k = 0; k < 4; k++) s.h_incOff[m.sortedId[m.tets[4 * t + k]] + 1]++;
+    for (int64_t i = 0; i < vb; i++) s.h_incOff[i + 1] += s.h_incOff[i];
+    const int64_t nInc = s.h_incOff[vb];
+    s.nInc = nInc;
+    s.h_incA.resize(4 * (size_t)nInc);
+    s.h_incB.resize(4 * (size_t)nInc);
+    std::vector<int32_t> cursor(s.h_incOff.begin(), s.h_incOff.end() - 1);
+    for (auto& m : M) {
+        m.nSolved = 0; m.nIncSolved = 0;
+        for (int t = 0; t < m.nT; t++) {
+            const int32_t* tv = &m.tets[4 * (size_t)t];
+            for (int k = 0; k < 4; k++) {
+                const int32_t own = tv[kEven[k][0]], ia = tv[kEven[k][1]], ib = tv[kEven[k][2]], ic = tv[kEven[k][3]];
+                const float* X = &m.pos0[3 * (size_t)own];
+                const float* A = &m.pos0[3 * (size_t)ia];
+                const float* B = &m.pos0[3 * (size_t)ib];
+                const float* C = &m.pos0[3 * (size_t)ic];
+                // Dm' = [A-X, B-X, C-X]; B' = Dm'^-1; m0 = -B'^T 1; w = B' m0   (double, rounded once)
+                double D[3][3];
+                for (int d = 0; d < 3; d++) { D[d][0] = (double)A[d] - X[d]; D[d][1] = (double)B[d] - X[d]; D[d][2] = (double)C[d] - X[d]; }
+                const double det = D[0][0] * (D[1][1] * D[2][2] - D[1][2] * D[2][1]) - D[0][1] * (D[1][0] * D[2][2] - D[1][2] * D[2][0]) +
+                                   D[0][2] * (D[1][0] * D[2][1] - D[1][1] * D[2][0]);
+                double Bi[3][3];
+                Bi[0][0] = (D[1][1] * D[2][2] - D[1][2] * D[2][1]) / det; Bi[0][1] = (D[0][2] * D[2][1] - D[0][1] * D[2][2]) / det; Bi[0][2] = (D[0][1] * D[1][2] - D[0][2] * D[1][1]) / det;
+                Bi[1][0] = (D[1][2] * D[2][0] - D[1][0] * D[2][2]) / det; Bi[1][1] = (D[0][0] * D[2][2] - D[0][2] * D[2][0]) / det; Bi[1][2] = (D[0][2] * D[1][0] - D[0][0] * D[1][2]) / det;
+                Bi[2][0] = (D[1][0] * D[2][1] - D[1][1] * D[2][0]) / det; Bi[2][1] = (D[0][1] * D[2][0] - D[0][0] * D[2][1]) / det; Bi[2][2] = (D[0][0] * D[1][1] - D[0][1] * D[1][0]) / det;
+                double m0[3], w[3];
+                for (int c = 0; c < 3; c++) m0[c] = -(Bi[0][c] + Bi[1][c] + Bi[2][c]);
+                for (int r = 0; r < 3; r++) w[r] = Bi[r][0] * m0[0] + Bi[r][1] * m0[1] + Bi[r][2] * m0[2];
+                const double mm = m0[0] * m0[0] + m0[1] * m0[1] + m0[2] * m0[2];
+                const int32_t sOwn = m.sortedId[own];
+                const int32_t at = cursor[sOwn]++;
+                int32_t* ra = &s.h_incA[4 * (size_t)at];
+                ra[0] = m.sortedId[ia]; ra[1] = m.sortedId[ib]; ra[2] = m.sortedId[ic];
+                const float vol = m.restVol[t];
+                std::memcpy(&ra[3], &vol, 4);
+                float* rb = &s.h_incB[4 * (size_t)at];
+                rb[0] = (float)w[0]; rb[1] = (float)w[1]; rb[2] = (float)w[2]; rb[3] = (float)mm;
+            }
+        }
+        for (int v = 0; v < m.nV; v++)
+            if (!m.fixedMask[v]) {
+                m.nSolved++;
+                m.nIncSolved += s.h_incOff[m.sortedId[v] + 1] - s.h_incOff[m.sortedId[v]];
+            }
+        // |N(c)|: distinct neighbour vertices read by this mesh's part of each group
+        m.nbrDistinctPerGroup.assign(nGroups, 0);
+        std::vector<int32_t> stamp(m.nV, -1);
+        for (size_t g = 0; g < nGroups; g++) {
+            int64_t cnt = 0;
+            for (int t = 0; t < m.nT; t++) {
+                const int32_t* tv = &m.tets[4 * (size_t)t];
+                bool touches = false;
+                for (int k = 0; k < 4; k++) if (m.groupOfVertex[tv[k]] == (int)g && !m.fixedMask[tv[k]]) touches = true;
+                if (!touches) continue;
+                for (int q = 0; q < 4; q++)
+                    if (m.groupOfVertex[tv[q]] != (int)g && stamp[tv[q]] != (int)g) { stamp[tv[q]] = (int)g; cnt++; }
+            }
+            m.nbrDistinctPerGroup[g] = cnt;
+        }
+    }
+    return true;
+}
+
+}  // namespace gb

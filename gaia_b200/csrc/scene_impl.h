@@ -1,0 +1,110 @@
+// Scene object behind gaia_handle: host meshes + device buffers + stream/graph state.
+#pragma once
+#include "scene.h"
+#include <cstdio>
+#include <map>
+
+namespace gb {
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        free();
+        n = count;
+        if (!count) return cudaSuccess;
+        return cudaMalloc((void**)&p, count * sizeof(T));
+    }
+    void free() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    ~DevBuf() { free(); }
+};
+
+struct CollisionState;   // collision.cu
+
+// what the colour-solve kernel needs to see of the contact data (filled by collision.cu)
+struct ContactView {
+    const int32_t* contactOfVertex;   // sorted vertex -> contact slot or -1
+    const int32_t* relOff;            // CSR over sorted vertices: contacts on faces this vertex belongs to
+    const int2* rel;                  // (contact slot, vertex order 0..2)
+    const float4* cF;                 // force.xyz, penetrationDepth
+    const float4* cH0;                // h00,h01,h02,h11
+    const float4* cH1;                // h12,h22,bary0,bary1
+    const float* cB2;                 // bary2
+};
+
+struct Scene {
+    gaia_physics_params phys;
+    gaia_collision_params col;
+    float dt = 0.f, dtSqrReciprocal = 0.f;
+    int device = 0;
+    std::string err;
+    bool finalized = false;
+    int frameId = 0, substep = 0;
+
+    std::vector<HostMesh> meshes;
+    std::vector<std::vector<int32_t>> groups;   // [mesh,v,...] per merged parallel group
+    std::vector<int32_t> groupStart;            // sorted-id range of each group
+    std::vector<int32_t> sortedToOrig;          // sorted id -> global original index (vertBase + v)
+    int64_t nVerts = 0, nTets = 0, nSurfVerts = 0, nSurfFaces = 0, nInc = 0;
+    // host staging of the incidence streams (freed after upload)
+    std::vector<int32_t> h_incOff, h_incA;
+    std::vector<float> h_incB;
+
+    // ---- device state (sorted order)
+    cudaStream_t stream = nullptr;
+    DevBuf<float4> pos, prev, inertia, vel, velPrev, accel, accPrevPrev, accPrevIter;
+    DevBuf<float> mass;
+    DevBuf<int32_t> info;          // meshId | fixed<<31
+    DevBuf<int32_t> incOff;
+    DevBuf<int4> incA;
+    DevBuf<float4> incB;
+    DevBuf<int32_t> sorted2orig, orig2sorted;
+    DevBuf<MeshParamsDev> meshParams;
+    DevBuf<float4> ioStage;        // original-order staging for get/set
+    DevBuf<int32_t> meshSubsteps;  // substeps each mesh has taken (hasVelocitiesPrev / hasApproxAcceleration)
+    DevBuf<int32_t> errFlags;      // [0]=NaN count, [1]=solver-failed count, [2]=contact overflow, [3]=traversal overflow
+    std::vector<MeshParamsDev> h_meshParams;
+    bool meshParamsDirty = true;
+    StepParamsDev stepParams;
+    float* pinnedIO = nullptr;
+    size_t pinnedIOBytes = 0;
+
+    CollisionState* cs = nullptr;
+
+    // statistics / profiling
+    gaia_stats stats;
+    bool profiling = false;
+    cudaEvent_t evA = nullptr, evB = nullptr;
+    double solveKernelMs = 0.0;    // accumulated colour-solve kernel time while profiling
+    int64_t solveKernelLaunches = 0;
+
+    ~Scene();
+};
+
+// host_setup.cpp
+void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
+                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed);
+bool host_finalize(Scene& s);
+
+// solve.cu
+cudaError_t device_upload(Scene& s);
+void sync_mesh_params(Scene& s);
+cudaError_t run_substeps(Scene& s, int nSubsteps);                 // one frame's worth of substeps
+cudaError_t run_iterations_only(Scene& s, int nIters);
+cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin, int64_t count, float* outXYZ);
+cudaError_t scatter_from_host(Scene& s, float4* devSorted, int64_t origBegin, int64_t count, const float* inXYZ, bool keepW);
+int check_device_errors(Scene& s);
+
+// collision.cu
+cudaError_t collision_init(Scene& s);
+void collision_destroy(Scene& s);
+cudaError_t collision_dcd(Scene& s, bool intermediate);
+cudaError_t collision_ccd(Scene& s);
+cudaError_t collision_prepare(Scene& s);
+cudaError_t collision_update_infos(Scene& s, int group);          // per-colour contact force/Hessian pre-pass
+int64_t collision_fetch_contacts(Scene& s, gaia_contact* out, int64_t cap);
+int64_t collision_leaf_order(Scene& s, int which, int32_t* out, int64_t cap);
+bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask);
+
+}  // namespace gb

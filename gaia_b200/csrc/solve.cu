@@ -1,0 +1,602 @@
+// Per-colour VBD vertex solve and the elementwise passes around it, hand-written for sm_100a.
+//
+// Reference semantics (CPU/TBB path):
+//   applyInitialStep / computeInertia / forwardStep    M/VBD/VBD_BaseMaterial.h:201-259, VBD_BaseMaterial.cpp:7-132
+//   accumlateMaterialForceAndHessian2 (Neo-Hookean)    M/VBD/VBD_NeoHookean.cpp:379-581
+//   accumlateInertiaForceAndHessian                    M/VBD/VBD_BaseMaterial.h:359-366
+//   accumlateBoundaryForceAndHessian + friction        M/VBD/VBDPhysics.cpp:2821-2954, 2563-2592
+//   accumlateCollisionForceAndHessian[PerCollision]    M/VBD/VBDPhysics.cpp:2956-3047
+//   VBDStepWithCollision + solve3x3_psd_stable         M/VBD/VBDPhysics.cpp:2402-2483, 3P/CuMatrix/.../CuMatrix.h:235-267
+//   colour sweep loop                                  M/VBD/VBDPhysics.cpp:1659-1702
+//   updateVelocities / dampVelocities                  M/VBD/VBDPhysics.cpp:2486-2561
+//   Chebyshev accelerator (GPU-path feature)           M/VBD/VBDPhysics.cpp:3558-3574, VBDPhysicsCompute.cu:910-944
+//
+// Kernel design: the work is a sparse gather bounded by HBM, not a contraction — no tensor cores.
+//   * vertices are colour-sorted, so a colour is one contiguous range [vBegin,vEnd) of every SoA array;
+//   * each vertex is owned by a sub-warp of L lanes; lane l streams the incidence records l, l+L, ... of the vertex
+//     (two coalesced 16-byte loads per record), gathers the three neighbour positions (16-byte loads that hit L2:
+//     the position array of a 10M-tet mesh is 28 MB against 126 MB of L2) and accumulates the closed-form
+//     Neo-Hookean force / Hessian of SURVEY.md §8(a) "math restatement" (≈100 flop instead of the 9x9 contraction);
+//   * a butterfly shuffle reduces 10 partial sums; lane 0 adds inertia, boundary and contact terms, solves the 3x3
+//     block and writes the new position in place (safe: a colour only reads other colours' positions).
+#include "scene_impl.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace gb {
+
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
+
+static const int kBlock = 256;
+
+__device__ __forceinline__ float3 f3(float4 v) { return make_float3(v.x, v.y, v.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return make_float3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ float3 operator+(float3 a, float3 b) { return make_float3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float3 operator*(float s, float3 a) { return make_float3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float3 cross3(float3 a, float3 b) {
+    return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+// streaming (read-once) loads: keep them out of L1 so the gathered positions stay cached
+__device__ __forceinline__ int4 ld_stream(const int4* p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float4 ld_stream(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+// IPC-style mollified friction (computeVertexFriction, VBDPhysics.cpp:2563-2592) for an axis-aligned tangent basis
+// T = [e_a, e_b]: adds force and the diagonal Hessian entries (a,a) and (b,b).
+__device__ __forceinline__ void boundary_friction(float mu, float lambda, float ua, float ub, float epsU, float& fa, float& fb, float& haa) {
+    const float uNorm = sqrtf(ua * ua + ub * ub);
+    fa = 0.f; fb = 0.f; haa = 0.f;
+    if (uNorm > 0.f) {
+        const float f1 = (uNorm > epsU) ? 1.f / uNorm : (-uNorm / epsU + 2.f) / epsU;
+        const float s = -mu * lambda * f1;
+        fa = s * ua; fb = s * ub;
+        haa = mu * lambda * f1;
+    }
+}
+
+template <int L, bool HAS_CONTACTS>
+__global__ void __launch_bounds__(kBlock)
+k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
+               const float* __restrict__ mass, const int32_t* __restrict__ info, const int32_t* __restrict__ incOff,
+               const int4* __restrict__ incA, const float4* __restrict__ incB, const MeshParamsDev* __restrict__ mp,
+               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags) {
+    const int tid = blockIdx.x * kBlock + threadIdx.x;
+    const int lane = tid & (L - 1);
+    const int s = vBegin + tid / L;
+    const bool inRange = s < vEnd;
+    int inf = inRange ? __ldg(info + s) : (int)0x80000000;
+    const bool fixed = inf < 0;
+    const int meshId = inf & 0x00FFFFFF;
+    float miu = 0.f, lmbd = 0.f, aConst = 0.f, dampH = 0.f, dampD = 0.f;
+    bool active = inRange && !fixed;
+    if (active) {
+        const MeshParamsDev* P = mp + meshId;
+        active = P->activeSolve != 0;
+        miu = P->miu; lmbd = P->lmbd; aConst = P->a; dampH = P->dampH; dampD = P->dampD;
+    }
+    const float4* posRO = pos;   // neighbour gathers only touch other colours: read-only for this launch
+    float fx = 0.f, fy = 0.f, fz = 0.f, s1 = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
+    float3 x = make_float3(0.f, 0.f, 0.f);
+    if (active) {
+        x = f3(pos[s]);
+        const int b = __ldg(incOff + s), e = __ldg(incOff + s + 1);
+        for (int j = b + lane; j < e; j += L) {
+            const int4 ia = ld_stream(incA + j);
+            const float4 wb = ld_stream(incB + j);
+            const float3 pa = f3(__ldg(posRO + ia.x)) - x;
+            const float3 pb = f3(__ldg(posRO + ia.y)) - x;
+            const float3 pc = f3(__ldg(posRO + ia.z)) - x;
+            const float A = __int_as_float(ia.w);
+            const float3 bc = cross3(pb, pc);
+            const float3 n = bc + cross3(pc, pa) + cross3(pa, pb);     // cof(Ds') * (1,1,1)
+            const float detB = 1.f / (6.f * A);
+            const float detF = dot3(pa, bc) * detB;
+            const float3 g = (-detB) * n;                              // cof(F) m_0
+            const float3 Fw = wb.x * pa + wb.y * pb + wb.z * pc;       // F m_0 = Ds' (B'B'^T e_0')
+            const float lk = lmbd * (detF - aConst);
+            fx += A * (miu * Fw.x + lk * g.x);
+            fy += A * (miu * Fw.y + lk * g.y);
+            fz += A * (miu * Fw.z + lk * g.z);
+            s1 += A * wb.w;
+            g00 += A * g.x * g.x; g01 += A * g.x * g.y; g02 += A * g.x * g.z;
+            g11 += A * g.y * g.y; g12 += A * g.y * g.z; g22 += A * g.z * g.z;
+        }
+    }
+#pragma unroll
+    for (int o = L / 2; o > 0; o >>= 1) {
+        fx += __shfl_xor_sync(0xffffffffu, fx, o); fy += __shfl_xor_sync(0xffffffffu, fy, o); fz += __shfl_xor_sync(0xffffffffu, fz, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        g00 += __shfl_xor_sync(0xffffffffu, g00, o); g01 += __shfl_xor_sync(0xffffffffu, g01, o); g02 += __shfl_xor_sync(0xffffffffu, g02, o);
+        g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
+    }
+    if (!active || lane != 0) return;
+
+    // elastic force and Hessian: f = -(mu*fmu + lmbd*flm), H = mu*s1*I + lmbd*G
+    float F0 = -fx, F1 = -fy, F2 = -fz;
+    float hd = miu * s1;
+    float h00 = lmbd * g00 + hd, h01 = lmbd * g01, h02 = lmbd * g02, h11 = lmbd * g11 + hd, h12 = lmbd * g12, h22 = lmbd * g22 + hd;
+    const bool needPrev = (dampH != 0.f) | (dampD != 0.f);
+    float3 xp = make_float3(0.f, 0.f, 0.f);
+    bool havePrev = false;
+    if (needPrev) {
+        xp = f3(__ldg(prev + s)); havePrev = true;
+        // dampingH = (H_vol*gamma_h + mu*|m|^2*A*gamma_d I)/dt ; f -= dampingH*(x - x_prev); H += dampingH
+        const float idt = 1.f / sp.dt;
+        const float3 d = x - xp;
+        const float ch = lmbd * dampH * idt, cd = miu * s1 * dampD * idt;
+        const float d00 = ch * g00 + cd, d01 = ch * g01, d02 = ch * g02, d11 = ch * g11 + cd, d12 = ch * g12, d22 = ch * g22 + cd;
+        F0 -= d00 * d.x + d01 * d.y + d02 * d.z;
+        F1 -= d01 * d.x + d11 * d.y + d12 * d.z;
+        F2 -= d02 * d.x + d12 * d.y + d22 * d.z;
+        h00 += d00; h01 += d01; h02 += d02; h11 += d11; h12 += d12; h22 += d22;
+    }
+    // inertia
+    {
+        const float m = __ldg(mass + s);
+        const float3 y = f3(__ldg(inertia + s));
+        const float w = m * sp.dtSqrReciprocal;
+        F0 += (m * (y.x - x.x)) * sp.dtSqrReciprocal;
+        F1 += (m * (y.y - x.y)) * sp.dtSqrReciprocal;
+        F2 += (m * (y.z - x.z)) * sp.dtSqrReciprocal;
+        h00 += w; h11 += w; h22 += w;
+    }
+    // world-box penalty + friction, per violated axis (CPU semantics)
+    if (sp.usePlaneGround) {
+        const float xs[3] = {x.x, x.y, x.z};
+        float Fb[3] = {0.f, 0.f, 0.f}, Hb[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            float depth = 0.f, sgn = 0.f;
+            if (xs[d] < sp.boundsMin[d]) { depth = sp.boundsMin[d] - xs[d]; sgn = 1.f; }
+            else if (xs[d] > sp.boundsMax[d]) { depth = xs[d] - sp.boundsMax[d]; sgn = -1.f; }
+            if (sgn != 0.f) {
+                Fb[d] += sgn * (depth * sp.kBoundary);
+                Hb[d] += sp.kBoundary;
+                if (applyFriction) {
+                    if (!havePrev) { xp = f3(__ldg(prev + s)); havePrev = true; }
+                    const float dx[3] = {x.x - xp.x, x.y - xp.y, x.z - xp.z};
+                    const int a = (d + 1) % 3, b2 = (d + 2) % 3;
+                    float fa, fb, haa;
+                    boundary_friction(sp.muBoundary, depth * sp.kBoundary, dx[a], dx[b2], sp.epsVBoundary * sp.dt, fa, fb, haa);
+                    Fb[a] += fa; Fb[b2] += fb; Hb[a] += haa; Hb[b2] += haa;
+                }
+            }
+        }
+        F0 += Fb[0]; F1 += Fb[1]; F2 += Fb[2];
+        h00 += Hb[0]; h11 += Hb[1]; h22 += Hb[2];
+    }
+    // vertex-face contacts: own contact with weight 1, contacts on faces this vertex belongs to with weight -bary
+    if (HAS_CONTACTS) {
+        const int own = __ldg(cv.contactOfVertex + s);
+        const int rb = __ldg(cv.relOff + s), re = __ldg(cv.relOff + s + 1);
+        for (int q = (own >= 0 ? -1 : 0); q < re - rb; q++) {
+            int slot; float bw;
+            if (q < 0) { slot = own; bw = 1.f; }
+            else {
+                const int2 r = __ldg(cv.rel + rb + q);
+                slot = r.x;
+                const float4 h1 = __ldg(cv.cH1 + slot);
+                bw = -(r.y == 0 ? h1.z : (r.y == 1 ? h1.w : __ldg(cv.cB2 + slot)));
+            }
+            const float4 cf = __ldg(cv.cF + slot);
+            if (cf.w > 0.f && bw != 0.f) {
+                const float4 c0 = __ldg(cv.cH0 + slot), c1 = __ldg(cv.cH1 + slot);
+                const float b2w = bw * bw;
+                F0 += cf.x * bw; F1 += cf.y * bw; F2 += cf.z * bw;
+                h00 += c0.x * b2w; h01 += c0.y * b2w; h02 += c0.z * b2w; h11 += c0.w * b2w; h12 += c1.x * b2w; h22 += c1.y * b2w;
+            }
+        }
+    }
+    // 3x3 solve (solve3x3_psd_stable) and in-place update
+    if (F0 * F0 + F1 * F1 + F2 * F2 > 1e-10f) {
+        const float i11 = h22 * h11 - h12 * h12;
+        const float i12 = -(h22 * h01 - h12 * h02);
+        const float i13 = h12 * h01 - h11 * h02;
+        const float det = h00 * i11 + h01 * i12 + h02 * i13;
+        float dx0, dx1, dx2, step;
+        if (fabsf(det) < 1e-5f * (fabsf(h00 * i11) + fabsf(h01 * i12) + fabsf(h02 * i13))) {
+            dx0 = F0; dx1 = F1; dx2 = F2; step = sp.stepSizeGD;
+            atomicAdd(errFlags + 1, 1);
+        } else {
+            const float deti = 1.f / det;
+            const float i22 = h22 * h00 - h02 * h02;
+            const float i23 = -(h12 * h00 - h01 * h02);
+            const float i33 = h11 * h00 - h01 * h01;
+            dx0 = deti * (i11 * F0 + i12 * F1 + i13 * F2);
+            dx1 = deti * (i12 * F0 + i22 * F1 + i23 * F2);
+            dx2 = deti * (i13 * F0 + i23 * F1 + i33 * F2);
+            step = sp.stepSize;
+        }
+        if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return; }
+        pos[s] = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
+    }
+}
+
+// applyInitialStep for every vertex of every active mesh (one launch)
+__global__ void __launch_bounds__(kBlock)
+k_initial_step(int n, float4* __restrict__ pos, float4* __restrict__ prev, float4* __restrict__ inertia, const float4* __restrict__ vel,
+               float4* __restrict__ velPrev, float4* __restrict__ accel, const int32_t* __restrict__ info,
+               const MeshParamsDev* __restrict__ mp, const int32_t* __restrict__ meshSubsteps, StepParamsDev sp) {
+    const int s = blockIdx.x * kBlock + threadIdx.x;
+    if (s >= n) return;
+    const int inf = __ldg(info + s);
+    const int meshId = inf & 0x00FFFFFF;
+    const MeshParamsDev P = mp[meshId];
+    if (!P.activeSolve) return;
+    const int nDone = __ldg(meshSubsteps + meshId);      // substeps this mesh has already taken
+    const float3 x = f3(pos[s]);
+    float3 v = f3(__ldg(vel + s));
+    const float dt = sp.dt;
+    prev[s] = make_float4(x.x, x.y, x.z, 0.f);
+    const int type = P.initType;
+    float3 vp = make_float3(0.f, 0.f, 0.f), acc = make_float3(0.f, 0.f, 0.f);
+    if (type == 2 || type == 4 || type == 6) {
+        // velocitiesPrev() = velocities() BEFORE gravity is added: it is the velocity the last substep ended with
+        if (type == 6 && nDone >= 1) {
+            const float3 old = f3(velPrev[s]);
+            acc = make_float3((v.x - old.x) / dt, (v.y - old.y) / dt, (v.z - old.z) / dt);
+            accel[s] = make_float4(acc.x, acc.y, acc.z, 0.f);
+        }
+        velPrev[s] = make_float4(v.x, v.y, v.z, 0.f);
+        vp = v;
+    }
+    // explicit _rn intrinsics: no FMA contraction, so y is bit-identical to the reference's separate multiply and add
+    if (sp.associateGravityWithInertia) {
+        v.x = __fadd_rn(v.x, __fmul_rn(dt, sp.gravity[0])); v.y = __fadd_rn(v.y, __fmul_rn(dt, sp.gravity[1])); v.z = __fadd_rn(v.z, __fmul_rn(dt, sp.gravity[2]));
+    }
+    if (inf < 0) v = make_float3(0.f, 0.f, 0.f);
+    const float3 y = make_float3(__fadd_rn(x.x, __fmul_rn(dt, v.x)), __fadd_rn(x.y, __fmul_rn(dt, v.y)), __fadd_rn(x.z, __fmul_rn(dt, v.z)));
+    inertia[s] = make_float4(y.x, y.y, y.z, 0.f);
+    float3 xn = x;
+    switch (type) {
+        case 0: xn = y; break;
+        case 2: xn = make_float3(__fadd_rn(x.x, __fmul_rn(dt, vp.x)), __fadd_rn(x.y, __fmul_rn(dt, vp.y)), __fadd_rn(x.z, __fmul_rn(dt, vp.z))); break;
+        case 3: xn = make_float3(__fadd_rn(__fmul_rn(0.5f, x.x), __fmul_rn(0.5f, y.x)), __fadd_rn(__fmul_rn(0.5f, x.y), __fmul_rn(0.5f, y.y)),
+                                 __fadd_rn(__fmul_rn(0.5f, x.z), __fmul_rn(0.5f, y.z))); break;
+        case 4: {
+            const float c = __fmul_rn(__fmul_rn(dt, dt), P.initRatio_g);
+            xn = make_float3(__fadd_rn(__fadd_rn(x.x, __fmul_rn(dt, vp.x)), __fmul_rn(c, sp.gravity[0])),
+                             __fadd_rn(__fadd_rn(x.y, __fmul_rn(dt, vp.y)), __fmul_rn(c, sp.gravity[1])),
+                             __fadd_rn(__fadd_rn(x.z, __fmul_rn(dt, vp.z)), __fmul_rn(c, sp.gravity[2])));
+        } break;
+        case 6:
+            if (nDone >= 1) {
+                const float gn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(sp.gravity[0], sp.gravity[0]), __fmul_rn(sp.gravity[1], sp.gravity[1])),
+                                                      __fmul_rn(sp.gravity[2], sp.gravity[2])));
+                const float3 gd = make_float3(sp.gravity[0] / gn, sp.gravity[1] / gn, sp.gravity[2] / gn);
+                float ac = __fadd_rn(__fadd_rn(__fmul_rn(acc.x, gd.x), __fmul_rn(acc.y, gd.y)), __fmul_rn(acc.z, gd.z));
+                ac = ac < gn ? ac : gn;
+                ac = ac > 1e-5f ? ac : 0.f;
+                const float c = __fmul_rn(dt, dt);
+                xn = make_float3(__fadd_rn(__fadd_rn(x.x, __fmul_rn(dt, vp.x)), __fmul_rn(__fmul_rn(c, gd.x), ac)),
+                                 __fadd_rn(__fadd_rn(x.y, __fmul_rn(dt, vp.y)), __fmul_rn(__fmul_rn(c, gd.y), ac)),
+                                 __fadd_rn(__fadd_rn(x.z, __fmul_rn(dt, vp.z)), __fmul_rn(__fmul_rn(c, gd.z), ac)));
+            }
+            break;
+        default: break;
+    }
+    if (type != 1) pos[s] = make_float4(xn.x, xn.y, xn.z, 0.f);
+}
+
+__global__ void k_count_substeps(int nMeshes, const MeshParamsDev* __restrict__ mp, int32_t* meshSubsteps) {
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < nMeshes && mp[m].activeSolve) meshSubsteps[m] += 1;
+}
+
+// updateVelocities + dampVelocities
+__global__ void __launch_bounds__(kBlock)
+k_update_velocity(int n, const float4* __restrict__ pos, const float4* __restrict__ prev, float4* __restrict__ vel,
+                  const int32_t* __restrict__ info, const MeshParamsDev* __restrict__ mp, StepParamsDev sp) {
+    const int s = blockIdx.x * kBlock + threadIdx.x;
+    if (s >= n) return;
+    const int inf = __ldg(info + s);
+    const MeshParamsDev* P = mp + (inf & 0x00FFFFFF);
+    if (!P->activeSolve) return;
+    const float3 x = f3(__ldg(pos + s)), xp = f3(__ldg(prev + s));
+    float3 v = make_float3((x.x - xp.x) / sp.dt, (x.y - xp.y) / sp.dt, (x.z - xp.z) / sp.dt);
+    const float vMag = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y)), __fmul_rn(v.z, v.z)));
+    const float maxV = P->maxVel;
+    if (P->hasNoGravZone && maxV > 0.f && x.y > P->noGravThreshold) {
+        if (vMag > maxV) { const float r = maxV / vMag; v = r * v; }
+    } else if (vMag > 1e-6f) {
+        float vNew = __fsub_rn(__fmul_rn(vMag, P->expVelDamp), P->constVelDamp);
+        vNew = vNew > 1e-6f ? vNew : 0.f;
+        const float r = vNew / vMag;
+        v = r * v;
+    } else {
+        v = make_float3(0.f, 0.f, 0.f);
+    }
+    if (inf < 0) v = make_float3(0.f, 0.f, 0.f);
+    vel[s] = make_float4(v.x, v.y, v.z, 0.f);
+}
+
+// Chebyshev: x <- x_{k-2} + omega (x - x_{k-2}) for non-colliding vertices; shift the history
+__global__ void __launch_bounds__(kBlock)
+k_accelerate(int n, float4* __restrict__ pos, float4* __restrict__ pp, float4* __restrict__ pIter, const int32_t* __restrict__ info,
+             const MeshParamsDev* __restrict__ mp, const uint8_t* __restrict__ colliding, float omega, int init) {
+    const int s = blockIdx.x * kBlock + threadIdx.x;
+    if (s >= n) return;
+    const int inf = __ldg(info + s);
+    if (inf < 0 || !mp[inf & 0x00FFFFFF].activeSolve) return;
+    float4 x = pos[s];
+    if (init) { pp[s] = x; pIter[s] = x; return; }
+    const float4 a = pp[s];
+    if (!(colliding && colliding[s])) {
+        x = make_float4(a.x + omega * (x.x - a.x), a.y + omega * (x.y - a.y), a.z + omega * (x.z - a.z), 0.f);
+        pos[s] = x;
+    }
+    pp[s] = pIter[s];
+    pIter[s] = x;
+}
+
+// sorted <-> original order transfers (xyz packed on the original side)
+__global__ void k_gather_xyz(int64_t count, int64_t origBegin, const float4* __restrict__ src, const int32_t* __restrict__ o2s, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float4 v = src[o2s[origBegin + i]];
+    out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+}
+__global__ void k_scatter_xyz(int64_t count, int64_t origBegin, float4* __restrict__ dst, const int32_t* __restrict__ o2s, const float* __restrict__ in) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    dst[o2s[origBegin + i]] = make_float4(in[3 * i], in[3 * i + 1], in[3 * i + 2], 0.f);
+}
+
+static inline int nblk(int64_t n, int per = kBlock) { return (int)((n + per - 1) / per); }
+
+Scene::~Scene() {
+    collision_destroy(*this);
+    if (pinnedIO) cudaFreeHost(pinnedIO);
+    if (evA) cudaEventDestroy(evA);
+    if (evB) cudaEventDestroy(evB);
+    if (stream) cudaStreamDestroy(stream);
+}
+
+static MeshParamsDev make_mesh_params(const HostMesh& m) {
+    MeshParamsDev p;
+    std::memset(&p, 0, sizeof(p));
+    p.miu = m.obj.miu; p.lmbd = m.obj.lmbd; p.a = 1 + m.obj.miu / m.obj.lmbd;
+    p.dampH = m.obj.dampingHydrostatic; p.dampD = m.obj.dampingDeviatoric;
+    p.frictionDynamic = m.obj.frictionDynamic; p.frictionEpsV = m.obj.frictionEpsV;
+    p.expVelDamp = m.obj.exponentialVelDamping; p.constVelDamp = m.obj.constantVelDamping;
+    p.maxVel = m.obj.maxVelocityMagnitude; p.noGravThreshold = m.obj.noGravZoneThreshold;
+    p.hasNoGravZone = m.obj.hasNoGravZone; p.initType = m.obj.initializationType; p.initRatio_g = m.obj.initRatio_g;
+    p.activeSolve = m.activeForMaterialSolve; p.activeCollide = m.activeForCollision;
+    p.vertBase = (int32_t)m.vertBase; p.tetBase = (int32_t)m.tetBase; p.surfVBase = (int32_t)m.surfVBase; p.surfFBase = (int32_t)m.surfFBase;
+    return p;
+}
+
+void sync_mesh_params(Scene& s) {
+    if (!s.meshParamsDirty) return;
+    s.h_meshParams.resize(s.meshes.size());
+    for (size_t i = 0; i < s.meshes.size(); i++) s.h_meshParams[i] = make_mesh_params(s.meshes[i]);
+    cudaMemcpyAsync(s.meshParams.p, s.h_meshParams.data(), s.h_meshParams.size() * sizeof(MeshParamsDev), cudaMemcpyHostToDevice, s.stream);
+    cudaStreamSynchronize(s.stream);
+    s.meshParamsDirty = false;
+}
+
+cudaError_t device_upload(Scene& s) {
+    const int64_t N = s.nVerts;
+    CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&s.evA)); CK(cudaEventCreate(&s.evB));
+    CK(s.pos.alloc(N + 1)); CK(s.prev.alloc(N + 1)); CK(s.inertia.alloc(N + 1)); CK(s.vel.alloc(N + 1));
+    CK(s.mass.alloc(N)); CK(s.info.alloc(N)); CK(s.incOff.alloc(N + 1));
+    CK(s.incA.alloc(s.nInc)); CK(s.incB.alloc(s.nInc));
+    CK(s.sorted2orig.alloc(N)); CK(s.orig2sorted.alloc(N));
+    CK(s.meshParams.alloc(s.meshes.size())); CK(s.errFlags.alloc(8));
+    CK(s.ioStage.alloc((size_t)(3 * N + 3) / 4 + 1));
+    bool needVelPrev = false, needAccel = false;
+    for (auto& m : s.meshes) {
+        const int t = m.obj.initializationType;
+        if (t == 2 || t == 4 || t == 6) needVelPrev = true;
+        if (t == 6) needAccel = true;
+    }
+    if (needVelPrev) CK(s.velPrev.alloc(N + 1));
+    if (needAccel) CK(s.accel.alloc(N + 1));
+    if (s.phys.useAccelerator) { CK(s.accPrevPrev.alloc(N + 1)); CK(s.accPrevIter.alloc(N + 1)); }
+    CK(cudaMemsetAsync(s.errFlags.p, 0, 8 * sizeof(int32_t), s.stream));
+    CK(s.meshSubsteps.alloc(s.meshes.size()));
+    CK(cudaMemsetAsync(s.meshSubsteps.p, 0, s.meshes.size() * sizeof(int32_t), s.stream));
+    // host images in sorted order
+    std::vector<float4> hpos(N + 1), hvel(N + 1);
+    std::vector<float> hmass(N);
+    std::vector<int32_t> hinfo(N), o2s(N);
+    for (auto& m : s.meshes)
+        for (int v = 0; v < m.nV; v++) {
+            const int32_t sid = m.sortedId[v];
+            hpos[sid] = make_float4(m.pos0[3 * (size_t)v], m.pos0[3 * (size_t)v + 1], m.pos0[3 * (size_t)v + 2], 0.f);
+            hvel[sid] = make_float4(m.obj.initialVelocity[0], m.obj.initialVelocity[1], m.obj.initialVelocity[2], 0.f);
+            hmass[sid] = m.mass[v];
+            hinfo[sid] = (m.id & 0x00FFFFFF) | (m.fixedMask[v] ? (int32_t)0x80000000 : 0);
+            o2s[m.vertBase + v] = sid;
+        }
+    hpos[N] = make_float4(0, 0, 0, 0); hvel[N] = hpos[N];
+    CK(cudaMemcpyAsync(s.pos.p, hpos.data(), (N + 1) * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemsetAsync(s.prev.p, 0, (N + 1) * sizeof(float4), s.stream));
+    CK(cudaMemsetAsync(s.inertia.p, 0, (N + 1) * sizeof(float4), s.stream));
+    CK(cudaMemcpyAsync(s.vel.p, hvel.data(), (N + 1) * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    if (needVelPrev) CK(cudaMemcpyAsync(s.velPrev.p, hvel.data(), (N + 1) * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    if (needAccel) CK(cudaMemsetAsync(s.accel.p, 0, (N + 1) * sizeof(float4), s.stream));
+    CK(cudaMemcpyAsync(s.mass.p, hmass.data(), N * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.info.p, hinfo.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.incOff.p, s.h_incOff.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.incA.p, s.h_incA.data(), s.nInc * sizeof(int4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.incB.p, s.h_incB.data(), s.nInc * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.sorted2orig.p, s.sortedToOrig.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.orig2sorted.p, o2s.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaStreamSynchronize(s.stream));
+    std::vector<int32_t>().swap(s.h_incA);
+    std::vector<float>().swap(s.h_incB);
+    // step constants
+    StepParamsDev& sp = s.stepParams;
+    sp.dt = s.dt; sp.dtSqrReciprocal = s.dtSqrReciprocal;
+    for (int d = 0; d < 3; d++) { sp.gravity[d] = s.phys.gravity[d]; sp.boundsMin[d] = s.phys.worldBoundsMin[d]; sp.boundsMax[d] = s.phys.worldBoundsMax[d]; }
+    sp.kBoundary = s.phys.boundaryCollisionStiffness; sp.muBoundary = s.phys.boundaryFrictionDynamic; sp.epsVBoundary = s.phys.boundaryFrictionEpsV;
+    sp.stepSize = s.phys.stepSize; sp.stepSizeGD = s.phys.stepSizeGD; sp.kCollision = s.phys.collisionStiffness;
+    sp.usePlaneGround = s.phys.usePlaneGround; sp.associateGravityWithInertia = s.phys.associateGravityWithInertia;
+    s.pinnedIOBytes = (size_t)(3 * N + 16) * sizeof(float);
+    CK(cudaMallocHost((void**)&s.pinnedIO, s.pinnedIOBytes));
+    s.meshParamsDirty = true;
+    sync_mesh_params(s);
+    return cudaSuccess;
+}
+
+
+static int g_lanes = 8;   // sub-warp width of the colour solve (tunable: GAIA_B200_LANES=4|8|16|32)
+
+template <bool HC>
+static void launch_solve(Scene& s, int L, int vb, int ve, int applyFriction, const ContactView& cv) {
+    const int n = ve - vb;
+#define LAUNCH(LL) k_solve_colour<LL, HC><<<nblk((int64_t)n * LL), kBlock, 0, s.stream>>>( \
+        vb, ve, s.pos.p, s.prev.p, s.inertia.p, s.mass.p, s.info.p, s.incOff.p, s.incA.p, s.incB.p, s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p)
+    switch (L) {
+        case 4: LAUNCH(4); break;
+        case 16: LAUNCH(16); break;
+        case 32: LAUNCH(32); break;
+        default: LAUNCH(8); break;
+    }
+#undef LAUNCH
+}
+
+static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
+    static bool envRead = false;
+    if (!envRead) { const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e); envRead = true; }
+    const int G = (int)s.groupStart.size() - 1;
+    const int N = (int)s.nVerts;
+    ContactView cv; std::memset(&cv, 0, sizeof(cv));
+    const uint8_t* colliding = nullptr;
+    bool hasContacts = collision_contact_view(s, cv, &colliding);
+    // per-iteration accounting (active, non-fixed vertices)
+    int64_t solvedPerIter = 0, bytesPerIter = 0;
+    for (auto& m : s.meshes) {
+        if (!m.activeForMaterialSolve) continue;
+        solvedPerIter += m.nSolved;
+        int64_t nb = 0; for (auto c : m.nbrDistinctPerGroup) nb += c;
+        bytesPerIter += 60 * m.nSolved + 56 * m.nIncSolved + 12 * nb;
+    }
+    float omega = 1.f;
+    if (s.phys.useAccelerator) {
+        k_accelerate<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.accPrevPrev.p, s.accPrevIter.p, s.info.p, s.meshParams.p, nullptr, 1.f, 1);
+        s.stats.kernelLaunches++;
+    }
+    for (int it = 0; it < nIters; it++) {
+        const int applyFriction = it >= s.phys.frictionStartIter;
+        if (s.phys.useAccelerator) {
+            const int order = it + 1;
+            const float rho = s.phys.acceleratorRho;
+            if (order == 1) omega = 1.f;
+            else if (order == 2) omega = 2 / (2 - rho * rho);
+            else omega = 4.f / (4 - rho * rho * omega);
+        }
+        for (int g = 0; g < G; g++) {
+            const int vb = s.groupStart[g], ve = s.groupStart[g + 1];
+            if (ve <= vb) continue;
+            if (hasContacts) { CK(collision_update_infos(s, g)); }
+            if (s.profiling) cudaEventRecord(s.evA, s.stream);
+            if (hasContacts) launch_solve<true>(s, g_lanes, vb, ve, applyFriction, cv);
+            else launch_solve<false>(s, g_lanes, vb, ve, applyFriction, cv);
+            if (s.profiling) {
+                cudaEventRecord(s.evB, s.stream);
+                cudaEventSynchronize(s.evB);
+                float ms = 0.f; cudaEventElapsedTime(&ms, s.evA, s.evB);
+                s.solveKernelMs += ms; s.solveKernelLaunches++;
+            }
+            s.stats.kernelLaunches++; s.stats.colourSweeps++;
+        }
+        s.stats.vertexSolves += solvedPerIter;
+        s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
+        if (s.phys.useAccelerator) {
+            k_accelerate<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.accPrevPrev.p, s.accPrevIter.p, s.info.p, s.meshParams.p, colliding, omega, 0);
+            s.stats.kernelLaunches++;
+        }
+        const int ici = s.phys.intermediateCollisionIterations;
+        if (allowIntermediateCD && ici > 0 && it % ici == ici - 1) {
+            CK(collision_dcd(s, true));
+            CK(collision_ccd(s));
+            CK(collision_prepare(s));
+            hasContacts = collision_contact_view(s, cv, &colliding);
+        }
+    }
+    return cudaGetLastError();
+}
+
+static cudaError_t initial_step(Scene& s) {
+    const int N = (int)s.nVerts;
+    k_initial_step<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.inertia.p, s.vel.p, s.velPrev.p, s.accel.p, s.info.p,
+                                                   s.meshParams.p, s.meshSubsteps.p, s.stepParams);
+    k_count_substeps<<<nblk((int64_t)s.meshes.size(), 128), 128, 0, s.stream>>>((int)s.meshes.size(), s.meshParams.p, s.meshSubsteps.p);
+    s.stats.kernelLaunches += 2;
+    return cudaGetLastError();
+}
+
+cudaError_t run_substeps(Scene& s, int nSubsteps) {
+    sync_mesh_params(s);
+    const int N = (int)s.nVerts;
+    for (s.substep = 0; s.substep < nSubsteps; s.substep++) {
+        CK(collision_dcd(s, false));
+        CK(initial_step(s));
+        CK(collision_ccd(s));
+        CK(collision_prepare(s));
+        CK(solve_iterations(s, s.phys.iterations, true));
+        k_update_velocity<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.vel.p, s.info.p, s.meshParams.p, s.stepParams);
+        s.stats.kernelLaunches++;
+        s.stats.substeps++;
+    }
+    s.stats.frames++;
+    return cudaGetLastError();
+}
+
+cudaError_t run_iterations_only(Scene& s, int nIters) {
+    sync_mesh_params(s);
+    s.substep = 0;
+    CK(collision_dcd(s, false));
+    CK(initial_step(s));
+    CK(collision_ccd(s));
+    CK(collision_prepare(s));
+    CK(solve_iterations(s, nIters, false));
+    return cudaGetLastError();
+}
+
+cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin, int64_t count, float* outXYZ) {
+    if (!count) return cudaSuccess;
+    float* stage = (float*)s.ioStage.p;
+    k_gather_xyz<<<nblk(count), kBlock, 0, s.stream>>>(count, origBegin, devSorted, s.orig2sorted.p, stage);
+    CK(cudaMemcpyAsync(s.pinnedIO, stage, 3 * count * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+    CK(cudaStreamSynchronize(s.stream));
+    std::memcpy(outXYZ, s.pinnedIO, 3 * count * sizeof(float));
+    s.stats.kernelLaunches++;
+    return cudaSuccess;
+}
+
+cudaError_t scatter_from_host(Scene& s, float4* devSorted, int64_t origBegin, int64_t count, const float* inXYZ, bool) {
+    if (!count) return cudaSuccess;
+    float* stage = (float*)s.ioStage.p;
+    std::memcpy(s.pinnedIO, inXYZ, 3 * count * sizeof(float));
+    CK(cudaMemcpyAsync(stage, s.pinnedIO, 3 * count * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    k_scatter_xyz<<<nblk(count), kBlock, 0, s.stream>>>(count, origBegin, devSorted, s.orig2sorted.p, stage);
+    CK(cudaStreamSynchronize(s.stream));
+    s.stats.kernelLaunches++;
+    return cudaSuccess;
+}
+
+int check_device_errors(Scene& s) {
+    int32_t h[8];
+    if (cudaMemcpyAsync(h, s.errFlags.p, sizeof(h), cudaMemcpyDeviceToHost, s.stream) != cudaSuccess) return GAIA_ERR_CUDA;
+    if (cudaStreamSynchronize(s.stream) != cudaSuccess) return GAIA_ERR_CUDA;
+    if (h[0]) { s.err = "NaN met in the vertex solve"; return GAIA_ERR_NAN; }
+    if (h[2]) { s.err = "contact list overflow"; return GAIA_ERR_OVERFLOW; }
+    if (h[3]) { s.err = "tetrahedral traversal stack overflow"; return GAIA_ERR_OVERFLOW; }
+    return GAIA_OK;
+}
+
+}  // namespace gb

@@ -1,0 +1,251 @@
+/*
+ * gaia_b200.h — C ABI of the B200-native Vertex Block Descent (VBD) step.
+ *
+ * This is the drop-in boundary for ONE hot path of AnkaChan/Gaia: the VBD step
+ * (per-colour vertex solve + collision detection).  The reference has no FFI
+ * layer; its seam is a set of C++ call sites inside `VBDPhysics`.  Every entry
+ * point below names the reference interface it replaces (paths relative to
+ * Simulator/Modules/ of the reference tree, "M/").
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types cross this boundary;
+ *   - every function returns GAIA_OK (0) or a negative gaia_status; the text of
+ *     the last error of a handle is available from gaia_b200_last_error();
+ *   - one host thread per handle; work is enqueued on an internal CUDA stream
+ *     and `*_get_*` calls synchronise before copying out;
+ *   - positions / velocities cross the boundary as xyz-interleaved float32
+ *     (the reference's Eigen 3xN column-major layout, M/TetMesh/TetMeshFEM.h:158)
+ *     in the ORIGINAL vertex order of each mesh — the colour-sorted device
+ *     order is internal;
+ *   - there is no CPU fallback: without a usable CUDA device create() fails.
+ */
+#ifndef GAIA_B200_H
+#define GAIA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GAIA_B200_ABI_VERSION 1
+
+typedef enum gaia_status {
+    GAIA_OK = 0,
+    GAIA_ERR_INVALID_ARG = -1,
+    GAIA_ERR_NO_DEVICE = -2,     /* no CUDA device / driver: there is no CPU path */
+    GAIA_ERR_CUDA = -3,
+    GAIA_ERR_STATE = -4,         /* call order violated (e.g. step before finalize) */
+    GAIA_ERR_UNSUPPORTED = -5,   /* a reference feature outside the hot path (e.g. bowl ground) */
+    GAIA_ERR_OVERFLOW = -6,      /* a device-side list overflowed its capacity */
+    GAIA_ERR_NAN = -7            /* NaN met in the solve (reference: std::exit(-1), M/VBD/VBDPhysics.cpp:2460) */
+} gaia_status;
+
+/* PhysicsParams of Parameters.json.
+ * Mirrors BasePhysicsParams (M/Parameters/PhysicsParameters.h:9-105) and
+ * VBDPhysicsParameters (M/VBD/VBDPhysicsParameters.h:5-82); same names, same
+ * defaults (gaia_b200_default_physics_params). Only fields the step reads. */
+typedef struct gaia_physics_params {
+    float gravity[3];                       /* (0,-10,0) */
+    float timeStep;                         /* 0.0166666 */
+    int32_t numSubsteps;                    /* 20 */
+    int32_t iterations;                     /* 1 */
+    int32_t usePlaneGround;                 /* 1 */
+    int32_t useBowlGround;                  /* 0; 1 -> GAIA_ERR_UNSUPPORTED */
+    int32_t checkAndUpdateWorldBounds;      /* 0 */
+    float worldBoundsMin[3];                /* -1e7 */
+    float worldBoundsMax[3];                /* +1e7 */
+    float boundaryFrictionDynamic;          /* 0.1 */
+    int32_t dcdTetMeshSceneBVHRebuildSteps; /* 16 */
+    int32_t dcdSurfaceSceneBVHRebuildSteps; /* 3 */
+    int32_t ccdBVHRebuildSteps;             /* 7 */
+    /* VBDPhysicsParameters */
+    float stepSize;                         /* 1.0 */
+    float stepSizeGD;                       /* 1e-3 */
+    int32_t associateGravityWithInertia;    /* 1 */
+    float collisionStiffness;               /* 1e5 */
+    int32_t intermediateCollisionIterations;/* -1 */
+    float boundaryCollisionStiffness;       /* 1e5 */
+    float boundaryFrictionEpsV;             /* 1.0 */
+    int32_t frictionStartIter;              /* 0 */
+    int32_t useAccelerator;                 /* 0 */
+    float acceleratorRho;                   /* 0.93 */
+    float collisionOffHeight;               /* 1e7 */
+} gaia_physics_params;
+
+/* CollisionParams of Parameters.json.
+ * Mirrors CollisionDetectionParamters (M/CollisionDetector/CollisionDetertionParameters.h:44-80). */
+typedef struct gaia_collision_params {
+    int32_t allowCCD;                                   /* 1 */
+    int32_t allowDCD;                                   /* 1 */
+    int32_t checkFeasibleRegion;                        /* 1 */
+    int32_t checkTetTraverse;                           /* 1 */
+    int32_t handleSelfCollision;                        /* 1 */
+    int32_t stopTraversingAfterPassingQueryPoint;       /* 1 */
+    int32_t tetrahedralTraverseForNonSelfIntersection;  /* 1 */
+    int32_t useStaticTraverse;                          /* 1 */
+    int32_t loopLessTraverse;                           /* 0 */
+    int32_t shiftQueryPointToCenter;                    /* 1 */
+    float centerShiftLevel;                             /* 0.01 */
+    int32_t maxNumberOfBVHQuery;                        /* 500 */
+    float feasibleRegionEpsilon;                        /* 1e-2 */
+    float rayTriIntersectionEPSILON;                    /* 1e-10 */
+    float maxSearchDistanceMultiplier;                  /* 1.8 */
+} gaia_collision_params;
+
+/* One entry of Models.json.
+ * Mirrors ObjectParams (M/Materials/Materials.h:12-53), ObjectParamsVBD
+ * (M/VBD/VBD_BaseMaterial.h:21-49) and ObjectParametersVBDNeoHookean
+ * (M/VBD/VBD_NeoHookean.h:16-34). */
+typedef struct gaia_object_params {
+    float scale[3];                 /* (1,1,1) */
+    float rotation[3];              /* axis*angle, (0,0,0) */
+    float translation[3];           /* (0,0,0) */
+    float initialVelocity[3];       /* (0,0,0) */
+    float density;                  /* 1 */
+    int32_t hasNoGravZone;          /* 0 */
+    float noGravZoneThreshold;      /* 0 */
+    float maxVelocityMagnitude;     /* -1 */
+    int32_t frameToAppear;          /* -1 */
+    /* ObjectParamsVBD */
+    float frictionDynamic;          /* 0.1 */
+    float frictionEpsV;             /* 0.01 */
+    float exponentialVelDamping;    /* 1.0 (raised to dt at create, M/VBD/VBDPhysics.cpp:794-807) */
+    float constantVelDamping;       /* 0.0 (multiplied by dt likewise) */
+    int32_t initializationType;     /* 0..6, M/VBD/VBD_BaseMaterial.cpp:16-131; 5 -> unsupported */
+    float initRatio_g;              /* 0.5 */
+    /* NeoHookean */
+    float miu;                      /* 1e4 */
+    float lmbd;                     /* 1e5 */
+    float dampingHydrostatic;       /* 0 */
+    float dampingDeviatoric;        /* 0 */
+} gaia_object_params;
+
+/* One detected vertex-face contact, for bit-exact parity of contact sets
+ * (CollidingPointInfo + CollisionDetectionResult,
+ *  M/CollisionDetector/CollisionDetertionParameters.h:166-222).
+ * Lists are returned sorted by (queryMesh, queryVertex). */
+typedef struct gaia_contact {
+    int32_t queryMesh;      /* idTMQuery */
+    int32_t queryVertex;    /* idVQuery (tet-mesh vertex id, original order) */
+    int32_t hitMesh;        /* intersectedMeshId */
+    int32_t hitTet;         /* intersectedElement (-1 for CCD contacts) */
+    int32_t hitFace;        /* closestSurfaceFaceId (-1 when no shortest path was found) */
+    int32_t fromCCD;        /* 0: DCD, 1: CCD */
+    int32_t shortestPathFound;
+    int32_t closestPointType; /* ClosestPointOnTriangleType as int */
+} gaia_contact;
+
+/* Per-phase accumulated device time (ms) with the reference's timer names
+ * (M/Timer/RunningTimeStatistics.h:54-183) and the counters the metric needs. */
+typedef struct gaia_stats {
+    double timeCsmpInitialStep;
+    double timeCsmpMaterialSolve;
+    double timeCsmpUpdateVelocity;
+    double timeCsmpUpdatingBVHDCD;
+    double timeCsmpColDetectDCD;
+    double timeCsmpUpdatingBVHCCD;
+    double timeCsmpColDetectCCD;
+    double timeCsmpFrame;
+    int64_t vertexSolves;       /* non-fixed active vertices solved, summed over colour sweeps */
+    int64_t colourSweeps;       /* colour kernels executed */
+    int64_t substeps;
+    int64_t frames;
+    int64_t kernelLaunches;     /* kernels of this library enqueued */
+    int64_t algorithmicBytes;   /* SURVEY §8(d) formula, summed over colour sweeps */
+    int64_t numContactsDCD;     /* last detection */
+    int64_t numContactsCCD;
+} gaia_stats;
+
+typedef struct gaia_handle gaia_handle;
+
+/* library ------------------------------------------------------------------ */
+int  gaia_b200_abi_version(void);
+const char* gaia_b200_last_error(const gaia_handle* h);     /* h may be NULL: last create() error */
+void gaia_b200_default_physics_params(gaia_physics_params* p);
+void gaia_b200_default_collision_params(gaia_collision_params* p);
+void gaia_b200_default_object_params(gaia_object_params* p);
+
+/* scene construction -------------------------------------------------------
+ * create:   VBDPhysics::loadRunningparameters + BasePhysicFramework::timeStepEqualize
+ *           (M/VBD/VBDPhysics.cpp:90, M/Framework/BasePhysicsFramework.cpp:245-249).
+ *           `device` is the CUDA ordinal (one process per GPU). */
+int gaia_b200_create(const gaia_physics_params* phys, const gaia_collision_params* col,
+                     int device, gaia_handle** out);
+void gaia_b200_destroy(gaia_handle* h);
+
+/* add_tet_mesh: VBDBaseTetMesh::initialize -> TetMeshFEM::initialize +
+ *           TetMeshTopology::initialize (M/TetMesh/TetMeshFEM.cpp:332-443, 40-330).
+ *           xyz: 3*nV floats as read from the .t file (transform is applied inside);
+ *           tets: 4*nT vertex ids; colouring = the *.vertexColoring.json lists,
+ *           flattened: colour c owns color_verts[color_offsets[c] .. color_offsets[c+1]).
+ *           Returns the mesh id (>=0) or a negative status. */
+int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT,
+                           const float* xyz, const int32_t* tets,
+                           const gaia_object_params* obj,
+                           int32_t nColors, const int32_t* color_offsets, const int32_t* color_verts,
+                           int32_t nFixed, const int32_t* fixedPoints);
+
+/* finalize: the rest of VBDPhysics::initialize (colour-group merge
+ *           M/VBD/VBDPhysics.cpp:236-274, initializeGPU :563-651,
+ *           initializeCollisionDetector BasePhysicsFramework.cpp:251-262). */
+int gaia_b200_finalize(gaia_handle* h);
+
+/* stepping ------------------------------------------------------------------
+ * run_frames: BasePhysicFramework::simulate loop body (enableModels -> runStep -> ++frameId,
+ *           BasePhysicsFramework.cpp:355-390) repeated nFrames times; runStep follows
+ *           VBDPhysics::runStep_hybridCollisionHandling (M/VBD/VBDPhysics.cpp:1634-1707). */
+int gaia_b200_run_frames(gaia_handle* h, int32_t nFrames);
+/* run_iterations: debugging/parity entry: applyInitialStep once, then nIters colour sweeps of
+ *           the material solve (no velocity update) — "positions after one iteration". */
+int gaia_b200_run_iterations(gaia_handle* h, int32_t nIters);
+int gaia_b200_synchronize(gaia_handle* h);
+int gaia_b200_frame_id(const gaia_handle* h);
+
+/* state access (VBDBaseTetMesh::syncToCPU / syncToGPU, M/VBD/VBD_BaseMaterial.h:120-128) */
+int gaia_b200_num_meshes(const gaia_handle* h);
+int gaia_b200_mesh_sizes(const gaia_handle* h, int mesh, int32_t* nV, int32_t* nT,
+                         int32_t* nSurfV, int32_t* nSurfF);
+int gaia_b200_get_positions(gaia_handle* h, int mesh, float* xyz);
+int gaia_b200_get_prev_positions(gaia_handle* h, int mesh, float* xyz);
+int gaia_b200_get_velocities(gaia_handle* h, int mesh, float* xyz);
+int gaia_b200_get_inertia(gaia_handle* h, int mesh, float* xyz);
+int gaia_b200_set_state(gaia_handle* h, int mesh, const float* pos, const float* vel);
+/* surface positions in writeAllToBinary order (M/IO/FileIO.cpp:52-83) */
+int gaia_b200_get_surface_positions(gaia_handle* h, int mesh, float* xyz);
+/* whole-scene transfers: all meshes concatenated in mesh order (one D2H / H2D) */
+int64_t gaia_b200_total_vertices(const gaia_handle* h);
+int gaia_b200_get_all_positions(gaia_handle* h, float* xyz);
+int gaia_b200_set_all_state(gaia_handle* h, const float* pos, const float* vel);
+
+/* integer parity surfaces ---------------------------------------------------- */
+int gaia_b200_get_world_bounds(const gaia_handle* h, float* min3, float* max3);
+int gaia_b200_num_parallel_groups(const gaia_handle* h);
+/* out: [mesh0,v0, mesh1,v1, ...] exactly as VBDPhysics::vertexParallelGroups[g] (M/VBD/VBDPhysics.h:219-224);
+ * call with out==NULL to query the pair count */
+int gaia_b200_get_parallel_group(const gaia_handle* h, int group, int32_t* out, int32_t* nPairs);
+int gaia_b200_get_surface_vertex_ids(const gaia_handle* h, int mesh, int32_t* out);   /* surfaceVIds */
+int gaia_b200_get_surface_faces(const gaia_handle* h, int mesh, int32_t* out);        /* surfaceFacesTetMeshVIds, 3*nSurfF */
+int gaia_b200_get_vertex_masses(const gaia_handle* h, int mesh, float* out);
+/* collision detection on the current state (VBDPhysics::dcd / ccd, M/VBD/VBDPhysics.cpp:1958-2116),
+ * without stepping; fills the contact list that get_contacts returns */
+int gaia_b200_detect_collisions(gaia_handle* h, int doDCD, int doCCD);
+int gaia_b200_get_contacts(gaia_handle* h, gaia_contact* out, int64_t capacity, int64_t* n);
+/* which: 0 = all-tets scene, 1 = surface-faces scene; out = primitive ids in Morton leaf order */
+int gaia_b200_get_bvh_leaf_order(gaia_handle* h, int which, int32_t* out, int64_t capacity, int64_t* n);
+
+/* mesh activation (VBDPhysics::enableModels, M/VBD/VBDPhysics.cpp:685-709) */
+int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int activeForMaterialSolve);
+
+/* statistics */
+int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out);
+int gaia_b200_reset_stats(gaia_handle* h);
+/* average device time (ms) of the colour-solve kernels since the last reset, measured with CUDA
+ * events on the launching stream when profiling is enabled */
+int gaia_b200_set_profiling(gaia_handle* h, int enabled);
+void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that time with their own events */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAIA_B200_H */

@@ -1,0 +1,115 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY. ctypes binding of oracle/liboracle.so (CPU restatement of the reference VBD step)
+and of oracle/_ref/libgaia_ref.so (the reference's own math compiled from /root/reference, when present).
+Imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs only."""
+import ctypes as C
+import os
+import numpy as np
+from gaia_b200.capi import (SceneBase, bind_scene_api, PhysicsParams, CollisionParams, default_physics_params,
+                            default_collision_params, _fp, _ip, _f32, _i32)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_LIB = os.path.join(_HERE, "liboracle.so")
+REF_LIB = os.path.join(_HERE, "_ref", "libgaia_ref.so")
+_lib = None
+_ref = None
+
+
+def load_oracle():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORACLE_LIB):
+            raise RuntimeError(f"{ORACLE_LIB} not built (make -C oracle)")
+        lib = C.CDLL(ORACLE_LIB)
+        lib.oracle_create.argtypes = [C.POINTER(PhysicsParams), C.POINTER(CollisionParams), C.c_int]
+        lib.oracle_create.restype = C.c_void_p
+        lib.oracle_destroy.argtypes = [C.c_void_p]; lib.oracle_destroy.restype = None
+        bind_scene_api(lib, "oracle_")
+        P, FP, IP = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
+        lib.oracle_num_threads.argtypes = [P]
+        lib.oracle_set_prev_positions.argtypes = [P, C.c_int, FP]
+        lib.oracle_get_dminv.argtypes = [P, C.c_int, FP]
+        lib.oracle_get_rest_volumes.argtypes = [P, C.c_int, FP]
+        lib.oracle_get_vertex_tet_csr.argtypes = [P, C.c_int, IP, IP, IP]
+        lib.oracle_set_brute_force.argtypes = [P, C.c_int]
+        lib.oracle_vertex_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
+        lib.oracle_solve3x3.argtypes = [FP, FP, FP]
+        lib.oracle_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]
+        lib.oracle_cubic_roots.argtypes = [FP, C.c_float, C.c_float, FP]
+        lib.oracle_point_in_tet.argtypes = [FP] * 5
+        lib.oracle_closest_point_triangle.argtypes = [FP] * 6
+        _lib = lib
+    return _lib
+
+
+def ref_available():
+    return os.path.exists(REF_LIB)
+
+
+def load_ref():
+    global _ref
+    if _ref is None:
+        lib = C.CDLL(REF_LIB)
+        FP, IP = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+        lib.ref_neohookean_vertex.argtypes = [C.c_int, C.c_int, FP, FP, IP, FP, FP, IP, IP, IP, C.c_float, C.c_float,
+                                              C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]
+        lib.ref_neohookean_vertex.restype = None
+        lib.ref_collision_per_collision.argtypes = [FP, FP, FP, FP, C.c_int] + [C.c_float] * 6 + [FP, FP]
+        lib.ref_collision_per_collision.restype = None
+        lib.ref_boundary.argtypes = [FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, FP, FP]
+        lib.ref_boundary.restype = None
+        lib.ref_solve3x3.argtypes = [FP, FP, FP]
+        lib.ref_damp_velocity.argtypes = [FP, C.c_float, C.c_float, C.c_float]; lib.ref_damp_velocity.restype = None
+        lib.ref_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]
+        lib.ref_cubic_roots.argtypes = [FP, C.c_float, C.c_float, FP]
+        _ref = lib
+    return _ref
+
+
+class OracleScene(SceneBase):
+    _prefix = "oracle_"
+
+    def __init__(self, phys=None, col=None, threads=0):
+        self._lib = load_oracle()
+        phys = phys or default_physics_params(); col = col or default_collision_params()
+        self.h = C.c_void_p(self._lib.oracle_create(C.byref(phys), C.byref(col), threads))
+
+    def close(self):
+        if self.h is not None:
+            self._lib.oracle_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def num_threads(self):
+        return self._lib.oracle_num_threads(self.h)
+
+    def set_prev_positions(self, mesh, prev):
+        p = _f32(prev)
+        self._call("set_prev_positions", mesh, _fp(p))
+
+    def set_brute_force(self, on=True):
+        self._call("set_brute_force", int(on))
+
+    def dminv(self, mesh):
+        a = np.empty((self.mesh_sizes(mesh)[1], 9), np.float32)
+        self._call("get_dminv", mesh, _fp(a)); return a
+
+    def rest_volumes(self, mesh):
+        a = np.empty(self.mesh_sizes(mesh)[1], np.float32)
+        self._call("get_rest_volumes", mesh, _fp(a)); return a
+
+    def vertex_tet_csr(self, mesh):
+        nV, nT = self.mesh_sizes(mesh)[:2]
+        infos = np.empty(2 * nV, np.int32); t = np.empty(4 * nT, np.int32); o = np.empty(4 * nT, np.int32)
+        self._call("get_vertex_tet_csr", mesh, _ip(infos), _ip(t), _ip(o))
+        return infos, t, o
+
+    def vertex_material_force_hessian(self, mesh, v):
+        f = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        self._call("vertex_material_force_hessian", mesh, v, _fp(f), _fp(h))
+        return f, h

@@ -1,0 +1,204 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
+// C entry points of the CPU oracle; they shadow the product's C ABI (include/gaia_b200.h) one to one, with the
+// prefix `oracle_`, so that tests drive both implementations with the same calls.
+#include "vbd_oracle.h"
+#include "oracle_ccd.h"
+#include <cstdio>
+
+using namespace orc;
+
+namespace orc { void collision_set_brute_force(Scene& s, bool on); }
+
+extern "C" {
+
+void* oracle_create(const gaia_physics_params* phys, const gaia_collision_params* col, int nThreads) {
+    Scene* s = new Scene();
+    s->phys = *phys; s->col = *col;
+    // BasePhysicFramework::timeStepEqualize (BasePhysicsFramework.cpp:245-249)
+    s->dt = s->phys.timeStep / s->phys.numSubsteps;
+    s->dtSqrReciprocal = 1.f / (s->dt * s->dt);
+    std::memset(&s->stats, 0, sizeof(s->stats));
+    if (nThreads <= 0) nThreads = (int)std::thread::hardware_concurrency();
+    s->pool = new Pool(nThreads);
+    return s;
+}
+void oracle_destroy(void* h) { delete (Scene*)h; }
+int oracle_num_threads(void* h) { return ((Scene*)h)->pool->size(); }
+
+int oracle_add_tet_mesh(void* h, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params* obj,
+                        int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed) {
+    Scene* s = (Scene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    s->meshes.emplace_back();
+    Mesh& m = s->meshes.back();
+    m.id = (int)s->meshes.size() - 1;
+    gaia_object_params o = *obj;
+    // VBDPhysics::timeStepEqualize (VBDPhysics.cpp:794-807)
+    o.exponentialVelDamping = std::pow(o.exponentialVelDamping, s->dt);
+    o.constantVelDamping = o.constantVelDamping * s->dt;
+    mesh_initialize(m, nV, nT, xyz, tets, o, nColors, colorOffsets, colorVerts, nFixed, fixed);
+    return m.id;
+}
+int oracle_finalize(void* h) { scene_finalize(*(Scene*)h); return GAIA_OK; }
+
+int oracle_run_frames(void* h, int32_t nFrames) {
+    Scene* s = (Scene*)h;
+    if (!s->finalized) return GAIA_ERR_STATE;
+    for (int f = 0; f < nFrames; f++) {
+        enable_models(*s);
+        run_step(*s);
+        ++s->frameId;
+        if (!s->err.empty()) return GAIA_ERR_NAN;
+    }
+    return GAIA_OK;
+}
+int oracle_run_iterations(void* h, int32_t nIters) {
+    Scene* s = (Scene*)h;
+    if (!s->finalized) return GAIA_ERR_STATE;
+    enable_models(*s);
+    run_iterations(*s, nIters);
+    return GAIA_OK;
+}
+int oracle_frame_id(void* h) { return ((Scene*)h)->frameId; }
+int oracle_num_meshes(void* h) { return (int)((Scene*)h)->meshes.size(); }
+int oracle_mesh_sizes(void* h, int mesh, int32_t* nV, int32_t* nT, int32_t* nSV, int32_t* nSF) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    *nV = m.nV; *nT = m.nT; *nSV = m.nSurfV(); *nSF = m.nSurfF();
+    return GAIA_OK;
+}
+static void copy_out(const std::vector<V3>& v, float* out) { std::memcpy(out, v.data(), v.size() * sizeof(V3)); }
+int oracle_get_positions(void* h, int mesh, float* xyz) { copy_out(((Scene*)h)->meshes[mesh].pos, xyz); return GAIA_OK; }
+int oracle_get_prev_positions(void* h, int mesh, float* xyz) { copy_out(((Scene*)h)->meshes[mesh].prev, xyz); return GAIA_OK; }
+int oracle_get_velocities(void* h, int mesh, float* xyz) { copy_out(((Scene*)h)->meshes[mesh].vel, xyz); return GAIA_OK; }
+int oracle_get_inertia(void* h, int mesh, float* xyz) { copy_out(((Scene*)h)->meshes[mesh].inertia, xyz); return GAIA_OK; }
+int oracle_set_state(void* h, int mesh, const float* pos, const float* vel) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    if (pos) std::memcpy(m.pos.data(), pos, m.pos.size() * sizeof(V3));
+    if (vel) std::memcpy(m.vel.data(), vel, m.vel.size() * sizeof(V3));
+    return GAIA_OK;
+}
+int oracle_set_prev_positions(void* h, int mesh, const float* prev) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    std::memcpy(m.prev.data(), prev, m.prev.size() * sizeof(V3));
+    return GAIA_OK;
+}
+int oracle_get_surface_positions(void* h, int mesh, float* xyz) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    for (int i = 0; i < m.nSurfV(); i++) { V3 p = m.pos[m.surfaceVIds[i]]; xyz[3 * i] = p.x; xyz[3 * i + 1] = p.y; xyz[3 * i + 2] = p.z; }
+    return GAIA_OK;
+}
+int oracle_get_world_bounds(void* h, float* mn, float* mx) {
+    Scene* s = (Scene*)h;
+    for (int d = 0; d < 3; d++) { mn[d] = s->phys.worldBoundsMin[d]; mx[d] = s->phys.worldBoundsMax[d]; }
+    return GAIA_OK;
+}
+int oracle_num_parallel_groups(void* h) { return (int)((Scene*)h)->vertexParallelGroups.size(); }
+int oracle_get_parallel_group(void* h, int g, int32_t* out, int32_t* nPairs) {
+    auto& v = ((Scene*)h)->vertexParallelGroups[g];
+    *nPairs = (int32_t)v.size() / 2;
+    if (out) std::memcpy(out, v.data(), v.size() * sizeof(int32_t));
+    return GAIA_OK;
+}
+int oracle_get_surface_vertex_ids(void* h, int mesh, int32_t* out) {
+    auto& v = ((Scene*)h)->meshes[mesh].surfaceVIds; std::memcpy(out, v.data(), v.size() * 4); return GAIA_OK;
+}
+int oracle_get_surface_faces(void* h, int mesh, int32_t* out) {
+    auto& v = ((Scene*)h)->meshes[mesh].surfFaces; std::memcpy(out, v.data(), v.size() * 4); return GAIA_OK;
+}
+int oracle_get_vertex_masses(void* h, int mesh, float* out) {
+    auto& v = ((Scene*)h)->meshes[mesh].mass; std::memcpy(out, v.data(), v.size() * 4); return GAIA_OK;
+}
+int oracle_get_dminv(void* h, int mesh, float* out) {
+    auto& v = ((Scene*)h)->meshes[mesh].DmInv; std::memcpy(out, v.data(), v.size() * 4); return GAIA_OK;
+}
+int oracle_get_rest_volumes(void* h, int mesh, float* out) {
+    auto& v = ((Scene*)h)->meshes[mesh].restVol; std::memcpy(out, v.data(), v.size() * 4); return GAIA_OK;
+}
+int oracle_get_vertex_tet_csr(void* h, int mesh, int32_t* infos, int32_t* tets, int32_t* orders) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    std::memcpy(infos, m.vNbrInfos.data(), m.vNbrInfos.size() * 4);
+    std::memcpy(tets, m.vNbrTets.data(), m.vNbrTets.size() * 4);
+    std::memcpy(orders, m.vNbrOrder.data(), m.vNbrOrder.size() * 4);
+    return GAIA_OK;
+}
+int oracle_enable_mesh(void* h, int mesh, int col, int solve) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    m.activeForCollision = col != 0; m.activeForMaterialSolve = solve != 0;
+    return GAIA_OK;
+}
+int oracle_set_brute_force(void* h, int on) { collision_set_brute_force(*(Scene*)h, on != 0); return GAIA_OK; }
+
+int oracle_detect_collisions(void* h, int doDCD, int doCCD) {
+    Scene* s = (Scene*)h;
+    gaia_collision_params saved = s->col;
+    s->col.allowDCD = saved.allowDCD && doDCD; s->col.allowCCD = saved.allowCCD && doCCD;
+    s->substep = 0;
+    dcd(*s, false);
+    ccd(*s);
+    prepare_collision_data(*s);
+    s->col = saved;
+    return GAIA_OK;
+}
+int oracle_get_contacts(void* h, gaia_contact* out, int64_t capacity, int64_t* n) {
+    Scene* s = (Scene*)h;
+    int64_t cnt = 0;
+    for (size_t im = 0; im < s->meshes.size(); im++) {
+        Mesh& m = s->meshes[im];
+        for (int sv = 0; sv < m.nSurfV(); sv++) {
+            ColResult& r = m.colResults[sv];
+            if (!r.numIntersections) continue;
+            if (out && cnt < capacity) {
+                gaia_contact c;
+                c.queryMesh = r.idTMQuery; c.queryVertex = r.idVQuery; c.hitMesh = r.intersectedMeshId;
+                c.hitTet = r.fromCCD ? -1 : r.intersectedElement; c.hitFace = r.closestSurfaceFaceId;
+                c.fromCCD = r.fromCCD; c.shortestPathFound = r.shortestPathFound; c.closestPointType = r.closestPointType;
+                out[cnt] = c;
+            }
+            cnt++;
+        }
+    }
+    *n = cnt;
+    return GAIA_OK;
+}
+// per-vertex force / Hessian probe for pinning against oracle/_ref (not part of the product ABI)
+int oracle_vertex_material_force_hessian(void* h, int mesh, int v, float* force3, float* hessian9) {
+    Scene* s = (Scene*)h;
+    V3 f; M3 H;
+    neohookean_force_hessian(*s, s->meshes[mesh], v, f, H);
+    force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
+    std::memcpy(hessian9, H.m, 36);
+    return GAIA_OK;
+}
+int oracle_solve3x3(const float* m9, const float* b3, float* out3) { return solve3x3_psd_stable(m9, b3, out3) ? 1 : 0; }
+int oracle_get_stats(void* h, gaia_stats* out) { *out = ((Scene*)h)->stats; return GAIA_OK; }
+int oracle_reset_stats(void* h) { std::memset(&((Scene*)h)->stats, 0, sizeof(gaia_stats)); return GAIA_OK; }
+
+// stand-alone predicate probes (tests pin them against oracle/_ref and against the CUDA predicates)
+int oracle_ccd_tri_point(const float* x0 /*9*/, const float* x1 /*9*/, const float* p0, const float* p1, float* t, float* bary3) {
+    ccdm::Vec3 x[2][3], p[2];
+    for (int k = 0; k < 3; k++) { x[0][k] = ccdm::Vec3(x0[3 * k], x0[3 * k + 1], x0[3 * k + 2]); x[1][k] = ccdm::Vec3(x1[3 * k], x1[3 * k + 1], x1[3 * k + 2]); }
+    p[0] = ccdm::Vec3(p0[0], p0[1], p0[2]); p[1] = ccdm::Vec3(p1[0], p1[1], p1[2]);
+    float tt = -1; ccdm::Vec3 b;
+    bool hit = ccdm::IntersectContinuousTriPoint(tt, x, p, b);
+    *t = tt; bary3[0] = b.x; bary3[1] = b.y; bary3[2] = b.z;
+    return hit ? 1 : 0;
+}
+int oracle_cubic_roots(const float* coef4, float x0, float x1, float* roots3) { return ccdm::cubic_roots(roots3, coef4, x0, x1); }
+
+}  // extern "C"
+
+namespace orc {
+bool point_in_tet(V3 p, V3 a, V3 b, V3 c, V3 d);
+V3 closest_point_triangle(V3 p, V3 a, V3 b, V3 c, V3& bary, int& type);
+}
+extern "C" {
+int oracle_point_in_tet(const float* p, const float* a, const float* b, const float* c, const float* d) {
+    return point_in_tet(V3(p[0], p[1], p[2]), V3(a[0], a[1], a[2]), V3(b[0], b[1], b[2]), V3(c[0], c[1], c[2]), V3(d[0], d[1], d[2])) ? 1 : 0;
+}
+int oracle_closest_point_triangle(const float* p, const float* a, const float* b, const float* c, float* cp3, float* bary3) {
+    V3 bary; int type;
+    V3 cp = closest_point_triangle(V3(p[0], p[1], p[2]), V3(a[0], a[1], a[2]), V3(b[0], b[1], b[2]), V3(c[0], c[1], c[2]), bary, type);
+    cp3[0] = cp.x; cp3[1] = cp.y; cp3[2] = cp.z; bary3[0] = bary.x; bary3[1] = bary.y; bary3[2] = bary.z;
+    return type;
+}
+}

@@ -1,0 +1,136 @@
+"""-m gpu: the CUDA VBD step (through the C ABI) against the CPU oracle on the same seeded inputs.
+Tolerances: integer work bit-exact; positions after one iteration <= 1e-5 relative (north_star); trajectories within the
+max-displacement tolerance stated per test."""
+import numpy as np
+import pytest
+
+from conftest import make_beam_scene, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(**kw):
+    from gaia_b200.capi import Scene
+    from oracle.binding import OracleScene
+    return make_beam_scene(Scene, **kw), make_beam_scene(OracleScene, threads=2, **kw)
+
+
+def test_setup_is_bit_exact():
+    g, o = _pair(obj_kw=dict(rotation=[0.3, -0.2, 0.9], scale=[1.5, 0.7, 1.1], translation=[0.2, 3.0, -1.0]))
+    assert np.array_equal(g.positions(0), o.positions(0))            # transform
+    assert np.array_equal(g.vertex_masses(0), o.vertex_masses(0))    # lumped mass
+    assert np.array_equal(g.surface_vertex_ids(0), o.surface_vertex_ids(0))
+    assert np.array_equal(g.surface_faces(0), o.surface_faces(0))
+    for a, b in zip(g.parallel_groups(), o.parallel_groups()):
+        assert np.array_equal(a, b)
+    assert g.mesh_sizes(0) == o.mesh_sizes(0)
+
+
+@pytest.mark.parametrize("init_type", [0, 1, 2, 3, 4, 6])
+def test_positions_after_one_iteration(init_type):
+    g, o = _pair(obj_kw=dict(initializationType=init_type))
+    for s in (g, o):
+        s.run_frames(1)          # give type 2/4/6 a velocity history
+        s.run_iterations(1)
+    assert np.array_equal(g.prev_positions(0), o.prev_positions(0)) or rel_err(g.prev_positions(0), o.prev_positions(0)) < 1e-5
+    assert rel_err(g.inertia(0), o.inertia(0)) < 1e-5
+    assert rel_err(g.positions(0), o.positions(0)) < 1e-5
+
+
+def test_first_iteration_from_rest_state():
+    g, o = _pair()
+    g.run_iterations(1); o.run_iterations(1)
+    assert np.array_equal(g.inertia(0), o.inertia(0))       # y = x + dt*(v + dt*g): elementwise, no contraction
+    assert rel_err(g.positions(0), o.positions(0)) < 1e-5
+
+
+def test_ground_contact_and_friction_trajectory():
+    # 30 frames: free fall, impact on the ground plane with friction, rebound. Tolerance: 1e-3 of the beam length
+    g, o = _pair(v0=(1.0, -5.0, 0.5), substeps=4, iterations=10)
+    for s in (g, o):
+        s.run_frames(30)
+    pg, po = g.positions(0), o.positions(0)
+    assert po[:, 1].min() < 0.05                              # it reached the ground
+    assert np.abs(pg - po).max() < 1e-3 * 1.5
+    assert rel_err(g.velocities(0), o.velocities(0)) < 5e-2
+
+
+def test_damping_and_velocity_damping():
+    kw = dict(obj_kw=dict(dampingHydrostatic=1e-4, dampingDeviatoric=1e-4, exponentialVelDamping=0.9, constantVelDamping=0.1,
+                          maxVelocityMagnitude=25.0))
+    g, o = _pair(**kw)
+    for s in (g, o):
+        s.run_frames(5)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 2e-4
+    assert np.abs(g.velocities(0) - o.velocities(0)).max() < 2e-2
+
+
+def test_fixed_points_and_greedy_colouring():
+    from gaia_b200 import capi, meshio
+    from gaia_b200.capi import Scene
+    from oracle.binding import OracleScene
+    verts, tets = meshio.kuhn_beam(8, 2, 2, h=0.2, origin=(0, 2.0, 0))
+    colors = meshio.greedy_coloring(len(verts), tets)
+    assert meshio.check_coloring(len(verts), tets, colors)
+    fixed = np.nonzero(verts[:, 0] < 1e-6)[0].astype(np.int32)
+    phys = capi.default_physics_params(numSubsteps=3, iterations=8)
+    col = capi.default_collision_params(allowDCD=0, allowCCD=0)
+    obj = capi.default_object_params(miu=5e4, lmbd=5e5, density=100)
+    out = []
+    for cls, kw in ((Scene, {}), (OracleScene, dict(threads=2))):
+        s = cls(phys, col, **kw)
+        s.add_tet_mesh(verts, tets, obj, colors, fixed)
+        s.finalize()
+        s.run_frames(10)
+        out.append((s.positions(0), s.velocities(0)))
+    (pg, vg), (po, vo) = out
+    assert np.array_equal(pg[fixed], verts[fixed]) and np.array_equal(po[fixed], verts[fixed])
+    assert (vg[fixed] == 0).all()
+    assert po[:, 1].min() < 1.99                                # the cantilever sagged
+    assert np.abs(pg - po).max() < 2e-4
+
+
+def test_two_meshes_group_merge_and_late_appearance():
+    from gaia_b200 import capi, meshio
+    from gaia_b200.capi import Scene
+    from oracle.binding import OracleScene
+    a = meshio.kuhn_beam(4, 2, 2, h=0.25, origin=(0, 1.0, 0)); ca = meshio.kuhn_coloring(4, 2, 2)
+    b = meshio.kuhn_beam(3, 3, 2, h=0.2, origin=(3, 0.5, 0)); cb = meshio.greedy_coloring(len(b[0]), b[1])
+    phys = capi.default_physics_params(numSubsteps=2, iterations=6, worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10])
+    col = capi.default_collision_params(allowDCD=0, allowCCD=0)
+    oa = capi.default_object_params(miu=1e5, lmbd=1e6, density=50)
+    ob = capi.default_object_params(miu=2e5, lmbd=8e5, density=20, frameToAppear=3, initialVelocity=[0, -2, 0])
+    res = []
+    for cls, kw in ((Scene, {}), (OracleScene, dict(threads=2))):
+        s = cls(phys, col, **kw)
+        s.add_tet_mesh(a[0], a[1], oa, ca); s.add_tet_mesh(b[0], b[1], ob, cb)
+        s.finalize()
+        groups = s.parallel_groups()
+        s.run_frames(2)
+        p_early = s.positions(1)
+        s.run_frames(6)
+        res.append((groups, p_early, s.positions(0), s.positions(1), s.stats()["vertexSolves"]))
+    for x, y in zip(res[0][0], res[1][0]):
+        assert np.array_equal(x, y)
+    assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][1], b[0])   # mesh 1 untouched before frame 3
+    assert np.abs(res[0][2] - res[1][2]).max() < 2e-4 and np.abs(res[0][3] - res[1][3]).max() < 2e-4
+    assert res[0][4] == res[1][4]                                                     # same vertex-solve count
+
+
+def test_chebyshev_accelerator_matches_oracle():
+    g, o = _pair(phys_kw=dict(useAccelerator=1, acceleratorRho=0.9), iterations=12)
+    for s in (g, o):
+        s.run_frames(4)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 2e-4
+
+
+def test_state_roundtrip_and_whole_scene_io():
+    g, o = _pair()
+    g.run_frames(2)
+    p, v = g.positions(0), g.velocities(0)
+    assert np.array_equal(g.all_positions(), p)
+    g.set_state(0, p + 0.25, v * 0.5)
+    assert np.array_equal(g.positions(0), (p + 0.25).astype(np.float32))
+    assert np.array_equal(g.velocities(0), (v * 0.5).astype(np.float32))
+    sp = g.surface_positions(0)
+    assert np.array_equal(sp, g.positions(0)[g.surface_vertex_ids(0)])
