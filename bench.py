@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""bench.py — VBD vertex-solves/s on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one frame of the hot path (VBDPhysics::runStep: numSubsteps x iterations colour sweeps + initial step,
+deformers, velocity update [+ collision detection when the workload enables it]) over one synthetic scene.
+Default workload at N=1: BASELINE.json configs[3], the single ~10M-tet Neo-Hookean beam twisted by two Rotator deformers
+(SURVEY.md §8(d) cfg 4) — the configuration north_star's roofline and scaling targets are stated on; it fits one GPU.
+  value        whole-job vertex-solves/s with the scene resident in HBM (CUDA events on the library's stream)
+  e2e          the same metric through the C ABI with HOST buffers: per step H2D of positions+velocities, runStep, D2H of
+               positions, all inside the timed region
+  roofline     dominant kernel (k_solve_colour): algorithmic bytes (SURVEY.md §8(d) formula) / CUDA-event kernel time
+  cpu_baseline the CPU oracle (a port of the reference's CPU/TBB path; the reference itself needs Eigen/oneTBB/Embree,
+               absent here) on a bounded sample of the same workload, all host threads
+--impl reference times that CPU oracle as the reference arm.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from gaia_b200 import capi, meshio  # noqa: E402
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# --------------------------------------------------------------------------------------------- workloads
+def workload_twist_beam(nx=472, ny=60, nz=60, h=0.02, collisions=False):
+    """SURVEY.md §8(d) cfg 4: regular hex grid split into 6 Kuhn tets per cell, both end caps driven by Rotator deformers
+    (+-pi/4 rad/s about x), NeoHookean mu=5e3 lambda=1e5 density 100 damping 1e-6, gravity 0, 5 substeps x 20 iterations."""
+    verts, tets = meshio.kuhn_beam(nx, ny, nz, h=h, origin=(0.0, 1.0, 0.0))
+    colors = meshio.kuhn_coloring(nx, ny, nz)
+    phys = capi.default_physics_params(gravity=[0, 0, 0], numSubsteps=5, iterations=20, collisionStiffness=2e4,
+                                       intermediateCollisionIterations=5 if collisions else -1,
+                                       worldBoundsMin=[-100, -100, -100], worldBoundsMax=[100, 100, 100])
+    col = capi.default_collision_params(allowDCD=1 if collisions else 0, allowCCD=0)
+    obj = capi.default_object_params(miu=5e3, lmbd=1e5, density=100, dampingHydrostatic=1e-6, dampingDeviatoric=1e-6)
+    gx = np.arange(len(verts)) // ((ny + 1) * (nz + 1))
+    left = np.nonzero(gx == 0)[0].astype(np.int32)
+    right = np.nonzero(gx == nx)[0].astype(np.int32)
+    cy, cz = 1.0 + 0.5 * ny * h, 0.5 * nz * h
+    deformers = [("rotator", left, (0.0, cy, cz), (1.0, 0.0, 0.0), np.pi / 4, -1.0),
+                 ("rotator", right, (0.0, cy, cz), (1.0, 0.0, 0.0), -np.pi / 4, -1.0)]
+    name = f"twist_beam {nx}x{ny}x{nz} cells ({len(tets)} tets, {len(verts)} verts), 5 substeps x 20 iters, 4 colours"
+    return dict(name=name, meshes=[(verts, tets, obj, colors, np.zeros(0, np.int32))], phys=phys, col=col, deformers=deformers)
+
+
+def build_scene(cls, wl, **kw):
+    s = cls(wl["phys"], wl["col"], **kw)
+    for v, t, obj, colors, fixed in wl["meshes"]:
+        s.add_tet_mesh(v, t, obj, colors, fixed)
+    for d in wl["deformers"]:
+        if d[0] == "rotator":
+            s.add_rotator(0, d[1], d[2], d[3], d[4], d[5])
+        else:
+            s.add_translator(0, d[1], d[2], d[3])
+    s.finalize()
+    return s
+
+
+WORKLOADS = {
+    "twist_beam_10m": lambda: workload_twist_beam(472, 60, 60),
+    "twist_beam_1m": lambda: workload_twist_beam(59, 60, 60),
+    "twist_beam_small": lambda: workload_twist_beam(24, 12, 12),
+}
+
+
+# --------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.samples, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 8:
+                self.samples.append(f)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        mx = [float(s[2]) for s in self.samples if s[2].replace(".", "").isdigit()]
+        reasons = set()
+        for s in self.samples:
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------------- CPU arm
+def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
+    """Time the CPU oracle on a bounded sample of the workload: a beam of the same cross-section and material, 1/8 of the
+    length, one frame (5 substeps x 20 iterations); iterations are reduced if one substep already exceeds the budget."""
+    from oracle.binding import OracleScene
+    sample_wl = workload_twist_beam(59, 60, 60) if "10m" in wl_name or "1m" in wl_name else WORKLOADS[wl_name]()
+    t0 = time.time()
+    o = build_scene(OracleScene, sample_wl, threads=threads)
+    setup = time.time() - t0
+    # calibrate with one iteration-only call, then run as many whole frames as fit
+    o.reset_stats()
+    t0 = time.time()
+    o.run_iterations(2)
+    t_it = (time.time() - t0) / 2
+    per_frame = t_it * sample_wl["phys"].numSubsteps * sample_wl["phys"].iterations
+    frames = max(1, int(max_seconds / max(per_frame, 1e-9)))
+    frames = min(frames, 3)
+    o.reset_stats()
+    t0 = time.time()
+    if per_frame > 2 * max_seconds:
+        n_it = max(2, int(max_seconds / t_it))
+        o.run_iterations(n_it)
+        what = f"{n_it} iterations"
+    else:
+        o.run_frames(frames)
+        what = f"{frames} frame(s)"
+    dt = time.time() - t0
+    st = o.stats()
+    return {"value": st["vertexSolves"] / dt, "unit": "vertex-solves/s", "cores": o.num_threads, "kind": "port",
+            "sample": f"{sample_wl['name']}: {what} in {dt:.1f}s (setup {setup:.1f}s), oracle = CPU restatement of "
+                      f"VBDPhysics::runStep_hybridCollisionHandling with std::thread pool"}, st["vertexSolves"], dt
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = WORKLOADS[args.workload]()
+    vals, tot_solves, tot_t = [], 0, 0.0
+    base = None
+    for i in range(args.warmup + args.steps):
+        # each step is a bounded sample (the CPU cannot run the full step in minutes); keep them short
+        base, solves, dt = cpu_baseline(args.workload, max_seconds=max(4.0, 40.0 / max(1, args.steps + args.warmup)))
+        if i >= args.warmup:
+            tot_solves += solves; tot_t += dt
+    value = tot_solves / tot_t
+    base["value"] = value
+    out = {"impl": "reference", "metric": "VBD vertex-solves/sec", "value": value, "unit": "vertex-solves/s", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": wl["name"], "parallelism": f"cpu{base['cores']}"},
+           "cpu_baseline": base, "e2e": {"value": value, "unit": "vertex-solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="twist_beam_10m", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-steps", type=int, default=1, help="extra untimed steps with per-kernel CUDA events for the roofline")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+
+    t0 = time.time()
+    wl = WORKLOADS[args.workload]()
+    if world > 1:
+        from gaia_b200 import multigpu
+        scene = multigpu.build_partitioned_scene(wl, rank, world, local_rank)
+    else:
+        scene = build_scene(capi.Scene, wl, device=local_rank)
+    log(f"[bench] rank {rank}: scene '{wl['name']}' built in {time.time() - t0:.1f}s")
+    stream = torch.cuda.ExternalStream(scene.cuda_stream, device=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(n):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        barrier()
+        return ms
+
+    step = lambda: scene.run_frames(1)  # noqa: E731
+    for _ in range(args.warmup):
+        step()
+    scene.synchronize()
+    scene.reset_stats()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    ms = timed(step, args.steps)
+    clk = clocks.stop()
+    st = scene.stats()
+    solves = st["vertexSolves"]
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([solves], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        solves = float(t.item())
+    value = solves / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers
+    nV = scene.total_vertices
+    pos_h = scene.all_positions()
+    vel_h = np.zeros_like(pos_h)
+
+    def e2e_step():
+        scene.set_all_state(pos_h, vel_h)     # H2D of this step's inputs (pinned staging inside the library)
+        scene.run_frames(1)
+        scene.all_positions(out=pos_h)        # D2H of this step's result
+
+    e2e_step()
+    scene.reset_stats()
+    t_wall0 = time.time()
+    ms_e2e = timed(e2e_step, args.steps)
+    wall_e2e = time.time() - t_wall0
+    st2 = scene.stats()
+    solves2 = st2["vertexSolves"]
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([solves2], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        solves2 = float(t.item())
+    e2e = {"value": solves2 / (ms_e2e * 1e-3), "unit": "vertex-solves/s", "h2d_bytes_per_step": int(2 * nV * 12),
+           "d2h_bytes_per_step": int(nV * 12), "wall_ms_per_step": 1e3 * wall_e2e / args.steps}
+
+    # ---- roofline of the dominant kernel: per-launch CUDA events on the launching stream (untimed extra steps)
+    roof = None
+    if rank == 0:
+        scene.reset_stats()
+        scene.set_profiling(True)
+        for _ in range(max(1, args.profile_steps)):
+            scene.run_frames(1)
+        scene.synchronize()
+        sp = scene.stats()
+        scene.set_profiling(False)
+        k_ms = sp["timeCsmpMaterialSolve"]
+        launches = sp["colourSweeps"]
+        alg_bytes = sp["algorithmicBytes"]
+        achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        roof = {"kernel": "k_solve_colour", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes / max(1, launches), "avg_launch_us": 1e3 * k_ms / max(1, launches),
+                "launches_profiled": launches, "kernel_share_of_step": (k_ms / max(1, args.profile_steps)) / (ms / args.steps)}
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            try:
+                with open(tpath) as f:
+                    tj = json.load(f)
+                roof["traffic"] = tj.get(args.workload, {}).get("dram_bytes_per_launch")
+            except (OSError, ValueError):
+                pass
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu, _, _ = cpu_baseline(args.workload)
+
+    if rank == 0:
+        out = {"metric": "VBD vertex-solves/sec", "value": value, "unit": "vertex-solves/s", "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+               "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": wl["name"], "parallelism": f"x-slab partition over {world} GPU(s)" if world > 1 else "1 GPU",
+                          "l2": "inputs larger than L2 (incidence streams 1.3 GB vs 126 MB), no flush needed",
+                          "sim_steps_per_s": st["substeps"] / (ms * 1e-3), "frames_per_s": args.steps / (ms * 1e-3)},
+               "clocks": clk, "e2e": e2e, "gpu_launches": int(st["kernelLaunches"]), "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(out), flush=True)
+    scene.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -144,6 +144,8 @@ def bind_scene_api(lib, prefix):
     FP, IP = C.POINTER(C.c_float), C.POINTER(C.c_int32)
     sig = {
         "add_tet_mesh": ([P, C.c_int32, C.c_int32, FP, IP, C.POINTER(ObjectParams), C.c_int32, IP, IP, C.c_int32, IP], C.c_int),
+        "add_rotator": ([P, C.c_int, IP, C.c_int32, FP, FP, C.c_double, C.c_double], C.c_int),
+        "add_translator": ([P, C.c_int, IP, C.c_int32, FP, C.c_double], C.c_int),
         "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
         "frame_id": ([P], C.c_int), "num_meshes": ([P], C.c_int),
         "mesh_sizes": ([P, C.c_int, IP, IP, IP, IP], C.c_int),
@@ -188,6 +190,14 @@ class SceneBase:
         fx = _i32(np.asarray(fixed, np.int32))
         return self._call("add_tet_mesh", xyz.shape[0], tets.shape[0], _fp(xyz), _ip(tets), C.byref(obj),
                           len(colors), _ip(offs), _ip(cv), len(fx), _ip(fx))
+
+    def add_rotator(self, mesh, verts, origin, axis, angular_velocity, end_time=-1.0):
+        v = _i32(verts); o = _f32(origin); a = _f32(axis)
+        self._call("add_rotator", mesh, _ip(v), len(v), _fp(o), _fp(a), float(angular_velocity), float(end_time))
+
+    def add_translator(self, mesh, verts, speed, end_time=-1.0):
+        v = _i32(verts); sp = _f32(speed)
+        self._call("add_translator", mesh, _ip(v), len(v), _fp(sp), float(end_time))
 
     def finalize(self):
         self._call("finalize")

@@ -99,6 +99,32 @@ int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT, const float* 
     return m.id;
 }
 
+static int add_deformer(gaia_handle* h, int type, int mesh, const int32_t* verts, int32_t n, const float* origin, const float* axis,
+                        const float* speed, double w, double endTime) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (s.finalized) return fail(s, GAIA_ERR_STATE, "deformers must be added before finalize");
+    if (mesh < 0 || mesh >= (int)s.meshes.size() || n < 0 || (n && !verts)) return fail(s, GAIA_ERR_INVALID_ARG, "bad deformer argument");
+    HostMesh& m = s.meshes[mesh];
+    for (int i = 0; i < n; i++) if (verts[i] < 0 || verts[i] >= m.nV) return fail(s, GAIA_ERR_INVALID_ARG, "deformer vertex out of range");
+    Deformer* d = new Deformer();
+    d->type = type; d->mesh = mesh; d->verts.assign(verts, verts + n); d->angularVelocity = w; d->endTime = endTime;
+    for (int k = 0; k < 3; k++) { if (origin) d->origin[k] = origin[k]; if (axis) d->axis[k] = axis[k]; if (speed) d->speed[k] = speed[k]; }
+    for (int i = 0; i < n; i++)                              // setFixed (VBDDeformer.h:20-43)
+        if (!m.fixedMask[verts[i]]) { m.fixedMask[verts[i]] = 1; m.fixedPoints.push_back(verts[i]); }
+    s.deformers.push_back(d);
+    return GAIA_OK;
+}
+int gaia_b200_add_rotator(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, const float origin[3], const float axis[3],
+                          double angularVelocity, double rotationEndTime) {
+    if (!origin || !axis) return GAIA_ERR_INVALID_ARG;
+    return add_deformer(h, 0, mesh, verts, n, origin, axis, nullptr, angularVelocity, rotationEndTime);
+}
+int gaia_b200_add_translator(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3], double deformationEndTime) {
+    if (!speed) return GAIA_ERR_INVALID_ARG;
+    return add_deformer(h, 1, mesh, verts, n, nullptr, nullptr, speed, 0.0, deformationEndTime);
+}
+
 int gaia_b200_finalize(gaia_handle* h) {
     REQUIRE(h);
     Scene& s = h->s;
@@ -107,6 +133,8 @@ int gaia_b200_finalize(gaia_handle* h) {
     cudaSetDevice(s.device);
     if (!host_finalize(s)) return GAIA_ERR_INVALID_ARG;
     cudaError_t e = device_upload(s);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    e = upload_deformers(s);
     if (e != cudaSuccess) return cuda_fail(s, e);
     e = collision_init(s);
     if (e != cudaSuccess) return cuda_fail(s, e);

@@ -245,8 +245,45 @@ bool host_finalize(Scene& s) {
     for (int64_t i = 0; i < vb; i++) s.h_incOff[i + 1] += s.h_incOff[i];
     const int64_t nInc = s.h_incOff[vb];
     s.nInc = nInc;
-    s.h_incA.resize(4 * (size_t)nInc);
-    s.h_incB.resize(4 * (size_t)nInc);
+    s.h_incIdx.resize((size_t)nInc);
+    s.h_incW.resize(4 * (size_t)nInc);
+    // distinct neighbours of every vertex (sorted ids, ascending) -> local slots referenced by the incidence records
+    s.h_nbOff.assign(vb + 1, 0);
+    {
+        // incidence CSR (mesh-local tet id, local vertex k) filled in ascending tet order
+        std::vector<int32_t> incTet((size_t)nInc);
+        std::vector<int32_t> fillAt(s.h_incOff.begin(), s.h_incOff.end() - 1);
+        for (auto& m : M)
+            for (int t = 0; t < m.nT; t++)
+                for (int k = 0; k < 4; k++) incTet[fillAt[m.sortedId[m.tets[4 * (size_t)t + k]]]++] = 4 * t + k;
+        std::vector<int32_t> tmp;
+        s.h_nbList.reserve((size_t)nInc);
+        // vertices are visited in sorted order so nbList is laid out exactly like the device reads it
+        for (int64_t sid = 0; sid < vb; sid++) {
+            const int64_t orig = s.sortedToOrig[sid];
+            // find mesh by base (meshes are few; linear scan from the back is fine, binary search for many)
+            size_t lo = 0, hi = M.size();
+            while (hi - lo > 1) { size_t mid = (lo + hi) / 2; if (M[mid].vertBase <= orig) lo = mid; else hi = mid; }
+            const HostMesh& m = M[lo];
+            tmp.clear();
+            for (int32_t j = s.h_incOff[sid]; j < s.h_incOff[sid + 1]; j++) {
+                const int t = incTet[j] >> 2, k = incTet[j] & 3;
+                for (int q = 0; q < 4; q++) if (q != k) tmp.push_back(m.sortedId[m.tets[4 * (size_t)t + q]]);
+            }
+            std::sort(tmp.begin(), tmp.end());
+            tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
+            if (s.h_incOff[sid + 1] - s.h_incOff[sid] > 65535) { s.err = "a vertex has more than 65535 incident tets"; return false; }
+            if (tmp.size() > 255) { s.err = "a vertex has more than 255 distinct neighbours"; return false; }
+            s.h_nbOff[sid + 1] = s.h_nbOff[sid] + (int32_t)tmp.size();
+            s.h_nbList.insert(s.h_nbList.end(), tmp.begin(), tmp.end());
+        }
+    }
+    s.nNb = s.h_nbOff[vb];
+    auto local_slot = [&](int32_t owner, int32_t nb) {
+        const int32_t* b0 = &s.h_nbList[s.h_nbOff[owner]];
+        const int32_t* e0 = &s.h_nbList[s.h_nbOff[owner + 1]];
+        return (uint32_t)(std::lower_bound(b0, e0, nb) - b0);
+    };
     std::vector<int32_t> cursor(s.h_incOff.begin(), s.h_incOff.end() - 1);
     for (auto& m : M) {
         m.nSolved = 0; m.nIncSolved = 0;
@@ -270,15 +307,14 @@ bool host_finalize(Scene& s) {
                 double m0[3], w[3];
                 for (int c = 0; c < 3; c++) m0[c] = -(Bi[0][c] + Bi[1][c] + Bi[2][c]);
                 for (int r = 0; r < 3; r++) w[r] = Bi[r][0] * m0[0] + Bi[r][1] * m0[1] + Bi[r][2] * m0[2];
-                const double mm = m0[0] * m0[0] + m0[1] * m0[1] + m0[2] * m0[2];
+                // the record carries A*w' and det(B') = 1/(6A) with A the reference's float rest volume:
+                //   A*mu*F m0 = mu*Ds'(A w');  A*|m0|^2 = -(1,1,1).(A w');  A*g = -n/6;  A*g g^T = det(B')/6 * n n^T
+                const double vol = (double)m.restVol[t];
                 const int32_t sOwn = m.sortedId[own];
                 const int32_t at = cursor[sOwn]++;
-                int32_t* ra = &s.h_incA[4 * (size_t)at];
-                ra[0] = m.sortedId[ia]; ra[1] = m.sortedId[ib]; ra[2] = m.sortedId[ic];
-                const float vol = m.restVol[t];
-                std::memcpy(&ra[3], &vol, 4);
-                float* rb = &s.h_incB[4 * (size_t)at];
-                rb[0] = (float)w[0]; rb[1] = (float)w[1]; rb[2] = (float)w[2]; rb[3] = (float)mm;
+                float* rw = &s.h_incW[4 * (size_t)at];
+                rw[0] = (float)(vol * w[0]); rw[1] = (float)(vol * w[1]); rw[2] = (float)(vol * w[2]); rw[3] = (float)(1.0 / (6.0 * vol));
+                s.h_incIdx[at] = local_slot(sOwn, m.sortedId[ia]) | (local_slot(sOwn, m.sortedId[ib]) << 8) | (local_slot(sOwn, m.sortedId[ic]) << 16);
             }
         }
         for (int v = 0; v < m.nV; v++)

@@ -22,6 +22,17 @@ struct DevBuf {
 
 struct CollisionState;   // collision.cu
 
+// VBDDeformer.h: Rotator / Translator evaluated on the device
+struct Deformer {
+    int type = 0;                      // 0 rotator, 1 translator
+    int mesh = 0;
+    std::vector<int32_t> verts;        // original vertex ids
+    float origin[3] = {0, 0, 0}, axis[3] = {0, 0, 0}, speed[3] = {0, 0, 0};
+    double angularVelocity = 0, endTime = -1;
+    DevBuf<int32_t> sid;               // sorted ids
+    DevBuf<float4> root, rootP;        // rotator: root, RootP; translator: original position in root
+};
+
 // what the colour-solve kernel needs to see of the contact data (filled by collision.cu)
 struct ContactView {
     const int32_t* contactOfVertex;   // sorted vertex -> contact slot or -1
@@ -48,8 +59,9 @@ struct Scene {
     std::vector<int32_t> sortedToOrig;          // sorted id -> global original index (vertBase + v)
     int64_t nVerts = 0, nTets = 0, nSurfVerts = 0, nSurfFaces = 0, nInc = 0;
     // host staging of the incidence streams (freed after upload)
-    std::vector<int32_t> h_incOff, h_incA;
-    std::vector<float> h_incB;
+    std::vector<int32_t> h_incOff, h_nbOff, h_nbList;
+    std::vector<uint32_t> h_incIdx;   // packed local neighbour slots a | b<<8 | c<<16
+    std::vector<float> h_incW;        // 4 floats per incidence: A*w'.xyz, det(B')
 
     // ---- device state (sorted order)
     cudaStream_t stream = nullptr;
@@ -57,8 +69,11 @@ struct Scene {
     DevBuf<float> mass;
     DevBuf<int32_t> info;          // meshId | fixed<<31
     DevBuf<int32_t> incOff;
-    DevBuf<int4> incA;
-    DevBuf<float4> incB;
+    DevBuf<float4> incW;           // per incidence: (A w'.x, A w'.y, A w'.z, det B')
+    DevBuf<uint32_t> incIdx;       // per incidence: local neighbour slots a | b<<8 | c<<16
+    DevBuf<int32_t> nbOff, nbList; // per vertex: distinct neighbour vertices (sorted ids)
+    DevBuf<int4> vtx;              // per vertex header: {incOff, nbOff, nInc | nNb << 16, meshId | fixed << 31}
+    int64_t nNb = 0;
     DevBuf<int32_t> sorted2orig, orig2sorted;
     DevBuf<MeshParamsDev> meshParams;
     DevBuf<float4> ioStage;        // original-order staging for get/set
@@ -71,6 +86,8 @@ struct Scene {
     size_t pinnedIOBytes = 0;
 
     CollisionState* cs = nullptr;
+    std::vector<Deformer*> deformers;
+    float curTime = 0.f;                // BasePhysicFramework::curTime (FloatingType)
 
     // statistics / profiling
     gaia_stats stats;
@@ -89,6 +106,7 @@ bool host_finalize(Scene& s);
 
 // solve.cu
 cudaError_t device_upload(Scene& s);
+cudaError_t upload_deformers(Scene& s);
 void sync_mesh_params(Scene& s);
 cudaError_t run_substeps(Scene& s, int nSubsteps);                 // one frame's worth of substeps
 cudaError_t run_iterations_only(Scene& s, int nIters);

@@ -64,63 +64,28 @@ __device__ __forceinline__ void boundary_friction(float mu, float lambda, float 
     }
 }
 
-template <int L, bool HAS_CONTACTS>
-__global__ void __launch_bounds__(kBlock)
-k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
-               const float* __restrict__ mass, const int32_t* __restrict__ info, const int32_t* __restrict__ incOff,
-               const int4* __restrict__ incA, const float4* __restrict__ incB, const MeshParamsDev* __restrict__ mp,
-               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags) {
-    const int tid = blockIdx.x * kBlock + threadIdx.x;
-    const int lane = tid & (L - 1);
-    const int s = vBegin + tid / L;
-    const bool inRange = s < vEnd;
-    int inf = inRange ? __ldg(info + s) : (int)0x80000000;
-    const bool fixed = inf < 0;
-    const int meshId = inf & 0x00FFFFFF;
-    float miu = 0.f, lmbd = 0.f, aConst = 0.f, dampH = 0.f, dampD = 0.f;
-    bool active = inRange && !fixed;
-    if (active) {
-        const MeshParamsDev* P = mp + meshId;
-        active = P->activeSolve != 0;
-        miu = P->miu; lmbd = P->lmbd; aConst = P->a; dampH = P->dampH; dampD = P->dampD;
-    }
-    const float4* posRO = pos;   // neighbour gathers only touch other colours: read-only for this launch
-    float fx = 0.f, fy = 0.f, fz = 0.f, s1 = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
-    float3 x = make_float3(0.f, 0.f, 0.f);
-    if (active) {
-        x = f3(pos[s]);
-        const int b = __ldg(incOff + s), e = __ldg(incOff + s + 1);
-        for (int j = b + lane; j < e; j += L) {
-            const int4 ia = ld_stream(incA + j);
-            const float4 wb = ld_stream(incB + j);
-            const float3 pa = f3(__ldg(posRO + ia.x)) - x;
-            const float3 pb = f3(__ldg(posRO + ia.y)) - x;
-            const float3 pc = f3(__ldg(posRO + ia.z)) - x;
-            const float A = __int_as_float(ia.w);
-            const float3 bc = cross3(pb, pc);
-            const float3 n = bc + cross3(pc, pa) + cross3(pa, pb);     // cof(Ds') * (1,1,1)
-            const float detB = 1.f / (6.f * A);
-            const float detF = dot3(pa, bc) * detB;
-            const float3 g = (-detB) * n;                              // cof(F) m_0
-            const float3 Fw = wb.x * pa + wb.y * pb + wb.z * pc;       // F m_0 = Ds' (B'B'^T e_0')
-            const float lk = lmbd * (detF - aConst);
-            fx += A * (miu * Fw.x + lk * g.x);
-            fy += A * (miu * Fw.y + lk * g.y);
-            fz += A * (miu * Fw.z + lk * g.z);
-            s1 += A * wb.w;
-            g00 += A * g.x * g.x; g01 += A * g.x * g.y; g02 += A * g.x * g.z;
-            g11 += A * g.y * g.y; g12 += A * g.y * g.z; g22 += A * g.z * g.z;
-        }
-    }
-#pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) {
-        fx += __shfl_xor_sync(0xffffffffu, fx, o); fy += __shfl_xor_sync(0xffffffffu, fy, o); fz += __shfl_xor_sync(0xffffffffu, fz, o);
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-        g00 += __shfl_xor_sync(0xffffffffu, g00, o); g01 += __shfl_xor_sync(0xffffffffu, g01, o); g02 += __shfl_xor_sync(0xffffffffu, g02, o);
-        g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
-    }
-    if (!active || lane != 0) return;
+__device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
 
+static const int kNbMax = 32;              // neighbour positions staged in shared memory per vertex (more spill to global gathers)
+static const int kNbStride = kNbMax + 1;   // +1 float4 of padding de-correlates the rows' banks
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+    return r;
+}
+
+// The vertex-level part of VBDStepWithCollision after the incident-tet sums are known: damping, inertia, world box +
+// friction, contacts, 3x3 solve, in-place update. Runs with one vertex per thread (all lanes busy).
+template <bool HAS_CONTACTS>
+__device__ __forceinline__ void solve_tail(int s, float3 x, float4 ys, float miu, float lmbd, float dampH, float dampD,
+                                           float fx, float fy, float fz, float s1, float g00, float g01, float g02, float g11, float g12, float g22,
+                                           float4* pos, const float4* __restrict__ prev, const StepParamsDev& sp, int applyFriction,
+                                           const ContactView& cv, int32_t* errFlags) {
     // elastic force and Hessian: f = -(mu*fmu + lmbd*flm), H = mu*s1*I + lmbd*G
     float F0 = -fx, F1 = -fy, F2 = -fz;
     float hd = miu * s1;
@@ -142,12 +107,11 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
     }
     // inertia
     {
-        const float m = __ldg(mass + s);
-        const float3 y = f3(__ldg(inertia + s));
+        const float m = ys.w;
         const float w = m * sp.dtSqrReciprocal;
-        F0 += (m * (y.x - x.x)) * sp.dtSqrReciprocal;
-        F1 += (m * (y.y - x.y)) * sp.dtSqrReciprocal;
-        F2 += (m * (y.z - x.z)) * sp.dtSqrReciprocal;
+        F0 += (m * (ys.x - x.x)) * sp.dtSqrReciprocal;
+        F1 += (m * (ys.y - x.y)) * sp.dtSqrReciprocal;
+        F2 += (m * (ys.z - x.z)) * sp.dtSqrReciprocal;
         h00 += w; h11 += w; h22 += w;
     }
     // world-box penalty + friction, per violated axis (CPU semantics)
@@ -222,10 +186,135 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
     }
 }
 
+// One block owns kBlock consecutive vertices of the colour and walks them in ROUNDS = L rounds of kBlock/L vertices:
+// in a round each vertex is served by a sub-warp of L lanes (incident-tet sums), the sums are parked in shared memory,
+// and after the last round every thread finishes ONE vertex (solve_tail) — so the scalar tail runs at full SIMT width.
+template <int L, bool HAS_CONTACTS, int PF, int ROUNDS>
+__global__ void __launch_bounds__(kBlock, 4)
+k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
+               const int4* __restrict__ vtx, const float4* __restrict__ incW, const uint32_t* __restrict__ incIdx,
+               const int32_t* __restrict__ nbList, const MeshParamsDev* __restrict__ mp,
+               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags) {
+    constexpr int VPR = kBlock / L;        // vertices per round
+    constexpr int VPB = VPR * ROUNDS;      // vertices per block
+    extern __shared__ float4 smem4[];
+    float4* smNb = smem4;                                   // [VPR][kNbStride] neighbour positions relative to the owner
+    float* acc = (float*)(smem4 + VPR * kNbStride);         // [10][VPB] incident-tet sums
+    const int lane = threadIdx.x & (L - 1);
+    const int sub = threadIdx.x / L;
+    const uint32_t rowAddr = (uint32_t)__cvta_generic_to_shared(smNb + sub * kNbStride);
+    float4* myNb = smNb + sub * kNbStride;
+    const int blockBase = vBegin + blockIdx.x * VPB;
+    const float4* posRO = pos;   // neighbour gathers only touch other colours: read-only for this launch
+
+#pragma unroll 1
+    for (int r = 0; r < ROUNDS; r++) {
+        const int slot = r * VPR + sub;
+        const int s = blockBase + slot;
+        const bool inRange = s < vEnd;
+        // ---- level 0 of the dependency chain: everything that only needs s
+        int4 va = make_int4(0, 0, 0, (int)0x80000000);      // {incOff, nbOff, nInc | nNb << 16, meshId | fixed << 31}
+        float4 xs = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (inRange) { va = __ldg(vtx + s); xs = pos[s]; }
+        bool active = inRange && va.w >= 0;
+        float miu = 0.f, lmbd = 0.f, aConst = 0.f;
+        if (active) {
+            const MeshParamsDev* P = mp + (va.w & 0x00FFFFFF);
+            active = P->activeSolve != 0;
+            miu = P->miu; lmbd = P->lmbd; aConst = P->a;
+        }
+        float fx = 0.f, fy = 0.f, fz = 0.f, s1 = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
+        const float3 x = f3(xs);
+        const int e = va.x + (active ? (va.z & 0xFFFF) : 0), nb0 = va.y;
+        const int nnbAll = active ? (va.z >> 16) : 0;
+        // ---- level 1: first incidence records and the neighbour ids (both only depend on va)
+        int j = va.x + lane;
+        float4 W = make_float4(0.f, 0.f, 0.f, 0.f), W1 = W, W2 = W;
+        uint32_t I = 0, I1 = 0, I2 = 0;
+        if (j < e) { W = ld_stream(incW + j); I = ld_stream(incIdx + j); }
+        if (PF >= 1 && j + L < e) { W1 = ld_stream(incW + j + L); I1 = ld_stream(incIdx + j + L); }
+        if (PF >= 2 && j + 2 * L < e) { W2 = ld_stream(incW + j + 2 * L); I2 = ld_stream(incIdx + j + 2 * L); }
+        {
+            const int nnb = min(nnbAll, kNbMax);
+            int idx[kNbMax / L];
+#pragma unroll
+            for (int q = 0; q < kNbMax / L; q++) { const int i = lane + q * L; idx[q] = (i < nnb) ? (int)ld_stream((const uint32_t*)nbList + nb0 + i) : -1; }
+            // ---- level 2: stage the distinct neighbour positions once (each is used by ~5 incident tets); L2 hits
+#pragma unroll
+            for (int q = 0; q < kNbMax / L; q++)
+                if (idx[q] >= 0) {
+                    const float4 p = __ldg(posRO + idx[q]);
+                    myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
+                }
+        }
+        __syncwarp();
+        const float lm6 = lmbd * (-1.f / 6.f);
+        for (; j < e; j += L) {
+            // software pipeline: the record PF+1 iterations ahead is requested before this one is consumed
+            float4 Wn = W; uint32_t In = 0;
+            const int jn = j + (PF + 1) * L;
+            if (jn < e) { Wn = ld_stream(incW + jn); In = ld_stream(incIdx + jn); }
+            float3 pa, pb, pc;
+            if (nnbAll <= kNbMax) {
+                pa = f3(lds128(rowAddr + ((I & 0xFFu) << 4)));
+                pb = f3(lds128(rowAddr + ((I >> 4) & 0xFF0u)));
+                pc = f3(lds128(rowAddr + ((I >> 12) & 0xFF0u)));
+            } else {
+                pa = f3(__ldg(posRO + __ldg(nbList + nb0 + (I & 255)))) - x;
+                pb = f3(__ldg(posRO + __ldg(nbList + nb0 + ((I >> 8) & 255)))) - x;
+                pc = f3(__ldg(posRO + __ldg(nbList + nb0 + ((I >> 16) & 255)))) - x;
+            }
+            // n = cof(Ds')(1,1,1) = b x c + c x a + a x b = (b-a) x (c-a);  det(Ds') = a . n;  A*g = -n/6
+            const float3 n = cross3(pb - pa, pc - pa);
+            const float k = dot3(pa, n) * W.w - aConst;                // det F - a,  det F = det(Ds') det(B')
+            const float c6 = lm6 * k;
+            fx += miu * (W.x * pa.x + W.y * pb.x + W.z * pc.x) + c6 * n.x;   // A*(mu F m0 + lmbd k g)
+            fy += miu * (W.x * pa.y + W.y * pb.y + W.z * pc.y) + c6 * n.y;
+            fz += miu * (W.x * pa.z + W.y * pb.z + W.z * pc.z) + c6 * n.z;
+            s1 -= (W.x + W.y) + W.z;                                   // A*|m0|^2
+            const float nx = W.w * n.x, ny = W.w * n.y, nz = W.w * n.z;       // 6 A g g^T = det(B') n n^T
+            g00 += nx * n.x; g01 += nx * n.y; g02 += nx * n.z; g11 += ny * n.y; g12 += ny * n.z; g22 += nz * n.z;
+            if (PF == 0) { W = Wn; I = In; }
+            else if (PF == 1) { W = W1; I = I1; W1 = Wn; I1 = In; }
+            else { W = W1; I = I1; W1 = W2; I1 = I2; W2 = Wn; I2 = In; }
+        }
+#pragma unroll
+        for (int o = L / 2; o > 0; o >>= 1) {
+            fx += __shfl_xor_sync(0xffffffffu, fx, o); fy += __shfl_xor_sync(0xffffffffu, fy, o); fz += __shfl_xor_sync(0xffffffffu, fz, o);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            g00 += __shfl_xor_sync(0xffffffffu, g00, o); g01 += __shfl_xor_sync(0xffffffffu, g01, o); g02 += __shfl_xor_sync(0xffffffffu, g02, o);
+            g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
+        }
+        if (lane == 0) {
+            acc[0 * VPB + slot] = fx; acc[1 * VPB + slot] = fy; acc[2 * VPB + slot] = fz; acc[3 * VPB + slot] = s1;
+            acc[4 * VPB + slot] = g00; acc[5 * VPB + slot] = g01; acc[6 * VPB + slot] = g02;
+            acc[7 * VPB + slot] = g11; acc[8 * VPB + slot] = g12; acc[9 * VPB + slot] = g22;
+        }
+        __syncwarp();      // the row of smNb is rewritten by the next round
+    }
+    __syncthreads();
+    // ---- transposed tail: thread t finishes vertex blockBase + t
+    for (int slot = threadIdx.x; slot < VPB; slot += kBlock) {
+        const int s = blockBase + slot;
+        if (s >= vEnd) continue;
+        const int4 va = __ldg(vtx + s);
+        if (va.w < 0) continue;
+        const MeshParamsDev* P = mp + (va.w & 0x00FFFFFF);
+        if (!P->activeSolve) continue;
+        const float4 xs = pos[s];
+        const float4 ys = __ldg(inertia + s);
+        solve_tail<HAS_CONTACTS>(s, f3(xs), ys, P->miu, P->lmbd, P->dampH, P->dampD,
+                                 acc[0 * VPB + slot], acc[1 * VPB + slot], acc[2 * VPB + slot], acc[3 * VPB + slot],
+                                 acc[4 * VPB + slot] * (1.f / 6.f), acc[5 * VPB + slot] * (1.f / 6.f), acc[6 * VPB + slot] * (1.f / 6.f),
+                                 acc[7 * VPB + slot] * (1.f / 6.f), acc[8 * VPB + slot] * (1.f / 6.f), acc[9 * VPB + slot] * (1.f / 6.f),
+                                 pos, prev, sp, applyFriction, cv, errFlags);
+    }
+}
+
 // applyInitialStep for every vertex of every active mesh (one launch)
 __global__ void __launch_bounds__(kBlock)
 k_initial_step(int n, float4* __restrict__ pos, float4* __restrict__ prev, float4* __restrict__ inertia, const float4* __restrict__ vel,
-               float4* __restrict__ velPrev, float4* __restrict__ accel, const int32_t* __restrict__ info,
+               float4* __restrict__ velPrev, float4* __restrict__ accel, const int32_t* __restrict__ info, const float* __restrict__ mass,
                const MeshParamsDev* __restrict__ mp, const int32_t* __restrict__ meshSubsteps, StepParamsDev sp) {
     const int s = blockIdx.x * kBlock + threadIdx.x;
     if (s >= n) return;
@@ -256,7 +345,7 @@ k_initial_step(int n, float4* __restrict__ pos, float4* __restrict__ prev, float
     }
     if (inf < 0) v = make_float3(0.f, 0.f, 0.f);
     const float3 y = make_float3(__fadd_rn(x.x, __fmul_rn(dt, v.x)), __fadd_rn(x.y, __fmul_rn(dt, v.y)), __fadd_rn(x.z, __fmul_rn(dt, v.z)));
-    inertia[s] = make_float4(y.x, y.y, y.z, 0.f);
+    inertia[s] = make_float4(y.x, y.y, y.z, __ldg(mass + s));   // .w = lumped mass, read by the colour solve
     float3 xn = x;
     switch (type) {
         case 0: xn = y; break;
@@ -339,6 +428,25 @@ k_accelerate(int n, float4* __restrict__ pos, float4* __restrict__ pp, float4* _
     pIter[s] = x;
 }
 
+// DeformerRotator / DeformerTranslater (VBDDeformer.h:45-131, 133-177)
+struct Rot9 { float r[9]; };   // row-major
+__global__ void k_apply_rotator(int n, const int32_t* __restrict__ sid, const float4* __restrict__ root, const float4* __restrict__ rootP,
+                                Rot9 R, float4* __restrict__ pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 o = root[i], q = rootP[i];
+    const float x = __fadd_rn(__fadd_rn(__fmul_rn(R.r[0], q.x), __fmul_rn(R.r[1], q.y)), __fmul_rn(R.r[2], q.z));
+    const float y = __fadd_rn(__fadd_rn(__fmul_rn(R.r[3], q.x), __fmul_rn(R.r[4], q.y)), __fmul_rn(R.r[5], q.z));
+    const float z = __fadd_rn(__fadd_rn(__fmul_rn(R.r[6], q.x), __fmul_rn(R.r[7], q.y)), __fmul_rn(R.r[8], q.z));
+    pos[sid[i]] = make_float4(__fadd_rn(o.x, x), __fadd_rn(o.y, y), __fadd_rn(o.z, z), 0.f);
+}
+__global__ void k_apply_translator(int n, const int32_t* __restrict__ sid, const float4* __restrict__ p0, float3 d, float4* __restrict__ pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 o = p0[i];
+    pos[sid[i]] = make_float4(__fadd_rn(d.x, o.x), __fadd_rn(d.y, o.y), __fadd_rn(d.z, o.z), 0.f);
+}
+
 // sorted <-> original order transfers (xyz packed on the original side)
 __global__ void k_gather_xyz(int64_t count, int64_t origBegin, const float4* __restrict__ src, const int32_t* __restrict__ o2s, float* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -356,6 +464,7 @@ static inline int nblk(int64_t n, int per = kBlock) { return (int)((n + per - 1)
 
 Scene::~Scene() {
     collision_destroy(*this);
+    for (Deformer* d : deformers) delete d;
     if (pinnedIO) cudaFreeHost(pinnedIO);
     if (evA) cudaEventDestroy(evA);
     if (evB) cudaEventDestroy(evB);
@@ -391,7 +500,7 @@ cudaError_t device_upload(Scene& s) {
     CK(cudaEventCreate(&s.evA)); CK(cudaEventCreate(&s.evB));
     CK(s.pos.alloc(N + 1)); CK(s.prev.alloc(N + 1)); CK(s.inertia.alloc(N + 1)); CK(s.vel.alloc(N + 1));
     CK(s.mass.alloc(N)); CK(s.info.alloc(N)); CK(s.incOff.alloc(N + 1));
-    CK(s.incA.alloc(s.nInc)); CK(s.incB.alloc(s.nInc));
+    CK(s.incW.alloc(s.nInc)); CK(s.incIdx.alloc(s.nInc)); CK(s.nbOff.alloc(N + 1)); CK(s.nbList.alloc(s.nNb)); CK(s.vtx.alloc(N));
     CK(s.sorted2orig.alloc(N)); CK(s.orig2sorted.alloc(N));
     CK(s.meshParams.alloc(s.meshes.size())); CK(s.errFlags.alloc(8));
     CK(s.ioStage.alloc((size_t)(3 * N + 3) / 4 + 1));
@@ -430,13 +539,20 @@ cudaError_t device_upload(Scene& s) {
     CK(cudaMemcpyAsync(s.mass.p, hmass.data(), N * sizeof(float), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.info.p, hinfo.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.incOff.p, s.h_incOff.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.incA.p, s.h_incA.data(), s.nInc * sizeof(int4), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.incB.p, s.h_incB.data(), s.nInc * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.incW.p, s.h_incW.data(), s.nInc * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.incIdx.p, s.h_incIdx.data(), s.nInc * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+    std::vector<int4> hvtx(N);
+    for (int64_t i = 0; i < N; i++)
+        hvtx[i] = make_int4(s.h_incOff[i], s.h_nbOff[i], (s.h_incOff[i + 1] - s.h_incOff[i]) | ((s.h_nbOff[i + 1] - s.h_nbOff[i]) << 16), hinfo[i]);
+    CK(cudaMemcpyAsync(s.vtx.p, hvtx.data(), N * sizeof(int4), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.nbOff.p, s.h_nbOff.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.nbList.p, s.h_nbList.data(), s.nNb * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.sorted2orig.p, s.sortedToOrig.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.orig2sorted.p, o2s.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaStreamSynchronize(s.stream));
-    std::vector<int32_t>().swap(s.h_incA);
-    std::vector<float>().swap(s.h_incB);
+    std::vector<uint32_t>().swap(s.h_incIdx);
+    std::vector<float>().swap(s.h_incW);
+    std::vector<int32_t>().swap(s.h_nbList);
     // step constants
     StepParamsDev& sp = s.stepParams;
     sp.dt = s.dt; sp.dtSqrReciprocal = s.dtSqrReciprocal;
@@ -452,25 +568,42 @@ cudaError_t device_upload(Scene& s) {
 }
 
 
-static int g_lanes = 8;   // sub-warp width of the colour solve (tunable: GAIA_B200_LANES=4|8|16|32)
+static int g_lanes = 4;     // sub-warp width of the colour solve (GAIA_B200_LANES = 2|4|8)
+static int g_variant = 1;   // prefetch depth of the incidence stream (GAIA_B200_VARIANT = 0|1|2)
+
+template <int L, bool HC, int PF, int ROUNDS>
+static void launch_one(Scene& s, int vb, int ve, int applyFriction, const ContactView& cv) {
+    const int n = ve - vb;
+    const int vpb = (kBlock / L) * ROUNDS;
+    const size_t smem = (size_t)(kBlock / L) * kNbStride * sizeof(float4) + (size_t)10 * vpb * sizeof(float);
+    static bool attrSet = false;
+    if (!attrSet) { cudaFuncSetAttribute(k_solve_colour<L, HC, PF, ROUNDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attrSet = true; }
+    k_solve_colour<L, HC, PF, ROUNDS><<<nblk(n, vpb), kBlock, smem, s.stream>>>(
+        vb, ve, s.pos.p, s.prev.p, s.inertia.p, s.vtx.p, s.incW.p, s.incIdx.p, s.nbList.p,
+        s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p);
+}
 
 template <bool HC>
-static void launch_solve(Scene& s, int L, int vb, int ve, int applyFriction, const ContactView& cv) {
-    const int n = ve - vb;
-#define LAUNCH(LL) k_solve_colour<LL, HC><<<nblk((int64_t)n * LL), kBlock, 0, s.stream>>>( \
-        vb, ve, s.pos.p, s.prev.p, s.inertia.p, s.mass.p, s.info.p, s.incOff.p, s.incA.p, s.incB.p, s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p)
+static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int applyFriction, const ContactView& cv) {
+    // big colours: every block walks L rounds (full-width tail); small colours keep one round per block so the grid
+    // still covers all 148 SMs
+    const bool big = (int64_t)(ve - vb) >= (int64_t)148 * 8 * kBlock;
+#define BYVAR(LL) if (big) { if (variant == 0) launch_one<LL, HC, 0, LL>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, LL>(s, vb, ve, applyFriction, cv); } \
+                  else { if (variant == 0) launch_one<LL, HC, 0, 1>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 1>(s, vb, ve, applyFriction, cv); }
     switch (L) {
-        case 4: LAUNCH(4); break;
-        case 16: LAUNCH(16); break;
-        case 32: LAUNCH(32); break;
-        default: LAUNCH(8); break;
+        case 8: BYVAR(8); break;
+        default: BYVAR(4); break;
     }
-#undef LAUNCH
+#undef BYVAR
 }
 
 static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
     static bool envRead = false;
-    if (!envRead) { const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e); envRead = true; }
+    if (!envRead) {
+        const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e);
+        e = getenv("GAIA_B200_VARIANT"); if (e) g_variant = atoi(e);
+        envRead = true;
+    }
     const int G = (int)s.groupStart.size() - 1;
     const int N = (int)s.nVerts;
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
@@ -503,8 +636,8 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
             if (ve <= vb) continue;
             if (hasContacts) { CK(collision_update_infos(s, g)); }
             if (s.profiling) cudaEventRecord(s.evA, s.stream);
-            if (hasContacts) launch_solve<true>(s, g_lanes, vb, ve, applyFriction, cv);
-            else launch_solve<false>(s, g_lanes, vb, ve, applyFriction, cv);
+            if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
+            else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
             if (s.profiling) {
                 cudaEventRecord(s.evB, s.stream);
                 cudaEventSynchronize(s.evB);
@@ -532,19 +665,74 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
 
 static cudaError_t initial_step(Scene& s) {
     const int N = (int)s.nVerts;
-    k_initial_step<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.inertia.p, s.vel.p, s.velPrev.p, s.accel.p, s.info.p,
+    k_initial_step<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.inertia.p, s.vel.p, s.velPrev.p, s.accel.p, s.info.p, s.mass.p,
                                                    s.meshParams.p, s.meshSubsteps.p, s.stepParams);
     k_count_substeps<<<nblk((int64_t)s.meshes.size(), 128), 128, 0, s.stream>>>((int)s.meshes.size(), s.meshParams.p, s.meshSubsteps.p);
     s.stats.kernelLaunches += 2;
     return cudaGetLastError();
 }
 
+static cudaError_t apply_deformers(Scene& s) {
+    for (Deformer* d : s.deformers) {
+        const int n = (int)d->verts.size();
+        if (!n) continue;
+        double t = (double)s.curTime;
+        if (t >= d->endTime && d->endTime > 0) t = d->endTime;
+        if (d->type == 0) {
+            const double theta = t * d->angularVelocity;
+            const double ux = d->axis[0], uy = d->axis[1], uz = d->axis[2];
+            const double c = cos(theta), sn = sin(theta);
+            Rot9 R;
+            R.r[0] = (float)(c + ux * ux * (1 - c)); R.r[1] = (float)(ux * uy * (1 - c) - uz * sn); R.r[2] = (float)(ux * uz * (1 - c) + uy * sn);
+            R.r[3] = (float)(uy * ux * (1 - c) + uz * sn); R.r[4] = (float)(c + uy * uy * (1 - c)); R.r[5] = (float)(uy * uz * (1 - c) - ux * sn);
+            R.r[6] = (float)(uz * ux * (1 - c) - uy * sn); R.r[7] = (float)(uz * uy * (1 - c) + ux * sn); R.r[8] = (float)(c + uz * uz * (1 - c));
+            k_apply_rotator<<<nblk(n), kBlock, 0, s.stream>>>(n, d->sid.p, d->root.p, d->rootP.p, R, s.pos.p);
+        } else {
+            // speed * curTime + originalPos: Eigen casts the double scalar to float first
+            const float tf = (float)t;
+            k_apply_translator<<<nblk(n), kBlock, 0, s.stream>>>(n, d->sid.p, d->root.p, make_float3(d->speed[0] * tf, d->speed[1] * tf, d->speed[2] * tf), s.pos.p);
+        }
+        s.stats.kernelLaunches++;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t upload_deformers(Scene& s) {
+    for (Deformer* d : s.deformers) {
+        const HostMesh& m = s.meshes[d->mesh];
+        const int n = (int)d->verts.size();
+        std::vector<int32_t> sid(n);
+        std::vector<float4> a(n), b(n);
+        for (int i = 0; i < n; i++) {
+            const int v = d->verts[i];
+            sid[i] = m.sortedId[v];
+            const float P[3] = {m.pos0[3 * (size_t)v], m.pos0[3 * (size_t)v + 1], m.pos0[3 * (size_t)v + 2]};
+            if (d->type == 0) {
+                const float OP[3] = {P[0] - d->origin[0], P[1] - d->origin[1], P[2] - d->origin[2]};
+                const float dt_ = OP[0] * d->axis[0] + OP[1] * d->axis[1] + OP[2] * d->axis[2];
+                const float root[3] = {dt_ * d->axis[0], dt_ * d->axis[1], dt_ * d->axis[2]};
+                a[i] = make_float4(root[0], root[1], root[2], 0.f);
+                b[i] = make_float4(P[0] - root[0], P[1] - root[1], P[2] - root[2], 0.f);
+            } else {
+                a[i] = make_float4(P[0], P[1], P[2], 0.f); b[i] = a[i];
+            }
+        }
+        CK(d->sid.alloc(n)); CK(d->root.alloc(n)); CK(d->rootP.alloc(n));
+        CK(cudaMemcpy(d->sid.p, sid.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d->root.p, a.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d->rootP.p, b.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+    }
+    return cudaSuccess;
+}
+
 cudaError_t run_substeps(Scene& s, int nSubsteps) {
     sync_mesh_params(s);
     const int N = (int)s.nVerts;
     for (s.substep = 0; s.substep < nSubsteps; s.substep++) {
+        s.curTime += s.dt;
         CK(collision_dcd(s, false));
         CK(initial_step(s));
+        CK(apply_deformers(s));
         CK(collision_ccd(s));
         CK(collision_prepare(s));
         CK(solve_iterations(s, s.phys.iterations, true));
@@ -559,8 +747,10 @@ cudaError_t run_substeps(Scene& s, int nSubsteps) {
 cudaError_t run_iterations_only(Scene& s, int nIters) {
     sync_mesh_params(s);
     s.substep = 0;
+    s.curTime += s.dt;
     CK(collision_dcd(s, false));
     CK(initial_step(s));
+    CK(apply_deformers(s));
     CK(collision_ccd(s));
     CK(collision_prepare(s));
     CK(solve_iterations(s, nIters, false));

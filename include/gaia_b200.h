@@ -186,6 +186,16 @@ int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT,
                            int32_t nColors, const int32_t* color_offsets, const int32_t* color_verts,
                            int32_t nFixed, const int32_t* fixedPoints);
 
+/* Deformers[] of Parameters.json (M/VBD/VBDDeformer.h:45-222), evaluated on the device after every applyInitialStep
+ * (VBDPhysics::applyDeformers, M/VBD/VBDPhysics.cpp:1572-1578). The selected vertices become fixed points (setFixed).
+ *   rotator:    p <- root + R(axis, angularVelocity * min(curTime, rotationEndTime)) * (p0 - root)
+ *   translator: p <- p0 + speed * min(curTime, deformationEndTime)
+ * end time <= 0 means "never stops". Must be called before finalize. */
+int gaia_b200_add_rotator(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, const float origin[3],
+                          const float axis[3], double angularVelocity, double rotationEndTime);
+int gaia_b200_add_translator(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3],
+                             double deformationEndTime);
+
 /* finalize: the rest of VBDPhysics::initialize (colour-group merge
  *           M/VBD/VBDPhysics.cpp:236-274, initializeGPU :563-651,
  *           initializeCollisionDetector BasePhysicsFramework.cpp:251-262). */

@@ -39,6 +39,36 @@ int oracle_add_tet_mesh(void* h, int32_t nV, int32_t nT, const float* xyz, const
     mesh_initialize(m, nV, nT, xyz, tets, o, nColors, colorOffsets, colorVerts, nFixed, fixed);
     return m.id;
 }
+static int add_deformer(void* h, int type, int mesh, const int32_t* verts, int32_t n, const float* origin, const float* axis, const float* speed,
+                        double w, double endTime) {
+    Scene* s = (Scene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    Mesh& m = s->meshes[mesh];
+    Deformer d;
+    d.type = type; d.mesh = mesh; d.verts.assign(verts, verts + n); d.angularVelocity = w; d.endTime = endTime;
+    if (origin) d.origin = V3(origin[0], origin[1], origin[2]);
+    if (axis) d.axis = V3(axis[0], axis[1], axis[2]);
+    if (speed) d.speed = V3(speed[0], speed[1], speed[2]);
+    for (int i = 0; i < n; i++) {
+        const int v = verts[i];
+        if (!m.fixedMask[v]) { m.fixedMask[v] = 1; m.fixedPoints.push_back(v); }
+        const V3 P = m.pos[v];
+        if (type == 0) {
+            const V3 OP = P - d.origin;
+            const V3 root = dot(OP, d.axis) * d.axis;
+            d.roots.push_back(root); d.rootPs.push_back(P - root);
+        } else { d.roots.push_back(P); d.rootPs.push_back(P); }
+    }
+    s->deformers.push_back(d);
+    return GAIA_OK;
+}
+int oracle_add_rotator(void* h, int mesh, const int32_t* verts, int32_t n, const float* origin, const float* axis, double w, double endTime) {
+    return add_deformer(h, 0, mesh, verts, n, origin, axis, nullptr, w, endTime);
+}
+int oracle_add_translator(void* h, int mesh, const int32_t* verts, int32_t n, const float* speed, double endTime) {
+    return add_deformer(h, 1, mesh, verts, n, nullptr, nullptr, speed, 0.0, endTime);
+}
+
 int oracle_finalize(void* h) { scene_finalize(*(Scene*)h); return GAIA_OK; }
 
 int oracle_run_frames(void* h, int32_t nFrames) {

@@ -370,6 +370,30 @@ static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
     }
 }
 
+static void apply_deformers(Scene& s) {
+    for (Deformer& d : s.deformers) {
+        Mesh& m = s.meshes[d.mesh];
+        double t = (double)s.curTime;
+        if (t >= d.endTime && d.endTime > 0) t = d.endTime;
+        if (d.type == 0) {
+            const double theta = t * d.angularVelocity;
+            const double ux = d.axis.x, uy = d.axis.y, uz = d.axis.z;
+            const double c = std::cos(theta), sn = std::sin(theta);
+            const float R[9] = {(float)(c + ux * ux * (1 - c)), (float)(ux * uy * (1 - c) - uz * sn), (float)(ux * uz * (1 - c) + uy * sn),
+                                (float)(uy * ux * (1 - c) + uz * sn), (float)(c + uy * uy * (1 - c)), (float)(uy * uz * (1 - c) - ux * sn),
+                                (float)(uz * ux * (1 - c) - uy * sn), (float)(uz * uy * (1 - c) + ux * sn), (float)(c + uz * uz * (1 - c))};
+            for (size_t i = 0; i < d.verts.size(); i++) {
+                const V3 q = d.rootPs[i];
+                const V3 rot(R[0] * q.x + R[1] * q.y + R[2] * q.z, R[3] * q.x + R[4] * q.y + R[5] * q.z, R[6] * q.x + R[7] * q.y + R[8] * q.z);
+                m.pos[d.verts[i]] = d.roots[i] + rot;
+            }
+        } else {
+            const float tf = (float)t;
+            for (size_t i = 0; i < d.verts.size(); i++) m.pos[d.verts[i]] = d.speed * tf + d.roots[i];
+        }
+    }
+}
+
 void enable_models(Scene& s) {
     // VBD override tests frameToAppear <= frameId (VBDPhysics.cpp:691)
     for (auto& m : s.meshes) {
@@ -382,8 +406,10 @@ void enable_models(Scene& s) {
 
 void run_step(Scene& s) {
     for (s.substep = 0; s.substep < s.phys.numSubsteps; s.substep++) {
+        s.curTime += s.dt;
         dcd(s, false);
         for (auto& m : s.meshes) if (m.activeForMaterialSolve) apply_initial_step(s, m);
+        apply_deformers(s);
         ccd(s);
         prepare_collision_data(s);
         solve_iterations(s, s.phys.iterations, true);
@@ -395,8 +421,10 @@ void run_step(Scene& s) {
 
 void run_iterations(Scene& s, int nIters) {
     s.substep = 0;
+    s.curTime += s.dt;
     dcd(s, false);
     for (auto& m : s.meshes) if (m.activeForMaterialSolve) apply_initial_step(s, m);
+    apply_deformers(s);
     ccd(s);
     prepare_collision_data(s);
     solve_iterations(s, nIters, false);

@@ -63,6 +63,15 @@ struct Mesh {
     int nSurfF() const { return (int)surfFaces.size() / 3; }
 };
 
+// DeformerRotator / DeformerTranslater (M/VBD/VBDDeformer.h:45-177)
+struct Deformer {
+    int type = 0, mesh = 0;
+    std::vector<int> verts;
+    V3 origin, axis, speed;
+    double angularVelocity = 0, endTime = -1;
+    std::vector<V3> roots, rootPs;   // translator: original positions in roots
+};
+
 struct Scene {
     gaia_physics_params phys;
     gaia_collision_params col;
@@ -73,6 +82,8 @@ struct Scene {
     std::vector<std::vector<int>> activeCollisionsEachGroup;
     bool finalized = false;
     int frameId = 0, substep = 0, iIter = 0;
+    float curTime = 0.f;
+    std::vector<Deformer> deformers;
     Pool* pool = nullptr;
     gaia_stats stats;
     std::string err;
