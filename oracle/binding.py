@@ -32,6 +32,8 @@ def load_oracle():
         lib.oracle_get_vertex_tet_csr.argtypes = [P, C.c_int, IP, IP, IP]
         lib.oracle_set_brute_force.argtypes = [P, C.c_int]
         lib.oracle_vertex_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
+        lib.oracle_contact_force_hessian.argtypes = [FP, FP, FP, FP, C.c_int] + [C.c_float] * 6 + [FP, FP, FP]
+        lib.oracle_boundary_force_hessian.argtypes = [FP, FP, FP, FP] + [C.c_float] * 4 + [C.c_int, FP, FP]
         lib.oracle_solve3x3.argtypes = [FP, FP, FP]
         lib.oracle_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]
         lib.oracle_cubic_roots.argtypes = [FP, C.c_float, C.c_float, FP]

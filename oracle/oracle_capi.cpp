@@ -7,7 +7,11 @@
 
 using namespace orc;
 
-namespace orc { void collision_set_brute_force(Scene& s, bool on); }
+namespace orc {
+void collision_set_brute_force(Scene& s, bool on);
+void probe_boundary(const Scene& s, const Mesh& m, int iV, V3& force, M3& hessian, bool apply_friction);
+void probe_collision_per_collision(const ColResult& r, int order, V3& force, M3& hessian);
+}
 
 extern "C" {
 
@@ -195,6 +199,45 @@ int oracle_vertex_material_force_hessian(void* h, int mesh, int v, float* force3
     Scene* s = (Scene*)h;
     V3 f; M3 H;
     neohookean_force_hessian(*s, s->meshes[mesh], v, f, H);
+    force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
+    std::memcpy(hessian9, H.m, 36);
+    return GAIA_OK;
+}
+// one vertex-face contact evaluated the CPU way (updateCollisionInfo + accumlateCollisionForceAndHessianPerCollision):
+// query vertex p in mesh 0, triangle tri (3 vertices) in mesh 1; order 0..2 = face vertex, 3 = the query vertex
+int oracle_contact_force_hessian(const float* p, const float* pPrev, const float* tri, const float* triPrev, int order, float k,
+                                 float mu0, float mu1, float epsV0, float epsV1, float dt, float* force3, float* hessian9, float* depth) {
+    Scene s;
+    std::memset(&s.phys, 0, sizeof(s.phys));
+    s.phys.collisionStiffness = k; s.dt = dt;
+    s.meshes.resize(2);
+    Mesh& a = s.meshes[0]; Mesh& b = s.meshes[1];
+    a.pos = {V3(p[0], p[1], p[2])}; a.prev = {V3(pPrev[0], pPrev[1], pPrev[2])};
+    a.obj.frictionDynamic = mu0; a.obj.frictionEpsV = epsV0;
+    for (int i = 0; i < 3; i++) { b.pos.push_back(V3(tri[3 * i], tri[3 * i + 1], tri[3 * i + 2])); b.prev.push_back(V3(triPrev[3 * i], triPrev[3 * i + 1], triPrev[3 * i + 2])); }
+    b.surfFaces = {0, 1, 2};
+    b.obj.frictionDynamic = mu1; b.obj.frictionEpsV = epsV1;
+    ColResult r;
+    r.numIntersections = 1; r.idVQuery = 0; r.idTMQuery = 0; r.intersectedMeshId = 1; r.closestSurfaceFaceId = 0; r.shortestPathFound = true;
+    update_collision_info(s, r);
+    V3 f; M3 H;
+    probe_collision_per_collision(r, order, f, H);
+    force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
+    std::memcpy(hessian9, H.m, 36);
+    if (depth) *depth = r.penetrationDepth;
+    return GAIA_OK;
+}
+int oracle_boundary_force_hessian(const float* p, const float* pPrev, const float* boundsMin, const float* boundsMax, float kB, float muB,
+                                  float epsVB, float dt, int applyFriction, float* force3, float* hessian9) {
+    Scene s;
+    std::memset(&s.phys, 0, sizeof(s.phys));
+    s.phys.usePlaneGround = 1; s.phys.boundaryCollisionStiffness = kB; s.phys.boundaryFrictionDynamic = muB; s.phys.boundaryFrictionEpsV = epsVB;
+    for (int d = 0; d < 3; d++) { s.phys.worldBoundsMin[d] = boundsMin[d]; s.phys.worldBoundsMax[d] = boundsMax[d]; }
+    s.dt = dt;
+    Mesh m;
+    m.pos = {V3(p[0], p[1], p[2])}; m.prev = {V3(pPrev[0], pPrev[1], pPrev[2])};
+    V3 f; M3 H;
+    probe_boundary(s, m, 0, f, H, applyFriction != 0);
     force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
     std::memcpy(hessian9, H.m, 36);
     return GAIA_OK;

@@ -419,6 +419,12 @@ void run_step(Scene& s) {
     s.stats.frames++;
 }
 
+// probes for tests/test_oracle_vs_ref.py (pin the restatement against the reference's own compiled math)
+void probe_boundary(const Scene& s, const Mesh& m, int iV, V3& force, M3& hessian, bool apply_friction) {
+    boundary_force_hessian(s, m, iV, force, hessian, apply_friction);
+}
+void probe_collision_per_collision(const ColResult& r, int order, V3& force, M3& hessian) { collision_per_collision(r, order, force, hessian); }
+
 void run_iterations(Scene& s, int nIters) {
     s.substep = 0;
     s.curTime += s.dt;

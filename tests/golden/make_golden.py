@@ -1,0 +1,105 @@
+#!/usr/bin/env python
+"""Generate tests/golden/ref_vectors.npz from the REFERENCE's own code.
+
+The vectors are outputs of oracle/_ref/libgaia_ref.so, i.e. of the reference's __host__ __device__ VBD math
+(Simulator/Modules/VBD/VBDPhysicsCompute.cu, VBD_GeneralCompute.h, 3rdParty/CuMatrix) and of its own CCD solver
+(Simulator/Modules/CollisionDetector/CCDSolver.h + 3rdParty/CyCodeBase), compiled from /root/reference by
+oracle/Makefile. The reference ships no golden vectors of its own; these pin the CPU oracle (and through
+it the CUDA path) to the reference's arithmetic on seeded inputs. Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+Inputs are regenerated from the seeds by the tests, so only outputs + inputs needed for replay are stored.
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases)  # noqa: E402
+from oracle.binding import load_ref, ref_available  # noqa: E402
+
+FP = C.POINTER(C.c_float)
+IP = C.POINTER(C.c_int32)
+
+
+def fp(a):
+    return a.ctypes.data_as(FP)
+
+
+def ip(a):
+    return a.ctypes.data_as(IP)
+
+
+def main():
+    if not ref_available():
+        raise SystemExit("oracle/_ref/libgaia_ref.so missing: run `make -C oracle` where /root/reference exists")
+    ref = load_ref()
+    out = {}
+    # ---- Neo-Hookean per-vertex force / Hessian (GAIA::accumulateMaterialForceAndHessianForVertex_NeoHookean)
+    cases = [("nh_plain", neohookean_case(seed=11, dampH=0.0, dampD=0.0))] + \
+            [(f"nh_damped{i}", c) for i, c in enumerate(single_tet_cases())]
+    for tag, c in cases:
+        nV, nT = len(c["pos"]), len(c["tets"])
+        F = np.zeros((nV, 3), np.float32); H = np.zeros((nV, 9), np.float32)
+        for v in range(nV):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            ref.ref_neohookean_vertex(nV, nT, fp(c["pos"]), fp(c["prev"]), ip(c["tets"]), fp(c["DmInv"]), fp(c["restVol"]),
+                                      ip(c["infos"]), ip(c["nbrTets"]), ip(c["nbrOrder"]), c["miu"], c["lmbd"], c["dampH"], c["dampD"],
+                                      c["dt"], v, fp(f), fp(h))
+            F[v] = f; H[v] = h
+        out[tag + "_force"] = F; out[tag + "_hessian"] = H
+    # ---- CuMatrix::solve3x3_psd_stable
+    Ms, Bs = solve3x3_cases()
+    X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)
+    for i in range(len(Ms)):
+        x = np.zeros(3, np.float32)
+        ok[i] = ref.ref_solve3x3(fp(Ms[i]), fp(Bs[i]), fp(x)); X[i] = x
+    out["solve_x"] = X; out["solve_ok"] = ok
+    # ---- cy::IntersectContinuousTriPoint<float>
+    x0, x1, p0, p1 = ccd_cases()
+    hit = np.zeros(len(x0), np.int32); tt = np.zeros(len(x0), np.float32); bary = np.zeros((len(x0), 3), np.float32)
+    for i in range(len(x0)):
+        t = C.c_float(-1); b = np.zeros(3, np.float32)
+        hit[i] = ref.ref_ccd_tri_point(fp(x0[i]), fp(x1[i]), fp(p0[i]), fp(p1[i]), C.byref(t), fp(b))
+        tt[i] = t.value; bary[i] = b
+    out["ccd_hit"] = hit; out["ccd_t"] = tt; out["ccd_bary"] = bary
+    # ---- cy::CubicRoots<float>
+    coefs = cubic_cases()
+    nr = np.zeros(len(coefs), np.int32); roots = np.zeros((len(coefs), 3), np.float32)
+    for i in range(len(coefs)):
+        r = np.zeros(3, np.float32)
+        nr[i] = ref.ref_cubic_roots(fp(coefs[i]), 0.0, 1.0, fp(r)); roots[i] = r
+    out["cubic_n"] = nr; out["cubic_roots"] = roots
+    # ---- vertex-face contact force / Hessian (GAIA::accumlateCollisionForceAndHessianPerCollision_v2)
+    cc = contact_cases()
+    Fc = np.zeros((len(cc["p"]), 4, 3), np.float32); Hc = np.zeros((len(cc["p"]), 4, 9), np.float32)
+    for i in range(len(cc["p"])):
+        for order in range(4):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            ref.ref_collision_per_collision(fp(cc["p"][i]), fp(cc["pPrev"][i]), fp(cc["tri"][i]), fp(cc["triPrev"][i]), order,
+                                            cc["k"], cc["mu0"], cc["mu1"], cc["eps0"], cc["eps1"], cc["dt"], fp(f), fp(h))
+            Fc[i, order] = f; Hc[i, order] = h
+    out["contact_force"] = Fc; out["contact_hessian"] = Hc
+    # ---- world-box penalty + friction (GAIA::accumulateBoundaryForceAndHessianGPU; one violated axis per case, where the
+    #      reference's CPU "per axis" and GPU "once" friction rules coincide)
+    bc = boundary_cases()
+    Fb = np.zeros((len(bc["p"]), 3), np.float32); Hb = np.zeros((len(bc["p"]), 9), np.float32)
+    bounds6 = np.ascontiguousarray(np.concatenate([bc["mn"], bc["mx"]]), np.float32)   # [min xyz, max xyz] (M/VBD/VBDPhysics.cpp:637-642)
+    for i in range(len(bc["p"])):
+        f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+        ref.ref_boundary(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bounds6), bc["kB"], bc["muB"], bc["epsVB"], bc["dt"], fp(f), fp(h))
+        Fb[i] = f; Hb[i] = h
+    out["boundary_force"] = Fb; out["boundary_hessian"] = Hb
+    path = os.path.join(ROOT, "tests", "golden", "ref_vectors.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, {k: v.shape for k, v in out.items()})
+
+
+if __name__ == "__main__":
+    main()

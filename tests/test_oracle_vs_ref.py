@@ -1,0 +1,145 @@
+"""Pin the CPU oracle to the reference's own arithmetic.
+
+tests/golden/ref_vectors.npz holds outputs of the REFERENCE's compiled code (oracle/_ref/libgaia_ref.so, built from
+/root/reference; generator: tests/golden/make_golden.py) on the seeded inputs of tests/golden_inputs.py. The oracle is
+replayed on the same inputs. Tolerances: the 3x3 solve, the cubic solver and the CCD test are the same sequence of
+float operations -> bit-exact; force/Hessian assemblies sum in a different association -> 2e-5 relative to the
+largest entry (the reference's GPU-variant code adds the mu*|m|^2*A damping term twice when damping > 0 — SURVEY.md §8(a)
+divergences — so the damped case is compared with that term added back)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from golden_inputs import neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases
+from oracle.binding import load_oracle, load_ref, ref_available
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vectors.npz"))
+FP = C.POINTER(C.c_float)
+
+
+def fp(a):
+    return a.ctypes.data_as(FP)
+
+
+def relmax(a, b):
+    return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max() / max(np.abs(b).max(), 1e-30))
+
+
+def test_neohookean_force_hessian_plain():
+    c = neohookean_case(seed=11, dampH=0.0, dampD=0.0)
+    o = c["scene"]
+    o.set_state(0, c["pos"], None); o.set_prev_positions(0, c["prev"])
+    F = np.zeros((len(c["pos"]), 3), np.float32); H = np.zeros((len(c["pos"]), 9), np.float32)
+    for v in range(len(c["pos"])):
+        F[v], H[v] = o.vertex_material_force_hessian(0, v)
+    assert relmax(F, GOLD["nh_plain_force"]) < 2e-5
+    assert relmax(H, GOLD["nh_plain_hessian"]) < 2e-5
+
+
+def test_neohookean_force_hessian_damped():
+    """CPU semantics (the oracle) vs the reference's GPU-variant code on one-tet meshes. The GPU variant
+    (VBDPhysicsCompute.cu:2147-2155, 2196-2221) (i) carries mu*|m|^2*A inside the Hessian it scales by dampingHydrostatic
+    and (ii) adds mu*|m|^2*A to the diagonal a second time; both extras are closed-form for a vertex with a single
+    incident tet, so: H_gpu = H_cpu + tmp*(1 + gamma_h/dt) I,  f_gpu = f_cpu - tmp*gamma_h/dt (x - x_prev)."""
+    for i, c in enumerate(single_tet_cases()):
+        o = c["scene"]
+        o.set_state(0, c["pos"], None); o.set_prev_positions(0, c["prev"])
+        B = c["DmInv"][0].astype(np.float64).reshape(3, 3, order="F")
+        rows = [-(B[0] + B[1] + B[2]), B[0], B[1], B[2]]
+        for v in range(4):
+            F, H = o.vertex_material_force_hessian(0, v)
+            tmp = float(rows[v] @ rows[v]) * c["miu"] * float(c["restVol"][0])
+            disp = c["pos"][v].astype(np.float64) - c["prev"][v].astype(np.float64)
+            Hx = H.astype(np.float64); Hx[[0, 4, 8]] += tmp * (1 + c["dampH"] / c["dt"])
+            Fx = F.astype(np.float64) - tmp * c["dampH"] / c["dt"] * disp
+            assert relmax(Hx, GOLD[f"nh_damped{i}_hessian"][v]) < 3e-5
+            assert relmax(Fx, GOLD[f"nh_damped{i}_force"][v]) < 3e-5
+            # and the damping terms are not negligible in this fixture
+            assert tmp * c["dampD"] / c["dt"] > 1e-3 * np.abs(H).max()
+
+
+def test_solve3x3_bit_exact():
+    lib = load_oracle()
+    Ms, Bs = solve3x3_cases()
+    for i in range(len(Ms)):
+        x = np.zeros(3, np.float32)
+        ok = lib.oracle_solve3x3(fp(Ms[i]), fp(Bs[i]), fp(x))
+        assert ok == GOLD["solve_ok"][i]
+        assert np.array_equal(x, GOLD["solve_x"][i], equal_nan=True)
+    assert 0 < GOLD["solve_ok"].sum() < len(Ms)       # both branches covered
+
+
+def test_cubic_roots_bit_exact():
+    lib = load_oracle()
+    coefs = cubic_cases()
+    for i in range(len(coefs)):
+        r = np.zeros(3, np.float32)
+        n = lib.oracle_cubic_roots(fp(coefs[i]), 0.0, 1.0, fp(r))
+        assert n == GOLD["cubic_n"][i]
+        assert np.array_equal(r[:n], GOLD["cubic_roots"][i][:n])
+    assert set(GOLD["cubic_n"].tolist()) >= {0, 1, 2}
+
+
+def test_ccd_tri_point_bit_exact():
+    lib = load_oracle()
+    x0, x1, p0, p1 = ccd_cases()
+    for i in range(len(x0)):
+        t = C.c_float(-1); b = np.zeros(3, np.float32)
+        hit = lib.oracle_ccd_tri_point(fp(x0[i]), fp(x1[i]), fp(p0[i]), fp(p1[i]), C.byref(t), fp(b))
+        assert hit == GOLD["ccd_hit"][i]
+        if hit:
+            assert t.value == GOLD["ccd_t"][i]
+            assert np.array_equal(b, GOLD["ccd_bary"][i])
+    assert 20 < GOLD["ccd_hit"].sum() < len(x0) - 20
+
+
+def test_contact_force_hessian():
+    lib = load_oracle()
+    cc = contact_cases()
+    nz = 0
+    for i in range(len(cc["p"])):
+        for order in range(4):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32); d = C.c_float()
+            lib.oracle_contact_force_hessian(fp(cc["p"][i]), fp(cc["pPrev"][i]), fp(cc["tri"][i]), fp(cc["triPrev"][i]), order, cc["k"],
+                                             cc["mu0"], cc["mu1"], cc["eps0"], cc["eps1"], cc["dt"], fp(f), fp(h), C.byref(d))
+            gf, gh = GOLD["contact_force"][i, order], GOLD["contact_hessian"][i, order]
+            assert (np.abs(gf).max() > 0) == (np.abs(f).max() > 0)
+            if np.abs(gf).max() > 0:
+                nz += 1
+                assert relmax(f, gf) < 2e-5 and relmax(h, gh) < 2e-5
+    assert nz > 100
+
+
+def test_boundary_force_hessian():
+    lib = load_oracle()
+    bc = boundary_cases()
+    nz = 0
+    for i in range(len(bc["p"])):
+        f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+        lib.oracle_boundary_force_hessian(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bc["mn"]), fp(bc["mx"]), bc["kB"], bc["muB"], bc["epsVB"],
+                                          bc["dt"], 1, fp(f), fp(h))
+        gf, gh = GOLD["boundary_force"][i], GOLD["boundary_hessian"][i]
+        if np.abs(gf).max() > 0:
+            nz += 1
+            assert relmax(f, gf) < 1e-6 and relmax(h, gh) < 1e-6
+        else:
+            assert np.abs(f).max() == 0
+    assert nz >= 30
+
+
+@pytest.mark.skipif(not ref_available(), reason="oracle/_ref/libgaia_ref.so is only built where /root/reference exists")
+def test_golden_file_matches_a_fresh_run_of_the_reference():
+    """The committed fixture is what the reference's code produces today (guards against a stale .npz)."""
+    ref = load_ref()
+    Ms, Bs = solve3x3_cases()
+    for i in range(0, len(Ms), 7):
+        x = np.zeros(3, np.float32)
+        ok = ref.ref_solve3x3(fp(Ms[i]), fp(Bs[i]), fp(x))
+        assert ok == GOLD["solve_ok"][i] and np.array_equal(x, GOLD["solve_x"][i], equal_nan=True)
+    x0, x1, p0, p1 = ccd_cases()
+    for i in range(0, len(x0), 5):
+        t = C.c_float(-1); b = np.zeros(3, np.float32)
+        hit = ref.ref_ccd_tri_point(fp(x0[i]), fp(x1[i]), fp(p0[i]), fp(p1[i]), C.byref(t), fp(b))
+        assert hit == GOLD["ccd_hit"][i] and (not hit or t.value == GOLD["ccd_t"][i])
