@@ -160,6 +160,7 @@ def bind_scene_api(lib, prefix):
         "get_contacts": ([P, C.POINTER(Contact), C.c_int64, C.POINTER(C.c_int64)], C.c_int),
         "enable_mesh": ([P, C.c_int, C.c_int, C.c_int], C.c_int),
         "get_stats": ([P, C.POINTER(Stats)], C.c_int), "reset_stats": ([P], C.c_int),
+        "get_bvh_leaf_order": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, prefix + name)
@@ -286,6 +287,13 @@ class SceneBase:
         self._call("get_contacts", arr.ctypes.data_as(C.POINTER(Contact)), n.value, C.byref(n))
         return arr[: n.value]
 
+    def bvh_leaf_order(self, which):
+        n = C.c_int64()
+        self._call("get_bvh_leaf_order", which, None, 0, C.byref(n))
+        a = np.empty(n.value, np.int32)
+        self._call("get_bvh_leaf_order", which, _ip(a), n.value, C.byref(n))
+        return a
+
     def enable_mesh(self, mesh, collide=True, solve=True):
         self._call("enable_mesh", mesh, int(collide), int(solve))
 
@@ -325,7 +333,6 @@ def load_library(path=None):
     lib.gaia_b200_total_vertices.argtypes = [P]; lib.gaia_b200_total_vertices.restype = C.c_int64
     lib.gaia_b200_get_all_positions.argtypes = [P, FP]
     lib.gaia_b200_set_all_state.argtypes = [P, FP, FP]
-    lib.gaia_b200_get_bvh_leaf_order.argtypes = [P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)]
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
@@ -376,13 +383,6 @@ class Scene(SceneBase):
 
     def set_all_state(self, pos, vel):
         self._call("set_all_state", _fp(pos), _fp(vel))
-
-    def bvh_leaf_order(self, which):
-        n = C.c_int64()
-        self._call("get_bvh_leaf_order", which, None, 0, C.byref(n))
-        a = np.empty(n.value, np.int32)
-        self._call("get_bvh_leaf_order", which, _ip(a), n.value, C.byref(n))
-        return a
 
     def set_profiling(self, on=True):
         self._call("set_profiling", int(on))

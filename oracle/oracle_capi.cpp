@@ -9,6 +9,7 @@ using namespace orc;
 
 namespace orc {
 void collision_set_brute_force(Scene& s, bool on);
+std::vector<int> morton_leaf_order(const Scene& s, int which);
 void probe_boundary(const Scene& s, const Mesh& m, int iV, V3& force, M3& hessian, bool apply_friction);
 void probe_collision_per_collision(const ColResult& r, int order, V3& force, M3& hessian);
 }
@@ -192,6 +193,12 @@ int oracle_get_contacts(void* h, gaia_contact* out, int64_t capacity, int64_t* n
         }
     }
     *n = cnt;
+    return GAIA_OK;
+}
+int oracle_get_bvh_leaf_order(void* h, int which, int32_t* out, int64_t capacity, int64_t* n) {
+    std::vector<int> o = morton_leaf_order(*(Scene*)h, which);
+    *n = (int64_t)o.size();
+    if (out) { if (capacity < *n) return GAIA_ERR_INVALID_ARG; std::memcpy(out, o.data(), o.size() * 4); }
     return GAIA_OK;
 }
 // per-vertex force / Hessian probe for pinning against oracle/_ref (not part of the product ABI)

@@ -667,6 +667,59 @@ void update_collision_info(Scene& s, ColResult& r) {
     }
 }
 
+// ---------------------------------------------------------------- Morton leaf order (integer parity surface)
+// The product's LBVH sorts primitives by (segment, 30-bit Morton code of the primitive's box centre); codes follow
+// lbvh::morton_code (M/BVH/MortonCode.h:8-31), the centre is normalised by the bounds of the active meshes' vertices (scene
+// trees) or of the primitive's own mesh (per-mesh surface trees); ties keep ascending primitive id (stable sort).
+static inline uint32_t expand_bits(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+static uint32_t morton_of(const Box& b, const Box& nb) {
+    uint32_t e[3];
+    for (int d = 0; d < 3; d++) {
+        const float c = 0.5f * (b.lo[d] + b.hi[d]);
+        const float ext = nb.hi[d] - nb.lo[d];
+        float u = ext > 0.f ? (c - nb.lo[d]) / ext : 0.f;
+        u = std::fmin(std::fmax(u * 1024.0f, 0.0f), 1023.0f);
+        e[d] = expand_bits((uint32_t)u);
+    }
+    return e[0] * 4 + e[1] * 2 + e[2];
+}
+std::vector<int> morton_leaf_order(const Scene& s, int which) {
+    std::vector<Box> meshBox(s.meshes.size());
+    Box scene; for (int d = 0; d < 3; d++) { scene.lo[d] = 3.0e38f; scene.hi[d] = -3.0e38f; }
+    for (size_t im = 0; im < s.meshes.size(); im++) {
+        Box b; for (int d = 0; d < 3; d++) { b.lo[d] = 3.0e38f; b.hi[d] = -3.0e38f; }
+        for (const V3& p : s.meshes[im].pos) box_add(b, p);
+        meshBox[im] = b;
+        if (s.meshes[im].activeForCollision) box_merge(scene, b);
+    }
+    std::vector<uint64_t> keys;
+    for (size_t im = 0; im < s.meshes.size(); im++) {
+        const Mesh& m = s.meshes[im];
+        const int n = which == 0 ? m.nT : m.nSurfF();
+        for (int i = 0; i < n; i++) {
+            const uint64_t seg = which == 1 ? ((uint64_t)im << 32) : 0ull;
+            if (!m.activeForCollision) { keys.push_back(seg | (1ull << 30)); continue; }
+            Box b; for (int d = 0; d < 3; d++) { b.lo[d] = 3e38f; b.hi[d] = -3e38f; }
+            if (which == 0) for (int k = 0; k < 4; k++) box_add(b, m.pos[m.tets[4 * (size_t)i + k]]);
+            else for (int k = 0; k < 3; k++) {
+                box_add(b, m.pos[m.surfFaces[3 * (size_t)i + k]]);
+            }
+            if (which == 2) for (int k = 0; k < 3; k++) box_add(b, m.prev[m.surfFaces[3 * (size_t)i + k]]);
+            keys.push_back(seg | morton_of(b, which == 1 ? meshBox[im] : scene));
+        }
+    }
+    std::vector<int> order(keys.size());
+    for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return keys[a] < keys[b]; });
+    return order;
+}
+
 // test hook: switch the accelerator off (brute force over all primitives)
 void collision_set_brute_force(Scene& s, bool on) { if (s.bvhTet) ((ColAccel*)s.bvhTet)->bruteForce = on; }
 

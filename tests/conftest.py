@@ -55,3 +55,34 @@ def make_beam_scene(cls, nx=6, ny=3, nz=3, h=0.25, y0=0.05, substeps=2, iteratio
 
 def rel_err(a, b):
     return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))
+
+
+def make_contact_scene(cls, n_objects=2, ccd=1, dcd=1, substeps=2, iterations=6, phys_kw=None, col_kw=None, gap=-0.08, v_rel=(0.0, -6.0, 0.0),
+                       **cls_kw):
+    """Config-2 shape in miniature: Kuhn-grid blocks stacked with a small overlap (gap < 0) above the ground plane, each
+    with its own material and colouring, the upper ones moving down. Returns the finalized scene."""
+    from gaia_b200 import capi, meshio
+    pk = dict(numSubsteps=substeps, iterations=iterations, worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10], collisionStiffness=1e5)
+    pk.update(phys_kw or {})
+    ck = dict(allowDCD=dcd, allowCCD=ccd)
+    ck.update(col_kw or {})
+    s = cls(capi.default_physics_params(**pk), capi.default_collision_params(**ck), **cls_kw)
+    y = 0.3
+    shapes = [(4, 2, 3, 0.25), (3, 2, 2, 0.22), (2, 3, 2, 0.2), (3, 3, 3, 0.15)]
+    for i in range(n_objects):
+        nx, ny, nz, h = shapes[i % len(shapes)]
+        ox = 0.11 * i - 0.05 * (i % 2); oz = 0.07 * (i % 3)
+        verts, tets = meshio.kuhn_beam(nx, ny, nz, h=h, origin=(ox, y, oz))
+        colors = meshio.kuhn_coloring(nx, ny, nz) if i % 2 == 0 else meshio.greedy_coloring(len(verts), tets)
+        obj = capi.default_object_params(miu=1e5 * (1 + 0.5 * i), lmbd=1e6, density=50 + 10 * i, frictionDynamic=0.2 + 0.1 * i,
+                                         initialVelocity=[v_rel[0] * i, v_rel[1] * i, v_rel[2] * i],
+                                         rotation=[0.0, 0.15 * i, 0.05 * i] if i else [0, 0, 0])
+        s.add_tet_mesh(verts, tets, obj, colors)
+        y += ny * h + gap
+    s.finalize()
+    return s
+
+
+def contacts_table(c):
+    """structured contact array -> plain int array for exact comparison"""
+    return np.stack([c[n] for n in c.dtype.names], 1) if len(c) else np.zeros((0, 8), np.int32)
