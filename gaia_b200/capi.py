@@ -333,6 +333,8 @@ def load_library(path=None):
     lib.gaia_b200_total_vertices.argtypes = [P]; lib.gaia_b200_total_vertices.restype = C.c_int64
     lib.gaia_b200_get_all_positions.argtypes = [P, FP]
     lib.gaia_b200_set_all_state.argtypes = [P, FP, FP]
+    lib.gaia_b200_set_time.argtypes = [P, C.c_int32, C.c_double]
+    lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
@@ -383,6 +385,13 @@ class Scene(SceneBase):
 
     def set_all_state(self, pos, vel):
         self._call("set_all_state", _fp(pos), _fp(vel))
+
+    def set_time(self, frame_id, cur_time):
+        self._call("set_time", int(frame_id), float(cur_time))
+
+    @property
+    def cur_time(self):
+        return self._lib.gaia_b200_cur_time(self.h)
 
     def set_profiling(self, on=True):
         self._call("set_profiling", int(on))

@@ -181,6 +181,14 @@ int gaia_b200_synchronize(gaia_handle* h) {
     return check_device_errors(s);
 }
 int gaia_b200_frame_id(const gaia_handle* h) { return h ? h->s.frameId : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_set_time(gaia_handle* h, int32_t frameId, double curTime) {
+    REQUIRE(h);
+    if (frameId < 0) return fail(h->s, GAIA_ERR_INVALID_ARG, "negative frame id");
+    h->s.frameId = frameId; h->s.curTime = (float)curTime;
+    collision_invalidate(h->s);
+    return GAIA_OK;
+}
+double gaia_b200_cur_time(const gaia_handle* h) { return h ? (double)h->s.curTime : 0.0; }
 int gaia_b200_num_meshes(const gaia_handle* h) { return h ? (int)h->s.meshes.size() : GAIA_ERR_INVALID_ARG; }
 int gaia_b200_mesh_sizes(const gaia_handle* h, int mesh, int32_t* nV, int32_t* nT, int32_t* nSurfV, int32_t* nSurfF) {
     REQUIRE(h);

@@ -346,6 +346,10 @@ cudaError_t collision_init(Scene& s) {
 }
 
 void collision_destroy(Scene& s) { delete s.cs; s.cs = nullptr; }
+void collision_invalidate(Scene& s) {
+    if (!s.cs) return;
+    s.cs->tetBvh.built = s.cs->surfBvh.built = s.cs->ccdBvh.built = false;
+}
 
 // ------------------------------------------------------------------------------------------------ BVH maintenance
 static bool activity_changed(const Scene& s, std::vector<uint8_t>& snap) {

@@ -117,6 +117,7 @@ int check_device_errors(Scene& s);
 // collision.cu
 cudaError_t collision_init(Scene& s);
 void collision_destroy(Scene& s);
+void collision_invalidate(Scene& s);                              // force BVH rebuilds at the next detection
 cudaError_t collision_dcd(Scene& s, bool intermediate);
 cudaError_t collision_ccd(Scene& s);
 cudaError_t collision_prepare(Scene& s);

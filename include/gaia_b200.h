@@ -211,6 +211,11 @@ int gaia_b200_run_frames(gaia_handle* h, int32_t nFrames);
 int gaia_b200_run_iterations(gaia_handle* h, int32_t nIters);
 int gaia_b200_synchronize(gaia_handle* h);
 int gaia_b200_frame_id(const gaia_handle* h);
+/* recovery (PhysicsState::initializePhysics, M/Framework/BasePhysicsFramework.h:177-200): frameId and curTime of a saved
+ * state; positions / velocities go through set_state. The BVHs are rebuilt at the next detection
+ * (BasePhysicFramework::recoverFromState, BasePhysicsFramework.cpp:264-282). */
+int gaia_b200_set_time(gaia_handle* h, int32_t frameId, double curTime);
+double gaia_b200_cur_time(const gaia_handle* h);
 
 /* state access (VBDBaseTetMesh::syncToCPU / syncToGPU, M/VBD/VBD_BaseMaterial.h:120-128) */
 int gaia_b200_num_meshes(const gaia_handle* h);
