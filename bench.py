@@ -305,6 +305,10 @@ def main():
                 with open(tpath) as f:
                     tj = json.load(f)
                 roof["traffic"] = tj.get(args.workload, {}).get("dram_bytes_per_launch")
+                if roof["traffic"]:
+                    # this layout moves fewer bytes than the reference-layout formula counts: also report the real DRAM rate
+                    roof["dram_achieved"] = roof["traffic"] / (roof["avg_launch_us"] * 1e-6) / 1e9
+                    roof["dram_frac"] = roof["dram_achieved"] / hbm_peak
             except (OSError, ValueError):
                 pass
 
