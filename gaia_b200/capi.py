@@ -161,6 +161,7 @@ def bind_scene_api(lib, prefix):
         "enable_mesh": ([P, C.c_int, C.c_int, C.c_int], C.c_int),
         "get_stats": ([P, C.POINTER(Stats)], C.c_int), "reset_stats": ([P], C.c_int),
         "get_bvh_leaf_order": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
+        "set_partition_mode": ([P, C.c_int32, C.c_int32], C.c_int), "set_ghosts": ([P, C.c_int, IP, C.c_int32], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, prefix + name)
@@ -199,6 +200,13 @@ class SceneBase:
     def add_translator(self, mesh, verts, speed, end_time=-1.0):
         v = _i32(verts); sp = _f32(speed)
         self._call("add_translator", mesh, _ip(v), len(v), _fp(sp), float(end_time))
+
+    def set_partition_mode(self, rank, world):
+        self._call("set_partition_mode", int(rank), int(world))
+
+    def set_ghosts(self, mesh, verts):
+        v = _i32(verts)
+        self._call("set_ghosts", mesh, _ip(v), len(v))
 
     def finalize(self):
         self._call("finalize")
@@ -333,6 +341,10 @@ def load_library(path=None):
     lib.gaia_b200_total_vertices.argtypes = [P]; lib.gaia_b200_total_vertices.restype = C.c_int64
     lib.gaia_b200_get_all_positions.argtypes = [P, FP]
     lib.gaia_b200_set_all_state.argtypes = [P, FP, FP]
+    lib.gaia_b200_get_sorted_ids.argtypes = [P, C.c_int, IP, C.c_int32, IP]
+    lib.gaia_b200_halo_ipc_handles.argtypes = [P, C.c_void_p]
+    lib.gaia_b200_halo_add_peer.argtypes = [P, C.c_int32, C.c_void_p, C.c_int32, IP, IP]
+    lib.gaia_b200_halo_finalize.argtypes = [P]
     lib.gaia_b200_set_time.argtypes = [P, C.c_int32, C.c_double]
     lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
@@ -385,6 +397,24 @@ class Scene(SceneBase):
 
     def set_all_state(self, pos, vel):
         self._call("set_all_state", _fp(pos), _fp(vel))
+
+    def sorted_ids(self, mesh, verts):
+        v = _i32(verts); out = np.empty(len(v), np.int32)
+        self._call("get_sorted_ids", mesh, _ip(v), len(v), _ip(out))
+        return out
+
+    def halo_ipc_handles(self):
+        buf = C.create_string_buffer(128)
+        self._call("halo_ipc_handles", buf)
+        return buf.raw
+
+    def halo_add_peer(self, peer_rank, handles, send_mesh_verts, remote_slots):
+        mv = _i32(send_mesh_verts).reshape(-1, 2); rs = _i32(remote_slots)
+        assert len(mv) == len(rs)
+        self._call("halo_add_peer", int(peer_rank), C.create_string_buffer(handles, 128), len(rs), _ip(mv), _ip(rs))
+
+    def halo_finalize(self):
+        self._call("halo_finalize")
 
     def set_time(self, frame_id, cur_time):
         self._call("set_time", int(frame_id), float(cur_time))

@@ -95,7 +95,7 @@ int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT, const float* 
     gaia_object_params o = *obj;
     o.exponentialVelDamping = std::pow(o.exponentialVelDamping, s.dt);   // VBDPhysics::timeStepEqualize
     o.constantVelDamping = o.constantVelDamping * s.dt;
-    host_mesh_init(m, nV, nT, xyz, tets, o, nColors, color_offsets, color_verts, nFixed, fixedPoints);
+    host_mesh_init(m, nV, nT, xyz, tets, o, nColors, color_offsets, color_verts, nFixed, fixedPoints, s.partitionMode);
     return m.id;
 }
 
@@ -320,6 +320,64 @@ int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int 
     s.meshes[mesh].activeForMaterialSolve = activeForMaterialSolve != 0;
     s.meshParamsDirty = true;
     return GAIA_OK;
+}
+
+int gaia_b200_set_partition_mode(gaia_handle* h, int32_t myRank, int32_t worldSize) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (!s.meshes.empty()) return fail(s, GAIA_ERR_STATE, "set_partition_mode must precede add_tet_mesh");
+    if (worldSize < 1 || myRank < 0 || myRank >= worldSize) return fail(s, GAIA_ERR_INVALID_ARG, "bad rank / world size");
+    s.partitionMode = true; s.myRank = myRank; s.worldSize = worldSize;
+    return GAIA_OK;
+}
+int gaia_b200_set_ghosts(gaia_handle* h, int mesh, const int32_t* verts, int32_t n) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (s.finalized) return fail(s, GAIA_ERR_STATE, "set_ghosts after finalize");
+    if (mesh < 0 || mesh >= (int)s.meshes.size() || n < 0 || (n && !verts)) return fail(s, GAIA_ERR_INVALID_ARG, "bad argument");
+    HostMesh& m = s.meshes[mesh];
+    for (int i = 0; i < n; i++) {
+        if (verts[i] < 0 || verts[i] >= m.nV) return fail(s, GAIA_ERR_INVALID_ARG, "ghost vertex out of range");
+        m.ghostMask[verts[i]] = 1;
+    }
+    return GAIA_OK;
+}
+int gaia_b200_get_sorted_ids(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, int32_t* out) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (mesh < 0 || mesh >= (int)s.meshes.size() || n < 0 || (n && (!verts || !out))) return fail(s, GAIA_ERR_INVALID_ARG, "bad argument");
+    const HostMesh& m = s.meshes[mesh];
+    for (int i = 0; i < n; i++) {
+        if (verts[i] < 0 || verts[i] >= m.nV) return fail(s, GAIA_ERR_INVALID_ARG, "vertex out of range");
+        out[i] = m.sortedId[verts[i]];
+    }
+    return GAIA_OK;
+}
+int gaia_b200_halo_ipc_handles(gaia_handle* h, void* out128) {
+    REQUIRE(h); FINALIZED(h);
+    if (!out128) return GAIA_ERR_INVALID_ARG;
+    cudaSetDevice(h->s.device);
+    cudaError_t e = halo_ipc_handles(h->s, out128);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(h->s, e);
+}
+int gaia_b200_halo_add_peer(gaia_handle* h, int32_t peerRank, const void* peerHandles128, int32_t nSend, const int32_t* sendMeshVerts,
+                            const int32_t* remoteSlots) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (!peerHandles128 || nSend < 0 || (nSend && (!sendMeshVerts || !remoteSlots)) || peerRank < 0 || peerRank >= s.worldSize || peerRank == s.myRank)
+        return fail(s, GAIA_ERR_INVALID_ARG, "bad halo peer argument");
+    for (int i = 0; i < nSend; i++) {
+        const int mm = sendMeshVerts[2 * i], v = sendMeshVerts[2 * i + 1];
+        if (mm < 0 || mm >= (int)s.meshes.size() || v < 0 || v >= s.meshes[mm].nV) return fail(s, GAIA_ERR_INVALID_ARG, "halo send vertex out of range");
+    }
+    cudaSetDevice(s.device);
+    cudaError_t e = halo_add_peer(s, peerRank, peerHandles128, nSend, sendMeshVerts, remoteSlots);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
+}
+int gaia_b200_halo_finalize(gaia_handle* h) {
+    REQUIRE(h); FINALIZED(h);
+    cudaError_t e = halo_finalize(h->s);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(h->s, e);
 }
 
 int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out) {

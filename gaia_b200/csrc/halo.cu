@@ -1,0 +1,184 @@
+// Per-colour halo exchange between partitions of one scene (one process per GPU): boundary vertex positions are stored
+// straight into the neighbours' position arrays over NVLink (peer memory opened with CUDA IPC) and ordered by
+// device-side epoch flags — no host round trip, no collective library call inside the colour loop.
+//
+// Protocol (identical call sequence on every partition; `epoch` counts sync points):
+//   push(g):  peerPos[remoteSlot] = pos[localSlot] for the boundary vertices of colour g (all colours for g = -1)
+//   sync():   flag[myRank] of every neighbour <- epoch (release.sys, after the pushes of this stream), then wait until
+//             every neighbour wrote >= epoch into my flags (acquire.sys)
+// A colour-g push may land while the neighbour is still sweeping colour g: that sweep never reads colour-g positions
+// (proper colouring), and a partition cannot run further ahead because it waits for the neighbour's colour-g flag before
+// sweeping colour g+1.
+#include "scene_impl.h"
+#include <algorithm>
+#include <cstring>
+
+namespace gb {
+
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
+
+static const int kMaxPeers = 8;
+
+struct HaloPeer {
+    int rank = -1;
+    float4* peerPos = nullptr;          // neighbour's position array (IPC mapping)
+    uint32_t* peerFlags = nullptr;      // neighbour's flag array (IPC mapping)
+    std::vector<int2> pairs;            // (local slot, remote slot), ordered by the colour group of the local slot
+    std::vector<int32_t> groupBegin;    // G + 1
+    DevBuf<int2> list;
+};
+
+struct HaloState {
+    DevBuf<uint32_t> flags;             // [worldSize] written by the neighbours
+    std::vector<HaloPeer> peers;
+    uint32_t epoch = 0;
+    bool ready = false;
+    int64_t bytesPushed = 0;
+};
+
+struct PushArgs {
+    int nPeers;
+    float4* peerPos[kMaxPeers];
+    const int2* list[kMaxPeers];
+    int begin[kMaxPeers], count[kMaxPeers];   // slice of each peer's list
+};
+struct SyncArgs {
+    int nPeers;
+    uint32_t* peerFlag[kMaxPeers];      // &neighbourFlags[myRank]
+    const uint32_t* myFlag[kMaxPeers];  // &myFlags[neighbourRank]
+};
+
+__global__ void k_halo_push(PushArgs a, const float4* __restrict__ pos) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int p = 0; p < a.nPeers; p++) {
+        if (i < a.count[p]) {
+            const int2 e = a.list[p][a.begin[p] + i];
+            a.peerPos[p][e.y] = pos[e.x];
+            return;
+        }
+        i -= a.count[p];
+    }
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// one thread per neighbour: publish my epoch, then wait for the neighbour's
+__global__ void k_halo_sync(SyncArgs a, uint32_t epoch, int32_t* errFlags) {
+    const int p = threadIdx.x;
+    if (p >= a.nPeers) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peerFlag[p]), "r"(epoch) : "memory");
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.myFlag[p]) : "memory");
+        if ((int32_t)(v - epoch) >= 0) break;
+        if (globaltimer_ns() - t0 > 10000000000ull) { atomicAdd(errFlags + 4, 1); break; }   // 10 s: a neighbour died
+        __nanosleep(200);
+    }
+}
+
+cudaError_t halo_ipc_handles(Scene& s, void* out128) {
+    if (!s.halo) {
+        s.halo = new HaloState();
+        CK(s.halo->flags.alloc(std::max(64, s.worldSize)));
+        CK(cudaMemset(s.halo->flags.p, 0, s.halo->flags.n * sizeof(uint32_t)));
+    }
+    cudaIpcMemHandle_t hp, hf;
+    CK(cudaIpcGetMemHandle(&hp, s.pos.p));
+    CK(cudaIpcGetMemHandle(&hf, s.halo->flags.p));
+    std::memcpy(out128, &hp, 64);
+    std::memcpy((char*)out128 + 64, &hf, 64);
+    return cudaSuccess;
+}
+
+cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nSend, const int32_t* sendMeshVerts, const int32_t* remoteSlots) {
+    HaloState* h = s.halo;
+    if (!h || (int)h->peers.size() >= kMaxPeers) return cudaErrorInvalidValue;
+    h->peers.emplace_back();
+    HaloPeer& p = h->peers.back();
+    p.rank = peerRank;
+    cudaIpcMemHandle_t hp, hf;
+    std::memcpy(&hp, handles128, 64);
+    std::memcpy(&hf, (const char*)handles128 + 64, 64);
+    CK(cudaIpcOpenMemHandle((void**)&p.peerPos, hp, cudaIpcMemLazyEnablePeerAccess));
+    CK(cudaIpcOpenMemHandle((void**)&p.peerFlags, hf, cudaIpcMemLazyEnablePeerAccess));
+    const int G = (int)s.groupStart.size() - 1;
+    p.pairs.resize(nSend);
+    for (int i = 0; i < nSend; i++) {
+        const HostMesh& m = s.meshes[sendMeshVerts[2 * i]];
+        p.pairs[i] = make_int2(m.sortedId[sendMeshVerts[2 * i + 1]], remoteSlots[i]);
+    }
+    std::stable_sort(p.pairs.begin(), p.pairs.end(), [](const int2& a, const int2& b) { return a.x < b.x; });   // sorted slot order = group order
+    p.groupBegin.assign(G + 1, 0);
+    for (int g = 0, i = 0; g <= G; g++) {
+        while (i < nSend && p.pairs[i].x < s.groupStart[g]) i++;
+        p.groupBegin[g] = i;
+    }
+    p.groupBegin[G] = nSend;
+    CK(p.list.alloc(std::max(nSend, 1)));
+    if (nSend) CK(cudaMemcpy(p.list.p, p.pairs.data(), (size_t)nSend * sizeof(int2), cudaMemcpyHostToDevice));
+    return cudaSuccess;
+}
+
+cudaError_t halo_finalize(Scene& s) {
+    if (!s.halo) return cudaErrorInvalidValue;
+    s.halo->ready = true;
+    return cudaSuccess;
+}
+
+void halo_destroy(Scene& s) {
+    if (!s.halo) return;
+    for (auto& p : s.halo->peers) {
+        if (p.peerPos) cudaIpcCloseMemHandle(p.peerPos);
+        if (p.peerFlags) cudaIpcCloseMemHandle(p.peerFlags);
+    }
+    delete s.halo;
+    s.halo = nullptr;
+}
+
+bool halo_active(const Scene& s) { return s.halo && s.halo->ready && !s.halo->peers.empty(); }
+
+// group < 0: every boundary vertex
+cudaError_t halo_push(Scene& s, int group) {
+    HaloState* h = s.halo;
+    PushArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.nPeers = (int)h->peers.size();
+    const int G = (int)s.groupStart.size() - 1;
+    int total = 0;
+    for (int p = 0; p < a.nPeers; p++) {
+        HaloPeer& hp = h->peers[p];
+        a.peerPos[p] = hp.peerPos; a.list[p] = hp.list.p;
+        a.begin[p] = group < 0 ? 0 : hp.groupBegin[group];
+        a.count[p] = (group < 0 ? hp.groupBegin[G] : hp.groupBegin[group + 1]) - a.begin[p];
+        total += a.count[p];
+    }
+    if (total > 0) {
+        k_halo_push<<<(total + 255) / 256, 256, 0, s.stream>>>(a, s.pos.p);
+        s.stats.kernelLaunches++;
+        h->bytesPushed += 16ll * total;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t halo_sync(Scene& s) {
+    HaloState* h = s.halo;
+    SyncArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.nPeers = (int)h->peers.size();
+    for (int p = 0; p < a.nPeers; p++) {
+        a.peerFlag[p] = h->peers[p].peerFlags + s.myRank;
+        a.myFlag[p] = h->flags.p + h->peers[p].rank;
+    }
+    h->epoch++;
+    k_halo_sync<<<1, 32, 0, s.stream>>>(a, h->epoch, s.errFlags.p);
+    s.stats.kernelLaunches++;
+    return cudaGetLastError();
+}
+
+}  // namespace gb

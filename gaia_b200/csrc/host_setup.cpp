@@ -124,7 +124,8 @@ static void surface_topology(HostMesh& m) {
 }
 
 void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
-                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed) {
+                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed,
+                    bool keepColourOrder) {
     m.nV = nV; m.nT = nT; m.obj = obj;
     m.tets.assign(tets, tets + 4 * (size_t)nT);
     m.pos0.assign(xyz, xyz + 3 * (size_t)nV);
@@ -163,12 +164,15 @@ void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const
         }
     }
     m.fixedMask.assign(nV, 0);
+    m.ghostMask.assign(nV, 0);
     m.fixedPoints.assign(fixed, fixed + nFixed);
     for (int i = 0; i < nFixed; i++) m.fixedMask[fixed[i]] = 1;
     for (int c = 0; c < nColors; c++) m.colors.emplace_back(colorVerts + colorOffsets[c], colorVerts + colorOffsets[c + 1]);
     // size-descending; ties keep file order (documented rule: stable sort)
-    std::stable_sort(m.colors.begin(), m.colors.end(),
-                     [](const std::vector<int32_t>& a, const std::vector<int32_t>& b) { return a.size() > b.size(); });
+    // (a partition of a multi-GPU scene keeps the given order: every partition must sweep the same global colour together)
+    if (!keepColourOrder)
+        std::stable_sort(m.colors.begin(), m.colors.end(),
+                         [](const std::vector<int32_t>& a, const std::vector<int32_t>& b) { return a.size() > b.size(); });
     surface_topology(m);
     if (obj.frameToAppear > 0) { m.activeForCollision = false; m.activeForMaterialSolve = false; }
 }
@@ -318,7 +322,7 @@ bool host_finalize(Scene& s) {
             }
         }
         for (int v = 0; v < m.nV; v++)
-            if (!m.fixedMask[v]) {
+            if (!m.fixedMask[v] && !m.ghostMask[v]) {
                 m.nSolved++;
                 m.nIncSolved += s.h_incOff[m.sortedId[v] + 1] - s.h_incOff[m.sortedId[v]];
             }
@@ -330,7 +334,7 @@ bool host_finalize(Scene& s) {
             for (int t = 0; t < m.nT; t++) {
                 const int32_t* tv = &m.tets[4 * (size_t)t];
                 bool touches = false;
-                for (int k = 0; k < 4; k++) if (m.groupOfVertex[tv[k]] == (int)g && !m.fixedMask[tv[k]]) touches = true;
+                for (int k = 0; k < 4; k++) if (m.groupOfVertex[tv[k]] == (int)g && !m.fixedMask[tv[k]] && !m.ghostMask[tv[k]]) touches = true;
                 if (!touches) continue;
                 for (int q = 0; q < 4; q++)
                     if (m.groupOfVertex[tv[q]] != (int)g && stamp[tv[q]] != (int)g) { stamp[tv[q]] = (int)g; cnt++; }

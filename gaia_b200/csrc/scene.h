@@ -20,6 +20,7 @@ struct HostMesh {
     std::vector<float> restVol;        // nT  (det(Dm)/6, float as the reference computes it)
     std::vector<float> mass;           // nV
     std::vector<uint8_t> fixedMask;
+    std::vector<uint8_t> ghostMask;    // owned by another partition (multi-GPU): never solved here, overwritten by the halo
     std::vector<int32_t> fixedPoints;
     std::vector<std::vector<int32_t>> colors;   // size-descending (stable)
     std::vector<int32_t> groupOfVertex;

@@ -21,6 +21,7 @@ struct DevBuf {
 };
 
 struct CollisionState;   // collision.cu
+struct HaloState;        // halo.cu
 
 // VBDDeformer.h: Rotator / Translator evaluated on the device
 struct Deformer {
@@ -86,6 +87,9 @@ struct Scene {
     size_t pinnedIOBytes = 0;
 
     CollisionState* cs = nullptr;
+    HaloState* halo = nullptr;
+    bool partitionMode = false;         // multi-GPU partition: colour order kept as given
+    int myRank = 0, worldSize = 1;
     std::vector<Deformer*> deformers;
     float curTime = 0.f;                // BasePhysicFramework::curTime (FloatingType)
 
@@ -101,7 +105,8 @@ struct Scene {
 
 // host_setup.cpp
 void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
-                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed);
+                    int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed,
+                    bool keepColourOrder);
 bool host_finalize(Scene& s);
 
 // solve.cu
@@ -113,6 +118,15 @@ cudaError_t run_iterations_only(Scene& s, int nIters);
 cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin, int64_t count, float* outXYZ);
 cudaError_t scatter_from_host(Scene& s, float4* devSorted, int64_t origBegin, int64_t count, const float* inXYZ, bool keepW);
 int check_device_errors(Scene& s);
+
+// halo.cu
+cudaError_t halo_ipc_handles(Scene& s, void* out128);
+cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nSend, const int32_t* sendMeshVerts, const int32_t* remoteSlots);
+cudaError_t halo_finalize(Scene& s);
+void halo_destroy(Scene& s);
+bool halo_active(const Scene& s);
+cudaError_t halo_push(Scene& s, int group);
+cudaError_t halo_sync(Scene& s);
 
 // collision.cu
 cudaError_t collision_init(Scene& s);

@@ -463,6 +463,7 @@ __global__ void k_scatter_xyz(int64_t count, int64_t origBegin, float4* __restri
 static inline int nblk(int64_t n, int per = kBlock) { return (int)((n + per - 1) / per); }
 
 Scene::~Scene() {
+    halo_destroy(*this);
     collision_destroy(*this);
     for (Deformer* d : deformers) delete d;
     if (pinnedIO) cudaFreeHost(pinnedIO);
@@ -526,7 +527,7 @@ cudaError_t device_upload(Scene& s) {
             hpos[sid] = make_float4(m.pos0[3 * (size_t)v], m.pos0[3 * (size_t)v + 1], m.pos0[3 * (size_t)v + 2], 0.f);
             hvel[sid] = make_float4(m.obj.initialVelocity[0], m.obj.initialVelocity[1], m.obj.initialVelocity[2], 0.f);
             hmass[sid] = m.mass[v];
-            hinfo[sid] = (m.id & 0x00FFFFFF) | (m.fixedMask[v] ? (int32_t)0x80000000 : 0);
+            hinfo[sid] = (m.id & 0x00FFFFFF) | ((m.fixedMask[v] || m.ghostMask[v]) ? (int32_t)0x80000000 : 0);
             o2s[m.vertBase + v] = sid;
         }
     hpos[N] = make_float4(0, 0, 0, 0); hvel[N] = hpos[N];
@@ -606,6 +607,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
     }
     const int G = (int)s.groupStart.size() - 1;
     const int N = (int)s.nVerts;
+    const bool halo = halo_active(s);
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
     bool hasContacts = collision_contact_view(s, cv, &colliding);
@@ -633,11 +635,13 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
         }
         for (int g = 0; g < G; g++) {
             const int vb = s.groupStart[g], ve = s.groupStart[g + 1];
-            if (ve <= vb) continue;
+            if (ve <= vb && !halo) continue;
             if (hasContacts) { CK(collision_update_infos(s, g)); }
             if (s.profiling) cudaEventRecord(s.evA, s.stream);
-            if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
-            else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
+            if (ve > vb) {
+                if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
+                else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
+            }
             if (s.profiling) {
                 cudaEventRecord(s.evB, s.stream);
                 cudaEventSynchronize(s.evB);
@@ -645,6 +649,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
                 s.solveKernelMs += ms; s.solveKernelLaunches++;
             }
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
+            if (halo) { CK(halo_push(s, g)); CK(halo_sync(s)); }
         }
         s.stats.vertexSolves += solvedPerIter;
         s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
@@ -725,6 +730,16 @@ cudaError_t upload_deformers(Scene& s) {
     return cudaSuccess;
 }
 
+// after the initial step every ghost must hold its owner's new position: barrier (nobody still reads the old ghosts),
+// push all boundary vertices, wait for the neighbours' pushes
+static cudaError_t halo_refresh(Scene& s) {
+    if (!halo_active(s)) return cudaSuccess;
+    CK(halo_sync(s));
+    CK(halo_push(s, -1));
+    CK(halo_sync(s));
+    return cudaSuccess;
+}
+
 cudaError_t run_substeps(Scene& s, int nSubsteps) {
     sync_mesh_params(s);
     const int N = (int)s.nVerts;
@@ -733,6 +748,7 @@ cudaError_t run_substeps(Scene& s, int nSubsteps) {
         CK(collision_dcd(s, false));
         CK(initial_step(s));
         CK(apply_deformers(s));
+        CK(halo_refresh(s));
         CK(collision_ccd(s));
         CK(collision_prepare(s));
         CK(solve_iterations(s, s.phys.iterations, true));
@@ -751,6 +767,7 @@ cudaError_t run_iterations_only(Scene& s, int nIters) {
     CK(collision_dcd(s, false));
     CK(initial_step(s));
     CK(apply_deformers(s));
+    CK(halo_refresh(s));
     CK(collision_ccd(s));
     CK(collision_prepare(s));
     CK(solve_iterations(s, nIters, false));
@@ -786,6 +803,7 @@ int check_device_errors(Scene& s) {
     if (h[0]) { s.err = "NaN met in the vertex solve"; return GAIA_ERR_NAN; }
     if (h[2]) { s.err = "contact list overflow"; return GAIA_ERR_OVERFLOW; }
     if (h[3]) { s.err = "tetrahedral traversal stack overflow"; return GAIA_ERR_OVERFLOW; }
+    if (h[4]) { s.err = "halo exchange timed out waiting for a neighbour partition"; return GAIA_ERR_TIMEOUT; }
     return GAIA_OK;
 }
 

@@ -38,7 +38,8 @@ typedef enum gaia_status {
     GAIA_ERR_STATE = -4,         /* call order violated (e.g. step before finalize) */
     GAIA_ERR_UNSUPPORTED = -5,   /* a reference feature outside the hot path (e.g. bowl ground) */
     GAIA_ERR_OVERFLOW = -6,      /* a device-side list overflowed its capacity */
-    GAIA_ERR_NAN = -7            /* NaN met in the solve (reference: std::exit(-1), M/VBD/VBDPhysics.cpp:2460) */
+    GAIA_ERR_NAN = -7,           /* NaN met in the solve (reference: std::exit(-1), M/VBD/VBDPhysics.cpp:2460) */
+    GAIA_ERR_TIMEOUT = -8        /* a neighbour partition stopped answering the halo exchange */
 } gaia_status;
 
 /* PhysicsParams of Parameters.json.
@@ -251,6 +252,29 @@ int gaia_b200_get_bvh_leaf_order(gaia_handle* h, int which, int32_t* out, int64_
 
 /* mesh activation (VBDPhysics::enableModels, M/VBD/VBDPhysics.cpp:685-709) */
 int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int activeForMaterialSolve);
+
+/* multi-GPU (no reference counterpart: the reference is single-process) ------------------------------
+ * One process per GPU holds one PARTITION of the scene: the tets incident to the vertices it owns, i.e. owned vertices
+ * plus a one-ring ghost layer. The per-vertex VBD update is local, so owned vertices see their full stencil; after every
+ * colour sweep each partition stores the new positions of its boundary vertices of that colour straight into the ghost
+ * slots of its neighbours' position arrays (peer memory over NVLink, opened through CUDA IPC) and the neighbours wait on
+ * a device-side epoch flag before the next colour.
+ *   set_partition_mode: keep the colour order as given (all partitions must sweep the same global colour at the same
+ *                       time; the per-mesh size-descending sort of M/TetMesh/TetMeshFEM.cpp:122-133 would differ per
+ *                       partition). Call before add_tet_mesh.
+ *   set_ghosts:         vertices of `mesh` owned by another partition: never solved here, overwritten by the halo.
+ *   get_sorted_ids:     device slot of each vertex (what a neighbour needs to address this partition's ghosts).
+ *   halo_ipc_handles:   128 bytes: cudaIpcMemHandle_t of the position array, then of the flag array.
+ *   halo_add_peer:      neighbour `peerRank`; send list = nSend vertices of mesh 0.. given as (mesh, vertex) pairs in
+ *                       `sendMeshVerts` [2*nSend] and the neighbour's slots `remoteSlots` [nSend] they are stored to.
+ *   halo_finalize:      after all peers were added and every process has opened its handles. */
+int gaia_b200_set_partition_mode(gaia_handle* h, int32_t myRank, int32_t worldSize);
+int gaia_b200_set_ghosts(gaia_handle* h, int mesh, const int32_t* verts, int32_t n);
+int gaia_b200_get_sorted_ids(gaia_handle* h, int mesh, const int32_t* verts, int32_t n, int32_t* out);
+int gaia_b200_halo_ipc_handles(gaia_handle* h, void* out128);
+int gaia_b200_halo_add_peer(gaia_handle* h, int32_t peerRank, const void* peerHandles128, int32_t nSend,
+                            const int32_t* sendMeshVerts, const int32_t* remoteSlots);
+int gaia_b200_halo_finalize(gaia_handle* h);
 
 /* statistics */
 int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out);

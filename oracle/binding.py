@@ -26,6 +26,9 @@ def load_oracle():
         bind_scene_api(lib, "oracle_")
         P, FP, IP = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
         lib.oracle_num_threads.argtypes = [P]
+        for f in ("phase_begin_substep", "phase_prepare", "phase_end_substep"):
+            getattr(lib, "oracle_" + f).argtypes = [P]
+        lib.oracle_phase_solve_group.argtypes = [P, C.c_int, C.c_int]
         lib.oracle_set_prev_positions.argtypes = [P, C.c_int, FP]
         lib.oracle_get_dminv.argtypes = [P, C.c_int, FP]
         lib.oracle_get_rest_volumes.argtypes = [P, C.c_int, FP]
@@ -89,6 +92,18 @@ class OracleScene(SceneBase):
     @property
     def num_threads(self):
         return self._lib.oracle_num_threads(self.h)
+
+    def phase_begin_substep(self):
+        self._call("phase_begin_substep")
+
+    def phase_prepare(self):
+        self._call("phase_prepare")
+
+    def phase_solve_group(self, g, apply_friction=True):
+        self._call("phase_solve_group", int(g), int(apply_friction))
+
+    def phase_end_substep(self):
+        self._call("phase_end_substep")
 
     def set_prev_positions(self, mesh, prev):
         p = _f32(prev)

@@ -41,7 +41,7 @@ int oracle_add_tet_mesh(void* h, int32_t nV, int32_t nT, const float* xyz, const
     // VBDPhysics::timeStepEqualize (VBDPhysics.cpp:794-807)
     o.exponentialVelDamping = std::pow(o.exponentialVelDamping, s->dt);
     o.constantVelDamping = o.constantVelDamping * s->dt;
-    mesh_initialize(m, nV, nT, xyz, tets, o, nColors, colorOffsets, colorVerts, nFixed, fixed);
+    mesh_initialize(m, nV, nT, xyz, tets, o, nColors, colorOffsets, colorVerts, nFixed, fixed, s->keepColourOrder);
     return m.id;
 }
 static int add_deformer(void* h, int type, int mesh, const int32_t* verts, int32_t n, const float* origin, const float* axis, const float* speed,
@@ -73,6 +73,19 @@ int oracle_add_rotator(void* h, int mesh, const int32_t* verts, int32_t n, const
 int oracle_add_translator(void* h, int mesh, const int32_t* verts, int32_t n, const float* speed, double endTime) {
     return add_deformer(h, 1, mesh, verts, n, nullptr, nullptr, speed, 0.0, endTime);
 }
+
+// multi-process tests: a partition keeps the global colour order; ghosts behave like fixed points (never solved, overwritten
+// by the exchange)
+int oracle_set_partition_mode(void* h, int32_t, int32_t) { ((Scene*)h)->keepColourOrder = true; return GAIA_OK; }
+int oracle_set_ghosts(void* h, int mesh, const int32_t* verts, int32_t n) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    for (int i = 0; i < n; i++) if (!m.fixedMask[verts[i]]) { m.fixedMask[verts[i]] = 1; m.fixedPoints.push_back(verts[i]); }
+    return GAIA_OK;
+}
+int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
+int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }
+int oracle_phase_solve_group(void* h, int g, int applyFriction) { phase_solve_group(*(Scene*)h, g, applyFriction != 0); return GAIA_OK; }
+int oracle_phase_end_substep(void* h) { phase_end_substep(*(Scene*)h); return GAIA_OK; }
 
 int oracle_finalize(void* h) { scene_finalize(*(Scene*)h); return GAIA_OK; }
 

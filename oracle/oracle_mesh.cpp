@@ -134,7 +134,8 @@ static void build_topology(Mesh& m) {
 }
 
 void mesh_initialize(Mesh& m, int nV, int nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
-                     int nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int nFixed, const int32_t* fixed) {
+                     int nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int nFixed, const int32_t* fixed,
+                     bool keepColourOrder) {
     m.nV = nV; m.nT = nT; m.obj = obj;
     m.pos.resize(nV);
     for (int v = 0; v < nV; v++) m.pos[v] = V3(xyz[3 * v], xyz[3 * v + 1], xyz[3 * v + 2]);
@@ -145,8 +146,9 @@ void mesh_initialize(Mesh& m, int nV, int nT, const float* xyz, const int32_t* t
     m.colors.clear();
     for (int c = 0; c < nColors; c++)
         m.colors.emplace_back(colorVerts + colorOffsets[c], colorVerts + colorOffsets[c + 1]);
-    std::stable_sort(m.colors.begin(), m.colors.end(),
-                     [](const std::vector<int>& a, const std::vector<int>& b) { return a.size() > b.size(); });
+    if (!keepColourOrder)
+        std::stable_sort(m.colors.begin(), m.colors.end(),
+                         [](const std::vector<int>& a, const std::vector<int>& b) { return a.size() > b.size(); });
     // rotation -> scale -> translation (TetMeshFEM.cpp:369-384)
     V3 rot(obj.rotation[0], obj.rotation[1], obj.rotation[2]);
     float ang = norm(rot);

@@ -315,6 +315,31 @@ static float accelerator_omega(int order, float rho, float prevOmega) {
     }
 }
 
+void phase_solve_group(Scene& s, int g, bool apply_friction) {
+    const std::vector<int>& grp = s.vertexParallelGroups[g];
+    const std::vector<int>& act = s.activeCollisionsEachGroup[g];
+    const int64_t nAct = (int64_t)act.size() / 2;
+    s.pool->parallel_for(nAct, [&](int64_t b, int64_t e) {
+        for (int64_t i = b; i < e; i++) {
+            Mesh& m = s.meshes[act[2 * i]];
+            update_collision_info(s, m.colResults[m.tetVertToSurf[act[2 * i + 1]]]);
+        }
+    }, 16);
+    const int64_t n = (int64_t)grp.size() / 2;
+    std::atomic<int64_t> solved{0};
+    s.pool->parallel_for(n, [&](int64_t b, int64_t e) {
+        int64_t cnt = 0;
+        for (int64_t i = b; i < e; i++) {
+            Mesh& m = s.meshes[grp[2 * i]];
+            const int v = grp[2 * i + 1];
+            if (!m.fixedMask[v] && m.activeForMaterialSolve) { vbd_step_with_collision(s, m, v, apply_friction); cnt++; }
+        }
+        solved += cnt;
+    }, 64);
+    s.stats.vertexSolves += solved.load();
+    s.stats.colourSweeps++;
+}
+
 static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
     const bool accel = s.phys.useAccelerator != 0;
     std::vector<std::vector<V3>> pp, pIter;
@@ -326,30 +351,7 @@ static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
             omega = accelerator_omega(s.iIter + 1, s.phys.acceleratorRho, omega);
             for (size_t im = 0; im < s.meshes.size(); im++) pIter[im] = s.meshes[im].pos;
         }
-        for (size_t g = 0; g < s.vertexParallelGroups.size(); g++) {
-            const std::vector<int>& grp = s.vertexParallelGroups[g];
-            const std::vector<int>& act = s.activeCollisionsEachGroup[g];
-            const int64_t nAct = (int64_t)act.size() / 2;
-            s.pool->parallel_for(nAct, [&](int64_t b, int64_t e) {
-                for (int64_t i = b; i < e; i++) {
-                    Mesh& m = s.meshes[act[2 * i]];
-                    update_collision_info(s, m.colResults[m.tetVertToSurf[act[2 * i + 1]]]);
-                }
-            }, 16);
-            const int64_t n = (int64_t)grp.size() / 2;
-            std::atomic<int64_t> solved{0};
-            s.pool->parallel_for(n, [&](int64_t b, int64_t e) {
-                int64_t cnt = 0;
-                for (int64_t i = b; i < e; i++) {
-                    Mesh& m = s.meshes[grp[2 * i]];
-                    const int v = grp[2 * i + 1];
-                    if (!m.fixedMask[v] && m.activeForMaterialSolve) { vbd_step_with_collision(s, m, v, apply_friction); cnt++; }
-                }
-                solved += cnt;
-            }, 64);
-            s.stats.vertexSolves += solved.load();
-            s.stats.colourSweeps++;
-        }
+        for (size_t g = 0; g < s.vertexParallelGroups.size(); g++) phase_solve_group(s, (int)g, apply_friction);
         if (accel) {
             for (size_t im = 0; im < s.meshes.size(); im++) {
                 Mesh& m = s.meshes[im];
@@ -403,6 +405,15 @@ void enable_models(Scene& s) {
         }
     }
 }
+
+void phase_begin_substep(Scene& s) {
+    s.curTime += s.dt;
+    dcd(s, false);
+    for (auto& m : s.meshes) if (m.activeForMaterialSolve) apply_initial_step(s, m);
+    apply_deformers(s);
+}
+void phase_prepare(Scene& s) { ccd(s); prepare_collision_data(s); }
+void phase_end_substep(Scene& s) { update_velocities(s); s.stats.substeps++; }
 
 void run_step(Scene& s) {
     for (s.substep = 0; s.substep < s.phys.numSubsteps; s.substep++) {

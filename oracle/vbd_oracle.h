@@ -81,6 +81,7 @@ struct Scene {
     // ActiveCollisionList (M/VBD/ActiveCollisionList.h:20-52): per group [mesh,v,...]
     std::vector<std::vector<int>> activeCollisionsEachGroup;
     bool finalized = false;
+    bool keepColourOrder = false;   // partition of a multi-GPU scene: colours stay in the given (global) order
     int frameId = 0, substep = 0, iIter = 0;
     float curTime = 0.f;
     std::vector<Deformer> deformers;
@@ -95,11 +96,17 @@ struct Scene {
 
 // oracle_mesh.cpp
 void mesh_initialize(Mesh& m, int nV, int nT, const float* xyz, const int32_t* tets, const gaia_object_params& obj,
-                     int nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int nFixed, const int32_t* fixed);
+                     int nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int nFixed, const int32_t* fixed,
+                     bool keepColourOrder = false);
 void scene_finalize(Scene& s);
 // oracle_step.cpp
 void run_step(Scene& s);                  // VBDPhysics::runStep_hybridCollisionHandling, one frame
 void run_iterations(Scene& s, int nIters); // initial step + nIters colour sweeps
+// phase-level stepping (multi-process tests drive the colour loop themselves and exchange ghosts between phases)
+void phase_begin_substep(Scene& s);       // curTime += dt, dcd, initial step, deformers
+void phase_prepare(Scene& s);             // ccd + prepareCollisionData
+void phase_solve_group(Scene& s, int g, bool applyFriction);
+void phase_end_substep(Scene& s);         // velocities
 void enable_models(Scene& s);
 void neohookean_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, M3& h);
 bool solve3x3_psd_stable(const float* m, const float* b, float* out);
