@@ -278,19 +278,26 @@ def main():
         t = torch.tensor([solves2], device="cuda", dtype=torch.float64)
         dist.all_reduce(t)
         solves2 = float(t.item())
-    e2e = {"value": solves2 / (ms_e2e * 1e-3), "unit": "vertex-solves/s", "h2d_bytes_per_step": int(2 * nV * 12),
-           "d2h_bytes_per_step": int(nV * 12), "wall_ms_per_step": 1e3 * wall_e2e / args.steps}
+    nV_all = nV
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([nV], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        nV_all = int(t.item())         # owned + ghost vertices of every partition
+    e2e = {"value": solves2 / (ms_e2e * 1e-3), "unit": "vertex-solves/s", "h2d_bytes_per_step": int(2 * nV_all * 12),
+           "d2h_bytes_per_step": int(nV_all * 12), "wall_ms_per_step": 1e3 * wall_e2e / args.steps}
 
     # ---- roofline of the dominant kernel: per-launch CUDA events on the launching stream (untimed extra steps)
+    # (every rank runs the same steps: partitions advance in lock-step through the halo protocol)
     roof = None
+    scene.reset_stats()
+    scene.set_profiling(True)
+    for _ in range(max(1, args.profile_steps)):
+        scene.run_frames(1)
+    scene.synchronize()
+    sp = scene.stats()
+    scene.set_profiling(False)
     if rank == 0:
-        scene.reset_stats()
-        scene.set_profiling(True)
-        for _ in range(max(1, args.profile_steps)):
-            scene.run_frames(1)
-        scene.synchronize()
-        sp = scene.stats()
-        scene.set_profiling(False)
         k_ms = sp["timeCsmpMaterialSolve"]
         launches = sp["colourSweeps"]
         alg_bytes = sp["algorithmicBytes"]
@@ -300,7 +307,7 @@ def main():
                 "algorithmic_bytes_per_launch": alg_bytes / max(1, launches), "avg_launch_us": 1e3 * k_ms / max(1, launches),
                 "launches_profiled": launches, "kernel_share_of_step": (k_ms / max(1, args.profile_steps)) / (ms / args.steps)}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
+        if os.path.exists(tpath) and world == 1:
             try:
                 with open(tpath) as f:
                     tj = json.load(f)

@@ -30,6 +30,7 @@ struct HaloPeer {
 
 struct HaloState {
     DevBuf<uint32_t> flags;             // [worldSize] written by the neighbours
+    DevBuf<uint32_t> ctl;               // [0] epoch, [1] block ticket
     std::vector<HaloPeer> peers;
     uint32_t epoch = 0;
     bool ready = false;
@@ -41,24 +42,9 @@ struct PushArgs {
     float4* peerPos[kMaxPeers];
     const int2* list[kMaxPeers];
     int begin[kMaxPeers], count[kMaxPeers];   // slice of each peer's list
+    uint32_t* peerFlag[kMaxPeers];            // &neighbourFlags[myRank]
+    const uint32_t* myFlag[kMaxPeers];        // &myFlags[neighbourRank]
 };
-struct SyncArgs {
-    int nPeers;
-    uint32_t* peerFlag[kMaxPeers];      // &neighbourFlags[myRank]
-    const uint32_t* myFlag[kMaxPeers];  // &myFlags[neighbourRank]
-};
-
-__global__ void k_halo_push(PushArgs a, const float4* __restrict__ pos) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    for (int p = 0; p < a.nPeers; p++) {
-        if (i < a.count[p]) {
-            const int2 e = a.list[p][a.begin[p] + i];
-            a.peerPos[p][e.y] = pos[e.x];
-            return;
-        }
-        i -= a.count[p];
-    }
-}
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
@@ -66,20 +52,43 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
-// one thread per neighbour: publish my epoch, then wait for the neighbour's
-__global__ void k_halo_sync(SyncArgs a, uint32_t epoch, int32_t* errFlags) {
-    const int p = threadIdx.x;
-    if (p >= a.nPeers) return;
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peerFlag[p]), "r"(epoch) : "memory");
-    const unsigned long long t0 = globaltimer_ns();
-    for (;;) {
-        uint32_t v;
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.myFlag[p]) : "memory");
-        if ((int32_t)(v - epoch) >= 0) break;
-        if (globaltimer_ns() - t0 > 10000000000ull) { atomicAdd(errFlags + 4, 1); break; }   // 10 s: a neighbour died
-        __nanosleep(200);
+// One launch per colour: every block stores its slice of the boundary positions into the neighbours' ghost slots; the last
+// block to finish (ticket counter) publishes the new epoch to every neighbour and waits for theirs. The epoch lives on the
+// device (ctl[0] = epoch, ctl[1] = ticket) so the launch can be replayed from a CUDA graph.
+__global__ void k_halo_push_sync(PushArgs a, const float4* __restrict__ pos, uint32_t* ctl, int32_t* errFlags) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int p = 0; p < a.nPeers; p++) {
+        if (i < a.count[p]) {
+            const int2 e = a.list[p][a.begin[p] + i];
+            a.peerPos[p][e.y] = pos[e.x];
+            break;
+        }
+        i -= a.count[p];
     }
+    __shared__ bool last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(ctl + 1, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    const uint32_t epoch = ctl[0] + 1;
+    const int p = threadIdx.x;
+    if (p < a.nPeers) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peerFlag[p]), "r"(epoch) : "memory");
+        if (!*(volatile int32_t*)(errFlags + 4)) {       // a neighbour already timed out: do not stall every later sync
+            const unsigned long long t0 = globaltimer_ns();
+            for (;;) {
+                uint32_t v;
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.myFlag[p]) : "memory");
+                if ((int32_t)(v - epoch) >= 0) break;
+                if (globaltimer_ns() - t0 > 5000000000ull) { atomicAdd(errFlags + 4, 1); break; }   // 5 s: a neighbour died or left the protocol
+                __nanosleep(100);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { ctl[0] = epoch; ctl[1] = 0; }
 }
 
 cudaError_t halo_ipc_handles(Scene& s, void* out128) {
@@ -87,6 +96,8 @@ cudaError_t halo_ipc_handles(Scene& s, void* out128) {
         s.halo = new HaloState();
         CK(s.halo->flags.alloc(std::max(64, s.worldSize)));
         CK(cudaMemset(s.halo->flags.p, 0, s.halo->flags.n * sizeof(uint32_t)));
+        CK(s.halo->ctl.alloc(4));
+        CK(cudaMemset(s.halo->ctl.p, 0, 4 * sizeof(uint32_t)));
     }
     cudaIpcMemHandle_t hp, hf;
     CK(cudaIpcGetMemHandle(&hp, s.pos.p));
@@ -143,8 +154,9 @@ void halo_destroy(Scene& s) {
 
 bool halo_active(const Scene& s) { return s.halo && s.halo->ready && !s.halo->peers.empty(); }
 
-// group < 0: every boundary vertex
-cudaError_t halo_push(Scene& s, int group) {
+// group >= 0: push that colour's boundary vertices, then sync; group == -1: push every boundary vertex, then sync;
+// group == -2: sync only (barrier among neighbours)
+cudaError_t halo_push_sync(Scene& s, int group) {
     HaloState* h = s.halo;
     PushArgs a;
     std::memset(&a, 0, sizeof(a));
@@ -155,30 +167,18 @@ cudaError_t halo_push(Scene& s, int group) {
         HaloPeer& hp = h->peers[p];
         a.peerPos[p] = hp.peerPos; a.list[p] = hp.list.p;
         a.begin[p] = group < 0 ? 0 : hp.groupBegin[group];
-        a.count[p] = (group < 0 ? hp.groupBegin[G] : hp.groupBegin[group + 1]) - a.begin[p];
+        a.count[p] = group == -2 ? 0 : (group < 0 ? hp.groupBegin[G] : hp.groupBegin[group + 1]) - a.begin[p];
+        a.peerFlag[p] = hp.peerFlags + s.myRank;
+        a.myFlag[p] = h->flags.p + hp.rank;
         total += a.count[p];
     }
-    if (total > 0) {
-        k_halo_push<<<(total + 255) / 256, 256, 0, s.stream>>>(a, s.pos.p);
-        s.stats.kernelLaunches++;
-        h->bytesPushed += 16ll * total;
-    }
+    k_halo_push_sync<<<std::max(1, (total + 255) / 256), 256, 0, s.stream>>>(a, s.pos.p, h->ctl.p, s.errFlags.p);
+    s.stats.kernelLaunches++;
+    h->bytesPushed += 16ll * total;
     return cudaGetLastError();
 }
 
-cudaError_t halo_sync(Scene& s) {
-    HaloState* h = s.halo;
-    SyncArgs a;
-    std::memset(&a, 0, sizeof(a));
-    a.nPeers = (int)h->peers.size();
-    for (int p = 0; p < a.nPeers; p++) {
-        a.peerFlag[p] = h->peers[p].peerFlags + s.myRank;
-        a.myFlag[p] = h->flags.p + h->peers[p].rank;
-    }
-    h->epoch++;
-    k_halo_sync<<<1, 32, 0, s.stream>>>(a, h->epoch, s.errFlags.p);
-    s.stats.kernelLaunches++;
-    return cudaGetLastError();
-}
+cudaError_t halo_push(Scene& s, int group) { return halo_push_sync(s, group); }
+cudaError_t halo_sync(Scene& s) { return halo_push_sync(s, -2); }
 
 }  // namespace gb

@@ -93,6 +93,11 @@ struct Scene {
     std::vector<Deformer*> deformers;
     float curTime = 0.f;                // BasePhysicFramework::curTime (FloatingType)
 
+    // CUDA graph of the colour loop of one substep (solve.cu: solve_iterations)
+    cudaGraphExec_t iterGraphExec = nullptr;
+    int iterGraphIters = -1, iterCalls = 0;
+    int64_t iterDelta[4] = {0, 0, 0, 0};
+
     // statistics / profiling
     gaia_stats stats;
     bool profiling = false;

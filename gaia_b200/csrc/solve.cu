@@ -467,6 +467,7 @@ Scene::~Scene() {
     collision_destroy(*this);
     for (Deformer* d : deformers) delete d;
     if (pinnedIO) cudaFreeHost(pinnedIO);
+    if (iterGraphExec) cudaGraphExecDestroy(iterGraphExec);
     if (evA) cudaEventDestroy(evA);
     if (evB) cudaEventDestroy(evB);
     if (stream) cudaStreamDestroy(stream);
@@ -493,6 +494,7 @@ void sync_mesh_params(Scene& s) {
     cudaMemcpyAsync(s.meshParams.p, s.h_meshParams.data(), s.h_meshParams.size() * sizeof(MeshParamsDev), cudaMemcpyHostToDevice, s.stream);
     cudaStreamSynchronize(s.stream);
     s.meshParamsDirty = false;
+    if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }   // per-iteration accounting changed
 }
 
 cudaError_t device_upload(Scene& s) {
@@ -586,10 +588,12 @@ static void launch_one(Scene& s, int vb, int ve, int applyFriction, const Contac
 
 template <bool HC>
 static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int applyFriction, const ContactView& cv) {
-    // big colours: every block walks L rounds (full-width tail); small colours keep one round per block so the grid
-    // still covers all 148 SMs
-    const bool big = (int64_t)(ve - vb) >= (int64_t)148 * 8 * kBlock;
-#define BYVAR(LL) if (big) { if (variant == 0) launch_one<LL, HC, 0, LL>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, LL>(s, vb, ve, applyFriction, cv); } \
+    // rounds per block: big colours walk L rounds per block (full-width tail); smaller ones fewer rounds, so that the grid
+    // still fills the 148 SMs x 4 resident blocks for a few waves
+    const int64_t n = ve - vb;
+    const int rounds = n >= (int64_t)148 * 8 * kBlock ? L : (n >= (int64_t)148 * 4 * kBlock ? 2 : 1);
+#define BYVAR(LL) if (rounds == LL) { if (variant == 0) launch_one<LL, HC, 0, LL>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, LL>(s, vb, ve, applyFriction, cv); } \
+                  else if (rounds == 2) { if (variant == 0) launch_one<LL, HC, 0, 2>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 2>(s, vb, ve, applyFriction, cv); } \
                   else { if (variant == 0) launch_one<LL, HC, 0, 1>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 1>(s, vb, ve, applyFriction, cv); }
     switch (L) {
         case 8: BYVAR(8); break;
@@ -598,7 +602,7 @@ static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int apply
 #undef BYVAR
 }
 
-static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
+static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
     static bool envRead = false;
     if (!envRead) {
         const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e);
@@ -649,7 +653,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
                 s.solveKernelMs += ms; s.solveKernelLaunches++;
             }
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
-            if (halo) { CK(halo_push(s, g)); CK(halo_sync(s)); }
+            if (halo) CK(halo_push(s, g));
         }
         s.stats.vertexSolves += solvedPerIter;
         s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
@@ -666,6 +670,36 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
         }
     }
     return cudaGetLastError();
+}
+
+// The colour loop of one substep is launch-bound for small colours (hundreds of ~10 us kernels): when nothing in it needs
+// the host (no collision pipeline, no per-kernel profiling) it is captured once into a CUDA graph and replayed.
+static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
+    static int useGraphs = -1;
+    if (useGraphs < 0) { const char* e = getenv("GAIA_B200_GRAPH"); useGraphs = e ? atoi(e) : 1; }
+    const bool graphable = useGraphs && !s.profiling && !s.cs && s.iterCalls > 0 && nIters > 0;
+    s.iterCalls++;
+    if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD);
+    if (!s.iterGraphExec || s.iterGraphIters != nIters) {
+        if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }
+        const gaia_stats before = s.stats;
+        CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+        cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD);
+        cudaGraph_t g = nullptr;
+        cudaError_t e2 = cudaStreamEndCapture(s.stream, &g);
+        if (e != cudaSuccess) return e;
+        CK(e2);
+        CK(cudaGraphInstantiate(&s.iterGraphExec, g, 0));
+        cudaGraphDestroy(g);
+        s.iterGraphIters = nIters;
+        s.iterDelta[0] = s.stats.vertexSolves - before.vertexSolves; s.iterDelta[1] = s.stats.colourSweeps - before.colourSweeps;
+        s.iterDelta[2] = s.stats.kernelLaunches - before.kernelLaunches; s.iterDelta[3] = s.stats.algorithmicBytes - before.algorithmicBytes;
+        s.stats = before;
+    }
+    CK(cudaGraphLaunch(s.iterGraphExec, s.stream));
+    s.stats.vertexSolves += s.iterDelta[0]; s.stats.colourSweeps += s.iterDelta[1];
+    s.stats.kernelLaunches += s.iterDelta[2]; s.stats.algorithmicBytes += s.iterDelta[3];
+    return cudaSuccess;
 }
 
 static cudaError_t initial_step(Scene& s) {
@@ -735,8 +769,7 @@ cudaError_t upload_deformers(Scene& s) {
 static cudaError_t halo_refresh(Scene& s) {
     if (!halo_active(s)) return cudaSuccess;
     CK(halo_sync(s));
-    CK(halo_push(s, -1));
-    CK(halo_sync(s));
+    CK(halo_push(s, -1));     // push + publish epoch + wait for the neighbours' pushes, one launch
     return cudaSuccess;
 }
 
