@@ -62,7 +62,7 @@ class Contact(C.Structure):
 class Stats(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("timeCsmpInitialStep", "timeCsmpMaterialSolve", "timeCsmpUpdateVelocity",
                                           "timeCsmpUpdatingBVHDCD", "timeCsmpColDetectDCD", "timeCsmpUpdatingBVHCCD",
-                                          "timeCsmpColDetectCCD", "timeCsmpFrame")] + \
+                                          "timeCsmpColDetectCCD", "timeCsmpFrame", "solveKernelMs")] + \
                [(n, C.c_int64) for n in ("vertexSolves", "colourSweeps", "substeps", "frames", "kernelLaunches",
                                          "algorithmicBytes", "numContactsDCD", "numContactsCCD")]
 

@@ -384,7 +384,7 @@ int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out) {
     REQUIRE(h);
     if (!out) return GAIA_ERR_INVALID_ARG;
     *out = h->s.stats;
-    if (h->s.profiling) out->timeCsmpMaterialSolve = h->s.solveKernelMs;
+    out->solveKernelMs = h->s.solveKernelMs;
     return GAIA_OK;
 }
 int gaia_b200_reset_stats(gaia_handle* h) {

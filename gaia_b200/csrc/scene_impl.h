@@ -101,7 +101,7 @@ struct Scene {
     // statistics / profiling
     gaia_stats stats;
     bool profiling = false;
-    cudaEvent_t evA = nullptr, evB = nullptr;
+    cudaEvent_t evA = nullptr, evB = nullptr, evP0 = nullptr, evP1 = nullptr;
     double solveKernelMs = 0.0;    // accumulated colour-solve kernel time while profiling
     int64_t solveKernelLaunches = 0;
 

@@ -469,6 +469,8 @@ Scene::~Scene() {
     if (pinnedIO) cudaFreeHost(pinnedIO);
     if (iterGraphExec) cudaGraphExecDestroy(iterGraphExec);
     if (evA) cudaEventDestroy(evA);
+    if (evP0) cudaEventDestroy(evP0);
+    if (evP1) cudaEventDestroy(evP1);
     if (evB) cudaEventDestroy(evB);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -500,7 +502,7 @@ void sync_mesh_params(Scene& s) {
 cudaError_t device_upload(Scene& s) {
     const int64_t N = s.nVerts;
     CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-    CK(cudaEventCreate(&s.evA)); CK(cudaEventCreate(&s.evB));
+    CK(cudaEventCreate(&s.evA)); CK(cudaEventCreate(&s.evB)); CK(cudaEventCreate(&s.evP0)); CK(cudaEventCreate(&s.evP1));
     CK(s.pos.alloc(N + 1)); CK(s.prev.alloc(N + 1)); CK(s.inertia.alloc(N + 1)); CK(s.vel.alloc(N + 1));
     CK(s.mass.alloc(N)); CK(s.info.alloc(N)); CK(s.incOff.alloc(N + 1));
     CK(s.incW.alloc(s.nInc)); CK(s.incIdx.alloc(s.nInc)); CK(s.nbOff.alloc(N + 1)); CK(s.nbList.alloc(s.nNb)); CK(s.vtx.alloc(N));
@@ -773,19 +775,39 @@ static cudaError_t halo_refresh(Scene& s) {
     return cudaSuccess;
 }
 
+// per-phase device time with the reference's timer names (M/Timer/RunningTimeStatistics.h), only while profiling
+template <class F>
+static cudaError_t timed_phase(Scene& s, double& acc, F&& fn) {
+    if (!s.profiling) return fn();
+    cudaEventRecord(s.evP0, s.stream);
+    cudaError_t e = fn();
+    cudaEventRecord(s.evP1, s.stream);
+    cudaEventSynchronize(s.evP1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, s.evP0, s.evP1);
+    acc += ms;
+    return e;
+}
+
 cudaError_t run_substeps(Scene& s, int nSubsteps) {
     sync_mesh_params(s);
     const int N = (int)s.nVerts;
     for (s.substep = 0; s.substep < nSubsteps; s.substep++) {
         s.curTime += s.dt;
-        CK(collision_dcd(s, false));
-        CK(initial_step(s));
-        CK(apply_deformers(s));
-        CK(halo_refresh(s));
-        CK(collision_ccd(s));
-        CK(collision_prepare(s));
-        CK(solve_iterations(s, s.phys.iterations, true));
-        k_update_velocity<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.vel.p, s.info.p, s.meshParams.p, s.stepParams);
+        CK(timed_phase(s, s.stats.timeCsmpColDetectDCD, [&] { return collision_dcd(s, false); }));
+        CK(timed_phase(s, s.stats.timeCsmpInitialStep, [&] { cudaError_t e = initial_step(s); if (e == cudaSuccess) e = apply_deformers(s); if (e == cudaSuccess) e = halo_refresh(s); return e; }));
+        CK(timed_phase(s, s.stats.timeCsmpColDetectCCD, [&] { cudaError_t e = collision_ccd(s); if (e == cudaSuccess) e = collision_prepare(s); return e; }));
+        {
+            const double solveBefore = s.solveKernelMs;
+            double whole = 0.0;
+            CK(timed_phase(s, whole, [&] { return solve_iterations(s, s.phys.iterations, true); }));
+            s.stats.timeCsmpMaterialSolve += whole;      // colour loop incl. contact pre-passes (and intermediate detection)
+            (void)solveBefore;
+        }
+        CK(timed_phase(s, s.stats.timeCsmpUpdateVelocity, [&] {
+            k_update_velocity<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.vel.p, s.info.p, s.meshParams.p, s.stepParams);
+            return cudaGetLastError();
+        }));
         s.stats.kernelLaunches++;
         s.stats.substeps++;
     }

@@ -437,7 +437,7 @@ void VBDPhysicsB200::writeStatistics(const std::string& outFolder, int frameId) 
     j << "{\n  \"timeCsmpInitialStep\": " << st.timeCsmpInitialStep << ",\n  \"timeCsmpMaterialSolve\": " << st.timeCsmpMaterialSolve
       << ",\n  \"timeCsmpUpdateVelocity\": " << st.timeCsmpUpdateVelocity << ",\n  \"timeCsmpUpdatingBVHDCD\": " << st.timeCsmpUpdatingBVHDCD
       << ",\n  \"timeCsmpColDetectDCD\": " << st.timeCsmpColDetectDCD << ",\n  \"timeCsmpUpdatingBVHCCD\": " << st.timeCsmpUpdatingBVHCCD
-      << ",\n  \"timeCsmpColDetectCCD\": " << st.timeCsmpColDetectCCD << ",\n  \"timeCsmpFrame\": " << st.timeCsmpFrame
+      << ",\n  \"timeCsmpColDetectCCD\": " << st.timeCsmpColDetectCCD << ",\n  \"timeCsmpFrame\": " << st.timeCsmpFrame << ",\n  \"solveKernelMs\": " << st.solveKernelMs
       << ",\n  \"vertexSolves\": " << st.vertexSolves << ",\n  \"colourSweeps\": " << st.colourSweeps << ",\n  \"substeps\": " << st.substeps
       << ",\n  \"kernelLaunches\": " << st.kernelLaunches << ",\n  \"algorithmicBytes\": " << st.algorithmicBytes
       << ",\n  \"numContactsDCD\": " << st.numContactsDCD << ",\n  \"numContactsCCD\": " << st.numContactsCCD << "\n}\n";

@@ -203,3 +203,20 @@ REFERENCE_ROOT = "/root/reference"
 
 def reference_available():
     return os.path.isdir(os.path.join(REFERENCE_ROOT, "Data"))
+
+
+def kuhn_blob(n, radii=(1.0, 1.0, 1.0), h=1.0, power=2.0):
+    """A blobby tet mesh: the cells of an n^3 Kuhn grid whose centre lies inside the super-ellipsoid
+    sum(|x_i / r_i|^power) <= 1 (coordinates scaled to [-1,1]); vertices compacted, spacing h.
+    Stands in for the reference's organic models (teapot, bunny, octopus, armadillo) in synthetic many-object scenes."""
+    verts, tets = kuhn_beam(n, n, n, h=1.0)
+    cells = tets.reshape(-1, 6, 4)
+    cen = verts[cells[:, 0, :]].mean(1)                    # tet 0 of a cell spans corner 0 and corner 7: its centroid is near the cell centre
+    u = (cen / n * 2.0 - 1.0) / np.asarray(radii, np.float32)
+    keep = (np.abs(u) ** power).sum(1) <= 1.0
+    t = cells[keep].reshape(-1, 4)
+    used = np.unique(t)
+    remap = -np.ones(len(verts), np.int64)
+    remap[used] = np.arange(len(used))
+    v = (verts[used] - n / 2.0) * np.float32(h)
+    return v.astype(np.float32), remap[t].astype(np.int32)

@@ -148,6 +148,7 @@ typedef struct gaia_stats {
     double timeCsmpUpdatingBVHCCD;
     double timeCsmpColDetectCCD;
     double timeCsmpFrame;
+    double solveKernelMs;       /* device time of the colour-solve kernels alone (CUDA events, profiling mode) */
     int64_t vertexSolves;       /* non-fixed active vertices solved, summed over colour sweeps */
     int64_t colourSweeps;       /* colour kernels executed */
     int64_t substeps;
