@@ -36,6 +36,16 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly ONE JSON line: everything libraries print on fd 1 (NCCL's version banner ...) goes to stderr
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
+
 # --------------------------------------------------------------------------------------------- workloads
 def workload_twist_beam(nx=472, ny=60, nz=60, h=0.02, collisions=False):
     """SURVEY.md §8(d) cfg 4: regular hex grid split into 6 Kuhn tets per cell, both end caps driven by Rotator deformers
@@ -209,7 +219,7 @@ def run_reference_arm(args):
            "config": {"workload": wl["name"], "parallelism": f"cpu{base['cores']}"},
            "cpu_baseline": base, "e2e": {"value": value, "unit": "vertex-solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 # --------------------------------------------------------------------------------------------- our arm
@@ -377,7 +387,7 @@ def main():
                           "l2": "inputs larger than L2 (incidence streams 1.3 GB vs 126 MB), no flush needed",
                           "sim_steps_per_s": st["substeps"] / (ms * 1e-3), "frames_per_s": args.steps / (ms * 1e-3)},
                "clocks": clk, "e2e": e2e, "gpu_launches": int(st["kernelLaunches"]), "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(out), flush=True)
+        emit(out)
     scene.close()
     if world > 1:
         import torch.distributed as dist

@@ -17,7 +17,7 @@ namespace gb {
 
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 
-static const int kMaxPeers = 8;
+static const int kMaxPeers = kMaxHaloPeers;
 
 struct HaloPeer {
     int rank = -1;
@@ -35,6 +35,10 @@ struct HaloState {
     uint32_t epoch = 0;
     bool ready = false;
     int64_t bytesPushed = 0;
+    DevBuf<int32_t> sendIdx;            // fused exchange: per sorted vertex, first entry << 4 | count
+    DevBuf<int2> sendEnt;               // (peer index, remote slot)
+    DevBuf<HaloPeerTable> tab;
+    DevBuf<int32_t> boundaryPrefix;     // [N+1]
 };
 
 struct PushArgs {
@@ -136,10 +140,74 @@ cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nS
     return cudaSuccess;
 }
 
+__global__ void k_mark_boundary(int n, const int32_t* __restrict__ sorted, int4* vtx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) vtx[sorted[i]].w |= kHaloBoundaryBit;
+}
+
+// Tables of the fused exchange (the colour solve pushes its own boundary vertices): every vertex this partition sends is
+// marked in its header and gets its (peer, remote slot) entries.
 cudaError_t halo_finalize(Scene& s) {
-    if (!s.halo) return cudaErrorInvalidValue;
-    s.halo->ready = true;
+    HaloState* h = s.halo;
+    if (!h) return cudaErrorInvalidValue;
+    const int64_t N = s.nVerts;
+    std::vector<int32_t> cnt(N, 0), idx(N, 0);
+    for (auto& p : h->peers) for (auto& e : p.pairs) cnt[e.x]++;
+    std::vector<int32_t> bverts;
+    int64_t total = 0;
+    for (int64_t v = 0; v < N; v++) {
+        if (!cnt[v]) continue;
+        if (cnt[v] > 15) return cudaErrorInvalidValue;
+        idx[v] = (int32_t)((total << 4) | cnt[v]);
+        total += cnt[v]; bverts.push_back((int32_t)v);
+        cnt[v] = 0;
+    }
+    if (total >= (1 << 27)) return cudaErrorInvalidValue;
+    std::vector<int2> ent(std::max<int64_t>(total, 1));
+    for (size_t pi = 0; pi < h->peers.size(); pi++)
+        for (auto& e : h->peers[pi].pairs) ent[(idx[e.x] >> 4) + cnt[e.x]++] = make_int2((int)pi, e.y);
+    CK(h->sendIdx.alloc(std::max<int64_t>(N, 1)));
+    CK(h->sendEnt.alloc(ent.size()));
+    CK(cudaMemcpy(h->sendIdx.p, idx.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->sendEnt.p, ent.data(), ent.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    if (!bverts.empty()) {
+        DevBuf<int32_t> d;
+        CK(d.alloc(bverts.size()));
+        CK(cudaMemcpy(d.p, bverts.data(), bverts.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        k_mark_boundary<<<((int)bverts.size() + 255) / 256, 256, 0, s.stream>>>((int)bverts.size(), d.p, s.vtx.p);
+        CK(cudaStreamSynchronize(s.stream));
+    }
+    {
+        std::vector<int32_t> prefix(N + 1, 0);
+        for (int64_t v = 0; v < N; v++) prefix[v + 1] = prefix[v] + (idx[v] ? 1 : 0);
+        CK(h->boundaryPrefix.alloc(N + 1));
+        CK(cudaMemcpy(h->boundaryPrefix.p, prefix.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    HaloPeerTable t;
+    std::memset(&t, 0, sizeof(t));
+    for (size_t p = 0; p < h->peers.size(); p++) {
+        t.peerPos[p] = h->peers[p].peerPos;
+        t.peerFlag[p] = h->peers[p].peerFlags + s.myRank;
+        t.myFlag[p] = h->flags.p + h->peers[p].rank;
+    }
+    CK(h->tab.alloc(1));
+    CK(cudaMemcpy(h->tab.p, &t, sizeof(t), cudaMemcpyHostToDevice));
+    h->ready = true;
     return cudaSuccess;
+}
+
+bool halo_view(Scene& s, HaloView& hv) {
+    if (!halo_active(s)) return false;
+    HaloState* h = s.halo;
+    std::memset(&hv, 0, sizeof(hv));
+    hv.nPeers = (int)h->peers.size();
+    hv.tab = h->tab.p;
+    hv.boundaryPrefix = h->boundaryPrefix.p; hv.sendIdx = h->sendIdx.p; hv.sendEnt = h->sendEnt.p; hv.ctl = h->ctl.p;
+    return true;
+}
+
+void halo_count_fused(Scene& s, int group) {
+    for (auto& p : s.halo->peers) s.halo->bytesPushed += 16ll * (p.groupBegin[group + 1] - p.groupBegin[group]);
 }
 
 void halo_destroy(Scene& s) {

@@ -10,6 +10,11 @@ template <class T>
 struct DevBuf {
     T* p = nullptr;
     size_t n = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;                 // owning: a copy would free the same allocation twice
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept { if (this != &o) { free(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; } return *this; }
     cudaError_t alloc(size_t count) {
         free();
         n = count;
@@ -43,6 +48,27 @@ struct ContactView {
     const float4* cH0;                // h00,h01,h02,h11
     const float4* cH1;                // h12,h22,bary0,bary1
     const float* cB2;                 // bary2
+};
+
+// what the colour-solve kernel needs for the fused halo exchange (filled by halo.cu): boundary vertices (bit 30 of
+// vtx.w) wait for the neighbours' epoch before they gather ghost positions and store their new position straight into
+// the neighbours' ghost slots; the last block of the launch publishes the new epoch
+static const int kMaxHaloPeers = 8;
+static const int kHaloBoundaryBit = 1 << 30;
+struct HaloPeerTable {                        // lives in device memory (indexed dynamically by the kernels)
+    float4* peerPos[kMaxHaloPeers];
+    uint32_t* peerFlag[kMaxHaloPeers];        // &neighbourFlags[myRank]
+    const uint32_t* myFlag[kMaxHaloPeers];    // &myFlags[neighbourRank]
+};
+struct HaloView {
+    int nPeers;
+    const HaloPeerTable* tab;
+    const int32_t* sendIdx;                   // per sorted vertex: first entry << 4 | entry count (boundary vertices only)
+    const int2* sendEnt;                      // (peer index, remote slot)
+    const int32_t* boundaryPrefix;            // [N+1] number of boundary vertices below a sorted id
+    uint32_t* ctl;                            // [0] epoch, [1] block ticket
+    int epochOffset;                          // colour launches of this batch before this one
+    int debug;                                // timing experiments (GAIA_B200_HALO_DEBUG)
 };
 
 struct Scene {
@@ -132,6 +158,8 @@ void halo_destroy(Scene& s);
 bool halo_active(const Scene& s);
 cudaError_t halo_push(Scene& s, int group);
 cudaError_t halo_sync(Scene& s);
+bool halo_view(Scene& s, HaloView& hv);                           // fused exchange available (halo_finalize done)
+void halo_count_fused(Scene& s, int group);                       // statistics: bytes a fused colour launch pushes
 
 // collision.cu
 cudaError_t collision_init(Scene& s);

@@ -82,10 +82,10 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
 // The vertex-level part of VBDStepWithCollision after the incident-tet sums are known: damping, inertia, world box +
 // friction, contacts, 3x3 solve, in-place update. Runs with one vertex per thread (all lanes busy).
 template <bool HAS_CONTACTS>
-__device__ __forceinline__ void solve_tail(int s, float3 x, float4 ys, float miu, float lmbd, float dampH, float dampD,
+__device__ __forceinline__ bool solve_tail(int s, float3 x, float4 ys, float miu, float lmbd, float dampH, float dampD,
                                            float fx, float fy, float fz, float s1, float g00, float g01, float g02, float g11, float g12, float g22,
                                            float4* pos, const float4* __restrict__ prev, const StepParamsDev& sp, int applyFriction,
-                                           const ContactView& cv, int32_t* errFlags) {
+                                           const ContactView& cv, int32_t* errFlags, float4& xNew) {
     // elastic force and Hessian: f = -(mu*fmu + lmbd*flm), H = mu*s1*I + lmbd*G
     float F0 = -fx, F1 = -fy, F2 = -fz;
     float hd = miu * s1;
@@ -181,20 +181,59 @@ __device__ __forceinline__ void solve_tail(int s, float3 x, float4 ys, float miu
             dx2 = deti * (i13 * F0 + i23 * F1 + i33 * F2);
             step = sp.stepSize;
         }
-        if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return; }
-        pos[s] = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
+        if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return false; }
+        xNew = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
+        pos[s] = xNew;
+        return true;
+    }
+    return false;
+}
+
+// Neighbour position gather. HALO launches read past L1 (ld.global.cg): ghost slots are written by the neighbours over
+// NVLink while the launch runs, and an L1 line fetched before the epoch was seen could hold the old value.
+#ifndef GAIA_GATHER_CG
+#define GAIA_GATHER_CG 0
+#endif
+template <bool HALO>
+__device__ __forceinline__ float4 ld_nb(const float4* p) { return (HALO || GAIA_GATHER_CG) ? __ldcg(p) : __ldg(p); }
+
+// Fused halo exchange, consumer side: wait until every neighbour partition has published `epoch` (its previous colour
+// launch, pushes included, is complete). One lane polls; 5 s without progress = a neighbour died (errFlags[4]).
+__device__ __forceinline__ void halo_wait(const HaloPeerTable* tab, uint32_t epoch, int nPeers, int32_t* errFlags) {
+    for (int p = 0; p < nPeers; p++) {
+        if (*(volatile int32_t*)(errFlags + 4)) return;
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(tab->myFlag[p]) : "memory");
+            if ((int32_t)(v - epoch) >= 0) break;
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 5000000000ull) { atomicAdd(errFlags + 4, 1); return; }
+            __nanosleep(64);
+        }
     }
 }
 
 // One block owns kBlock consecutive vertices of the colour and walks them in ROUNDS = L rounds of kBlock/L vertices:
 // in a round each vertex is served by a sub-warp of L lanes (incident-tet sums), the sums are parked in shared memory,
 // and after the last round every thread finishes ONE vertex (solve_tail) — so the scalar tail runs at full SIMT width.
-template <int L, bool HAS_CONTACTS, int PF, int ROUNDS>
-__global__ void __launch_bounds__(kBlock, 4)
-k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
+//
+// HALO (multi-GPU partitions): the exchange of this colour's boundary positions is part of the launch.
+// Epochs count colour launches: launch number o of a batch (hv.epochOffset = o) first publishes "everything before me
+// is complete" (base + o, base = ctl[0]) to the neighbours - stream order makes the previous launch's peer stores
+// visible first - and a block that holds boundary vertices (bit 30 of the vertex header; found through a prefix count
+// over the block's vertex range) waits until every neighbour has published the same epoch, gathers its neighbour
+// positions past L1 (ghost slots are written by peers over NVLink while the launch runs) and after its solve stores the
+// new positions straight into the neighbours' ghost slots. Blocks without boundary vertices never wait, so the NVLink
+// latency hides behind them; nothing is added to their critical path (no barrier, no atomic).
+template <int L, bool HAS_CONTACTS, int PF, int ROUNDS, bool GHOST>
+__device__ __forceinline__ void
+accumulate_block(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
                const int4* __restrict__ vtx, const float4* __restrict__ incW, const uint32_t* __restrict__ incIdx,
                const int32_t* __restrict__ nbList, const MeshParamsDev* __restrict__ mp,
-               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags) {
+               const StepParamsDev& sp, int applyFriction, const ContactView& cv, int32_t* errFlags, const HaloView& hv) {
     constexpr int VPR = kBlock / L;        // vertices per round
     constexpr int VPB = VPR * ROUNDS;      // vertices per block
     extern __shared__ float4 smem4[];
@@ -206,6 +245,7 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
     float4* myNb = smNb + sub * kNbStride;
     const int blockBase = vBegin + blockIdx.x * VPB;
     const float4* posRO = pos;   // neighbour gathers only touch other colours: read-only for this launch
+    bool waited = false;         // GHOST: the block has seen the neighbours' epoch
 
 #pragma unroll 1
     for (int r = 0; r < ROUNDS; r++) {
@@ -227,6 +267,7 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
         const float3 x = f3(xs);
         const int e = va.x + (active ? (va.z & 0xFFFF) : 0), nb0 = va.y;
         const int nnbAll = active ? (va.z >> 16) : 0;
+
         // ---- level 1: first incidence records and the neighbour ids (both only depend on va)
         int j = va.x + lane;
         float4 W = make_float4(0.f, 0.f, 0.f, 0.f), W1 = W, W2 = W;
@@ -240,12 +281,26 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
 #pragma unroll
             for (int q = 0; q < kNbMax / L; q++) { const int i = lane + q * L; idx[q] = (i < nnb) ? (int)ld_stream((const uint32_t*)nbList + nb0 + i) : -1; }
             // ---- level 2: stage the distinct neighbour positions once (each is used by ~5 incident tets); L2 hits
-#pragma unroll
-            for (int q = 0; q < kNbMax / L; q++)
-                if (idx[q] >= 0) {
-                    const float4 p = __ldg(posRO + idx[q]);
-                    myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
+            if (GHOST) {
+                if (!waited) {
+                    if (threadIdx.x == 0 && !(hv.debug & 1)) halo_wait(hv.tab, *(volatile const uint32_t*)hv.ctl + (uint32_t)hv.epochOffset, hv.nPeers, errFlags);
+                    __syncthreads();
+                    waited = true;
                 }
+#pragma unroll
+                for (int q = 0; q < kNbMax / L; q++)
+                    if (idx[q] >= 0) {
+                        const float4 p = __ldcg(posRO + idx[q]);
+                        myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
+                    }
+            } else {
+#pragma unroll
+                for (int q = 0; q < kNbMax / L; q++)
+                    if (idx[q] >= 0) {
+                        const float4 p = __ldg(posRO + idx[q]);
+                        myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
+                    }
+            }
         }
         __syncwarp();
         const float lm6 = lmbd * (-1.f / 6.f);
@@ -260,20 +315,29 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
                 pb = f3(lds128(rowAddr + ((I >> 4) & 0xFF0u)));
                 pc = f3(lds128(rowAddr + ((I >> 12) & 0xFF0u)));
             } else {
-                pa = f3(__ldg(posRO + __ldg(nbList + nb0 + (I & 255)))) - x;
-                pb = f3(__ldg(posRO + __ldg(nbList + nb0 + ((I >> 8) & 255)))) - x;
-                pc = f3(__ldg(posRO + __ldg(nbList + nb0 + ((I >> 16) & 255)))) - x;
+                pa = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + (I & 255)))) - x;
+                pb = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + ((I >> 8) & 255)))) - x;
+                pc = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + ((I >> 16) & 255)))) - x;
             }
             // n = cof(Ds')(1,1,1) = b x c + c x a + a x b = (b-a) x (c-a);  det(Ds') = a . n;  A*g = -n/6
-            const float3 n = cross3(pb - pa, pc - pa);
-            const float k = dot3(pa, n) * W.w - aConst;                // det F - a,  det F = det(Ds') det(B')
-            const float c6 = lm6 * k;
-            fx += miu * (W.x * pa.x + W.y * pb.x + W.z * pc.x) + c6 * n.x;   // A*(mu F m0 + lmbd k g)
-            fy += miu * (W.x * pa.y + W.y * pb.y + W.z * pc.y) + c6 * n.y;
-            fz += miu * (W.x * pa.z + W.y * pb.z + W.z * pc.z) + c6 * n.z;
-            s1 -= (W.x + W.y) + W.z;                                   // A*|m0|^2
-            const float nx = W.w * n.x, ny = W.w * n.y, nz = W.w * n.z;       // 6 A g g^T = det(B') n n^T
-            g00 += nx * n.x; g01 += nx * n.y; g02 += nx * n.z; g11 += ny * n.y; g12 += ny * n.z; g22 += nz * n.z;
+            // (explicit _rn intrinsics: the contraction pattern is fixed, so every instantiation of this body - any L, PF,
+            // ROUNDS, with or without the ghost path - produces the same bits)
+            const float3 u = pb - pa, v = pc - pa;
+            float3 n;
+            n.x = __fmaf_rn(u.y, v.z, -__fmul_rn(u.z, v.y));
+            n.y = __fmaf_rn(u.z, v.x, -__fmul_rn(u.x, v.z));
+            n.z = __fmaf_rn(u.x, v.y, -__fmul_rn(u.y, v.x));
+            const float detDs = __fmaf_rn(pa.z, n.z, __fmaf_rn(pa.y, n.y, __fmul_rn(pa.x, n.x)));
+            const float k = __fmaf_rn(detDs, W.w, -aConst);            // det F - a,  det F = det(Ds') det(B')
+            const float c6 = __fmul_rn(lm6, k);
+            // A*(mu F m0 + lmbd k g)
+            fx = __fmaf_rn(c6, n.x, __fmaf_rn(miu, __fmaf_rn(W.z, pc.x, __fmaf_rn(W.y, pb.x, __fmul_rn(W.x, pa.x))), fx));
+            fy = __fmaf_rn(c6, n.y, __fmaf_rn(miu, __fmaf_rn(W.z, pc.y, __fmaf_rn(W.y, pb.y, __fmul_rn(W.x, pa.y))), fy));
+            fz = __fmaf_rn(c6, n.z, __fmaf_rn(miu, __fmaf_rn(W.z, pc.z, __fmaf_rn(W.y, pb.z, __fmul_rn(W.x, pa.z))), fz));
+            s1 = __fsub_rn(s1, __fadd_rn(__fadd_rn(W.x, W.y), W.z));   // A*|m0|^2
+            const float nx = __fmul_rn(W.w, n.x), ny = __fmul_rn(W.w, n.y), nz = __fmul_rn(W.w, n.z);   // 6 A g g^T = det(B') n n^T
+            g00 = __fmaf_rn(nx, n.x, g00); g01 = __fmaf_rn(nx, n.y, g01); g02 = __fmaf_rn(nx, n.z, g02);
+            g11 = __fmaf_rn(ny, n.y, g11); g12 = __fmaf_rn(ny, n.z, g12); g22 = __fmaf_rn(nz, n.z, g22);
             if (PF == 0) { W = Wn; I = In; }
             else if (PF == 1) { W = W1; I = I1; W1 = Wn; I1 = In; }
             else { W = W1; I = I1; W1 = W2; I1 = I2; W2 = Wn; I2 = In; }
@@ -292,6 +356,33 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
         }
         __syncwarp();      // the row of smNb is rewritten by the next round
     }
+}
+
+template <int L, bool HAS_CONTACTS, int PF, int ROUNDS, bool HALO>
+__global__ void __launch_bounds__(kBlock, 4)
+k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
+               const int4* __restrict__ vtx, const float4* __restrict__ incW, const uint32_t* __restrict__ incIdx,
+               const int32_t* __restrict__ nbList, const MeshParamsDev* __restrict__ mp,
+               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags, HaloView hv) {
+    constexpr int VPR = kBlock / L;
+    constexpr int VPB = VPR * ROUNDS;
+    extern __shared__ float4 smem4[];
+    float* acc = (float*)(smem4 + VPR * kNbStride);         // [10][VPB] incident-tet sums
+    const int blockBase = vBegin + blockIdx.x * VPB;
+    bool ghostBlock = false;
+    if (HALO) {
+        if (blockIdx.x == 0 && threadIdx.x < hv.nPeers) {
+            const uint32_t done = *(volatile const uint32_t*)hv.ctl + (uint32_t)hv.epochOffset;
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(hv.tab->peerFlag[threadIdx.x]), "r"(done) : "memory");
+        }
+        // a block that holds boundary vertices takes the ghost-safe copy of the accumulation (wait + gathers past L1);
+        // all other blocks run exactly the single-GPU code. Both copies use the same pinned arithmetic.
+        ghostBlock = __ldg(hv.boundaryPrefix + min(blockBase + VPB, vEnd)) != __ldg(hv.boundaryPrefix + min(blockBase, vEnd));
+    }
+    if (HALO && ghostBlock) accumulate_block<L, HAS_CONTACTS, PF, ROUNDS, true>(vBegin, vEnd, pos, prev, inertia, vtx, incW, incIdx, nbList, mp, sp, applyFriction, cv, errFlags, hv);
+    else accumulate_block<L, HAS_CONTACTS, PF, ROUNDS, false>(vBegin, vEnd, pos, prev, inertia, vtx, incW, incIdx, nbList, mp, sp, applyFriction, cv, errFlags, hv);
+    bool pushed = false;         // HALO: this thread stored into a neighbour's memory
     __syncthreads();
     // ---- transposed tail: thread t finishes vertex blockBase + t
     for (int slot = threadIdx.x; slot < VPB; slot += kBlock) {
@@ -303,12 +394,35 @@ k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ pre
         if (!P->activeSolve) continue;
         const float4 xs = pos[s];
         const float4 ys = __ldg(inertia + s);
-        solve_tail<HAS_CONTACTS>(s, f3(xs), ys, P->miu, P->lmbd, P->dampH, P->dampD,
+        float4 xNew;
+        const bool wrote = solve_tail<HAS_CONTACTS>(s, f3(xs), ys, P->miu, P->lmbd, P->dampH, P->dampD,
                                  acc[0 * VPB + slot], acc[1 * VPB + slot], acc[2 * VPB + slot], acc[3 * VPB + slot],
                                  acc[4 * VPB + slot] * (1.f / 6.f), acc[5 * VPB + slot] * (1.f / 6.f), acc[6 * VPB + slot] * (1.f / 6.f),
                                  acc[7 * VPB + slot] * (1.f / 6.f), acc[8 * VPB + slot] * (1.f / 6.f), acc[9 * VPB + slot] * (1.f / 6.f),
-                                 pos, prev, sp, applyFriction, cv, errFlags);
+                                 pos, prev, sp, applyFriction, cv, errFlags, xNew);
+        if (HALO && wrote && (va.w & kHaloBoundaryBit) && !(hv.debug & 2)) {
+            const int si = __ldg(hv.sendIdx + s);
+            for (int q = 0; q < (si & 15); q++) {
+                const int2 en = __ldg(hv.sendEnt + (si >> 4) + q);
+                hv.tab->peerPos[en.x][en.y] = xNew;
+            }
+            pushed = true;
+        }
     }
+    // the next launch of the stream publishes the epoch; the stores must be performed system-wide before it does
+    if (HALO && pushed) __threadfence_system();
+}
+
+
+// End of a batch of fused colour launches: publish the last epoch and advance the base.
+__global__ void k_halo_advance(HaloView hv, int n) {
+    const uint32_t done = *(volatile const uint32_t*)hv.ctl + (uint32_t)n;
+    if (threadIdx.x < hv.nPeers) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(hv.tab->peerFlag[threadIdx.x]), "r"(done) : "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) hv.ctl[0] = done;
 }
 
 // applyInitialStep for every vertex of every active mesh (one launch)
@@ -576,24 +690,33 @@ cudaError_t device_upload(Scene& s) {
 static int g_lanes = 4;     // sub-warp width of the colour solve (GAIA_B200_LANES = 2|4|8)
 static int g_variant = 1;   // prefetch depth of the incidence stream (GAIA_B200_VARIANT = 0|1|2)
 
-template <int L, bool HC, int PF, int ROUNDS>
-static void launch_one(Scene& s, int vb, int ve, int applyFriction, const ContactView& cv) {
+template <int L, bool HC, int PF, int ROUNDS, bool HALO = false>
+static void launch_one(Scene& s, int vb, int ve, int applyFriction, const ContactView& cv, const HaloView* hvp = nullptr) {
+    HaloView hv;
+    if (hvp) hv = *hvp; else std::memset(&hv, 0, sizeof(hv));
     const int n = ve - vb;
     const int vpb = (kBlock / L) * ROUNDS;
     const size_t smem = (size_t)(kBlock / L) * kNbStride * sizeof(float4) + (size_t)10 * vpb * sizeof(float);
     static bool attrSet = false;
-    if (!attrSet) { cudaFuncSetAttribute(k_solve_colour<L, HC, PF, ROUNDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attrSet = true; }
-    k_solve_colour<L, HC, PF, ROUNDS><<<nblk(n, vpb), kBlock, smem, s.stream>>>(
+    if (!attrSet) { cudaFuncSetAttribute(k_solve_colour<L, HC, PF, ROUNDS, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attrSet = true; }
+    k_solve_colour<L, HC, PF, ROUNDS, HALO><<<nblk(n, vpb), kBlock, smem, s.stream>>>(
         vb, ve, s.pos.p, s.prev.p, s.inertia.p, s.vtx.p, s.incW.p, s.incIdx.p, s.nbList.p,
-        s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p);
+        s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p, hv);
 }
 
 template <bool HC>
-static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int applyFriction, const ContactView& cv) {
+static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int applyFriction, const ContactView& cv, const HaloView* hv = nullptr) {
     // rounds per block: big colours walk L rounds per block (full-width tail); smaller ones fewer rounds, so that the grid
     // still fills the 148 SMs x 4 resident blocks for a few waves
     const int64_t n = ve - vb;
     const int rounds = n >= (int64_t)148 * 8 * kBlock ? L : (n >= (int64_t)148 * 4 * kBlock ? 2 : 1);
+    if (hv) {   // fused halo exchange: the default shape only (4 lanes, prefetch depth 1)
+        const int r4 = n >= (int64_t)148 * 8 * kBlock ? 4 : (n >= (int64_t)148 * 4 * kBlock ? 2 : 1);
+        if (r4 == 4) launch_one<4, HC, 1, 4, true>(s, vb, ve, applyFriction, cv, hv);
+        else if (r4 == 2) launch_one<4, HC, 1, 2, true>(s, vb, ve, applyFriction, cv, hv);
+        else launch_one<4, HC, 1, 1, true>(s, vb, ve, applyFriction, cv, hv);
+        return;
+    }
 #define BYVAR(LL) if (rounds == LL) { if (variant == 0) launch_one<LL, HC, 0, LL>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, LL>(s, vb, ve, applyFriction, cv); } \
                   else if (rounds == 2) { if (variant == 0) launch_one<LL, HC, 0, 2>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 2>(s, vb, ve, applyFriction, cv); } \
                   else { if (variant == 0) launch_one<LL, HC, 0, 1>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 1>(s, vb, ve, applyFriction, cv); }
@@ -614,6 +737,20 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     const int G = (int)s.groupStart.size() - 1;
     const int N = (int)s.nVerts;
     const bool halo = halo_active(s);
+    static int fusedHalo = -1;
+    if (fusedHalo < 0) { const char* e = getenv("GAIA_B200_HALO_FUSED"); fusedHalo = e ? atoi(e) : 1; }
+    HaloView hv;
+    const bool fused = halo && fusedHalo && !s.phys.useAccelerator && halo_view(s, hv);   // (the accelerator needs full refreshes)
+    static int haloDebug = -1;      // timing experiments only: 1 = do not wait, 2 = do not store to peers (results are wrong)
+    if (haloDebug < 0) { const char* e = getenv("GAIA_B200_HALO_DEBUG"); haloDebug = e ? atoi(e) : 0; }
+    if (fused) hv.debug = haloDebug;
+    static uint32_t* dbgCtl = nullptr;
+    bool forceHalo = false;
+    if (!halo && getenv("GAIA_B200_FORCE_HALO_KERNEL")) {      // single-GPU timing of the HALO kernel variant (no peers)
+        static int32_t* dbgPrefix = nullptr;
+        if (!dbgCtl) { cudaMalloc((void**)&dbgCtl, 16); cudaMemset(dbgCtl, 0, 16); cudaMalloc((void**)&dbgPrefix, (N + 1) * 4); cudaMemset(dbgPrefix, 0, (N + 1) * 4); }
+        std::memset(&hv, 0, sizeof(hv)); hv.ctl = dbgCtl; hv.boundaryPrefix = dbgPrefix; forceHalo = true;
+    }
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
     bool hasContacts = collision_contact_view(s, cv, &colliding);
@@ -644,9 +781,10 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             if (ve <= vb && !halo) continue;
             if (hasContacts) { CK(collision_update_infos(s, g)); }
             if (s.profiling) cudaEventRecord(s.evA, s.stream);
+            hv.epochOffset = it * G + g;
             if (ve > vb) {
-                if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
-                else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv);
+                if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
+                else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
             }
             if (s.profiling) {
                 cudaEventRecord(s.evB, s.stream);
@@ -655,13 +793,15 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
                 s.solveKernelMs += ms; s.solveKernelLaunches++;
             }
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
-            if (halo) CK(halo_push(s, g));
+            if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
+            else if (halo) CK(halo_push(s, g));
         }
         s.stats.vertexSolves += solvedPerIter;
         s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
         if (s.phys.useAccelerator) {
             k_accelerate<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.accPrevPrev.p, s.accPrevIter.p, s.info.p, s.meshParams.p, colliding, omega, 0);
             s.stats.kernelLaunches++;
+            if (halo) { CK(halo_sync(s)); CK(halo_push(s, -1)); }    // the extrapolated positions replace the ghosts' copies
         }
         const int ici = s.phys.intermediateCollisionIterations;
         if (allowIntermediateCD && ici > 0 && it % ici == ici - 1) {
@@ -671,6 +811,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             hasContacts = collision_contact_view(s, cv, &colliding);
         }
     }
+    if (fused) { k_halo_advance<<<1, 32, 0, s.stream>>>(hv, nIters * G); s.stats.kernelLaunches++; }
     return cudaGetLastError();
 }
 

@@ -97,7 +97,7 @@ def _worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4])
 def test_partitioned_oracle_equals_single_bit_exact(tmp_path, world):
     import torch.multiprocessing as mp
     from oracle.binding import OracleScene
