@@ -1,0 +1,163 @@
+/*
+ * gaia_b200_cloth.h — C ABI of the B200-native VBD *cloth* step.
+ *
+ * Replaces, for triangle-mesh scenes, the call sites of
+ *   VBDClothSimulationFramework::runStep_CDEveryIter          M/VBDCloth/VBDClothPhysics.cpp:389-518
+ *   ClothContactDetector (VF / EE radius queries)              M/CollisionDetector/ClothContactDetector.{h,cpp}
+ *   VBDTriMeshStVk (StVK membrane + quadratic bending)         M/VBDCloth/VBDTriMeshStVK.cpp:50-98, 721-982
+ * Same conventions as gaia_b200.h (status codes, one host thread per handle, xyz-interleaved float32 in the ORIGINAL
+ * vertex order of each mesh, no CPU fallback).
+ *
+ * Meshes: the first `numSimMeshes` meshes added with add_tri_mesh(simulated=1) are cloth (baseTriMeshesForSimulation);
+ * meshes added with simulated=0 are colliders (colliderTriMeshes: every vertex fixed, positions may be replaced
+ * between frames with set_positions) and must come after all simulated meshes, like triMeshesAll
+ * (M/Framework/BaseClothSimPhsicsFramework.cpp:57-63).
+ */
+#ifndef GAIA_B200_CLOTH_H
+#define GAIA_B200_CLOTH_H
+
+#include "gaia_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* PhysicsParams + ContactDetectorParams of the cloth Parameters.json: BasePhysicsParams
+ * (M/Parameters/PhysicsParameters.h:9-105), VBDClothPhysicsParameters (M/VBDCloth/VBDClothPhysicsParameters.h:5-80),
+ * ClothContactDetectorParameters (M/CollisionDetector/ClothContactDetector.h:13-30). Same names, same defaults. */
+typedef struct gaia_cloth_physics_params {
+    float gravity[3];                       /* (0,-10,0) */
+    float timeStep;                         /* 0.0166666 */
+    int32_t numSubsteps;                    /* 20 */
+    int32_t iterations;                     /* 1 */
+    float worldBoundsMin[3];                /* -1e7 */
+    float worldBoundsMax[3];                /* +1e7 */
+    float boundaryFrictionDynamic;          /* 0.1 */
+    /* VBDClothPhysicsParameters */
+    float stepSize;                         /* 1.0 */
+    int32_t associateGravityWithInertia;    /* 1 */
+    int32_t applyAcceleration;              /* 0 */
+    float acceleratorRho;                   /* 0.95 */
+    int32_t handleCollision;                /* 1 */
+    float contactStiffness;                 /* 1e4 */
+    float contactRadius;                    /* 1.0 */
+    float thickness;                        /* 0.0 */
+    float conservativeStepRelaxation;       /* 0.45 */
+    float boundaryContactStiffness;         /* 1e4 */
+    float boundaryFrictionEpsValue;         /* 1e-2 */
+    int32_t contactEnergyTypes;             /* 1: quadratic + logarithmic two stages (0: quadratic, 2: IPC-like) */
+    int32_t contactBVHReconstructionSteps;  /* 32 */
+    float degenerateTriangleThres;          /* 1e-6 */
+    /* ClothContactDetectorParameters */
+    float maxQueryDis;                      /* 0.4 */
+} gaia_cloth_physics_params;
+
+/* One entry of the cloth Models.json: ObjectParams (M/Materials/Materials.h:12-53), TriMeshParams
+ * (M/TriMesh/TriMesh.cpp:449-463), VBDObjectParamsTriMesh (M/VBDCloth/VBDBaseTriMesh.h:8-20),
+ * VBDObjectParamsTriMeshStVk (M/VBDCloth/VBDTriMeshStVK.h:12-22). Rest shape: use3DRestpose = true
+ * (TriMeshFEM::computeRestposeTrianglesFrom3D, M/TriMesh/TriMesh.cpp:213-244). */
+typedef struct gaia_cloth_object_params {
+    float scale[3];                 /* (1,1,1) */
+    float rotation[3];              /* axis*angle, (0,0,0) */
+    float translation[3];           /* (0,0,0) */
+    float density;                  /* 1 */
+    int32_t hasNoGravZone;          /* 0 */
+    float noGravZoneThreshold;      /* 0 */
+    float maxVelocityMagnitude;     /* -1 */
+    float frictionDynamic;          /* 0.1 */
+    float frictionEpsV;             /* 0.1 */
+    float bendingStiffness;         /* 0 */
+    float exponentialVelDamping;    /* 1.0 (used as is: the cloth framework does not raise it to dt) */
+    float constantVelDamping;       /* 0.0 */
+    int32_t initializationType;     /* 0 inertia, 1 adaptive gravity, 2 previous position, 3 inertia truncated to the
+                                       conservative bound, 4 keep (M/VBDCloth/VBDBaseTriMesh.cpp:77-163) */
+    float miu;                      /* 1e4 */
+    float lambda;                   /* 1e4 */
+    float dampingStVK;              /* 0 */
+    float dampingBending;           /* 0 */
+} gaia_cloth_object_params;
+
+/* Detected contacts, for bit-exact parity of the contact sets (VFContactPointInfo / EEContactPointInfo,
+ * M/CollisionDetector/ClothContactDetector.h:32-103). VF list sorted by (vertexMesh, vertex, faceMesh, face);
+ * EE list by (mesh1, edge1, mesh2, edge2). Edge ids are the reference's (creation order of MeshFrame edges,
+ * M/TriMesh/TriMesh.cpp:499-560). */
+typedef struct gaia_cloth_vf_contact {
+    int32_t vertexMesh, vertex, faceMesh, face;
+    int32_t primitiveType;   /* ClosestPointOnPrimitiveType: 0 vertex, 1 edge, 2 face */
+    int32_t primitiveId;     /* vertex / edge / face id the closest point lies on */
+} gaia_cloth_vf_contact;
+typedef struct gaia_cloth_ee_contact {
+    int32_t mesh1, edge1, mesh2, edge2;
+} gaia_cloth_ee_contact;
+
+typedef struct gaia_cloth_stats {
+    double timeCsmpUpdatingCollisionInfoDCD;   /* detection phases (BVH + queries + bounds), ms, profiling mode */
+    double timeCsmpInitialStep;
+    double timeCsmpMaterialSolve;
+    double solveKernelMs;           /* colour-solve kernels alone */
+    int64_t vertexSolves;
+    int64_t colourSweeps;
+    int64_t substeps;
+    int64_t frames;
+    int64_t kernelLaunches;
+    int64_t algorithmicBytes;       /* SURVEY §8(d) cloth formula, summed over colour sweeps */
+    int64_t numberCollisionDetection;   /* RunningTimeStatistics::numberCollisionDetection */
+    int64_t numContactsVF;          /* last detection */
+    int64_t numContactsEE;
+} gaia_cloth_stats;
+
+typedef struct gaia_cloth_handle gaia_cloth_handle;
+
+void gaia_b200_cloth_default_physics_params(gaia_cloth_physics_params* p);
+void gaia_b200_cloth_default_object_params(gaia_cloth_object_params* p);
+const char* gaia_b200_cloth_last_error(const gaia_cloth_handle* h);
+
+/* create: BaseClothPhsicsFramework::parseRunningParameters + timeStepEqualize */
+int gaia_b200_cloth_create(const gaia_cloth_physics_params* phys, int device, gaia_cloth_handle** out);
+void gaia_b200_cloth_destroy(gaia_cloth_handle* h);
+
+/* add_tri_mesh: TriMeshFEM::initialize (loadObj is the caller's: xyz = 3*nV floats, faces = 3*nF vertex ids) +
+ * TriMeshTopology::initialize (M/TriMesh/TriMesh.cpp:15-111, 481-753) + VBDTriMeshStVk::initialize. Colouring as in
+ * gaia_b200_add_tet_mesh (ignored for colliders). Returns the mesh id. */
+int gaia_b200_cloth_add_tri_mesh(gaia_cloth_handle* h, int32_t simulated, int32_t nV, int32_t nF,
+                                 const float* xyz, const int32_t* faces, const gaia_cloth_object_params* obj,
+                                 int32_t nColors, const int32_t* color_offsets, const int32_t* color_verts,
+                                 int32_t nFixed, const int32_t* fixedPoints);
+/* finalize: VBDClothSimulationFramework::initialize (parallel groups :72-138, contact detector) */
+int gaia_b200_cloth_finalize(gaia_cloth_handle* h);
+
+/* run_frames: BasePhysicFramework::simulate loop body with runStep = runStep_CDEveryIter */
+int gaia_b200_cloth_run_frames(gaia_cloth_handle* h, int32_t nFrames);
+/* parity entry: one substep's first `nIters` iterations (detection, initial guess, colour sweeps), no velocity update */
+int gaia_b200_cloth_run_iterations(gaia_cloth_handle* h, int32_t nIters);
+int gaia_b200_cloth_synchronize(gaia_cloth_handle* h);
+
+int gaia_b200_cloth_num_meshes(const gaia_cloth_handle* h);
+int gaia_b200_cloth_mesh_sizes(const gaia_cloth_handle* h, int mesh, int32_t* nV, int32_t* nF, int32_t* nE);
+int gaia_b200_cloth_get_positions(gaia_cloth_handle* h, int mesh, float* xyz);
+int gaia_b200_cloth_get_velocities(gaia_cloth_handle* h, int mesh, float* xyz);
+int gaia_b200_cloth_set_state(gaia_cloth_handle* h, int mesh, const float* pos, const float* vel);   /* vel may be NULL */
+int64_t gaia_b200_cloth_total_vertices(const gaia_cloth_handle* h);
+int gaia_b200_cloth_get_all_positions(gaia_cloth_handle* h, float* xyz);
+int gaia_b200_cloth_set_all_state(gaia_cloth_handle* h, const float* pos, const float* vel);
+
+/* integer parity surfaces */
+int gaia_b200_cloth_get_edges(const gaia_cloth_handle* h, int mesh, int32_t* out);   /* per edge: eV1,eV2,eV12Next,eV21Next,fId1,fId2 */
+int gaia_b200_cloth_num_parallel_groups(const gaia_cloth_handle* h);
+int gaia_b200_cloth_get_parallel_group(const gaia_cloth_handle* h, int group, int32_t* out, int32_t* nPairs);
+int gaia_b200_cloth_get_vertex_masses(const gaia_cloth_handle* h, int mesh, float* out);
+/* applyCollisionDetection on the current state without stepping; fills the lists below and the conservative bounds */
+int gaia_b200_cloth_detect_contacts(gaia_cloth_handle* h);
+int gaia_b200_cloth_get_vf_contacts(gaia_cloth_handle* h, gaia_cloth_vf_contact* out, int64_t capacity, int64_t* n);
+int gaia_b200_cloth_get_ee_contacts(gaia_cloth_handle* h, gaia_cloth_ee_contact* out, int64_t capacity, int64_t* n);
+int gaia_b200_cloth_get_conservative_bounds(gaia_cloth_handle* h, int mesh, float* out);   /* vertexConvervativeBounds */
+
+int gaia_b200_cloth_get_stats(gaia_cloth_handle* h, gaia_cloth_stats* out);
+int gaia_b200_cloth_reset_stats(gaia_cloth_handle* h);
+int gaia_b200_cloth_set_profiling(gaia_cloth_handle* h, int enabled);
+void* gaia_b200_cloth_cuda_stream(gaia_cloth_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAIA_B200_CLOTH_H */

@@ -1,0 +1,100 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY. ctypes binding of the cloth part of oracle/liboracle.so (CPU restatement of the
+reference VBD cloth step). Imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs only."""
+import ctypes as C
+
+import numpy as np
+
+from gaia_b200.capi import _f32, _fp
+from gaia_b200.cloth import ClothPhysicsParams, ClothSceneBase, bind_cloth_api, default_cloth_physics_params
+from .binding import load_oracle
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    lib = load_oracle()
+    if not _bound:
+        P, FP = C.c_void_p, C.POINTER(C.c_float)
+        lib.oracle_cloth_create.argtypes = [C.POINTER(ClothPhysicsParams), C.c_int]
+        lib.oracle_cloth_create.restype = C.c_void_p
+        lib.oracle_cloth_destroy.argtypes = [P]; lib.oracle_cloth_destroy.restype = None
+        lib.oracle_cloth_num_threads.argtypes = [P]
+        lib.oracle_cloth_set_brute_force.argtypes = [P, C.c_int]; lib.oracle_cloth_set_brute_force.restype = None
+        lib.oracle_cloth_set_prev_positions.argtypes = [P, C.c_int, FP]
+        lib.oracle_cloth_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
+        lib.oracle_cloth_vertex_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
+        lib.oracle_cloth_elastic_energy.argtypes = [P, C.c_int]; lib.oracle_cloth_elastic_energy.restype = C.c_float
+        lib.oracle_cloth_contact_repulsion.argtypes = [P, C.c_float, FP, FP]; lib.oracle_cloth_contact_repulsion.restype = None
+        lib.oracle_cloth_get_dminv.argtypes = [P, C.c_int, FP, FP]
+        lib.oracle_cloth_get_bending_forms.argtypes = [P, C.c_int, FP]
+        lib.oracle_cloth_closest_points_segments.argtypes = [FP, FP, FP, FP, FP]; lib.oracle_cloth_closest_points_segments.restype = None
+        bind_cloth_api(lib, "oracle_cloth_")
+        _bound = True
+    return lib
+
+
+class OracleClothScene(ClothSceneBase):
+    _prefix = "oracle_cloth_"
+
+    def __init__(self, phys=None, threads=0):
+        self._lib = _lib()
+        self.phys = phys if phys is not None else default_cloth_physics_params()
+        self.h = C.c_void_p(self._lib.oracle_cloth_create(C.byref(self.phys), int(threads)))
+
+    @property
+    def num_threads(self):
+        return self._lib.oracle_cloth_num_threads(self.h)
+
+    def set_brute_force(self, on=True):
+        self._lib.oracle_cloth_set_brute_force(self.h, 1 if on else 0)
+
+    def set_prev_positions(self, mesh, prev):
+        p = _f32(prev)
+        self._lib.oracle_cloth_set_prev_positions(self.h, mesh, _fp(p))
+
+    def material_force_hessian(self, mesh, v):
+        f = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        self._lib.oracle_cloth_material_force_hessian(self.h, mesh, v, _fp(f), _fp(h))
+        return f, h.reshape(3, 3).T.copy()          # column-major -> H[r, c]
+
+    def vertex_force_hessian(self, mesh, v):
+        f = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        self._lib.oracle_cloth_vertex_force_hessian(self.h, mesh, v, _fp(f), _fp(h))
+        return f, h.reshape(3, 3).T.copy()
+
+    def elastic_energy(self, mesh):
+        return float(self._lib.oracle_cloth_elastic_energy(self.h, mesh))
+
+    def contact_repulsion(self, dis):
+        a = np.empty(1, np.float32); b = np.empty(1, np.float32)
+        self._lib.oracle_cloth_contact_repulsion(self.h, float(dis), _fp(a), _fp(b))
+        return float(a[0]), float(b[0])
+
+    def dminv(self, mesh):
+        nF = self.mesh_sizes(mesh)[1]
+        d = np.empty((nF, 4), np.float32); a = np.empty(nF, np.float32)
+        self._lib.oracle_cloth_get_dminv(self.h, mesh, _fp(d), _fp(a))
+        return d, a
+
+    def bending_forms(self, mesh):
+        q = np.empty((self.mesh_sizes(mesh)[2], 4, 4), np.float32)
+        self._lib.oracle_cloth_get_bending_forms(self.h, mesh, _fp(q))
+        return q
+
+    def close(self):
+        if self.h:
+            self._lib.oracle_cloth_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def closest_points_segments(p0, p1, q0, q1):
+    out = np.empty(8, np.float32)
+    _lib().oracle_cloth_closest_points_segments(_fp(_f32(p0)), _fp(_f32(p1)), _fp(_f32(q0)), _fp(_f32(q1)), _fp(out))
+    return out[:3], out[3:6], float(out[6]), float(out[7])

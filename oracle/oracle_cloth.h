@@ -1,0 +1,100 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
+// State of the CPU restatement of the reference VBD *cloth* step (M/VBDCloth, M/TriMesh,
+// M/CollisionDetector/ClothContactDetector.*). Parity status: UNPINNED beyond this restatement — the reference cloth code
+// needs Eigen/oneTBB/Embree (absent here) and ships no golden vectors; the restatement is checked against closed-form
+// properties (finite differences of the StVK / bending / contact energies, brute-force contact sets) in
+// tests/test_oracle_cloth.py.
+#pragma once
+#include "oracle_common.h"
+#include "../include/gaia_b200_cloth.h"
+
+namespace orc {
+
+// EdgeInfo (M/TriMesh/TriMesh.h:51-60)
+struct ClothEdge { int eV1, eV2, eV12Next, eV21Next, fId1, fId2; };
+
+// ClosestPointOnTriangleType (M/CollisionDetector/CollisionDetertionParameters.h): AtA..NotFound as in the tet oracle
+enum { cAtA = 0, cAtB, cAtC, cAtAB, cAtBC, cAtAC, cAtInterior, cNotFound };
+
+// VFContactPointInfo (M/CollisionDetector/ClothContactDetector.h:32-49)
+struct VFContact {
+    int vMesh, v, fMesh, f;
+    int closestType, primType, primId;
+    float d;
+    V3 cp, bary;
+};
+// EEContactPointInfo (:86-103)
+struct EEContact {
+    int m1, e1, m2, e2;
+    float mu1, mu2;
+    V3 c1, c2;
+    float d;
+};
+// FVContactInfo (:79-84)
+struct FVLink { int vMesh, v, contactId; };
+
+struct TriMesh {
+    int id = 0, nV = 0, nF = 0, nE = 0;
+    bool simulated = true;
+    gaia_cloth_object_params obj;
+    std::vector<V3> pos, prev, vel, velPrev, inertia, accel, next, posAtCD, prevIter;
+    std::vector<int> faces;                 // 3*nF (facePos)
+    std::vector<float> DmInv;               // 4*nF, each 2x2 column-major
+    std::vector<float> restArea, mass;
+    std::vector<uint8_t> fixedMask;
+    std::vector<int> fixedPoints;
+    // TriMeshTopology (M/TriMesh/TriMesh.cpp:481-753)
+    std::vector<ClothEdge> edges;
+    std::vector<int> face3Edges, face3NbrFaces;          // 3*nF each
+    std::vector<int> vNbrVOff, vNbrV;                    // CSR: neighbour vertices
+    std::vector<int> vNbrFOff, vNbrF, vNbrFOrder;        // CSR: incident faces + order of the vertex in the face
+    std::vector<int> vNbrEOff, vNbrE, vNbrEOrder;        // CSR: incident edges + order (0: eV1, 1: eV2)
+    std::vector<int> vBendOff, vBend, vBendOrder;        // CSR: relevant bendings (edge id, order 0..3)
+    std::vector<std::array<float, 16>> Q;                // edgeLaplacianQuadraticForms, row-major 4x4
+    std::vector<std::vector<int>> colors;
+    std::vector<int> globalColor;
+    // contact state
+    std::vector<float> bounds;              // vertexConvervativeBounds
+    std::vector<uint8_t> activeCollisionMask;
+    std::vector<std::vector<VFContact>> vf; // per vertex
+    std::vector<float> vfMinDis;            // per vertex
+    std::vector<std::vector<EEContact>> ee; // per edge (simulated meshes only)
+    std::vector<float> eeMinDis;
+    std::vector<float> faceMinDis;          // per face
+    std::vector<std::vector<FVLink>> faceLinks;
+    bool hasVelocitiesPrev = false, hasApproxAcceleration = false;
+};
+
+struct ClothScene {
+    gaia_cloth_physics_params phys;
+    float dt = 0.f, dtSqrReciprocal = 0.f;
+    std::vector<TriMesh> meshes;
+    int numSim = 0;
+    bool finalized = false;
+    bool bruteForce = false;                // contact candidates by brute force instead of the grid
+    std::vector<std::vector<int>> groups;   // [mesh,v,...]
+    bool collisionDetectionRequired = false;
+    int frameId = 0, substep = 0, iIter = 0;
+    float curTime = 0.f;
+    gaia_cloth_stats stats;
+    Pool* pool = nullptr;
+    ~ClothScene() { delete pool; }
+};
+
+void cloth_mesh_initialize(TriMesh& m, bool simulated, int nV, int nF, const float* xyz, const int32_t* faces,
+                           const gaia_cloth_object_params& obj, int nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
+                           int nFixed, const int32_t* fixed);
+void cloth_finalize(ClothScene& s);
+void cloth_detect(ClothScene& s);
+void cloth_run_substeps(ClothScene& s, int nSubsteps);
+void cloth_run_iterations(ClothScene& s, int nIters);
+// probes for the unit tests
+void cloth_material_force_hessian(const ClothScene& s, const TriMesh& m, int v, V3& force, M3& hessian);
+void cloth_vertex_force_hessian(ClothScene& s, int mesh, int v, V3& force, M3& hessian);
+float cloth_elastic_energy(const ClothScene& s, const TriMesh& m);
+void cloth_contact_repulsion(const ClothScene& s, float dis, float& dEdD, float& d2E);
+V3 closest_point_triangle(V3 p, V3 a, V3 b, V3 c, V3& bary, int& type);   // oracle_collision.cpp
+void closest_points_segments(V3 p0, V3 p1, V3 q0, V3 q1, V3& ps, V3& qt, float& s, float& t);   // oracle_cloth_contact.cpp
+bool solve3x3_psd_stable(const float* m, const float* b, float* out);      // oracle_step.cpp
+
+}  // namespace orc

@@ -1,0 +1,173 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
+// C entry points of the CPU cloth oracle; they shadow include/gaia_b200_cloth.h one to one with the prefix
+// `oracle_cloth_` (handle = void*), plus a few probes for the unit tests.
+#include "oracle_cloth.h"
+
+using namespace orc;
+
+extern "C" {
+
+void* oracle_cloth_create(const gaia_cloth_physics_params* phys, int nThreads) {
+    ClothScene* s = new ClothScene();
+    s->phys = *phys;
+    s->dt = s->phys.timeStep / s->phys.numSubsteps;          // BasePhysicFramework::timeStepEqualize
+    s->dtSqrReciprocal = 1.f / (s->dt * s->dt);
+    std::memset(&s->stats, 0, sizeof(s->stats));
+    if (nThreads <= 0) nThreads = (int)std::thread::hardware_concurrency();
+    s->pool = new Pool(nThreads);
+    return s;
+}
+void oracle_cloth_destroy(void* h) { delete (ClothScene*)h; }
+int oracle_cloth_num_threads(void* h) { return ((ClothScene*)h)->pool->size(); }
+void oracle_cloth_set_brute_force(void* h, int on) { ((ClothScene*)h)->bruteForce = on != 0; }
+
+int oracle_cloth_add_tri_mesh(void* h, int32_t simulated, int32_t nV, int32_t nF, const float* xyz, const int32_t* faces,
+                              const gaia_cloth_object_params* obj, int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
+                              int32_t nFixed, const int32_t* fixed) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    if (simulated && !s->meshes.empty() && !s->meshes.back().simulated) return GAIA_ERR_STATE;   // colliders come last
+    s->meshes.emplace_back();
+    TriMesh& m = s->meshes.back();
+    m.id = (int)s->meshes.size() - 1;
+    cloth_mesh_initialize(m, simulated != 0, nV, nF, xyz, faces, *obj, nColors, colorOffsets, colorVerts, nFixed, fixed);
+    return m.id;
+}
+int oracle_cloth_finalize(void* h) { cloth_finalize(*(ClothScene*)h); return GAIA_OK; }
+int oracle_cloth_run_frames(void* h, int32_t n) {
+    ClothScene* s = (ClothScene*)h;
+    for (int i = 0; i < n; i++) cloth_run_substeps(*s, s->phys.numSubsteps);
+    return GAIA_OK;
+}
+int oracle_cloth_run_iterations(void* h, int32_t n) { cloth_run_iterations(*(ClothScene*)h, n); return GAIA_OK; }
+int oracle_cloth_synchronize(void*) { return GAIA_OK; }
+int oracle_cloth_num_meshes(void* h) { return (int)((ClothScene*)h)->meshes.size(); }
+int oracle_cloth_mesh_sizes(void* h, int mesh, int32_t* nV, int32_t* nF, int32_t* nE) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    if (nV) *nV = m.nV;
+    if (nF) *nF = m.nF;
+    if (nE) *nE = m.nE;
+    return GAIA_OK;
+}
+static void copy_out(const std::vector<V3>& v, float* out) { std::memcpy(out, v.data(), v.size() * sizeof(V3)); }
+int oracle_cloth_get_positions(void* h, int mesh, float* xyz) { copy_out(((ClothScene*)h)->meshes[mesh].pos, xyz); return GAIA_OK; }
+int oracle_cloth_get_velocities(void* h, int mesh, float* xyz) { copy_out(((ClothScene*)h)->meshes[mesh].vel, xyz); return GAIA_OK; }
+int oracle_cloth_set_state(void* h, int mesh, const float* pos, const float* vel) {
+    TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    if (pos) std::memcpy((void*)m.pos.data(), pos, m.pos.size() * sizeof(V3));
+    if (vel) std::memcpy((void*)m.vel.data(), vel, m.vel.size() * sizeof(V3));
+    return GAIA_OK;
+}
+int oracle_cloth_set_prev_positions(void* h, int mesh, const float* prev) {
+    TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    std::memcpy((void*)m.prev.data(), prev, m.prev.size() * sizeof(V3));
+    return GAIA_OK;
+}
+int64_t oracle_cloth_total_vertices(void* h) { int64_t n = 0; for (auto& m : ((ClothScene*)h)->meshes) n += m.nV; return n; }
+int oracle_cloth_get_all_positions(void* h, float* xyz) {
+    for (auto& m : ((ClothScene*)h)->meshes) { copy_out(m.pos, xyz); xyz += 3 * (size_t)m.nV; }
+    return GAIA_OK;
+}
+int oracle_cloth_set_all_state(void* h, const float* pos, const float* vel) {
+    for (auto& m : ((ClothScene*)h)->meshes) {
+        if (pos) { std::memcpy((void*)m.pos.data(), pos, m.pos.size() * sizeof(V3)); pos += 3 * (size_t)m.nV; }
+        if (vel) { std::memcpy((void*)m.vel.data(), vel, m.vel.size() * sizeof(V3)); vel += 3 * (size_t)m.nV; }
+    }
+    return GAIA_OK;
+}
+int oracle_cloth_get_edges(void* h, int mesh, int32_t* out) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    for (int e = 0; e < m.nE; e++) {
+        const ClothEdge& E = m.edges[e];
+        const int32_t v[6] = {E.eV1, E.eV2, E.eV12Next, E.eV21Next, E.fId1, E.fId2};
+        std::memcpy(out + 6 * (size_t)e, v, sizeof(v));
+    }
+    return GAIA_OK;
+}
+int oracle_cloth_num_parallel_groups(void* h) { return (int)((ClothScene*)h)->groups.size(); }
+int oracle_cloth_get_parallel_group(void* h, int g, int32_t* out, int32_t* nPairs) {
+    const auto& grp = ((ClothScene*)h)->groups[g];
+    if (nPairs) *nPairs = (int32_t)(grp.size() / 2);
+    if (out) std::memcpy(out, grp.data(), grp.size() * sizeof(int32_t));
+    return GAIA_OK;
+}
+int oracle_cloth_get_vertex_masses(void* h, int mesh, float* out) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    std::memcpy(out, m.mass.data(), m.mass.size() * sizeof(float));
+    return GAIA_OK;
+}
+int oracle_cloth_detect_contacts(void* h) { cloth_detect(*(ClothScene*)h); return GAIA_OK; }
+int oracle_cloth_get_vf_contacts(void* h, gaia_cloth_vf_contact* out, int64_t cap, int64_t* n) {
+    int64_t k = 0;
+    for (auto& m : ((ClothScene*)h)->meshes)
+        for (auto& l : m.vf)
+            for (auto& c : l) {
+                if (out && k < cap) out[k] = {c.vMesh, c.v, c.fMesh, c.f, c.primType, c.primId};
+                k++;
+            }
+    if (n) *n = k;
+    return GAIA_OK;
+}
+int oracle_cloth_get_ee_contacts(void* h, gaia_cloth_ee_contact* out, int64_t cap, int64_t* n) {
+    int64_t k = 0;
+    for (auto& m : ((ClothScene*)h)->meshes)
+        for (auto& l : m.ee)
+            for (auto& c : l) {
+                if (out && k < cap) out[k] = {c.m1, c.e1, c.m2, c.e2};
+                k++;
+            }
+    if (n) *n = k;
+    return GAIA_OK;
+}
+int oracle_cloth_get_conservative_bounds(void* h, int mesh, float* out) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    std::memcpy(out, m.bounds.data(), m.bounds.size() * sizeof(float));
+    return GAIA_OK;
+}
+int oracle_cloth_get_stats(void* h, gaia_cloth_stats* out) { *out = ((ClothScene*)h)->stats; return GAIA_OK; }
+int oracle_cloth_reset_stats(void* h) {
+    ClothScene* s = (ClothScene*)h;
+    const int64_t a = s->stats.numContactsVF, b = s->stats.numContactsEE;
+    std::memset(&s->stats, 0, sizeof(s->stats));
+    s->stats.numContactsVF = a; s->stats.numContactsEE = b;
+    return GAIA_OK;
+}
+int oracle_cloth_set_profiling(void*, int) { return GAIA_OK; }
+
+// ---- probes
+int oracle_cloth_material_force_hessian(void* h, int mesh, int v, float* f3, float* h9) {
+    ClothScene* s = (ClothScene*)h;
+    V3 f; M3 H;
+    cloth_material_force_hessian(*s, s->meshes[mesh], v, f, H);
+    f3[0] = f.x; f3[1] = f.y; f3[2] = f.z;
+    std::memcpy(h9, H.m, sizeof(H.m));
+    return GAIA_OK;
+}
+int oracle_cloth_vertex_force_hessian(void* h, int mesh, int v, float* f3, float* h9) {
+    ClothScene* s = (ClothScene*)h;
+    V3 f; M3 H;
+    cloth_vertex_force_hessian(*s, mesh, v, f, H);
+    f3[0] = f.x; f3[1] = f.y; f3[2] = f.z;
+    std::memcpy(h9, H.m, sizeof(H.m));
+    return GAIA_OK;
+}
+float oracle_cloth_elastic_energy(void* h, int mesh) { ClothScene* s = (ClothScene*)h; return cloth_elastic_energy(*s, s->meshes[mesh]); }
+void oracle_cloth_contact_repulsion(void* h, float dis, float* dEdD, float* d2E) { cloth_contact_repulsion(*(ClothScene*)h, dis, *dEdD, *d2E); }
+int oracle_cloth_get_dminv(void* h, int mesh, float* out4, float* area) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    if (out4) std::memcpy(out4, m.DmInv.data(), m.DmInv.size() * sizeof(float));
+    if (area) std::memcpy(area, m.restArea.data(), m.restArea.size() * sizeof(float));
+    return GAIA_OK;
+}
+int oracle_cloth_get_bending_forms(void* h, int mesh, float* out16) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    for (int e = 0; e < m.nE; e++) std::memcpy(out16 + 16 * (size_t)e, m.Q[e].data(), 16 * sizeof(float));
+    return GAIA_OK;
+}
+void oracle_cloth_closest_points_segments(const float* p0, const float* p1, const float* q0, const float* q1, float* out8) {
+    V3 ps, qt; float s, t;
+    orc::closest_points_segments(V3(p0[0], p0[1], p0[2]), V3(p1[0], p1[1], p1[2]), V3(q0[0], q0[1], q0[2]), V3(q1[0], q1[1], q1[2]), ps, qt, s, t);
+    out8[0] = ps.x; out8[1] = ps.y; out8[2] = ps.z; out8[3] = qt.x; out8[4] = qt.y; out8[5] = qt.z; out8[6] = s; out8[7] = t;
+}
+
+}  // extern "C"
