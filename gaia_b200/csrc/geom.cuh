@@ -133,7 +133,7 @@ GDEV float eval2(const float c[3], float x) { float r = c[2]; r = r * x + c[1]; 
 GDEV float fmin2(float a, float b) { return a <= b ? a : b; }
 GDEV float fmax2(float a, float b) { return a >= b ? a : b; }
 
-__device__ __noinline__ float find_closed3(const float coef[4], const float deriv[4], float x0, float x1, float y0, float xError) {
+static __device__ __noinline__ float find_closed3(const float coef[4], const float deriv[4], float x0, float x1, float y0, float xError) {
     const float ep2 = 2 * xError;
     float xr = (x0 + x1) / 2;
     if (x1 - x0 <= ep2) return xr;
@@ -195,7 +195,7 @@ GDEV void deflate3(float def[3], const float coef[4], float root) {
 }
 
 // roots has room for 4 floats (roots + 1 receives up to two quadratic roots, one of which may be discarded)
-__device__ __noinline__ int cubic_roots(float roots[4], const float coef[4], float x0, float x1) {
+static __device__ __noinline__ int cubic_roots(float roots[4], const float coef[4], float x0, float x1) {
     const float xError = 6e-4f;
     const float y0 = eval3(coef, x0), y1 = eval3(coef, x1);
     const float a = coef[3] * 3, b_2 = coef[2], c = coef[1];
@@ -280,7 +280,7 @@ GDEV void barycentric(V3 p, V3 a, V3 b, V3 c, V3& out) {
 
 // x0[k], x1[k]: triangle vertex k at t=0 / t=1; p0, p1: the point. Returns the first coplanar time in [0,1] at which the
 // point lies inside the triangle.
-__device__ __noinline__ bool tri_point(float& tt, const V3 x0[3], const V3 x1[3], V3 p0, V3 p1, V3& barys) {
+static __device__ __noinline__ bool tri_point(float& tt, const V3 x0[3], const V3 x1[3], V3 p0, V3 p1, V3& barys) {
     const V3 a0[4] = {x0[0], x0[1], x0[2], p0};
     const V3 a1[4] = {x1[0], x1[1], x1[2], p1};
     float t[4];

@@ -1,0 +1,219 @@
+"""GPU: the CUDA cloth step (gaia_b200_cloth_*) against the CPU oracle, through the C ABI.
+
+Integer work (edge ids, parallel groups, VF/EE contact sets) and everything derived from the contact queries
+(conservative bounds) must be bit-exact; positions after one iteration within 1e-5 relative; trajectories within the
+tolerance written in each test. The cloth kernels are compiled without FMA contraction and follow the CPU path's operation
+order, so most comparisons come out identical; the tolerances below are the bars, not the observed differences."""
+import numpy as np
+import pytest
+
+from gaia_b200 import cloth
+from oracle.binding_cloth import OracleClothScene
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def pair(build):
+    """build(scene) adds the meshes; returns (gpu, oracle), both finalized"""
+    out = []
+    for cls, kw in ((cloth.ClothScene, {}), (OracleClothScene, dict(threads=4))):
+        s = build(cls, kw)
+        s.finalize()
+        out.append(s)
+    return out
+
+
+def drape_scene(n=15, phys_kw=None, obj_kw=None, fixed=(), height=0.9, sphere=(0.25, 12, 20, (0, 0.6, 0)), wrinkle=0.0, seed=0):
+    v, f = cloth.grid_cloth(n, 1.0, origin=(0, height, 0))
+    if wrinkle:
+        v = v + np.random.RandomState(seed).uniform(-wrinkle, wrinkle, v.shape).astype(np.float32)
+    pk = dict(numSubsteps=5, iterations=8, contactRadius=0.02, maxQueryDis=0.03, contactStiffness=1e5)
+    pk.update(phys_kw or {})
+    ok = dict(density=0.2, miu=2e3, bendingStiffness=0.5, dampingStVK=1e-6, dampingBending=1e-6)
+    ok["lambda"] = 2e3
+    ok.update(obj_kw or {})
+
+    def build(cls, kw):
+        s = cls(cloth.default_cloth_physics_params(**pk), **kw)
+        s.add_tri_mesh(v, f, cloth.default_cloth_object_params(**ok), cloth.grid_cloth_coloring(n), fixed=fixed)
+        if sphere is not None:
+            sv, sf = cloth.uv_sphere(*sphere)
+            s.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(frictionDynamic=0.3), simulated=False)
+        return s
+    return pair(build)
+
+
+def two_layer_scene(n=9, gap=0.02, phys_kw=None):
+    pk = dict(numSubsteps=2, iterations=4, contactRadius=0.03, maxQueryDis=0.045)
+    pk.update(phys_kw or {})
+    rng = np.random.RandomState(5)
+    layers = []
+    for layer in range(2):
+        v, f = cloth.grid_cloth(n, 1.0, origin=(0.013 * layer, 1.0 + gap * layer, 0.007 * layer))
+        layers.append((v + rng.uniform(-0.004, 0.004, v.shape).astype(np.float32), f))
+    sv, sf = cloth.uv_sphere(0.2, 8, 12, center=(0, 0.78, 0))
+
+    def build(cls, kw):
+        s = cls(cloth.default_cloth_physics_params(**pk), **kw)
+        for i, (v, f) in enumerate(layers):
+            obj = cloth.default_cloth_object_params(bendingStiffness=1.0, density=0.2, miu=1e3, frictionDynamic=0.1 + 0.2 * i)
+            s.add_tri_mesh(v, f, obj, cloth.grid_cloth_coloring(n) if i == 0 else cloth.greedy_cloth_coloring(len(v), f))
+        s.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(), simulated=False)
+        return s
+    return pair(build)
+
+
+def test_setup_integers_and_rest_shape_are_bit_exact():
+    g, o = two_layer_scene()
+    assert g.num_meshes == o.num_meshes == 3
+    for m in range(3):
+        assert g.mesh_sizes(m) == o.mesh_sizes(m)
+        assert np.array_equal(g.edges(m), o.edges(m))
+        assert np.array_equal(g.vertex_masses(m), o.vertex_masses(m))
+        assert np.array_equal(g.positions(m), o.positions(m))
+    gg, og = g.parallel_groups(), o.parallel_groups()
+    assert len(gg) == len(og) and all(np.array_equal(a, b) for a, b in zip(gg, og))
+
+
+def test_contact_sets_and_bounds_are_bit_exact_two_layers():
+    g, o = two_layer_scene()
+    g.detect_contacts(); o.detect_contacts()
+    vfg, vfo = g.vf_contacts(), o.vf_contacts()
+    eeg, eeo = g.ee_contacts(), o.ee_contacts()
+    assert len(vfo) > 50 and len(eeo) > 50
+    assert np.array_equal(vfg, vfo)
+    assert np.array_equal(eeg, eeo)
+    for m in range(2):
+        assert np.array_equal(g.conservative_bounds(m), o.conservative_bounds(m))
+    st = g.stats()
+    assert st["numContactsVF"] == len(vfo) and st["numContactsEE"] == len(eeo)
+
+
+def test_contact_sets_bit_exact_against_brute_force_on_a_crumpled_sheet():
+    # a sheet folded onto itself: many self contacts of every closest-primitive type
+    n = 14
+    v, f = cloth.grid_cloth(n, 1.0, origin=(0, 1.0, 0))
+    x = v[:, 0].copy()
+    fold = x > 0.1
+    v[fold, 0] = 0.2 - x[fold]                       # fold the right part over the left
+    v[fold, 1] += 0.024
+    v += np.random.RandomState(11).uniform(-0.003, 0.003, v.shape).astype(np.float32)
+    pk = dict(contactRadius=0.02, maxQueryDis=0.04)
+
+    def build(cls, kw):
+        s = cls(cloth.default_cloth_physics_params(**pk), **kw)
+        s.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(n))
+        return s
+    g, o = pair(build)
+    o.set_brute_force(True)
+    g.detect_contacts(); o.detect_contacts()
+    vfo, eeo = o.vf_contacts(), o.ee_contacts()
+    assert len(vfo) > 100 and len(eeo) > 100 and len(set(vfo[:, 4])) >= 2
+    assert np.array_equal(g.vf_contacts(), vfo)
+    assert np.array_equal(g.ee_contacts(), eeo)
+    assert np.array_equal(g.conservative_bounds(0), o.conservative_bounds(0))
+
+
+@pytest.mark.parametrize("energy", [0, 1, 2])
+def test_positions_after_one_iteration_with_contacts(energy):
+    g, o = two_layer_scene(phys_kw=dict(contactEnergyTypes=energy))
+    g.run_iterations(1); o.run_iterations(1)
+    for m in range(2):
+        pg, po = g.positions(m), o.positions(m)
+        assert np.isfinite(pg).all()
+        assert rel_err(pg, po) < 1e-5, (energy, m, rel_err(pg, po))
+    g.run_iterations(3); o.run_iterations(3)
+    for m in range(2):
+        assert rel_err(g.positions(m), o.positions(m)) < 2e-5
+
+
+def test_free_fall_with_pinned_corners_no_collision():
+    n = 12
+    g, o = drape_scene(n, phys_kw=dict(handleCollision=0, numSubsteps=4, iterations=10), fixed=[0, n - 1], sphere=None, wrinkle=0.01)
+    x0 = o.positions(0)
+    g.run_frames(10); o.run_frames(10)
+    pg, po = g.positions(0), o.positions(0)
+    assert np.array_equal(pg[[0, n - 1]], x0[[0, n - 1]])
+    assert po[:, 1].min() < x0[:, 1].min() - 0.05
+    assert np.abs(pg - po).max() < 1e-4, np.abs(pg - po).max()
+    assert np.abs(g.velocities(0) - o.velocities(0)).max() < 1e-2
+
+
+def test_drape_over_sphere_trajectory_and_contact_sets():
+    """30 frames of a 15x15 sheet falling onto a sphere collider: positions within 1e-3 (0.1 % of the sheet width) of the
+    oracle's at every checkpoint, and from the GPU's own final state both detectors return the same contact sets."""
+    g, o = drape_scene(15)
+    for frame in range(3):
+        g.run_frames(10); o.run_frames(10)
+        pg, po = g.positions(0), o.positions(0)
+        assert np.isfinite(pg).all()
+        assert np.abs(pg - po).max() < 1e-3, (frame, np.abs(pg - po).max())
+    R, c = 0.25, np.array([0, 0.6, 0], np.float32)
+    assert np.linalg.norm(pg - c, axis=1).min() > R * np.cos(np.pi / 20) - 0.02       # no tunnelling
+    sg, so = g.stats(), o.stats()
+    assert sg["numberCollisionDetection"] >= 150 and sg["numContactsVF"] > 0
+    assert sg["vertexSolves"] == so["vertexSolves"] and sg["colourSweeps"] == so["colourSweeps"]
+    # same state -> identical contact sets
+    o.set_state(0, pg, g.velocities(0))
+    g.detect_contacts(); o.detect_contacts()
+    assert np.array_equal(g.vf_contacts(), o.vf_contacts())
+    assert np.array_equal(g.ee_contacts(), o.ee_contacts())
+    assert np.array_equal(g.conservative_bounds(0), o.conservative_bounds(0))
+
+
+@pytest.mark.parametrize("init_type", [0, 1, 2, 3])
+def test_accelerator_and_initialization_types(init_type):
+    g, o = drape_scene(8, phys_kw=dict(applyAcceleration=1, acceleratorRho=0.9, numSubsteps=4, iterations=6, contactRadius=0.03, maxQueryDis=0.05),
+                       obj_kw=dict(initializationType=init_type, bendingStiffness=5.0), fixed=[0, 7], sphere=None, height=1.0)
+    g.run_frames(4); o.run_frames(4)
+    pg, po = g.positions(0), o.positions(0)
+    assert np.isfinite(pg).all()
+    assert np.abs(pg - po).max() < 2e-4, (init_type, np.abs(pg - po).max())
+
+
+def test_state_io_roundtrip_and_error_paths():
+    g, o = two_layer_scene()
+    x = g.all_positions()
+    assert x.shape[0] == g.total_vertices == o.total_vertices
+    assert np.array_equal(x, o.all_positions())
+    y = x + np.float32(0.25)
+    g.set_all_state(y, np.ones_like(y))
+    assert np.array_equal(g.all_positions(), y)
+    assert np.array_equal(g.velocities(1), np.ones((g.mesh_sizes(1)[0], 3), np.float32))
+    g.set_state(0, x[:g.mesh_sizes(0)[0]])
+    assert np.array_equal(g.positions(0), x[:g.mesh_sizes(0)[0]])
+    with pytest.raises(cloth.GaiaError):
+        g.add_tri_mesh(x[:9], np.array([[0, 1, 2]], np.int32), cloth.default_cloth_object_params(), [np.arange(9, dtype=np.int32)])
+    # a simulated mesh without a colouring is refused
+    s = cloth.ClothScene(cloth.default_cloth_physics_params())
+    with pytest.raises(cloth.GaiaError):
+        s.add_tri_mesh(x[:9], np.array([[0, 1, 2]], np.int32), cloth.default_cloth_object_params())
+    # too many contacts on one vertex: reported, never silently dropped
+    v, f = cloth.grid_cloth(12, 0.1, origin=(0, 1, 0))
+    s = cloth.ClothScene(cloth.default_cloth_physics_params(maxQueryDis=0.2, contactRadius=0.1))
+    s.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(12))
+    s.finalize()
+    with pytest.raises(cloth.GaiaError, match="contacts on one"):
+        s.detect_contacts()
+
+
+def test_million_vertex_sheet_properties():
+    """BASELINE config 3 at full size (1000 x 1000 vertices) through size-independent properties: a flat sheet in free fall
+    with no collider keeps its shape exactly in x/z, every vertex falls by the same amount, and pinned vertices stay."""
+    n = 1000
+    v, f = cloth.grid_cloth_fast(n, 100.0, origin=(0, 50.0, 0))
+    s = cloth.ClothScene(cloth.default_cloth_physics_params(numSubsteps=2, iterations=3, gravity=[0, -1000, 0], contactRadius=0.03,
+                                                           maxQueryDis=0.045))
+    obj = cloth.default_cloth_object_params(density=0.02, bendingStiffness=10.0)
+    s.add_tri_mesh(v, f, obj, cloth.grid_cloth_coloring(n))
+    s.finalize()
+    s.run_frames(1)
+    x = s.positions(0)
+    assert np.isfinite(x).all()
+    dy = x[:, 1] - v[:, 1]
+    assert dy.max() < -0.03 and (dy.max() - dy.min()) < 1e-2 * abs(dy.mean())   # the fall is capped by the conservative bounds
+    assert np.abs(x[:, [0, 2]] - v[:, [0, 2]]).max() < 1e-3
+    st = s.stats()
+    assert st["vertexSolves"] == n * n * 6 and st["numContactsVF"] == 0 and st["numContactsEE"] == 0
