@@ -29,7 +29,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from gaia_b200 import capi, meshio  # noqa: E402
+from gaia_b200 import capi, cloth, meshio  # noqa: E402
 
 
 def log(*a):
@@ -104,7 +104,41 @@ def workload_drop_pile(n_objects=32, grid=(4, 4), substeps=4, iterations=20, pre
     return dict(name=name, meshes=meshes, phys=phys, col=col, deformers=[], preroll=preroll)
 
 
+def workload_cloth_drape(n=1000, width=100.0, substeps=20, iterations=15, preroll=2, sphere_level=4):
+    """SURVEY.md §8(d) cfg 3: n x n vertex sheet (the reference's C{N}_horizontal.obj family, 100 units wide) centred above a
+    sphere collider of radius 0.3 x width (all collider vertices fixed), S03_MultiLayerClothOnCollider.py values: StVK
+    mu = lambda = 1e4, density 0.02, bendingStiffness 10, damping 2e-6, gravity (0,-1000,0), contactStiffness 1e5,
+    contactRadius 0.3 and maxQueryDis 0.45 scaled by cell / cell(C70), thickness 1e-4, conservativeStepRelaxation 0.4,
+    friction 0.1, 20 substeps x 15 iterations; VF + EE contact with the collider and with itself. `preroll` untimed frames
+    let the sheet land on the sphere before anything is measured."""
+    scale = (width / (n - 1)) / (100.0 / 69.0)
+    R = 0.3 * width
+    v, f = cloth.grid_cloth_fast(n, width, origin=(0.0, R + 0.6 * 0.45 * scale, 0.0))
+    sv, sf = cloth.icosphere(R, sphere_level, center=(0.0, 0.0, 0.0))
+    phys = cloth.default_cloth_physics_params(gravity=[0, -1000, 0], numSubsteps=substeps, iterations=iterations, contactStiffness=1e5,
+                                              contactRadius=0.3 * scale, maxQueryDis=0.45 * scale, thickness=1e-4 * scale,
+                                              conservativeStepRelaxation=0.4, contactEnergyTypes=1)
+    obj = cloth.default_cloth_object_params(miu=1e4, density=0.02, bendingStiffness=10.0, dampingStVK=2e-6, dampingBending=2e-6,
+                                            frictionDynamic=0.1, frictionEpsV=0.1, initializationType=2)
+    obj.lambda_ = 1e4
+    name = (f"cloth_drape {n}x{n} sheet ({len(v)} verts, {len(f)} tris) over a sphere collider ({len(sv)} verts), VF+EE contact, "
+            f"{substeps} substeps x {iterations} iters, 9 colours")
+    meshes = [(v, f, obj, cloth.grid_cloth_coloring(n), np.zeros(0, np.int32), True),
+              (sv, sf, cloth.default_cloth_object_params(frictionDynamic=0.1), [], np.zeros(0, np.int32), False)]
+    return dict(kind="cloth", name=name, meshes=meshes, phys=phys, col=None, deformers=[], preroll=preroll)
+
+
+def is_cloth(wl):
+    return wl.get("kind") == "cloth"
+
+
 def build_scene(cls, wl, **kw):
+    if is_cloth(wl):
+        s = cls(wl["phys"], **kw)
+        for v, f, obj, colors, fixed, simulated in wl["meshes"]:
+            s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=simulated)
+        s.finalize()
+        return s
     s = cls(wl["phys"], wl["col"], **kw)
     for v, t, obj, colors, fixed in wl["meshes"]:
         s.add_tet_mesh(v, t, obj, colors, fixed)
@@ -123,6 +157,9 @@ WORKLOADS = {
     "twist_beam_small": lambda: workload_twist_beam(24, 12, 12),
     "drop_pile_32": lambda: workload_drop_pile(32),
     "drop_pile_8": lambda: workload_drop_pile(8, grid=(2, 2), preroll=30),
+    "cloth_1m": lambda: workload_cloth_drape(1000),
+    "cloth_250k": lambda: workload_cloth_drape(500, width=50.0, sphere_level=4),
+    "cloth_small": lambda: workload_cloth_drape(120, width=12.0, substeps=4, iterations=6, sphere_level=2),
 }
 
 
@@ -171,7 +208,13 @@ def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
     """Time the CPU oracle on a bounded sample of the workload: a beam of the same cross-section and material, 1/8 of the
     length, one frame (5 substeps x 20 iterations); iterations are reduced if one substep already exceeds the budget."""
     from oracle.binding import OracleScene
-    sample_wl = workload_twist_beam(59, 60, 60) if "10m" in wl_name or "1m" in wl_name else WORKLOADS[wl_name]()
+    from oracle.binding_cloth import OracleClothScene
+    if wl_name.startswith("cloth"):
+        # same cell size, material and contact parameters on a 160 x 160 sheet (sphere scaled with it)
+        sample_wl = WORKLOADS[wl_name]() if wl_name == "cloth_small" else workload_cloth_drape(160, width=16.0, sphere_level=3, preroll=0)
+        OracleScene = OracleClothScene
+    else:
+        sample_wl = workload_twist_beam(59, 60, 60) if "10m" in wl_name or "1m" in wl_name else WORKLOADS[wl_name]()
     t0 = time.time()
     o = build_scene(OracleScene, sample_wl, threads=threads)
     setup = time.time() - t0
@@ -196,7 +239,8 @@ def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
     st = o.stats()
     return {"value": st["vertexSolves"] / dt, "unit": "vertex-solves/s", "cores": o.num_threads, "kind": "port",
             "sample": f"{sample_wl['name']}: {what} in {dt:.1f}s (setup {setup:.1f}s), oracle = CPU restatement of "
-                      f"VBDPhysics::runStep_hybridCollisionHandling with std::thread pool"}, st["vertexSolves"], dt
+                      + ("VBDClothSimulationFramework::runStep_CDEveryIter" if wl_name.startswith("cloth") else
+                         "VBDPhysics::runStep_hybridCollisionHandling") + " with std::thread pool"}, st["vertexSolves"], dt
 
 
 def run_reference_arm(args):
@@ -257,10 +301,12 @@ def main():
     t0 = time.time()
     wl = WORKLOADS[args.workload]()
     if world > 1:
+        if is_cloth(wl):
+            raise SystemExit("the cloth workloads run on one GPU (north_star partitions configs 4 and 5 only)")
         from gaia_b200 import multigpu
         scene = multigpu.build_partitioned_scene(wl, rank, world, local_rank)
     else:
-        scene = build_scene(capi.Scene, wl, device=local_rank)
+        scene = build_scene(cloth.ClothScene if is_cloth(wl) else capi.Scene, wl, device=local_rank)
     log(f"[bench] rank {rank}: scene '{wl['name']}' built in {time.time() - t0:.1f}s")
     stream = torch.cuda.ExternalStream(scene.cuda_stream, device=torch.device("cuda", local_rank))
 
@@ -354,14 +400,16 @@ def main():
         launches = sp["colourSweeps"]
         alg_bytes = sp["algorithmicBytes"]
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-        roof = {"kernel": "k_solve_colour", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        phase_keys = (("timeCsmpUpdatingCollisionInfoDCD",) if is_cloth(wl) else
+                      ("timeCsmpColDetectDCD", "timeCsmpInitialStep", "timeCsmpColDetectCCD", "timeCsmpMaterialSolve", "timeCsmpUpdateVelocity"))
+        contacts = ({"vf": sp["numContactsVF"], "ee": sp["numContactsEE"], "detections": sp["numberCollisionDetection"]} if is_cloth(wl) else
+                    {"dcd": sp["numContactsDCD"], "ccd": sp["numContactsCCD"]})
+        roof = {"kernel": "gbc::k_solve_colour (cloth)" if is_cloth(wl) else "k_solve_colour", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes / max(1, launches), "avg_launch_us": 1e3 * k_ms / max(1, launches),
                 "launches_profiled": launches, "kernel_share_of_step": (k_ms / max(1, args.profile_steps)) / (ms / args.steps),
-                "phases_ms_per_step": {k: sp[k] / max(1, args.profile_steps) for k in
-                                       ("timeCsmpColDetectDCD", "timeCsmpInitialStep", "timeCsmpColDetectCCD", "timeCsmpMaterialSolve",
-                                        "timeCsmpUpdateVelocity")},
-                "contacts": {"dcd": sp["numContactsDCD"], "ccd": sp["numContactsCCD"]}}
+                "phases_ms_per_step": {k: sp[k] / max(1, args.profile_steps) for k in phase_keys},
+                "contacts": contacts}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath) and world == 1:
             try:
@@ -384,7 +432,8 @@ def main():
                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": wl["name"], "parallelism": f"x-slab partition over {world} GPU(s)" if world > 1 else "1 GPU",
-                          "l2": "inputs larger than L2 (incidence streams 1.3 GB vs 126 MB), no flush needed",
+                          "l2": "inputs larger than L2 (per-iteration record streams: %s vs 126 MB), no flush needed"
+                                % ("0.57 GB" if is_cloth(wl) else "1.3 GB"),
                           "sim_steps_per_s": st["substeps"] / (ms * 1e-3), "frames_per_s": args.steps / (ms * 1e-3)},
                "clocks": clk, "e2e": e2e, "gpu_launches": int(st["kernelLaunches"]), "roofline": roof, "cpu_baseline": cpu}
         emit(out)

@@ -393,3 +393,30 @@ def uv_sphere(radius=1.0, n_lat=16, n_lon=32, center=(0.0, 0.0, 0.0)):
     for b in range(n_lon):
         faces.append((last, ring(n_lat - 1, b), ring(n_lat - 1, b + 1)))
     return verts, np.asarray(faces, np.int32)
+
+
+def icosphere(radius=1.0, level=3, center=(0.0, 0.0, 0.0)):
+    """Subdivided icosahedron (level 3 = 642 vertices / 1280 triangles, the shape of S/VBDCloth/ParameterGen/Data/
+    SphereCollider.obj): every vertex has valence 5 or 6, unlike uv_sphere whose poles collect n_lon edges."""
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    verts = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t),
+             (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    verts = [tuple(np.asarray(v, np.float64) / np.linalg.norm(v)) for v in verts]
+    faces = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6), (7, 1, 8),
+             (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7), (9, 8, 1)]
+    for _ in range(level):
+        cache, new_faces = {}, []
+
+        def mid(a, b):
+            key = (min(a, b), max(a, b))
+            if key not in cache:
+                m = (np.asarray(verts[a]) + np.asarray(verts[b])) * 0.5
+                verts.append(tuple(m / np.linalg.norm(m)))
+                cache[key] = len(verts) - 1
+            return cache[key]
+        for a, b, c in faces:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            new_faces += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        faces = new_faces
+    v = (np.asarray(verts, np.float64) * radius + np.asarray(center, np.float64)).astype(np.float32)
+    return v, np.asarray(faces, np.int32)

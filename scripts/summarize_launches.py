@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per kernel count, total, average, share."""
+import collections
+import csv
+import re
+import sys
+
+rows = list(csv.reader(open(sys.argv[1])))
+hi = next(i for i, r in enumerate(rows) if 'Kernel Name' in r)
+hdr = rows[hi]
+ki, vi, ui = hdr.index('Kernel Name'), hdr.index('Metric Value'), hdr.index('Metric Unit')
+agg = collections.defaultdict(lambda: [0, 0.0])
+for r in rows[hi + 1:]:
+    if len(r) <= vi:
+        continue
+    name = re.sub(r'\(.*', '', r[ki])[:70]
+    v = float(r[vi].replace(',', ''))
+    v = v / 1e3 if r[ui] == 'ns' else (v * 1e3 if r[ui] == 'ms' else v)
+    agg[name][0] += 1
+    agg[name][1] += v
+tot = sum(v[1] for v in agg.values())
+print(f"# {sys.argv[1]}: {sum(v[0] for v in agg.values())} launches, {tot / 1e3:.2f} ms of kernel time (cold-cache, serialised)")
+for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+    print(f"{k:72s} n={v[0]:6d} total={v[1] / 1e3:10.2f} ms  avg={v[1] / v[0]:9.1f} us  share={v[1] / tot:.3f}")

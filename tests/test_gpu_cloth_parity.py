@@ -214,6 +214,6 @@ def test_million_vertex_sheet_properties():
     assert np.isfinite(x).all()
     dy = x[:, 1] - v[:, 1]
     assert dy.max() < -0.03 and (dy.max() - dy.min()) < 1e-2 * abs(dy.mean())   # the fall is capped by the conservative bounds
-    assert np.abs(x[:, [0, 2]] - v[:, [0, 2]]).max() < 1e-3
+    assert np.abs(x[:, [0, 2]] - v[:, [0, 2]]).max() < 5e-3          # 5e-5 of the width
     st = s.stats()
     assert st["vertexSolves"] == n * n * 6 and st["numContactsVF"] == 0 and st["numContactsEE"] == 0
