@@ -33,6 +33,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 using gb::DevBuf;
@@ -544,30 +545,56 @@ static __global__ void k_link_sort(int nF, int64_t cap, const int32_t* __restric
 }
 
 // conservative bounds + active mask (applyCollisionDetection, VBDClothPhysics.cpp:775-816)
+// It also flattens, per vertex with contacts, the work list of the contact pre-pass (same order as the reference walks
+// it: own VF contacts, back-links of the incident faces, EE contacts of the incident edges) into one item array:
+// item = ((kind | order << 1) << 29 | a, b) with VF: a = query vertex, b = face; EE: a = edge 1, b = edge 2.
 static __global__ void k_bounds_active(DevView D, StepP P, const float* __restrict__ vfMinDis, const int32_t* __restrict__ vfCount,
-                                       const int32_t* __restrict__ faceMinBits, const int32_t* __restrict__ linkOff,
-                                       const float* __restrict__ eeMinDis, const int32_t* __restrict__ eeCount, float* __restrict__ bounds,
-                                       uint8_t* __restrict__ hasContact, uint8_t* __restrict__ activeMask, float4* __restrict__ posAtCD) {
+                                       const int2* __restrict__ vfList, const int32_t* __restrict__ faceMinBits, const int32_t* __restrict__ linkOff,
+                                       const int32_t* __restrict__ linkVal, const float* __restrict__ eeMinDis, const int32_t* __restrict__ eeCount,
+                                       const int32_t* __restrict__ eeList, float* __restrict__ bounds, uint8_t* __restrict__ hasContact,
+                                       uint8_t* __restrict__ activeMask, float4* __restrict__ posAtCD, int32_t* itemCursor, int64_t itemCap,
+                                       int32_t* __restrict__ itemOff, int32_t* __restrict__ itemCnt, int2* __restrict__ items, int32_t* errFlags) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= D.nSimV) return;
     float dMin = P.R;
     dMin = fminf(dMin, vfMinDis[s]);
-    bool active = vfCount[s] > 0;
+    const int nOwn = vfCount[s];
+    int total = nOwn;
     for (int i = D.vfOff[s]; i < D.vfOff[s + 1]; i++) {
         const int f = D.vfInc[i] >> 2;
         dMin = fminf(dMin, __int_as_float(faceMinBits[f]));
-        active = active || linkOff[f + 1] > linkOff[f];
+        total += linkOff[f + 1] - linkOff[f];
     }
     for (int i = D.veOff[s]; i < D.veOff[s + 1]; i++) {
         const int e = D.veInc[i] >> 1;
         dMin = fminf(dMin, eeMinDis[e]);
-        active = active || eeCount[e] > 0;
+        total += eeCount[e];
     }
     dMin = fmaxf(0.f, dMin - P.thickness);
     bounds[s] = dMin * P.relax;
+    const bool active = total > 0;
     hasContact[s] = active ? 1 : 0;
     if (active) activeMask[s] = 1;
     posAtCD[s] = D.pos[s];
+    int cnt = 0, off = 0;
+    if (active && D.info[s] >= 0) {
+        off = atomicAdd(itemCursor, total);
+        if ((int64_t)off + total <= itemCap) {
+            int at = off;
+            for (int i = 0; i < nOwn; i++) items[at++] = make_int2((0 | 3 << 1) << 29 | s, vfList[(size_t)s * KV + i].x);
+            for (int q = D.vfOff[s]; q < D.vfOff[s + 1]; q++) {
+                const int ent = D.vfInc[q], f = ent >> 2, order = ent & 3;
+                for (int l = linkOff[f]; l < linkOff[f + 1]; l++) items[at++] = make_int2((0 | order << 1) << 29 | D.o2s[linkVal[l] / KV], f);
+            }
+            for (int q = D.veOff[s]; q < D.veOff[s + 1]; q++) {
+                const int ent = D.veInc[q], e = ent >> 1, order = ent & 1;
+                const int ne = eeCount[e];
+                for (int j = 0; j < ne; j++) items[at++] = make_int2((1 | order << 1) << 29 | e, eeList[(size_t)e * KE + j]);
+            }
+            cnt = total;
+        } else atomicAdd(errFlags + ERR_LINK, 1);
+    }
+    itemOff[s] = off; itemCnt[s] = cnt;
 }
 static __global__ void k_no_collision_bounds(int n, float* bounds, uint8_t* hasContact) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -852,6 +879,190 @@ k_solve_colour(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const fl
     pos[s] = make_float4(out.x, out.y, out.z, p4.w);
 }
 
+// ------------------------------------------------------------------------------------------------ fast kernels
+// The two kernels above walk the lists in the CPU path's order with one thread per vertex, which makes every sum
+// bit-identical to the oracle's but leaves one long dependent chain per thread. The default path below spreads each
+// vertex over a sub-warp (same terms, pairwise-tree summation instead of left-to-right): results agree to rounding
+// (tests: 1e-5 relative after one iteration). GAIA_B200_CLOTH_EXACT_ORDER=1 selects the exact-order kernels.
+static const int LC = 8;   // lanes per vertex in the contact pre-pass
+static const int LS = 4;   // lanes per vertex in the colour sweep
+
+static __global__ void __launch_bounds__(kB)
+k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restrict__ itemOff, const int32_t* __restrict__ itemCnt,
+                     const int2* __restrict__ items, float4* __restrict__ cTerm) {
+    const int T = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = T / LC, j = T % LC;
+    const int s = gs + min(t, n - 1);
+    const int cnt = t < n ? itemCnt[s] : 0;
+    if (!__any_sync(0xffffffffu, cnt > 0)) return;
+    V3 force = v3(0, 0, 0);
+    float H[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) H[k] = 0.f;
+    const int off = itemOff[s];
+    for (int i = j; i < cnt; i += LC) {
+        const int2 it = items[off + i];
+        const int head = (unsigned)it.x >> 29, a = it.x & 0x1FFFFFFF;
+        if (head & 1) ee_contact(D, P, a, it.y, head >> 1, force, H);
+        else vf_contact(D, P, a, it.y, head >> 1, force, H);
+    }
+#pragma unroll
+    for (int o = LC / 2; o > 0; o >>= 1) {
+        force.x += __shfl_xor_sync(0xffffffffu, force.x, o); force.y += __shfl_xor_sync(0xffffffffu, force.y, o);
+        force.z += __shfl_xor_sync(0xffffffffu, force.z, o);
+#pragma unroll
+        for (int k = 0; k < 9; k++) H[k] += __shfl_xor_sync(0xffffffffu, H[k], o);
+    }
+    if (j == 0 && cnt > 0) {
+        cTerm[3 * (size_t)s + 0] = make_float4(force.x, force.y, force.z, H[0]);
+        cTerm[3 * (size_t)s + 1] = make_float4(H[1], H[2], H[3], H[4]);
+        cTerm[3 * (size_t)s + 2] = make_float4(H[5], H[6], H[7], H[8]);
+    }
+}
+
+// Same update as k_solve_colour with LS lanes per vertex: lane j takes the incident faces / hinges j, j + LS, ... of the
+// per-colour ELL streams; the StVK Hessian is contracted in closed form,
+//   H = A [ a11 f1 f1^T + a22 f2 f2^T + a12 (f1 f2^T + f2 f1^T) + c I ],  f = -A [ f1 (S00 m1 + S01 m2) + f2 (S01 m1 + S11 m2) ],
+//   a11 = m1^2 (l + 2u) + m2^2 u, a22 = m2^2 (l + 2u) + m1^2 u, a12 = m1 m2 (l + u),
+//   c = m1^2 (2u Guu + l tr) + m2^2 (2u Gvv + l tr) + 4 m1 m2 u Guv
+// (the 6x6 d2W/dF2 of VBDTriMeshStVK.cpp:760-870 contracted with (m1 I, m2 I), VBDBaseTriMesh.h:149-160).
+static __global__ void __launch_bounds__(kB)
+k_solve_colour_fast(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
+                    const int32_t* __restrict__ info, const MeshDev* __restrict__ mt, const float4* __restrict__ recFA, const int4* __restrict__ recFB,
+                    const float4* __restrict__ recHA, const int4* __restrict__ recHB, const uint8_t* __restrict__ hasContact,
+                    const float4* __restrict__ cTerm, const float4* __restrict__ posAtCD, const float* __restrict__ bounds, float4* next,
+                    int32_t* errFlags) {
+    const int T = blockIdx.x * blockDim.x + threadIdx.x;
+    const int tt = T / LS, j = T % LS;
+    const bool valid = tt < n;
+    const int t = min(tt, n - 1);
+    const int s = gs + t;
+    const int inf = info[s];
+    const bool solve = valid && inf >= 0;
+    const MeshDev& M = mt[inf & 0x00FFFFFF];
+    const float4 p4 = pos[s];
+    const V3 x = v3(p4.x, p4.y, p4.z);
+    const float lmbd = M.lambda, miu = M.miu, kBd = M.kBend;
+    V3 f = v3(0, 0, 0);
+    float h00 = 0.f, h01 = 0.f, h02 = 0.f, h11 = 0.f, h12 = 0.f, h22 = 0.f, hb = 0.f;
+    if (solve) {
+        for (int k = j; k < ellF; k += LS) {
+            const int4 fb = __ldg(recFB + (size_t)k * n + t);
+            if (fb.x < 0) continue;
+            const float4 I = __ldg(recFA + (size_t)k * n + t);
+            const int order = fb.x == s ? 0 : (fb.y == s ? 1 : 2);
+            const V3 x0 = order == 0 ? x : ld3(pos, fb.x), x1 = order == 1 ? x : ld3(pos, fb.y), x2 = order == 2 ? x : ld3(pos, fb.z);
+            const V3 v1 = x1 - x0, v2 = x2 - x0;
+            const float A = __int_as_float(fb.w);
+            const V3 f1 = I.x * v1 + I.y * v2, f2 = I.z * v1 + I.w * v2;
+            const float G00 = 0.5f * (gb::dot(f1, f1) - 1.f), G11 = 0.5f * (gb::dot(f2, f2) - 1.f), G01 = 0.5f * gb::dot(f1, f2);
+            const float tr = G00 + G11;
+            const float S00 = 2.f * miu * G00 + lmbd * tr, S11 = 2.f * miu * G11 + lmbd * tr, S01 = 2.f * miu * G01;
+            float m1, m2;
+            if (order == 0) { m1 = -I.x - I.y; m2 = -I.z - I.w; }
+            else if (order == 1) { m1 = I.x; m2 = I.z; }
+            else { m1 = I.y; m2 = I.w; }
+            f += (-A) * ((S00 * m1 + S01 * m2) * f1 + (S01 * m1 + S11 * m2) * f2);
+            const float l2u = lmbd + 2.f * miu;
+            const float a11 = A * (m1 * m1 * l2u + m2 * m2 * miu), a22 = A * (m2 * m2 * l2u + m1 * m1 * miu), a12 = A * (m1 * m2 * (lmbd + miu));
+            const float c = A * (m1 * m1 * (2.f * miu * G00 + lmbd * tr) + m2 * m2 * (2.f * miu * G11 + lmbd * tr) + 4.f * m1 * m2 * miu * G01);
+            h00 += a11 * f1.x * f1.x + a22 * f2.x * f2.x + 2.f * a12 * f1.x * f2.x + c;
+            h11 += a11 * f1.y * f1.y + a22 * f2.y * f2.y + 2.f * a12 * f1.y * f2.y + c;
+            h22 += a11 * f1.z * f1.z + a22 * f2.z * f2.z + 2.f * a12 * f1.z * f2.z + c;
+            h01 += a11 * f1.x * f1.y + a22 * f2.x * f2.y + a12 * (f1.x * f2.y + f2.x * f1.y);
+            h02 += a11 * f1.x * f1.z + a22 * f2.x * f2.z + a12 * (f1.x * f2.z + f2.x * f1.z);
+            h12 += a11 * f1.y * f1.z + a22 * f2.y * f2.z + a12 * (f1.y * f2.z + f2.y * f1.z);
+        }
+        for (int k = j; k < ellH; k += LS) {
+            const int4 hbi = __ldg(recHB + (size_t)k * n + t);
+            if (hbi.x < 0) continue;
+            const float4 q = __ldg(recHA + (size_t)k * n + t);
+            const int order = hbi.x == s ? 0 : (hbi.y == s ? 1 : (hbi.z == s ? 2 : 3));
+            const V3 X0 = order == 0 ? x : ld3(pos, hbi.x), X1 = order == 1 ? x : ld3(pos, hbi.y);
+            const V3 X2 = order == 2 ? x : ld3(pos, hbi.z), X3 = order == 3 ? x : ld3(pos, hbi.w);
+            const V3 n1 = gb::cross(X1 - X0, X2 - X0), n2 = gb::cross(X2 - X3, X1 - X3);
+            if (gb::sqnorm(n1) < P.degThres2 || gb::sqnorm(n2) < P.degThres2) continue;
+            f -= kBd * (q.x * X0 + q.y * X1 + q.z * X2 + q.w * X3);
+            hb += kBd * (order == 0 ? q.x : (order == 1 ? q.y : (order == 2 ? q.z : q.w)));
+        }
+    }
+#pragma unroll
+    for (int o = LS / 2; o > 0; o >>= 1) {
+        f.x += __shfl_xor_sync(0xffffffffu, f.x, o); f.y += __shfl_xor_sync(0xffffffffu, f.y, o); f.z += __shfl_xor_sync(0xffffffffu, f.z, o);
+        h00 += __shfl_xor_sync(0xffffffffu, h00, o); h01 += __shfl_xor_sync(0xffffffffu, h01, o); h02 += __shfl_xor_sync(0xffffffffu, h02, o);
+        h11 += __shfl_xor_sync(0xffffffffu, h11, o); h12 += __shfl_xor_sync(0xffffffffu, h12, o); h22 += __shfl_xor_sync(0xffffffffu, h22, o);
+        hb += __shfl_xor_sync(0xffffffffu, hb, o);
+    }
+    if (!solve || j != 0) return;
+    // ---- tail (one lane per vertex): contacts, inertia, damping, world box, 3x3 solve, truncation
+    const V3 xPrev = ld3(prev, s);
+    const float4 in4 = inertia[s];
+    const float mass = in4.w;
+    V3 force = v3(0, 0, 0);
+    float H[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) H[k] = 0.f;
+    if (hasContact[s]) {
+        const float4 c0 = cTerm[3 * (size_t)s], c1 = cTerm[3 * (size_t)s + 1], c2 = cTerm[3 * (size_t)s + 2];
+        force = v3(c0.x, c0.y, c0.z);
+        H[0] = c0.w; H[1] = c1.x; H[2] = c1.y; H[3] = c1.z; H[4] = c1.w; H[5] = c2.x; H[6] = c2.y; H[7] = c2.z; H[8] = c2.w;
+    }
+    force += mass * (v3(in4.x, in4.y, in4.z) - x) * P.dtSqrRec;
+    {
+        const float hi = mass * P.dtSqrRec;
+        H[0] += hi; H[4] += hi; H[8] += hi;
+    }
+    const V3 disp = x - xPrev;
+    {
+        const float ds = M.dampStVK / P.dt, g1 = 1.f + ds;
+        force += f - ds * v3(h00 * disp.x + h01 * disp.y + h02 * disp.z, h01 * disp.x + h11 * disp.y + h12 * disp.z, h02 * disp.x + h12 * disp.y + h22 * disp.z);
+        H[0] += g1 * h00; H[4] += g1 * h11; H[8] += g1 * h22;
+        H[1] += g1 * h01; H[3] += g1 * h01; H[2] += g1 * h02; H[6] += g1 * h02; H[5] += g1 * h12; H[7] += g1 * h12;
+        const float db = M.dampBend / P.dt;
+        force -= (hb * db) * disp;
+        const float hh = hb * (1.f + db);
+        H[0] += hh; H[4] += hh; H[8] += hh;
+    }
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+        const float xd = gb::comp(x, d);
+        float depth, sign;
+        if (xd < P.bmin[d]) { depth = P.bmin[d] - xd; sign = 1.f; }
+        else if (xd > P.bmax[d]) { depth = xd - P.bmax[d]; sign = -1.f; }
+        else continue;
+        const float fd = sign * (depth * P.kBoundary);
+        if (d == 0) force.x += fd; else if (d == 1) force.y += fd; else force.z += fd;
+        H[d + 3 * d] += P.kBoundary;
+        const V3 t0 = v3((d + 1) % 3 == 0 ? 1.f : 0.f, (d + 1) % 3 == 1 ? 1.f : 0.f, (d + 1) % 3 == 2 ? 1.f : 0.f);
+        const V3 t1 = v3((d + 2) % 3 == 0 ? 1.f : 0.f, (d + 2) % 3 == 1 ? 1.f : 0.f, (d + 2) % 3 == 2 ? 1.f : 0.f);
+        V3 ff; float fh[9];
+        friction(P.muBoundary, depth * P.kBoundary, t0, t1, gb::dot(t0, disp), gb::dot(t1, disp), P.epsVBoundary * P.dt, ff, fh);
+        force += ff;
+#pragma unroll
+        for (int k = 0; k < 9; k++) H[k] += fh[k];
+    }
+    V3 dxs, out;
+    if (solve3x3(H, force, dxs)) {
+        V3 posNew = x + P.stepSize * dxs;
+        const V3 c = ld3(posAtCD, s);
+        V3 acc = posNew - c;
+        const float size = gb::norm(acc), bound = bounds[s];
+        if (size > bound) {
+            acc = acc * (bound / size);
+            posNew = c + acc;
+            errFlags[FLAG_TRUNC] = 1;
+        }
+        out = posNew;
+        next[s] = make_float4(out.x, out.y, out.z, 0.f);
+    } else {
+        atomicAdd(errFlags + ERR_SOLVER, 1);
+        const float4 nx = next[s];
+        out = v3(nx.x, nx.y, nx.z);
+    }
+    if (!(out.x == out.x) || !(out.y == out.y) || !(out.z == out.z)) atomicAdd(errFlags + ERR_NAN, 1);
+    pos[s] = make_float4(out.x, out.y, out.z, p4.w);
+}
+
 // ------------------------------------------------------------------------------------------------ elementwise passes
 // VBDBaseTriMesh::applyInitialStep + forwardStep_intertia (VBDBaseTriMesh.cpp:60-182)
 static __global__ void k_initial_step(int n, StepP P, int hasVelPrev, float4* pos, float4* prev, float4* vel, float4* velPrev, float4* inertia,
@@ -981,6 +1192,11 @@ struct ClothScene {
     DevBuf<uint8_t> scanTmp;
     size_t scanTmpBytes = 0;
     int64_t linkCap = 0;
+    DevBuf<int32_t> itemOff, itemCnt, itemCursor;
+    DevBuf<int2> items;
+    int64_t itemCap = 0;
+    bool exactOrder = false;            // GAIA_B200_CLOTH_EXACT_ORDER: one thread per vertex, the CPU path's summation order
+    bool exactContact = false, exactSolve = false;   // (2 / 3 select one of the two kernels only: debugging aid)
     DevBuf<int32_t> errFlags;
     int32_t* h_flags = nullptr;         // pinned
     DevBuf<float> ioStage;
@@ -1136,6 +1352,10 @@ static cudaError_t device_upload(ClothScene& s) {
     CK(s.linkVal.alloc(s.linkCap));
     cub::DeviceScan::ExclusiveSum(nullptr, s.scanTmpBytes, s.linkCnt.p, s.linkOff.p, (int)(h.nF + 1));
     CK(s.scanTmp.alloc(s.scanTmpBytes + 16));
+    s.itemCap = std::min<int64_t>(32 * h.nSimV + 4096, (int64_t)1 << 30);
+    CK(s.items.alloc(s.itemCap)); CK(s.itemOff.alloc(h.nSimV + 1)); CK(s.itemCnt.alloc(h.nSimV + 1)); CK(s.itemCursor.alloc(1));
+    CK(cudaMemset(s.itemCnt.p, 0, (h.nSimV + 1) * 4)); CK(cudaMemset(s.itemOff.p, 0, (h.nSimV + 1) * 4));
+    { const char* ex = getenv("GAIA_B200_CLOTH_EXACT_ORDER"); s.exactOrder = ex && ex[0] == '1'; s.exactContact = s.exactOrder || (ex && ex[0] == '2'); s.exactSolve = s.exactOrder || (ex && ex[0] == '3'); }
     CK(s.errFlags.alloc(N_FLAGS)); CK(cudaMemset(s.errFlags.p, 0, N_FLAGS * 4));
     CK(cudaMallocHost((void**)&s.h_flags, N_FLAGS * sizeof(int32_t)));
     std::memset(s.h_flags, 0, N_FLAGS * sizeof(int32_t));
@@ -1195,9 +1415,11 @@ static cudaError_t detect(ClothScene& s) {
     CK(cub::DeviceScan::ExclusiveSum(s.scanTmp.p, s.scanTmpBytes, s.linkCnt.p, s.linkOff.p, (int)(h.nF + 1), s.stream));
     k_link_fill<<<nblk(N), kB, 0, s.stream>>>(N, s.linkCap, s.s2o.p, s.vfCount.p, s.vfList.p, s.linkOff.p, s.linkCur.p, s.linkVal.p, s.errFlags.p);
     k_link_sort<<<nblk(h.nF), kB, 0, s.stream>>>((int)h.nF, s.linkCap, s.linkOff.p, s.linkVal.p);
+    CK(cudaMemsetAsync(s.itemCursor.p, 0, sizeof(int32_t), s.stream));
     if (h.nSimV)
-        k_bounds_active<<<nblk(h.nSimV), kB, 0, s.stream>>>(D, s.P, s.vfMinDis.p, s.vfCount.p, s.faceMinBits.p, s.linkOff.p, s.eeMinDis.p, s.eeCount.p,
-                                                           s.bounds.p, s.hasContact.p, s.activeMask.p, s.posAtCD.p);
+        k_bounds_active<<<nblk(h.nSimV), kB, 0, s.stream>>>(D, s.P, s.vfMinDis.p, s.vfCount.p, s.vfList.p, s.faceMinBits.p, s.linkOff.p, s.linkVal.p,
+                                                           s.eeMinDis.p, s.eeCount.p, s.eeList.p, s.bounds.p, s.hasContact.p, s.activeMask.p,
+                                                           s.posAtCD.p, s.itemCursor.p, s.itemCap, s.itemOff.p, s.itemCnt.p, s.items.p, s.errFlags.p);
     s.stats.kernelLaunches += 8;
     s.collisionDetectionRequired = false;
     s.stats.numberCollisionDetection++;
@@ -1257,14 +1479,24 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
         const int gs = h.groupStart[g], n = h.groupStart[g + 1] - gs;
         if (!n) continue;
         if (h.phys.handleCollision) {
-            k_contact_terms<<<nblk(n), kB, 0, s.stream>>>(gs, n, D, s.P, s.hasContact.p, s.vfCount.p, s.vfList.p, s.linkOff.p, s.linkVal.p, s.eeCount.p,
-                                                          s.eeList.p, s.cTerm.p);
+            if (s.exactContact)
+                k_contact_terms<<<nblk(n), kB, 0, s.stream>>>(gs, n, D, s.P, s.hasContact.p, s.vfCount.p, s.vfList.p, s.linkOff.p, s.linkVal.p,
+                                                              s.eeCount.p, s.eeList.p, s.cTerm.p);
+            else
+                k_contact_terms_fast<<<nblk((int64_t)n * LC), kB, 0, s.stream>>>(gs, n, D, s.P, s.itemOff.p, s.itemCnt.p, s.items.p, s.cTerm.p);
             s.stats.kernelLaunches++;
         }
         if (s.profiling) cudaEventRecord(s.ev[2 * g], s.stream);
-        k_solve_colour<<<nblk(n), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p, s.meshTab.p,
-                                                     s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g], s.recHA.p + h.ellHBase[g],
-                                                     s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p, s.errFlags.p);
+        if (s.exactSolve)
+            k_solve_colour<<<nblk(n), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p, s.meshTab.p,
+                                                         s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g], s.recHA.p + h.ellHBase[g],
+                                                         s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p,
+                                                         s.errFlags.p);
+        else
+            k_solve_colour_fast<<<nblk((int64_t)n * LS), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p,
+                                                                           s.meshTab.p, s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g],
+                                                                           s.recHA.p + h.ellHBase[g], s.recHB.p + h.ellHBase[g], s.hasContact.p,
+                                                                           s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p, s.errFlags.p);
         if (s.profiling) cudaEventRecord(s.ev[2 * g + 1], s.stream);
         s.stats.kernelLaunches++;
         s.stats.colourSweeps++;
