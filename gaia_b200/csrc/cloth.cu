@@ -885,7 +885,6 @@ k_solve_colour(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const fl
 // vertex over a sub-warp (same terms, pairwise-tree summation instead of left-to-right): results agree to rounding
 // (tests: 1e-5 relative after one iteration). GAIA_B200_CLOTH_EXACT_ORDER=1 selects the exact-order kernels.
 static const int LC = 8;   // lanes per vertex in the contact pre-pass
-static const int LS = 4;   // lanes per vertex in the colour sweep
 
 static __global__ void __launch_bounds__(kB)
 k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restrict__ itemOff, const int32_t* __restrict__ itemCnt,
@@ -926,6 +925,7 @@ k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restric
 //   a11 = m1^2 (l + 2u) + m2^2 u, a22 = m2^2 (l + 2u) + m1^2 u, a12 = m1 m2 (l + u),
 //   c = m1^2 (2u Guu + l tr) + m2^2 (2u Gvv + l tr) + 4 m1 m2 u Guv
 // (the 6x6 d2W/dF2 of VBDTriMeshStVK.cpp:760-870 contracted with (m1 I, m2 I), VBDBaseTriMesh.h:149-160).
+template <int LS, int UF, int UH>
 static __global__ void __launch_bounds__(kB)
 k_solve_colour_fast(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
                     const int32_t* __restrict__ info, const MeshDev* __restrict__ mt, const float4* __restrict__ recFA, const int4* __restrict__ recFB,
@@ -946,44 +946,79 @@ k_solve_colour_fast(int gs, int n, int ellF, int ellH, StepP P, float4* pos, con
     V3 f = v3(0, 0, 0);
     float h00 = 0.f, h01 = 0.f, h02 = 0.f, h11 = 0.f, h12 = 0.f, h22 = 0.f, hb = 0.f;
     if (solve) {
-        for (int k = j; k < ellF; k += LS) {
-            const int4 fb = __ldg(recFB + (size_t)k * n + t);
-            if (fb.x < 0) continue;
-            const float4 I = __ldg(recFA + (size_t)k * n + t);
-            const int order = fb.x == s ? 0 : (fb.y == s ? 1 : 2);
-            const V3 x0 = order == 0 ? x : ld3(pos, fb.x), x1 = order == 1 ? x : ld3(pos, fb.y), x2 = order == 2 ? x : ld3(pos, fb.z);
-            const V3 v1 = x1 - x0, v2 = x2 - x0;
-            const float A = __int_as_float(fb.w);
-            const V3 f1 = I.x * v1 + I.y * v2, f2 = I.z * v1 + I.w * v2;
-            const float G00 = 0.5f * (gb::dot(f1, f1) - 1.f), G11 = 0.5f * (gb::dot(f2, f2) - 1.f), G01 = 0.5f * gb::dot(f1, f2);
-            const float tr = G00 + G11;
-            const float S00 = 2.f * miu * G00 + lmbd * tr, S11 = 2.f * miu * G11 + lmbd * tr, S01 = 2.f * miu * G01;
-            float m1, m2;
-            if (order == 0) { m1 = -I.x - I.y; m2 = -I.z - I.w; }
-            else if (order == 1) { m1 = I.x; m2 = I.z; }
-            else { m1 = I.y; m2 = I.w; }
-            f += (-A) * ((S00 * m1 + S01 * m2) * f1 + (S01 * m1 + S11 * m2) * f2);
-            const float l2u = lmbd + 2.f * miu;
-            const float a11 = A * (m1 * m1 * l2u + m2 * m2 * miu), a22 = A * (m2 * m2 * l2u + m1 * m1 * miu), a12 = A * (m1 * m2 * (lmbd + miu));
-            const float c = A * (m1 * m1 * (2.f * miu * G00 + lmbd * tr) + m2 * m2 * (2.f * miu * G11 + lmbd * tr) + 4.f * m1 * m2 * miu * G01);
-            h00 += a11 * f1.x * f1.x + a22 * f2.x * f2.x + 2.f * a12 * f1.x * f2.x + c;
-            h11 += a11 * f1.y * f1.y + a22 * f2.y * f2.y + 2.f * a12 * f1.y * f2.y + c;
-            h22 += a11 * f1.z * f1.z + a22 * f2.z * f2.z + 2.f * a12 * f1.z * f2.z + c;
-            h01 += a11 * f1.x * f1.y + a22 * f2.x * f2.y + a12 * (f1.x * f2.y + f2.x * f1.y);
-            h02 += a11 * f1.x * f1.z + a22 * f2.x * f2.z + a12 * (f1.x * f2.z + f2.x * f1.z);
-            h12 += a11 * f1.y * f1.z + a22 * f2.y * f2.z + a12 * (f1.y * f2.z + f2.y * f1.z);
+        // UF (UH) rounds of records are loaded, then all their neighbour positions gathered, before the first use: the sweep is
+        // bound by the latency of these dependent loads, so they are kept in flight together
+        for (int k0 = j; k0 < ellF; k0 += UF * LS) {
+            int4 fb[UF]; float4 I[UF]; V3 xa[UF], xb[UF];
+#pragma unroll
+            for (int u = 0; u < UF; u++) {
+                const int k = k0 + u * LS;
+                fb[u] = k < ellF ? __ldg(recFB + (size_t)k * n + t) : make_int4(-1, -1, -1, 0);
+                I[u] = k < ellF ? __ldg(recFA + (size_t)k * n + t) : make_float4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < UF; u++) {
+                const int ia = fb[u].x == s ? fb[u].y : fb[u].x, ib = fb[u].z == s ? fb[u].y : fb[u].z;
+                xa[u] = fb[u].x >= 0 ? ld3(pos, ia) : x; xb[u] = fb[u].x >= 0 ? ld3(pos, ib) : x;
+            }
+#pragma unroll
+            for (int u = 0; u < UF; u++) {
+                if (fb[u].x < 0) continue;
+                const int order = fb[u].x == s ? 0 : (fb[u].y == s ? 1 : 2);
+                const V3 x0 = order == 0 ? x : xa[u], x1 = order == 0 ? xa[u] : (order == 1 ? x : xb[u]), x2 = order == 2 ? x : xb[u];
+                const V3 v1 = x1 - x0, v2 = x2 - x0;
+                const float A = __int_as_float(fb[u].w);
+                const float4 Iu = I[u];
+                const V3 f1 = Iu.x * v1 + Iu.y * v2, f2 = Iu.z * v1 + Iu.w * v2;
+                const float G00 = 0.5f * (gb::dot(f1, f1) - 1.f), G11 = 0.5f * (gb::dot(f2, f2) - 1.f), G01 = 0.5f * gb::dot(f1, f2);
+                const float tr = G00 + G11;
+                const float S00 = 2.f * miu * G00 + lmbd * tr, S11 = 2.f * miu * G11 + lmbd * tr, S01 = 2.f * miu * G01;
+                float m1, m2;
+                if (order == 0) { m1 = -Iu.x - Iu.y; m2 = -Iu.z - Iu.w; }
+                else if (order == 1) { m1 = Iu.x; m2 = Iu.z; }
+                else { m1 = Iu.y; m2 = Iu.w; }
+                f += (-A) * ((S00 * m1 + S01 * m2) * f1 + (S01 * m1 + S11 * m2) * f2);
+                const float l2u = lmbd + 2.f * miu;
+                const float a11 = A * (m1 * m1 * l2u + m2 * m2 * miu), a22 = A * (m2 * m2 * l2u + m1 * m1 * miu), a12 = A * (m1 * m2 * (lmbd + miu));
+                const float c = A * (m1 * m1 * (2.f * miu * G00 + lmbd * tr) + m2 * m2 * (2.f * miu * G11 + lmbd * tr) + 4.f * m1 * m2 * miu * G01);
+                h00 += a11 * f1.x * f1.x + a22 * f2.x * f2.x + 2.f * a12 * f1.x * f2.x + c;
+                h11 += a11 * f1.y * f1.y + a22 * f2.y * f2.y + 2.f * a12 * f1.y * f2.y + c;
+                h22 += a11 * f1.z * f1.z + a22 * f2.z * f2.z + 2.f * a12 * f1.z * f2.z + c;
+                h01 += a11 * f1.x * f1.y + a22 * f2.x * f2.y + a12 * (f1.x * f2.y + f2.x * f1.y);
+                h02 += a11 * f1.x * f1.z + a22 * f2.x * f2.z + a12 * (f1.x * f2.z + f2.x * f1.z);
+                h12 += a11 * f1.y * f1.z + a22 * f2.y * f2.z + a12 * (f1.y * f2.z + f2.y * f1.z);
+            }
         }
-        for (int k = j; k < ellH; k += LS) {
-            const int4 hbi = __ldg(recHB + (size_t)k * n + t);
-            if (hbi.x < 0) continue;
-            const float4 q = __ldg(recHA + (size_t)k * n + t);
-            const int order = hbi.x == s ? 0 : (hbi.y == s ? 1 : (hbi.z == s ? 2 : 3));
-            const V3 X0 = order == 0 ? x : ld3(pos, hbi.x), X1 = order == 1 ? x : ld3(pos, hbi.y);
-            const V3 X2 = order == 2 ? x : ld3(pos, hbi.z), X3 = order == 3 ? x : ld3(pos, hbi.w);
-            const V3 n1 = gb::cross(X1 - X0, X2 - X0), n2 = gb::cross(X2 - X3, X1 - X3);
-            if (gb::sqnorm(n1) < P.degThres2 || gb::sqnorm(n2) < P.degThres2) continue;
-            f -= kBd * (q.x * X0 + q.y * X1 + q.z * X2 + q.w * X3);
-            hb += kBd * (order == 0 ? q.x : (order == 1 ? q.y : (order == 2 ? q.z : q.w)));
+        for (int k0 = j; k0 < ellH; k0 += UH * LS) {
+            int4 hbi[UH]; float4 q[UH]; V3 Xa[UH], Xb[UH], Xc[UH];
+#pragma unroll
+            for (int u = 0; u < UH; u++) {
+                const int k = k0 + u * LS;
+                hbi[u] = k < ellH ? __ldg(recHB + (size_t)k * n + t) : make_int4(-1, -1, -1, -1);
+                q[u] = k < ellH ? __ldg(recHA + (size_t)k * n + t) : make_float4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < UH; u++) {
+                // the three vertices of the hinge other than s, in slot order
+                const int4 h4 = hbi[u];
+                const int order = h4.x == s ? 0 : (h4.y == s ? 1 : (h4.z == s ? 2 : 3));
+                const int ia = order == 0 ? h4.y : h4.x, ib = order <= 1 ? h4.z : h4.y, ic = order == 3 ? h4.z : h4.w;
+                const bool on = h4.x >= 0;
+                Xa[u] = on ? ld3(pos, ia) : x; Xb[u] = on ? ld3(pos, ib) : x; Xc[u] = on ? ld3(pos, ic) : x;
+            }
+#pragma unroll
+            for (int u = 0; u < UH; u++) {
+                const int4 h4 = hbi[u];
+                if (h4.x < 0) continue;
+                const int order = h4.x == s ? 0 : (h4.y == s ? 1 : (h4.z == s ? 2 : 3));
+                const V3 X0 = order == 0 ? x : Xa[u], X1 = order == 0 ? Xa[u] : (order == 1 ? x : Xb[u]);
+                const V3 X2 = order <= 1 ? Xb[u] : (order == 2 ? x : Xc[u]), X3 = order == 3 ? x : Xc[u];
+                const V3 n1 = gb::cross(X1 - X0, X2 - X0), n2 = gb::cross(X2 - X3, X1 - X3);
+                if (gb::sqnorm(n1) < P.degThres2 || gb::sqnorm(n2) < P.degThres2) continue;
+                const float4 qu = q[u];
+                f -= kBd * (qu.x * X0 + qu.y * X1 + qu.z * X2 + qu.w * X3);
+                hb += kBd * (order == 0 ? qu.x : (order == 1 ? qu.y : (order == 2 ? qu.z : qu.w)));
+            }
         }
     }
 #pragma unroll
@@ -1196,6 +1231,7 @@ struct ClothScene {
     DevBuf<int2> items;
     int64_t itemCap = 0;
     bool exactOrder = false;            // GAIA_B200_CLOTH_EXACT_ORDER: one thread per vertex, the CPU path's summation order
+    int variant = 0;
     bool exactContact = false, exactSolve = false;   // (2 / 3 select one of the two kernels only: debugging aid)
     DevBuf<int32_t> errFlags;
     int32_t* h_flags = nullptr;         // pinned
@@ -1356,6 +1392,7 @@ static cudaError_t device_upload(ClothScene& s) {
     CK(s.items.alloc(s.itemCap)); CK(s.itemOff.alloc(h.nSimV + 1)); CK(s.itemCnt.alloc(h.nSimV + 1)); CK(s.itemCursor.alloc(1));
     CK(cudaMemset(s.itemCnt.p, 0, (h.nSimV + 1) * 4)); CK(cudaMemset(s.itemOff.p, 0, (h.nSimV + 1) * 4));
     { const char* ex = getenv("GAIA_B200_CLOTH_EXACT_ORDER"); s.exactOrder = ex && ex[0] == '1'; s.exactContact = s.exactOrder || (ex && ex[0] == '2'); s.exactSolve = s.exactOrder || (ex && ex[0] == '3'); }
+    { const char* va = getenv("GAIA_B200_CLOTH_VARIANT"); s.variant = va ? atoi(va) : 0; }
     CK(s.errFlags.alloc(N_FLAGS)); CK(cudaMemset(s.errFlags.p, 0, N_FLAGS * 4));
     CK(cudaMallocHost((void**)&s.h_flags, N_FLAGS * sizeof(int32_t)));
     std::memset(s.h_flags, 0, N_FLAGS * sizeof(int32_t));
@@ -1492,11 +1529,22 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
                                                          s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g], s.recHA.p + h.ellHBase[g],
                                                          s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p,
                                                          s.errFlags.p);
-        else
-            k_solve_colour_fast<<<nblk((int64_t)n * LS), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p,
-                                                                           s.meshTab.p, s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g],
-                                                                           s.recHA.p + h.ellHBase[g], s.recHB.p + h.ellHBase[g], s.hasContact.p,
-                                                                           s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p, s.errFlags.p);
+        else {
+            // variants: lanes per vertex / rounds of face and hinge records kept in flight (GAIA_B200_CLOTH_VARIANT, default 0)
+            auto launch = [&](auto kern, int lanes) {
+                kern<<<nblk((int64_t)n * lanes), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p, s.meshTab.p,
+                                                                   s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g], s.recHA.p + h.ellHBase[g],
+                                                                   s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p,
+                                                                   s.next.p, s.errFlags.p);
+            };
+            switch (s.variant) {
+                case 1: launch(k_solve_colour_fast<4, 1, 1>, 4); break;
+                case 2: launch(k_solve_colour_fast<8, 1, 2>, 8); break;
+                case 3: launch(k_solve_colour_fast<8, 1, 1>, 8); break;
+                case 4: launch(k_solve_colour_fast<2, 2, 2>, 2); break;
+                default: launch(k_solve_colour_fast<4, 2, 3>, 4); break;
+            }
+        }
         if (s.profiling) cudaEventRecord(s.ev[2 * g + 1], s.stream);
         s.stats.kernelLaunches++;
         s.stats.colourSweeps++;

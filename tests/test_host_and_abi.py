@@ -17,10 +17,43 @@ from gaia_b200 import capi, meshio
 HOST_BIN = os.path.join(ROOT, "gaia_b200", "host", "gaia_vbd_b200")
 
 
-def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "gaia_b200.h")).read()
+def declared_symbols(header="gaia_b200.h"):
+    text = open(os.path.join(ROOT, "include", header)).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(gaia_b200_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_cloth_symbol_and_layouts_match():
+    from gaia_b200 import cloth
+    lib = capi.load_library()
+    names = declared_symbols("gaia_b200_cloth.h")
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/gaia_b200_cloth.h but not exported"
+    text = open(os.path.join(ROOT, "include", "gaia_b200_cloth.h")).read()
+    for cname, cls in (("gaia_cloth_physics_params", cloth.ClothPhysicsParams), ("gaia_cloth_object_params", cloth.ClothObjectParams),
+                       ("gaia_cloth_vf_contact", cloth.ClothVFContact), ("gaia_cloth_ee_contact", cloth.ClothEEContact),
+                       ("gaia_cloth_stats", cloth.ClothStats)):
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), text, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        fields = []
+        for ln in body.split(";"):
+            m = re.match(r"\s*\w+\s+(.*)", ln, re.S)
+            if m:
+                fields += [re.match(r"(\w+)", x.strip()).group(1) for x in m.group(1).split(",")]
+        assert fields == [n.rstrip("_") for n, _ in cls._fields_], cname
+    p = cloth.ClothPhysicsParams(); lib.gaia_b200_cloth_default_physics_params(C.byref(p))
+    assert bytes(p) == bytes(cloth.default_cloth_physics_params())
+    o = cloth.ClothObjectParams(); lib.gaia_b200_cloth_default_object_params(C.byref(o))
+    assert bytes(o) == bytes(cloth.default_cloth_object_params())
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the no-GPU failure mode")
+def test_cloth_create_fails_loudly_without_gpu():
+    from gaia_b200 import cloth
+    with pytest.raises(capi.GaiaError) as e:
+        cloth.ClothScene()
+    assert "no CPU path" in str(e.value)
 
 
 def test_library_exports_every_declared_symbol():
