@@ -884,7 +884,7 @@ k_solve_colour(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const fl
 // bit-identical to the oracle's but leaves one long dependent chain per thread. The default path below spreads each
 // vertex over a sub-warp (same terms, pairwise-tree summation instead of left-to-right): results agree to rounding
 // (tests: 1e-5 relative after one iteration). GAIA_B200_CLOTH_EXACT_ORDER=1 selects the exact-order kernels.
-static const int LC = 8;   // lanes per vertex in the contact pre-pass
+static const int LC = 8;   // lanes per vertex in the contact pre-pass (the colour sweep takes 1, 4 or 8: see iteration())
 
 static __global__ void __launch_bounds__(kB)
 k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restrict__ itemOff, const int32_t* __restrict__ itemCnt,
@@ -926,7 +926,7 @@ k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restric
 //   c = m1^2 (2u Guu + l tr) + m2^2 (2u Gvv + l tr) + 4 m1 m2 u Guv
 // (the 6x6 d2W/dF2 of VBDTriMeshStVK.cpp:760-870 contracted with (m1 I, m2 I), VBDBaseTriMesh.h:149-160).
 template <int LS, int UF, int UH>
-static __global__ void __launch_bounds__(kB)
+static __global__ void __launch_bounds__(kB, 6)
 k_solve_colour_fast(int gs, int n, int ellF, int ellH, StepP P, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
                     const int32_t* __restrict__ info, const MeshDev* __restrict__ mt, const float4* __restrict__ recFA, const int4* __restrict__ recFB,
                     const float4* __restrict__ recHA, const int4* __restrict__ recHB, const uint8_t* __restrict__ hasContact,
@@ -1530,19 +1530,20 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
                                                          s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p, s.next.p,
                                                          s.errFlags.p);
         else {
-            // variants: lanes per vertex / rounds of face and hinge records kept in flight (GAIA_B200_CLOTH_VARIANT, default 0)
             auto launch = [&](auto kern, int lanes) {
                 kern<<<nblk((int64_t)n * lanes), kB, 0, s.stream>>>(gs, n, h.ellF[g], h.ellH[g], s.P, s.pos.p, s.prev.p, s.inertia.p, s.info.p, s.meshTab.p,
                                                                    s.recFA.p + h.ellFBase[g], s.recFB.p + h.ellFBase[g], s.recHA.p + h.ellHBase[g],
                                                                    s.recHB.p + h.ellHBase[g], s.hasContact.p, s.cTerm.p, s.posAtCD.p, s.bounds.p,
                                                                    s.next.p, s.errFlags.p);
             };
-            switch (s.variant) {
+            // lanes per vertex / rounds of face and hinge records in flight, by colour size (measured on B200, scripts/
+            // cloth_variants.py): big colours fill the GPU with one thread per vertex and want loads in flight; small ones
+            // need the extra lanes to have enough warps. GAIA_B200_CLOTH_VARIANT = 1 / 2 / 3 forces one (tests).
+            const int v = s.variant ? s.variant : (n >= 80000 ? 3 : (n >= 8000 ? 1 : 2));
+            switch (v) {
                 case 1: launch(k_solve_colour_fast<4, 1, 1>, 4); break;
                 case 2: launch(k_solve_colour_fast<8, 1, 2>, 8); break;
-                case 3: launch(k_solve_colour_fast<8, 1, 1>, 8); break;
-                case 4: launch(k_solve_colour_fast<2, 2, 2>, 2); break;
-                default: launch(k_solve_colour_fast<4, 2, 3>, 4); break;
+                default: launch(k_solve_colour_fast<1, 2, 2>, 1); break;
             }
         }
         if (s.profiling) cudaEventRecord(s.ev[2 * g + 1], s.stream);

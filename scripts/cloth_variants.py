@@ -7,7 +7,7 @@ from gaia_b200 import cloth
 
 wl = bench.WORKLOADS[sys.argv[1] if len(sys.argv) > 1 else "cloth_1m"]()
 ref = None
-for variant in ("1", "0", "2", "3", "4"):
+for variant in (sys.argv[2].split(",") if len(sys.argv) > 2 else ("1", "0", "2", "3", "4")):
     os.environ["GAIA_B200_CLOTH_VARIANT"] = variant
     s = bench.build_scene(cloth.ClothScene, wl, device=0)
     s.run_frames(1)

@@ -117,6 +117,19 @@ def test_contact_sets_bit_exact_against_brute_force_on_a_crumpled_sheet():
     assert np.array_equal(g.conservative_bounds(0), o.conservative_bounds(0))
 
 
+@pytest.mark.parametrize("variant", ["1", "2", "3"])
+def test_every_colour_sweep_variant_matches_after_one_iteration(variant, monkeypatch):
+    """The sweep kernel is instantiated with 4, 8 or 1 lanes per vertex and picked by colour size; each is forced here."""
+    monkeypatch.setenv("GAIA_B200_CLOTH_VARIANT", variant)
+    g, o = two_layer_scene(rot=0.6)
+    g.run_iterations(1); o.run_iterations(1)
+    for m in range(2):
+        assert rel_err(g.positions(m), o.positions(m)) < 1e-5
+    g2, o2 = drape_scene(11, wrinkle=0.01)
+    g2.run_frames(2); o2.run_frames(2)
+    assert np.abs(g2.positions(0) - o2.positions(0)).max() < 1e-4
+
+
 @pytest.mark.parametrize("energy", [0, 1, 2])
 def test_positions_after_one_iteration_with_contacts(energy):
     # the upper layer is turned by 0.6 rad: with the two grids aligned, nearly parallel edge pairs make the edge-edge
