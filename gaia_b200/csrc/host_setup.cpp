@@ -200,8 +200,11 @@ bool host_finalize(Scene& s) {
         std::iota(free_.begin(), free_.end(), 0);
         for (auto& colour : m.colors) {
             size_t pick = 0;
-            for (size_t i = 1; i < free_.size(); i++)
-                if (s.groups[free_[i]].size() < s.groups[free_[pick]].size()) pick = i;   // first smallest
+            // (a partition of a multi-GPU scene is handed the GLOBAL group of each colour as the colour's index: every
+            //  partition must sweep the same global group together, so nothing is re-balanced locally)
+            if (!s.partitionMode)
+                for (size_t i = 1; i < free_.size(); i++)
+                    if (s.groups[free_[i]].size() < s.groups[free_[pick]].size()) pick = i;   // first smallest
             const int g = free_[pick];
             free_.erase(free_.begin() + pick);
             for (int32_t v : colour) {

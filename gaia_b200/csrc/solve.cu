@@ -740,7 +740,9 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     static int fusedHalo = -1;
     if (fusedHalo < 0) { const char* e = getenv("GAIA_B200_HALO_FUSED"); fusedHalo = e ? atoi(e) : 1; }
     HaloView hv;
-    const bool fused = halo && fusedHalo && !s.phys.useAccelerator && halo_view(s, hv);   // (the accelerator needs full refreshes)
+    // (the accelerator needs full refreshes; with contacts the per-colour pre-pass reads ghost positions BEFORE the sweep,
+    //  so the exchange of the previous colour must be complete when it starts: the separate push + wait launch is used)
+    const bool fused = halo && fusedHalo && !s.phys.useAccelerator && !s.cs && halo_view(s, hv);
     static int haloDebug = -1;      // timing experiments only: 1 = do not wait, 2 = do not store to peers (results are wrong)
     if (haloDebug < 0) { const char* e = getenv("GAIA_B200_HALO_DEBUG"); haloDebug = e ? atoi(e) : 0; }
     if (fused) hv.debug = haloDebug;

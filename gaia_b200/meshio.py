@@ -220,3 +220,17 @@ def kuhn_blob(n, radii=(1.0, 1.0, 1.0), h=1.0, power=2.0):
     remap[used] = np.arange(len(used))
     v = (verts[used] - n / 2.0) * np.float32(h)
     return v.astype(np.float32), remap[t].astype(np.int32)
+
+
+def place(verts, obj):
+    """World-space rest positions of an object: rotation (axis * angle) -> scale -> translation, as TetMeshFEM::initialize
+    does (M/TetMesh/TetMeshFEM.cpp:369-384). float64 numpy; used for partitioning decisions only."""
+    p = np.asarray(verts, np.float64)
+    rot = np.array([obj.rotation[0], obj.rotation[1], obj.rotation[2]], np.float64)
+    ang = np.linalg.norm(rot)
+    if ang > 0:
+        a = rot / ang
+        K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+        R = np.eye(3) + np.sin(ang) * K + (1 - np.cos(ang)) * (K @ K)
+        p = p @ R.T
+    return p * np.array([obj.scale[0], obj.scale[1], obj.scale[2]]) + np.array([obj.translation[0], obj.translation[1], obj.translation[2]])

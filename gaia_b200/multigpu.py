@@ -144,3 +144,137 @@ def gather_owned_positions(scene, part, n_global):
     for ids, p in everyone:
         out[ids] = p
     return out
+
+
+# ------------------------------------------------------------------------------------------------ many-object scenes
+def global_groups(color_lists):
+    """The merge of per-mesh colours into global parallel groups (M/VBD/VBDPhysics.cpp:236-274, findSmallestParallelGroup
+    :99-122) restated on sizes alone, for ALL meshes of the global scene: returns, per mesh, its colours arranged by global
+    group id (empty where the mesh has no colour in that group). A partition hands these to add_tet_mesh in partition mode,
+    where colour i goes to group i, so every partition sweeps the same global group at the same time."""
+    n_groups = max(len(c) for c in color_lists)
+    sizes = [0] * n_groups
+    out = []
+    for colors in color_lists:
+        ordered = global_color_order(colors)
+        free = list(range(len(ordered)))
+        arranged = [np.zeros(0, np.int32) for _ in range(n_groups)]
+        for c in ordered:
+            pick = 0
+            for i in range(1, len(free)):
+                if sizes[free[i]] < sizes[free[pick]]:
+                    pick = i
+            g = free.pop(pick)
+            arranged[g] = np.asarray(c, np.int32)
+            sizes[g] += len(c)
+        out.append(arranged)
+    return out
+
+
+def object_boxes(meshes, transform):
+    """[n,2,3] world-space boxes of every object at rest (transform(verts, obj) applies the object's placement)."""
+    boxes = np.empty((len(meshes), 2, 3), np.float64)
+    for k, m in enumerate(meshes):
+        p = transform(m[0], m[2])
+        boxes[k, 0] = p.min(0); boxes[k, 1] = p.max(0)
+    return boxes
+
+
+class ObjectSharding:
+    """Whole objects assigned to ranks by equal-count slabs of their centroid along `axis`; each rank additionally holds
+    GHOST copies (every vertex a ghost: never solved there, overwritten by the owner's per-colour pushes) of
+      tier 1: objects of other ranks that may touch an owned object, and
+      tier 2: objects that may touch a tier-1 object - they only make sure a tier-1 vertex picks the same single contact
+              here as on its owner (the reference keeps ONE contact per vertex, rules R1-R3),
+    "may touch" = the boxes, grown by `margin`, overlap in the coordinates `axes` (the vertical is left out for a falling
+    pile: objects keep their column). The assignment is static and deterministic from the rest boxes: every rank derives
+    every rank's tables without communication."""
+
+    def __init__(self, boxes, world, margin, axis=0, axes=(0, 2)):
+        n = len(boxes)
+        self.world = world
+        cen = 0.5 * (boxes[:, 0, axis] + boxes[:, 1, axis])
+        order = np.argsort(cen, kind="stable")
+        self.owner = np.empty(n, np.int32)
+        for r in range(world):
+            self.owner[order[(n * r) // world:(n * (r + 1)) // world]] = r
+        lo = boxes[:, 0][:, list(axes)] - margin
+        hi = boxes[:, 1][:, list(axes)] + margin
+        touch = np.ones((n, n), bool)
+        for d in range(lo.shape[1]):
+            touch &= (lo[:, None, d] <= hi[None, :, d]) & (lo[None, :, d] <= hi[:, None, d])
+        self.local, self.tier = [], []
+        for r in range(world):
+            owned = self.owner == r
+            t1 = touch[owned].any(0) & ~owned
+            t2 = touch[t1].any(0) & ~owned & ~t1 if t1.any() else np.zeros(n, bool)
+            tier = np.full(n, -1, np.int32)
+            tier[owned] = 0; tier[t1] = 1; tier[t2] = 2
+            self.tier.append(tier)
+            self.local.append(np.nonzero(tier >= 0)[0])          # ascending global id: local mesh order = global order
+
+    def local_id(self, rank, k):
+        return int(np.searchsorted(self.local[rank], k))
+
+    def sends(self, rank):
+        """{peer: [global object ids owned by `rank` that `peer` ghosts, ascending]}"""
+        out = {}
+        for q in range(self.world):
+            if q == rank:
+                continue
+            ks = [int(k) for k in self.local[q] if self.owner[k] == rank]
+            if ks:
+                out[q] = ks
+        return out
+
+    def recvs(self, rank):
+        """{peer: [global object ids owned by `peer` that `rank` ghosts, ascending]}"""
+        out = {}
+        for k in self.local[rank]:
+            q = int(self.owner[k])
+            if q != rank:
+                out.setdefault(q, []).append(int(k))
+        return out
+
+
+def add_sharded_meshes(scene, meshes, sharding, rank):
+    """Adds the local objects (owned + ghosts) of `rank` in global order; returns the list of global ids added."""
+    arranged = global_groups([m[3] for m in meshes])
+    scene.set_partition_mode(rank, sharding.world)
+    for k in sharding.local[rank]:
+        v, t, obj, _, fixed = meshes[k]
+        mesh = scene.add_tet_mesh(v, t, obj, arranged[k], fixed)
+        if sharding.owner[k] != rank:
+            scene.set_ghosts(mesh, np.arange(len(v), dtype=np.int32))
+    return sharding.local[rank]
+
+
+def build_object_sharded_scene(wl, rank, world, local_rank, margin=None):
+    """bench.py / tests: the many-object workload `wl` sharded by object over `world` GPUs.
+    Requires an initialised torch.distributed process group (used at set-up only)."""
+    import torch.distributed as dist
+    from . import capi, meshio
+    meshes = wl["meshes"]
+    boxes = object_boxes(meshes, meshio.place)
+    if margin is None:
+        margin = 0.25 * float(np.median(boxes[:, 1] - boxes[:, 0]))
+    sh = ObjectSharding(boxes, world, margin)
+    s = capi.Scene(wl["phys"], wl["col"], device=local_rank)
+    add_sharded_meshes(s, meshes, sh, rank)
+    s.finalize()
+    s.sharding = sh
+    recv = sh.recvs(rank)
+    mine = {"handles": s.halo_ipc_handles(),
+            "ghost_slots": {q: np.concatenate([s.sorted_ids(sh.local_id(rank, k), np.arange(len(meshes[k][0]), dtype=np.int32)) for k in ks])
+                            for q, ks in recv.items()}}
+    everyone = [None] * world
+    dist.all_gather_object(everyone, mine)
+    for q, ks in sorted(sh.sends(rank).items()):
+        mv = np.concatenate([np.stack([np.full(len(meshes[k][0]), sh.local_id(rank, k), np.int32), np.arange(len(meshes[k][0]), dtype=np.int32)], 1)
+                             for k in ks])
+        remote = everyone[q]["ghost_slots"][rank]
+        assert len(remote) == len(mv), (rank, q, len(remote), len(mv))
+        s.halo_add_peer(q, everyone[q]["handles"], mv, remote)
+    s.halo_finalize()
+    dist.barrier()
+    return s

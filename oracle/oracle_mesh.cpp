@@ -223,7 +223,8 @@ void scene_finalize(Scene& s) {
             // findSmallestParallelGroup(available, groups, remove=true) (VBDPhysics.cpp:99-122)
             size_t best = s.vertexParallelGroups[available[0]].size();
             int bestId = available[0]; size_t bestI = 0;
-            for (size_t i = 1; i < available.size(); i++)
+            // (a partition keeps the global group of each colour = the colour's index: oracle_set_partition_mode)
+            for (size_t i = 1; i < available.size() && !s.keepColourOrder; i++)
                 if (s.vertexParallelGroups[available[i]].size() < best) {
                     best = s.vertexParallelGroups[available[i]].size(); bestId = available[i]; bestI = i;
                 }

@@ -121,3 +121,131 @@ def test_partitioned_oracle_equals_single_bit_exact(tmp_path, world):
     assert seen.all()
     assert np.abs(ref - verts).max() > 1e-3          # something moved
     assert np.array_equal(got, ref)
+
+
+# ------------------------------------------------------------------------------------------------ many-object sharding
+def _pile_workload():
+    """Six blocks in three columns (two stacked per column, columns overlapping sideways): contacts inside a column and
+    across columns, so that with 2-3 ranks there are contacts between objects of different owners."""
+    meshes = []
+    shapes = [(3, 2, 2, 0.25), (2, 2, 3, 0.22), (3, 3, 2, 0.2)]
+    for col_ in range(3):
+        y = 0.25
+        for lvl in range(2):
+            nx, ny, nz, h = shapes[(col_ + lvl) % 3]
+            v, t = meshio.kuhn_beam(nx, ny, nz, h=h, origin=(0.0, 0.0, 0.0))
+            colors = meshio.kuhn_coloring(nx, ny, nz) if (col_ + lvl) % 2 == 0 else meshio.greedy_coloring(len(v), t)
+            i = 2 * col_ + lvl
+            obj = capi.default_object_params(miu=1e5 * (1 + 0.3 * i), lmbd=1e6, density=50 + 5 * i, frictionDynamic=0.2 + 0.05 * i,
+                                             translation=[0.62 * col_ + 0.03 * lvl, y, 0.05 * lvl], rotation=[0.0, 0.1 * i, 0.03 * i],
+                                             initialVelocity=[0.1 * (1 - col_), -2.0 - lvl, 0.05 * i])
+            meshes.append((v, t, obj, colors, np.zeros(0, np.int32)))
+            y += ny * h - 0.06
+    phys = capi.default_physics_params(numSubsteps=2, iterations=5, worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10],
+                                       collisionStiffness=1e5)
+    col = capi.default_collision_params(allowDCD=1, allowCCD=1)
+    return dict(meshes=meshes, phys=phys, col=col)
+
+
+def test_global_groups_restate_the_merge():
+    from oracle.binding import OracleScene
+    wl = _pile_workload()
+    o = OracleScene(wl["phys"], wl["col"], threads=1)
+    for v, t, obj, colors, fixed in wl["meshes"]:
+        o.add_tet_mesh(v, t, obj, colors, fixed)
+    o.finalize()
+    groups = o.parallel_groups()
+    arranged = multigpu.global_groups([m[3] for m in wl["meshes"]])
+    assert all(len(a) == len(groups) for a in arranged)
+    for g, pairs in enumerate(groups):
+        want = np.concatenate([np.stack([np.full(len(a[g]), k, np.int32), a[g]], 1) for k, a in enumerate(arranged)])
+        assert np.array_equal(pairs, want)
+
+
+def test_object_sharding_tables():
+    wl = _pile_workload()
+    boxes = multigpu.object_boxes(wl["meshes"], meshio.place)
+    for world in (2, 3):
+        sh = multigpu.ObjectSharding(boxes, world, margin=0.05)
+        assert sorted(np.concatenate([np.nonzero(sh.owner == r)[0] for r in range(world)]).tolist()) == list(range(6))
+        for r in range(world):
+            assert (sh.tier[r][sh.owner == r] == 0).all()
+            for q, ks in sh.sends(r).items():
+                assert ks == sh.recvs(q)[r]
+        # an object touching an owned object is always local
+        sh0 = multigpu.ObjectSharding(boxes, world, margin=0.05)
+        assert all(len(l) >= 2 for l in sh0.local)
+
+
+def _pile_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from oracle.binding import OracleScene
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    wl = _pile_workload()
+    meshes = wl["meshes"]
+    sh = multigpu.ObjectSharding(multigpu.object_boxes(meshes, meshio.place), world, margin=0.05)
+    o = OracleScene(wl["phys"], wl["col"], threads=1)
+    multigpu.add_sharded_meshes(o, meshes, sh, rank)
+    o.finalize()
+    groups = o.parallel_groups()
+    sends = sh.sends(rank)
+
+    def exchange(g):
+        msg = {}
+        for q, ks in sends.items():
+            items = []
+            for k in ks:
+                lm = sh.local_id(rank, k)
+                pos = o.positions(lm)
+                sel = np.arange(len(pos)) if g < 0 else groups[g][groups[g][:, 0] == lm][:, 1]
+                items.append((k, sel, pos[sel]))
+            msg[q] = items
+        everyone = [None] * world
+        dist.all_gather_object(everyone, msg)
+        for src, m in enumerate(everyone):
+            if src == rank or rank not in m:
+                continue
+            for k, sel, p in m[rank]:
+                lm = sh.local_id(rank, k)
+                pos = o.positions(lm)
+                pos[sel] = p
+                o.set_state(lm, pos, None)
+
+    for frame in range(4):
+        for sub in range(wl["phys"].numSubsteps):
+            o.phase_begin_substep()
+            exchange(-1)
+            o.phase_prepare()
+            for it in range(wl["phys"].iterations):
+                for g in range(len(groups)):
+                    o.phase_solve_group(g, True)
+                    exchange(g)
+            o.phase_end_substep()
+    out = {int(k): o.positions(sh.local_id(rank, k)) for k in sh.local[rank] if sh.owner[k] == rank}
+    np.save(os.path.join(out_dir, f"pile_rank{rank}.npy"), np.array([out], dtype=object), allow_pickle=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_object_sharded_oracle_equals_single_bit_exact(tmp_path, world):
+    import torch.multiprocessing as mp
+    from oracle.binding import OracleScene
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    mp.spawn(_pile_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    wl = _pile_workload()
+    o = OracleScene(wl["phys"], wl["col"], threads=1)
+    for v, t, obj, colors, fixed in wl["meshes"]:
+        o.add_tet_mesh(v, t, obj, colors, fixed)
+    o.finalize()
+    o.run_frames(4)
+    assert len(o.contacts()) > 0                       # the scene really is in contact
+    seen = set()
+    for r in range(world):
+        d = np.load(tmp_path / f"pile_rank{r}.npy", allow_pickle=True)[0]
+        for k, p in d.items():
+            assert np.array_equal(p, o.positions(k)), (r, k, np.abs(p - o.positions(k)).max())
+            seen.add(k)
+    assert seen == set(range(6))
