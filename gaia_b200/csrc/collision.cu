@@ -797,27 +797,19 @@ __global__ void k_prepare(int nSlots, const int32_t* __restrict__ cNum, const in
     }
 }
 
-// relations of a vertex in ascending (contact slot, vertex order): the order the CPU path pushes them in
-__global__ void k_sort_relations(int nContactsSlots, const int32_t* __restrict__ cNum, const int32_t* __restrict__ cFlags, const int32_t* __restrict__ cFace,
-                                 const int4* __restrict__ faceSid, const int32_t* __restrict__ relOff, int2* rel) {
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= nContactsSlots) return;
-    if (!cNum[slot] || !(cFlags[slot] & 2)) return;
-    const int4 fv = __ldg(faceSid + cFace[slot]);
-    const int fvs[3] = {fv.x, fv.y, fv.z};
-    for (int k = 0; k < 3; k++) {
-        const int b = relOff[fvs[k]], e = relOff[fvs[k] + 1];
-        if (e - b < 2) continue;
-        // the thread holding the smallest (slot,k) of the segment sorts it; every segment is sorted exactly once
-        int2 mn = rel[b];
-        for (int q = b + 1; q < e; q++) { const int2 r = rel[q]; if (r.x < mn.x || (r.x == mn.x && r.y < mn.y)) mn = r; }
-        if (mn.x != slot || mn.y != k) continue;
-        for (int i = b + 1; i < e; i++) {
-            const int2 key = rel[i];
-            int j = i - 1;
-            while (j >= b && (rel[j].x > key.x || (rel[j].x == key.x && rel[j].y > key.y))) { rel[j + 1] = rel[j]; j--; }
-            rel[j + 1] = key;
-        }
+// relations of a vertex in ascending (contact slot, vertex order): the order the CPU path pushes them in.
+// One thread per vertex owns its segment (an earlier version let "the contact holding the smallest entry" sort the segment:
+// other contacts scanned it for the minimum WHILE it was being shifted, could elect themselves as well, and corrupted it).
+__global__ void k_sort_relations(int nVerts, const int32_t* __restrict__ relOff, int2* rel) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nVerts) return;
+    const int b = relOff[v], e = relOff[v + 1];
+    if (e - b < 2) return;
+    for (int i = b + 1; i < e; i++) {
+        const int2 key = rel[i];
+        int j = i - 1;
+        while (j >= b && (rel[j].x > key.x || (rel[j].x == key.x && rel[j].y > key.y))) { rel[j + 1] = rel[j]; j--; }
+        rel[j + 1] = key;
     }
 }
 __global__ void k_group_offsets(int G, const int32_t* __restrict__ groupCount, int32_t* groupOff) {
@@ -856,7 +848,7 @@ cudaError_t collision_prepare(Scene& s) {
     k_prepare<1><<<nblk(nS), kB, 0, s.stream>>>(nS, c->cNum.p, c->cFace.p, c->cFlags.p, c->surfSid.p, c->faceSid.p, c->groupStart.p, G,
                                               c->contactOfVertex.p, c->relCount.p, c->relOff.p, c->rel.p, c->colliding.p, c->groupCount.p,
                                               c->groupOff.p, c->groupList.p);
-    k_sort_relations<<<nblk(nS), kB, 0, s.stream>>>(nS, c->cNum.p, c->cFlags.p, c->cFace.p, c->faceSid.p, c->relOff.p, c->rel.p);
+    k_sort_relations<<<nblk(N, 256), 256, 0, s.stream>>>((int)N, c->relOff.p, c->rel.p);
     s.stats.kernelLaunches += 4;
     return cudaGetLastError();
 }

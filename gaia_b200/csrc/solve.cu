@@ -796,7 +796,12 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             }
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
-            else if (halo) CK(halo_push(s, g));
+            else if (halo) {
+                // with contacts the pre-pass of this colour read ghost positions of EVERY colour: a neighbour that is ahead
+                // must not overwrite them before this rank has finished it -> barrier among neighbours, then push + wait
+                if (s.cs) CK(halo_sync(s));
+                CK(halo_push(s, g));
+            }
         }
         s.stats.vertexSolves += solvedPerIter;
         s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);

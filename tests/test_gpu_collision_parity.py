@@ -148,3 +148,23 @@ def test_intermediate_collision_detection_and_accelerator():
         s.run_frames(6)
     for i in range(2):
         assert np.abs(g.positions(i) - o.positions(i)).max() < 2e-3
+
+
+@pytest.mark.gpu
+def test_contact_runs_are_bit_deterministic():
+    """Two runs of the same stacked-contact scene give identical bits (a race in the relation sort once made vertices that
+    sit on several contact faces accumulate their face-side terms in a run-dependent order)."""
+    from gaia_b200 import capi
+    from conftest import make_contact_scene
+    runs = []
+    for rep in range(2):
+        g = make_contact_scene(capi.Scene, n_objects=4, substeps=2, iterations=6)
+        hist = []
+        for f in range(25):
+            g.run_frames(1)
+            hist.append(np.concatenate([g.positions(m) for m in range(4)]))
+        assert g.stats()["numContactsDCD"] + g.stats()["numContactsCCD"] > 0
+        runs.append(hist)
+        g.close()
+    for a, b in zip(*runs):
+        assert np.array_equal(a, b)
