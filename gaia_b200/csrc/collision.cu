@@ -575,74 +575,106 @@ __device__ bool tet_traverse(const float4* __restrict__ pos, const TopoView& tp,
     return false;
 }
 
-// DCD phase 2 (closestPointQuery + closestPointQueryFunc, rule R2) for the vertices phase 1 found inside a tet
+// DCD phase 2 (closestPointQuery + closestPointQueryFunc, rule R2) for the vertices phase 1 found inside a tet.
+// ONE WARP PER HIT. The query is long and data-dependent: without the reference's Embree-order-dependent cap on visited
+// candidates (rule R2 drops it), a vertex whose nearby faces all fail the feasibility / traversal tests walks through
+// hundreds of candidate faces, each with its own tetrahedral traversal (measured: 8 ms for a few thousand hits with one
+// thread per hit). Here all lanes run the nearest-first BVH descent redundantly (uniform control flow, shared stack),
+// collect up to 32 candidate leaves, then each lane evaluates ONE candidate; the best (smallest distance, ties -> smallest
+// face id) is reduced over the warp and shrinks the search radius for the rest of the descent. The result is the minimum
+// over all acceptable faces, independent of the visiting order, i.e. identical to the sequential query.
 __global__ void __launch_bounds__(kB)
 k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitList, ColParamsDev cp, BvhView bv, const int2* __restrict__ segRange,
              TopoView tp, const int32_t* __restrict__ surfSid, const int32_t* __restrict__ surfMesh, const int32_t* __restrict__ tetMesh,
              const float4* __restrict__ pos, const int32_t* __restrict__ cHitTet, int32_t* cFace, int32_t* cFlags, int32_t* errFlags) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= *nHits) return;
+    __shared__ int sStack[kB / 32][kStack];
+    __shared__ int sCand[kB / 32][32];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= *nHits) return;                       // whole warps leave together
+    const unsigned full = 0xffffffffu;
     const int slot = hitList[i];
     const int meshQ = surfMesh[slot];
     const int sQ = surfSid[slot];
     const V3 q = v3(pos[sQ]);
     const int embraceTet = cHitTet[slot];
     const int g = tetMesh[embraceTet];
-    float radius = __int_as_float(0x7f800000);
+    const float kInf = __int_as_float(0x7f800000);
+    float radius = kInf;
     int bestFace = -1, bestType = NotFound;
     const int2 seg = segRange[g];
+    V3 target = q;
+    if (cp.shiftQueryToCenter) {
+        const int4 tv = __ldg(tp.tetSid + embraceTet);
+        V3 cen = (((v3(0.f, 0.f, 0.f) + v3(pos[tv.x])) + v3(pos[tv.y])) + v3(pos[tv.z])) + v3(pos[tv.w]);
+        cen = cen * 0.25f;
+        target = (1.f - cp.centerShiftLevel) * q + cp.centerShiftLevel * cen;
+    }
     if (seg.y > seg.x) {
-        int stack[kStack];
         int sp = 0;
-        stack[sp++] = (seg.y - seg.x > 1) ? seg.x : bv.n + seg.x;
-        while (sp) {
-            const int node = stack[--sp];
-            const float r2 = radius == __int_as_float(0x7f800000) ? 1e30f : radius * radius * 1.0001f + 1e-12f;
-            if (box_dist2(bv.lo[node], bv.hi[node], q) > r2) continue;
-            if (node >= bv.n) {
-                const int face = bv.order[node - bv.n];
+        sStack[w][sp++] = (seg.y - seg.x > 1) ? seg.x : bv.n + seg.x;
+        __syncwarp();
+        for (;;) {
+            int nCand = 0;
+            while (sp > 0 && nCand < 32) {
+                const int node = sStack[w][--sp];
+                const float r2 = radius == kInf ? 1e30f : radius * radius * 1.0001f + 1e-12f;
+                if (box_dist2(bv.lo[node], bv.hi[node], q) > r2) continue;
+                if (node >= bv.n) { sCand[w][nCand++] = bv.order[node - bv.n]; continue; }
+                const int2 ch = bv.child[node];
+                if (sp + 2 > kStack) { if (lane == 0) atomicAdd(errFlags + 3, 1); continue; }
+                // nearer child on top of the stack: the radius shrinks sooner
+                const float dx = box_dist2(bv.lo[ch.x], bv.hi[ch.x], q), dy = box_dist2(bv.lo[ch.y], bv.hi[ch.y], q);
+                __syncwarp();
+                if (dx <= dy) { sStack[w][sp++] = ch.y; sStack[w][sp++] = ch.x; } else { sStack[w][sp++] = ch.x; sStack[w][sp++] = ch.y; }
+                __syncwarp();
+            }
+            __syncwarp();
+            if (nCand == 0) break;
+            // ---- one candidate per lane
+            float myD = kInf; int myFace = 0x7FFFFFFF, myType = NotFound;
+            if (lane < nCand) {
+                const int face = sCand[w][lane];
                 const int4 fv = __ldg(tp.faceSid + face);
                 const V3 a = v3(pos[fv.x]), b = v3(pos[fv.y]), c = v3(pos[fv.z]);
                 int type; V3 bary;
                 const V3 cpnt = closest_point_triangle(q, a, b, c, bary, type);
                 const float d = norm(q - cpnt);
+                bool ok = true;
                 if (g == meshQ) {
                     int cpId = -1;
                     if (type == AtA) cpId = fv.x; else if (type == AtB) cpId = fv.y; else if (type == AtC) cpId = fv.z;
-                    if (cpId != -1 && cpId == sQ) continue;
+                    if (cpId != -1 && cpId == sQ) ok = false;
                 }
-                if (!(d < radius || (d == radius && bestFace >= 0 && face < bestFace))) continue;
-                if (cp.checkFeasibleRegion && !feasible_region(q, pos, tp, face, fv, type, cp.feasibleEps)) continue;
-                if (cp.checkTetTraverse && (g == meshQ || cp.traverseNonSelf)) {
+                if (ok && !(d < radius || (d == radius && bestFace >= 0 && face < bestFace))) ok = false;
+                if (ok && cp.checkFeasibleRegion && !feasible_region(q, pos, tp, face, fv, type, cp.feasibleEps)) ok = false;
+                if (ok && cp.checkTetTraverse && (g == meshQ || cp.traverseNonSelf)) {
                     V3 tracing;
                     if (type == AtInterior) tracing = cpnt;
                     else tracing = cpnt * (1.f - cp.centerShiftLevel) + (cp.centerShiftLevel / 3.0f) * ((a + b) + c);
-                    V3 target;
-                    if (cp.shiftQueryToCenter) {
-                        const int4 tv = __ldg(tp.tetSid + embraceTet);
-                        V3 cen = (((v3(0.f, 0.f, 0.f) + v3(pos[tv.x])) + v3(pos[tv.y])) + v3(pos[tv.z])) + v3(pos[tv.w]);
-                        cen = cen * 0.25f;
-                        target = (1.f - cp.centerShiftLevel) * q + cp.centerShiftLevel * cen;
-                    } else target = q;
                     V3 dir = target - tracing;
                     const float len = norm(dir);
                     dir = dir / len;
                     const float maxDis = cp.stopAfterPassing ? cp.maxSearchMult * len : -1.f;
                     const int4 fi = __ldg(tp.faceInfo + face);
-                    if (!tet_traverse(pos, tp, tracing, dir, maxDis, fi.x, fi.y, embraceTet, cp.rayEps, errFlags)) continue;
+                    if (!tet_traverse(pos, tp, tracing, dir, maxDis, fi.x, fi.y, embraceTet, cp.rayEps, errFlags)) ok = false;
                 }
-                radius = d; bestFace = face; bestType = type;
-            } else {
-                const int2 ch = bv.child[node];
-                if (sp + 2 > kStack) { atomicAdd(errFlags + 3, 1); continue; }
-                // nearer child on top of the stack: the radius shrinks sooner
-                const float dx = box_dist2(bv.lo[ch.x], bv.hi[ch.x], q), dy = box_dist2(bv.lo[ch.y], bv.hi[ch.y], q);
-                if (dx <= dy) { stack[sp++] = ch.y; stack[sp++] = ch.x; } else { stack[sp++] = ch.x; stack[sp++] = ch.y; }
+                if (ok) { myD = d; myFace = face; myType = type; }
             }
+            __syncwarp();
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float od = __shfl_xor_sync(full, myD, o);
+                const int of = __shfl_xor_sync(full, myFace, o), ot = __shfl_xor_sync(full, myType, o);
+                if (od < myD || (od == myD && of < myFace)) { myD = od; myFace = of; myType = ot; }
+            }
+            if (myFace != 0x7FFFFFFF) { radius = myD; bestFace = myFace; bestType = myType; }
         }
     }
-    if (bestFace >= 0) { cFace[slot] = bestFace; cFlags[slot] = 2 | (bestType << 8); }
-    else { cFace[slot] = -1; cFlags[slot] = (NotFound << 8); }
+    if (lane == 0) {
+        if (bestFace >= 0) { cFace[slot] = bestFace; cFlags[slot] = 2 | (bestType << 8); }
+        else { cFace[slot] = -1; cFlags[slot] = (NotFound << 8); }
+    }
 }
 
 // CCD (vertexContinuousCollisionDetection + continuousTriPointIntersectionFunc, rule R3)
@@ -728,8 +760,9 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
         CK(cudaMemcpyAsync(&hits, nHits, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CK(cudaStreamSynchronize(s.stream));
         if (hits > 0)
-            k_dcd_phase2<<<nblk(hits), kB, 0, s.stream>>>(nHits, c->hitList.p, c->cp, view_of(c->surfBvh), c->surfBvh.segRange.p, tp, c->surfSid.p,
-                                                        c->surfMesh.p, c->tetMesh.p, s.pos.p, c->cHitTet.p, c->cFace.p, c->cFlags.p, s.errFlags.p);
+            k_dcd_phase2<<<nblk((int64_t)hits * 32), kB, 0, s.stream>>>(nHits, c->hitList.p, c->cp, view_of(c->surfBvh), c->surfBvh.segRange.p, tp,
+                                                                      c->surfSid.p, c->surfMesh.p, c->tetMesh.p, s.pos.p, c->cHitTet.p, c->cFace.p,
+                                                                      c->cFlags.p, s.errFlags.p);
         s.stats.kernelLaunches += 2;
     } else if (s.col.allowCCD && !intermediate) {
         k_clear_results<<<nblk(nS), kB, 0, s.stream>>>(nS, c->cNum.p, c->cHitTet.p, c->cFace.p, c->cFlags.p);

@@ -159,11 +159,12 @@ def test_contact_runs_are_bit_deterministic():
     runs = []
     for rep in range(2):
         g = make_contact_scene(capi.Scene, n_objects=4, substeps=2, iterations=6)
-        hist = []
+        hist, most = [], 0
         for f in range(25):
             g.run_frames(1)
             hist.append(np.concatenate([g.positions(m) for m in range(4)]))
-        assert g.stats()["numContactsDCD"] + g.stats()["numContactsCCD"] > 0
+            most = max(most, g.stats()["numContactsDCD"] + g.stats()["numContactsCCD"])
+        assert most > 0
         runs.append(hist)
         g.close()
     for a, b in zip(*runs):
