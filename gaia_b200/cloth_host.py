@@ -1,0 +1,153 @@
+"""Host side of the cloth path for scenes in the reference's own file formats: the cloth `Models.json` / `Parameters.json`
+(S/VBDCloth/ParameterGen, e.g. S03_MultiLayerClothOnCollider.py), `.obj` meshes and `*.vertexColoring*.json` colourings.
+
+    python -m gaia_b200.cloth_host Models.json Parameters.json outFolder [-R repoRoot] [--frames N]
+
+Mirrors what BaseClothPhsicsFramework does around the step (M/Framework/BaseClothSimPhsicsFramework.cpp: loadRunningparameters,
+initialize, simulate, writeOutputs): parameters keep the reference's names, meshes are loaded in file order (simulated
+models, a collider being a model whose vertices are all fixed, as S03 does it), frames are written as `A%08d.ply`
+(all meshes together, ASCII) or `A%08d.bin` (raw float32 positions). Not handled here, and refused loudly: `Deformers`
+(they move fixed vertices every substep) and `ColliderParams` mesh sequences.
+"""
+import argparse
+import json
+import os
+
+import numpy as np
+
+from . import cloth, meshio
+
+
+def load_obj(path):
+    """Triangle .obj: `v x y z` and `f a b c` (with or without /vt/vn); returns (verts float32 [n,3], faces int32 [m,3])."""
+    verts, faces = [], []
+    with open(path) as f:
+        for line in f:
+            if line.startswith("v "):
+                p = line.split()
+                verts.append((float(p[1]), float(p[2]), float(p[3])))
+            elif line.startswith("f "):
+                ids = [int(tok.split("/")[0]) for tok in line.split()[1:]]
+                if len(ids) != 3:
+                    raise ValueError(f"{path}: only triangle faces are supported")
+                faces.append([i - 1 if i > 0 else len(verts) + i for i in ids])
+    return np.asarray(verts, np.float32), np.asarray(faces, np.int32)
+
+
+def save_obj(path, verts, faces):
+    with open(path, "w") as f:
+        for p in verts:
+            f.write("v %.6f %.6f %.6f\n" % tuple(p))
+        for t in faces:
+            f.write("f %d %d %d\n" % (t[0] + 1, t[1] + 1, t[2] + 1))
+
+
+_PHYS = ("timeStep", "numSubsteps", "iterations", "boundaryFrictionDynamic", "stepSize", "associateGravityWithInertia",
+         "applyAcceleration", "handleCollision", "contactStiffness", "contactRadius", "thickness", "conservativeStepRelaxation",
+         "boundaryContactStiffness", "boundaryFrictionEpsValue", "contactEnergyTypes", "contactBVHReconstructionSteps",
+         "degenerateTriangleThres")
+_OBJ = ("density", "hasNoGravZone", "noGravZoneThreshold", "maxVelocityMagnitude", "frictionDynamic", "frictionEpsV",
+        "bendingStiffness", "exponentialVelDamping", "constantVelDamping", "initializationType", "miu", "lambda", "dampingStVK",
+        "dampingBending")
+
+
+def cloth_physics_params_from_json(j):
+    """PhysicsParams + ContactDetectorParams -> ClothPhysicsParams (absent keys keep the reference's defaults)."""
+    pp = j.get("PhysicsParams", {})
+    kw = {k: (int(pp[k]) if isinstance(pp[k], bool) else pp[k]) for k in _PHYS if k in pp}
+    if "gravity" in pp:
+        kw["gravity"] = pp["gravity"]
+    if "worldBounds" in pp:
+        kw["worldBoundsMin"], kw["worldBoundsMax"] = pp["worldBounds"][0], pp["worldBounds"][1]
+    if "accelerationRho" in pp:            # the scripts write accelerationRho, the struct field is acceleratorRho
+        kw["acceleratorRho"] = pp["accelerationRho"]
+    if "acceleratorRho" in pp:
+        kw["acceleratorRho"] = pp["acceleratorRho"]
+    cd = j.get("ContactDetectorParams", {})
+    if "maxQueryDis" in cd:
+        kw["maxQueryDis"] = cd["maxQueryDis"]
+    return cloth.default_cloth_physics_params(**kw)
+
+
+def cloth_object_params_from_json(m):
+    kw = {k: (int(m[k]) if isinstance(m[k], bool) else m[k]) for k in _OBJ if k in m}
+    for k in ("scale", "rotation", "translation"):
+        if k in m:
+            kw[k] = m[k]
+    return cloth.default_cloth_object_params(**kw)
+
+
+def load_cloth_scene_json(models_json, params_json, repo_root, allow_deformers=False):
+    """-> (ClothPhysicsParams, [(verts, faces, ClothObjectParams, colours, fixedPoints, initialVelocity)], raw parameter dict)"""
+    with open(params_json) as f:
+        pj = json.load(f)
+    with open(models_json) as f:
+        mj = json.load(f)
+    if pj.get("Deformers") and not allow_deformers:
+        raise NotImplementedError("cloth Deformers are outside this host (they move fixed vertices every substep)")
+    if pj.get("ColliderParams", {}).get("ColliderMeshes"):
+        raise NotImplementedError("ColliderParams mesh sequences are outside this host; add the collider as a model with all vertices fixed")
+    phys = cloth_physics_params_from_json(pj)
+    meshes = []
+    for m in mj["Models"]:
+        v, f = load_obj(meshio.resolve_path(m["path"], repo_root))
+        colors = meshio.load_coloring(meshio.resolve_path(m["verticesColoringCategoriesPath"], repo_root))
+        meshes.append((v, f, cloth_object_params_from_json(m), colors, np.asarray(m.get("fixedPoints", []), np.int32),
+                       np.asarray(m.get("initialVelocity", [0, 0, 0]), np.float32)))
+    return phys, meshes, pj
+
+
+def build_scene(cls, phys, meshes, **kw):
+    s = cls(phys, **kw)
+    for v, f, obj, colors, fixed, v0 in meshes:
+        s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=True)
+    s.finalize()
+    for i, (v, f, obj, colors, fixed, v0) in enumerate(meshes):
+        if np.any(v0 != 0):
+            s.set_state(i, None, np.tile(v0, (len(v), 1)))
+    return s
+
+
+def write_frame(scene, meshes, out_dir, frame, ext="ply"):
+    pos = [scene.positions(i) for i in range(len(meshes))]
+    name = os.path.join(out_dir, "A%08d.%s" % (frame, ext))
+    if ext == "bin":
+        np.concatenate(pos).astype(np.float32).tofile(name)
+    else:
+        base, faces = 0, []
+        for p, m in zip(pos, meshes):
+            faces.append(m[1] + base)
+            base += len(p)
+        meshio.write_ply_ascii(name, np.concatenate(pos), np.concatenate(faces))
+    return name
+
+
+def simulate(models_json, params_json, out_dir, repo_root=".", frames=None, device=0):
+    phys, meshes, pj = load_cloth_scene_json(models_json, params_json, repo_root)
+    pp = pj.get("PhysicsParams", {})
+    n = int(pp.get("numFrames", 1)) if frames is None else frames
+    ext = pp.get("outputExt", "ply")
+    os.makedirs(out_dir, exist_ok=True)
+    s = build_scene(cloth.ClothScene, phys, meshes, device=device)
+    write_frame(s, meshes, out_dir, 0, ext)
+    for fr in range(1, n + 1):
+        s.run_frames(1)
+        write_frame(s, meshes, out_dir, fr, ext)
+    st = s.stats()
+    s.close()
+    return st
+
+
+def main():
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("models"); ap.add_argument("parameters"); ap.add_argument("out")
+    ap.add_argument("-R", "--repoRoot", default=".")
+    ap.add_argument("--frames", type=int, default=None)
+    ap.add_argument("--device", type=int, default=0)
+    a = ap.parse_args()
+    st = simulate(a.models, a.parameters, a.out, a.repoRoot, a.frames, a.device)
+    print(json.dumps(st))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,93 @@
+"""The host side of the cloth path reads the reference's cloth scene files (Models.json / Parameters.json, .obj,
+vertexColoring json) — CPU: schema + file formats, with the oracle as the solver; GPU: the same scene through the product."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import has_gpu
+from gaia_b200 import cloth, cloth_host, meshio
+from oracle.binding_cloth import OracleClothScene
+
+
+def write_scene(tmp, n=10, frames=3):
+    v, f = cloth.grid_cloth(n, 1.0)
+    sv, sf = cloth.icosphere(0.25, 1)
+    cloth_host.save_obj(os.path.join(tmp, "sheet.obj"), v, f)
+    cloth_host.save_obj(os.path.join(tmp, "ball.obj"), sv, sf)
+    with open(os.path.join(tmp, "sheet.obj.vertexColoring.json"), "w") as fh:
+        json.dump([c.tolist() for c in cloth.grid_cloth_coloring(n)], fh)
+    with open(os.path.join(tmp, "ball.obj.vertexColoring.json"), "w") as fh:
+        json.dump([c.tolist() for c in cloth.greedy_cloth_coloring(len(sv), sf)], fh)
+    base = {"density": 0.2, "miu": 2000.0, "lambda": 2000.0, "bendingStiffness": 0.5, "dampingStVK": 1e-6, "dampingBending": 1e-6,
+            "initializationType": 2, "scale": [1, 1, 1], "rotation": [0, 0, 0], "hasNoGravZone": False, "materialName": "StVK_triMesh"}
+    models = [dict(base, path="${REPO_ROOT}\\sheet.obj", verticesColoringCategoriesPath="${REPO_ROOT}\\sheet.obj.vertexColoring.json",
+                   translation=[0.0, 0.88, 0.0], fixedPoints=[], initialVelocity=[0.0, -0.5, 0.0]),
+              dict(base, path="${REPO_ROOT}\\ball.obj", verticesColoringCategoriesPath="${REPO_ROOT}\\ball.obj.vertexColoring.json",
+                   translation=[0.0, 0.6, 0.0], fixedPoints=list(range(len(sv))))]
+    params = {"PhysicsParams": {"timeStep": 0.01666666, "numSubsteps": 4, "iterations": 6, "gravity": [0.0, -10.0, 0.0], "numFrames": frames,
+                                "contactStiffness": 1e5, "contactRadius": 0.02, "thickness": 1e-4, "conservativeStepRelaxation": 0.4,
+                                "handleCollision": True, "applyAcceleration": False, "accelerationRho": 0.9, "outputExt": "ply",
+                                "worldBounds": [[-10, -10, -10], [10, 10, 10]]},
+              "ContactDetectorParams": {"maxQueryDis": 0.03}, "ViewerParams": {"enableViewer": False}, "Deformers": []}
+    with open(os.path.join(tmp, "Models.json"), "w") as fh:
+        json.dump({"Models": models}, fh)
+    with open(os.path.join(tmp, "Parameters.json"), "w") as fh:
+        json.dump(params, fh)
+    return os.path.join(tmp, "Models.json"), os.path.join(tmp, "Parameters.json"), (v, f, sv, sf)
+
+
+def test_scene_files_parse_and_drive_the_oracle(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path))
+    phys, meshes, pj = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    assert phys.numSubsteps == 4 and phys.iterations == 6 and phys.handleCollision == 1 and abs(phys.maxQueryDis - 0.03) < 1e-9
+    assert abs(phys.acceleratorRho - 0.9) < 1e-6 and abs(phys.thickness - 1e-4) < 1e-10
+    assert len(meshes) == 2 and np.allclose(meshes[0][0], v, atol=1e-6) and np.array_equal(meshes[0][1], f)
+    assert meshes[0][2].initializationType == 2 and abs(meshes[0][2].lambda_ - 2000.0) < 1e-3
+    assert len(meshes[1][4]) == len(sv) and np.allclose(meshes[0][5], [0, -0.5, 0])
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)
+    x0 = o.positions(0)
+    o.run_frames(3)
+    x = o.positions(0)
+    assert np.isfinite(x).all() and x[:, 1].mean() < x0[:, 1].mean() - 1e-3
+    assert np.allclose(o.positions(1), sv + np.float32([0, 0.6, 0]), atol=2e-6)      # the collider stays (.obj keeps 6 decimals)
+    out = cloth_host.write_frame(o, meshes, str(tmp_path), 3, "ply")
+    head = open(out).read(400)
+    assert "element vertex %d" % (len(v) + len(sv)) in head and "element face %d" % (len(f) + len(sf)) in head
+    out = cloth_host.write_frame(o, meshes, str(tmp_path), 3, "bin")
+    assert os.path.getsize(out) == 12 * (len(v) + len(sv))
+
+
+def test_deformers_are_refused_loudly(tmp_path):
+    m, p, _ = write_scene(str(tmp_path))
+    pj = json.load(open(p))
+    pj["Deformers"] = [{"DeformerName": "Rotator"}]
+    json.dump(pj, open(p, "w"))
+    with pytest.raises(NotImplementedError):
+        cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+
+
+@pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
+def test_reference_cloth_experiment_files_parse():
+    d = ("/root/reference/Simulator/VBDCloth/ParameterGen/Parameters/S01_Twisting/"
+         "C100_Twist_ContactR0.2_CStif100000.0_bd20_damping3e-05_relaxiation0.42_thick0.01_CDPerIter")
+    phys, meshes, pj = cloth_host.load_cloth_scene_json(d + "/Models.json", d + "/Parameters.json", "/root/reference", allow_deformers=True)
+    assert phys.numSubsteps == 5 and phys.iterations == 10 and abs(phys.contactRadius - 0.2) < 1e-7 and abs(phys.maxQueryDis - 0.3) < 1e-7
+    v, f, obj, colors, fixed, v0 = meshes[0]
+    assert v.shape == (10000, 3) and f.shape == (19602, 3) and abs(obj.bendingStiffness - 20) < 1e-6 and obj.initializationType == 2
+    assert sum(len(c) for c in colors) == 10000 and cloth.check_cloth_coloring(10000, f, colors)
+    assert len(pj["Deformers"]) == 2
+
+
+@pytest.mark.gpu
+def test_gpu_scene_from_files_matches_the_oracle(tmp_path):
+    m, p, _ = write_scene(str(tmp_path))
+    st = cloth_host.simulate(m, p, str(tmp_path / "out"), str(tmp_path), frames=3)
+    assert st["frames"] == 3 and st["numberCollisionDetection"] >= 12
+    assert sorted(os.listdir(tmp_path / "out")) == ["A%08d.ply" % i for i in range(4)]
+    phys, meshes, _ = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    g = cloth_host.build_scene(cloth.ClothScene, phys, meshes)
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)
+    g.run_frames(3); o.run_frames(3)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 1e-4
