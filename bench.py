@@ -364,6 +364,8 @@ def main():
     nV = scene.total_vertices
     pos_h = scene.all_positions()
     vel_h = np.zeros_like(pos_h)
+    if not is_cloth(wl):                      # the step's host buffers are page-locked once, as the reference does with its Eigen storage
+        scene.register_host_buffer(pos_h); scene.register_host_buffer(vel_h)
 
     def e2e_step():
         scene.set_all_state(pos_h, vel_h)     # H2D of this step's inputs (pinned staging inside the library)

@@ -398,6 +398,22 @@ class Scene(SceneBase):
     def set_all_state(self, pos, vel):
         self._call("set_all_state", _fp(pos), _fp(vel))
 
+    def register_host_buffer(self, arr):
+        """Page-lock a C-contiguous numpy array: get / set calls on it then DMA without the staging copy. Keep `arr` alive."""
+        assert arr.flags["C_CONTIGUOUS"]
+        fn = self._lib.gaia_b200_register_host_buffer
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        rc = fn(self.h, arr.ctypes.data, arr.nbytes)
+        if rc < 0:
+            raise GaiaError(f"gaia_b200_register_host_buffer failed: {rc} {self.last_error()}")
+
+    def unregister_host_buffer(self, arr):
+        fn = self._lib.gaia_b200_unregister_host_buffer
+        fn.argtypes = [C.c_void_p, C.c_void_p]
+        rc = fn(self.h, arr.ctypes.data)
+        if rc < 0:
+            raise GaiaError(f"gaia_b200_unregister_host_buffer failed: {rc} {self.last_error()}")
+
     def sorted_ids(self, mesh, verts):
         v = _i32(verts); out = np.empty(len(v), np.int32)
         self._call("get_sorted_ids", mesh, _ip(v), len(v), _ip(out))

@@ -256,6 +256,29 @@ int gaia_b200_set_all_state(gaia_handle* h, const float* pos, const float* vel) 
     return GAIA_OK;
 }
 
+int gaia_b200_register_host_buffer(gaia_handle* h, void* ptr, int64_t bytes) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (!ptr || bytes <= 0) return fail(s, GAIA_ERR_INVALID_ARG, "bad host buffer");
+    cudaSetDevice(s.device);
+    cudaError_t e = cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    s.hostRegs.push_back({(char*)ptr, (size_t)bytes});
+    return GAIA_OK;
+}
+int gaia_b200_unregister_host_buffer(gaia_handle* h, void* ptr) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    for (size_t i = 0; i < s.hostRegs.size(); i++)
+        if (s.hostRegs[i].first == (char*)ptr) {
+            if (s.stream) cudaStreamSynchronize(s.stream);
+            cudaHostUnregister(ptr);
+            s.hostRegs.erase(s.hostRegs.begin() + i);
+            return GAIA_OK;
+        }
+    return fail(s, GAIA_ERR_INVALID_ARG, "buffer was not registered");
+}
+
 int gaia_b200_get_world_bounds(const gaia_handle* h, float* mn, float* mx) {
     REQUIRE(h);
     for (int d = 0; d < 3; d++) { mn[d] = h->s.phys.worldBoundsMin[d]; mx[d] = h->s.phys.worldBoundsMax[d]; }

@@ -110,6 +110,7 @@ struct Scene {
     bool meshParamsDirty = true;
     StepParamsDev stepParams;
     float* pinnedIO = nullptr;
+    std::vector<std::pair<char*, size_t>> hostRegs;   // caller buffers page-locked with register_host_buffer
     size_t pinnedIOBytes = 0;
 
     CollisionState* cs = nullptr;

@@ -23,6 +23,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 namespace gb {
 
@@ -580,6 +581,7 @@ Scene::~Scene() {
     halo_destroy(*this);
     collision_destroy(*this);
     for (Deformer* d : deformers) delete d;
+    for (auto& r : hostRegs) cudaHostUnregister(r.first);
     if (pinnedIO) cudaFreeHost(pinnedIO);
     if (iterGraphExec) cudaGraphExecDestroy(iterGraphExec);
     if (evA) cudaEventDestroy(evA);
@@ -977,13 +979,40 @@ cudaError_t run_iterations_only(Scene& s, int nIters) {
     return cudaGetLastError();
 }
 
+// host <-> pinned staging copies of tens of MB: split over a few threads (one memcpy thread moves ~8 GB/s, which would make
+// the staging copy, not PCIe, the cost of get/set on a 10 M-tet scene)
+static void par_memcpy(void* dst, const void* src, size_t bytes) {
+    const size_t kMin = (size_t)2 << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<size_t>(std::min<size_t>(8, hw ? hw : 1), bytes / kMin);
+    if (nt <= 1) { std::memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    const size_t per = ((bytes / nt) + 63) & ~(size_t)63;
+    for (int i = 0; i < nt; i++) {
+        const size_t b = per * i, e = std::min(bytes, b + per);
+        if (b >= e) break;
+        th.emplace_back([=] { std::memcpy((char*)dst + b, (const char*)src + b, e - b); });
+    }
+    for (auto& t : th) t.join();
+}
+
+static bool host_registered(const Scene& s, const void* p, size_t bytes) {
+    for (auto& r : s.hostRegs) if ((const char*)p >= r.first && (const char*)p + bytes <= r.first + r.second) return true;
+    return false;
+}
+
 cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin, int64_t count, float* outXYZ) {
     if (!count) return cudaSuccess;
     float* stage = (float*)s.ioStage.p;
     k_gather_xyz<<<nblk(count), kBlock, 0, s.stream>>>(count, origBegin, devSorted, s.orig2sorted.p, stage);
-    CK(cudaMemcpyAsync(s.pinnedIO, stage, 3 * count * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-    CK(cudaStreamSynchronize(s.stream));
-    std::memcpy(outXYZ, s.pinnedIO, 3 * count * sizeof(float));
+    if (host_registered(s, outXYZ, 3 * count * sizeof(float))) {
+        CK(cudaMemcpyAsync(outXYZ, stage, 3 * count * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+    } else {
+        CK(cudaMemcpyAsync(s.pinnedIO, stage, 3 * count * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+        par_memcpy(outXYZ, s.pinnedIO, 3 * count * sizeof(float));
+    }
     s.stats.kernelLaunches++;
     return cudaSuccess;
 }
@@ -991,8 +1020,12 @@ cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin,
 cudaError_t scatter_from_host(Scene& s, float4* devSorted, int64_t origBegin, int64_t count, const float* inXYZ, bool) {
     if (!count) return cudaSuccess;
     float* stage = (float*)s.ioStage.p;
-    std::memcpy(s.pinnedIO, inXYZ, 3 * count * sizeof(float));
-    CK(cudaMemcpyAsync(stage, s.pinnedIO, 3 * count * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    if (host_registered(s, inXYZ, 3 * count * sizeof(float))) {
+        CK(cudaMemcpyAsync(stage, inXYZ, 3 * count * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    } else {
+        par_memcpy(s.pinnedIO, inXYZ, 3 * count * sizeof(float));
+        CK(cudaMemcpyAsync(stage, s.pinnedIO, 3 * count * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    }
     k_scatter_xyz<<<nblk(count), kBlock, 0, s.stream>>>(count, origBegin, devSorted, s.orig2sorted.p, stage);
     CK(cudaStreamSynchronize(s.stream));
     s.stats.kernelLaunches++;

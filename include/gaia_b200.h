@@ -234,6 +234,12 @@ int gaia_b200_get_surface_positions(gaia_handle* h, int mesh, float* xyz);
 int64_t gaia_b200_total_vertices(const gaia_handle* h);
 int gaia_b200_get_all_positions(gaia_handle* h, float* xyz);
 int gaia_b200_set_all_state(gaia_handle* h, const float* pos, const float* vel);
+/* Page-lock a caller buffer (cudaHostRegister) so that get / set calls whose pointer lies inside it DMA straight from / to
+ * it instead of going through the library's pinned staging buffer; the reference does the same to its Eigen storage
+ * (ManagedBuffer, 3P/CuMatrix/CuMatrix/Buffers/ManagedBuffer.h:72-76). The buffer must stay alive until it is unregistered
+ * or the handle is destroyed. */
+int gaia_b200_register_host_buffer(gaia_handle* h, void* ptr, int64_t bytes);
+int gaia_b200_unregister_host_buffer(gaia_handle* h, void* ptr);
 
 /* integer parity surfaces ---------------------------------------------------- */
 int gaia_b200_get_world_bounds(const gaia_handle* h, float* min3, float* max3);

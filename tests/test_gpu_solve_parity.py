@@ -134,3 +134,24 @@ def test_state_roundtrip_and_whole_scene_io():
     assert np.array_equal(g.velocities(0), (v * 0.5).astype(np.float32))
     sp = g.surface_positions(0)
     assert np.array_equal(sp, g.positions(0)[g.surface_vertex_ids(0)])
+
+
+@pytest.mark.gpu
+def test_registered_host_buffers_take_the_direct_dma_path():
+    from gaia_b200 import capi
+    from conftest import make_beam_scene
+    g = make_beam_scene(capi.Scene)
+    g.run_frames(1)
+    ref = g.all_positions()
+    buf = np.zeros_like(ref)
+    g.register_host_buffer(buf)
+    assert np.array_equal(g.all_positions(out=buf), ref)          # D2H straight into the page-locked array
+    buf += np.float32(0.125)
+    vel = np.ones_like(buf)
+    g.set_all_state(buf, vel)                                      # pos from the registered array, vel through staging
+    assert np.array_equal(g.all_positions(), ref + np.float32(0.125))
+    g.unregister_host_buffer(buf)
+    with pytest.raises(capi.GaiaError):
+        g.unregister_host_buffer(buf)
+    assert np.array_equal(g.all_positions(out=buf), ref + np.float32(0.125))
+    g.close()
