@@ -875,7 +875,9 @@ cudaError_t collision_prepare(Scene& s) {
     for (int g = 0; g < G; g++) { c->h_groupOff[g] = run; run += c->h_groupCount[g]; }
     c->h_groupOff[G] = run;
     c->prepared = true;
-    if (c->nActive == 0) return cudaGetLastError();
+    // (a captured colour loop always runs the contact variant with device-sized pre-passes: its tables must be valid,
+    //  i.e. all-empty, when nothing is in contact)
+    if (c->nActive == 0 && !collision_graphable(s)) return cudaGetLastError();
     CK(cub::DeviceScan::ExclusiveSum(c->scanTmp.p, c->scanTmpBytes, c->relCount.p, c->relOff.p, (int)(N + 1), s.stream));
     k_group_offsets<<<1, 32, 0, s.stream>>>(G, c->groupCount.p, c->groupOff.p);
     k_prepare<1><<<nblk(nS), kB, 0, s.stream>>>(nS, c->cNum.p, c->cFace.p, c->cFlags.p, c->surfSid.p, c->faceSid.p, c->groupStart.p, G,
@@ -889,10 +891,15 @@ cudaError_t collision_prepare(Scene& s) {
 // ------------------------------------------------------------------------------------------------ per-colour contact pre-pass
 // updateCollisionInfo for the active contacts of one parallel group (VBDPhysics.cpp:1675-1680, 2205-2311)
 __global__ void __launch_bounds__(kB)
-k_update_infos(int n, const int32_t* __restrict__ list, ColParamsDev cp, const int32_t* __restrict__ surfSid, const int32_t* __restrict__ surfMesh,
+k_update_infos(int n, const int32_t* __restrict__ list, const int32_t* __restrict__ groupOff, int group, ColParamsDev cp, const int32_t* __restrict__ surfSid, const int32_t* __restrict__ surfMesh,
                const int32_t* __restrict__ cFace, const int4* __restrict__ faceSid, const float4* __restrict__ pos, const float4* __restrict__ prev,
                const MeshParamsDev* __restrict__ mp, float4* cF, float4* cH0, float4* cH1, float* cB2) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (groupOff) {      // device-sized launch (captured colour loop): the group's run of the list is read here
+        const int b = groupOff[group];
+        n = groupOff[group + 1] - b;
+        list += b;
+    }
     if (i >= n) return;
     const int slot = list[i];
     const int sq = surfSid[slot];
@@ -945,22 +952,34 @@ k_update_infos(int n, const int32_t* __restrict__ list, ColParamsDev cp, const i
     cB2[slot] = bary.z;
 }
 
-cudaError_t collision_update_infos(Scene& s, int group) {
+// A colour loop captured into a CUDA graph cannot size the pre-pass from this substep's host-side counts: it launches
+// over the capacity of the list instead and reads the group's run on the device. Worth it only while that capacity is a
+// few hundred blocks (small scenes, which are the launch-bound ones).
+static constexpr int64_t kGraphSurfCap = 1 << 18;
+bool collision_graphable(const Scene& s) { return s.cs && s.nSurfVerts <= kGraphSurfCap; }
+
+cudaError_t collision_update_infos(Scene& s, int group, bool deviceSized) {
     CollisionState* c = s.cs;
     if (!c || !c->prepared) return cudaSuccess;
+    if (deviceSized) {
+        k_update_infos<<<nblk(s.nSurfVerts), kB, 0, s.stream>>>(0, c->groupList.p, c->groupOff.p, group, c->cp, c->surfSid.p, c->surfMesh.p, c->cFace.p,
+                                                              c->faceSid.p, s.pos.p, s.prev.p, s.meshParams.p, c->cF.p, c->cH0.p, c->cH1.p, c->cB2.p);
+        s.stats.kernelLaunches++;
+        return cudaSuccess;
+    }
     const int n = c->h_groupCount[group];
     if (n <= 0) return cudaSuccess;
-    k_update_infos<<<nblk(n), kB, 0, s.stream>>>(n, c->groupList.p + c->h_groupOff[group], c->cp, c->surfSid.p, c->surfMesh.p, c->cFace.p,
+    k_update_infos<<<nblk(n), kB, 0, s.stream>>>(n, c->groupList.p + c->h_groupOff[group], nullptr, 0, c->cp, c->surfSid.p, c->surfMesh.p, c->cFace.p,
                                                c->faceSid.p, s.pos.p, s.prev.p, s.meshParams.p, c->cF.p, c->cH0.p, c->cH1.p, c->cB2.p);
     s.stats.kernelLaunches++;
     return cudaSuccess;
 }
 
-bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask) {
+bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask, bool force) {
     CollisionState* c = s.cs;
     if (!c || !c->prepared) { *collidingMask = nullptr; return false; }
     *collidingMask = c->colliding.p;
-    if (c->nActive == 0) return false;
+    if (c->nActive == 0 && !force) return false;
     cv.contactOfVertex = c->contactOfVertex.p; cv.relOff = c->relOff.p; cv.rel = c->rel.p;
     cv.cF = c->cF.p; cv.cH0 = c->cH0.p; cv.cH1 = c->cH1.p; cv.cB2 = c->cB2.p;
     return true;

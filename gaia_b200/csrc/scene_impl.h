@@ -169,9 +169,10 @@ void collision_invalidate(Scene& s);                              // force BVH r
 cudaError_t collision_dcd(Scene& s, bool intermediate);
 cudaError_t collision_ccd(Scene& s);
 cudaError_t collision_prepare(Scene& s);
-cudaError_t collision_update_infos(Scene& s, int group);          // per-colour contact force/Hessian pre-pass
+cudaError_t collision_update_infos(Scene& s, int group, bool deviceSized = false);   // per-colour contact force/Hessian pre-pass
+bool collision_graphable(const Scene& s);                         // contact lists small enough for device-sized pre-pass launches
 int64_t collision_fetch_contacts(Scene& s, gaia_contact* out, int64_t cap);
 int64_t collision_leaf_order(Scene& s, int which, int32_t* out, int64_t cap);
-bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask);
+bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask, bool force = false);
 
 }  // namespace gb

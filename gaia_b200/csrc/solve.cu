@@ -729,7 +729,7 @@ static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int apply
 #undef BYVAR
 }
 
-static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
+static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD, bool captured = false) {
     static bool envRead = false;
     if (!envRead) {
         const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e);
@@ -757,7 +757,8 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     }
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
-    bool hasContacts = collision_contact_view(s, cv, &colliding);
+    // (captured: the contact variant runs every substep, with device-sized pre-passes; empty tables when nothing touches)
+    bool hasContacts = collision_contact_view(s, cv, &colliding, captured);
     // per-iteration accounting (active, non-fixed vertices)
     int64_t solvedPerIter = 0, bytesPerIter = 0;
     for (auto& m : s.meshes) {
@@ -783,7 +784,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
         for (int g = 0; g < G; g++) {
             const int vb = s.groupStart[g], ve = s.groupStart[g + 1];
             if (ve <= vb && !halo) continue;
-            if (hasContacts) { CK(collision_update_infos(s, g)); }
+            if (hasContacts) { CK(collision_update_infos(s, g, captured)); }
             if (s.profiling) cudaEventRecord(s.evA, s.stream);
             hv.epochOffset = it * G + g;
             if (ve > vb) {
@@ -806,7 +807,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             }
         }
         s.stats.vertexSolves += solvedPerIter;
-        s.stats.algorithmicBytes += bytesPerIter + 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
+        s.stats.algorithmicBytes += bytesPerIter + (captured ? 0 : 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD));
         if (s.phys.useAccelerator) {
             k_accelerate<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.accPrevPrev.p, s.accPrevIter.p, s.info.p, s.meshParams.p, colliding, omega, 0);
             s.stats.kernelLaunches++;
@@ -825,18 +826,23 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
 }
 
 // The colour loop of one substep is launch-bound for small colours (hundreds of ~10 us kernels): when nothing in it needs
-// the host (no collision pipeline, no per-kernel profiling) it is captured once into a CUDA graph and replayed.
+// the host (no intermediate detection, no per-kernel profiling, no separate halo launches) it is captured once into a CUDA
+// graph and replayed. With the collision pipeline on, the contact pre-passes are launched over the capacity of the contact
+// list and read this substep's counts on the device (collision_graphable: small scenes only).
 static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
     static int useGraphs = -1;
     if (useGraphs < 0) { const char* e = getenv("GAIA_B200_GRAPH"); useGraphs = e ? atoi(e) : 1; }
-    const bool graphable = useGraphs && !s.profiling && !s.cs && s.iterCalls > 0 && nIters > 0;
+    const bool withContacts = s.cs != nullptr;
+    const bool contactsOk = !withContacts || (collision_graphable(s) && !halo_active(s) && !s.phys.useAccelerator &&
+                                              !(allowIntermediateCD && s.phys.intermediateCollisionIterations > 0));
+    const bool graphable = useGraphs && !s.profiling && contactsOk && s.iterCalls > 0 && nIters > 0;
     s.iterCalls++;
     if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD);
     if (!s.iterGraphExec || s.iterGraphIters != nIters) {
         if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }
         const gaia_stats before = s.stats;
         CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
-        cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD);
+        cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD, withContacts);
         cudaGraph_t g = nullptr;
         cudaError_t e2 = cudaStreamEndCapture(s.stream, &g);
         if (e != cudaSuccess) return e;
@@ -851,6 +857,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
     CK(cudaGraphLaunch(s.iterGraphExec, s.stream));
     s.stats.vertexSolves += s.iterDelta[0]; s.stats.colourSweeps += s.iterDelta[1];
     s.stats.kernelLaunches += s.iterDelta[2]; s.stats.algorithmicBytes += s.iterDelta[3];
+    if (withContacts) s.stats.algorithmicBytes += (int64_t)nIters * 92 * (s.stats.numContactsDCD + s.stats.numContactsCCD);
     return cudaSuccess;
 }
 
