@@ -91,3 +91,79 @@ def test_gpu_scene_from_files_matches_the_oracle(tmp_path):
     o = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)
     g.run_frames(3); o.run_frames(3)
     assert np.abs(g.positions(0) - o.positions(0)).max() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------ C++ host (gaia_vbdcloth_b200)
+import subprocess  # noqa: E402
+
+CLOTH_HOST_BIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gaia_b200", "host", "gaia_vbdcloth_b200")
+
+
+def test_cpp_cloth_host_dry_run_reads_the_schema(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert ("dryRun: 2 models, %d vertices, %d triangles, numFrames 3, numSubsteps 4, iterations 6, contactRadius 0.02, outputExt ply"
+            % (len(v) + len(sv), len(f) + len(sf))) in r.stdout
+
+
+def test_cpp_cloth_host_refuses_deformers_cpu_mode_and_missing_gpu(tmp_path):
+    m, p, _ = write_scene(str(tmp_path))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "--CPU"], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CPU path" in r.stderr
+    if not has_gpu():
+        r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path)], capture_output=True, text=True)
+        assert r.returncode == 3 and "gaia_b200_cloth_create failed" in r.stderr        # no silent CPU fallback
+    pj = json.load(open(p))
+    pj["Deformers"] = [{"DeformerName": "Rotator"}]
+    json.dump(pj, open(p, "w"))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 3 and "Deformers" in r.stderr
+
+
+@pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
+def test_cpp_cloth_host_reads_a_reference_experiment(tmp_path):
+    d = ("/root/reference/Simulator/VBDCloth/ParameterGen/Parameters/S01_Twisting/"
+         "C100_Twist_ContactR0.2_CStif100000.0_bd20_damping3e-05_relaxiation0.42_thick0.01_CDPerIter")
+    pj = json.load(open(d + "/Parameters.json"))
+    pj["Deformers"] = []                       # the twist itself is driven by deformers, which this host refuses
+    p = str(tmp_path / "Parameters.json")
+    json.dump(pj, open(p, "w"))
+    r = subprocess.run([CLOTH_HOST_BIN, d + "/Models.json", p, "/tmp/unused", "-R", "/root/reference", "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "10000 vertices, 19602 triangles" in r.stdout and "numSubsteps 5, iterations 10, contactRadius 0.2" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cpp_cloth_host_frames_match_the_python_binding(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path), frames=4)
+    pj = json.load(open(p))
+    pj["PhysicsParams"].update(outputExt="bin", binaryModeVisualizationSteps=2, outputRecoveryStateStep=2, outputStatistics=True)
+    json.dump(pj, open(p, "w"))
+    out = tmp_path / "out"
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(out), "-R", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    phys, meshes, _ = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    g = cloth_host.build_scene(cloth.ClothScene, phys, meshes)
+    for fr in range(5):
+        if fr:
+            g.run_frames(1)
+        a = np.fromfile(out / ("A%08d.bin" % fr), np.float32).reshape(-1, 3)
+        assert np.array_equal(a, np.concatenate([g.positions(0), g.positions(1)])), fr       # same library underneath: bit-identical
+    assert (out / "TemplateMesh" / "TemplateMesh_Model_000000_sheet.ply").exists()
+    assert (out / "A00000002.ply").exists() and not (out / "A00000001.ply").exists()
+    st = json.load(open(out / "RecoveryStates" / "A00000002.json"))
+    assert st["frameId"] == 2 and st["format"] == "binary" and st["meshesState"]["nVerts"] == [len(v), len(sv)]
+    stats = json.load(open(out / "Statistics" / "A00000003.json"))
+    assert stats["substeps"] == 4 and stats["numberCollisionDetection"] >= 4
+    head = open(out / "A00000002.ply").read(300)
+    assert "element vertex %d" % (len(v) + len(sv)) in head and "element face %d" % (len(f) + len(sf)) in head
+    # a run recovered from frame 2 carries on (positions and velocities are the whole state the reference saves too)
+    part = tmp_path / "part"
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(part), "-R", str(tmp_path), "-r", str(out / "RecoveryStates" / "A00000002.json")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and "Recovering state from" in r.stdout, r.stderr
+    a = np.fromfile(out / "A00000004.bin", np.float32)
+    b = np.fromfile(part / "A00000004.bin", np.float32)
+    assert a.shape == b.shape and np.abs(a - b).max() < 1e-3
+    g.close()
