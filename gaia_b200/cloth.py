@@ -84,7 +84,10 @@ def bind_cloth_api(lib, prefix):
     P, FP, IP = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
     sig = {
         "add_tri_mesh": ([P, C.c_int32, C.c_int32, C.c_int32, FP, IP, C.POINTER(ClothObjectParams), C.c_int32, IP, IP, C.c_int32, IP], C.c_int),
+        "add_rotator": ([P, C.c_int, IP, C.c_int32, FP, FP, C.c_double, C.c_double], C.c_int),
+        "add_translator": ([P, C.c_int, IP, C.c_int32, FP, C.c_float, C.c_float], C.c_int),
         "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
+        "frame_id": ([P], C.c_int), "cur_time": ([P], C.c_double), "set_time": ([P, C.c_int32, C.c_double], C.c_int),
         "synchronize": ([P], C.c_int), "num_meshes": ([P], C.c_int), "mesh_sizes": ([P, C.c_int, IP, IP, IP], C.c_int),
         "get_positions": ([P, C.c_int, FP], C.c_int), "get_velocities": ([P, C.c_int, FP], C.c_int),
         "set_state": ([P, C.c_int, FP, FP], C.c_int), "total_vertices": ([P], C.c_int64),
@@ -126,6 +129,16 @@ class ClothSceneBase:
         return self._call("add_tri_mesh", 1 if simulated else 0, xyz.shape[0], faces.shape[0], _fp(xyz), _ip(faces), C.byref(obj),
                           len(colors), _ip(offs), _ip(cv), len(fx), _ip(fx))
 
+    def add_rotator(self, mesh, verts, center, axis, angular_velocity, rotation_end_time=-1.0):
+        """ClothDeformerRotator on `verts` of `mesh` (they become fixed points); before finalize."""
+        v = _i32(np.asarray(verts, np.int32)); c = _f32(np.asarray(center, np.float32)); a = _f32(np.asarray(axis, np.float32))
+        return self._call("add_rotator", mesh, _ip(v), len(v), _fp(c), _fp(a), float(angular_velocity), float(rotation_end_time))
+
+    def add_translator(self, mesh, verts, speed, start_time=0.0, end_time=-1.0):
+        """ClothDeformerTranslater on `verts` of `mesh` (they become fixed points); before finalize."""
+        v = _i32(np.asarray(verts, np.int32)); sp = _f32(np.asarray(speed, np.float32))
+        return self._call("add_translator", mesh, _ip(v), len(v), _fp(sp), float(start_time), float(end_time))
+
     def finalize(self):
         self._call("finalize")
 
@@ -137,6 +150,17 @@ class ClothSceneBase:
 
     def synchronize(self):
         self._call("synchronize")
+
+    @property
+    def frame_id(self):
+        return int(getattr(self._lib, self._prefix + "frame_id")(self.h))
+
+    @property
+    def cur_time(self):
+        return float(getattr(self._lib, self._prefix + "cur_time")(self.h))
+
+    def set_time(self, frame_id, cur_time):
+        self._call("set_time", int(frame_id), float(cur_time))
 
     @property
     def num_meshes(self):

@@ -6,8 +6,9 @@
 Mirrors what BaseClothPhsicsFramework does around the step (M/Framework/BaseClothSimPhsicsFramework.cpp: loadRunningparameters,
 initialize, simulate, writeOutputs): parameters keep the reference's names, meshes are loaded in file order (simulated
 models, a collider being a model whose vertices are all fixed, as S03 does it), frames are written as `A%08d.ply`
-(all meshes together, ASCII) or `A%08d.bin` (raw float32 positions). Not handled here, and refused loudly: `Deformers`
-(they move fixed vertices every substep) and `ColliderParams` mesh sequences.
+(all meshes together, ASCII) or `A%08d.bin` (raw float32 positions). `Deformers` (Rotator / Translator,
+M/VBDCloth/VBDClothDeformer.h:202-242) are handed to the library. Not handled here, and refused loudly: `ColliderParams`
+mesh sequences.
 """
 import argparse
 import json
@@ -77,14 +78,15 @@ def cloth_object_params_from_json(m):
     return cloth.default_cloth_object_params(**kw)
 
 
-def load_cloth_scene_json(models_json, params_json, repo_root, allow_deformers=False):
-    """-> (ClothPhysicsParams, [(verts, faces, ClothObjectParams, colours, fixedPoints, initialVelocity)], raw parameter dict)"""
+def load_cloth_scene_json(models_json, params_json, repo_root, allow_deformers=True):
+    """-> (ClothPhysicsParams, [(verts, faces, ClothObjectParams, colours, fixedPoints, initialVelocity)], raw parameter dict);
+    the raw dict's "Deformers" list goes to build_scene(deformers=...)"""
     with open(params_json) as f:
         pj = json.load(f)
     with open(models_json) as f:
         mj = json.load(f)
     if pj.get("Deformers") and not allow_deformers:
-        raise NotImplementedError("cloth Deformers are outside this host (they move fixed vertices every substep)")
+        raise NotImplementedError("cloth Deformers refused by the caller")
     if pj.get("ColliderParams", {}).get("ColliderMeshes"):
         raise NotImplementedError("ColliderParams mesh sequences are outside this host; add the collider as a model with all vertices fixed")
     phys = cloth_physics_params_from_json(pj)
@@ -97,10 +99,26 @@ def load_cloth_scene_json(models_json, params_json, repo_root, allow_deformers=F
     return phys, meshes, pj
 
 
-def build_scene(cls, phys, meshes, **kw):
+def add_deformers(scene, deformers):
+    """loadClothDeformers: one library deformer per (deformer, selected mesh)"""
+    for d in deformers or []:
+        name = d.get("DeformerName")
+        if len(d["selectedMeshes"]) != len(d["selectedVertices"]):
+            raise ValueError("deformer: selectedMeshes / selectedVertices size mismatch")
+        for mesh, verts in zip(d["selectedMeshes"], d["selectedVertices"]):
+            if name == "Rotator":
+                scene.add_rotator(mesh, verts, d["center"], d["axis"], d["angularVelocity"], d.get("rotationEndTime", -1))
+            elif name == "Translator":
+                scene.add_translator(mesh, verts, d["speed"], d.get("deformationStartTime", 0.0), d.get("deformationEndTime", -1))
+            else:
+                raise ValueError(f"Unrecognized deformer: {name}")
+
+
+def build_scene(cls, phys, meshes, deformers=None, **kw):
     s = cls(phys, **kw)
     for v, f, obj, colors, fixed, v0 in meshes:
         s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=True)
+    add_deformers(s, deformers)
     s.finalize()
     for i, (v, f, obj, colors, fixed, v0) in enumerate(meshes):
         if np.any(v0 != 0):
@@ -128,7 +146,7 @@ def simulate(models_json, params_json, out_dir, repo_root=".", frames=None, devi
     n = int(pp.get("numFrames", 1)) if frames is None else frames
     ext = pp.get("outputExt", "ply")
     os.makedirs(out_dir, exist_ok=True)
-    s = build_scene(cloth.ClothScene, phys, meshes, device=device)
+    s = build_scene(cloth.ClothScene, phys, meshes, deformers=pj.get("Deformers"), device=device)
     write_frame(s, meshes, out_dir, 0, ext)
     for fr in range(1, n + 1):
         s.run_frames(1)

@@ -1146,6 +1146,32 @@ static __global__ void k_initial_step(int n, StepP P, int hasVelPrev, float4* po
 }
 
 // updateVelocity (VBDClothPhysics.cpp:2318-2359)
+// ------------------------------------------------------------------------------------------------ deformers
+// ClothDeformerRotator::operator() (M/VBDCloth/VBDClothDeformer.h:71-117): p = root + R * RootP, R built on the host in
+// double from theta = curTime * angularVelocity and rounded to float like Eigen's Matrix3f; row sums left to right.
+struct Rot9 { float m[9]; };
+static __global__ void k_deform_rotate(int n, const int32_t* __restrict__ sid, const float4* __restrict__ root, const float4* __restrict__ rootP,
+                                       Rot9 R, float4* pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 r = root[i], q = rootP[i];
+    const int s = sid[i];
+    float4 p = pos[s];
+    p.x = r.x + ((R.m[0] * q.x + R.m[1] * q.y) + R.m[2] * q.z);
+    p.y = r.y + ((R.m[3] * q.x + R.m[4] * q.y) + R.m[5] * q.z);
+    p.z = r.z + ((R.m[6] * q.x + R.m[7] * q.y) + R.m[8] * q.z);
+    pos[s] = p;
+}
+// ClothDeformerTranslater::operator() (:176-190): p += speed * dt while the deformation is active
+static __global__ void k_deform_translate(int n, const int32_t* __restrict__ sid, float3 speed, float dt, float4* pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int s = sid[i];
+    float4 p = pos[s];
+    p.x += speed.x * dt; p.y += speed.y * dt; p.z += speed.z * dt;
+    pos[s] = p;
+}
+
 static __global__ void k_update_velocity(int n, StepP P, const float4* __restrict__ pos, const float4* __restrict__ prev, float4* vel,
                                          const int32_t* __restrict__ info, const MeshDev* __restrict__ mt) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1241,6 +1267,9 @@ struct ClothScene {
     bool collisionDetectionRequired = false;
     int64_t substepsTaken = 0;
     int frameId = 0;
+    float curTime = 0.f;                // += dt every substep, like the framework's curTime (float accumulation)
+    struct DeformerDev { DevBuf<int32_t> sid; DevBuf<float4> root, rootP; };
+    std::vector<DeformerDev> deformerDev;   // one per h.deformers entry
     bool detectedOnce = false;
     gaia_cloth_stats stats;
     bool profiling = false;
@@ -1266,6 +1295,27 @@ static cudaError_t upload(DevBuf<T>& buf, const std::vector<T>& v) {
     CK(buf.alloc(v.size()));
     if (v.empty()) return cudaSuccess;
     return cudaMemcpy(buf.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+static cudaError_t upload_deformers(ClothScene& s) {
+    s.deformerDev.clear();
+    s.deformerDev.resize(s.h.deformers.size());
+    for (size_t i = 0; i < s.h.deformers.size(); i++) {
+        const ClothDeformer& d = s.h.deformers[i];
+        const ClothMesh& m = s.h.meshes[d.mesh];
+        std::vector<int32_t> sid(d.verts.size());
+        std::vector<float4> root(d.verts.size()), rootP(d.verts.size());
+        for (size_t k = 0; k < d.verts.size(); k++) {
+            sid[k] = m.sortedId[d.verts[k]];
+            if (d.type == 0) {
+                root[k] = make_float4(d.roots[3 * k], d.roots[3 * k + 1], d.roots[3 * k + 2], 0.f);
+                rootP[k] = make_float4(d.rootPs[3 * k], d.rootPs[3 * k + 1], d.rootPs[3 * k + 2], 0.f);
+            }
+        }
+        CK(upload(s.deformerDev[i].sid, sid));
+        if (d.type == 0) { CK(upload(s.deformerDev[i].root, root)); CK(upload(s.deformerDev[i].rootP, rootP)); }
+    }
+    return cudaSuccess;
 }
 
 static void make_step_params(ClothScene& s) {
@@ -1484,11 +1534,36 @@ static float accelerator_omega(float rho, int order, float prevOmega) {
 }
 
 // one iteration of runStep_CDEveryIter (:399-509); returns a GAIA status
+static void apply_deformers(ClothScene& s) {
+    for (size_t i = 0; i < s.h.deformers.size(); i++) {
+        const ClothDeformer& d = s.h.deformers[i];
+        const int n = (int)d.verts.size();
+        if (!n) continue;
+        auto& dev = s.deformerDev[i];
+        if (d.type == 0) {
+            float curTime = s.curTime;
+            if (curTime >= d.rotationEnd && d.rotationEnd > 0) curTime = (float)d.rotationEnd;
+            const double theta = curTime * d.angularVelocity;
+            const double ux = d.axis[0], uy = d.axis[1], uz = d.axis[2], c = std::cos(theta), sn = std::sin(theta);
+            Rot9 R;
+            R.m[0] = (float)(c + ux * ux * (1 - c));      R.m[1] = (float)(ux * uy * (1 - c) - uz * sn); R.m[2] = (float)(ux * uz * (1 - c) + uy * sn);
+            R.m[3] = (float)(uy * ux * (1 - c) + uz * sn); R.m[4] = (float)(c + uy * uy * (1 - c));      R.m[5] = (float)(uy * uz * (1 - c) - ux * sn);
+            R.m[6] = (float)(uz * ux * (1 - c) - uy * sn); R.m[7] = (float)(uz * uy * (1 - c) + ux * sn); R.m[8] = (float)(c + uz * uz * (1 - c));
+            k_deform_rotate<<<nblk(n), kB, 0, s.stream>>>(n, dev.sid.p, dev.root.p, dev.rootP.p, R, s.pos.p);
+        } else {
+            if (!(s.curTime >= d.deformationStartTime && (s.curTime < d.deformationEndTime || d.deformationEndTime < 0))) continue;
+            k_deform_translate<<<nblk(n), kB, 0, s.stream>>>(n, dev.sid.p, make_float3(d.speed[0], d.speed[1], d.speed[2]), s.h.dt, s.pos.p);
+        }
+        s.stats.kernelLaunches++;
+    }
+}
+
 static int iteration(ClothScene& s, int iIter, float& omega) {
     ClothHost& h = s.h;
     const int nSim = (int)h.nSimV;
     cudaError_t e;
     auto cuda = [&](cudaError_t x) { if (x != cudaSuccess) { s.err = std::string("CUDA: ") + cudaGetErrorString(x); return false; } return true; };
+    if (iIter == 0) apply_deformers(s);       // applyDeformers(), VBDClothPhysics.cpp:408-412
     if (iIter == 0 && nSim) if (!cuda(cudaMemsetAsync(s.activeMask.p, 0, nSim, s.stream))) return GAIA_ERR_CUDA;
     cudaEvent_t evD0 = nullptr;
     if (s.collisionDetectionRequired || iIter == 0) {
@@ -1578,6 +1653,7 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
 static int run_substeps(ClothScene& s, int nSubsteps) {
     const int nSim = (int)s.h.nSimV;
     for (int sub = 0; sub < nSubsteps; sub++) {
+        s.curTime += s.h.dt;
         float omega = 1.f;
         for (int it = 0; it < s.h.phys.iterations; it++) { const int rc = iteration(s, it, omega); if (rc < 0) return rc; }
         if (nSim) {
@@ -1680,8 +1756,58 @@ int gaia_b200_cloth_finalize(gaia_cloth_handle* h) {
     if (!cloth_host_finalize(s.h, err)) return cfail(s, GAIA_ERR_INVALID_ARG, err);
     CCUDA(h, cudaSetDevice(s.device));
     CCUDA(h, device_upload(s));
+    CCUDA(h, upload_deformers(s));
     s.finalized = true;
     return GAIA_OK;
+}
+
+// loadClothDeformers (M/VBDCloth/VBDClothDeformer.h:202-242): after the mesh is added, before finalize. The selected vertices
+// join the mesh's fixed points (setFixedPointCloth, :5-21); a rotator keeps root / RootP of their positions at creation.
+static int add_deformer_common(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, ClothDeformer& d) {
+    ClothScene& s = h->s;
+    if (s.finalized) return cfail(s, GAIA_ERR_STATE, "deformers are added before finalize");
+    if (mesh < 0 || mesh >= (int)s.h.meshes.size()) return cfail(s, GAIA_ERR_INVALID_ARG, "mesh id out of range");
+    ClothMesh& m = s.h.meshes[mesh];
+    if (!m.simulated) return cfail(s, GAIA_ERR_INVALID_ARG, "deformers select vertices of simulated meshes");
+    if (n < 0 || (n > 0 && !verts)) return cfail(s, GAIA_ERR_INVALID_ARG, "bad vertex selection");
+    for (int i = 0; i < n; i++) if (verts[i] < 0 || verts[i] >= m.nV) return cfail(s, GAIA_ERR_INVALID_ARG, "selected vertex out of range");
+    d.mesh = mesh;
+    d.verts.assign(verts, verts + n);
+    for (int i = 0; i < n; i++) m.fixedMask[verts[i]] = 1;
+    return GAIA_OK;
+}
+int gaia_b200_cloth_add_rotator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float center[3], const float axis[3],
+                                double angularVelocity, double rotationEndTime) {
+    CREQ(h);
+    if (!center || !axis) return cfail(h->s, GAIA_ERR_INVALID_ARG, "null argument");
+    ClothDeformer d;
+    d.type = 0;
+    const int rc = add_deformer_common(h, mesh, verts, n, d);
+    if (rc < 0) return rc;
+    for (int k = 0; k < 3; k++) { d.o[k] = center[k]; d.axis[k] = axis[k]; }
+    d.angularVelocity = angularVelocity; d.rotationEnd = rotationEndTime;
+    const ClothMesh& m = h->s.h.meshes[mesh];
+    for (int i = 0; i < n; i++) {
+        const float* P = &m.pos0[3 * (size_t)verts[i]];
+        const float op[3] = {P[0] - d.o[0], P[1] - d.o[1], P[2] - d.o[2]};
+        const float t = (op[0] * d.axis[0] + op[1] * d.axis[1]) + op[2] * d.axis[2];
+        for (int k = 0; k < 3; k++) { const float r = t * d.axis[k]; d.roots.push_back(r); d.rootPs.push_back(P[k] - r); }
+    }
+    h->s.h.deformers.push_back(std::move(d));
+    return (int)h->s.h.deformers.size() - 1;
+}
+int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3],
+                                   float deformationStartTime, float deformationEndTime) {
+    CREQ(h);
+    if (!speed) return cfail(h->s, GAIA_ERR_INVALID_ARG, "null argument");
+    ClothDeformer d;
+    d.type = 1;
+    const int rc = add_deformer_common(h, mesh, verts, n, d);
+    if (rc < 0) return rc;
+    for (int k = 0; k < 3; k++) d.speed[k] = speed[k];
+    d.deformationStartTime = deformationStartTime; d.deformationEndTime = deformationEndTime;
+    h->s.h.deformers.push_back(std::move(d));
+    return (int)h->s.h.deformers.size() - 1;
 }
 
 int gaia_b200_cloth_run_frames(gaia_cloth_handle* h, int32_t nFrames) {
@@ -1693,8 +1819,17 @@ int gaia_b200_cloth_run_frames(gaia_cloth_handle* h, int32_t nFrames) {
 int gaia_b200_cloth_run_iterations(gaia_cloth_handle* h, int32_t nIters) {
     CREQ(h); CFIN(h);
     CCUDA(h, cudaSetDevice(h->s.device));
+    h->s.curTime += h->s.h.dt;
     float omega = 1.f;
     for (int it = 0; it < nIters; it++) { const int rc = iteration(h->s, it, omega); if (rc < 0) return rc; }
+    return GAIA_OK;
+}
+int gaia_b200_cloth_frame_id(const gaia_cloth_handle* h) { return h ? h->s.frameId : GAIA_ERR_INVALID_ARG; }
+double gaia_b200_cloth_cur_time(const gaia_cloth_handle* h) { return h ? (double)h->s.curTime : 0.0; }
+int gaia_b200_cloth_set_time(gaia_cloth_handle* h, int32_t frameId, double curTime) {
+    CREQ(h);
+    h->s.frameId = frameId;
+    h->s.curTime = (float)curTime;
     return GAIA_OK;
 }
 int gaia_b200_cloth_synchronize(gaia_cloth_handle* h) {

@@ -36,8 +36,21 @@ struct ClothMesh {
     int64_t vBase = 0, fBase = 0, eBase = 0; // offsets in "meshes concatenated" order
 };
 
+// ClothDeformerRotator / ClothDeformerTranslater (M/VBDCloth/VBDClothDeformer.h:43-200): selected vertices become fixed and
+// are moved by the host schedule at the first iteration of every substep
+struct ClothDeformer {
+    int type = 0;                      // 0 rotator, 1 translator
+    int mesh = 0;
+    std::vector<int32_t> verts;
+    float o[3] = {0, 0, 0}, axis[3] = {0, 0, 0}, speed[3] = {0, 0, 0};
+    double angularVelocity = 0.0, rotationEnd = -1.0;
+    float deformationStartTime = 0.f, deformationEndTime = -1.f;
+    std::vector<float> roots, rootPs;  // rotator: 3 per selected vertex, from the positions at creation
+};
+
 struct ClothHost {
     gaia_cloth_physics_params phys;
+    std::vector<ClothDeformer> deformers;
     float dt = 0.f, dtSqrReciprocal = 0.f;
     std::vector<ClothMesh> meshes;
     int numSim = 0;

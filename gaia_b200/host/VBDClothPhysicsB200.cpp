@@ -72,9 +72,21 @@ void VBDClothPhysicsB200::loadRunningparameters(std::string inModelInputFile, st
     gaia_b200_cloth_default_physics_params(&phys_);
     const Value params = jsonmin::parse_file(inParameterFile);
     const Value modelsFile = jsonmin::parse_file(inModelInputFile);
-    if (const Value* ds = params.find("Deformers"))
-        if (ds->is_array() && ds->size() > 0)
-            throw std::runtime_error("cloth Deformers are outside this host (they move fixed vertices from the host every substep)");
+    if (const Value* ds = params.find("Deformers")) {      // loadClothDeformers, M/VBDCloth/VBDClothDeformer.h:202-242
+        for (auto& d : ds->arr) {
+            ClothDeformerInput in;
+            std::string name;
+            d.get("DeformerName", name);
+            if (name == "Rotator") { in.type = 0; d.get_vec3("center", in.center); d.get_vec3("axis", in.axis); d.get("angularVelocity", in.angularVelocity); d.get("rotationEndTime", in.rotationEndTime); }
+            else if (name == "Translator") { in.type = 1; d.get_vec3("speed", in.speed); d.get("deformationStartTime", in.deformationStartTime); d.get("deformationEndTime", in.deformationEndTime); }
+            else throw std::runtime_error("Unrecognized deformer: " + name);
+            d.get_ints("selectedMeshes", in.selectedMeshes);
+            if (const Value* sv = d.find("selectedVertices"))
+                for (auto& l : sv->arr) { in.selectedVertices.emplace_back(); for (auto& v : l.arr) in.selectedVertices.back().push_back((int32_t)v.as_double()); }
+            if (in.selectedVertices.size() != in.selectedMeshes.size()) throw std::runtime_error("deformer: selectedMeshes / selectedVertices size mismatch");
+            deformers_.push_back(in);
+        }
+    }
     if (const Value* cp = params.find("ColliderParams"))
         if (const Value* cm = cp->find("ColliderMeshes"))
             if (cm->is_array() && cm->size() > 0)
@@ -170,6 +182,12 @@ void VBDClothPhysicsB200::initialize() {
                                                     m.fixedPoints.empty() ? nullptr : m.fixedPoints.data());
         check(rc, "gaia_b200_cloth_add_tri_mesh");
     }
+    for (auto& d : deformers_)
+        for (size_t i = 0; i < d.selectedMeshes.size(); i++) {
+            const std::vector<int32_t>& v = d.selectedVertices[i];
+            if (d.type == 0) check(gaia_b200_cloth_add_rotator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.center, d.axis, d.angularVelocity, d.rotationEndTime), "gaia_b200_cloth_add_rotator");
+            else check(gaia_b200_cloth_add_translator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.speed, d.deformationStartTime, d.deformationEndTime), "gaia_b200_cloth_add_translator");
+        }
     check(gaia_b200_cloth_finalize(h_), "gaia_b200_cloth_finalize");
     for (size_t i = 0; i < models_.size(); i++) {
         const float* v0 = models_[i].initialVelocity;
@@ -186,8 +204,8 @@ void VBDClothPhysicsB200::initialize() {
 
 void VBDClothPhysicsB200::runStep() {
     check(gaia_b200_cloth_run_frames(h_, 1), "gaia_b200_cloth_run_frames");
-    frameId_++;
-    curTime_ += phys_.timeStep;
+    frameId_ = gaia_b200_cloth_frame_id(h_);
+    curTime_ = gaia_b200_cloth_cur_time(h_);
 }
 
 void VBDClothPhysicsB200::simulate() {
@@ -343,6 +361,7 @@ void VBDClothPhysicsB200::recoverFromState(const std::string& stateFileIn) {
             check(gaia_b200_cloth_set_state(h_, (int)m, p.data(), v.data()), "gaia_b200_cloth_set_state");
         }
     }
+    check(gaia_b200_cloth_set_time(h_, frameId, curTime), "gaia_b200_cloth_set_time");
     frameId_ = frameId;
     curTime_ = curTime;
 }

@@ -14,8 +14,8 @@
 //   VBDClothSimulationFramework::runStep (= runStep_CDEveryIter)        M/VBDCloth/VBDClothPhysics.cpp:389-518
 //   TriMeshFEM::loadObj (triangle .obj)                                 M/TriMesh/TriMesh.cpp:15-111
 // Models are the simulated meshes (baseTriMeshesForSimulation); a collider is a model whose vertices are all fixed, as
-// S03_MultiLayerClothOnCollider.py writes it. Refused loudly: `Deformers` of the cloth Parameters.json and
-// `ColliderParams` mesh sequences (they replace vertex positions from the host every substep / frame).
+// S03_MultiLayerClothOnCollider.py writes it. `Deformers` (Rotator / Translator, M/VBDCloth/VBDClothDeformer.h) are passed
+// to the library. Refused loudly: `ColliderParams` mesh sequences (they replace collider positions from files every frame).
 #pragma once
 #include <cstdint>
 #include <map>
@@ -32,6 +32,15 @@ struct ClothModelInput {
     std::vector<int32_t> fixedPoints;
     float initialVelocity[3] = {0, 0, 0};
     int meshCacheId = -1;
+};
+
+struct ClothDeformerInput {
+    int type = 0;   // 0 Rotator, 1 Translator
+    float center[3] = {0, 0, 0}, axis[3] = {0, 0, 0}, speed[3] = {0, 0, 0};
+    double angularVelocity = 0, rotationEndTime = -1;
+    float deformationStartTime = 0.f, deformationEndTime = -1.f;
+    std::vector<int> selectedMeshes;
+    std::vector<std::vector<int32_t>> selectedVertices;
 };
 
 struct HostTriMeshData {
@@ -91,6 +100,7 @@ private:
     std::vector<ClothModelInput> models_;
     std::vector<HostTriMeshData> meshCache_;
     std::map<std::string, std::vector<std::vector<int32_t>>> colourings_;
+    std::vector<ClothDeformerInput> deformers_;
     gaia_cloth_handle* h_ = nullptr;
     int frameId_ = 0;
     double curTime_ = 0.0;

@@ -123,6 +123,17 @@ int gaia_b200_cloth_add_tri_mesh(gaia_cloth_handle* h, int32_t simulated, int32_
                                  const float* xyz, const int32_t* faces, const gaia_cloth_object_params* obj,
                                  int32_t nColors, const int32_t* color_offsets, const int32_t* color_verts,
                                  int32_t nFixed, const int32_t* fixedPoints);
+/* Deformers of the cloth Parameters.json (loadClothDeformers, M/VBDCloth/VBDClothDeformer.h:202-242), applied at the first
+ * iteration of every substep (VBDClothSimulationFramework::applyDeformers, M/VBDCloth/VBDClothPhysics.cpp:408-412, 2464-2470).
+ * Call after add_tri_mesh of `mesh` and before finalize; the selected vertices become fixed points (setFixedPointCloth).
+ * Rotator (:43-132): p = root + R(curTime * angularVelocity) * RootP with root = ((P - center).axis) axis and
+ * RootP = P - root exactly as the reference computes them (so the turn is about the axis through the origin and `center`
+ * only enters through its component along the axis); rotationEndTime <= 0: never stops. Translator (:134-200): p += speed * dt while deformationStartTime <= curTime < deformationEndTime (end < 0:
+ * never stops). Return the deformer id. */
+int gaia_b200_cloth_add_rotator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float center[3],
+                                const float axis[3], double angularVelocity, double rotationEndTime);
+int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3],
+                                   float deformationStartTime, float deformationEndTime);
 /* finalize: VBDClothSimulationFramework::initialize (parallel groups :72-138, contact detector) */
 int gaia_b200_cloth_finalize(gaia_cloth_handle* h);
 
@@ -131,6 +142,11 @@ int gaia_b200_cloth_run_frames(gaia_cloth_handle* h, int32_t nFrames);
 /* parity entry: one substep's first `nIters` iterations (detection, initial guess, colour sweeps), no velocity update */
 int gaia_b200_cloth_run_iterations(gaia_cloth_handle* h, int32_t nIters);
 int gaia_b200_cloth_synchronize(gaia_cloth_handle* h);
+/* frameId / curTime of the framework (curTime += dt every substep; the deformers' clock); set_time: ClothPhysicsState::
+ * initializePhysics when a run is recovered (M/Framework/BaseClothSimPhsicsFramework.h:94-96) */
+int gaia_b200_cloth_frame_id(const gaia_cloth_handle* h);
+double gaia_b200_cloth_cur_time(const gaia_cloth_handle* h);
+int gaia_b200_cloth_set_time(gaia_cloth_handle* h, int32_t frameId, double curTime);
 
 int gaia_b200_cloth_num_meshes(const gaia_cloth_handle* h);
 int gaia_b200_cloth_mesh_sizes(const gaia_cloth_handle* h, int mesh, int32_t* nV, int32_t* nF, int32_t* nE);

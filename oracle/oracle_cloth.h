@@ -65,8 +65,20 @@ struct TriMesh {
     bool hasVelocitiesPrev = false, hasApproxAcceleration = false;
 };
 
+// ClothDeformerRotator / ClothDeformerTranslater (M/VBDCloth/VBDClothDeformer.h:43-200)
+struct ClothDeformer {
+    int type = 0;                           // 0 rotator, 1 translator
+    int mesh = 0;
+    std::vector<int> verts;
+    V3 o, axis, speed;
+    double angularVelocity = 0.0, rotationEnd = -1.0;
+    float deformationStartTime = 0.f, deformationEndTime = -1.f;
+    std::vector<V3> roots, rootPs;
+};
+
 struct ClothScene {
     gaia_cloth_physics_params phys;
+    std::vector<ClothDeformer> deformers;
     float dt = 0.f, dtSqrReciprocal = 0.f;
     std::vector<TriMesh> meshes;
     int numSim = 0;
@@ -85,6 +97,9 @@ void cloth_mesh_initialize(TriMesh& m, bool simulated, int nV, int nF, const flo
                            const gaia_cloth_object_params& obj, int nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
                            int nFixed, const int32_t* fixed);
 void cloth_finalize(ClothScene& s);
+void cloth_add_rotator(ClothScene& s, int mesh, const int32_t* verts, int n, const float center[3], const float axis[3],
+                       double angularVelocity, double rotationEnd);
+void cloth_add_translator(ClothScene& s, int mesh, const int32_t* verts, int n, const float speed[3], float tStart, float tEnd);
 void cloth_detect(ClothScene& s);
 void cloth_run_substeps(ClothScene& s, int nSubsteps);
 void cloth_run_iterations(ClothScene& s, int nIters);

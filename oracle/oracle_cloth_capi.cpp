@@ -33,6 +33,19 @@ int oracle_cloth_add_tri_mesh(void* h, int32_t simulated, int32_t nV, int32_t nF
     cloth_mesh_initialize(m, simulated != 0, nV, nF, xyz, faces, *obj, nColors, colorOffsets, colorVerts, nFixed, fixed);
     return m.id;
 }
+int oracle_cloth_add_rotator(void* h, int mesh, const int32_t* verts, int32_t n, const float* center, const float* axis,
+                             double angularVelocity, double rotationEndTime) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized || mesh < 0 || mesh >= (int)s->meshes.size()) return GAIA_ERR_STATE;
+    cloth_add_rotator(*s, mesh, verts, n, center, axis, angularVelocity, rotationEndTime);
+    return (int)s->deformers.size() - 1;
+}
+int oracle_cloth_add_translator(void* h, int mesh, const int32_t* verts, int32_t n, const float* speed, float tStart, float tEnd) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized || mesh < 0 || mesh >= (int)s->meshes.size()) return GAIA_ERR_STATE;
+    cloth_add_translator(*s, mesh, verts, n, speed, tStart, tEnd);
+    return (int)s->deformers.size() - 1;
+}
 int oracle_cloth_finalize(void* h) { cloth_finalize(*(ClothScene*)h); return GAIA_OK; }
 int oracle_cloth_run_frames(void* h, int32_t n) {
     ClothScene* s = (ClothScene*)h;
@@ -41,6 +54,9 @@ int oracle_cloth_run_frames(void* h, int32_t n) {
 }
 int oracle_cloth_run_iterations(void* h, int32_t n) { cloth_run_iterations(*(ClothScene*)h, n); return GAIA_OK; }
 int oracle_cloth_synchronize(void*) { return GAIA_OK; }
+int oracle_cloth_frame_id(void* h) { return ((ClothScene*)h)->frameId; }
+double oracle_cloth_cur_time(void* h) { return (double)((ClothScene*)h)->curTime; }
+int oracle_cloth_set_time(void* h, int32_t frameId, double curTime) { ((ClothScene*)h)->frameId = frameId; ((ClothScene*)h)->curTime = (float)curTime; return GAIA_OK; }
 int oracle_cloth_num_meshes(void* h) { return (int)((ClothScene*)h)->meshes.size(); }
 int oracle_cloth_mesh_sizes(void* h, int mesh, int32_t* nV, int32_t* nF, int32_t* nE) {
     const TriMesh& m = ((ClothScene*)h)->meshes[mesh];

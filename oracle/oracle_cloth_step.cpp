@@ -1,5 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h, oracle_cloth.h).
 // The cloth VBD step: VBDClothSimulationFramework::runStep_CDEveryIter and everything it calls per vertex.
+#include <algorithm>
+#include <cmath>
 #include "oracle_cloth.h"
 
 namespace orc {
@@ -331,8 +333,70 @@ static float accelerator_omega(float rho, int order, float prevOmega) {
 }
 
 // one iteration of runStep_CDEveryIter (:399-509)
+// setFixedPointCloth (M/VBDCloth/VBDClothDeformer.h:5-21)
+static void set_fixed_points(TriMesh& m, const std::vector<int>& verts) {
+    for (int v : verts) {
+        m.fixedMask[v] = 1;
+        if (std::find(m.fixedPoints.begin(), m.fixedPoints.end(), v) == m.fixedPoints.end()) m.fixedPoints.push_back(v);
+    }
+}
+
+// ClothDeformerRotator constructor (:44-69)
+void cloth_add_rotator(ClothScene& s, int mesh, const int32_t* verts, int n, const float center[3], const float axis[3],
+                       double angularVelocity, double rotationEnd) {
+    ClothDeformer d;
+    d.type = 0; d.mesh = mesh; d.verts.assign(verts, verts + n);
+    d.o = V3(center[0], center[1], center[2]); d.axis = V3(axis[0], axis[1], axis[2]);
+    d.angularVelocity = angularVelocity; d.rotationEnd = rotationEnd;
+    TriMesh& m = s.meshes[mesh];
+    set_fixed_points(m, d.verts);
+    for (int v : d.verts) {
+        const V3 P = m.pos[v];
+        const V3 OP = P - d.o;
+        const V3 root = dot(OP, d.axis) * d.axis;
+        d.roots.push_back(root);
+        d.rootPs.push_back(P - root);
+    }
+    s.deformers.push_back(d);
+}
+
+// ClothDeformerTranslater constructor (:135-149)
+void cloth_add_translator(ClothScene& s, int mesh, const int32_t* verts, int n, const float speed[3], float tStart, float tEnd) {
+    ClothDeformer d;
+    d.type = 1; d.mesh = mesh; d.verts.assign(verts, verts + n);
+    d.speed = V3(speed[0], speed[1], speed[2]);
+    d.deformationStartTime = tStart; d.deformationEndTime = tEnd;
+    set_fixed_points(s.meshes[mesh], d.verts);
+    s.deformers.push_back(d);
+}
+
+// VBDClothSimulationFramework::applyDeformers (M/VBDCloth/VBDClothPhysics.cpp:2464-2470) with the two operator()s
+// (VBDClothDeformer.h:71-117, 151-191)
+static void apply_deformers(ClothScene& s) {
+    for (const ClothDeformer& d : s.deformers) {
+        TriMesh& m = s.meshes[d.mesh];
+        if (d.type == 0) {
+            float curTime = s.curTime;
+            if (curTime >= d.rotationEnd && d.rotationEnd > 0) curTime = (float)d.rotationEnd;
+            const double theta = curTime * d.angularVelocity;
+            const double ux = d.axis.x, uy = d.axis.y, uz = d.axis.z;
+            const float R[9] = {(float)(cos(theta) + ux * ux * (1 - cos(theta))), (float)(ux * uy * (1 - cos(theta)) - uz * sin(theta)), (float)(ux * uz * (1 - cos(theta)) + uy * sin(theta)),
+                                (float)(uy * ux * (1 - cos(theta)) + uz * sin(theta)), (float)(cos(theta) + uy * uy * (1 - cos(theta))), (float)(uy * uz * (1 - cos(theta)) - ux * sin(theta)),
+                                (float)(uz * ux * (1 - cos(theta)) - uy * sin(theta)), (float)(uz * uy * (1 - cos(theta)) + ux * sin(theta)), (float)(cos(theta) + uz * uz * (1 - cos(theta)))};
+            for (size_t i = 0; i < d.verts.size(); i++) {
+                const V3& q = d.rootPs[i];
+                const V3 rot((R[0] * q.x + R[1] * q.y) + R[2] * q.z, (R[3] * q.x + R[4] * q.y) + R[5] * q.z, (R[6] * q.x + R[7] * q.y) + R[8] * q.z);
+                m.pos[d.verts[i]] = d.roots[i] + rot;
+            }
+        } else if (s.curTime >= d.deformationStartTime && (s.curTime < d.deformationEndTime || d.deformationEndTime < 0)) {
+            for (int v : d.verts) m.pos[v] += d.speed * s.dt;
+        }
+    }
+}
+
 static void cloth_iteration(ClothScene& s, int iIter, float& omega) {
     s.iIter = iIter;
+    if (iIter == 0) apply_deformers(s);
     if (iIter == 0) for (int i = 0; i < s.numSim; i++) std::fill(s.meshes[i].activeCollisionMask.begin(), s.meshes[i].activeCollisionMask.end(), 0);
     if (s.collisionDetectionRequired || iIter == 0) {
         if (s.phys.handleCollision) cloth_detect(s);

@@ -2,6 +2,7 @@
 vertexColoring json) — CPU: schema + file formats, with the oracle as the solver; GPU: the same scene through the product."""
 import json
 import os
+import subprocess
 
 import numpy as np
 import pytest
@@ -59,13 +60,15 @@ def test_scene_files_parse_and_drive_the_oracle(tmp_path):
     assert os.path.getsize(out) == 12 * (len(v) + len(sv))
 
 
-def test_deformers_are_refused_loudly(tmp_path):
+def test_collider_sequences_are_refused_loudly(tmp_path):
     m, p, _ = write_scene(str(tmp_path))
     pj = json.load(open(p))
-    pj["Deformers"] = [{"DeformerName": "Rotator"}]
+    pj["ColliderParams"] = {"ColliderMeshes": [{"path": "x"}]}
     json.dump(pj, open(p, "w"))
     with pytest.raises(NotImplementedError):
         cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 3 and "ColliderParams" in r.stderr
 
 
 @pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
@@ -94,8 +97,6 @@ def test_gpu_scene_from_files_matches_the_oracle(tmp_path):
 
 
 # ------------------------------------------------------------------------------------------------ C++ host (gaia_vbdcloth_b200)
-import subprocess  # noqa: E402
-
 CLOTH_HOST_BIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gaia_b200", "host", "gaia_vbdcloth_b200")
 
 
@@ -107,28 +108,20 @@ def test_cpp_cloth_host_dry_run_reads_the_schema(tmp_path):
             % (len(v) + len(sv), len(f) + len(sf))) in r.stdout
 
 
-def test_cpp_cloth_host_refuses_deformers_cpu_mode_and_missing_gpu(tmp_path):
+def test_cpp_cloth_host_refuses_cpu_mode_and_missing_gpu(tmp_path):
     m, p, _ = write_scene(str(tmp_path))
     r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "--CPU"], capture_output=True, text=True)
     assert r.returncode == 2 and "no CPU path" in r.stderr
     if not has_gpu():
         r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path)], capture_output=True, text=True)
         assert r.returncode == 3 and "gaia_b200_cloth_create failed" in r.stderr        # no silent CPU fallback
-    pj = json.load(open(p))
-    pj["Deformers"] = [{"DeformerName": "Rotator"}]
-    json.dump(pj, open(p, "w"))
-    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
-    assert r.returncode == 3 and "Deformers" in r.stderr
 
 
 @pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
 def test_cpp_cloth_host_reads_a_reference_experiment(tmp_path):
     d = ("/root/reference/Simulator/VBDCloth/ParameterGen/Parameters/S01_Twisting/"
          "C100_Twist_ContactR0.2_CStif100000.0_bd20_damping3e-05_relaxiation0.42_thick0.01_CDPerIter")
-    pj = json.load(open(d + "/Parameters.json"))
-    pj["Deformers"] = []                       # the twist itself is driven by deformers, which this host refuses
-    p = str(tmp_path / "Parameters.json")
-    json.dump(pj, open(p, "w"))
+    p = d + "/Parameters.json"                 # two Rotators twist the sheet
     r = subprocess.run([CLOTH_HOST_BIN, d + "/Models.json", p, "/tmp/unused", "-R", "/root/reference", "--dryRun"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     assert "10000 vertices, 19602 triangles" in r.stdout and "numSubsteps 5, iterations 10, contactRadius 0.2" in r.stdout
@@ -167,3 +160,58 @@ def test_cpp_cloth_host_frames_match_the_python_binding(tmp_path):
     b = np.fromfile(part / "A00000004.bin", np.float32)
     assert a.shape == b.shape and np.abs(a - b).max() < 1e-3
     g.close()
+
+
+def test_oracle_deformers_follow_the_reference_schedule():
+    """ClothDeformerRotator / ClothDeformerTranslater (M/VBDCloth/VBDClothDeformer.h:43-200) in the oracle: the selected
+    vertices become fixed, the rotator places them at root + R(curTime * w) RootP, the translator adds speed * dt per substep
+    while start <= curTime < end."""
+    n = 10
+    v, f = cloth.grid_cloth(n, 1.0, origin=(0, 1.0, 0))
+    phys = cloth.default_cloth_physics_params(numSubsteps=4, iterations=4, contactRadius=0.02, maxQueryDis=0.03, gravity=[0, 0, 0])
+    obj = cloth.default_cloth_object_params(density=0.2, miu=2e3, bendingStiffness=0.5, initializationType=2)
+    obj.lambda_ = 2e3
+    o = OracleClothScene(phys, threads=2)
+    o.add_tri_mesh(v, f, obj, cloth.grid_cloth_coloring(n))
+    left = np.nonzero(v[:, 0] < v[:, 0].min() + 1e-6)[0]
+    right = np.nonzero(v[:, 0] > v[:, 0].max() - 1e-6)[0]
+    o.add_rotator(0, left, [0, 1.0, 0], [1, 0, 0], 2.0, -1.0)
+    o.add_translator(0, right, [0.0, 0.6, 0.0], 0.0, 0.05)
+    o.finalize()
+    o.run_frames(6)
+    x = o.positions(0)
+    th = 2.0 * o.cur_time
+    assert abs(o.cur_time - 6 * phys.timeStep) < 1e-5
+    # reference quirk kept: root = ((P - o).axis) axis is a vector from o but is subtracted from the absolute P, so the
+    # turn is about the axis through the ORIGIN; `center` only enters through its component along the axis
+    ry, rz = v[left, 1], v[left, 2]
+    assert np.allclose(x[left, 0], v[left, 0], atol=1e-6)
+    assert np.allclose(x[left, 1], np.cos(th) * ry - np.sin(th) * rz, atol=2e-6)
+    assert np.allclose(x[left, 2], np.sin(th) * ry + np.cos(th) * rz, atol=2e-6)
+    dt = phys.timeStep / 4
+    steps = sum(1 for k in range(1, 25) if np.float32(k * dt) < 0.05)
+    assert np.allclose(x[right, 1] - v[right, 1], 0.6 * dt * steps, atol=1e-5)
+    assert np.isfinite(x).all() and np.abs(x - v).max() > 0.05
+    assert (o.velocities(0)[left] == 0).all()
+
+
+def test_scene_files_with_deformers_reach_the_solver(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path))
+    pj = json.load(open(p))
+    corner = [0, 9]
+    pj["Deformers"] = [{"DeformerName": "Translator", "speed": [0.0, 0.5, 0.0], "selectedMeshes": [0], "selectedVertices": [corner],
+                        "deformationEndTime": -1},
+                       {"DeformerName": "Rotator", "center": [0, 0.9, 0], "axis": [0, 1, 0], "angularVelocity": 1.0, "selectedMeshes": [0],
+                        "selectedVertices": [[90, 99]], "rotationEndTime": 60}]
+    json.dump(pj, open(p, "w"))
+    phys, meshes, pj2 = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, deformers=pj2["Deformers"], threads=2)
+    y0 = o.positions(0)[corner, 1].copy()
+    o.run_frames(2)
+    assert np.allclose(o.positions(0)[corner, 1] - y0, 0.5 * 2 * phys.timeStep, atol=1e-5)
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    pj["Deformers"].append({"DeformerName": "Bender", "selectedMeshes": [], "selectedVertices": []})
+    json.dump(pj, open(p, "w"))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 3 and "Unrecognized deformer" in r.stderr
