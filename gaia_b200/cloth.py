@@ -86,6 +86,7 @@ def bind_cloth_api(lib, prefix):
         "add_tri_mesh": ([P, C.c_int32, C.c_int32, C.c_int32, FP, IP, C.POINTER(ClothObjectParams), C.c_int32, IP, IP, C.c_int32, IP], C.c_int),
         "add_rotator": ([P, C.c_int, IP, C.c_int32, FP, FP, C.c_double, C.c_double], C.c_int),
         "add_translator": ([P, C.c_int, IP, C.c_int32, FP, C.c_float, C.c_float], C.c_int),
+        "set_collider_sequence": ([P, C.c_int, C.c_int32, IP, FP, C.c_int32, C.c_int32], C.c_int),
         "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
         "frame_id": ([P], C.c_int), "cur_time": ([P], C.c_double), "set_time": ([P, C.c_int32, C.c_double], C.c_int),
         "synchronize": ([P], C.c_int), "num_meshes": ([P], C.c_int), "mesh_sizes": ([P, C.c_int, IP, IP, IP], C.c_int),
@@ -138,6 +139,13 @@ class ClothSceneBase:
         """ClothDeformerTranslater on `verts` of `mesh` (they become fixed points); before finalize."""
         v = _i32(np.asarray(verts, np.int32)); sp = _f32(np.asarray(speed, np.float32))
         return self._call("add_translator", mesh, _ip(v), len(v), _fp(sp), float(start_time), float(end_time))
+
+    def set_collider_sequence(self, mesh, key_positions, key_frames=None, interpolate_substep=True, interpolate_iter=1):
+        """ColliderTrimeshSequence: key-frame meshes [nKeys, nV, 3] of collider `mesh` (added with simulated=False); before finalize."""
+        kp = _f32(np.asarray(key_positions, np.float32))
+        kf = _i32(np.asarray(key_frames, np.int32)) if key_frames is not None else None
+        return self._call("set_collider_sequence", mesh, kp.shape[0], _ip(kf) if kf is not None else None, _fp(kp),
+                          1 if interpolate_substep else 0, int(interpolate_iter))
 
     def finalize(self):
         self._call("finalize")

@@ -7,8 +7,8 @@ Mirrors what BaseClothPhsicsFramework does around the step (M/Framework/BaseClot
 initialize, simulate, writeOutputs): parameters keep the reference's names, meshes are loaded in file order (simulated
 models, a collider being a model whose vertices are all fixed, as S03 does it), frames are written as `A%08d.ply`
 (all meshes together, ASCII) or `A%08d.bin` (raw float32 positions). `Deformers` (Rotator / Translator,
-M/VBDCloth/VBDClothDeformer.h:202-242) are handed to the library. Not handled here, and refused loudly: `ColliderParams`
-mesh sequences.
+M/VBDCloth/VBDClothDeformer.h:202-242) and `ColliderParams.ColliderMeshes` of type "TriMeshSequence" (key-frame .obj files
+of one topology, M/SpatialQuery/ColiiderTriMeshSequence.h) are handed to the library; other collider types are refused.
 """
 import argparse
 import json
@@ -87,8 +87,9 @@ def load_cloth_scene_json(models_json, params_json, repo_root, allow_deformers=T
         mj = json.load(f)
     if pj.get("Deformers") and not allow_deformers:
         raise NotImplementedError("cloth Deformers refused by the caller")
-    if pj.get("ColliderParams", {}).get("ColliderMeshes"):
-        raise NotImplementedError("ColliderParams mesh sequences are outside this host; add the collider as a model with all vertices fixed")
+    for c in pj.get("ColliderParams", {}).get("ColliderMeshes", []) or []:
+        if c.get("colliderType") != "TriMeshSequence":
+            raise NotImplementedError(f"Unrecognized collider type: {c.get('colliderType')}")
     phys = cloth_physics_params_from_json(pj)
     meshes = []
     for m in mj["Models"]:
@@ -114,10 +115,37 @@ def add_deformers(scene, deformers):
                 raise ValueError(f"Unrecognized deformer: {name}")
 
 
-def build_scene(cls, phys, meshes, deformers=None, **kw):
+def load_collider_sequences(pj, repo_root):
+    """ColliderParams.ColliderMeshes -> [(key positions [nKeys, nV, 3], faces, ClothObjectParams, keyFrames | None,
+    interpolateSubstep, interpolateIter)] (ColliderTrimeshSequenceParams::fromJson)"""
+    out = []
+    for c in pj.get("ColliderParams", {}).get("ColliderMeshes", []) or []:
+        files = c.get("meshFiles", [])
+        kf = c.get("keyFrames") or None
+        if kf is not None and len(kf) > len(files):
+            kf = kf[:len(files)]
+        n = len(kf) if kf is not None else len(files)
+        if n == 0:
+            raise ValueError("collider sequence without mesh files")
+        keys, faces = [], None
+        for path in files[:n]:
+            v, f = load_obj(meshio.resolve_path(path, repo_root))
+            if faces is not None and (f.shape != faces.shape or len(v) != len(keys[0])):
+                raise ValueError("collider key frames must share one topology")
+            faces = f if faces is None else faces
+            keys.append(v)
+        out.append((np.stack(keys), faces, cloth_object_params_from_json(c), kf, bool(c.get("interpolateSubstep", True)),
+                    int(c.get("interpolateIter", 1))))
+    return out
+
+
+def build_scene(cls, phys, meshes, deformers=None, colliders=None, **kw):
     s = cls(phys, **kw)
     for v, f, obj, colors, fixed, v0 in meshes:
         s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=True)
+    for keys, faces, obj, kf, sub, it in colliders or []:
+        cid = s.add_tri_mesh(keys[0], faces, obj, simulated=False)
+        s.set_collider_sequence(cid, keys, kf, sub, it)
     add_deformers(s, deformers)
     s.finalize()
     for i, (v, f, obj, colors, fixed, v0) in enumerate(meshes):
@@ -146,7 +174,8 @@ def simulate(models_json, params_json, out_dir, repo_root=".", frames=None, devi
     n = int(pp.get("numFrames", 1)) if frames is None else frames
     ext = pp.get("outputExt", "ply")
     os.makedirs(out_dir, exist_ok=True)
-    s = build_scene(cloth.ClothScene, phys, meshes, deformers=pj.get("Deformers"), device=device)
+    s = build_scene(cloth.ClothScene, phys, meshes, deformers=pj.get("Deformers"), colliders=load_collider_sequences(pj, repo_root),
+                    device=device)
     write_frame(s, meshes, out_dir, 0, ext)
     for fr in range(1, n + 1):
         s.run_frames(1)

@@ -1172,6 +1172,17 @@ static __global__ void k_deform_translate(int n, const int32_t* __restrict__ sid
     pos[s] = p;
 }
 
+// ColliderTrimeshSequence::update / set_state (M/SpatialQuery/ColiiderTriMeshSequence.h:59-129): positions = prev * (1 - t) + next * t
+static __global__ void k_collider_lerp(int n, const float4* __restrict__ a, const float4* __restrict__ b, float t, float4* pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 A = a[i], B = b[i];
+    const float w = 1 - t;
+    float4 p = pos[i];
+    p.x = A.x * w + B.x * t; p.y = A.y * w + B.y * t; p.z = A.z * w + B.z * t;
+    pos[i] = p;
+}
+
 static __global__ void k_update_velocity(int n, StepP P, const float4* __restrict__ pos, const float4* __restrict__ prev, float4* vel,
                                          const int32_t* __restrict__ info, const MeshDev* __restrict__ mt) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1266,10 +1277,11 @@ struct ClothScene {
     StepP P;
     bool collisionDetectionRequired = false;
     int64_t substepsTaken = 0;
-    int frameId = 0;
+    int frameId = 0, substep = 0;
     float curTime = 0.f;                // += dt every substep, like the framework's curTime (float accumulation)
     struct DeformerDev { DevBuf<int32_t> sid; DevBuf<float4> root, rootP; };
     std::vector<DeformerDev> deformerDev;   // one per h.deformers entry
+    std::vector<DevBuf<float4>> colliderKeyDev;   // one per h.colliderSeqs entry: nKeys x nV positions
     bool detectedOnce = false;
     gaia_cloth_stats stats;
     bool profiling = false;
@@ -1314,6 +1326,19 @@ static cudaError_t upload_deformers(ClothScene& s) {
         }
         CK(upload(s.deformerDev[i].sid, sid));
         if (d.type == 0) { CK(upload(s.deformerDev[i].root, root)); CK(upload(s.deformerDev[i].rootP, rootP)); }
+    }
+    s.colliderKeyDev.clear();
+    s.colliderKeyDev.resize(s.h.colliderSeqs.size());
+    for (size_t q = 0; q < s.h.colliderSeqs.size(); q++) {
+        const ColliderSequence& c = s.h.colliderSeqs[q];
+        const ClothMesh& m = s.h.meshes[c.mesh];
+        std::vector<float4> keys(c.keyFrames.size() * (size_t)m.nV);
+        for (size_t k = 0; k < c.keyFrames.size(); k++)
+            for (int v = 0; v < m.nV; v++) {          // colliders keep their vertex order in the sorted arrays
+                const float* p = &c.keyPos[(k * (size_t)m.nV + v) * 3];
+                keys[k * (size_t)m.nV + (m.sortedId[v] - m.sortedId[0])] = make_float4(p[0], p[1], p[2], 0.f);
+            }
+        CK(upload(s.colliderKeyDev[q], keys));
     }
     return cudaSuccess;
 }
@@ -1558,6 +1583,54 @@ static void apply_deformers(ClothScene& s) {
     }
 }
 
+// DynamicCollider::updateColliderMeshes (M/SpatialQuery/DynamicCollider.h:39-50) over the key-frame sequences; returns
+// true when a collider moved (collision detection is then required, VBDClothPhysics.cpp:415-418)
+static bool update_colliders(ClothScene& s, int substep, int iIter) {
+    bool any = false;
+    const int numSubsteps = s.h.phys.numSubsteps;
+    for (size_t q = 0; q < s.h.colliderSeqs.size(); q++) {
+        ColliderSequence& c = s.h.colliderSeqs[q];
+        const ClothMesh& m = s.h.meshes[c.mesh];
+        const int nV = m.nV, frameId = s.frameId;
+        float4* dst = s.pos.p + m.sortedId[0];
+        const float4* keys = s.colliderKeyDev[q].p;
+        auto key = [&](size_t k) { return keys + k * (size_t)nV; };
+        auto lerp = [&](size_t k0, size_t k1, float t) {
+            k_collider_lerp<<<nblk(nV), kB, 0, s.stream>>>(nV, key(k0), key(k1), t, dst);
+            s.stats.kernelLaunches++;
+        };
+        const std::vector<int32_t>& kf = c.keyFrames;
+        bool updated = false;
+        if (c.firstTime) {            // set_state(frameId)
+            c.firstTime = false;
+            if (frameId < kf.front()) lerp(0, 0, 0.f);
+            else if (frameId >= kf.back()) lerp(kf.size() - 1, kf.size() - 1, 0.f);
+            else {
+                const size_t hi = std::upper_bound(kf.begin(), kf.end(), frameId) - kf.begin();
+                lerp(hi - 1, hi, float(frameId - kf[hi - 1]) / (kf[hi] - kf[hi - 1]));
+            }
+            updated = true;
+        } else if (!(frameId < kf.front() || frameId >= kf.back())) {
+            const size_t hi = std::upper_bound(kf.begin(), kf.end(), frameId) - kf.begin();
+            const int prevF = kf[hi - 1], numFrames = kf[hi] - prevF;
+            if (c.interpolateSubstep) {
+                if (iIter < c.interpolateIter) {
+                    float t = float(frameId - prevF) / numFrames;
+                    t += float(substep) / ((size_t)numSubsteps * numFrames);
+                    t += float(iIter) / ((size_t)c.interpolateIter * numSubsteps * numFrames);
+                    lerp(hi - 1, hi, t);
+                    updated = true;
+                }
+            } else if (substep == 0 && iIter == 0) {
+                lerp(hi - 1, hi, float(frameId - prevF) / numFrames);
+                updated = true;
+            }
+        }
+        any = any || updated;
+    }
+    return any;
+}
+
 static int iteration(ClothScene& s, int iIter, float& omega) {
     ClothHost& h = s.h;
     const int nSim = (int)h.nSimV;
@@ -1565,6 +1638,7 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
     auto cuda = [&](cudaError_t x) { if (x != cudaSuccess) { s.err = std::string("CUDA: ") + cudaGetErrorString(x); return false; } return true; };
     if (iIter == 0) apply_deformers(s);       // applyDeformers(), VBDClothPhysics.cpp:408-412
     if (iIter == 0 && nSim) if (!cuda(cudaMemsetAsync(s.activeMask.p, 0, nSim, s.stream))) return GAIA_ERR_CUDA;
+    if (!h.colliderSeqs.empty() && update_colliders(s, s.substep, iIter)) s.collisionDetectionRequired = true;
     cudaEvent_t evD0 = nullptr;
     if (s.collisionDetectionRequired || iIter == 0) {
         if (s.profiling) { evD0 = s.ev[0]; cudaEventRecord(s.ev[0], s.stream); }
@@ -1653,6 +1727,7 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
 static int run_substeps(ClothScene& s, int nSubsteps) {
     const int nSim = (int)s.h.nSimV;
     for (int sub = 0; sub < nSubsteps; sub++) {
+        s.substep = sub;
         s.curTime += s.h.dt;
         float omega = 1.f;
         for (int it = 0; it < s.h.phys.iterations; it++) { const int rc = iteration(s, it, omega); if (rc < 0) return rc; }
@@ -1796,6 +1871,35 @@ int gaia_b200_cloth_add_rotator(gaia_cloth_handle* h, int mesh, const int32_t* v
     h->s.h.deformers.push_back(std::move(d));
     return (int)h->s.h.deformers.size() - 1;
 }
+// ColliderTrimeshSequenceParams::fromJson + ColliderTrimeshSequence::initialize (M/SpatialQuery/ColiiderTriMeshSequence.h:13-41,
+// 131-144): key-frame meshes of a collider added with simulated = 0 (same topology), transformed like the mesh itself
+int gaia_b200_cloth_set_collider_sequence(gaia_cloth_handle* h, int mesh, int32_t nKeys, const int32_t* keyFrames, const float* xyz,
+                                          int32_t interpolateSubstep, int32_t interpolateIter) {
+    CREQ(h);
+    ClothScene& s = h->s;
+    if (s.finalized) return cfail(s, GAIA_ERR_STATE, "collider sequences are set before finalize");
+    if (mesh < 0 || mesh >= (int)s.h.meshes.size()) return cfail(s, GAIA_ERR_INVALID_ARG, "mesh id out of range");
+    const ClothMesh& m = s.h.meshes[mesh];
+    if (m.simulated) return cfail(s, GAIA_ERR_INVALID_ARG, "a key-frame sequence drives a collider (simulated = 0)");
+    if (nKeys < 1 || !xyz) return cfail(s, GAIA_ERR_INVALID_ARG, "bad key frames");
+    if (interpolateIter < 1) return cfail(s, GAIA_ERR_INVALID_ARG, "interpolateIter must be >= 1");
+    for (auto& c : s.h.colliderSeqs) if (c.mesh == mesh) return cfail(s, GAIA_ERR_STATE, "the collider already has a sequence");
+    ColliderSequence c;
+    c.mesh = mesh;
+    c.keyFrames.resize(nKeys);
+    for (int i = 0; i < nKeys; i++) c.keyFrames[i] = keyFrames ? keyFrames[i] : i;      // default: one key per frame
+    for (int i = 1; i < nKeys; i++) if (c.keyFrames[i] <= c.keyFrames[i - 1]) return cfail(s, GAIA_ERR_INVALID_ARG, "keyFrames should be in increasing order");
+    c.interpolateIter = interpolateIter;
+    c.interpolateSubstep = interpolateSubstep != 0 || interpolateIter > 1;
+    if (c.interpolateIter > std::max(1, s.h.phys.iterations)) return cfail(s, GAIA_ERR_INVALID_ARG, "interpolateIter exceeds the iterations of a substep");
+    for (int k = 0; k < nKeys; k++) {
+        std::vector<float> p(xyz + (size_t)k * 3 * m.nV, xyz + (size_t)(k + 1) * 3 * m.nV);
+        cloth_transform_points(m.obj, m.nV, p);
+        c.keyPos.insert(c.keyPos.end(), p.begin(), p.end());
+    }
+    s.h.colliderSeqs.push_back(std::move(c));
+    return GAIA_OK;
+}
 int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3],
                                    float deformationStartTime, float deformationEndTime) {
     CREQ(h);
@@ -1820,6 +1924,7 @@ int gaia_b200_cloth_run_iterations(gaia_cloth_handle* h, int32_t nIters) {
     CREQ(h); CFIN(h);
     CCUDA(h, cudaSetDevice(h->s.device));
     h->s.curTime += h->s.h.dt;
+    h->s.substep = 0;
     float omega = 1.f;
     for (int it = 0; it < nIters; it++) { const int rc = iteration(h->s, it, omega); if (rc < 0) return rc; }
     return GAIA_OK;

@@ -48,9 +48,21 @@ struct ClothDeformer {
     std::vector<float> roots, rootPs;  // rotator: 3 per selected vertex, from the positions at creation
 };
 
+// ColliderTrimeshSequence (M/SpatialQuery/ColiiderTriMeshSequence.h:4-151): key-frame meshes of one collider, interpolated
+// per frame / substep / iteration
+struct ColliderSequence {
+    int mesh = 0;
+    std::vector<int32_t> keyFrames;
+    std::vector<float> keyPos;         // nKeys * 3*nV, transformed like the mesh
+    bool interpolateSubstep = true;
+    int interpolateIter = 1;
+    bool firstTime = true;
+};
+
 struct ClothHost {
     gaia_cloth_physics_params phys;
     std::vector<ClothDeformer> deformers;
+    std::vector<ColliderSequence> colliderSeqs;
     float dt = 0.f, dtSqrReciprocal = 0.f;
     std::vector<ClothMesh> meshes;
     int numSim = 0;
@@ -65,6 +77,7 @@ struct ClothHost {
     int64_t nRecF = 0, nRecH = 0;
 };
 
+void cloth_transform_points(const gaia_cloth_object_params& obj, int32_t nV, std::vector<float>& pos);
 void cloth_mesh_init(ClothMesh& m, bool simulated, int32_t nV, int32_t nF, const float* xyz, const int32_t* faces,
                      const gaia_cloth_object_params& obj, int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
                      int32_t nFixed, const int32_t* fixed);

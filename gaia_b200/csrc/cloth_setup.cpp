@@ -132,24 +132,29 @@ void build_quadratic_forms(ClothMesh& m) {
 }
 }  // namespace
 
-void cloth_mesh_init(ClothMesh& m, bool simulated, int32_t nV, int32_t nF, const float* xyz, const int32_t* faces,
-                     const gaia_cloth_object_params& obj, int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
-                     int32_t nFixed, const int32_t* fixed) {
-    m.nV = nV; m.nF = nF; m.simulated = simulated; m.obj = obj;
-    m.pos0.assign(xyz, xyz + 3 * (size_t)nV);
-    m.faces.assign(faces, faces + 3 * (size_t)nF);
+// applyRotationScalingTranslation (M/TriMesh/TriMesh.cpp:113-132): axis-angle rotation, per-axis scale, translation
+void cloth_transform_points(const gaia_cloth_object_params& obj, int32_t nV, std::vector<float>& pos) {
     const F3 rot = f3(obj.rotation[0], obj.rotation[1], obj.rotation[2]);
     const float ang = norm(rot);
     if (ang > 1e-5f) {
         float R[3][3];
         rotation_matrix(ang, rot / ang, R);
         for (int v = 0; v < nV; v++) {
-            const F3 p = P(m.pos0, v);
-            for (int r = 0; r < 3; r++) m.pos0[3 * (size_t)v + r] = R[r][0] * p.x + R[r][1] * p.y + R[r][2] * p.z;
+            const F3 p = P(pos, v);
+            for (int r = 0; r < 3; r++) pos[3 * (size_t)v + r] = R[r][0] * p.x + R[r][1] * p.y + R[r][2] * p.z;
         }
     }
     for (int v = 0; v < nV; v++)
-        for (int d = 0; d < 3; d++) m.pos0[3 * (size_t)v + d] = m.pos0[3 * (size_t)v + d] * obj.scale[d] + obj.translation[d];
+        for (int d = 0; d < 3; d++) pos[3 * (size_t)v + d] = pos[3 * (size_t)v + d] * obj.scale[d] + obj.translation[d];
+}
+
+void cloth_mesh_init(ClothMesh& m, bool simulated, int32_t nV, int32_t nF, const float* xyz, const int32_t* faces,
+                     const gaia_cloth_object_params& obj, int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
+                     int32_t nFixed, const int32_t* fixed) {
+    m.nV = nV; m.nF = nF; m.simulated = simulated; m.obj = obj;
+    m.pos0.assign(xyz, xyz + 3 * (size_t)nV);
+    m.faces.assign(faces, faces + 3 * (size_t)nF);
+    cloth_transform_points(obj, nV, m.pos0);
     m.DmInv.assign(4 * (size_t)nF, 0.f); m.restArea.assign(nF, 0.f); m.mass.assign(nV, 0.f);
     for (int f = 0; f < nF; f++) {
         F3 n = raw_normal(m, f);

@@ -87,10 +87,24 @@ void VBDClothPhysicsB200::loadRunningparameters(std::string inModelInputFile, st
             deformers_.push_back(in);
         }
     }
-    if (const Value* cp = params.find("ColliderParams"))
+    if (const Value* cp = params.find("ColliderParams"))       // createColliderMesh, M/Framework/BaseClothSimPhsicsFramework.cpp:95-114
         if (const Value* cm = cp->find("ColliderMeshes"))
-            if (cm->is_array() && cm->size() > 0)
-                throw std::runtime_error("ColliderParams mesh sequences are outside this host; add the collider as a model with all vertices fixed");
+            for (auto& c : cm->arr) {
+                ColliderInput in;
+                std::string type;
+                c.get("colliderType", type);
+                if (type != "TriMeshSequence") throw std::runtime_error("Unrecognized collider type: " + type);
+                gaia_b200_cloth_default_object_params(&in.obj);
+                c.get_vec3("scale", in.obj.scale); c.get_vec3("rotation", in.obj.rotation); c.get_vec3("translation", in.obj.translation);
+                c.get("frictionDynamic", in.obj.frictionDynamic); c.get("frictionEpsV", in.obj.frictionEpsV);
+                if (const Value* mf = c.find("meshFiles")) for (auto& f : mf->arr) in.meshFiles.push_back(resolve(f.str));
+                c.get_ints("keyFrames", in.keyFrames);
+                c.get("interpolateSubstep", in.interpolateSubstep); c.get("interpolateIter", in.interpolateIter);
+                if (in.keyFrames.size() > in.meshFiles.size()) in.keyFrames.resize(in.meshFiles.size());
+                if (!in.keyFrames.empty()) in.meshFiles.resize(in.keyFrames.size());
+                if (in.meshFiles.empty()) throw std::runtime_error("collider sequence without mesh files");
+                colliders_.push_back(in);
+            }
     if (const Value* p = params.find("PhysicsParams")) {
         bool b;
         p->get_vec3("gravity", phys_.gravity);
@@ -182,6 +196,23 @@ void VBDClothPhysicsB200::initialize() {
                                                     m.fixedPoints.empty() ? nullptr : m.fixedPoints.data());
         check(rc, "gaia_b200_cloth_add_tri_mesh");
     }
+    for (auto& c : colliders_) {       // colliderTriMeshes come after the simulated meshes (triMeshesAll)
+        std::vector<float> keys;
+        HostTriMeshData first;
+        for (size_t k = 0; k < c.meshFiles.size(); k++) {
+            HostTriMeshData hm;
+            loadObj(c.meshFiles[k], hm);
+            if (k == 0) first = hm;
+            else if (hm.verts.size() != first.verts.size() || hm.faces.size() != first.faces.size()) throw std::runtime_error("collider key frames must share one topology");
+            keys.insert(keys.end(), hm.verts.begin(), hm.verts.end());
+        }
+        const int id = gaia_b200_cloth_add_tri_mesh(h_, 0, (int32_t)(first.verts.size() / 3), (int32_t)(first.faces.size() / 3), first.verts.data(),
+                                                    first.faces.data(), &c.obj, 0, nullptr, nullptr, 0, nullptr);
+        check(id, "gaia_b200_cloth_add_tri_mesh (collider)");
+        std::vector<int32_t> kf(c.keyFrames.begin(), c.keyFrames.end());
+        check(gaia_b200_cloth_set_collider_sequence(h_, id, (int32_t)c.meshFiles.size(), kf.empty() ? nullptr : kf.data(), keys.data(),
+                                                    c.interpolateSubstep ? 1 : 0, c.interpolateIter), "gaia_b200_cloth_set_collider_sequence");
+    }
     for (auto& d : deformers_)
         for (size_t i = 0; i < d.selectedMeshes.size(); i++) {
             const std::vector<int32_t>& v = d.selectedVertices[i];
@@ -228,7 +259,7 @@ void VBDClothPhysicsB200::simulate() {
 
 // writeAllToPLY / writeAllToBinary over baseTriMeshesForSimulation: all vertices and the mesh's own triangles
 void VBDClothPhysicsB200::writeOutputs(const std::string& outFolder, int frameId) {
-    const int nM = gaia_b200_cloth_num_meshes(h_);
+    const int nM = (int)models_.size();      // baseTriMeshesForSimulation: colliders are not written
     std::vector<std::vector<float>> pos(nM);
     for (int m = 0; m < nM; m++) {
         int32_t nV, nF, nE;
@@ -279,7 +310,7 @@ void VBDClothPhysicsB200::writeOutputs(const std::string& outFolder, int frameId
 }
 
 void VBDClothPhysicsB200::saveRecoveryState(const std::string& file, bool binary) {
-    const int nM = gaia_b200_cloth_num_meshes(h_);
+    const int nM = (int)models_.size();      // baseTriMeshesForSimulation: colliders are not written
     std::ofstream j(file);
     if (!j) throw std::runtime_error("cannot write " + file);
     j.precision(17);
@@ -325,7 +356,7 @@ void VBDClothPhysicsB200::recoverFromState(const std::string& stateFileIn) {
     const Value j = jsonmin::parse_file(stateFile);
     int frameId = -1; double curTime = 0; std::string format = "text";
     j.get("frameId", frameId); j.get("curTime", curTime); j.get("format", format);
-    const int nM = gaia_b200_cloth_num_meshes(h_);
+    const int nM = (int)models_.size();      // baseTriMeshesForSimulation: colliders are not written
     const Value* ms = j.find("meshesState");
     if (!ms) throw std::runtime_error("recovery state has no meshesState");
     if (format == "binary") {

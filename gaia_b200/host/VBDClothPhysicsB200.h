@@ -15,7 +15,8 @@
 //   TriMeshFEM::loadObj (triangle .obj)                                 M/TriMesh/TriMesh.cpp:15-111
 // Models are the simulated meshes (baseTriMeshesForSimulation); a collider is a model whose vertices are all fixed, as
 // S03_MultiLayerClothOnCollider.py writes it. `Deformers` (Rotator / Translator, M/VBDCloth/VBDClothDeformer.h) are passed
-// to the library. Refused loudly: `ColliderParams` mesh sequences (they replace collider positions from files every frame).
+// to the library, and so are `ColliderParams.ColliderMeshes` of type "TriMeshSequence" (key-frame .obj files of one topology,
+// M/SpatialQuery/ColiiderTriMeshSequence.h); other collider types are refused loudly.
 #pragma once
 #include <cstdint>
 #include <map>
@@ -41,6 +42,14 @@ struct ClothDeformerInput {
     float deformationStartTime = 0.f, deformationEndTime = -1.f;
     std::vector<int> selectedMeshes;
     std::vector<std::vector<int32_t>> selectedVertices;
+};
+
+struct ColliderInput {
+    gaia_cloth_object_params obj;
+    std::vector<std::string> meshFiles;
+    std::vector<int> keyFrames;
+    bool interpolateSubstep = true;
+    int interpolateIter = 1;
 };
 
 struct HostTriMeshData {
@@ -101,6 +110,7 @@ private:
     std::vector<HostTriMeshData> meshCache_;
     std::map<std::string, std::vector<std::vector<int32_t>>> colourings_;
     std::vector<ClothDeformerInput> deformers_;
+    std::vector<ColliderInput> colliders_;
     gaia_cloth_handle* h_ = nullptr;
     int frameId_ = 0;
     double curTime_ = 0.0;

@@ -134,6 +134,14 @@ int gaia_b200_cloth_add_rotator(gaia_cloth_handle* h, int mesh, const int32_t* v
                                 const float axis[3], double angularVelocity, double rotationEndTime);
 int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t* verts, int32_t n, const float speed[3],
                                    float deformationStartTime, float deformationEndTime);
+/* Key-frame sequence of a collider mesh (ColliderParams.ColliderMeshes[i] with colliderType "TriMeshSequence":
+ * ColliderTrimeshSequenceParams / ColliderTrimeshSequence, M/SpatialQuery/ColiiderTriMeshSequence.h:4-151). `mesh` was added
+ * with simulated = 0; xyz holds nKeys meshes of its topology (nKeys * 3*nV floats, transformed like the mesh); keyFrames are
+ * increasing frame ids (NULL: 0, 1, 2, ...). Every iteration the collider is moved to prev * (1 - t) + next * t with the
+ * reference's t (per frame; per substep when interpolateSubstep; per iteration for the first interpolateIter iterations),
+ * and a moved collider triggers collision detection (VBDClothPhysics.cpp:413-418). Before finalize. */
+int gaia_b200_cloth_set_collider_sequence(gaia_cloth_handle* h, int mesh, int32_t nKeys, const int32_t* keyFrames, const float* xyz,
+                                          int32_t interpolateSubstep, int32_t interpolateIter);
 /* finalize: VBDClothSimulationFramework::initialize (parallel groups :72-138, contact detector) */
 int gaia_b200_cloth_finalize(gaia_cloth_handle* h);
 

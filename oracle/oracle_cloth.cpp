@@ -140,6 +140,35 @@ static void build_bending_forms(TriMesh& m) {
 
 // TriMeshFEM::initialize + applyRotationScalingTranslation + computeRestposeTrianglesFrom3D (M/TriMesh/TriMesh.cpp:15-132,
 // 213-244), VBDBaseTriMesh::initialize (M/VBDCloth/VBDBaseTriMesh.cpp:28-58), VBDTriMeshStVk::initialize
+// applyRotationScalingTranslation (M/TriMesh/TriMesh.cpp:113-132): rotation (axis-angle), scale, translation
+void cloth_transform_points(const gaia_cloth_object_params& obj, std::vector<V3>& pos) {
+    const V3 rot(obj.rotation[0], obj.rotation[1], obj.rotation[2]);
+    const float ang = norm(rot);
+    if (ang > CMP_EPSILON) {
+        M3 R; cloth_angle_axis(ang, rot / ang, R);
+        for (auto& p : pos) p = V3(R(0, 0) * p.x + R(0, 1) * p.y + R(0, 2) * p.z, R(1, 0) * p.x + R(1, 1) * p.y + R(1, 2) * p.z,
+                                   R(2, 0) * p.x + R(2, 1) * p.y + R(2, 2) * p.z);
+    }
+    for (auto& p : pos) p = V3(p.x * obj.scale[0] + obj.translation[0], p.y * obj.scale[1] + obj.translation[1], p.z * obj.scale[2] + obj.translation[2]);
+}
+
+// ColliderTrimeshSequence::initialize (M/SpatialQuery/ColiiderTriMeshSequence.h:131-144)
+void cloth_set_collider_sequence(ClothScene& s, int mesh, int nKeys, const int32_t* keyFrames, const float* xyz, bool interpolateSubstep, int interpolateIter) {
+    const TriMesh& m = s.meshes[mesh];
+    ColliderSequence c;
+    c.mesh = mesh;
+    for (int i = 0; i < nKeys; i++) c.keyFrames.push_back(keyFrames ? keyFrames[i] : i);
+    c.interpolateIter = interpolateIter;
+    c.interpolateSubstep = interpolateSubstep || interpolateIter > 1;
+    for (int k = 0; k < nKeys; k++) {
+        std::vector<V3> p(m.nV);
+        for (int v = 0; v < m.nV; v++) p[v] = V3(xyz[((size_t)k * m.nV + v) * 3], xyz[((size_t)k * m.nV + v) * 3 + 1], xyz[((size_t)k * m.nV + v) * 3 + 2]);
+        cloth_transform_points(m.obj, p);
+        c.keyPos.push_back(p);
+    }
+    s.colliderSeqs.push_back(c);
+}
+
 void cloth_mesh_initialize(TriMesh& m, bool simulated, int nV, int nF, const float* xyz, const int32_t* faces,
                            const gaia_cloth_object_params& obj, int nColors, const int32_t* colorOffsets, const int32_t* colorVerts,
                            int nFixed, const int32_t* fixed) {
@@ -147,15 +176,7 @@ void cloth_mesh_initialize(TriMesh& m, bool simulated, int nV, int nF, const flo
     m.pos.resize(nV);
     for (int i = 0; i < nV; i++) m.pos[i] = V3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
     m.faces.assign(faces, faces + 3 * nF);
-    // rotation (axis-angle), scale, translation
-    const V3 rot(obj.rotation[0], obj.rotation[1], obj.rotation[2]);
-    const float ang = norm(rot);
-    if (ang > CMP_EPSILON) {
-        M3 R; cloth_angle_axis(ang, rot / ang, R);
-        for (auto& p : m.pos) p = V3(R(0, 0) * p.x + R(0, 1) * p.y + R(0, 2) * p.z, R(1, 0) * p.x + R(1, 1) * p.y + R(1, 2) * p.z,
-                                     R(2, 0) * p.x + R(2, 1) * p.y + R(2, 2) * p.z);
-    }
-    for (auto& p : m.pos) p = V3(p.x * obj.scale[0] + obj.translation[0], p.y * obj.scale[1] + obj.translation[1], p.z * obj.scale[2] + obj.translation[2]);
+    cloth_transform_points(obj, m.pos);
     m.prev.assign(nV, V3()); m.vel.assign(nV, V3()); m.velPrev.assign(nV, V3()); m.inertia.assign(nV, V3());
     m.accel.assign(nV, V3()); m.next = m.pos; m.posAtCD.assign(nV, V3()); m.prevIter = m.pos;
     // rest pose from the 3-D triangles

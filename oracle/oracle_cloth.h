@@ -76,9 +76,20 @@ struct ClothDeformer {
     std::vector<V3> roots, rootPs;
 };
 
+// ColliderTrimeshSequence (M/SpatialQuery/ColiiderTriMeshSequence.h:4-151)
+struct ColliderSequence {
+    int mesh = 0;
+    std::vector<int> keyFrames;
+    std::vector<std::vector<V3>> keyPos;
+    bool interpolateSubstep = true;
+    int interpolateIter = 1;
+    bool firstTime = true;
+};
+
 struct ClothScene {
     gaia_cloth_physics_params phys;
     std::vector<ClothDeformer> deformers;
+    std::vector<ColliderSequence> colliderSeqs;
     float dt = 0.f, dtSqrReciprocal = 0.f;
     std::vector<TriMesh> meshes;
     int numSim = 0;
@@ -100,6 +111,8 @@ void cloth_finalize(ClothScene& s);
 void cloth_add_rotator(ClothScene& s, int mesh, const int32_t* verts, int n, const float center[3], const float axis[3],
                        double angularVelocity, double rotationEnd);
 void cloth_add_translator(ClothScene& s, int mesh, const int32_t* verts, int n, const float speed[3], float tStart, float tEnd);
+void cloth_set_collider_sequence(ClothScene& s, int mesh, int nKeys, const int32_t* keyFrames, const float* xyz, bool interpolateSubstep, int interpolateIter);
+void cloth_transform_points(const gaia_cloth_object_params& obj, std::vector<V3>& pos);
 void cloth_detect(ClothScene& s);
 void cloth_run_substeps(ClothScene& s, int nSubsteps);
 void cloth_run_iterations(ClothScene& s, int nIters);

@@ -40,6 +40,13 @@ int oracle_cloth_add_rotator(void* h, int mesh, const int32_t* verts, int32_t n,
     cloth_add_rotator(*s, mesh, verts, n, center, axis, angularVelocity, rotationEndTime);
     return (int)s->deformers.size() - 1;
 }
+int oracle_cloth_set_collider_sequence(void* h, int mesh, int32_t nKeys, const int32_t* keyFrames, const float* xyz, int32_t interpolateSubstep,
+                                       int32_t interpolateIter) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized || mesh < 0 || mesh >= (int)s->meshes.size() || s->meshes[mesh].simulated) return GAIA_ERR_STATE;
+    cloth_set_collider_sequence(*s, mesh, nKeys, keyFrames, xyz, interpolateSubstep != 0, interpolateIter);
+    return GAIA_OK;
+}
 int oracle_cloth_add_translator(void* h, int mesh, const int32_t* verts, int32_t n, const float* speed, float tStart, float tEnd) {
     ClothScene* s = (ClothScene*)h;
     if (s->finalized || mesh < 0 || mesh >= (int)s->meshes.size()) return GAIA_ERR_STATE;

@@ -394,10 +394,55 @@ static void apply_deformers(ClothScene& s) {
     }
 }
 
+// DynamicCollider::updateColliderMeshes -> ColliderTrimeshSequence::update / set_state
+// (M/SpatialQuery/ColiiderTriMeshSequence.h:59-129); true when a collider moved
+static bool update_colliders(ClothScene& s) {
+    bool any = false;
+    const int numSubsteps = s.phys.numSubsteps;
+    for (ColliderSequence& c : s.colliderSeqs) {
+        TriMesh& m = s.meshes[c.mesh];
+        const int frameId = s.frameId;
+        const std::vector<int>& kf = c.keyFrames;
+        auto lerp = [&](size_t k0, size_t k1, float t) {
+            const float w = 1 - t;
+            for (int v = 0; v < m.nV; v++) m.pos[v] = c.keyPos[k0][v] * w + c.keyPos[k1][v] * t;
+        };
+        bool updated = false;
+        if (c.firstTime) {
+            c.firstTime = false;
+            if (frameId < kf.front()) lerp(0, 0, 0.f);
+            else if (frameId >= kf.back()) lerp(kf.size() - 1, kf.size() - 1, 0.f);
+            else {
+                const size_t hi = std::upper_bound(kf.begin(), kf.end(), frameId) - kf.begin();
+                lerp(hi - 1, hi, float(frameId - kf[hi - 1]) / (kf[hi] - kf[hi - 1]));
+            }
+            updated = true;
+        } else if (!(frameId < kf.front() || frameId >= kf.back())) {
+            const size_t hi = std::upper_bound(kf.begin(), kf.end(), frameId) - kf.begin();
+            const int prevF = kf[hi - 1], numFrames = kf[hi] - prevF;
+            if (c.interpolateSubstep) {
+                if (s.iIter < c.interpolateIter) {
+                    float t = float(frameId - prevF) / numFrames;
+                    t += float(s.substep) / ((size_t)numSubsteps * numFrames);
+                    t += float(s.iIter) / ((size_t)c.interpolateIter * numSubsteps * numFrames);
+                    lerp(hi - 1, hi, t);
+                    updated = true;
+                }
+            } else if (s.substep == 0 && s.iIter == 0) {
+                lerp(hi - 1, hi, float(frameId - prevF) / numFrames);
+                updated = true;
+            }
+        }
+        any = any || updated;
+    }
+    return any;
+}
+
 static void cloth_iteration(ClothScene& s, int iIter, float& omega) {
     s.iIter = iIter;
     if (iIter == 0) apply_deformers(s);
     if (iIter == 0) for (int i = 0; i < s.numSim; i++) std::fill(s.meshes[i].activeCollisionMask.begin(), s.meshes[i].activeCollisionMask.end(), 0);
+    if (!s.colliderSeqs.empty() && update_colliders(s)) s.collisionDetectionRequired = true;     // VBDClothPhysics.cpp:413-418
     if (s.collisionDetectionRequired || iIter == 0) {
         if (s.phys.handleCollision) cloth_detect(s);
         else for (int i = 0; i < s.numSim; i++) std::fill(s.meshes[i].bounds.begin(), s.meshes[i].bounds.end(), std::numeric_limits<float>::max());

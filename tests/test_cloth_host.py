@@ -60,15 +60,39 @@ def test_scene_files_parse_and_drive_the_oracle(tmp_path):
     assert os.path.getsize(out) == 12 * (len(v) + len(sv))
 
 
-def test_collider_sequences_are_refused_loudly(tmp_path):
-    m, p, _ = write_scene(str(tmp_path))
+def add_collider_sequence(tmp, p, sv, sf, collider_type="TriMeshSequence"):
+    """ColliderParams as the cloth parameter scripts write them (S03_MultiLayerClothOnCollider.py:14-35, 143-145)"""
+    files = []
+    for k, dy in enumerate((0.0, 0.2, 0.25)):
+        name = os.path.join(tmp, "mover%d.obj" % k)
+        cloth_host.save_obj(name, sv + np.float32([0.05 * k, dy, 0]), sf)
+        files.append("${REPO_ROOT}\\mover%d.obj" % k)
     pj = json.load(open(p))
-    pj["ColliderParams"] = {"ColliderMeshes": [{"path": "x"}]}
+    pj["ColliderParams"] = {"ColliderMeshes": [{"colliderType": collider_type, "path": files[0], "meshFiles": files, "keyFrames": [0, 2, 4],
+                                                "interpolateSubstep": True, "interpolateIter": 2, "scale": [1, 1, 1], "rotation": [0, 0, 0],
+                                                "translation": [0.0, 0.35, 0.0], "frictionDynamic": 0.3}]}
     json.dump(pj, open(p, "w"))
+
+
+def test_collider_sequence_from_scene_files(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path))
+    add_collider_sequence(str(tmp_path), p, sv, sf)
+    phys, meshes, pj = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    cols = cloth_host.load_collider_sequences(pj, str(tmp_path))
+    assert len(cols) == 1 and cols[0][0].shape == (3, len(sv), 3) and cols[0][3] == [0, 2, 4] and cols[0][5] == 2
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, colliders=cols, threads=2)
+    assert o.num_meshes == 3
+    y0 = o.positions(2)[:, 1].mean()
+    o.run_frames(3)
+    y3 = o.positions(2)[:, 1].mean()
+    assert abs(y0 - (sv[:, 1].mean() + 0.35)) < 1e-5 and 0.2 < y3 - y0 < 0.25          # between key 1 (frame 2) and key 2 (frame 4)
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    add_collider_sequence(str(tmp_path), p, sv, sf, collider_type="Implicit")
     with pytest.raises(NotImplementedError):
         cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
     r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
-    assert r.returncode == 3 and "ColliderParams" in r.stderr
+    assert r.returncode == 3 and "Unrecognized collider type" in r.stderr
 
 
 @pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
@@ -132,12 +156,16 @@ def test_cpp_cloth_host_frames_match_the_python_binding(tmp_path):
     m, p, (v, f, sv, sf) = write_scene(str(tmp_path), frames=4)
     pj = json.load(open(p))
     pj["PhysicsParams"].update(outputExt="bin", binaryModeVisualizationSteps=2, outputRecoveryStateStep=2, outputStatistics=True)
+    pj["Deformers"] = [{"DeformerName": "Translator", "speed": [0.0, 0.3, 0.0], "selectedMeshes": [0], "selectedVertices": [[0, 9]],
+                        "deformationEndTime": -1}]
     json.dump(pj, open(p, "w"))
+    add_collider_sequence(str(tmp_path), p, sv, sf)
     out = tmp_path / "out"
     r = subprocess.run([CLOTH_HOST_BIN, m, p, str(out), "-R", str(tmp_path)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr + r.stdout
-    phys, meshes, _ = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
-    g = cloth_host.build_scene(cloth.ClothScene, phys, meshes)
+    phys, meshes, pj = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    g = cloth_host.build_scene(cloth.ClothScene, phys, meshes, deformers=pj["Deformers"],
+                               colliders=cloth_host.load_collider_sequences(pj, str(tmp_path)))
     for fr in range(5):
         if fr:
             g.run_frames(1)

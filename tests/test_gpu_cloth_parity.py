@@ -350,3 +350,77 @@ def test_twisted_strip_self_contact_sets_match_from_the_same_state():
         assert np.array_equal(g.conservative_bounds(0), o.conservative_bounds(0)), chunk
         seen_vf = max(seen_vf, len(vf)); seen_ee = max(seen_ee, len(g.ee_contacts()))
     assert seen_vf > 20 and seen_ee > 20, (seen_vf, seen_ee)          # the strip really wrung itself into contact
+
+
+def moving_collider_scene(interpolate_substep=True, interpolate_iter=1, key_frames=(0, 4, 8)):
+    """a pinned sheet and a sphere collider played from three key-frame meshes (rises into the sheet, then moves sideways)"""
+    n = 15
+    v, f = cloth.grid_cloth(n, 1.0, origin=(0, 0.9, 0))
+    sv, sf = cloth.icosphere(0.25, 2, center=(0, 0.0, 0))
+    keys = np.stack([sv + np.float32([0, 0.45, 0]), sv + np.float32([0, 0.68, 0]), sv + np.float32([0.15, 0.68, 0.05])])
+    pk = dict(numSubsteps=4, iterations=6, contactRadius=0.02, maxQueryDis=0.03, contactStiffness=1e5, thickness=1e-3)
+
+    def build(cls, kw):
+        s = cls(cloth.default_cloth_physics_params(**pk), **kw)
+        obj = cloth.default_cloth_object_params(density=0.2, miu=2e3, bendingStiffness=0.5, dampingStVK=1e-6, dampingBending=1e-6)
+        obj.lambda_ = 2e3
+        s.add_tri_mesh(v, f, obj, cloth.grid_cloth_coloring(n), fixed=[0, n - 1, n * (n - 1), n * n - 1])
+        cid = s.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(frictionDynamic=0.3, scale=[1.1, 1.0, 0.9], translation=[0.02, 0, 0]),
+                             simulated=False)
+        s.set_collider_sequence(cid, keys, key_frames, interpolate_substep, interpolate_iter)
+        return s
+    g, o = pair(build)
+    return g, o, keys
+
+
+@pytest.mark.parametrize("mode", [(True, 1), (True, 3), (False, 1)])
+def test_key_framed_collider_is_played_like_the_oracle(mode, monkeypatch):
+    """A sphere played from key frames rams a pinned sheet (1.4 cm per substep against a 2 cm contact radius: vertices hit
+    their conservative bounds and detection re-runs mid-substep, so rounding differences are amplified at once). The bar is
+    the exact-order kernels, which must reproduce the oracle bit for bit - collider motion, contact response, friction and
+    all; the default tree-summation kernels are only held to the same gross motion (mean deviation <= 2e-3, max <= 3e-2)."""
+    g, o, keys = moving_collider_scene(*mode)
+    monkeypatch.setenv("GAIA_B200_CLOTH_EXACT_ORDER", "1")
+    gx, _, _ = moving_collider_scene(*mode)
+    seen = 0
+    for fr in range(10):
+        g.run_frames(1); o.run_frames(1); gx.run_frames(1)
+        assert np.array_equal(g.positions(1), o.positions(1)), fr           # same interpolation arithmetic on both sides
+        assert np.array_equal(gx.positions(0), o.positions(0)), fr
+        d = np.abs(g.positions(0) - o.positions(0))
+        assert d.max() < 3e-2 and d.mean() < 2e-3, (fr, d.max(), d.mean())
+        seen = max(seen, g.stats()["numContactsVF"])
+    assert np.array_equal(gx.velocities(0), o.velocities(0))
+    assert gx.stats()["numberCollisionDetection"] == o.stats()["numberCollisionDetection"]
+    # past the last key frame the collider stays where the last interpolation left it (the reference never snaps to the last
+    # key): within one interpolation step of the last mesh, transformed like the collider mesh itself
+    last = keys[2] * np.float32([1.1, 1.0, 0.9]) + np.float32([0.02, 0, 0])
+    assert np.abs(g.positions(1) - last).max() < 0.17 / 4 + 1e-6
+    assert seen > 0                                                       # the sphere really pushed into the sheet
+    pg = g.positions(0)
+    assert pg[:, 1].max() > 0.93 and np.isfinite(pg).all()
+    o.set_state(0, pg, g.velocities(0))
+    g.detect_contacts(); o.detect_contacts()
+    assert np.array_equal(g.vf_contacts(), o.vf_contacts()) and np.array_equal(g.ee_contacts(), o.ee_contacts())
+
+
+def test_collider_sequence_argument_checks():
+    v, f = cloth.grid_cloth(6, 1.0)
+    sv, sf = cloth.icosphere(0.2, 1)
+    s = cloth.ClothScene(cloth.default_cloth_physics_params(iterations=4, contactRadius=0.02, maxQueryDis=0.03))
+    s.add_tri_mesh(v, f, cloth.default_cloth_object_params(translation=[0, 1.0, 0]), cloth.grid_cloth_coloring(6))
+    c = s.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(), simulated=False)
+    with pytest.raises(cloth.GaiaError):
+        s.set_collider_sequence(0, np.stack([v, v]))                      # a simulated mesh is not a collider
+    with pytest.raises(cloth.GaiaError):
+        s.set_collider_sequence(c, np.stack([sv, sv]), key_frames=[3, 3])  # key frames must increase
+    with pytest.raises(cloth.GaiaError):
+        s.set_collider_sequence(c, np.stack([sv, sv]), interpolate_iter=9)
+    s.set_collider_sequence(c, np.stack([sv, sv + 0.1]))
+    with pytest.raises(cloth.GaiaError):
+        s.set_collider_sequence(c, np.stack([sv, sv]))                    # one sequence per collider
+    s.finalize()
+    s.run_frames(2)
+    x = s.positions(1) - sv                                                # frame 0 interpolates towards key 1, frame 1 is past it
+    assert (x > 0.07).all() and (x < 0.1 + 1e-6).all()
+    s.close()
