@@ -140,6 +140,9 @@ def build_scene(cls, wl, **kw):
         s.finalize()
         return s
     s = cls(wl["phys"], wl["col"], **kw)
+    if cls is capi.Scene and len(wl["meshes"]) > 1:      # many-object scenes: the rule the sharded builder applies too
+        from gaia_b200.multigpu import scene_solver_lanes
+        s.set_solver_lanes(scene_solver_lanes([m[3] for m in wl["meshes"]]))
     for v, t, obj, colors, fixed in wl["meshes"]:
         s.add_tet_mesh(v, t, obj, colors, fixed)
     for d in wl["deformers"]:

@@ -348,6 +348,7 @@ def load_library(path=None):
     lib.gaia_b200_set_time.argtypes = [P, C.c_int32, C.c_double]
     lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
+    lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
         getattr(lib, "gaia_b200_" + f).restype = None
@@ -441,6 +442,10 @@ class Scene(SceneBase):
 
     def set_profiling(self, on=True):
         self._call("set_profiling", int(on))
+
+    def set_solver_lanes(self, lanes):
+        """0 (default 4), 4 or 8 lanes per vertex; runs compared bit for bit must use the same value"""
+        self._call("set_solver_lanes", int(lanes))
 
     @property
     def cuda_stream(self):

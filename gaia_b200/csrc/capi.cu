@@ -417,6 +417,13 @@ int gaia_b200_reset_stats(gaia_handle* h) {
     return GAIA_OK;
 }
 int gaia_b200_set_profiling(gaia_handle* h, int enabled) { REQUIRE(h); h->s.profiling = enabled != 0; return GAIA_OK; }
+int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
+    REQUIRE(h);
+    if (lanes != 0 && lanes != 4 && lanes != 8) return fail(h->s, GAIA_ERR_INVALID_ARG, "solver lanes: 0 (default), 4 or 8");
+    if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }
+    h->s.solveLanes = lanes;
+    return GAIA_OK;
+}
 void* gaia_b200_cuda_stream(gaia_handle* h) { return h ? (void*)h->s.stream : nullptr; }
 
 }  // extern "C"

@@ -123,6 +123,7 @@ struct Scene {
     // CUDA graph of the colour loop of one substep (solve.cu: solve_iterations)
     cudaGraphExec_t iterGraphExec = nullptr;
     int iterGraphIters = -1, iterCalls = 0;
+    int solveLanes = 0;   // lanes per vertex of the colour sweep outside the fused-halo path: 0 = default (4), 4 or 8
     int64_t iterDelta[4] = {0, 0, 0, 0};
 
     // statistics / profiling

@@ -730,9 +730,9 @@ static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int apply
 }
 
 static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD, bool captured = false) {
-    static bool envRead = false;
+    static bool envRead = false, lanesFromEnv = false;
     if (!envRead) {
-        const char* e = getenv("GAIA_B200_LANES"); if (e) g_lanes = atoi(e);
+        const char* e = getenv("GAIA_B200_LANES"); if (e) { g_lanes = atoi(e); lanesFromEnv = true; }
         e = getenv("GAIA_B200_VARIANT"); if (e) g_variant = atoi(e);
         envRead = true;
     }
@@ -788,8 +788,9 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             if (s.profiling) cudaEventRecord(s.evA, s.stream);
             hv.epochOffset = it * G + g;
             if (ve > vb) {
-                if (hasContacts) launch_solve<true>(s, g_lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
-                else launch_solve<false>(s, g_lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
+                const int lanes = (s.solveLanes && !lanesFromEnv) ? s.solveLanes : g_lanes;
+                if (hasContacts) launch_solve<true>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
+                else launch_solve<false>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
             }
             if (s.profiling) {
                 cudaEventRecord(s.evB, s.stream);

@@ -213,6 +213,16 @@ void VBDPhysicsB200::initialize() {
             else check(gaia_b200_add_translator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.speed, d.endTime), "gaia_b200_add_translator");
         }
     check(gaia_b200_finalize(h_), "gaia_b200_finalize");
+    // single-GPU driver: 8 lanes per vertex when every parallel group is small (see gaia_b200_set_solver_lanes)
+    if (models_.size() > 1) {
+        int32_t largest = 0;
+        for (int g = 0; g < gaia_b200_num_parallel_groups(h_); g++) {
+            int32_t n = 0;
+            check(gaia_b200_get_parallel_group(h_, g, nullptr, &n), "gaia_b200_get_parallel_group");
+            largest = n > largest ? n : largest;
+        }
+        check(gaia_b200_set_solver_lanes(h_, largest < 65536 ? 8 : 4), "gaia_b200_set_solver_lanes");
+    }
     frameId_ = 0;
 }
 

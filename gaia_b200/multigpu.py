@@ -181,6 +181,18 @@ def global_groups(color_lists):
     return out
 
 
+def scene_solver_lanes(color_lists, small=65536):
+    """Lanes per vertex of the colour sweep (Scene.set_solver_lanes) from the GLOBAL scene: 8 when every global parallel
+    group is small, else 4. Computed from all meshes of the scene, never from a rank's share, so that a sharded run and the
+    single-GPU run of the same scene sum in the same association and stay bit-identical."""
+    n_groups = max(len(c) for c in color_lists)
+    sizes = [0] * n_groups
+    for arranged in global_groups(color_lists):
+        for g, c in enumerate(arranged):
+            sizes[g] += len(c)
+    return 8 if max(sizes) < small else 4
+
+
 def object_boxes(meshes, transform):
     """[n,2,3] world-space boxes of every object at rest (transform(verts, obj) applies the object's placement)."""
     boxes = np.empty((len(meshes), 2, 3), np.float64)
@@ -272,6 +284,7 @@ def build_object_sharded_scene(wl, rank, world, local_rank, margin=None):
     s = capi.Scene(wl["phys"], wl["col"], device=local_rank)
     add_sharded_meshes(s, meshes, sh, rank)
     s.finalize()
+    s.set_solver_lanes(scene_solver_lanes([m[3] for m in meshes]))      # from the global scene: same on every rank and on one GPU
     s.sharding = sh
     recv = sh.recvs(rank)
     mine = {"handles": s.halo_ipc_handles(),

@@ -290,6 +290,11 @@ int gaia_b200_reset_stats(gaia_handle* h);
  * events on the launching stream when profiling is enabled */
 int gaia_b200_set_profiling(gaia_handle* h, int enabled);
 void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that time with their own events */
+/* Tuning: sub-warp lanes per vertex of the colour sweep (0 = default 4; 8 shortens the per-vertex chain and wins ~8 % when
+ * colours are small, < ~64 k vertices). The lane count fixes the association of the per-vertex sums: runs that must be
+ * bit-identical to each other (a sharded run and its single-GPU reference) have to use the same value, which is why the
+ * library never picks it from a rank's local sizes. The fused-halo sweep of a partitioned mesh always uses 4. */
+int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
 
 #ifdef __cplusplus
 }

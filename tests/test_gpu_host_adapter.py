@@ -19,6 +19,8 @@ def _python_run(m, p, root, frames):
     phys, col, meshes = meshio.load_scene_json(m, p, root)
     s = capi.Scene(phys, col)
     meshio.add_scene_meshes(s, meshes)
+    if len(meshes) > 1:
+        s.set_solver_lanes(8)          # the host driver's rule for small many-object scenes (VBDPhysicsB200::initialize)
     out = [np.concatenate([s.surface_positions(i) for i in range(len(meshes))])]
     for _ in range(frames):
         s.run_frames(1)

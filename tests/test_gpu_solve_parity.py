@@ -177,3 +177,23 @@ def test_hundred_frame_trajectory_config1_shape():
             assert worst[-1] < 1e-4, (chunk, worst)
     assert o.positions(0)[:, 1].min() < 0.02                      # it landed
     assert max(worst) < 5e-3, worst
+
+
+@pytest.mark.gpu
+def test_solver_lanes_option_changes_association_only():
+    """gaia_b200_set_solver_lanes: 8 lanes per vertex instead of 4 is the same arithmetic per tet with a different tree of
+    partial sums - one iteration agrees with the oracle to the same 1e-5 bar, and the two settings differ by rounding only."""
+    from gaia_b200 import capi
+    g4, o = _pair()
+    g8, _ = _pair()
+    g8.set_solver_lanes(8)
+    with pytest.raises(capi.GaiaError):
+        g8.set_solver_lanes(3)
+    for s in (g4, g8, o):
+        s.run_frames(1)
+        s.run_iterations(1)
+    assert rel_err(g4.positions(0), o.positions(0)) < 1e-5 and rel_err(g8.positions(0), o.positions(0)) < 1e-5
+    assert np.abs(g4.positions(0) - g8.positions(0)).max() < 1e-5
+    g8.set_solver_lanes(0)
+    g4.run_frames(2); g8.run_frames(2)          # back on the default: the two runs only differ by the one 8-lane frame
+    assert np.abs(g4.positions(0) - g8.positions(0)).max() < 1e-4
