@@ -243,3 +243,52 @@ def test_scene_files_with_deformers_reach_the_solver(tmp_path):
     json.dump(pj, open(p, "w"))
     r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
     assert r.returncode == 3 and "Unrecognized deformer" in r.stderr
+
+
+@pytest.mark.parametrize("interp_substep,interp_iter", [(True, 1), (True, 2), (False, 1)])
+def test_oracle_collider_sequence_follows_the_reference_interpolation(interp_substep, interp_iter):
+    """ColliderTrimeshSequence::update (M/SpatialQuery/ColiiderTriMeshSequence.h:59-104) restated in Python: after every frame
+    the collider sits where the LAST update of that frame put it: t = (f - f0)/n + substep/(S n) + iter/(I S n) for the
+    first I iterations of a substep (interpolateSubstep), or (f - f0)/n once per frame; past the last key nothing moves."""
+    S, IT = 3, 4
+    n = 8
+    v, f = cloth.grid_cloth(n, 1.0, origin=(0, 2.0, 0))
+    sv, sf = cloth.icosphere(0.2, 1)
+    keys = np.stack([sv, sv + np.float32([0.3, 0.0, 0.0]), sv + np.float32([0.3, 0.6, 0.0])])
+    kf = [1, 3, 6]
+    phys = cloth.default_cloth_physics_params(numSubsteps=S, iterations=IT, contactRadius=0.02, maxQueryDis=0.03, gravity=[0, 0, 0])
+    o = OracleClothScene(phys, threads=2)
+    o.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(n))
+    c = o.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(), simulated=False)
+    o.set_collider_sequence(c, keys, kf, interp_substep, interp_iter)
+    o.finalize()
+    interp_substep = interp_substep or interp_iter > 1
+
+    def lerp(k, t):
+        t = np.float32(t)
+        return keys[k] * (np.float32(1) - t) + keys[k + 1] * t
+
+    expect = None
+    first = True
+    for frame in range(8):
+        for sub in range(S):
+            for it in range(IT):
+                if first:                                   # set_state(frameId)
+                    first = False
+                    expect = keys[0] if frame < kf[0] else keys[-1]
+                    continue
+                if frame < kf[0] or frame >= kf[-1]:
+                    continue
+                k = max(i for i in range(len(kf)) if kf[i] <= frame)
+                nfr = kf[k + 1] - kf[k]
+                if interp_substep:
+                    if it < interp_iter:
+                        t = np.float32(frame - kf[k]) / np.float32(nfr)
+                        t = t + np.float32(sub) / np.float32(S * nfr)
+                        t = t + np.float32(it) / np.float32(interp_iter * S * nfr)
+                        expect = lerp(k, t)
+                elif sub == 0 and it == 0:
+                    expect = lerp(k, np.float32(frame - kf[k]) / np.float32(nfr))
+        o.run_frames(1)
+        assert np.allclose(o.positions(c), expect, atol=1e-6), frame
+    assert np.array_equal(o.positions(0), v)                # far away, no gravity: the sheet never moved
