@@ -6,7 +6,9 @@ import re
 import sys
 
 rows = list(csv.reader(open(sys.argv[1])))
-hi = next(i for i, r in enumerate(rows) if 'Kernel Name' in r)
+hi = next((i for i, r in enumerate(rows) if 'Kernel Name' in r), None)
+if hi is None:
+    sys.exit(f"{sys.argv[1]}: no launch table (ncu was cut off before it wrote its report?)")
 hdr = rows[hi]
 ki, vi, ui = hdr.index('Kernel Name'), hdr.index('Metric Value'), hdr.index('Metric Unit')
 agg = collections.defaultdict(lambda: [0, 0.0])
