@@ -162,6 +162,23 @@ def test_global_groups_restate_the_merge():
         assert np.array_equal(pairs, want)
 
 
+def test_solver_lanes_rule_uses_the_global_group_sizes():
+    """scene_solver_lanes: one answer per GLOBAL scene (8 when every merged parallel group is below the bound), whatever a
+    rank holds of it - that is what keeps a sharded run on the same summation association as the single-GPU run."""
+    from oracle.binding import OracleScene
+    wl = _pile_workload()
+    colors = [m[3] for m in wl["meshes"]]
+    o = OracleScene(wl["phys"], wl["col"], threads=1)
+    for v, t, obj, c, fixed in wl["meshes"]:
+        o.add_tet_mesh(v, t, obj, c, fixed)
+    o.finalize()
+    largest = max(len(g) for g in o.parallel_groups())
+    assert multigpu.scene_solver_lanes(colors) == 8                          # a small pile
+    assert multigpu.scene_solver_lanes(colors, small=largest + 1) == 8       # the bound is on the largest merged group
+    assert multigpu.scene_solver_lanes(colors, small=largest) == 4
+    assert multigpu.scene_solver_lanes(colors[:1], small=largest) == 8       # a rank's share alone would answer differently
+
+
 def test_object_sharding_tables():
     wl = _pile_workload()
     boxes = multigpu.object_boxes(wl["meshes"], meshio.place)
