@@ -349,6 +349,9 @@ def load_library(path=None):
     lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
+    lib.gaia_b200_color_graph.argtypes = [C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
+    lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
+    lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
         getattr(lib, "gaia_b200_" + f).restype = None
@@ -450,3 +453,32 @@ class Scene(SceneBase):
     @property
     def cuda_stream(self):
         return self._lib.gaia_b200_cuda_stream(self.h)
+
+
+# ---------------------------------------------------------------------------------------------- vertex colouring (host code)
+def _categories(fn, n, *args):
+    colors = np.empty(n, np.int32); off = np.empty(n + 1, np.int32); nodes = np.empty(n, np.int32)
+    nc = fn(*args, _ip(colors), _ip(off), _ip(nodes))
+    if nc < 0:
+        raise GaiaError(f"colouring failed: {nc}")
+    return [nodes[off[c]:off[c + 1]].copy() for c in range(nc)]
+
+
+def color_graph(num_nodes, edges, balance=True, goal_max_min_ratio=1.05):
+    """The reference tool's `greedy` colouring (+ balancing) of an undirected graph given as an [nE, 2] edge list; returns the
+    colour categories in the tool's order (what it writes to *.vertexColoring.json)."""
+    e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
+    return _categories(load_library().gaia_b200_color_graph, int(num_nodes), int(num_nodes), len(e), _ip(e), 1 if balance else 0,
+                       float(goal_max_min_ratio))
+
+
+def color_tet_mesh(n_verts, tets, balance=True, goal_max_min_ratio=1.05):
+    t = _i32(np.asarray(tets, np.int32).reshape(-1, 4))
+    return _categories(load_library().gaia_b200_color_tet_mesh, int(n_verts), int(n_verts), len(t), _ip(t), 1 if balance else 0,
+                       float(goal_max_min_ratio))
+
+
+def color_tri_mesh(n_verts, faces, edge_energy=True, balance=True, goal_max_min_ratio=1.05):
+    f = _i32(np.asarray(faces, np.int32).reshape(-1, 3))
+    return _categories(load_library().gaia_b200_color_tri_mesh, int(n_verts), int(n_verts), len(f), _ip(f), 1 if edge_energy else 0,
+                       1 if balance else 0, float(goal_max_min_ratio))

@@ -296,6 +296,24 @@ void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that
  * library never picks it from a rank's local sizes. The fused-halo sweep of a partitioned mesh always uses 4. */
 int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
 
+/* Vertex graph colouring (host code; no device needed) -------------------------
+ * The reference colours its meshes with an offline tool (S/GraphColoring/GraphColoring.cpp: `-v -a greedy -b -r ratio`;
+ * OrderedGreedy, M/GraphColoring/gready.cpp:16-117; balanceColoredCategories, M/GraphColoring/ColoringAlgorithms.cpp:82-198)
+ * whose output is the `*.vertexColoring.json` that add_tet_mesh / add_tri_mesh take. These calls restate it (same node
+ * order, colour choice and balancing moves; O(E log V) instead of the tool's O(V^2) scan; balancing moves are capped, the
+ * tool's loop is unbounded). Parity with the tool's own output is UNPINNED this round: tests check validity and balance.
+ * colors: numNodes colour ids (may be NULL); categoryOffsets (numColours + 1, sized numNodes + 1 by the caller) and
+ * categoryNodes (numNodes): the colour categories in the tool's order (both NULL to skip). Return the number of colours.
+ * color_graph takes the undirected edge list as given; the mesh variants build the vertex graph of TetMeshVertexGraph
+ * (vertices sharing a tet) / TriMeshVertexGraph (vertices sharing a triangle, plus the two wing vertices of every interior
+ * edge when edgeEnergy != 0: they share a bending hinge), with unique edges. */
+int gaia_b200_color_graph(int32_t numNodes, int64_t nEdges, const int32_t* edges, int32_t balance, float goalMaxMinRatio,
+                          int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
+int gaia_b200_color_tet_mesh(int32_t nV, int32_t nT, const int32_t* tets, int32_t balance, float goalMaxMinRatio,
+                             int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
+int gaia_b200_color_tri_mesh(int32_t nV, int32_t nF, const int32_t* faces, int32_t edgeEnergy, int32_t balance, float goalMaxMinRatio,
+                             int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
+
 #ifdef __cplusplus
 }
 #endif
