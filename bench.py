@@ -46,127 +46,7 @@ def emit(obj):
     _REAL_STDOUT.flush()
 
 
-# --------------------------------------------------------------------------------------------- workloads
-def workload_twist_beam(nx=472, ny=60, nz=60, h=0.02, collisions=False):
-    """SURVEY.md §8(d) cfg 4: regular hex grid split into 6 Kuhn tets per cell, both end caps driven by Rotator deformers
-    (+-pi/4 rad/s about x), NeoHookean mu=5e3 lambda=1e5 density 100 damping 1e-6, gravity 0, 5 substeps x 20 iterations."""
-    verts, tets = meshio.kuhn_beam(nx, ny, nz, h=h, origin=(0.0, 1.0, 0.0))
-    colors = meshio.kuhn_coloring(nx, ny, nz)
-    phys = capi.default_physics_params(gravity=[0, 0, 0], numSubsteps=5, iterations=20, collisionStiffness=2e4,
-                                       intermediateCollisionIterations=5 if collisions else -1,
-                                       worldBoundsMin=[-100, -100, -100], worldBoundsMax=[100, 100, 100])
-    col = capi.default_collision_params(allowDCD=1 if collisions else 0, allowCCD=0)
-    obj = capi.default_object_params(miu=5e3, lmbd=1e5, density=100, dampingHydrostatic=1e-6, dampingDeviatoric=1e-6)
-    gx = np.arange(len(verts)) // ((ny + 1) * (nz + 1))
-    left = np.nonzero(gx == 0)[0].astype(np.int32)
-    right = np.nonzero(gx == nx)[0].astype(np.int32)
-    cy, cz = 1.0 + 0.5 * ny * h, 0.5 * nz * h
-    deformers = [("rotator", left, (0.0, cy, cz), (1.0, 0.0, 0.0), np.pi / 4, -1.0),
-                 ("rotator", right, (0.0, cy, cz), (1.0, 0.0, 0.0), -np.pi / 4, -1.0)]
-    name = f"twist_beam {nx}x{ny}x{nz} cells ({len(tets)} tets, {len(verts)} verts), 5 substeps x 20 iters, 4 colours"
-    return dict(name=name, meshes=[(verts, tets, obj, colors, np.zeros(0, np.int32))], phys=phys, col=col, deformers=deformers)
-
-
-_BLOB_CACHE = {}
-
-
-def workload_drop_pile(n_objects=32, grid=(4, 4), substeps=4, iterations=20, preroll=40, seed=123):
-    """SURVEY.md §8(d) cfg 2 (S01_Experiment_HybridModelsDrop), synthetic stand-in: n_objects tet models cycling four
-    blob shapes (~2-3.5k vertices, 8 colours each, like teapot / bunny / octopus / armadillo) dropping into a box with
-    self / inter-object collision: S01's step settings (4 substeps x 20 iterations, DCD + CCD, collisionStiffness 1e5,
-    friction 0.2 / epsV 0.01, material mu 1e5 lambda 1e6 density 50). All objects are present from frame 0 (stacked
-    layers); `preroll` untimed frames bring them into contact before anything is measured."""
-    rng = np.random.RandomState(seed)
-    shapes = [(16, (1, 1, 1), 2.0), (18, (1, 0.6, 0.8), 2.0), (16, (1, 1, 0.55), 4.0), (17, (0.75, 1, 0.75), 1.5)]
-    meshes = []
-    h = 0.1
-    per_layer = grid[0] * grid[1]
-    for i in range(n_objects):
-        key = i % len(shapes)
-        if key not in _BLOB_CACHE:
-            n, r, pw = shapes[key]
-            v, t = meshio.kuhn_blob(n, r, h, pw)
-            _BLOB_CACHE[key] = (v, t, meshio.greedy_coloring(len(v), t))
-        v, t, colors = _BLOB_CACHE[key]
-        layer, j = divmod(i, per_layer)
-        gx, gz = divmod(j, grid[1])
-        pos = [(gx - (grid[0] - 1) / 2) * 2.1 + rng.uniform(-0.1, 0.1), 1.2 + 2.0 * layer + rng.uniform(0, 0.2), (gz - (grid[1] - 1) / 2) * 2.1 + rng.uniform(-0.1, 0.1)]
-        obj = capi.default_object_params(miu=1e5, lmbd=1e6, density=50, frictionDynamic=0.2, frictionEpsV=0.01, translation=pos,
-                                         rotation=[0, float(rng.uniform(0, 3.0)), 0], initialVelocity=[0, -2.0, 0], maxVelocityMagnitude=25.0,
-                                         exponentialVelDamping=0.95, constantVelDamping=0.02)
-        meshes.append((v, t, obj, colors, np.zeros(0, np.int32)))
-    half = grid[0] * 2.1 / 2 + 0.3
-    phys = capi.default_physics_params(numSubsteps=substeps, iterations=iterations, collisionStiffness=1e5, boundaryCollisionStiffness=1e5,
-                                       boundaryFrictionDynamic=0.1, worldBoundsMin=[-half, 0, -half], worldBoundsMax=[half, 50, half])
-    col = capi.default_collision_params(allowDCD=1, allowCCD=1)
-    nV = sum(len(m[0]) for m in meshes); nT = sum(len(m[1]) for m in meshes)
-    name = f"drop_pile {n_objects} tet models ({nT} tets, {nV} verts) into a box, DCD+CCD, {substeps} substeps x {iterations} iters, 8 colours"
-    return dict(name=name, meshes=meshes, phys=phys, col=col, deformers=[], preroll=preroll)
-
-
-def workload_cloth_drape(n=1000, width=100.0, substeps=20, iterations=15, preroll=2, sphere_level=4):
-    """SURVEY.md §8(d) cfg 3: n x n vertex sheet (the reference's C{N}_horizontal.obj family, 100 units wide) centred above a
-    sphere collider of radius 0.3 x width (all collider vertices fixed), S03_MultiLayerClothOnCollider.py values: StVK
-    mu = lambda = 1e4, density 0.02, bendingStiffness 10, damping 2e-6, gravity (0,-1000,0), contactStiffness 1e5,
-    contactRadius 0.3 and maxQueryDis 0.45 scaled by cell / cell(C70), thickness 1e-4, conservativeStepRelaxation 0.4,
-    friction 0.1, 20 substeps x 15 iterations; VF + EE contact with the collider and with itself. `preroll` untimed frames
-    let the sheet land on the sphere before anything is measured."""
-    scale = (width / (n - 1)) / (100.0 / 69.0)
-    R = 0.3 * width
-    v, f = cloth.grid_cloth_fast(n, width, origin=(0.0, R + 0.6 * 0.45 * scale, 0.0))
-    sv, sf = cloth.icosphere(R, sphere_level, center=(0.0, 0.0, 0.0))
-    phys = cloth.default_cloth_physics_params(gravity=[0, -1000, 0], numSubsteps=substeps, iterations=iterations, contactStiffness=1e5,
-                                              contactRadius=0.3 * scale, maxQueryDis=0.45 * scale, thickness=1e-4 * scale,
-                                              conservativeStepRelaxation=0.4, contactEnergyTypes=1)
-    obj = cloth.default_cloth_object_params(miu=1e4, density=0.02, bendingStiffness=10.0, dampingStVK=2e-6, dampingBending=2e-6,
-                                            frictionDynamic=0.1, frictionEpsV=0.1, initializationType=2)
-    obj.lambda_ = 1e4
-    name = (f"cloth_drape {n}x{n} sheet ({len(v)} verts, {len(f)} tris) over a sphere collider ({len(sv)} verts), VF+EE contact, "
-            f"{substeps} substeps x {iterations} iters, 9 colours")
-    meshes = [(v, f, obj, cloth.grid_cloth_coloring(n), np.zeros(0, np.int32), True),
-              (sv, sf, cloth.default_cloth_object_params(frictionDynamic=0.1), [], np.zeros(0, np.int32), False)]
-    return dict(kind="cloth", name=name, meshes=meshes, phys=phys, col=None, deformers=[], preroll=preroll)
-
-
-def is_cloth(wl):
-    return wl.get("kind") == "cloth"
-
-
-def build_scene(cls, wl, **kw):
-    if is_cloth(wl):
-        s = cls(wl["phys"], **kw)
-        for v, f, obj, colors, fixed, simulated in wl["meshes"]:
-            s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=simulated)
-        s.finalize()
-        return s
-    s = cls(wl["phys"], wl["col"], **kw)
-    if cls is capi.Scene and len(wl["meshes"]) > 1:      # many-object scenes: the rule the sharded builder applies too
-        from gaia_b200.multigpu import scene_solver_lanes
-        s.set_solver_lanes(scene_solver_lanes([m[3] for m in wl["meshes"]]))
-    for v, t, obj, colors, fixed in wl["meshes"]:
-        s.add_tet_mesh(v, t, obj, colors, fixed)
-    for d in wl["deformers"]:
-        if d[0] == "rotator":
-            s.add_rotator(0, d[1], d[2], d[3], d[4], d[5])
-        else:
-            s.add_translator(0, d[1], d[2], d[3])
-    s.finalize()
-    return s
-
-
-WORKLOADS = {
-    "twist_beam_10m": lambda: workload_twist_beam(472, 60, 60),
-    "twist_beam_1m": lambda: workload_twist_beam(59, 60, 60),
-    "twist_beam_small": lambda: workload_twist_beam(24, 12, 12),
-    "drop_pile_32": lambda: workload_drop_pile(32),
-    "drop_pile_8": lambda: workload_drop_pile(8, grid=(2, 2), preroll=30),
-    # SURVEY.md §8(d) cfg 5 shape: many replicated models on a jittered lattice, 2 substeps x 20 iterations, DCD + CCD
-    "drop_pile_512": lambda: workload_drop_pile(512, grid=(8, 8), substeps=2, iterations=20, preroll=20),
-    "drop_pile_4096": lambda: workload_drop_pile(4096, grid=(16, 16), substeps=2, iterations=20, preroll=10),
-    "cloth_1m": lambda: workload_cloth_drape(1000),
-    "cloth_250k": lambda: workload_cloth_drape(500, width=50.0, sphere_level=4),
-    "cloth_small": lambda: workload_cloth_drape(120, width=12.0, substeps=4, iterations=6, sphere_level=2),
-}
+from gaia_b200.workloads import WORKLOADS, build_scene, is_cloth, workload_cloth_drape, workload_twist_beam  # noqa: E402
 
 
 # --------------------------------------------------------------------------------------------- clocks

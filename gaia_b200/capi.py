@@ -161,6 +161,8 @@ def bind_scene_api(lib, prefix):
         "enable_mesh": ([P, C.c_int, C.c_int, C.c_int], C.c_int),
         "get_stats": ([P, C.POINTER(Stats)], C.c_int), "reset_stats": ([P], C.c_int),
         "get_bvh_leaf_order": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
+        "get_active_list": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
+        "get_relations": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
         "set_partition_mode": ([P, C.c_int32, C.c_int32], C.c_int), "set_ghosts": ([P, C.c_int, IP, C.c_int32], C.c_int),
     }
     for name, (args, res) in sig.items():
@@ -300,6 +302,24 @@ class SceneBase:
         self._call("get_bvh_leaf_order", which, None, 0, C.byref(n))
         a = np.empty(n.value, np.int32)
         self._call("get_bvh_leaf_order", which, _ip(a), n.value, C.byref(n))
+        return a
+
+    def active_list(self, group):
+        """(n, 2) int32 (queryMesh, queryVertex) of the contacts active in one parallel group, ascending (row a15)."""
+        n = C.c_int64()
+        self._call("get_active_list", group, None, 0, C.byref(n))
+        a = np.empty((n.value, 2), np.int32)
+        if n.value:
+            self._call("get_active_list", group, _ip(a), n.value, C.byref(n))
+        return a
+
+    def relations(self, mesh):
+        """(n, 4) int32 (vertex, queryMesh, queryVertex, face-vertex order): face-side contact relations of a mesh (row a15)."""
+        n = C.c_int64()
+        self._call("get_relations", mesh, None, 0, C.byref(n))
+        a = np.empty((n.value, 4), np.int32)
+        if n.value:
+            self._call("get_relations", mesh, _ip(a), n.value, C.byref(n))
         return a
 
     def enable_mesh(self, mesh, collide=True, solve=True):

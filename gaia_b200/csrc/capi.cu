@@ -335,6 +335,23 @@ int gaia_b200_get_bvh_leaf_order(gaia_handle* h, int which, int32_t* out, int64_
     return *n < 0 ? GAIA_ERR_INVALID_ARG : GAIA_OK;
 }
 
+int gaia_b200_get_active_list(gaia_handle* h, int group, int32_t* out, int64_t capacity, int64_t* n) {
+    REQUIRE(h); FINALIZED(h);
+    if (!n) return GAIA_ERR_INVALID_ARG;
+    if (group < 0 || group >= (int)h->s.groupStart.size() - 1) return fail(h->s, GAIA_ERR_INVALID_ARG, "bad parallel group");
+    cudaSetDevice(h->s.device);
+    *n = collision_fetch_active_list(h->s, group, out, capacity);
+    return *n < 0 ? GAIA_ERR_CUDA : GAIA_OK;
+}
+int gaia_b200_get_relations(gaia_handle* h, int mesh, int32_t* out, int64_t capacity, int64_t* n) {
+    REQUIRE(h); FINALIZED(h);
+    if (!n) return GAIA_ERR_INVALID_ARG;
+    if (mesh < 0 || mesh >= (int)h->s.meshes.size()) return fail(h->s, GAIA_ERR_INVALID_ARG, "bad mesh id");
+    cudaSetDevice(h->s.device);
+    *n = collision_fetch_relations(h->s, mesh, out, capacity);
+    return *n < 0 ? GAIA_ERR_CUDA : GAIA_OK;
+}
+
 int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int activeForMaterialSolve) {
     REQUIRE(h);
     Scene& s = h->s;

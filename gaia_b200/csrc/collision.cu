@@ -1026,6 +1026,61 @@ int64_t collision_fetch_contacts(Scene& s, gaia_contact* out, int64_t cap) {
     return cnt;
 }
 
+// a15: the per-group active list (ActiveCollisionList::addToActiveCollisionList, M/VBD/ActiveCollisionList.cpp:43-110) as
+// (mesh, vertex) pairs of the contacts' QUERY vertices, sorted ascending (the device fills the list with atomics; the
+// canonical order of the parity surface is the sorted one). Returns the number of pairs, -1 on a CUDA error.
+int64_t collision_fetch_active_list(Scene& s, int group, int32_t* out, int64_t cap) {
+    CollisionState* c = s.cs;
+    if (!c || !c->prepared || c->nActive == 0) return 0;
+    if (group < 0 || group >= c->G) return -2;
+    if (cudaStreamSynchronize(s.stream) != cudaSuccess) return -1;
+    const int n = c->h_groupCount[group];
+    if (n <= 0 || !out) return std::max(n, 0);
+    std::vector<int32_t> slots(n);
+    if (cudaMemcpy(slots.data(), c->groupList.p + c->h_groupOff[group], (size_t)n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    std::vector<std::pair<int32_t, int32_t>> pairs(n);
+    for (int i = 0; i < n; i++) {
+        size_t lo = 0, hi = s.meshes.size();
+        while (hi - lo > 1) { const size_t mid = (lo + hi) / 2; if (s.meshes[mid].surfVBase <= slots[i]) lo = mid; else hi = mid; }
+        const HostMesh& m = s.meshes[lo];
+        pairs[i] = {m.id, m.surfaceVIds[slots[i] - m.surfVBase]};
+    }
+    std::sort(pairs.begin(), pairs.end());
+    for (int i = 0; i < n && i < cap; i++) { out[2 * i] = pairs[i].first; out[2 * i + 1] = pairs[i].second; }
+    return n;
+}
+
+// a15: face-side relations of one mesh (prepareCollisionDataCPU, M/VBD/VBDPhysics.cpp:1793-1806): rows
+// (vertex, queryMesh, queryVertex, face-vertex order), sorted ascending. Returns the number of rows.
+int64_t collision_fetch_relations(Scene& s, int mesh, int32_t* out, int64_t cap) {
+    CollisionState* c = s.cs;
+    if (!c || !c->prepared || c->nActive == 0) return 0;
+    if (cudaStreamSynchronize(s.stream) != cudaSuccess) return -1;
+    const HostMesh& m = s.meshes[mesh];
+    const int64_t N = s.nVerts;
+    std::vector<int32_t> off(N + 1);
+    if (cudaMemcpy(off.data(), c->relOff.p, (size_t)(N + 1) * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    std::vector<int2> rel((size_t)off[N]);
+    if (off[N] && cudaMemcpy(rel.data(), c->rel.p, rel.size() * sizeof(int2), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    struct Row { int32_t v, qm, qv, k; };
+    std::vector<Row> rows;
+    for (int v = 0; v < m.nV; v++) {
+        const int sid = m.sortedId[v];
+        for (int q = off[sid]; q < off[sid + 1]; q++) {
+            const int slot = rel[q].x;
+            size_t lo = 0, hi = s.meshes.size();
+            while (hi - lo > 1) { const size_t mid = (lo + hi) / 2; if (s.meshes[mid].surfVBase <= slot) lo = mid; else hi = mid; }
+            const HostMesh& qmesh = s.meshes[lo];
+            rows.push_back({v, qmesh.id, qmesh.surfaceVIds[slot - qmesh.surfVBase], rel[q].y});
+        }
+    }
+    std::sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) {
+        if (a.v != b.v) return a.v < b.v; if (a.qm != b.qm) return a.qm < b.qm; if (a.qv != b.qv) return a.qv < b.qv; return a.k < b.k; });
+    const int64_t n = (int64_t)rows.size();
+    if (out) for (int64_t i = 0; i < n && i < cap; i++) { out[4 * i] = rows[i].v; out[4 * i + 1] = rows[i].qm; out[4 * i + 2] = rows[i].qv; out[4 * i + 3] = rows[i].k; }
+    return n;
+}
+
 int64_t collision_leaf_order(Scene& s, int which, int32_t* out, int64_t cap) {
     CollisionState* c = s.cs;
     if (!c) return 0;

@@ -174,6 +174,8 @@ cudaError_t collision_update_infos(Scene& s, int group, bool deviceSized = false
 bool collision_graphable(const Scene& s);                         // contact lists small enough for device-sized pre-pass launches
 int64_t collision_fetch_contacts(Scene& s, gaia_contact* out, int64_t cap);
 int64_t collision_leaf_order(Scene& s, int which, int32_t* out, int64_t cap);
+int64_t collision_fetch_active_list(Scene& s, int group, int32_t* out, int64_t cap);
+int64_t collision_fetch_relations(Scene& s, int mesh, int32_t* out, int64_t cap);
 bool collision_contact_view(Scene& s, ContactView& cv, const uint8_t** collidingMask, bool force = false);
 
 }  // namespace gb

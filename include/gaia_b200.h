@@ -256,6 +256,17 @@ int gaia_b200_detect_collisions(gaia_handle* h, int doDCD, int doCCD);
 int gaia_b200_get_contacts(gaia_handle* h, gaia_contact* out, int64_t capacity, int64_t* n);
 /* which: 0 = all-tets scene, 1 = surface-faces scene; out = primitive ids in Morton leaf order */
 int gaia_b200_get_bvh_leaf_order(gaia_handle* h, int which, int32_t* out, int64_t capacity, int64_t* n);
+/* Prepared collision data of the last step / run_iterations call (integer parity surfaces of SURVEY.md §8 row a15):
+ *  - the active collision list of one parallel group, VBDPhysics::activeCollisionsEachParallelGroup[group] as filled by
+ *    ActiveCollisionList::addToActiveCollisionList (M/VBD/ActiveCollisionList.cpp:43-110, called from
+ *    prepareCollisionDataCPU, M/VBD/VBDPhysics.cpp:1709-1810): pairs (queryMesh, queryVertex) of every contact that
+ *    involves a vertex of the group (its own vertex or one of the three face vertices), each contact once per group;
+ *    returned sorted ascending (the reference's order is its serial loop order = ascending too);
+ *  - the face-side relations of one mesh (VBDCollisionDetectionResult relations, VBDPhysics.cpp:1793-1806): rows
+ *    (vertex, queryMesh, queryVertex, order of `vertex` in the contact's face), sorted ascending.
+ * out == NULL queries the count (pairs / rows). */
+int gaia_b200_get_active_list(gaia_handle* h, int group, int32_t* outPairs, int64_t capacity, int64_t* nPairs);
+int gaia_b200_get_relations(gaia_handle* h, int mesh, int32_t* outRows, int64_t capacity, int64_t* nRows);
 
 /* mesh activation (VBDPhysics::enableModels, M/VBD/VBDPhysics.cpp:685-709) */
 int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int activeForMaterialSolve);

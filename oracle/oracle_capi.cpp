@@ -3,6 +3,7 @@
 // prefix `oracle_`, so that tests drive both implementations with the same calls.
 #include "vbd_oracle.h"
 #include "oracle_ccd.h"
+#include <algorithm>
 #include <cstdio>
 
 using namespace orc;
@@ -206,6 +207,31 @@ int oracle_get_contacts(void* h, gaia_contact* out, int64_t capacity, int64_t* n
         }
     }
     *n = cnt;
+    return GAIA_OK;
+}
+// a15 parity surfaces (twins of gaia_b200_get_active_list / get_relations): prepare_collision_data's outputs, sorted
+int oracle_get_active_list(void* h, int group, int32_t* out, int64_t capacity, int64_t* n) {
+    Scene* s = (Scene*)h;
+    if (group < 0 || group >= (int)s->activeCollisionsEachGroup.size()) { *n = 0; return GAIA_OK; }
+    const std::vector<int>& g = s->activeCollisionsEachGroup[group];
+    std::vector<std::pair<int, int>> pairs;
+    for (size_t i = 0; i + 1 < g.size(); i += 2) pairs.push_back({g[i], g[i + 1]});
+    std::sort(pairs.begin(), pairs.end());
+    *n = (int64_t)pairs.size();
+    if (out) for (int64_t i = 0; i < *n && i < capacity; i++) { out[2 * i] = pairs[i].first; out[2 * i + 1] = pairs[i].second; }
+    return GAIA_OK;
+}
+int oracle_get_relations(void* h, int mesh, int32_t* out, int64_t capacity, int64_t* n) {
+    Scene* s = (Scene*)h;
+    Mesh& m = s->meshes[mesh];
+    struct Row { int32_t v, qm, qv, k; };
+    std::vector<Row> rows;
+    for (int v = 0; v < (int)m.colRelations.size(); v++)
+        for (auto& r : m.colRelations[v]) rows.push_back({v, r.meshId, s->meshes[r.meshId].surfaceVIds[r.surfaceVertexId], r.collisionVertexOrder});
+    std::sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) {
+        if (a.v != b.v) return a.v < b.v; if (a.qm != b.qm) return a.qm < b.qm; if (a.qv != b.qv) return a.qv < b.qv; return a.k < b.k; });
+    *n = (int64_t)rows.size();
+    if (out) for (int64_t i = 0; i < *n && i < capacity; i++) { out[4 * i] = rows[i].v; out[4 * i + 1] = rows[i].qm; out[4 * i + 2] = rows[i].qv; out[4 * i + 3] = rows[i].k; }
     return GAIA_OK;
 }
 int oracle_get_bvh_leaf_order(void* h, int which, int32_t* out, int64_t capacity, int64_t* n) {

@@ -57,6 +57,16 @@ def rel_err(a, b):
     return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))
 
 
+def per_vertex_rel(a, b, scale=None):
+    """north_star's "per-vertex positions within 1e-5 relative": max over vertices of |a_v - b_v| / max(|b_v|, L), L = the
+    diagonal of b's bounding box unless given (a vertex near the origin is measured against the size of the scene)."""
+    a = np.asarray(a, np.float64).reshape(-1, 3); b = np.asarray(b, np.float64).reshape(-1, 3)
+    if scale is None:
+        scale = float(np.linalg.norm(b.max(0) - b.min(0)))
+    den = np.maximum(np.linalg.norm(b, axis=1), max(scale, 1e-30))
+    return float((np.linalg.norm(a - b, axis=1) / den).max())
+
+
 def make_contact_scene(cls, n_objects=2, ccd=1, dcd=1, substeps=2, iterations=6, phys_kw=None, col_kw=None, gap=-0.08, v_rel=(0.0, -6.0, 0.0),
                        **cls_kw):
     """Config-2 shape in miniature: Kuhn-grid blocks stacked with a small overlap (gap < 0) above the ground plane, each

@@ -1,0 +1,234 @@
+"""-m gpu: parity on what is BENCHMARKED and on what BASELINE.json's configs NAME.
+
+  * the twisted beam of the headline bench (two Rotator deformers on the tet path, M/VBD/VBDDeformer.h:45-131,
+    M/VBD/VBDPhysics.cpp:1572-1578) at a size the oracle finishes in seconds;
+  * the reference's own meshes with the colourings it ships (tests/golden/ref_root mirrors the reference's Data/ tree):
+    irregular valence, 8 unequal colours, vertices with more than 32 distinct neighbours (the sweep's spill path);
+  * config 1 (one model dropping onto the ground plane, SURVEY.md §8(d) parameters, 100 frames);
+  * config 2 in miniature (the four S01 meshes stacked, DCD + CCD) with every integer surface compared bit-exactly:
+    contact sets, BVH leaf orders, per-group active lists and face-side relations (row a15).
+
+Norms. `per_vertex_rel` is the per-vertex measure north_star asks for: max_v |x_v - x_v^oracle| / max(|x_v^oracle|, L),
+L = the diagonal of the scene's bounding box (a vertex near the origin is measured against the size of the scene, not
+against its own tiny coordinate). `step_rel` is the stricter, informative one: error relative to the iteration's own
+displacement."""
+import numpy as np
+import pytest
+
+from conftest import contacts_table, per_vertex_rel
+
+pytestmark = pytest.mark.gpu
+
+
+def _both(wl, threads=4):
+    from gaia_b200.capi import Scene
+    from gaia_b200.workloads import build_scene
+    from oracle.binding import OracleScene
+    return build_scene(Scene, wl), build_scene(OracleScene, wl, threads=threads)
+
+
+def _all(s):
+    return np.concatenate([s.positions(m) for m in range(s.num_meshes)])
+
+
+# ------------------------------------------------------------------------------------------ the benchmarked configuration
+def test_twist_beam_rotators_match_the_oracle():
+    """bench.py's default workload in miniature (24x12x12 cells, same material / deformers / step settings)."""
+    from gaia_b200.workloads import workload_twist_beam
+    wl = workload_twist_beam(24, 12, 12)
+    g, o = _both(wl)
+    driven = np.concatenate([d[1] for d in wl["deformers"]])
+    for s in (g, o):
+        s.run_frames(1)
+        s.run_iterations(1)
+    pg, po = g.positions(0), o.positions(0)
+    assert np.array_equal(pg[driven], po[driven])                      # Rotator targets: bit-identical
+    assert not np.array_equal(po[driven], wl["meshes"][0][0][driven])  # ... and they did move
+    assert per_vertex_rel(pg, po) < 1e-5
+    assert np.array_equal(g.prev_positions(0), o.prev_positions(0)) or per_vertex_rel(g.prev_positions(0), o.prev_positions(0)) < 1e-5
+    # 20 frames of twisting (pi/4 rad/s at both caps: 0.52 rad of relative twist). Tolerance: 2e-4 absolute = 0.08 % of the
+    # beam's 0.24-unit cross-section
+    for s in (g, o):
+        s.run_frames(19)
+    pg, po = g.positions(0), o.positions(0)
+    assert np.array_equal(pg[driven], po[driven])
+    assert np.abs(po - wl["meshes"][0][0]).max() > 0.02                # the caps turned
+    assert np.abs(pg - po).max() < 2e-4, float(np.abs(pg - po).max())
+
+
+def test_translator_deformer_on_the_tet_path():
+    from gaia_b200.workloads import workload_twist_beam
+    wl = workload_twist_beam(10, 4, 4)
+    left = wl["deformers"][0][1]
+    right = wl["deformers"][1][1]
+    wl["deformers"] = [("translator", right, (0.3, 0.05, 0.0), 0.05), ("rotator", left, wl["deformers"][0][2], (1.0, 0.0, 0.0), 0.5, 0.03)]
+    g, o = _both(wl)
+    for s in (g, o):
+        s.run_frames(6)          # 0.1 s: the translator stops at endTime 0.05, the rotator at 0.03
+    pg, po = g.positions(0), o.positions(0)
+    assert np.array_equal(pg[right], po[right]) and np.array_equal(pg[left], po[left])
+    x0 = wl["meshes"][0][0]
+    assert np.allclose(po[right] - x0[right], [0.3 * 0.05, 0.05 * 0.05, 0.0], atol=1e-6)
+    assert np.abs(pg - po).max() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------ reference meshes
+@pytest.mark.parametrize("model", ["teapot", "bunny_small", "beam_1k", "octopus_5k", "armadillo_lowres"])
+def test_reference_mesh_setup_and_one_iteration(model):
+    from gaia_b200.workloads import ref_mesh, workload_model_drop
+    v, t, colors = ref_mesh(model)
+    wl = workload_model_drop(model, scale=(1.0, 1.0, 1.0), rotation=(0.3, -0.2, 0.5), height=0.0)
+    lo = v.min(0)
+    wl["meshes"][0][2].translation[1] = float(2.0 - lo[1])
+    g, o = _both(wl)
+    # integer / set-up surfaces: bit-exact
+    assert np.array_equal(g.positions(0), o.positions(0))
+    assert np.array_equal(g.vertex_masses(0), o.vertex_masses(0))
+    assert np.array_equal(g.surface_vertex_ids(0), o.surface_vertex_ids(0))
+    assert np.array_equal(g.surface_faces(0), o.surface_faces(0))
+    gg, og = g.parallel_groups(), o.parallel_groups()
+    assert len(gg) == len(og) == 8
+    for a, b in zip(gg, og):
+        assert np.array_equal(a, b)
+    assert [len(a) for a in og] == sorted((len(c) for c in colors), reverse=True)     # size-descending sort of the colours
+    for s in (g, o):
+        s.run_frames(1)
+        s.run_iterations(1)
+    before = o.prev_positions(0)
+    pg, po = g.positions(0), o.positions(0)
+    assert per_vertex_rel(pg, po) < 1e-5, per_vertex_rel(pg, po)
+    step = np.linalg.norm(po - before, axis=1).max()
+    assert np.linalg.norm(pg - po, axis=1).max() < 1e-3 * step          # step_rel: 0.1 % of the iteration's displacement
+
+
+def test_sweep_spill_path_is_exercised_by_reference_meshes():
+    """k_solve_colour stages at most kNbMax = 32 distinct neighbour positions per vertex in shared memory; vertices with more
+    gather from global memory (`nnbAll > kNbMax`). The teapot and the bunny have such vertices; their new positions must
+    meet the same 1e-5 bar."""
+    from gaia_b200 import meshio
+    from gaia_b200.workloads import ref_mesh, workload_model_drop
+    for model in ("teapot", "bunny_small"):
+        v, t, _ = ref_mesh(model)
+        offs, _ = meshio.vertex_adjacency(len(v), t)
+        big = np.nonzero(np.diff(offs) > 32)[0]
+        assert len(big) >= 2
+        wl = workload_model_drop(model, height=3.0)
+        g, o = _both(wl)
+        for s in (g, o):
+            s.run_frames(2)
+            s.run_iterations(3)
+        pg, po = g.positions(0), o.positions(0)
+        assert not np.array_equal(po[big], o.prev_positions(0)[big])     # they were solved
+        assert per_vertex_rel(pg[big], po[big], scale=np.linalg.norm(po.max(0) - po.min(0))) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ config 1
+def test_config1_teapot_drop_100_frames():
+    """BASELINE configs[0] with SURVEY.md §8(d)'s parameters: the teapot (S01 scale / rotation / material) dropped from
+    height 10 with v = (0,-10,0) onto the ground plane, 4 substeps x 20 iterations, 100 frames (impact at frame ~45, rebound).
+    Stated tolerance: max |x_gpu - x_oracle| <= 5e-3 (0.16 % of the 3.1-unit teapot) at every 10-frame checkpoint, and
+    <= 5e-4 before the impact. (Sensitivity of the scene itself: a 1e-6 perturbation of the initial positions - one float32
+    ulp at height 10 - moves the ORACLE's own trajectory by 1.3e-4 within 10 frames and 8.6e-4 by frame 100.)"""
+    from gaia_b200.workloads import workload_model_drop
+    g, o = _both(workload_model_drop("teapot"), threads=4)
+    worst, lowest = [], 1e9
+    for chunk in range(10):
+        for s in (g, o):
+            s.run_frames(10)
+        pg, po = g.positions(0), o.positions(0)
+        assert np.isfinite(pg).all()
+        worst.append(float(np.abs(pg - po).max()))
+        lowest = min(lowest, float(po[:, 1].min()))
+        if chunk < 4:
+            assert po[:, 1].min() > 0.5 and worst[-1] < 5e-4, (chunk, worst)
+    assert lowest < 0.01 and max(worst) < 5e-3, (lowest, worst)
+    assert g.stats()["vertexSolves"] == o.stats()["vertexSolves"]
+
+
+# ------------------------------------------------------------------------------------------ config 2 in miniature
+def _assert_integer_surfaces_equal(g, o, n_meshes, n_groups):
+    cg, co = contacts_table(g.contacts()), contacts_table(o.contacts())
+    assert np.array_equal(cg, co)
+    total = 0
+    for grp in range(n_groups):
+        a, b = g.active_list(grp), o.active_list(grp)
+        assert np.array_equal(a, b), grp
+        total += len(b)
+    rels = 0
+    for m in range(n_meshes):
+        a, b = g.relations(m), o.relations(m)
+        assert np.array_equal(a, b), m
+        rels += len(b)
+    return len(co), total, rels
+
+
+def test_config2_miniature_integer_surfaces_and_trajectory():
+    """teapot + bunny + octopus + armadillo (S01 scales, shipped colourings, S01 material / friction / contact stiffness)
+    stacked with a small overlap: DCD + CCD contact sets, LBVH leaf orders, per-group active lists and face-side relations
+    bit-exact on identical states, at the start and on the GPU's own state after 20, 30 and 40 frames (the pile toppling,
+    ~150 contacts). Trajectory: the stack is chaotic once the bodies start to topple - perturbing the ORACLE's initial
+    positions by 1e-7 moves its own trajectory by 1.7e-5 at frame 10, 4.8e-5 at frame 20 and 6e-2 at frame 30 - so the
+    free-running comparison covers the first 20 frames (stated tolerance 1e-3 absolute, 0.03 % of the ~3-unit models) and
+    each later 10-frame segment restarts from the GPU's state (same tolerance per segment)."""
+    from gaia_b200.workloads import workload_ref_stack
+    wl = workload_ref_stack()
+    g, o = _both(wl, threads=8)
+
+    def integer_check():
+        state = [(g.positions(m), g.velocities(m)) for m in range(4)]
+        for s in (g, o):
+            for m, (p, v) in enumerate(state):
+                s.set_state(m, p, v)
+            s.run_iterations(0)          # DCD on the state, initial step, CCD, prepare
+        for m in range(4):
+            assert np.array_equal(g.positions(m), o.positions(m)) and np.array_equal(g.prev_positions(m), o.prev_positions(m))
+        out = _assert_integer_surfaces_equal(g, o, 4, 8)
+        for which in (0, 1, 2):
+            assert np.array_equal(g.bvh_leaf_order(which), o.bvh_leaf_order(which)), which
+        for s in (g, o):
+            for m, (p, v) in enumerate(state):
+                s.set_state(m, p, v)
+        return out
+
+    n_contacts, n_active, n_rel = integer_check()
+    found = int((o.contacts()["shortestPathFound"] == 1).sum())
+    assert n_contacts > 10 and found > 10
+    assert n_rel == 3 * found and found <= n_active <= 4 * found
+    worst, most = [], 0
+    for chunk in range(4):
+        for s in (g, o):
+            s.run_frames(10)
+        worst.append(max(float(np.abs(g.positions(m) - o.positions(m)).max()) for m in range(4)))
+        if chunk >= 1:
+            n_contacts, _, _ = integer_check()           # also puts the oracle on the GPU's state
+            most = max(most, n_contacts)
+    assert most > 60, most
+    assert max(worst) < 1e-3, worst
+
+
+def test_self_collision_relations_bit_exact():
+    """row a15 on the self-collision scene of test_gpu_collision_parity (a beam folded onto itself): a vertex can sit on
+    several contact faces and be a query vertex at once - the relation lists must agree entry by entry."""
+    from gaia_b200 import capi, meshio
+    from gaia_b200.capi import Scene
+    from oracle.binding import OracleScene
+    verts, tets = meshio.kuhn_beam(16, 2, 2, h=0.1, origin=(0, 1, 0))
+    colors = meshio.kuhn_coloring(16, 2, 2)
+    folded = verts.copy()
+    hi = verts[:, 0] > 0.8
+    folded[hi, 0] = 1.6 - verts[hi, 0] + 0.013
+    folded[hi, 1] = verts[hi, 1] + 0.12
+    folded[hi, 2] = verts[hi, 2] + 0.017
+    res = []
+    for cls, kw in ((Scene, {}), (OracleScene, dict(threads=2))):
+        s = cls(capi.default_physics_params(numSubsteps=2, iterations=4, gravity=[0, 0, 0]), capi.default_collision_params(allowCCD=0), **kw)
+        s.add_tet_mesh(verts, tets, capi.default_object_params(miu=1e5, lmbd=1e6, density=50), colors)
+        s.finalize()
+        s.set_state(0, folded, np.zeros_like(folded))
+        s.run_iterations(0)
+        res.append(s)
+    g, o = res
+    n_contacts, n_active, n_rel = _assert_integer_surfaces_equal(g, o, 1, 4)
+    assert n_contacts > 5 and n_rel > 0
+    rel = o.relations(0)
+    assert np.bincount(rel[:, 0]).max() >= 2          # some vertex carries relations of more than one contact
