@@ -140,9 +140,9 @@ cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nS
     return cudaSuccess;
 }
 
-__global__ void k_mark_boundary(int n, const int32_t* __restrict__ sorted, int4* vtx) {
+__global__ void k_mark_boundary(int n, const int32_t* __restrict__ sorted, int4* vtx, int4* vtx2) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) vtx[sorted[i]].w |= kHaloBoundaryBit;
+    if (i < n) { vtx[sorted[i]].w |= kHaloBoundaryBit; vtx2[sorted[i]].w |= kHaloBoundaryBit; }
 }
 
 // Tables of the fused exchange (the colour solve pushes its own boundary vertices): every vertex this partition sends is
@@ -174,7 +174,7 @@ cudaError_t halo_finalize(Scene& s) {
         DevBuf<int32_t> d;
         CK(d.alloc(bverts.size()));
         CK(cudaMemcpy(d.p, bverts.data(), bverts.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-        k_mark_boundary<<<((int)bverts.size() + 255) / 256, 256, 0, s.stream>>>((int)bverts.size(), d.p, s.vtx.p);
+        k_mark_boundary<<<((int)bverts.size() + 255) / 256, 256, 0, s.stream>>>((int)bverts.size(), d.p, s.vtx.p, s.vtx2.p);
         CK(cudaStreamSynchronize(s.stream));
     }
     {
@@ -182,6 +182,7 @@ cudaError_t halo_finalize(Scene& s) {
         for (int64_t v = 0; v < N; v++) prefix[v + 1] = prefix[v] + (idx[v] ? 1 : 0);
         CK(h->boundaryPrefix.alloc(N + 1));
         CK(cudaMemcpy(h->boundaryPrefix.p, prefix.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CK(sweep_mark_halo_tiles(s, h->boundaryPrefix.p));
     }
     HaloPeerTable t;
     std::memset(&t, 0, sizeof(t));

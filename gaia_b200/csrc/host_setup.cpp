@@ -348,4 +348,65 @@ bool host_finalize(Scene& s) {
     return true;
 }
 
+// Tile streams of the colour sweep (sweep.cu). The Neo-Hookean vertex force splits into a part that is LINEAR in the
+// neighbour positions, -mu * sum_tets Ds'(A w') = -mu * sum_nb W_nb (x_nb - x) with W_nb the sum of A w' over the tets
+// that share the neighbour, and the volumetric part that needs the tet (det F and the opposite face's normal). So a
+// vertex carries one 8-byte entry per distinct neighbour {sorted id, W_nb} and one 8-byte record per incident tet
+// {det B', three neighbour slots}; A*sum|m0|^2 = -sum_nb W_nb is a per-vertex constant in the header. Tiles are runs of
+// at most tileV vertices of one colour whose entries fit the shared-memory stage; sums are formed in double in ascending
+// tet order and rounded once, so a partition of the mesh builds the same numbers for the vertices it owns.
+bool build_tile_streams(Scene& s, int tileV) {
+    const int64_t N = s.nVerts;
+    const size_t nGroups = s.groupStart.size() - 1;
+    tileV = std::max(1, std::min(tileV, kTileV));
+    s.h_vtx2.assign(N, make_int4(0, 0, 0, (int)0x80000000));
+    s.h_rec.clear(); s.h_nbw.clear(); s.h_tiles.clear();
+    s.h_rec.reserve((size_t)s.nInc + 2 * (size_t)(N / tileV + nGroups + 1));
+    s.h_nbw.reserve((size_t)s.nNb + 2 * (size_t)(N / tileV + nGroups + 1));
+    s.groupTileStart.assign(nGroups + 1, 0);
+    std::vector<int32_t> info(N);
+    for (auto& m : s.meshes)
+        for (int v = 0; v < m.nV; v++)
+            info[m.sortedId[v]] = (m.id & 0x00FFFFFF) | ((m.fixedMask[v] || m.ghostMask[v]) ? (int32_t)0x80000000 : 0);
+    std::vector<double> wsum;
+    auto bits = [](float f) { int32_t i; std::memcpy(&i, &f, 4); return i; };
+    for (size_t g = 0; g < nGroups; g++) {
+        s.groupTileStart[g] = (int32_t)s.h_tiles.size();
+        int64_t v = s.groupStart[g];
+        const int64_t ve = s.groupStart[g + 1];
+        while (v < ve) {
+            TileDesc t;
+            std::memset(&t, 0, sizeof(t));
+            t.vBegin = (int32_t)v; t.recBegin = (int32_t)s.h_rec.size(); t.nbBegin = (int32_t)s.h_nbw.size();
+            int nRec = 0, nNb = 0;
+            while (v < ve && t.nV < tileV) {
+                const bool solved = info[v] >= 0;
+                const int r = solved ? s.h_incOff[v + 1] - s.h_incOff[v] : 0;
+                const int n = solved ? s.h_nbOff[v + 1] - s.h_nbOff[v] : 0;
+                if (r > kTileRecCap || n > kTileNbCap) { s.err = "a vertex has more incident tets than a sweep tile holds"; return false; }
+                if (nRec + r > kTileRecCap || nNb + n > kTileNbCap) break;
+                wsum.assign(n, 0.0);
+                double s1 = 0.0;
+                for (int j = s.h_incOff[v]; j < s.h_incOff[v] + r; j++) {
+                    const float* W = &s.h_incW[4 * (size_t)j];
+                    const uint32_t I = s.h_incIdx[j];
+                    wsum[I & 255] += W[0]; wsum[(I >> 8) & 255] += W[1]; wsum[(I >> 16) & 255] += W[2];
+                    s1 -= (double)W[0] + (double)W[1] + (double)W[2];
+                    s.h_rec.push_back(make_uint2((uint32_t)bits(W[3]), I));
+                }
+                for (int q = 0; q < n; q++) s.h_nbw.push_back(make_int2(s.h_nbList[s.h_nbOff[v] + q], bits((float)wsum[q])));
+                s.h_vtx2[v] = make_int4(nRec | (r << 16), nNb | (n << 16), bits((float)s1), info[v]);
+                nRec += r; nNb += n; t.nV++; v++;
+            }
+            if (nRec & 1) { s.h_rec.push_back(make_uint2(0, 0)); nRec++; }
+            if (nNb & 1) { s.h_nbw.push_back(make_int2(0, 0)); nNb++; }
+            t.recCount = nRec; t.nbCount = nNb;
+            s.h_tiles.push_back(t);
+        }
+    }
+    s.groupTileStart[nGroups] = (int32_t)s.h_tiles.size();
+    if (s.h_rec.size() >= ((size_t)1 << 31) || s.h_nbw.size() >= ((size_t)1 << 31)) { s.err = "scene too large for 32-bit stream offsets"; return false; }
+    return true;
+}
+
 }  // namespace gb

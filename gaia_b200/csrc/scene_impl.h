@@ -71,6 +71,12 @@ struct HaloView {
     int debug;                                // timing experiments (GAIA_B200_HALO_DEBUG)
 };
 
+// One tile of the colour sweep (sweep.cu): up to kTileV consecutive vertices of one colour whose incidence records and
+// neighbour entries are contiguous in the `rec` / `nbw` streams, so one cp.async.bulk per stream brings a tile into shared
+// memory. Counts are padded to even (16-byte copies); begins are even.
+static const int kTileV = 64, kTileRecCap = 1536, kTileNbCap = 896;
+struct TileDesc { int32_t vBegin, nV, recBegin, recCount, nbBegin, nbCount, flags, pad; };
+
 struct Scene {
     gaia_physics_params phys;
     gaia_collision_params col;
@@ -101,6 +107,20 @@ struct Scene {
     DevBuf<int32_t> nbOff, nbList; // per vertex: distinct neighbour vertices (sorted ids)
     DevBuf<int4> vtx;              // per vertex header: {incOff, nbOff, nInc | nNb << 16, meshId | fixed << 31}
     int64_t nNb = 0;
+    // tile streams of the colour sweep (sweep.cu; built by build_tile_streams)
+    std::vector<int4> h_vtx2;          // per vertex: {recLocal | nRec << 16, nbLocal | nNb << 16, bits(A*sum|m0|^2), meshId | flags}
+    std::vector<uint2> h_rec;          // per incidence: {bits(det B'), slots a | b << 8 | c << 16}
+    std::vector<int2> h_nbw;           // per (vertex, distinct neighbour): {sorted id, bits(sum of A*w' over the shared tets)}
+    std::vector<TileDesc> h_tiles;
+    std::vector<int32_t> groupTileStart;   // [G + 1]
+    DevBuf<int4> vtx2;
+    DevBuf<uint2> rec;
+    DevBuf<int2> nbw;
+    DevBuf<TileDesc> tiles;
+    int numSMs = 148;
+    bool legacySweep = false;          // round-1 kernel (k_solve_colour), kept while the tile sweep is being validated
+    int tileVOverride = 0;
+    uint32_t sweepAttrSet = 0;         // kernel variants whose shared-memory attribute is set on this scene's device
     DevBuf<int32_t> sorted2orig, orig2sorted;
     DevBuf<MeshParamsDev> meshParams;
     DevBuf<float4> ioStage;        // original-order staging for get/set
@@ -130,6 +150,8 @@ struct Scene {
     gaia_stats stats;
     bool profiling = false;
     cudaEvent_t evA = nullptr, evB = nullptr, evP0 = nullptr, evP1 = nullptr;
+    std::vector<cudaEvent_t> profEv;   // event pairs around the colour-solve launches of one iteration loop (profiling only)
+    size_t profUsed = 0;
     double solveKernelMs = 0.0;    // accumulated colour-solve kernel time while profiling
     int64_t solveKernelLaunches = 0;
 
@@ -141,6 +163,12 @@ void host_mesh_init(HostMesh& m, int32_t nV, int32_t nT, const float* xyz, const
                     int32_t nColors, const int32_t* colorOffsets, const int32_t* colorVerts, int32_t nFixed, const int32_t* fixed,
                     bool keepColourOrder);
 bool host_finalize(Scene& s);
+bool build_tile_streams(Scene& s, int tileV);
+
+// sweep.cu: the per-colour vertex solve over tiles (TMA-fed persistent blocks)
+cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv);
+cudaError_t sweep_upload(Scene& s);
+cudaError_t sweep_mark_halo_tiles(Scene& s, const int32_t* boundaryPrefixDev);
 
 // solve.cu
 cudaError_t device_upload(Scene& s);

@@ -584,6 +584,7 @@ Scene::~Scene() {
     for (auto& r : hostRegs) cudaHostUnregister(r.first);
     if (pinnedIO) cudaFreeHost(pinnedIO);
     if (iterGraphExec) cudaGraphExecDestroy(iterGraphExec);
+    for (cudaEvent_t e : profEv) if (e) cudaEventDestroy(e);
     if (evA) cudaEventDestroy(evA);
     if (evP0) cudaEventDestroy(evP0);
     if (evP1) cudaEventDestroy(evP1);
@@ -671,6 +672,19 @@ cudaError_t device_upload(Scene& s) {
     CK(cudaMemcpyAsync(s.sorted2orig.p, s.sortedToOrig.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.orig2sorted.p, o2s.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaStreamSynchronize(s.stream));
+    {   // tile streams of the colour sweep: small colours get smaller tiles, so that a colour still spreads over the SMs
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0) s.numSMs = sms;
+        int64_t largest = 0;
+        for (size_t g = 0; g + 1 < s.groupStart.size(); g++) largest = std::max<int64_t>(largest, s.groupStart[g + 1] - s.groupStart[g]);
+        if (const char* e = getenv("GAIA_B200_LEGACY_SWEEP")) s.legacySweep = atoi(e) != 0;      // (validation of the tile sweep only)
+        if (const char* e = getenv("GAIA_B200_TILE_V")) s.tileVOverride = atoi(e);
+        int tileV = kTileV;
+        while (tileV > 8 && largest < (int64_t)s.numSMs * 3 * tileV) tileV >>= 1;
+        if (!build_tile_streams(s, s.tileVOverride > 0 ? s.tileVOverride : tileV)) return cudaErrorInvalidValue;
+        CK(sweep_upload(s));
+    }
     std::vector<uint32_t>().swap(s.h_incIdx);
     std::vector<float>().swap(s.h_incW);
     std::vector<int32_t>().swap(s.h_nbList);
@@ -785,19 +799,22 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             const int vb = s.groupStart[g], ve = s.groupStart[g + 1];
             if (ve <= vb && !halo) continue;
             if (hasContacts) { CK(collision_update_infos(s, g, captured)); }
-            if (s.profiling) cudaEventRecord(s.evA, s.stream);
+            cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+            if (s.profiling) {      // a pair of events per launch, read back at the end of the loop: no host sync between launches
+                if (s.profUsed + 2 > s.profEv.size()) { s.profEv.resize(s.profUsed + 2, nullptr); }
+                for (size_t q = s.profUsed; q < s.profUsed + 2; q++) if (!s.profEv[q]) CK(cudaEventCreate(&s.profEv[q]));
+                pe0 = s.profEv[s.profUsed]; pe1 = s.profEv[s.profUsed + 1]; s.profUsed += 2;
+                cudaEventRecord(pe0, s.stream);
+            }
             hv.epochOffset = it * G + g;
-            if (ve > vb) {
+            if (ve > vb && !s.legacySweep) {
+                CK(sweep_launch(s, g, s.solveLanes == 8 ? 8 : 4, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
+            } else if (ve > vb) {
                 const int lanes = (s.solveLanes && !lanesFromEnv) ? s.solveLanes : g_lanes;
                 if (hasContacts) launch_solve<true>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
                 else launch_solve<false>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
             }
-            if (s.profiling) {
-                cudaEventRecord(s.evB, s.stream);
-                cudaEventSynchronize(s.evB);
-                float ms = 0.f; cudaEventElapsedTime(&ms, s.evA, s.evB);
-                s.solveKernelMs += ms; s.solveKernelLaunches++;
-            }
+            if (s.profiling) cudaEventRecord(pe1, s.stream);
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
             else if (halo) {
@@ -823,6 +840,14 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
         }
     }
     if (fused) { k_halo_advance<<<1, 32, 0, s.stream>>>(hv, nIters * G); s.stats.kernelLaunches++; }
+    if (s.profiling && s.profUsed) {
+        CK(cudaStreamSynchronize(s.stream));
+        for (size_t q = 0; q + 1 < s.profUsed; q += 2) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, s.profEv[q], s.profEv[q + 1]) == cudaSuccess) { s.solveKernelMs += ms; s.solveKernelLaunches++; }
+        }
+        s.profUsed = 0;
+    }
     return cudaGetLastError();
 }
 
@@ -1048,6 +1073,7 @@ int check_device_errors(Scene& s) {
     if (h[2]) { s.err = "contact list overflow"; return GAIA_ERR_OVERFLOW; }
     if (h[3]) { s.err = "tetrahedral traversal stack overflow"; return GAIA_ERR_OVERFLOW; }
     if (h[4]) { s.err = "halo exchange timed out waiting for a neighbour partition"; return GAIA_ERR_TIMEOUT; }
+    if (h[5]) { s.err = "colour sweep: a bulk copy never completed"; return GAIA_ERR_TIMEOUT; }
     return GAIA_OK;
 }
 

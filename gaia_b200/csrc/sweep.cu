@@ -1,0 +1,546 @@
+// Per-colour VBD vertex solve over TILES, hand-written for sm_100a: persistent blocks fed by the bulk-copy engine.
+//
+// Reference semantics (CPU/TBB path) - the same list as solve.cu:
+//   accumlateMaterialForceAndHessian2 (Neo-Hookean)    M/VBD/VBD_NeoHookean.cpp:379-581
+//   accumlateInertiaForceAndHessian                    M/VBD/VBD_BaseMaterial.h:359-366
+//   accumlateBoundaryForceAndHessian + friction        M/VBD/VBDPhysics.cpp:2821-2954, 2563-2592
+//   accumlateCollisionForceAndHessian[PerCollision]    M/VBD/VBDPhysics.cpp:2956-3047
+//   VBDStepWithCollision + solve3x3_psd_stable         M/VBD/VBDPhysics.cpp:2402-2483, 3P/CuMatrix/.../CuMatrix.h:235-267
+// The kernel this replaces in the reference: VBDSolveParallelGroup_vertexSweep_2hierarchiesGPU, M/VBD/VBDPhysicsCompute.cu:803-908
+// (one block per vertex, one thread per incident tet, 9x9 Hessians in shared memory).
+//
+// Design. A colour is a list of tiles (host_setup.cpp: build_tile_streams): <= 64 consecutive vertices
+// whose per-tet records (8 B: det B', three 8-bit neighbour slots) and per-neighbour entries (8 B: sorted id, summed
+// weight of the linear term) are contiguous in HBM. A block is persistent over the tiles t = first + blockIdx.x + k*gridDim.x:
+//   * thread 0 is the producer: cp.async.bulk (UBLKCP) copies of the tile's records, neighbour entries, vertex headers and
+//     own positions into a 2-deep shared-memory ring, completion counted by an mbarrier (complete_tx) - the streams never
+//     pass through registers or the LSU/L1 path, and the copy of tile k+2 is in flight while tile k is computed;
+//   * L lanes serve one vertex. The scattered part - gathering the ~14 distinct neighbour positions - is software
+//     pipelined one round ahead in registers (issued before the current round's arithmetic, consumed after it), staged
+//     into shared memory relative to the owner, and feeds the linear term  -mu * sum_nb W_nb (x_nb - x)  on the way;
+//   * the volumetric term walks the records: three ld.shared.v4 per tet, n = (b-a)x(c-a), det F = (a.n) det B',
+//     f -= lmbd (det F - a) n/6 ... (SURVEY.md §8(a) "math restatement"), 10 sums butterfly-reduced over the L lanes;
+//   * the vertex-level tail (damping, inertia, world box + friction, contacts, 3x3 solve, in-place store, halo push)
+//     runs transposed: thread t finishes vertex t of the tile, at full SIMT width.
+// Arithmetic per vertex depends only on L (never on the tiling), and every contraction is written with _rn intrinsics,
+// so partitions of a mesh and the single-GPU run produce the same bits.
+#include "scene_impl.h"
+#include <algorithm>
+#include <cstring>
+
+namespace gb {
+
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
+
+static const int kSweepThreads = 256;
+static const int kSweepBlocksPerSM = 3;
+
+// ---- shared memory map (bytes). Rings: records 2 deep, neighbour entries 3 deep, vertex headers / own positions 4 deep
+// (the tail of tile k-1 still reads its headers while the copies of tile k+3 are issued).
+static const int kRecStage = kTileRecCap * 8, kNbwStage = kTileNbCap * 8, kVtxStage = kTileV * 16;
+static const int kSmRec = 0;                                          // [2][kTileRecCap] uint2
+static const int kSmNbw = kSmRec + 2 * kRecStage;                      // [3][kTileNbCap] int2
+static const int kSmHdr = kSmNbw + 3 * kNbwStage;                      // [4][kTileV] int4
+static const int kSmPos = kSmHdr + 4 * kVtxStage;                      // [4][kTileV] float4
+static const int kSmRel = kSmPos + 4 * kVtxStage;                      // [kTileNbCap] float4: neighbour positions relative to the owner
+static const int kSmAcc = kSmRel + kTileNbCap * 16;                    // [2][9][kTileV] float
+static const int kSmInfo = kSmAcc + 2 * 9 * kTileV * 4;                // [4] TileDesc
+static const int kSmBarRec = kSmInfo + 4 * 32;                         // [2] mbarrier: records of tile k landed
+static const int kSmBarNb = kSmBarRec + 2 * 8;                         // [3] mbarrier: neighbour entries + headers + positions landed
+static const int kSmTotal = kSmBarNb + 3 * 8;
+static_assert(3 * (kSmTotal + 1024) <= 227 * 1024, "three blocks per SM");
+
+__device__ __forceinline__ float3 f3(float4 v) { return make_float3(v.x, v.y, v.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return make_float3(a.x - b.x, a.y - b.y, a.z - b.z); }
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// global -> shared bulk copy (TMA engine, 1-D): size is a multiple of 16 bytes, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 r;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+struct SweepArgs {
+    int tileBegin, tileEnd;              // tiles of this colour
+    float4* pos;
+    const float4* prev;
+    const float4* inertia;
+    const int4* vtx2;
+    const uint2* rec;
+    const int2* nbw;
+    const TileDesc* tiles;
+    const MeshParamsDev* mp;
+    StepParamsDev sp;
+    int applyFriction;
+    int needPrev;                        // some mesh has damping, or the world box has friction: the tail reads x_prev
+    ContactView cv;
+    int32_t* errFlags;
+    HaloView hv;
+};
+
+// IPC-style mollified friction (computeVertexFriction, VBDPhysics.cpp:2563-2592) for an axis-aligned tangent basis
+__device__ __forceinline__ void box_friction(float mu, float lambda, float ua, float ub, float epsU, float& fa, float& fb, float& haa) {
+    const float uNorm = sqrtf(ua * ua + ub * ub);
+    fa = 0.f; fb = 0.f; haa = 0.f;
+    if (uNorm > 0.f) {
+        const float f1 = (uNorm > epsU) ? 1.f / uNorm : (-uNorm / epsU + 2.f) / epsU;
+        const float s = -mu * lambda * f1;
+        fa = s * ua; fb = s * ub;
+        haa = mu * lambda * f1;
+    }
+}
+
+// The vertex-level part of VBDStepWithCollision once the incident-tet sums are known. (fx,fy,fz) = -f_elastic,
+// s1 = A sum|m0|^2, g = sum A g g^T (already / 6). Returns true when a new position was written.
+template <bool HAS_CONTACTS>
+__device__ __forceinline__ bool vertex_tail(int s, float3 x, float4 ys, float3 xp, const MeshParamsDev* __restrict__ P,
+                                            float fx, float fy, float fz, float s1, float g00, float g01, float g02, float g11, float g12, float g22,
+                                            float4* pos, const StepParamsDev& sp, int applyFriction, const ContactView& cv, int32_t* errFlags, float4& xNew) {
+    const float miu = P->miu, lmbd = P->lmbd, dampH = P->dampH, dampD = P->dampD;
+    float F0 = -fx, F1 = -fy, F2 = -fz;
+    const float hd = miu * s1;
+    float h00 = lmbd * g00 + hd, h01 = lmbd * g01, h02 = lmbd * g02, h11 = lmbd * g11 + hd, h12 = lmbd * g12, h22 = lmbd * g22 + hd;
+    if ((dampH != 0.f) | (dampD != 0.f)) {
+        // dampingH = (H_vol*gamma_h + mu*|m|^2*A*gamma_d I)/dt ; f -= dampingH*(x - x_prev); H += dampingH
+        const float idt = 1.f / sp.dt;
+        const float3 d = x - xp;
+        const float ch = lmbd * dampH * idt, cd = miu * s1 * dampD * idt;
+        const float d00 = ch * g00 + cd, d01 = ch * g01, d02 = ch * g02, d11 = ch * g11 + cd, d12 = ch * g12, d22 = ch * g22 + cd;
+        F0 -= d00 * d.x + d01 * d.y + d02 * d.z;
+        F1 -= d01 * d.x + d11 * d.y + d12 * d.z;
+        F2 -= d02 * d.x + d12 * d.y + d22 * d.z;
+        h00 += d00; h01 += d01; h02 += d02; h11 += d11; h12 += d12; h22 += d22;
+    }
+    {   // inertia
+        const float m = ys.w;
+        const float w = m * sp.dtSqrReciprocal;
+        F0 += (m * (ys.x - x.x)) * sp.dtSqrReciprocal;
+        F1 += (m * (ys.y - x.y)) * sp.dtSqrReciprocal;
+        F2 += (m * (ys.z - x.z)) * sp.dtSqrReciprocal;
+        h00 += w; h11 += w; h22 += w;
+    }
+    if (sp.usePlaneGround) {   // world-box penalty + friction, per violated axis (CPU semantics)
+        const float xs[3] = {x.x, x.y, x.z};
+        float Fb[3] = {0.f, 0.f, 0.f}, Hb[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            float depth = 0.f, sgn = 0.f;
+            if (xs[d] < sp.boundsMin[d]) { depth = sp.boundsMin[d] - xs[d]; sgn = 1.f; }
+            else if (xs[d] > sp.boundsMax[d]) { depth = xs[d] - sp.boundsMax[d]; sgn = -1.f; }
+            if (sgn != 0.f) {
+                Fb[d] += sgn * (depth * sp.kBoundary);
+                Hb[d] += sp.kBoundary;
+                if (applyFriction) {
+                    const float dx[3] = {x.x - xp.x, x.y - xp.y, x.z - xp.z};
+                    const int a = (d + 1) % 3, b2 = (d + 2) % 3;
+                    float fa, fb, haa;
+                    box_friction(sp.muBoundary, depth * sp.kBoundary, dx[a], dx[b2], sp.epsVBoundary * sp.dt, fa, fb, haa);
+                    Fb[a] += fa; Fb[b2] += fb; Hb[a] += haa; Hb[b2] += haa;
+                }
+            }
+        }
+        F0 += Fb[0]; F1 += Fb[1]; F2 += Fb[2];
+        h00 += Hb[0]; h11 += Hb[1]; h22 += Hb[2];
+    }
+    if (HAS_CONTACTS) {   // own contact with weight 1, contacts on faces this vertex belongs to with weight -bary
+        const int own = __ldg(cv.contactOfVertex + s);
+        const int rb = __ldg(cv.relOff + s), re = __ldg(cv.relOff + s + 1);
+        for (int q = (own >= 0 ? -1 : 0); q < re - rb; q++) {
+            int slot; float bw;
+            if (q < 0) { slot = own; bw = 1.f; }
+            else {
+                const int2 r = __ldg(cv.rel + rb + q);
+                slot = r.x;
+                const float4 h1 = __ldg(cv.cH1 + slot);
+                bw = -(r.y == 0 ? h1.z : (r.y == 1 ? h1.w : __ldg(cv.cB2 + slot)));
+            }
+            const float4 cf = __ldg(cv.cF + slot);
+            if (cf.w > 0.f && bw != 0.f) {
+                const float4 c0 = __ldg(cv.cH0 + slot), c1 = __ldg(cv.cH1 + slot);
+                const float b2w = bw * bw;
+                F0 += cf.x * bw; F1 += cf.y * bw; F2 += cf.z * bw;
+                h00 += c0.x * b2w; h01 += c0.y * b2w; h02 += c0.z * b2w; h11 += c0.w * b2w; h12 += c1.x * b2w; h22 += c1.y * b2w;
+            }
+        }
+    }
+    // 3x3 solve (solve3x3_psd_stable) and in-place update
+    if (F0 * F0 + F1 * F1 + F2 * F2 > 1e-10f) {
+        const float i11 = h22 * h11 - h12 * h12;
+        const float i12 = -(h22 * h01 - h12 * h02);
+        const float i13 = h12 * h01 - h11 * h02;
+        const float det = h00 * i11 + h01 * i12 + h02 * i13;
+        float dx0, dx1, dx2, step;
+        if (fabsf(det) < 1e-5f * (fabsf(h00 * i11) + fabsf(h01 * i12) + fabsf(h02 * i13))) {
+            dx0 = F0; dx1 = F1; dx2 = F2; step = sp.stepSizeGD;
+            atomicAdd(errFlags + 1, 1);
+        } else {
+            const float deti = 1.f / det;
+            const float i22 = h22 * h00 - h02 * h02;
+            const float i23 = -(h12 * h00 - h01 * h02);
+            const float i33 = h11 * h00 - h01 * h01;
+            dx0 = deti * (i11 * F0 + i12 * F1 + i13 * F2);
+            dx1 = deti * (i12 * F0 + i22 * F1 + i23 * F2);
+            dx2 = deti * (i13 * F0 + i23 * F1 + i33 * F2);
+            step = sp.stepSize;
+        }
+        if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return false; }
+        xNew = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
+        pos[s] = xNew;
+        return true;
+    }
+    return false;
+}
+
+// Fused halo exchange, consumer side: wait until every neighbour partition has published `epoch` (its previous colour
+// launch, pushes included, is complete). One lane polls; 5 s without progress = a neighbour died (errFlags[4]).
+__device__ __forceinline__ void sweep_halo_wait(const HaloPeerTable* tab, uint32_t epoch, int nPeers, int32_t* errFlags) {
+    for (int p = 0; p < nPeers; p++) {
+        if (*(volatile int32_t*)(errFlags + 4)) return;
+        const unsigned long long t0 = gtimer();
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(tab->myFlag[p]) : "memory");
+            if ((int32_t)(v - epoch) >= 0) break;
+            if (gtimer() - t0 > 5000000000ull) { atomicAdd(errFlags + 4, 1); return; }
+            __nanosleep(64);
+        }
+    }
+}
+
+// what a thread holds of the NEXT round while the current one is computed: its share of the vertex's neighbour gathers
+template <int NQ>
+struct Prefetch {
+    float4 p[NQ];      // gathered neighbour positions (absolute)
+    float w[NQ];       // their linear-term weights
+    int hdrY;          // nbLocal | nNb << 16 of the vertex (0 when the lane has no vertex)
+};
+
+template <int L, bool HAS_CONTACTS, bool HALO>
+__global__ void __launch_bounds__(kSweepThreads, kSweepBlocksPerSM)
+k_sweep_tiles(const SweepArgs a) {
+    constexpr int VPR = kSweepThreads / L;          // vertices per round
+    constexpr int NQ = 16 / L;                      // gathers held in registers per lane (16 neighbours per vertex)
+    extern __shared__ __align__(128) unsigned char smem[];
+    const uint32_t sb = smem_u32(smem);
+    const int tid = threadIdx.x, lane = tid & (L - 1), sub = tid / L;
+    const int nMine = (a.tileEnd - a.tileBegin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // tiles of this block
+    TileDesc* info = (TileDesc*)(smem + kSmInfo);
+    const float4* posRO = a.pos;      // gathers only touch other colours: read-only for this launch
+
+    if (HALO && blockIdx.x == 0 && tid < a.hv.nPeers) {
+        // everything this stream launched before is complete (stream order): publish it to the neighbours
+        const uint32_t done = *(volatile const uint32_t*)a.hv.ctl + (uint32_t)a.hv.epochOffset;
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.hv.tab->peerFlag[tid]), "r"(done) : "memory");
+    }
+    if (nMine <= 0) return;
+    if (tid == 0) {
+        for (int i = 0; i < 5; i++) mbar_init(sb + kSmBarRec + 8 * i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    // ---- producer (thread 0). Tile k: neighbour entries -> slot k % 3, headers + own positions -> slot k & 3 (one
+    // barrier, the data the gathers need first); records -> slot k & 1 (their own barrier, needed half a tile later)
+    auto issue_nb = [&](int k) {
+        const TileDesc d = a.tiles[a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x];
+        const int s3 = k % 3, s4 = k & 3;
+        info[s4] = d;
+        const uint32_t bar = sb + kSmBarNb + 8 * s3;
+        const uint32_t bNb = (uint32_t)d.nbCount * 8u, bV = (uint32_t)d.nV * 16u;
+        mbar_expect_tx(bar, bNb + 2 * bV);
+        if (bNb) bulk_g2s(sb + kSmNbw + s3 * kNbwStage, a.nbw + d.nbBegin, bNb, bar);
+        bulk_g2s(sb + kSmHdr + s4 * kVtxStage, a.vtx2 + d.vBegin, bV, bar);
+        bulk_g2s(sb + kSmPos + s4 * kVtxStage, a.pos + d.vBegin, bV, bar);
+    };
+    auto issue_rec = [&](int k) {
+        const TileDesc d = a.tiles[a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x];
+        const uint32_t bar = sb + kSmBarRec + 8 * (k & 1);
+        const uint32_t bRec = (uint32_t)d.recCount * 8u;
+        mbar_expect_tx(bar, bRec);
+        if (bRec) bulk_g2s(sb + kSmRec + (k & 1) * kRecStage, a.rec + d.recBegin, bRec, bar);
+    };
+    if (tid == 0) {
+        issue_nb(0); issue_rec(0);
+        if (nMine > 1) { issue_nb(1); issue_rec(1); }
+        if (nMine > 2) issue_nb(2);
+    }
+    // (returns false when the copies never arrived - a watchdog for a sick device: the block leaves instead of spinning)
+    auto wait_bar = [&](uint32_t bar, uint32_t parity) -> bool {
+        if (mbar_try_wait(bar, parity)) return true;
+        const unsigned long long t0 = gtimer();
+        while (!mbar_try_wait(bar, parity))
+            if (gtimer() - t0 > 4000000000ull) { if (tid == 0) atomicAdd(a.errFlags + 5, 1); return false; }
+        return true;
+    };
+
+    bool haloWaited = false;
+    // ---- gathers of round (k, r): wait for the tile's neighbour entries (first round), then request this lane's positions
+    auto prefetch = [&](int k, int r, Prefetch<NQ>& pf) -> bool {
+        const int s3 = k % 3, s4 = k & 3;
+        if (r == 0 && !wait_bar(sb + kSmBarNb + 8 * s3, (uint32_t)(k / 3) & 1u)) return false;
+        bool ghost = false;
+        if (HALO) {
+            // a tile that holds boundary vertices also holds vertices whose neighbours are ghosts: wait for the neighbour
+            // partitions' previous colour before gathering, and gather past L1
+            ghost = (info[s4].flags & 1) != 0;
+            if (ghost && !haloWaited) {
+                if (tid == 0 && !(a.hv.debug & 1)) sweep_halo_wait(a.hv.tab, *(volatile const uint32_t*)a.hv.ctl + (uint32_t)a.hv.epochOffset, a.hv.nPeers, a.errFlags);
+                __syncthreads();
+                haloWaited = true;
+            }
+        }
+        const int v = r * VPR + sub;
+        pf.hdrY = 0;
+        if (v < info[s4].nV) {
+            const int4 h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + v * 16);
+            if (h.w >= 0 && a.mp[h.w & 0x00FFFFFF].activeSolve) pf.hdrY = h.y;
+        }
+        const int nbLocal = pf.hdrY & 0xFFFF, nNb = pf.hdrY >> 16;
+        const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + nbLocal * 8;
+#pragma unroll
+        for (int q = 0; q < NQ; q++) {
+            const int i = lane + q * L;
+            pf.p[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+            pf.w[q] = 0.f;
+            if (i < nNb) {
+                const uint2 e = lds64(nbAddr + i * 8);
+                pf.w[q] = __uint_as_float(e.y);
+                pf.p[q] = (HALO && ghost) ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
+            }
+        }
+        return true;
+    };
+
+    Prefetch<NQ> pf;
+    if (!prefetch(0, 0, pf)) return;
+
+#pragma unroll 1
+    for (int k = 0; k < nMine; k++) {
+        const int st = k & 1, s3 = k % 3, s4 = k & 3;
+        const int nV = info[s4].nV, vBegin = info[s4].vBegin;
+        const bool ghostTile = HALO && (info[s4].flags & 1);
+        const int rounds = (nV + VPR - 1) / VPR;
+        float* acc = (float*)(smem + kSmAcc + st * (9 * kTileV * 4));
+        // the tail's per-vertex inputs that are not in shared memory: pulled into L1 now, read after the rounds
+        if (tid < nV) {
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.inertia + vBegin + tid));
+            if (a.needPrev) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.prev + vBegin + tid));
+        }
+
+#pragma unroll 1
+        for (int r = 0; r < rounds; r++) {
+            // ---- current round: stage the gathered neighbours relative to the owner, linear term on the way
+            const int v = r * VPR + sub;
+            const int nbLocal = pf.hdrY & 0xFFFF, nNb = pf.hdrY >> 16;
+            const bool active = nNb > 0;       // (a solved vertex of a tet mesh always has neighbours)
+            int4 h = make_int4(0, 0, 0, 0);
+            float3 x = make_float3(0.f, 0.f, 0.f);
+            if (active) {
+                h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + v * 16);
+                x = f3(*(const float4*)(smem + kSmPos + s4 * kVtxStage + v * 16));
+            }
+            const uint32_t relAddr = sb + kSmRel + nbLocal * 16;
+            float lx = 0.f, ly = 0.f, lz = 0.f;
+#pragma unroll
+            for (int q = 0; q < NQ; q++) {
+                const int i = lane + q * L;
+                if (i < nNb) {
+                    const float rx = __fsub_rn(pf.p[q].x, x.x), ry = __fsub_rn(pf.p[q].y, x.y), rz = __fsub_rn(pf.p[q].z, x.z);
+                    const float w = pf.w[q];
+                    // (the loaded .w is stored too: all four registers of the gather stay live until here, so the compiler
+                    //  cannot hand one of them to another value and stall on the in-flight load)
+                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(relAddr + i * 16), "f"(rx), "f"(ry), "f"(rz), "f"(pf.p[q].w) : "memory");
+                    lx = __fmaf_rn(w, rx, lx); ly = __fmaf_rn(w, ry, ly); lz = __fmaf_rn(w, rz, lz);
+                }
+            }
+            if (nNb > NQ * L) {      // vertices with more than 16 distinct neighbours: the rest is gathered in place
+                const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + nbLocal * 8;
+                for (int i = lane + NQ * L; i < nNb; i += L) {
+                    const uint2 e = lds64(nbAddr + i * 8);
+                    const float4 p = ghostTile ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
+                    const float w = __uint_as_float(e.y);
+                    const float rx = __fsub_rn(p.x, x.x), ry = __fsub_rn(p.y, x.y), rz = __fsub_rn(p.z, x.z);
+                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(relAddr + i * 16), "f"(rx), "f"(ry), "f"(rz), "f"(w) : "memory");
+                    lx = __fmaf_rn(w, rx, lx); ly = __fmaf_rn(w, ry, ly); lz = __fmaf_rn(w, rz, lz);
+                }
+            }
+            // ---- next round's gathers go out now; they land while this round's records are processed
+            if (r + 1 < rounds) prefetch(k, r + 1, pf);
+            else if (k + 1 < nMine) { if (!prefetch(k + 1, 0, pf)) return; }
+            if (r == 0 && !wait_bar(sb + kSmBarRec + 8 * st, (uint32_t)(k >> 1) & 1u)) return;
+            __syncwarp();
+
+            // ---- volumetric term over the incident tets: lane l takes records l, l+L, ...
+            float miu = 0.f, lmbd = 0.f, aConst = 0.f;
+            if (active) { const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF); miu = P->miu; lmbd = P->lmbd; aConst = P->a; }
+            float fx = 0.f, fy = 0.f, fz = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
+            const int nRec = active ? (h.x >> 16) : 0;
+            const uint32_t recAddr = sb + kSmRec + st * kRecStage + (h.x & 0xFFFF) * 8;
+            uint2 R = make_uint2(0u, 0u);
+            if (lane < nRec) R = lds64(recAddr + lane * 8);
+#pragma unroll 2
+            for (int j = lane; j < nRec; j += L) {
+                uint2 Rn = R;
+                if (j + L < nRec) Rn = lds64(recAddr + (j + L) * 8);       // the next record is requested before this one is consumed
+                const float dB = __uint_as_float(R.x);
+                const uint32_t I = R.y;
+                const float3 pa = f3(lds128(relAddr + ((I & 0xFFu) << 4)));
+                const float3 pb = f3(lds128(relAddr + ((I >> 4) & 0xFF0u)));
+                const float3 pc = f3(lds128(relAddr + ((I >> 12) & 0xFF0u)));
+                // n = (b-a) x (c-a);  det(Ds') = a . n;  det F = det(Ds') det(B');  A*g = -n/6;  6 A g g^T = det(B') n n^T
+                const float3 u = pb - pa, w = pc - pa;
+                float3 n;
+                n.x = __fmaf_rn(u.y, w.z, -__fmul_rn(u.z, w.y));
+                n.y = __fmaf_rn(u.z, w.x, -__fmul_rn(u.x, w.z));
+                n.z = __fmaf_rn(u.x, w.y, -__fmul_rn(u.y, w.x));
+                const float detDs = __fmaf_rn(pa.z, n.z, __fmaf_rn(pa.y, n.y, __fmul_rn(pa.x, n.x)));
+                const float kk = __fmaf_rn(detDs, dB, -aConst);        // det F - a
+                fx = __fmaf_rn(kk, n.x, fx); fy = __fmaf_rn(kk, n.y, fy); fz = __fmaf_rn(kk, n.z, fz);
+                const float nx = __fmul_rn(dB, n.x), ny = __fmul_rn(dB, n.y), nz = __fmul_rn(dB, n.z);
+                g00 = __fmaf_rn(nx, n.x, g00); g01 = __fmaf_rn(nx, n.y, g01); g02 = __fmaf_rn(nx, n.z, g02);
+                g11 = __fmaf_rn(ny, n.y, g11); g12 = __fmaf_rn(ny, n.z, g12); g22 = __fmaf_rn(nz, n.z, g22);
+                R = Rn;
+            }
+            // -f = mu * sum_nb W (x_nb - x) + lmbd * sum_tets (det F - a) * (-n / 6)
+            const float lm6 = lmbd * (-1.f / 6.f);
+            fx = __fmaf_rn(lm6, fx, __fmul_rn(miu, lx)); fy = __fmaf_rn(lm6, fy, __fmul_rn(miu, ly)); fz = __fmaf_rn(lm6, fz, __fmul_rn(miu, lz));
+#pragma unroll
+            for (int o = L / 2; o > 0; o >>= 1) {
+                fx += __shfl_xor_sync(0xffffffffu, fx, o); fy += __shfl_xor_sync(0xffffffffu, fy, o); fz += __shfl_xor_sync(0xffffffffu, fz, o);
+                g00 += __shfl_xor_sync(0xffffffffu, g00, o); g01 += __shfl_xor_sync(0xffffffffu, g01, o); g02 += __shfl_xor_sync(0xffffffffu, g02, o);
+                g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
+            }
+            if (lane == 0 && v < nV) {
+                acc[0 * kTileV + v] = fx; acc[1 * kTileV + v] = fy; acc[2 * kTileV + v] = fz;
+                acc[3 * kTileV + v] = g00; acc[4 * kTileV + v] = g01; acc[5 * kTileV + v] = g02;
+                acc[6 * kTileV + v] = g11; acc[7 * kTileV + v] = g12; acc[8 * kTileV + v] = g22;
+            }
+        }
+        __syncthreads();      // sums complete; this tile's record / neighbour slots and the staging rows are free again
+        if (tid == 0) {
+            if (k + 2 < nMine) issue_rec(k + 2);
+            if (k + 3 < nMine) issue_nb(k + 3);
+        }
+
+        // ---- transposed tail: thread t finishes vertex t of the tile
+        bool pushed = false;
+        if (tid < nV) {
+            const int4 h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + tid * 16);
+            const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF);
+            if (h.w >= 0 && P->activeSolve) {
+                const int s = vBegin + tid;
+                const float3 x = f3(*(const float4*)(smem + kSmPos + s4 * kVtxStage + tid * 16));
+                const float4 ys = __ldg(a.inertia + s);
+                float4 xpv = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (a.needPrev) xpv = __ldg(a.prev + s);
+                float4 xNew;
+                const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, acc[0 * kTileV + tid], acc[1 * kTileV + tid], acc[2 * kTileV + tid],
+                                       __int_as_float(h.z), acc[3 * kTileV + tid] * (1.f / 6.f), acc[4 * kTileV + tid] * (1.f / 6.f),
+                                       acc[5 * kTileV + tid] * (1.f / 6.f), acc[6 * kTileV + tid] * (1.f / 6.f), acc[7 * kTileV + tid] * (1.f / 6.f),
+                                       acc[8 * kTileV + tid] * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
+                if (HALO && wrote && (h.w & kHaloBoundaryBit) && !(a.hv.debug & 2)) {
+                    const int si = __ldg(a.hv.sendIdx + s);
+                    for (int q = 0; q < (si & 15); q++) {
+                        const int2 en = __ldg(a.hv.sendEnt + (si >> 4) + q);
+                        a.hv.tab->peerPos[en.x][en.y] = xNew;
+                    }
+                    pushed = true;
+                }
+            }
+        }
+        // the next launch of the stream publishes the epoch; the stores must be performed system-wide before it does
+        if (HALO && pushed) __threadfence_system();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------- host
+cudaError_t sweep_upload(Scene& s) {
+    CK(s.vtx2.alloc(s.h_vtx2.size())); CK(s.rec.alloc(s.h_rec.size() + 2)); CK(s.nbw.alloc(s.h_nbw.size() + 2)); CK(s.tiles.alloc(s.h_tiles.size() + 1));
+    CK(cudaMemcpyAsync(s.vtx2.p, s.h_vtx2.data(), s.h_vtx2.size() * sizeof(int4), cudaMemcpyHostToDevice, s.stream));
+    if (!s.h_rec.empty()) CK(cudaMemcpyAsync(s.rec.p, s.h_rec.data(), s.h_rec.size() * sizeof(uint2), cudaMemcpyHostToDevice, s.stream));
+    if (!s.h_nbw.empty()) CK(cudaMemcpyAsync(s.nbw.p, s.h_nbw.data(), s.h_nbw.size() * sizeof(int2), cudaMemcpyHostToDevice, s.stream));
+    if (!s.h_tiles.empty()) CK(cudaMemcpyAsync(s.tiles.p, s.h_tiles.data(), s.h_tiles.size() * sizeof(TileDesc), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaStreamSynchronize(s.stream));
+    std::vector<uint2>().swap(s.h_rec);
+    std::vector<int2>().swap(s.h_nbw);
+    std::vector<int4>().swap(s.h_vtx2);
+    return cudaSuccess;
+}
+
+// HALO: a tile that holds boundary vertices (vertices this partition sends = vertices with ghost neighbours) waits for the
+// neighbours' epoch and gathers past L1
+__global__ void k_tile_halo_flags(int nTiles, TileDesc* tiles, const int32_t* __restrict__ boundaryPrefix) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nTiles) return;
+    const int b = tiles[t].vBegin, e = b + tiles[t].nV;
+    tiles[t].flags = (boundaryPrefix[e] != boundaryPrefix[b]) ? 1 : 0;
+}
+cudaError_t sweep_mark_halo_tiles(Scene& s, const int32_t* boundaryPrefixDev) {
+    const int n = (int)s.h_tiles.size();
+    if (n) k_tile_halo_flags<<<(n + 255) / 256, 256, 0, s.stream>>>(n, s.tiles.p, boundaryPrefixDev);
+    return cudaStreamSynchronize(s.stream);
+}
+
+template <int L, bool HC, bool HALO>
+static cudaError_t launch_tiles(Scene& s, const SweepArgs& a) {
+    const int nTiles = a.tileEnd - a.tileBegin;
+    if (nTiles <= 0) return cudaSuccess;
+    const uint32_t variant = 1u << ((L == 8 ? 4 : 0) + (HC ? 2 : 0) + (HALO ? 1 : 0));
+    if (!(s.sweepAttrSet & variant)) {      // per scene = per device (a second scene on another GPU sets its own)
+        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmTotal));
+        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        s.sweepAttrSet |= variant;
+    }
+    const int grid = std::min(nTiles, s.numSMs * kSweepBlocksPerSM);
+    k_sweep_tiles<L, HC, HALO><<<grid, kSweepThreads, kSmTotal, s.stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv) {
+    SweepArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.tileBegin = s.groupTileStart[group]; a.tileEnd = s.groupTileStart[group + 1];
+    a.pos = s.pos.p; a.prev = s.prev.p; a.inertia = s.inertia.p; a.vtx2 = s.vtx2.p; a.rec = s.rec.p; a.nbw = s.nbw.p; a.tiles = s.tiles.p;
+    a.mp = s.meshParams.p; a.sp = s.stepParams; a.applyFriction = applyFriction; a.cv = cv; a.errFlags = s.errFlags.p;
+    a.needPrev = 0;
+    for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
+    if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
+    if (hv) a.hv = *hv;
+    const bool l8 = lanes == 8;
+    if (hv) {
+        if (hasContacts) return l8 ? launch_tiles<8, true, true>(s, a) : launch_tiles<4, true, true>(s, a);
+        return l8 ? launch_tiles<8, false, true>(s, a) : launch_tiles<4, false, true>(s, a);
+    }
+    if (hasContacts) return l8 ? launch_tiles<8, true, false>(s, a) : launch_tiles<4, true, false>(s, a);
+    return l8 ? launch_tiles<8, false, false>(s, a) : launch_tiles<4, false, false>(s, a);
+}
+
+}  // namespace gb

@@ -126,20 +126,20 @@ def test_sweep_spill_path_is_exercised_by_reference_meshes():
 def test_config1_teapot_drop_100_frames():
     """BASELINE configs[0] with SURVEY.md §8(d)'s parameters: the teapot (S01 scale / rotation / material) dropped from
     height 10 with v = (0,-10,0) onto the ground plane, 4 substeps x 20 iterations, 100 frames (impact at frame ~45, rebound).
-    Stated tolerance: max |x_gpu - x_oracle| <= 5e-3 (0.16 % of the 3.1-unit teapot) at every 10-frame checkpoint, and
-    <= 5e-4 before the impact. (Sensitivity of the scene itself: a 1e-6 perturbation of the initial positions - one float32
+    Stated tolerance: max |x_gpu - x_oracle| <= 5e-3 (0.16 % of the 3.1-unit teapot) at every 5-frame checkpoint, and
+    <= 5e-4 before the impact (the lowest vertex is below the ground plane at frames 44-48: checkpoint 45 sees it). (Sensitivity of the scene itself: a 1e-6 perturbation of the initial positions - one float32
     ulp at height 10 - moves the ORACLE's own trajectory by 1.3e-4 within 10 frames and 8.6e-4 by frame 100.)"""
     from gaia_b200.workloads import workload_model_drop
     g, o = _both(workload_model_drop("teapot"), threads=4)
     worst, lowest = [], 1e9
-    for chunk in range(10):
+    for chunk in range(20):
         for s in (g, o):
-            s.run_frames(10)
+            s.run_frames(5)
         pg, po = g.positions(0), o.positions(0)
         assert np.isfinite(pg).all()
         worst.append(float(np.abs(pg - po).max()))
         lowest = min(lowest, float(po[:, 1].min()))
-        if chunk < 4:
+        if chunk < 8:
             assert po[:, 1].min() > 0.5 and worst[-1] < 5e-4, (chunk, worst)
     assert lowest < 0.01 and max(worst) < 5e-3, (lowest, worst)
     assert g.stats()["vertexSolves"] == o.stats()["vertexSolves"]
@@ -183,8 +183,20 @@ def test_config2_miniature_integer_surfaces_and_trajectory():
         for m in range(4):
             assert np.array_equal(g.positions(m), o.positions(m)) and np.array_equal(g.prev_positions(m), o.prev_positions(m))
         out = _assert_integer_surfaces_equal(g, o, 4, 8)
-        for which in (0, 1, 2):
-            assert np.array_equal(g.bvh_leaf_order(which), o.bvh_leaf_order(which)), which
+        # LBVH leaf orders: the product keeps the order of its last (re)build, so they are compared on a fresh pair whose
+        # trees are built on exactly this state (tet / surface scenes at the detection before the initial step, the swept
+        # scene after it)
+        g2, o2 = _both(wl, threads=8)
+        for s in (g2, o2):
+            for m, (p, v) in enumerate(state):
+                s.set_state(m, p, v)
+            s.detect_collisions(True, False)
+        for which in (0, 1):
+            assert np.array_equal(g2.bvh_leaf_order(which), o2.bvh_leaf_order(which)), which
+        for s in (g2, o2):
+            s.run_iterations(0)
+        assert np.array_equal(g2.bvh_leaf_order(2), o2.bvh_leaf_order(2))
+        g2.close()
         for s in (g, o):
             for m, (p, v) in enumerate(state):
                 s.set_state(m, p, v)
