@@ -348,6 +348,115 @@ bool host_finalize(Scene& s) {
     return true;
 }
 
+// ---- record order of one vertex: triangle strips over its link.
+// The incident tets of a vertex, seen from the vertex, are the triangles (a,b,c) of its link. The sweep keeps the three
+// neighbour positions of a lane's current tet in registers; when the lane's next tet shares an edge with the current one in
+// the strict triangle-strip pattern (it replaces the OLDEST of the three vertices) only ONE position has to be read from
+// shared memory instead of three. plan_strips orders the triangles into strips (greedy: start at the unused triangle with
+// the fewest unused neighbours, try its six vertex orders, keep the longest run), emit_lane_records replays a lane's share
+// of that order against the register file the kernel will hold and writes either a continuation (one slot) or a restart
+// (three slots). Ties are broken by the triangle's position in ascending tet order and by ORIGINAL vertex ids only, so a
+// partition of the mesh (order-preserving renumbering) plans the same strips for the vertices it owns.
+struct LinkTri { int32_t v[3]; };          // link-local vertex indices (rank of the original id among the neighbours), oriented
+
+static void plan_strips(const std::vector<LinkTri>& tri, int nLinkV, std::vector<int>& order, std::vector<int>& scratch) {
+    const int n = (int)tri.size();
+    order.clear();
+    // edge -> up to two triangles (further ones on a non-manifold edge are simply not linked)
+    std::vector<int>& edgeTri = scratch;
+    edgeTri.assign((size_t)nLinkV * nLinkV * 2, -1);
+    auto ekey = [&](int a, int b) { return (size_t)(std::min(a, b) * nLinkV + std::max(a, b)) * 2; };
+    for (int t = 0; t < n; t++)
+        for (int e = 0; e < 3; e++) {
+            const size_t k = ekey(tri[t].v[e], tri[t].v[(e + 1) % 3]);
+            if (edgeTri[k] < 0) edgeTri[k] = t; else if (edgeTri[k + 1] < 0) edgeTri[k + 1] = t;
+        }
+    auto across = [&](int t, int a, int b) { const size_t k = ekey(a, b); return edgeTri[k] == t ? edgeTri[k + 1] : (edgeTri[k + 1] == t ? edgeTri[k] : -1); };
+    auto third = [&](int t, int a, int b) { for (int e = 0; e < 3; e++) if (tri[t].v[e] != a && tri[t].v[e] != b) return tri[t].v[e]; return -1; };
+    std::vector<char> used(n, 0);
+    std::vector<int> run, best;
+    static const int kPerm[6][3] = {{0, 1, 2}, {1, 2, 0}, {2, 0, 1}, {0, 2, 1}, {2, 1, 0}, {1, 0, 2}};
+    int left = n;
+    while (left) {
+        int start = -1, fewest = 4;
+        for (int t = 0; t < n; t++) {
+            if (used[t]) continue;
+            int c = 0;
+            for (int e = 0; e < 3; e++) { const int o = across(t, tri[t].v[e], tri[t].v[(e + 1) % 3]); if (o >= 0 && !used[o]) c++; }
+            if (c < fewest) { fewest = c; start = t; }
+        }
+        best.clear();
+        for (int pidx = 0; pidx < 6; pidx++) {
+            run.clear(); run.push_back(start);
+            used[start] = 1;
+            int v1 = tri[start].v[kPerm[pidx][1]], v2 = tri[start].v[kPerm[pidx][2]], cur = start;
+            for (;;) {
+                const int nx = across(cur, v1, v2);
+                if (nx < 0 || used[nx]) break;
+                const int v3 = third(nx, v1, v2);
+                if (v3 < 0) break;
+                used[nx] = 1; run.push_back(nx);
+                v1 = v2; v2 = v3; cur = nx;
+            }
+            for (int t : run) used[t] = 0;
+            if (run.size() > best.size()) best = run;
+        }
+        for (int t : best) { used[t] = 1; order.push_back(t); }
+        left -= (int)best.size();
+    }
+}
+
+// Lane's share `seq` of the planned order -> records. reg[i] = link vertex held by register i of the kernel; step t replaces
+// register t % 3. Returns the number of shared-memory position reads the lane will do.
+static int emit_lane_records(const std::vector<LinkTri>& tri, const int* seq, int cnt, const int* slotOfLinkV, const float* detB,
+                             uint2* out, int stride) {
+    int reg[3] = {-1, -1, -1}, reads = 0;
+    auto bits = [](float f) { uint32_t i; std::memcpy(&i, &f, 4); return i; };
+    for (int t = 0; t < cnt; t++) {
+        const LinkTri& T = tri[seq[t]];
+        const int r0 = t % 3, r1 = (t + 1) % 3, r2 = (t + 2) % 3;
+        int place[3] = {-1, -1, -1};      // link vertex for registers r0 (new), r1, r2
+        bool cont = false;
+        if (t > 0) {
+            // continuation: the triangle holds the vertices in r1 and r2; its third vertex goes to r0
+            int nw = -1, hit = 0;
+            for (int e = 0; e < 3; e++) { if (T.v[e] == reg[r1] || T.v[e] == reg[r2]) hit++; else nw = T.v[e]; }
+            if (hit == 2 && reg[r1] != reg[r2] && nw >= 0) { cont = true; place[0] = nw; place[1] = reg[r1]; place[2] = reg[r2]; }
+        }
+        if (!cont) {
+            // restart: put the edge shared with the NEXT triangle of the lane into r2 and r0 (r1 is replaced next), if any
+            int o = 0;
+            if (t + 1 < cnt) {
+                const LinkTri& N = tri[seq[t + 1]];
+                for (int e = 0; e < 3; e++) {
+                    bool inN = false;
+                    for (int f = 0; f < 3; f++) inN |= (N.v[f] == T.v[e]);
+                    if (!inN) { o = e; break; }           // the vertex the next triangle does not have goes to r1
+                }
+            }
+            // the vertex after next drops r2: prefer the strict-strip order (v0 -> r1, v1 -> r2, v2 -> r0)
+            place[1] = T.v[o]; place[2] = T.v[(o + 1) % 3]; place[0] = T.v[(o + 2) % 3];
+            if (t + 2 < cnt && t + 1 < cnt) {
+                const LinkTri& N2 = tri[seq[t + 2]];
+                bool keeps = false;                        // the triangle after next must still hold what sits in r0
+                for (int f = 0; f < 3; f++) keeps |= (N2.v[f] == place[0]);
+                if (!keeps) std::swap(place[0], place[2]);
+            }
+        }
+        reg[r0] = place[0]; reg[r1] = place[1]; reg[r2] = place[2];
+        // orientation of (reg0, reg1, reg2) against the triangle's own (a, b, c)
+        int pos[3];
+        for (int i = 0; i < 3; i++) for (int e = 0; e < 3; e++) if (reg[i] == T.v[e]) pos[i] = e;
+        const bool even = (pos[1] == (pos[0] + 1) % 3);
+        uint32_t I = (uint32_t)slotOfLinkV[place[0]];
+        if (!cont) I |= ((uint32_t)slotOfLinkV[place[1]] << 8) | ((uint32_t)slotOfLinkV[place[2]] << 16) | (1u << 30);
+        if (!even) I |= 1u << 31;
+        out[(size_t)t * stride] = make_uint2(bits(detB[seq[t]]), I);
+        reads += cont ? 1 : 3;
+    }
+    return reads;
+}
+
 // Tile streams of the colour sweep (sweep.cu). The Neo-Hookean vertex force splits into a part that is LINEAR in the
 // neighbour positions, -mu * sum_tets Ds'(A w') = -mu * sum_nb W_nb (x_nb - x) with W_nb the sum of A w' over the tets
 // that share the neighbour, and the volumetric part that needs the tet (det F and the opposite face's normal). So a
@@ -369,6 +478,12 @@ bool build_tile_streams(Scene& s, int tileV) {
         for (int v = 0; v < m.nV; v++)
             info[m.sortedId[v]] = (m.id & 0x00FFFFFF) | ((m.fixedMask[v] || m.ghostMask[v]) ? (int32_t)0x80000000 : 0);
     std::vector<double> wsum;
+    std::vector<LinkTri> tri;
+    std::vector<float> detB;
+    std::vector<int> order, scratch;
+    int identity[256];
+    for (int i = 0; i < 256; i++) identity[i] = i;
+    s.sweepPosReads = 0;
     auto bits = [](float f) { int32_t i; std::memcpy(&i, &f, 4); return i; };
     for (size_t g = 0; g < nGroups; g++) {
         s.groupTileStart[g] = (int32_t)s.h_tiles.size();
@@ -387,12 +502,25 @@ bool build_tile_streams(Scene& s, int tileV) {
                 if (nRec + r > kTileRecCap || nNb + n > kTileNbCap) break;
                 wsum.assign(n, 0.0);
                 double s1 = 0.0;
-                for (int j = s.h_incOff[v]; j < s.h_incOff[v] + r; j++) {
+                tri.resize(r); detB.resize(r);
+                for (int q = 0; q < r; q++) {
+                    const int j = s.h_incOff[v] + q;
                     const float* W = &s.h_incW[4 * (size_t)j];
                     const uint32_t I = s.h_incIdx[j];
                     wsum[I & 255] += W[0]; wsum[(I >> 8) & 255] += W[1]; wsum[(I >> 16) & 255] += W[2];
                     s1 -= (double)W[0] + (double)W[1] + (double)W[2];
-                    s.h_rec.push_back(make_uint2((uint32_t)bits(W[3]), I));
+                    tri[q].v[0] = (int)(I & 255); tri[q].v[1] = (int)((I >> 8) & 255); tri[q].v[2] = (int)((I >> 16) & 255);
+                    detB[q] = W[3];
+                }
+                // records in lane-strided strip order: lane l walks records l, l + 4, ... = its share of the planned order
+                plan_strips(tri, n, order, scratch);
+                const size_t base = s.h_rec.size();
+                s.h_rec.resize(base + r);
+                for (int l = 0, at = 0; l < kSweepLanes; l++) {
+                    const int cnt = (r - l + kSweepLanes - 1) / kSweepLanes;
+                    if (cnt <= 0) break;
+                    s.sweepPosReads += emit_lane_records(tri, order.data() + at, cnt, identity, detB.data(), s.h_rec.data() + base + l, kSweepLanes);
+                    at += cnt;
                 }
                 for (int q = 0; q < n; q++) s.h_nbw.push_back(make_int2(s.h_nbList[s.h_nbOff[v] + q], bits((float)wsum[q])));
                 s.h_vtx2[v] = make_int4(nRec | (r << 16), nNb | (n << 16), bits((float)s1), info[v]);

@@ -74,6 +74,7 @@ struct HaloView {
 // One tile of the colour sweep (sweep.cu): up to kTileV consecutive vertices of one colour whose incidence records and
 // neighbour entries are contiguous in the `rec` / `nbw` streams, so one cp.async.bulk per stream brings a tile into shared
 // memory. Counts are padded to even (16-byte copies); begins are even.
+static const int kSweepLanes = 4;      // lanes per vertex of the colour sweep (fixes the record order and the association of the sums)
 static const int kTileV = 64, kTileRecCap = 1536, kTileNbCap = 896;
 struct TileDesc { int32_t vBegin, nV, recBegin, recCount, nbBegin, nbCount, flags, pad; };
 
@@ -113,6 +114,7 @@ struct Scene {
     std::vector<int2> h_nbw;           // per (vertex, distinct neighbour): {sorted id, bits(sum of A*w' over the shared tets)}
     std::vector<TileDesc> h_tiles;
     std::vector<int32_t> groupTileStart;   // [G + 1]
+    int64_t sweepPosReads = 0;             // shared-memory position reads per sweep over all vertices (3 per restart, 1 per strip step)
     DevBuf<int4> vtx2;
     DevBuf<uint2> rec;
     DevBuf<int2> nbw;

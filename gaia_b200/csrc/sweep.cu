@@ -35,17 +35,18 @@ namespace gb {
 static const int kSweepThreads = 256;
 static const int kSweepBlocksPerSM = 3;
 
-// ---- shared memory map (bytes). Rings: records 2 deep, neighbour entries 3 deep, vertex headers / own positions 4 deep
-// (the tail of tile k-1 still reads its headers while the copies of tile k+3 are issued).
+// ---- shared memory map (bytes). Rings: records 2 deep, neighbour entries / vertex headers / own positions 3 deep.
 static const int kRecStage = kTileRecCap * 8, kNbwStage = kTileNbCap * 8, kVtxStage = kTileV * 16;
 static const int kSmRec = 0;                                          // [2][kTileRecCap] uint2
 static const int kSmNbw = kSmRec + 2 * kRecStage;                      // [3][kTileNbCap] int2
-static const int kSmHdr = kSmNbw + 3 * kNbwStage;                      // [4][kTileV] int4
-static const int kSmPos = kSmHdr + 4 * kVtxStage;                      // [4][kTileV] float4
-static const int kSmRel = kSmPos + 4 * kVtxStage;                      // [kTileNbCap] float4: neighbour positions relative to the owner
-static const int kSmAcc = kSmRel + kTileNbCap * 16;                    // [2][9][kTileV] float
-static const int kSmInfo = kSmAcc + 2 * 9 * kTileV * 4;                // [4] TileDesc
-static const int kSmBarRec = kSmInfo + 4 * 32;                         // [2] mbarrier: records of tile k landed
+static const int kSmHdr = kSmNbw + 3 * kNbwStage;                      // [3][kTileV] int4
+static const int kSmPos = kSmHdr + 3 * kVtxStage;                      // [3][kTileV] float4
+static const int kSmRel = kSmPos + 3 * kVtxStage;                      // [kTileNbCap] float4: neighbour positions relative to the owner
+static const int kTailGroup = kSweepThreads / kTileV;                  // tiles whose vertex-level tails run together, one vertex per thread
+static const int kSmAcc = kSmRel + kTileNbCap * 16;                    // [kTailGroup][9][kTileV] float: incident-tet sums
+static const int kSmInfo = kSmAcc + kTailGroup * 9 * kTileV * 4;       // [4] TileDesc
+static const int kSmTail = kSmInfo + 4 * 32;                           // [kTailGroup] int2 {vBegin, nV} of the tiles awaiting their tail
+static const int kSmBarRec = kSmTail + kTailGroup * 8;                         // [2] mbarrier: records of tile k landed
 static const int kSmBarNb = kSmBarRec + 2 * 8;                         // [3] mbarrier: neighbour entries + headers + positions landed
 static const int kSmTotal = kSmBarNb + 3 * 8;
 static_assert(3 * (kSmTotal + 1024) <= 227 * 1024, "three blocks per SM");
@@ -277,8 +278,8 @@ k_sweep_tiles(const SweepArgs a) {
         const uint32_t bNb = (uint32_t)d.nbCount * 8u, bV = (uint32_t)d.nV * 16u;
         mbar_expect_tx(bar, bNb + 2 * bV);
         if (bNb) bulk_g2s(sb + kSmNbw + s3 * kNbwStage, a.nbw + d.nbBegin, bNb, bar);
-        bulk_g2s(sb + kSmHdr + s4 * kVtxStage, a.vtx2 + d.vBegin, bV, bar);
-        bulk_g2s(sb + kSmPos + s4 * kVtxStage, a.pos + d.vBegin, bV, bar);
+        bulk_g2s(sb + kSmHdr + s3 * kVtxStage, a.vtx2 + d.vBegin, bV, bar);
+        bulk_g2s(sb + kSmPos + s3 * kVtxStage, a.pos + d.vBegin, bV, bar);
     };
     auto issue_rec = [&](int k) {
         const TileDesc d = a.tiles[a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x];
@@ -320,7 +321,7 @@ k_sweep_tiles(const SweepArgs a) {
         const int v = r * VPR + sub;
         pf.hdrY = 0;
         if (v < info[s4].nV) {
-            const int4 h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + v * 16);
+            const int4 h = *(const int4*)(smem + kSmHdr + s3 * kVtxStage + v * 16);
             if (h.w >= 0 && a.mp[h.w & 0x00FFFFFF].activeSolve) pf.hdrY = h.y;
         }
         const int nbLocal = pf.hdrY & 0xFFFF, nNb = pf.hdrY >> 16;
@@ -348,12 +349,16 @@ k_sweep_tiles(const SweepArgs a) {
         const int nV = info[s4].nV, vBegin = info[s4].vBegin;
         const bool ghostTile = HALO && (info[s4].flags & 1);
         const int rounds = (nV + VPR - 1) / VPR;
-        float* acc = (float*)(smem + kSmAcc + st * (9 * kTileV * 4));
-        // the tail's per-vertex inputs that are not in shared memory: pulled into L1 now, read after the rounds
+        const int tg = k % kTailGroup;                 // position of this tile in its tail group
+        float* acc = (float*)(smem + kSmAcc + tg * (9 * kTileV * 4));
+        // the tail's per-vertex inputs are read from global memory: pulled into L1 now
         if (tid < nV) {
             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.inertia + vBegin + tid));
             if (a.needPrev) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.prev + vBegin + tid));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.vtx2 + vBegin + tid));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.pos + vBegin + tid));
         }
+        if (tid == 0) ((int2*)(smem + kSmTail))[tg] = make_int2(vBegin, nV);
 
 #pragma unroll 1
         for (int r = 0; r < rounds; r++) {
@@ -364,8 +369,8 @@ k_sweep_tiles(const SweepArgs a) {
             int4 h = make_int4(0, 0, 0, 0);
             float3 x = make_float3(0.f, 0.f, 0.f);
             if (active) {
-                h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + v * 16);
-                x = f3(*(const float4*)(smem + kSmPos + s4 * kVtxStage + v * 16));
+                h = *(const int4*)(smem + kSmHdr + s3 * kVtxStage + v * 16);
+                x = f3(*(const float4*)(smem + kSmPos + s3 * kVtxStage + v * 16));
             }
             const uint32_t relAddr = sb + kSmRel + nbLocal * 16;
             float lx = 0.f, ly = 0.f, lz = 0.f;
@@ -404,31 +409,47 @@ k_sweep_tiles(const SweepArgs a) {
             float fx = 0.f, fy = 0.f, fz = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
             const int nRec = active ? (h.x >> 16) : 0;
             const uint32_t recAddr = sb + kSmRec + st * kRecStage + (h.x & 0xFFFF) * 8;
+            // The lane's records follow triangle strips over the vertex's link (host_setup.cpp: plan_strips): step t keeps two
+            // of the three neighbour positions in registers and replaces register t % 3 by ONE shared-memory read; a restart
+            // record (bit 30) reloads all three. Bit 31: (p0,p1,p2) is an odd permutation of the tet's (a,b,c): n flips.
+            const int cnt = (nRec - lane + L - 1) / L;
+            float3 p0 = make_float3(0.f, 0.f, 0.f), p1 = p0, p2 = p0;
             uint2 R = make_uint2(0u, 0u);
-            if (lane < nRec) R = lds64(recAddr + lane * 8);
-#pragma unroll 2
-            for (int j = lane; j < nRec; j += L) {
-                uint2 Rn = R;
-                if (j + L < nRec) Rn = lds64(recAddr + (j + L) * 8);       // the next record is requested before this one is consumed
-                const float dB = __uint_as_float(R.x);
-                const uint32_t I = R.y;
-                const float3 pa = f3(lds128(relAddr + ((I & 0xFFu) << 4)));
-                const float3 pb = f3(lds128(relAddr + ((I >> 4) & 0xFF0u)));
-                const float3 pc = f3(lds128(relAddr + ((I >> 12) & 0xFF0u)));
-                // n = (b-a) x (c-a);  det(Ds') = a . n;  det F = det(Ds') det(B');  A*g = -n/6;  6 A g g^T = det(B') n n^T
-                const float3 u = pb - pa, w = pc - pa;
-                float3 n;
-                n.x = __fmaf_rn(u.y, w.z, -__fmul_rn(u.z, w.y));
-                n.y = __fmaf_rn(u.z, w.x, -__fmul_rn(u.x, w.z));
-                n.z = __fmaf_rn(u.x, w.y, -__fmul_rn(u.y, w.x));
-                const float detDs = __fmaf_rn(pa.z, n.z, __fmaf_rn(pa.y, n.y, __fmul_rn(pa.x, n.x)));
-                const float kk = __fmaf_rn(detDs, dB, -aConst);        // det F - a
-                fx = __fmaf_rn(kk, n.x, fx); fy = __fmaf_rn(kk, n.y, fy); fz = __fmaf_rn(kk, n.z, fz);
-                const float nx = __fmul_rn(dB, n.x), ny = __fmul_rn(dB, n.y), nz = __fmul_rn(dB, n.z);
-                g00 = __fmaf_rn(nx, n.x, g00); g01 = __fmaf_rn(nx, n.y, g01); g02 = __fmaf_rn(nx, n.z, g02);
-                g11 = __fmaf_rn(ny, n.y, g11); g12 = __fmaf_rn(ny, n.z, g12); g22 = __fmaf_rn(nz, n.z, g22);
-                R = Rn;
+            if (cnt > 0) R = lds64(recAddr + lane * 8);
+#define GAIA_STRIP_STEP(PN, PB, PC, T)                                                                                        \
+            {                                                                                                                 \
+                uint2 Rn = R;                                                                                                 \
+                if ((T) + 1 < cnt) Rn = lds64(recAddr + (lane + ((T) + 1) * L) * 8);   /* requested before this one is consumed */ \
+                const uint32_t I = R.y;                                                                                       \
+                PN = f3(lds128(relAddr + ((I & 0xFFu) << 4)));                                                                \
+                if (I & 0x40000000u) {                                                                                        \
+                    PB = f3(lds128(relAddr + ((I >> 4) & 0xFF0u)));                                                           \
+                    PC = f3(lds128(relAddr + ((I >> 12) & 0xFF0u)));                                                          \
+                }                                                                                                             \
+                /* n = (p1-p0) x (p2-p0) = +-(b-a) x (c-a); det(Ds') = a.n = p0.n; det F = det(Ds') det(B'); 6 A g g^T = det(B') n n^T */ \
+                const float3 u = p1 - p0, w = p2 - p0;                                                                        \
+                float3 n;                                                                                                     \
+                n.x = __fmaf_rn(u.y, w.z, -__fmul_rn(u.z, w.y));                                                              \
+                n.y = __fmaf_rn(u.z, w.x, -__fmul_rn(u.x, w.z));                                                              \
+                n.z = __fmaf_rn(u.x, w.y, -__fmul_rn(u.y, w.x));                                                              \
+                const float detDs = __fmaf_rn(p0.z, n.z, __fmaf_rn(p0.y, n.y, __fmul_rn(p0.x, n.x)));                         \
+                const uint32_t flip = I & 0x80000000u;                                                                        \
+                const float dB = __uint_as_float(R.x);                                                                        \
+                const float kk = __fmaf_rn(detDs, __uint_as_float(R.x ^ flip), -aConst);        /* det F - a */              \
+                const float ks = __uint_as_float(__float_as_uint(kk) ^ flip);                   /* (det F - a) * sign of n */ \
+                fx = __fmaf_rn(ks, n.x, fx); fy = __fmaf_rn(ks, n.y, fy); fz = __fmaf_rn(ks, n.z, fz);                        \
+                const float nx = __fmul_rn(dB, n.x), ny = __fmul_rn(dB, n.y), nz = __fmul_rn(dB, n.z);                        \
+                g00 = __fmaf_rn(nx, n.x, g00); g01 = __fmaf_rn(nx, n.y, g01); g02 = __fmaf_rn(nx, n.z, g02);                  \
+                g11 = __fmaf_rn(ny, n.y, g11); g12 = __fmaf_rn(ny, n.z, g12); g22 = __fmaf_rn(nz, n.z, g22);                  \
+                R = Rn;                                                                                                       \
             }
+#pragma unroll 1
+            for (int t = 0; t < cnt; t += 3) {
+                GAIA_STRIP_STEP(p0, p1, p2, t)
+                if (t + 1 < cnt) GAIA_STRIP_STEP(p1, p2, p0, t + 1)
+                if (t + 2 < cnt) GAIA_STRIP_STEP(p2, p0, p1, t + 2)
+            }
+#undef GAIA_STRIP_STEP
             // -f = mu * sum_nb W (x_nb - x) + lmbd * sum_tets (det F - a) * (-n / 6)
             const float lm6 = lmbd * (-1.f / 6.f);
             fx = __fmaf_rn(lm6, fx, __fmul_rn(miu, lx)); fy = __fmaf_rn(lm6, fy, __fmul_rn(miu, ly)); fz = __fmaf_rn(lm6, fz, __fmul_rn(miu, lz));
@@ -450,34 +471,40 @@ k_sweep_tiles(const SweepArgs a) {
             if (k + 3 < nMine) issue_nb(k + 3);
         }
 
-        // ---- transposed tail: thread t finishes vertex t of the tile
-        bool pushed = false;
-        if (tid < nV) {
-            const int4 h = *(const int4*)(smem + kSmHdr + s4 * kVtxStage + tid * 16);
-            const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF);
-            if (h.w >= 0 && P->activeSolve) {
-                const int s = vBegin + tid;
-                const float3 x = f3(*(const float4*)(smem + kSmPos + s4 * kVtxStage + tid * 16));
-                const float4 ys = __ldg(a.inertia + s);
-                float4 xpv = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (a.needPrev) xpv = __ldg(a.prev + s);
-                float4 xNew;
-                const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, acc[0 * kTileV + tid], acc[1 * kTileV + tid], acc[2 * kTileV + tid],
-                                       __int_as_float(h.z), acc[3 * kTileV + tid] * (1.f / 6.f), acc[4 * kTileV + tid] * (1.f / 6.f),
-                                       acc[5 * kTileV + tid] * (1.f / 6.f), acc[6 * kTileV + tid] * (1.f / 6.f), acc[7 * kTileV + tid] * (1.f / 6.f),
-                                       acc[8 * kTileV + tid] * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
-                if (HALO && wrote && (h.w & kHaloBoundaryBit) && !(a.hv.debug & 2)) {
-                    const int si = __ldg(a.hv.sendIdx + s);
-                    for (int q = 0; q < (si & 15); q++) {
-                        const int2 en = __ldg(a.hv.sendEnt + (si >> 4) + q);
-                        a.hv.tab->peerPos[en.x][en.y] = xNew;
+        // ---- transposed tails of the last kTailGroup tiles, one vertex per thread (full SIMT width)
+        if (tg == kTailGroup - 1 || k == nMine - 1) {
+            const int2 tv = ((const int2*)(smem + kSmTail))[tid / kTileV];
+            const int vt = tid % kTileV;
+            const float* ac = (const float*)(smem + kSmAcc + (tid / kTileV) * (9 * kTileV * 4));
+            bool pushed = false;
+            if (tid / kTileV <= tg && vt < tv.y) {
+                const int s = tv.x + vt;
+                const int4 h = __ldg(a.vtx2 + s);
+                const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF);
+                if (h.w >= 0 && P->activeSolve) {
+                    const float3 x = f3(a.pos[s]);
+                    const float4 ys = __ldg(a.inertia + s);
+                    float4 xpv = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (a.needPrev) xpv = __ldg(a.prev + s);
+                    float4 xNew;
+                    const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, ac[0 * kTileV + vt], ac[1 * kTileV + vt], ac[2 * kTileV + vt],
+                                           __int_as_float(h.z), ac[3 * kTileV + vt] * (1.f / 6.f), ac[4 * kTileV + vt] * (1.f / 6.f),
+                                           ac[5 * kTileV + vt] * (1.f / 6.f), ac[6 * kTileV + vt] * (1.f / 6.f), ac[7 * kTileV + vt] * (1.f / 6.f),
+                                           ac[8 * kTileV + vt] * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
+                    if (HALO && wrote && (h.w & kHaloBoundaryBit) && !(a.hv.debug & 2)) {
+                        const int si = __ldg(a.hv.sendIdx + s);
+                        for (int q = 0; q < (si & 15); q++) {
+                            const int2 en = __ldg(a.hv.sendEnt + (si >> 4) + q);
+                            a.hv.tab->peerPos[en.x][en.y] = xNew;
+                        }
+                        pushed = true;
                     }
-                    pushed = true;
                 }
             }
+            // the next launch of the stream publishes the epoch; the stores must be performed system-wide before it does
+            if (HALO && pushed) __threadfence_system();
+            __syncthreads();      // the sums are consumed: the next group may overwrite them
         }
-        // the next launch of the stream publishes the epoch; the stores must be performed system-wide before it does
-        if (HALO && pushed) __threadfence_system();
     }
 }
 
@@ -534,13 +561,9 @@ cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool
     for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
     if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
     if (hv) a.hv = *hv;
-    const bool l8 = lanes == 8;
-    if (hv) {
-        if (hasContacts) return l8 ? launch_tiles<8, true, true>(s, a) : launch_tiles<4, true, true>(s, a);
-        return l8 ? launch_tiles<8, false, true>(s, a) : launch_tiles<4, false, true>(s, a);
-    }
-    if (hasContacts) return l8 ? launch_tiles<8, true, false>(s, a) : launch_tiles<4, true, false>(s, a);
-    return l8 ? launch_tiles<8, false, false>(s, a) : launch_tiles<4, false, false>(s, a);
+    (void)lanes;      // the record order is laid out for kSweepLanes lanes per vertex
+    if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true>(s, a) : launch_tiles<kSweepLanes, false, true>(s, a);
+    return hasContacts ? launch_tiles<kSweepLanes, true, false>(s, a) : launch_tiles<kSweepLanes, false, false>(s, a);
 }
 
 }  // namespace gb
