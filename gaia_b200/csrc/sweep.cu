@@ -82,6 +82,26 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
     asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(addr));
     return r;
 }
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t r;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ int4 lds128i(uint32_t addr) {
+    int4 r;
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ void sts128i(uint32_t addr, int4 v) {
+    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts32f(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+__device__ __forceinline__ float lds32f(uint32_t addr) { return __uint_as_float(lds32(addr)); }
+// predicated 16-byte store (no branch around it)
+__device__ __forceinline__ void sts128_if(bool pred, uint32_t addr, float x, float y, float z, float w) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\t@p st.shared.v4.f32 [%0], {%1,%2,%3,%4};\n\t}"
+                 ::"r"(addr), "f"(x), "f"(y), "f"(z), "f"(w), "r"((uint32_t)pred) : "memory");
+}
 __device__ __forceinline__ unsigned long long gtimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -101,6 +121,7 @@ struct SweepArgs {
     StepParamsDev sp;
     int applyFriction;
     int needPrev;                        // some mesh has damping, or the world box has friction: the tail reads x_prev
+    int allActive;                       // every mesh is active for the material solve (no per-vertex look-up needed)
     ContactView cv;
     int32_t* errFlags;
     HaloView hv;
@@ -249,10 +270,9 @@ k_sweep_tiles(const SweepArgs a) {
     constexpr int VPR = kSweepThreads / L;          // vertices per round
     constexpr int NQ = 16 / L;                      // gathers held in registers per lane (16 neighbours per vertex)
     extern __shared__ __align__(128) unsigned char smem[];
-    const uint32_t sb = smem_u32(smem);
+    const uint32_t sb = smem_u32(smem);             // every shared-memory access below goes through 32-bit shared addresses
     const int tid = threadIdx.x, lane = tid & (L - 1), sub = tid / L;
     const int nMine = (a.tileEnd - a.tileBegin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // tiles of this block
-    TileDesc* info = (TileDesc*)(smem + kSmInfo);
     const float4* posRO = a.pos;      // gathers only touch other colours: read-only for this launch
 
     if (HALO && blockIdx.x == 0 && tid < a.hv.nPeers) {
@@ -268,25 +288,26 @@ k_sweep_tiles(const SweepArgs a) {
     }
     __syncthreads();
 
-    // ---- producer (thread 0). Tile k: neighbour entries -> slot k % 3, headers + own positions -> slot k & 3 (one
-    // barrier, the data the gathers need first); records -> slot k & 1 (their own barrier, needed half a tile later)
+    // ---- producer (thread 0). Tile k: neighbour entries, headers and own positions -> slot k % 3 (one barrier: the data the
+    // gathers need first); records -> slot k & 1 (their own barrier, needed half a tile later). info ring: slot k & 3.
     auto issue_nb = [&](int k) {
-        const TileDesc d = a.tiles[a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x];
-        const int s3 = k % 3, s4 = k & 3;
-        info[s4] = d;
+        const int4* dp = (const int4*)(a.tiles + a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x);
+        const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);       // {vBegin, nV, recBegin, recCount}, {nbBegin, nbCount, flags, -}
+        const int s3 = k % 3;
+        sts128i(sb + kSmInfo + (k & 3) * 32, d0); sts128i(sb + kSmInfo + (k & 3) * 32 + 16, d1);
         const uint32_t bar = sb + kSmBarNb + 8 * s3;
-        const uint32_t bNb = (uint32_t)d.nbCount * 8u, bV = (uint32_t)d.nV * 16u;
+        const uint32_t bNb = (uint32_t)d1.y * 8u, bV = (uint32_t)d0.y * 16u;
         mbar_expect_tx(bar, bNb + 2 * bV);
-        if (bNb) bulk_g2s(sb + kSmNbw + s3 * kNbwStage, a.nbw + d.nbBegin, bNb, bar);
-        bulk_g2s(sb + kSmHdr + s3 * kVtxStage, a.vtx2 + d.vBegin, bV, bar);
-        bulk_g2s(sb + kSmPos + s3 * kVtxStage, a.pos + d.vBegin, bV, bar);
+        if (bNb) bulk_g2s(sb + kSmNbw + s3 * kNbwStage, a.nbw + d1.x, bNb, bar);
+        bulk_g2s(sb + kSmHdr + s3 * kVtxStage, a.vtx2 + d0.x, bV, bar);
+        bulk_g2s(sb + kSmPos + s3 * kVtxStage, a.pos + d0.x, bV, bar);
     };
     auto issue_rec = [&](int k) {
-        const TileDesc d = a.tiles[a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x];
+        const int4 d0 = __ldg((const int4*)(a.tiles + a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x));
         const uint32_t bar = sb + kSmBarRec + 8 * (k & 1);
-        const uint32_t bRec = (uint32_t)d.recCount * 8u;
+        const uint32_t bRec = (uint32_t)d0.w * 8u;
         mbar_expect_tx(bar, bRec);
-        if (bRec) bulk_g2s(sb + kSmRec + (k & 1) * kRecStage, a.rec + d.recBegin, bRec, bar);
+        if (bRec) bulk_g2s(sb + kSmRec + (k & 1) * kRecStage, a.rec + d0.z, bRec, bar);
     };
     if (tid == 0) {
         issue_nb(0); issue_rec(0);
@@ -303,15 +324,15 @@ k_sweep_tiles(const SweepArgs a) {
     };
 
     bool haloWaited = false;
-    // ---- gathers of round (k, r): wait for the tile's neighbour entries (first round), then request this lane's positions
-    auto prefetch = [&](int k, int r, Prefetch<NQ>& pf) -> bool {
-        const int s3 = k % 3, s4 = k & 3;
-        if (r == 0 && !wait_bar(sb + kSmBarNb + 8 * s3, (uint32_t)(k / 3) & 1u)) return false;
+    // ---- gathers of round r of the tile in ring slots (s3, s4): wait for the tile's neighbour entries (first round), then
+    // request this lane's positions
+    auto prefetch = [&](int s3, int s4, uint32_t parNb, int r, Prefetch<NQ>& pf) -> bool {
+        if (r == 0 && !wait_bar(sb + kSmBarNb + 8 * s3, parNb)) return false;
         bool ghost = false;
         if (HALO) {
             // a tile that holds boundary vertices also holds vertices whose neighbours are ghosts: wait for the neighbour
             // partitions' previous colour before gathering, and gather past L1
-            ghost = (info[s4].flags & 1) != 0;
+            ghost = (lds32(sb + kSmInfo + s4 * 32 + 24) & 1u) != 0;
             if (ghost && !haloWaited) {
                 if (tid == 0 && !(a.hv.debug & 1)) sweep_halo_wait(a.hv.tab, *(volatile const uint32_t*)a.hv.ctl + (uint32_t)a.hv.epochOffset, a.hv.nPeers, a.errFlags);
                 __syncthreads();
@@ -320,19 +341,18 @@ k_sweep_tiles(const SweepArgs a) {
         }
         const int v = r * VPR + sub;
         pf.hdrY = 0;
-        if (v < info[s4].nV) {
-            const int4 h = *(const int4*)(smem + kSmHdr + s3 * kVtxStage + v * 16);
-            if (h.w >= 0 && a.mp[h.w & 0x00FFFFFF].activeSolve) pf.hdrY = h.y;
+        if (v < (int)lds32(sb + kSmInfo + s4 * 32 + 4)) {
+            const int hw = (int)lds32(sb + kSmHdr + s3 * kVtxStage + v * 16 + 12);
+            if (hw >= 0 && (a.allActive || a.mp[hw & 0x00FFFFFF].activeSolve)) pf.hdrY = (int)lds32(sb + kSmHdr + s3 * kVtxStage + v * 16 + 4);
         }
-        const int nbLocal = pf.hdrY & 0xFFFF, nNb = pf.hdrY >> 16;
-        const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + nbLocal * 8;
+        const int nNb = pf.hdrY >> 16;
+        const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + ((pf.hdrY & 0xFFFF) + lane) * 8;
 #pragma unroll
         for (int q = 0; q < NQ; q++) {
-            const int i = lane + q * L;
             pf.p[q] = make_float4(0.f, 0.f, 0.f, 0.f);
             pf.w[q] = 0.f;
-            if (i < nNb) {
-                const uint2 e = lds64(nbAddr + i * 8);
+            if (lane + q * L < nNb) {
+                const uint2 e = lds64(nbAddr + q * (L * 8));
                 pf.w[q] = __uint_as_float(e.y);
                 pf.p[q] = (HALO && ghost) ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
             }
@@ -341,16 +361,20 @@ k_sweep_tiles(const SweepArgs a) {
     };
 
     Prefetch<NQ> pf;
-    if (!prefetch(0, 0, pf)) return;
+    if (!prefetch(0, 0, 0u, 0, pf)) return;
 
+    int s3 = 0;                 // k % 3
+    uint32_t parNb = 0;         // (k / 3) & 1
 #pragma unroll 1
     for (int k = 0; k < nMine; k++) {
-        const int st = k & 1, s3 = k % 3, s4 = k & 3;
-        const int nV = info[s4].nV, vBegin = info[s4].vBegin;
-        const bool ghostTile = HALO && (info[s4].flags & 1);
+        const int st = k & 1, s4 = k & 3;
+        const int s3n = (s3 == 2) ? 0 : s3 + 1;
+        const uint32_t parNbN = (s3 == 2) ? parNb ^ 1u : parNb;
+        const int vBegin = (int)lds32(sb + kSmInfo + s4 * 32), nV = (int)lds32(sb + kSmInfo + s4 * 32 + 4);
+        const bool ghostTile = HALO && (lds32(sb + kSmInfo + s4 * 32 + 24) & 1u);
         const int rounds = (nV + VPR - 1) / VPR;
         const int tg = k % kTailGroup;                 // position of this tile in its tail group
-        float* acc = (float*)(smem + kSmAcc + tg * (9 * kTileV * 4));
+        const uint32_t accAddr = sb + kSmAcc + tg * (9 * kTileV * 4);
         // the tail's per-vertex inputs are read from global memory: pulled into L1 now
         if (tid < nV) {
             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.inertia + vBegin + tid));
@@ -358,7 +382,7 @@ k_sweep_tiles(const SweepArgs a) {
             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.vtx2 + vBegin + tid));
             asm volatile("prefetch.global.L1 [%0];" ::"l"(a.pos + vBegin + tid));
         }
-        if (tid == 0) ((int2*)(smem + kSmTail))[tg] = make_int2(vBegin, nV);
+        if (tid == 0) asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(sb + kSmTail + tg * 8), "r"(vBegin), "r"(nV) : "memory");
 
 #pragma unroll 1
         for (int r = 0; r < rounds; r++) {
@@ -369,22 +393,19 @@ k_sweep_tiles(const SweepArgs a) {
             int4 h = make_int4(0, 0, 0, 0);
             float3 x = make_float3(0.f, 0.f, 0.f);
             if (active) {
-                h = *(const int4*)(smem + kSmHdr + s3 * kVtxStage + v * 16);
-                x = f3(*(const float4*)(smem + kSmPos + s3 * kVtxStage + v * 16));
+                h = lds128i(sb + kSmHdr + s3 * kVtxStage + v * 16);
+                x = f3(lds128(sb + kSmPos + s3 * kVtxStage + v * 16));
             }
             const uint32_t relAddr = sb + kSmRel + nbLocal * 16;
             float lx = 0.f, ly = 0.f, lz = 0.f;
 #pragma unroll
             for (int q = 0; q < NQ; q++) {
-                const int i = lane + q * L;
-                if (i < nNb) {
-                    const float rx = __fsub_rn(pf.p[q].x, x.x), ry = __fsub_rn(pf.p[q].y, x.y), rz = __fsub_rn(pf.p[q].z, x.z);
-                    const float w = pf.w[q];
-                    // (the loaded .w is stored too: all four registers of the gather stay live until here, so the compiler
-                    //  cannot hand one of them to another value and stall on the in-flight load)
-                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(relAddr + i * 16), "f"(rx), "f"(ry), "f"(rz), "f"(pf.p[q].w) : "memory");
-                    lx = __fmaf_rn(w, rx, lx); ly = __fmaf_rn(w, ry, ly); lz = __fmaf_rn(w, rz, lz);
-                }
+                // (lanes without a neighbour hold p = 0, w = 0: the arithmetic runs unconditionally, only the store is predicated.
+                //  The loaded .w is stored too: all four registers of the gather stay live until here, so the compiler cannot
+                //  hand one of them to another value and stall on the in-flight load)
+                const float rx = __fsub_rn(pf.p[q].x, x.x), ry = __fsub_rn(pf.p[q].y, x.y), rz = __fsub_rn(pf.p[q].z, x.z);
+                sts128_if(lane + q * L < nNb, relAddr + (lane + q * L) * 16, rx, ry, rz, pf.p[q].w);
+                lx = __fmaf_rn(pf.w[q], rx, lx); ly = __fmaf_rn(pf.w[q], ry, ly); lz = __fmaf_rn(pf.w[q], rz, lz);
             }
             if (nNb > NQ * L) {      // vertices with more than 16 distinct neighbours: the rest is gathered in place
                 const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + nbLocal * 8;
@@ -393,33 +414,34 @@ k_sweep_tiles(const SweepArgs a) {
                     const float4 p = ghostTile ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
                     const float w = __uint_as_float(e.y);
                     const float rx = __fsub_rn(p.x, x.x), ry = __fsub_rn(p.y, x.y), rz = __fsub_rn(p.z, x.z);
-                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(relAddr + i * 16), "f"(rx), "f"(ry), "f"(rz), "f"(w) : "memory");
+                    sts128_if(true, relAddr + i * 16, rx, ry, rz, p.w);
                     lx = __fmaf_rn(w, rx, lx); ly = __fmaf_rn(w, ry, ly); lz = __fmaf_rn(w, rz, lz);
                 }
             }
             // ---- next round's gathers go out now; they land while this round's records are processed
-            if (r + 1 < rounds) prefetch(k, r + 1, pf);
-            else if (k + 1 < nMine) { if (!prefetch(k + 1, 0, pf)) return; }
+            if (r + 1 < rounds) prefetch(s3, s4, parNb, r + 1, pf);
+            else if (k + 1 < nMine) { if (!prefetch(s3n, (k + 1) & 3, parNbN, 0, pf)) return; }
             if (r == 0 && !wait_bar(sb + kSmBarRec + 8 * st, (uint32_t)(k >> 1) & 1u)) return;
             __syncwarp();
 
-            // ---- volumetric term over the incident tets: lane l takes records l, l+L, ...
+            // ---- volumetric term over the incident tets
             float miu = 0.f, lmbd = 0.f, aConst = 0.f;
             if (active) { const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF); miu = P->miu; lmbd = P->lmbd; aConst = P->a; }
             float fx = 0.f, fy = 0.f, fz = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
             const int nRec = active ? (h.x >> 16) : 0;
-            const uint32_t recAddr = sb + kSmRec + st * kRecStage + (h.x & 0xFFFF) * 8;
+            uint32_t recAddr = sb + kSmRec + st * kRecStage + ((h.x & 0xFFFF) + lane) * 8;      // this lane's next record
             // The lane's records follow triangle strips over the vertex's link (host_setup.cpp: plan_strips): step t keeps two
             // of the three neighbour positions in registers and replaces register t % 3 by ONE shared-memory read; a restart
             // record (bit 30) reloads all three. Bit 31: (p0,p1,p2) is an odd permutation of the tet's (a,b,c): n flips.
             const int cnt = (nRec - lane + L - 1) / L;
             float3 p0 = make_float3(0.f, 0.f, 0.f), p1 = p0, p2 = p0;
             uint2 R = make_uint2(0u, 0u);
-            if (cnt > 0) R = lds64(recAddr + lane * 8);
+            if (cnt > 0) R = lds64(recAddr);
 #define GAIA_STRIP_STEP(PN, PB, PC, T)                                                                                        \
             {                                                                                                                 \
                 uint2 Rn = R;                                                                                                 \
-                if ((T) + 1 < cnt) Rn = lds64(recAddr + (lane + ((T) + 1) * L) * 8);   /* requested before this one is consumed */ \
+                recAddr += L * 8;                                                                                             \
+                if ((T) + 1 < cnt) Rn = lds64(recAddr);                   /* requested before this one is consumed */         \
                 const uint32_t I = R.y;                                                                                       \
                 PN = f3(lds128(relAddr + ((I & 0xFFu) << 4)));                                                                \
                 if (I & 0x40000000u) {                                                                                        \
@@ -460,9 +482,10 @@ k_sweep_tiles(const SweepArgs a) {
                 g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
             }
             if (lane == 0 && v < nV) {
-                acc[0 * kTileV + v] = fx; acc[1 * kTileV + v] = fy; acc[2 * kTileV + v] = fz;
-                acc[3 * kTileV + v] = g00; acc[4 * kTileV + v] = g01; acc[5 * kTileV + v] = g02;
-                acc[6 * kTileV + v] = g11; acc[7 * kTileV + v] = g12; acc[8 * kTileV + v] = g22;
+                const uint32_t aa = accAddr + v * 4;
+                sts32f(aa + 0 * kTileV * 4, fx); sts32f(aa + 1 * kTileV * 4, fy); sts32f(aa + 2 * kTileV * 4, fz);
+                sts32f(aa + 3 * kTileV * 4, g00); sts32f(aa + 4 * kTileV * 4, g01); sts32f(aa + 5 * kTileV * 4, g02);
+                sts32f(aa + 6 * kTileV * 4, g11); sts32f(aa + 7 * kTileV * 4, g12); sts32f(aa + 8 * kTileV * 4, g22);
             }
         }
         __syncthreads();      // sums complete; this tile's record / neighbour slots and the staging rows are free again
@@ -473,12 +496,13 @@ k_sweep_tiles(const SweepArgs a) {
 
         // ---- transposed tails of the last kTailGroup tiles, one vertex per thread (full SIMT width)
         if (tg == kTailGroup - 1 || k == nMine - 1) {
-            const int2 tv = ((const int2*)(smem + kSmTail))[tid / kTileV];
-            const int vt = tid % kTileV;
-            const float* ac = (const float*)(smem + kSmAcc + (tid / kTileV) * (9 * kTileV * 4));
+            const int tt = tid / kTileV, vt = tid % kTileV;
+            int tvx, tvy;
+            asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(tvx), "=r"(tvy) : "r"(sb + kSmTail + tt * 8));
+            const uint32_t ac = sb + kSmAcc + tt * (9 * kTileV * 4) + vt * 4;
             bool pushed = false;
-            if (tid / kTileV <= tg && vt < tv.y) {
-                const int s = tv.x + vt;
+            if (tt <= tg && vt < tvy) {
+                const int s = tvx + vt;
                 const int4 h = __ldg(a.vtx2 + s);
                 const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF);
                 if (h.w >= 0 && P->activeSolve) {
@@ -487,10 +511,10 @@ k_sweep_tiles(const SweepArgs a) {
                     float4 xpv = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (a.needPrev) xpv = __ldg(a.prev + s);
                     float4 xNew;
-                    const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, ac[0 * kTileV + vt], ac[1 * kTileV + vt], ac[2 * kTileV + vt],
-                                           __int_as_float(h.z), ac[3 * kTileV + vt] * (1.f / 6.f), ac[4 * kTileV + vt] * (1.f / 6.f),
-                                           ac[5 * kTileV + vt] * (1.f / 6.f), ac[6 * kTileV + vt] * (1.f / 6.f), ac[7 * kTileV + vt] * (1.f / 6.f),
-                                           ac[8 * kTileV + vt] * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
+                    const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, lds32f(ac + 0 * kTileV * 4), lds32f(ac + 1 * kTileV * 4), lds32f(ac + 2 * kTileV * 4),
+                                           __int_as_float(h.z), lds32f(ac + 3 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 4 * kTileV * 4) * (1.f / 6.f),
+                                           lds32f(ac + 5 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 6 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 7 * kTileV * 4) * (1.f / 6.f),
+                                           lds32f(ac + 8 * kTileV * 4) * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
                     if (HALO && wrote && (h.w & kHaloBoundaryBit) && !(a.hv.debug & 2)) {
                         const int si = __ldg(a.hv.sendIdx + s);
                         for (int q = 0; q < (si & 15); q++) {
@@ -505,6 +529,7 @@ k_sweep_tiles(const SweepArgs a) {
             if (HALO && pushed) __threadfence_system();
             __syncthreads();      // the sums are consumed: the next group may overwrite them
         }
+        s3 = s3n; parNb = parNbN;
     }
 }
 
@@ -560,6 +585,8 @@ cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool
     a.needPrev = 0;
     for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
     if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
+    a.allActive = 1;
+    for (auto& m : s.meshes) if (!m.activeForMaterialSolve) a.allActive = 0;
     if (hv) a.hv = *hv;
     (void)lanes;      // the record order is laid out for kSweepLanes lanes per vertex
     if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true>(s, a) : launch_tiles<kSweepLanes, false, true>(s, a);
