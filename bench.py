@@ -46,7 +46,7 @@ def emit(obj):
     _REAL_STDOUT.flush()
 
 
-from gaia_b200.workloads import WORKLOADS, build_scene, is_cloth, workload_cloth_drape, workload_twist_beam  # noqa: E402
+from gaia_b200.workloads import WORKLOADS, build_scene, is_cloth, workload_cloth_drape, workload_drop_pile, workload_twist_beam  # noqa: E402
 
 
 # --------------------------------------------------------------------------------------------- clocks
@@ -64,6 +64,9 @@ class ClockSampler:
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.time()
+            while not self.samples and time.time() - t0 < 3.0:      # nvidia-smi needs a moment before its first line
+                time.sleep(0.02)
         except OSError:
             self.proc = None
 
@@ -89,18 +92,48 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.samples)}
 
 
+def physical_cores():
+    """distinct (physical id, core id) pairs of /proc/cpuinfo; falls back to the logical count"""
+    try:
+        seen, phys, core = set(), None, None
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("physical id"):
+                    phys = line.split(":")[1].strip()
+                elif line.startswith("core id"):
+                    core = line.split(":")[1].strip()
+                elif not line.strip():
+                    if phys is not None and core is not None:
+                        seen.add((phys, core))
+                    phys = core = None
+        return len(seen) or os.cpu_count()
+    except OSError:
+        return os.cpu_count()
+
+
 # --------------------------------------------------------------------------------------------- CPU arm
 def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
     """Time the CPU oracle on a bounded sample of the workload: a beam of the same cross-section and material, 1/8 of the
     length, one frame (5 substeps x 20 iterations); iterations are reduced if one substep already exceeds the budget."""
+    from oracle import binding, binding_cloth
     from oracle.binding import OracleScene
     from oracle.binding_cloth import OracleClothScene
+    speed = binding.use_speed_build()          # -O3 -march=x86-64-v3, FMA contraction allowed (oracle/Makefile: liboracle_fast.so)
+    binding_cloth.use_speed_build()
     if wl_name.startswith("cloth"):
         # same cell size, material and contact parameters on a 160 x 160 sheet (sphere scaled with it)
         sample_wl = WORKLOADS[wl_name]() if wl_name == "cloth_small" else workload_cloth_drape(160, width=16.0, sphere_level=3, preroll=0)
         OracleScene = OracleClothScene
+    elif wl_name.startswith("twist_beam"):
+        sample_wl = workload_twist_beam(59, 60, 60, collisions="nodcd" not in wl_name) if "10m" in wl_name or "1m" in wl_name else WORKLOADS[wl_name]()
+    elif wl_name.startswith("drop_pile"):
+        # same shapes, material, contact parameters and step settings on at most 32 objects, timed from the start of the drop
+        full = WORKLOADS[wl_name]()
+        sample_wl = workload_drop_pile(min(32, len(full["meshes"])), substeps=full["phys"].numSubsteps, iterations=full["phys"].iterations, preroll=0)
+    elif wl_name == "s01":
+        sample_wl = WORKLOADS["s01"]()          # the scene itself; the CPU is timed on its first frames (models 0, 1, ... in free fall and first contacts)
     else:
-        sample_wl = workload_twist_beam(59, 60, 60) if "10m" in wl_name or "1m" in wl_name else WORKLOADS[wl_name]()
+        sample_wl = WORKLOADS[wl_name]()
     t0 = time.time()
     o = build_scene(OracleScene, sample_wl, threads=threads)
     setup = time.time() - t0
@@ -123,7 +156,9 @@ def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
         what = f"{frames} frame(s)"
     dt = time.time() - t0
     st = o.stats()
-    return {"value": st["vertexSolves"] / dt, "unit": "vertex-solves/s", "cores": o.num_threads, "kind": "port",
+    return {"value": st["vertexSolves"] / dt, "unit": "vertex-solves/s", "cores": o.num_threads, "physical_cores": physical_cores(), "kind": "port",
+            "build": "liboracle_fast.so: -O3 -march=x86-64-v3 -ffp-contract=fast" if speed else "liboracle.so (parity build: -O3 -march=x86-64-v2 -ffp-contract=off)",
+            "sample_workload": sample_wl["name"],
             "sample": f"{sample_wl['name']}: {what} in {dt:.1f}s (setup {setup:.1f}s), oracle = CPU restatement of "
                       + ("VBDClothSimulationFramework::runStep_CDEveryIter" if wl_name.startswith("cloth") else
                          "VBDPhysics::runStep_hybridCollisionHandling") + " with std::thread pool"}, st["vertexSolves"], dt
@@ -146,7 +181,8 @@ def run_reference_arm(args):
     out = {"impl": "reference", "metric": "VBD vertex-solves/sec", "value": value, "unit": "vertex-solves/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": wl["name"], "parallelism": f"cpu{base['cores']}"},
+           "config": {"workload": base["sample_workload"] + " [bounded sample of: " + wl["name"] + "]",
+                      "parallelism": f"cpu: {base['cores']} threads on {base['physical_cores']} physical cores"},
            "cpu_baseline": base, "e2e": {"value": value, "unit": "vertex-solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     emit(out)
@@ -295,12 +331,12 @@ def main():
                       ("timeCsmpColDetectDCD", "timeCsmpInitialStep", "timeCsmpColDetectCCD", "timeCsmpMaterialSolve", "timeCsmpUpdateVelocity"))
         contacts = ({"vf": sp["numContactsVF"], "ee": sp["numContactsEE"], "detections": sp["numberCollisionDetection"]} if is_cloth(wl) else
                     {"dcd": sp["numContactsDCD"], "ccd": sp["numContactsCCD"]})
-        roof = {"kernel": "gbc::k_solve_colour (cloth)" if is_cloth(wl) else "k_solve_colour", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        roof = {"kernel": "gbc::k_solve_colour (cloth)" if is_cloth(wl) else "gb::k_sweep_tiles", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes / max(1, launches), "avg_launch_us": 1e3 * k_ms / max(1, launches),
                 "launches_profiled": launches, "kernel_share_of_step": (k_ms / max(1, args.profile_steps)) / (ms / args.steps),
                 "phases_ms_per_step": {k: sp[k] / max(1, args.profile_steps) for k in phase_keys},
-                "contacts": contacts}
+                "contacts": contacts, "detection": "DCD %s, CCD %s" % (("on" if wl["col"].allowDCD else "off"), ("on" if wl["col"].allowCCD else "off")) if not is_cloth(wl) else "VF + EE every iteration that needs it"}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath) and world == 1:
             try:
@@ -314,6 +350,15 @@ def main():
             except (OSError, ValueError):
                 pass
 
+    if is_cloth(wl):
+        per_iter = 656.0 * nV
+    else:
+        lb = scene.layout_bytes()
+        per_iter = lb["records"] + lb["neighbours"] + lb["vertex_state"] + lb["tiles"]
+    l2_note = ("inputs larger than L2 (one iteration streams %.2f GB of records, neighbour entries and vertex state vs 126 MB of L2), no flush needed"
+               % (per_iter / 1e9)) if per_iter > 2 * 126e6 else \
+              ("inputs SMALLER than L2 (%.1f MB per iteration vs 126 MB): the step is latency-bound, L2-resident by nature of the scene; no flush"
+               % (per_iter / 1e6))
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, _, _ = cpu_baseline(args.workload)
@@ -323,8 +368,7 @@ def main():
                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": wl["name"], "parallelism": (f"{'objects sharded' if len(wl['meshes']) > 1 else 'x-slab partition'} over {world} GPU(s)") if world > 1 else "1 GPU",
-                          "l2": "inputs larger than L2 (per-iteration record streams: %s vs 126 MB), no flush needed"
-                                % ("0.57 GB" if is_cloth(wl) else "1.3 GB"),
+                          "l2": l2_note,
                           "sim_steps_per_s": st["substeps"] / (ms * 1e-3), "frames_per_s": args.steps / (ms * 1e-3)},
                "clocks": clk, "e2e": e2e, "gpu_launches": int(st["kernelLaunches"]), "roofline": roof, "cpu_baseline": cpu}
         emit(out)

@@ -369,6 +369,7 @@ def load_library(path=None):
     lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
+    lib.gaia_b200_get_layout_bytes.argtypes = [P, C.POINTER(C.c_int64)]
     lib.gaia_b200_color_graph.argtypes = [C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
@@ -465,6 +466,11 @@ class Scene(SceneBase):
 
     def set_profiling(self, on=True):
         self._call("set_profiling", int(on))
+
+    def layout_bytes(self):
+        a = (C.c_int64 * 6)()
+        self._call("get_layout_bytes", a)
+        return dict(zip(("records", "neighbours", "vertex_state", "tiles", "pos_reads", "incidences"), [int(x) for x in a]))
 
     def set_solver_lanes(self, lanes):
         """0 (default 4), 4 or 8 lanes per vertex; runs compared bit for bit must use the same value"""

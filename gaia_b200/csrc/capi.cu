@@ -309,7 +309,7 @@ int gaia_b200_detect_collisions(gaia_handle* h, int doDCD, int doCCD) {
     REQUIRE(h); FINALIZED(h);
     Scene& s = h->s;
     cudaSetDevice(s.device);
-    sync_mesh_params(s);
+    { const cudaError_t e0 = sync_mesh_params(s); if (e0 != cudaSuccess) return cuda_fail(s, e0); }
     const gaia_collision_params saved = s.col;
     s.col.allowDCD = saved.allowDCD && doDCD; s.col.allowCCD = saved.allowCCD && doCCD;
     s.substep = 0;
@@ -439,6 +439,14 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
     if (lanes != 0 && lanes != 4 && lanes != 8) return fail(h->s, GAIA_ERR_INVALID_ARG, "solver lanes: 0 (default), 4 or 8");
     if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }
     h->s.solveLanes = lanes;
+    return GAIA_OK;
+}
+int gaia_b200_get_layout_bytes(gaia_handle* h, int64_t out[6]) {
+    REQUIRE(h); FINALIZED(h);
+    if (!out) return GAIA_ERR_INVALID_ARG;
+    const Scene& s = h->s;
+    out[0] = (int64_t)s.rec.n * 8; out[1] = (int64_t)s.nbw.n * 8; out[2] = (int64_t)s.nVerts * (16 + 16 + 16 + 16);
+    out[3] = (int64_t)s.tiles.n * (int64_t)sizeof(TileDesc); out[4] = s.sweepPosReads; out[5] = s.nInc;
     return GAIA_OK;
 }
 void* gaia_b200_cuda_stream(gaia_handle* h) { return h ? (void*)h->s.stream : nullptr; }

@@ -30,6 +30,8 @@ namespace gb {
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 static const int kB = 128;
 static inline int nblk(int64_t n, int per = kB) { return (int)((n + per - 1) / per); }
+// grid of a grid-stride kernel: at most one full wave of 148 SMs x 16 blocks (a launch that decides on the device to do nothing costs one wave)
+static inline int capped(int64_t n, int per = kB) { return (int)std::min<int64_t>((n + per - 1) / per, 148 * 16); }
 
 struct ColParamsDev {
     int32_t allowCCD, checkFeasibleRegion, checkTetTraverse, handleSelfCollision, stopAfterPassing, traverseNonSelf, shiftQueryToCenter;
@@ -46,7 +48,7 @@ struct Lbvh {
     DevBuf<int32_t> idIn, order;         // order[j] = primitive at sorted position j
     DevBuf<int2> child;
     DevBuf<int32_t> parent;              // [2n]
-    DevBuf<float4> lo, hi;               // [2n]
+    DevBuf<float4> box;                  // [2n][2]: lo, hi of a node side by side (one 32-byte sector per node visit)
     DevBuf<int32_t> flags;
     DevBuf<int2> segRange;               // per segment: [lo,hi) in sorted positions
     DevBuf<uint8_t> tmp;
@@ -57,7 +59,7 @@ struct Lbvh {
         n = n_;
         if (!n) return cudaSuccess;
         CK(primLo.alloc(n)); CK(primHi.alloc(n)); CK(keyIn.alloc(n)); CK(keyOut.alloc(n)); CK(idIn.alloc(n)); CK(order.alloc(n));
-        CK(child.alloc(n)); CK(parent.alloc(2 * (size_t)n)); CK(lo.alloc(2 * (size_t)n)); CK(hi.alloc(2 * (size_t)n)); CK(flags.alloc(n));
+        CK(child.alloc(n)); CK(parent.alloc(2 * (size_t)n)); CK(box.alloc(4 * (size_t)n)); CK(flags.alloc(n));
         CK(segRange.alloc(segs.size()));
         CK(cudaMemcpy(segRange.p, segs.data(), segs.size() * sizeof(int2), cudaMemcpyHostToDevice));
         cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, keyIn.p, keyOut.p, idIn.p, order.p, n);
@@ -111,22 +113,27 @@ __global__ void k_karras(int n, const uint64_t* __restrict__ keys, const int2* _
 
 __device__ __forceinline__ float4 ldcg4(const float4* p) { return __ldcg(p); }
 
-// bottom-up refit: the second thread to reach a node merges its children
+// bottom-up refit: the second thread to reach a node merges its children (and leaves the node's counter at zero for the
+// next refit). `need` (optional): device flag of the lazy refit - when it reads 0 the boxes are still conservative and the
+// whole launch is a no-op.
 __global__ void k_refit(int n, const int32_t* __restrict__ order, const float4* __restrict__ primLo, const float4* __restrict__ primHi,
-                        const int2* __restrict__ child, const int32_t* __restrict__ parent, float4* lo, float4* hi, int32_t* flags) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
-    const int prim = order[j];
-    lo[n + j] = primLo[prim]; hi[n + j] = primHi[prim];
-    int cur = parent[n + j];
-    while (cur >= 0) {
-        __threadfence();
-        if (atomicAdd(flags + cur, 1) == 0) return;
-        const int2 c = child[cur];
-        const float4 a0 = ldcg4(lo + c.x), a1 = ldcg4(hi + c.x), b0 = ldcg4(lo + c.y), b1 = ldcg4(hi + c.y);
-        lo[cur] = make_float4(fminf(a0.x, b0.x), fminf(a0.y, b0.y), fminf(a0.z, b0.z), 0.f);
-        hi[cur] = make_float4(fmaxf(a1.x, b1.x), fmaxf(a1.y, b1.y), fmaxf(a1.z, b1.z), 0.f);
-        cur = parent[cur];
+                        const int2* __restrict__ child, const int32_t* __restrict__ parent, float4* box, int32_t* flags,
+                        const int32_t* __restrict__ need) {
+    if (need && !*need) return;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {     // capped grid: a skipped refit costs one wave
+        const int prim = order[j];
+        box[2 * (n + j)] = primLo[prim]; box[2 * (n + j) + 1] = primHi[prim];
+        int cur = parent[n + j];
+        while (cur >= 0) {
+            __threadfence();
+            if (atomicAdd(flags + cur, 1) == 0) break;
+            flags[cur] = 0;
+            const int2 c = child[cur];
+            const float4 a0 = ldcg4(box + 2 * c.x), a1 = ldcg4(box + 2 * c.x + 1), b0 = ldcg4(box + 2 * c.y), b1 = ldcg4(box + 2 * c.y + 1);
+            box[2 * cur] = make_float4(fminf(a0.x, b0.x), fminf(a0.y, b0.y), fminf(a0.z, b0.z), 0.f);
+            box[2 * cur + 1] = make_float4(fmaxf(a1.x, b1.x), fmaxf(a1.y, b1.y), fmaxf(a1.z, b1.z), 0.f);
+            cur = parent[cur];
+        }
     }
 }
 
@@ -199,10 +206,10 @@ __device__ __forceinline__ uint32_t morton_of(float3 lo, float3 hi, const float*
     return e[0] * 4 + e[1] * 2 + e[2];
 }
 static const float kInflate = 1e-4f;
-__device__ __forceinline__ void store_box(float3 lo, float3 hi, float4* outLo, float4* outHi) {
-    const float mx = kInflate * (1.f + fmaxf(fabsf(lo.x), fabsf(hi.x)));
-    const float my = kInflate * (1.f + fmaxf(fabsf(lo.y), fabsf(hi.y)));
-    const float mz = kInflate * (1.f + fmaxf(fabsf(lo.z), fabsf(hi.z)));
+__device__ __forceinline__ void store_box(float3 lo, float3 hi, float4* outLo, float4* outHi, float margin) {
+    const float mx = kInflate * (1.f + fmaxf(fabsf(lo.x), fabsf(hi.x))) + margin;
+    const float my = kInflate * (1.f + fmaxf(fabsf(lo.y), fabsf(hi.y))) + margin;
+    const float mz = kInflate * (1.f + fmaxf(fabsf(lo.z), fabsf(hi.z))) + margin;
     *outLo = make_float4(lo.x - mx, lo.y - my, lo.z - mz, 0.f);
     *outHi = make_float4(hi.x + mx, hi.y + my, hi.z + mz, 0.f);
 }
@@ -216,23 +223,42 @@ __device__ __forceinline__ void grow(float3& lo, float3& hi, float4 p) {
 template <int WHICH>
 __global__ void k_prim_boxes(int n, const int4* __restrict__ prims, const int32_t* __restrict__ primMesh, const float4* __restrict__ pos,
                              const float4* __restrict__ prev, const MeshParamsDev* __restrict__ mp, const float* __restrict__ normBox, int nMeshes,
-                             int segmented, int writeKeys, float4* __restrict__ primLo, float4* __restrict__ primHi, uint64_t* __restrict__ keys) {
+                             int segmented, int writeKeys, float4* __restrict__ primLo, float4* __restrict__ primHi, uint64_t* __restrict__ keys,
+                             float margin, const int32_t* __restrict__ need) {
+    if (need && !*need) return;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int4 v = __ldg(prims + i);
+        const int mesh = WHICH == 0 ? __ldg(primMesh + i) : v.w;
+        const uint64_t segHi = segmented ? ((uint64_t)(uint32_t)mesh << 32) : 0ull;
+        if (!mp[mesh].activeCollide) {
+            primLo[i] = make_float4(3e38f, 3e38f, 3e38f, 0.f); primHi[i] = make_float4(-3e38f, -3e38f, -3e38f, 0.f);
+            if (writeKeys) keys[i] = segHi | (1ull << 30);
+            continue;
+        }
+        float3 lo = make_float3(3e38f, 3e38f, 3e38f), hi = make_float3(-3e38f, -3e38f, -3e38f);
+        grow(lo, hi, pos[v.x]); grow(lo, hi, pos[v.y]); grow(lo, hi, pos[v.z]);
+        if (WHICH == 0) grow(lo, hi, pos[v.w]);
+        if (WHICH == 2) { grow(lo, hi, prev[v.x]); grow(lo, hi, prev[v.y]); grow(lo, hi, prev[v.z]); }
+        if (writeKeys) keys[i] = segHi | morton_of(lo, hi, normBox + 6 * (segmented ? mesh : nMeshes));
+        store_box(lo, hi, primLo + i, primHi + i, margin);
+    }
+}
+
+// Lazy refit of the DCD trees. Their boxes are inflated by `margin` when they are computed, around the positions kept in
+// refPos; as long as no vertex has moved further than `margin` from refPos every box still contains its primitive, the
+// culling stays conservative (queries test the primitives themselves, so results do not change), and the refit - the
+// expensive part of a detection on a 10 M-tet mesh, repeated every few iterations by intermediateCollisionIterations - is
+// skipped. The decision is taken on the device: one flag, read by the box / refit kernels.
+__global__ void k_disp_check(int n, const float4* __restrict__ pos, const float4* __restrict__ ref, float margin2, int32_t* need) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int4 v = __ldg(prims + i);
-    const int mesh = WHICH == 0 ? __ldg(primMesh + i) : v.w;
-    const uint64_t segHi = segmented ? ((uint64_t)(uint32_t)mesh << 32) : 0ull;
-    if (!mp[mesh].activeCollide) {
-        primLo[i] = make_float4(3e38f, 3e38f, 3e38f, 0.f); primHi[i] = make_float4(-3e38f, -3e38f, -3e38f, 0.f);
-        if (writeKeys) keys[i] = segHi | (1ull << 30);
-        return;
-    }
-    float3 lo = make_float3(3e38f, 3e38f, 3e38f), hi = make_float3(-3e38f, -3e38f, -3e38f);
-    grow(lo, hi, pos[v.x]); grow(lo, hi, pos[v.y]); grow(lo, hi, pos[v.z]);
-    if (WHICH == 0) grow(lo, hi, pos[v.w]);
-    if (WHICH == 2) { grow(lo, hi, prev[v.x]); grow(lo, hi, prev[v.y]); grow(lo, hi, prev[v.z]); }
-    if (writeKeys) keys[i] = segHi | morton_of(lo, hi, normBox + 6 * (segmented ? mesh : nMeshes));
-    store_box(lo, hi, primLo + i, primHi + i);
+    const float4 a = pos[i], b = __ldg(ref + i);
+    const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
+    if (!(dx * dx + dy * dy + dz * dz <= margin2)) *need = 1;      // (NaN counts as moved)
+}
+__global__ void k_copy_ref(int n, const float4* __restrict__ pos, float4* __restrict__ ref, const int32_t* __restrict__ need) {
+    if (!*need) return;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) ref[i] = pos[i];
 }
 
 // ------------------------------------------------------------------------------------------------ collision state
@@ -248,6 +274,9 @@ struct CollisionState {
     DevBuf<int32_t> groupStart;   // G + 1
     int G = 0;
     Lbvh tetBvh, surfBvh, ccdBvh;
+    DevBuf<float4> refPos;        // lazy refit of the DCD trees: positions their boxes were computed at
+    DevBuf<int32_t> needRefit;    // device flag: some vertex left its margin (or a rebuild forces the refit)
+    float lazyMargin = 0.f;
     DevBuf<int32_t> boundsOrd;    // 6 * (nMeshes + 1)
     DevBuf<float> normBox;        // 6 * (nMeshes + 1)
     // dense results per surface-vertex slot
@@ -326,7 +355,15 @@ cudaError_t collision_init(Scene& s) {
     CK(up(c->surfNbrOff, surfNbrOff)); CK(up(c->surfNbr, surfNbr)); CK(up(c->slotOfSorted, slotOfSorted));
     c->G = (int)s.groupStart.size() - 1;
     CK(up(c->groupStart, s.groupStart));
-    if (s.col.allowDCD) { CK(c->tetBvh.alloc((int)nT, oneSegT)); CK(c->surfBvh.alloc((int)nF, faceSegs)); }
+    if (s.col.allowDCD) {
+        CK(c->tetBvh.alloc((int)nT, oneSegT)); CK(c->surfBvh.alloc((int)nF, faceSegs));
+        CK(c->refPos.alloc(N + 1)); CK(c->needRefit.alloc(1));
+        // margin = a tenth of the typical tet edge (cube root of 6 x the mean rest volume): refits become rare for slowly
+        // deforming bodies while the boxes - and with them the number of nodes a query visits - grow by a few per cent only
+        double vol = 0.0; int64_t cnt = 0;
+        for (auto& m : s.meshes) for (float v : m.restVol) { vol += std::fabs((double)v); cnt++; }
+        c->lazyMargin = cnt ? 0.1f * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
+    }
     if (s.col.allowCCD) CK(c->ccdBvh.alloc((int)nF, oneSegF));
     const size_t nM = s.meshes.size();
     CK(c->boundsOrd.alloc(6 * (nM + 1))); CK(c->normBox.alloc(6 * (nM + 1)));
@@ -369,26 +406,33 @@ static cudaError_t compute_norm_boxes(Scene& s) {
     return cudaGetLastError();
 }
 
+static bool activity_differs(const Scene& s, const std::vector<uint8_t>& snap) {
+    if (snap.size() != s.meshes.size()) return true;
+    for (size_t i = 0; i < s.meshes.size(); i++) if (snap[i] != (uint8_t)s.meshes[i].activeForCollision) return true;
+    return false;
+}
+
+// margin / need: lazy refit (DCD trees); need == nullptr: boxes and refit always run
 template <int WHICH>
-static cudaError_t update_bvh(Scene& s, Lbvh& b, bool rebuild, bool segmented) {
+static cudaError_t update_bvh(Scene& s, Lbvh& b, bool rebuild, bool segmented, float margin = 0.f, const int32_t* need = nullptr) {
     CollisionState* c = s.cs;
     if (!b.n) return cudaSuccess;
     const int nM = (int)s.meshes.size();
     const bool ch = activity_changed(s, b.activeAtBuild);
     const bool doBuild = !b.built || rebuild || ch;
-    if (doBuild) CK(compute_norm_boxes(s));
+    if (doBuild) { CK(compute_norm_boxes(s)); need = nullptr; }
     const int4* prims = WHICH == 0 ? c->tetSid.p : c->faceSid.p;
-    k_prim_boxes<WHICH><<<nblk(b.n), kB, 0, s.stream>>>(b.n, prims, c->tetMesh.p, s.pos.p, s.prev.p, s.meshParams.p, c->normBox.p, nM,
-                                                      segmented ? 1 : 0, doBuild ? 1 : 0, b.primLo.p, b.primHi.p, b.keyIn.p);
+    k_prim_boxes<WHICH><<<capped(b.n), kB, 0, s.stream>>>(b.n, prims, c->tetMesh.p, s.pos.p, s.prev.p, s.meshParams.p, c->normBox.p, nM,
+                                                      segmented ? 1 : 0, doBuild ? 1 : 0, b.primLo.p, b.primHi.p, b.keyIn.p, margin, need);
     s.stats.kernelLaunches++;
     if (doBuild) {
         CK(cub::DeviceRadixSort::SortPairs(b.tmp.p, b.tmpBytes, b.keyIn.p, b.keyOut.p, b.idIn.p, b.order.p, b.n, 0, 64, s.stream));
         k_karras<<<nblk(b.n), kB, 0, s.stream>>>(b.n, b.keyOut.p, b.segRange.p, b.child.p, b.parent.p);
         s.stats.kernelLaunches += 3;
         b.built = true;
+        CK(cudaMemsetAsync(b.flags.p, 0, (size_t)b.n * sizeof(int32_t), s.stream));     // (refits leave the counters at zero)
     }
-    CK(cudaMemsetAsync(b.flags.p, 0, (size_t)b.n * sizeof(int32_t), s.stream));
-    k_refit<<<nblk(b.n), kB, 0, s.stream>>>(b.n, b.order.p, b.primLo.p, b.primHi.p, b.child.p, b.parent.p, b.lo.p, b.hi.p, b.flags.p);
+    k_refit<<<nblk(b.n), kB, 0, s.stream>>>(b.n, b.order.p, b.primLo.p, b.primHi.p, b.child.p, b.parent.p, b.box.p, b.flags.p, need);
     s.stats.kernelLaunches++;
     return cudaGetLastError();
 }
@@ -404,18 +448,26 @@ __device__ __forceinline__ float box_dist2(float4 lo, float4 hi, V3 p) {
     return dx * dx + dy * dy + dz * dz;
 }
 
-struct BvhView { int n; const int2* child; const float4 *lo, *hi; const int32_t* order; };
-static BvhView view_of(const Lbvh& b) { BvhView v; v.n = b.n; v.child = b.child.p; v.lo = b.lo.p; v.hi = b.hi.p; v.order = b.order.p; return v; }
+struct BvhView { int n; const int2* child; const float4* box; const int32_t* order; };
+static BvhView view_of(const Lbvh& b) { BvhView v; v.n = b.n; v.child = b.child.p; v.box = b.box.p; v.order = b.order.p; return v; }
 
 static const int kStack = 64;
 
-// DCD phase 1 (vertexCollisionDetection + tetIntersectionFunc, rule R1): the containing tet with the smallest global id
+// DCD phase 1 (vertexCollisionDetection + tetIntersectionFunc, rule R1): the containing tet with the smallest global id.
+// One WARP per surface vertex: the nodes whose box holds the point form a frontier kept in shared memory; every round the 32
+// lanes test 32 frontier nodes at once (internal node: its children join the frontier; leaf: the tet itself is tested) and
+// the smallest containing tet id is warp-reduced at the end. A point on the surface of a regular mesh sits in the boxes of
+// ~50 tets and of their ancestors, ~250 node visits that one thread would walk one dependent load after the other.
+static const int kFrontier = 384;          // frontier capacity per warp (overflow -> errFlags[3], like the traversal stacks)
 __global__ void __launch_bounds__(kB)
 k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const int32_t* __restrict__ surfSid, const int32_t* __restrict__ surfMesh,
              const MeshParamsDev* __restrict__ mp, const float4* __restrict__ pos, const int4* __restrict__ tetSid,
              const int32_t* __restrict__ tetMesh, uint8_t* penetrated, int32_t* cNum, int32_t* cHitTet, int32_t* cFace, int32_t* cFlags,
              int32_t* hitList, int32_t* nHits, int32_t* errFlags) {
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ int32_t frontierAll[(kB / 32) * kFrontier];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t* frontier = frontierAll + warp * kFrontier;
+    const int slot = blockIdx.x * (kB / 32) + warp;
     if (slot >= nSlots) return;
     const int mesh = surfMesh[slot];
     if (!mp[mesh].activeCollide) return;
@@ -424,33 +476,51 @@ k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const in
     if (intermediate) {
         if (!(penetrated[slot] || !cp.allowCCD)) return;
     } else {
-        penetrated[slot] = 0;
+        if (lane == 0) penetrated[slot] = 0;
         if (!(p.y < cp.offHeight)) return;
     }
     int best = 0x7FFFFFFF;
     if (bv.n > 0) {
-        int stack[kStack];
-        int sp = 0;
-        const int root = bv.n > 1 ? 0 : bv.n;   // single-leaf scene: the leaf itself
-        stack[sp++] = root;
-        while (sp) {
-            const int node = stack[--sp];
-            if (!box_contains(bv.lo[node], bv.hi[node], p)) continue;
+        // the frontier only ever holds nodes whose box contains the point: children are tested before they are queued
+        const int root = bv.n > 1 ? 0 : bv.n;               // single-leaf scene: the leaf itself
+        int qn = box_contains(bv.box[2 * root], bv.box[2 * root + 1], p) ? 1 : 0;
+        if (lane == 0) frontier[0] = root;
+        __syncwarp();
+        while (qn > 0) {
+            const int m = qn < 32 ? qn : 32;
+            int node = -1;
+            if (lane < m) node = frontier[qn - 1 - lane];
+            qn -= m;
+            __syncwarp();
+            int c0 = -1, c1 = -1;
             if (node >= bv.n) {
                 const int t = bv.order[node - bv.n];
-                if (t >= best) continue;
                 const int g = tetMesh[t];
-                if (!cp.handleSelfCollision && g == mesh) continue;
-                const int4 tv = __ldg(tetSid + t);
-                if (g == mesh && (tv.x == s || tv.y == s || tv.z == s || tv.w == s)) continue;
-                if (point_in_tet(p, v3(pos[tv.x]), v3(pos[tv.y]), v3(pos[tv.z]), v3(pos[tv.w]))) best = t;
-            } else {
+                if (t < best && (cp.handleSelfCollision || g != mesh)) {
+                    const int4 tv = __ldg(tetSid + t);
+                    if (!(g == mesh && (tv.x == s || tv.y == s || tv.z == s || tv.w == s)) &&
+                        point_in_tet(p, v3(pos[tv.x]), v3(pos[tv.y]), v3(pos[tv.z]), v3(pos[tv.w]))) best = t;
+                }
+            } else if (node >= 0) {
                 const int2 ch = bv.child[node];
-                if (sp + 2 > kStack) { atomicAdd(errFlags + 3, 1); continue; }
-                stack[sp++] = ch.x; stack[sp++] = ch.y;
+                const float4 l0 = bv.box[2 * ch.x], h0 = bv.box[2 * ch.x + 1], l1 = bv.box[2 * ch.y], h1 = bv.box[2 * ch.y + 1];
+                if (box_contains(l0, h0, p)) c0 = ch.x;
+                if (box_contains(l1, h1, p)) c1 = ch.y;
             }
+            const int mine = (c0 >= 0) + (c1 >= 0);
+            int incl = mine;                                 // inclusive prefix sum of the pushes over the warp
+            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+            const int nPush = __shfl_sync(0xffffffffu, incl, 31);
+            if (qn + nPush > kFrontier) { if (lane == 0) atomicAdd(errFlags + 3, 1); break; }
+            int at = qn + incl - mine;
+            if (c0 >= 0) frontier[at++] = c0;
+            if (c1 >= 0) frontier[at] = c1;
+            qn += nPush;
+            __syncwarp();
         }
     }
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane) return;
     // CollisionDetectionResult::clear() + the new result
     if (best != 0x7FFFFFFF) {
         cNum[slot] = 1; cHitTet[slot] = best; cFace[slot] = -1; cFlags[slot] = (NotFound << 8);
@@ -619,12 +689,12 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
             while (sp > 0 && nCand < 32) {
                 const int node = sStack[w][--sp];
                 const float r2 = radius == kInf ? 1e30f : radius * radius * 1.0001f + 1e-12f;
-                if (box_dist2(bv.lo[node], bv.hi[node], q) > r2) continue;
+                if (box_dist2(bv.box[2 * node], bv.box[2 * node + 1], q) > r2) continue;
                 if (node >= bv.n) { sCand[w][nCand++] = bv.order[node - bv.n]; continue; }
                 const int2 ch = bv.child[node];
                 if (sp + 2 > kStack) { if (lane == 0) atomicAdd(errFlags + 3, 1); continue; }
                 // nearer child on top of the stack: the radius shrinks sooner
-                const float dx = box_dist2(bv.lo[ch.x], bv.hi[ch.x], q), dy = box_dist2(bv.lo[ch.y], bv.hi[ch.y], q);
+                const float dx = box_dist2(bv.box[2 * ch.x], bv.box[2 * ch.x + 1], q), dy = box_dist2(bv.box[2 * ch.y], bv.box[2 * ch.y + 1], q);
                 __syncwarp();
                 if (dx <= dy) { sStack[w][sp++] = ch.y; sStack[w][sp++] = ch.x; } else { sStack[w][sp++] = ch.x; sStack[w][sp++] = ch.y; }
                 __syncwarp();
@@ -702,7 +772,7 @@ k_ccd(int nSlots, ColParamsDev cp, BvhView bv, const int4* __restrict__ faceSid,
         stack[sp++] = bv.n > 1 ? 0 : bv.n;
         while (sp) {
             const int node = stack[--sp];
-            if (box_dist2(bv.lo[node], bv.hi[node], mid) > r2) continue;
+            if (box_dist2(bv.box[2 * node], bv.box[2 * node + 1], mid) > r2) continue;
             if (node >= bv.n) {
                 const int face = bv.order[node - bv.n];
                 const int4 fv = __ldg(faceSid + face);
@@ -747,12 +817,24 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
             rebuildTet = (s.substep == 0) && !(s.frameId % s.phys.dcdTetMeshSceneBVHRebuildSteps) && s.frameId;
             rebuildSurf = (s.substep == 0) && !(s.frameId % s.phys.dcdSurfaceSceneBVHRebuildSteps) && s.frameId;
         }
-        CK(update_bvh<0>(s, c->tetBvh, rebuildTet, false));
-        CK(update_bvh<1>(s, c->surfBvh, rebuildSurf, true));
+        {
+            const int N = (int)s.nVerts;
+            const bool force = rebuildTet || rebuildSurf || !c->tetBvh.built || !c->surfBvh.built ||
+                               activity_differs(s, c->tetBvh.activeAtBuild) || activity_differs(s, c->surfBvh.activeAtBuild);
+            if (force) CK(cudaMemsetAsync(c->needRefit.p, 0x01, sizeof(int32_t), s.stream));
+            else {
+                CK(cudaMemsetAsync(c->needRefit.p, 0, sizeof(int32_t), s.stream));
+                k_disp_check<<<nblk(N), kB, 0, s.stream>>>(N, s.pos.p, c->refPos.p, c->lazyMargin * c->lazyMargin, c->needRefit.p);
+            }
+            CK(update_bvh<0>(s, c->tetBvh, rebuildTet, false, c->lazyMargin, c->needRefit.p));
+            CK(update_bvh<1>(s, c->surfBvh, rebuildSurf, true, c->lazyMargin, c->needRefit.p));
+            k_copy_ref<<<capped(N), kB, 0, s.stream>>>(N, s.pos.p, c->refPos.p, c->needRefit.p);
+            s.stats.kernelLaunches += 2;
+        }
         int32_t* nHits = c->groupCount.p + c->G + 2;
         CK(cudaMemsetAsync(nHits, 0, sizeof(int32_t), s.stream));
         TopoView tp{c->tetSid.p, c->tetNbr.p, c->faceSid.p, c->faceInfo.p, c->faceNbr.p, c->surfNbrOff.p, c->surfNbr.p, c->slotOfSorted.p};
-        k_dcd_phase1<<<nblk(nS), kB, 0, s.stream>>>(nS, intermediate ? 1 : 0, c->cp, view_of(c->tetBvh), c->surfSid.p, c->surfMesh.p, s.meshParams.p,
+        k_dcd_phase1<<<nblk((int64_t)nS * 32), kB, 0, s.stream>>>(nS, intermediate ? 1 : 0, c->cp, view_of(c->tetBvh), c->surfSid.p, c->surfMesh.p, s.meshParams.p,
                                                   s.pos.p, c->tetSid.p, c->tetMesh.p, c->penetrated.p, c->cNum.p, c->cHitTet.p, c->cFace.p,
                                                   c->cFlags.p, c->hitList.p, nHits, s.errFlags.p);
         // phase 2 runs over the compacted hit list; its length stays on the device (grid sized for the worst case, early exit)

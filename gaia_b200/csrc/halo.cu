@@ -140,9 +140,9 @@ cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nS
     return cudaSuccess;
 }
 
-__global__ void k_mark_boundary(int n, const int32_t* __restrict__ sorted, int4* vtx, int4* vtx2) {
+__global__ void k_mark_boundary(int n, const int32_t* __restrict__ sorted, int4* vtx2) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { vtx[sorted[i]].w |= kHaloBoundaryBit; vtx2[sorted[i]].w |= kHaloBoundaryBit; }
+    if (i < n) vtx2[sorted[i]].w |= kHaloBoundaryBit;
 }
 
 // Tables of the fused exchange (the colour solve pushes its own boundary vertices): every vertex this partition sends is
@@ -174,7 +174,7 @@ cudaError_t halo_finalize(Scene& s) {
         DevBuf<int32_t> d;
         CK(d.alloc(bverts.size()));
         CK(cudaMemcpy(d.p, bverts.data(), bverts.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-        k_mark_boundary<<<((int)bverts.size() + 255) / 256, 256, 0, s.stream>>>((int)bverts.size(), d.p, s.vtx.p, s.vtx2.p);
+        k_mark_boundary<<<((int)bverts.size() + 255) / 256, 256, 0, s.stream>>>((int)bverts.size(), d.p, s.vtx2.p);
         CK(cudaStreamSynchronize(s.stream));
     }
     {

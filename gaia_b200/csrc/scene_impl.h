@@ -68,7 +68,7 @@ struct HaloView {
     const int32_t* boundaryPrefix;            // [N+1] number of boundary vertices below a sorted id
     uint32_t* ctl;                            // [0] epoch, [1] block ticket
     int epochOffset;                          // colour launches of this batch before this one
-    int debug;                                // timing experiments (GAIA_B200_HALO_DEBUG)
+    int debug;                                // 0 (kept for layout; bit 0 = do not wait, bit 1 = do not push: timing experiments only)
 };
 
 // One tile of the colour sweep (sweep.cu): up to kTileV consecutive vertices of one colour whose incidence records and
@@ -102,11 +102,6 @@ struct Scene {
     DevBuf<float4> pos, prev, inertia, vel, velPrev, accel, accPrevPrev, accPrevIter;
     DevBuf<float> mass;
     DevBuf<int32_t> info;          // meshId | fixed<<31
-    DevBuf<int32_t> incOff;
-    DevBuf<float4> incW;           // per incidence: (A w'.x, A w'.y, A w'.z, det B')
-    DevBuf<uint32_t> incIdx;       // per incidence: local neighbour slots a | b<<8 | c<<16
-    DevBuf<int32_t> nbOff, nbList; // per vertex: distinct neighbour vertices (sorted ids)
-    DevBuf<int4> vtx;              // per vertex header: {incOff, nbOff, nInc | nNb << 16, meshId | fixed << 31}
     int64_t nNb = 0;
     // tile streams of the colour sweep (sweep.cu; built by build_tile_streams)
     std::vector<int4> h_vtx2;          // per vertex: {recLocal | nRec << 16, nbLocal | nNb << 16, bits(A*sum|m0|^2), meshId | flags}
@@ -120,8 +115,6 @@ struct Scene {
     DevBuf<int2> nbw;
     DevBuf<TileDesc> tiles;
     int numSMs = 148;
-    bool legacySweep = false;          // round-1 kernel (k_solve_colour), kept while the tile sweep is being validated
-    int tileVOverride = 0;
     uint32_t sweepAttrSet = 0;         // kernel variants whose shared-memory attribute is set on this scene's device
     DevBuf<int32_t> sorted2orig, orig2sorted;
     DevBuf<MeshParamsDev> meshParams;
@@ -145,7 +138,7 @@ struct Scene {
     // CUDA graph of the colour loop of one substep (solve.cu: solve_iterations)
     cudaGraphExec_t iterGraphExec = nullptr;
     int iterGraphIters = -1, iterCalls = 0;
-    int solveLanes = 0;   // lanes per vertex of the colour sweep outside the fused-halo path: 0 = default (4), 4 or 8
+    int solveLanes = 0;   // gaia_b200_set_solver_lanes: accepted for compatibility, the sweep always uses kSweepLanes
     int64_t iterDelta[4] = {0, 0, 0, 0};
 
     // statistics / profiling
@@ -168,14 +161,14 @@ bool host_finalize(Scene& s);
 bool build_tile_streams(Scene& s, int tileV);
 
 // sweep.cu: the per-colour vertex solve over tiles (TMA-fed persistent blocks)
-cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv);
+cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv);
 cudaError_t sweep_upload(Scene& s);
 cudaError_t sweep_mark_halo_tiles(Scene& s, const int32_t* boundaryPrefixDev);
 
 // solve.cu
 cudaError_t device_upload(Scene& s);
 cudaError_t upload_deformers(Scene& s);
-void sync_mesh_params(Scene& s);
+cudaError_t sync_mesh_params(Scene& s);
 cudaError_t run_substeps(Scene& s, int nSubsteps);                 // one frame's worth of substeps
 cudaError_t run_iterations_only(Scene& s, int nIters);
 cudaError_t gather_to_host(Scene& s, const float4* devSorted, int64_t origBegin, int64_t count, float* outXYZ);

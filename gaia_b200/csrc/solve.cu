@@ -11,14 +11,8 @@
 //   updateVelocities / dampVelocities                  M/VBD/VBDPhysics.cpp:2486-2561
 //   Chebyshev accelerator (GPU-path feature)           M/VBD/VBDPhysics.cpp:3558-3574, VBDPhysicsCompute.cu:910-944
 //
-// Kernel design: the work is a sparse gather bounded by HBM, not a contraction — no tensor cores.
-//   * vertices are colour-sorted, so a colour is one contiguous range [vBegin,vEnd) of every SoA array;
-//   * each vertex is owned by a sub-warp of L lanes; lane l streams the incidence records l, l+L, ... of the vertex
-//     (two coalesced 16-byte loads per record), gathers the three neighbour positions (16-byte loads that hit L2:
-//     the position array of a 10M-tet mesh is 28 MB against 126 MB of L2) and accumulates the closed-form
-//     Neo-Hookean force / Hessian of SURVEY.md §8(a) "math restatement" (≈100 flop instead of the 9x9 contraction);
-//   * a butterfly shuffle reduces 10 partial sums; lane 0 adds inertia, boundary and contact terms, solves the 3x3
-//     block and writes the new position in place (safe: a colour only reads other colours' positions).
+// This file: the step schedule (initial step, deformers, colour loop, velocity update), the elementwise kernels and the
+// host <-> device transfers. The per-colour vertex solve itself lives in sweep.cu.
 #include "scene_impl.h"
 #include <algorithm>
 #include <cmath>
@@ -39,381 +33,6 @@ __device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a
 __device__ __forceinline__ float3 cross3(float3 a, float3 b) {
     return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
-
-// streaming (read-once) loads: keep them out of L1 so the gathered positions stay cached
-__device__ __forceinline__ int4 ld_stream(const int4* p) {
-    int4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ float4 ld_stream(const float4* p) {
-    float4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-    return r;
-}
-
-// IPC-style mollified friction (computeVertexFriction, VBDPhysics.cpp:2563-2592) for an axis-aligned tangent basis
-// T = [e_a, e_b]: adds force and the diagonal Hessian entries (a,a) and (b,b).
-__device__ __forceinline__ void boundary_friction(float mu, float lambda, float ua, float ub, float epsU, float& fa, float& fb, float& haa) {
-    const float uNorm = sqrtf(ua * ua + ub * ub);
-    fa = 0.f; fb = 0.f; haa = 0.f;
-    if (uNorm > 0.f) {
-        const float f1 = (uNorm > epsU) ? 1.f / uNorm : (-uNorm / epsU + 2.f) / epsU;
-        const float s = -mu * lambda * f1;
-        fa = s * ua; fb = s * ub;
-        haa = mu * lambda * f1;
-    }
-}
-
-__device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
-    uint32_t r;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
-    return r;
-}
-
-static const int kNbMax = 32;              // neighbour positions staged in shared memory per vertex (more spill to global gathers)
-static const int kNbStride = kNbMax + 1;   // +1 float4 of padding de-correlates the rows' banks
-
-__device__ __forceinline__ float4 lds128(uint32_t addr) {
-    float4 r;
-    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
-    return r;
-}
-
-// The vertex-level part of VBDStepWithCollision after the incident-tet sums are known: damping, inertia, world box +
-// friction, contacts, 3x3 solve, in-place update. Runs with one vertex per thread (all lanes busy).
-template <bool HAS_CONTACTS>
-__device__ __forceinline__ bool solve_tail(int s, float3 x, float4 ys, float miu, float lmbd, float dampH, float dampD,
-                                           float fx, float fy, float fz, float s1, float g00, float g01, float g02, float g11, float g12, float g22,
-                                           float4* pos, const float4* __restrict__ prev, const StepParamsDev& sp, int applyFriction,
-                                           const ContactView& cv, int32_t* errFlags, float4& xNew) {
-    // elastic force and Hessian: f = -(mu*fmu + lmbd*flm), H = mu*s1*I + lmbd*G
-    float F0 = -fx, F1 = -fy, F2 = -fz;
-    float hd = miu * s1;
-    float h00 = lmbd * g00 + hd, h01 = lmbd * g01, h02 = lmbd * g02, h11 = lmbd * g11 + hd, h12 = lmbd * g12, h22 = lmbd * g22 + hd;
-    const bool needPrev = (dampH != 0.f) | (dampD != 0.f);
-    float3 xp = make_float3(0.f, 0.f, 0.f);
-    bool havePrev = false;
-    if (needPrev) {
-        xp = f3(__ldg(prev + s)); havePrev = true;
-        // dampingH = (H_vol*gamma_h + mu*|m|^2*A*gamma_d I)/dt ; f -= dampingH*(x - x_prev); H += dampingH
-        const float idt = 1.f / sp.dt;
-        const float3 d = x - xp;
-        const float ch = lmbd * dampH * idt, cd = miu * s1 * dampD * idt;
-        const float d00 = ch * g00 + cd, d01 = ch * g01, d02 = ch * g02, d11 = ch * g11 + cd, d12 = ch * g12, d22 = ch * g22 + cd;
-        F0 -= d00 * d.x + d01 * d.y + d02 * d.z;
-        F1 -= d01 * d.x + d11 * d.y + d12 * d.z;
-        F2 -= d02 * d.x + d12 * d.y + d22 * d.z;
-        h00 += d00; h01 += d01; h02 += d02; h11 += d11; h12 += d12; h22 += d22;
-    }
-    // inertia
-    {
-        const float m = ys.w;
-        const float w = m * sp.dtSqrReciprocal;
-        F0 += (m * (ys.x - x.x)) * sp.dtSqrReciprocal;
-        F1 += (m * (ys.y - x.y)) * sp.dtSqrReciprocal;
-        F2 += (m * (ys.z - x.z)) * sp.dtSqrReciprocal;
-        h00 += w; h11 += w; h22 += w;
-    }
-    // world-box penalty + friction, per violated axis (CPU semantics)
-    if (sp.usePlaneGround) {
-        const float xs[3] = {x.x, x.y, x.z};
-        float Fb[3] = {0.f, 0.f, 0.f}, Hb[3] = {0.f, 0.f, 0.f};
-#pragma unroll
-        for (int d = 0; d < 3; d++) {
-            float depth = 0.f, sgn = 0.f;
-            if (xs[d] < sp.boundsMin[d]) { depth = sp.boundsMin[d] - xs[d]; sgn = 1.f; }
-            else if (xs[d] > sp.boundsMax[d]) { depth = xs[d] - sp.boundsMax[d]; sgn = -1.f; }
-            if (sgn != 0.f) {
-                Fb[d] += sgn * (depth * sp.kBoundary);
-                Hb[d] += sp.kBoundary;
-                if (applyFriction) {
-                    if (!havePrev) { xp = f3(__ldg(prev + s)); havePrev = true; }
-                    const float dx[3] = {x.x - xp.x, x.y - xp.y, x.z - xp.z};
-                    const int a = (d + 1) % 3, b2 = (d + 2) % 3;
-                    float fa, fb, haa;
-                    boundary_friction(sp.muBoundary, depth * sp.kBoundary, dx[a], dx[b2], sp.epsVBoundary * sp.dt, fa, fb, haa);
-                    Fb[a] += fa; Fb[b2] += fb; Hb[a] += haa; Hb[b2] += haa;
-                }
-            }
-        }
-        F0 += Fb[0]; F1 += Fb[1]; F2 += Fb[2];
-        h00 += Hb[0]; h11 += Hb[1]; h22 += Hb[2];
-    }
-    // vertex-face contacts: own contact with weight 1, contacts on faces this vertex belongs to with weight -bary
-    if (HAS_CONTACTS) {
-        const int own = __ldg(cv.contactOfVertex + s);
-        const int rb = __ldg(cv.relOff + s), re = __ldg(cv.relOff + s + 1);
-        for (int q = (own >= 0 ? -1 : 0); q < re - rb; q++) {
-            int slot; float bw;
-            if (q < 0) { slot = own; bw = 1.f; }
-            else {
-                const int2 r = __ldg(cv.rel + rb + q);
-                slot = r.x;
-                const float4 h1 = __ldg(cv.cH1 + slot);
-                bw = -(r.y == 0 ? h1.z : (r.y == 1 ? h1.w : __ldg(cv.cB2 + slot)));
-            }
-            const float4 cf = __ldg(cv.cF + slot);
-            if (cf.w > 0.f && bw != 0.f) {
-                const float4 c0 = __ldg(cv.cH0 + slot), c1 = __ldg(cv.cH1 + slot);
-                const float b2w = bw * bw;
-                F0 += cf.x * bw; F1 += cf.y * bw; F2 += cf.z * bw;
-                h00 += c0.x * b2w; h01 += c0.y * b2w; h02 += c0.z * b2w; h11 += c0.w * b2w; h12 += c1.x * b2w; h22 += c1.y * b2w;
-            }
-        }
-    }
-    // 3x3 solve (solve3x3_psd_stable) and in-place update
-    if (F0 * F0 + F1 * F1 + F2 * F2 > 1e-10f) {
-        const float i11 = h22 * h11 - h12 * h12;
-        const float i12 = -(h22 * h01 - h12 * h02);
-        const float i13 = h12 * h01 - h11 * h02;
-        const float det = h00 * i11 + h01 * i12 + h02 * i13;
-        float dx0, dx1, dx2, step;
-        if (fabsf(det) < 1e-5f * (fabsf(h00 * i11) + fabsf(h01 * i12) + fabsf(h02 * i13))) {
-            dx0 = F0; dx1 = F1; dx2 = F2; step = sp.stepSizeGD;
-            atomicAdd(errFlags + 1, 1);
-        } else {
-            const float deti = 1.f / det;
-            const float i22 = h22 * h00 - h02 * h02;
-            const float i23 = -(h12 * h00 - h01 * h02);
-            const float i33 = h11 * h00 - h01 * h01;
-            dx0 = deti * (i11 * F0 + i12 * F1 + i13 * F2);
-            dx1 = deti * (i12 * F0 + i22 * F1 + i23 * F2);
-            dx2 = deti * (i13 * F0 + i23 * F1 + i33 * F2);
-            step = sp.stepSize;
-        }
-        if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return false; }
-        xNew = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
-        pos[s] = xNew;
-        return true;
-    }
-    return false;
-}
-
-// Neighbour position gather. HALO launches read past L1 (ld.global.cg): ghost slots are written by the neighbours over
-// NVLink while the launch runs, and an L1 line fetched before the epoch was seen could hold the old value.
-#ifndef GAIA_GATHER_CG
-#define GAIA_GATHER_CG 0
-#endif
-template <bool HALO>
-__device__ __forceinline__ float4 ld_nb(const float4* p) { return (HALO || GAIA_GATHER_CG) ? __ldcg(p) : __ldg(p); }
-
-// Fused halo exchange, consumer side: wait until every neighbour partition has published `epoch` (its previous colour
-// launch, pushes included, is complete). One lane polls; 5 s without progress = a neighbour died (errFlags[4]).
-__device__ __forceinline__ void halo_wait(const HaloPeerTable* tab, uint32_t epoch, int nPeers, int32_t* errFlags) {
-    for (int p = 0; p < nPeers; p++) {
-        if (*(volatile int32_t*)(errFlags + 4)) return;
-        unsigned long long t0;
-        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
-        for (;;) {
-            uint32_t v;
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(tab->myFlag[p]) : "memory");
-            if ((int32_t)(v - epoch) >= 0) break;
-            unsigned long long t1;
-            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 5000000000ull) { atomicAdd(errFlags + 4, 1); return; }
-            __nanosleep(64);
-        }
-    }
-}
-
-// One block owns kBlock consecutive vertices of the colour and walks them in ROUNDS = L rounds of kBlock/L vertices:
-// in a round each vertex is served by a sub-warp of L lanes (incident-tet sums), the sums are parked in shared memory,
-// and after the last round every thread finishes ONE vertex (solve_tail) — so the scalar tail runs at full SIMT width.
-//
-// HALO (multi-GPU partitions): the exchange of this colour's boundary positions is part of the launch.
-// Epochs count colour launches: launch number o of a batch (hv.epochOffset = o) first publishes "everything before me
-// is complete" (base + o, base = ctl[0]) to the neighbours - stream order makes the previous launch's peer stores
-// visible first - and a block that holds boundary vertices (bit 30 of the vertex header; found through a prefix count
-// over the block's vertex range) waits until every neighbour has published the same epoch, gathers its neighbour
-// positions past L1 (ghost slots are written by peers over NVLink while the launch runs) and after its solve stores the
-// new positions straight into the neighbours' ghost slots. Blocks without boundary vertices never wait, so the NVLink
-// latency hides behind them; nothing is added to their critical path (no barrier, no atomic).
-template <int L, bool HAS_CONTACTS, int PF, int ROUNDS, bool GHOST>
-__device__ __forceinline__ void
-accumulate_block(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
-               const int4* __restrict__ vtx, const float4* __restrict__ incW, const uint32_t* __restrict__ incIdx,
-               const int32_t* __restrict__ nbList, const MeshParamsDev* __restrict__ mp,
-               const StepParamsDev& sp, int applyFriction, const ContactView& cv, int32_t* errFlags, const HaloView& hv) {
-    constexpr int VPR = kBlock / L;        // vertices per round
-    constexpr int VPB = VPR * ROUNDS;      // vertices per block
-    extern __shared__ float4 smem4[];
-    float4* smNb = smem4;                                   // [VPR][kNbStride] neighbour positions relative to the owner
-    float* acc = (float*)(smem4 + VPR * kNbStride);         // [10][VPB] incident-tet sums
-    const int lane = threadIdx.x & (L - 1);
-    const int sub = threadIdx.x / L;
-    const uint32_t rowAddr = (uint32_t)__cvta_generic_to_shared(smNb + sub * kNbStride);
-    float4* myNb = smNb + sub * kNbStride;
-    const int blockBase = vBegin + blockIdx.x * VPB;
-    const float4* posRO = pos;   // neighbour gathers only touch other colours: read-only for this launch
-    bool waited = false;         // GHOST: the block has seen the neighbours' epoch
-
-#pragma unroll 1
-    for (int r = 0; r < ROUNDS; r++) {
-        const int slot = r * VPR + sub;
-        const int s = blockBase + slot;
-        const bool inRange = s < vEnd;
-        // ---- level 0 of the dependency chain: everything that only needs s
-        int4 va = make_int4(0, 0, 0, (int)0x80000000);      // {incOff, nbOff, nInc | nNb << 16, meshId | fixed << 31}
-        float4 xs = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (inRange) { va = __ldg(vtx + s); xs = pos[s]; }
-        bool active = inRange && va.w >= 0;
-        float miu = 0.f, lmbd = 0.f, aConst = 0.f;
-        if (active) {
-            const MeshParamsDev* P = mp + (va.w & 0x00FFFFFF);
-            active = P->activeSolve != 0;
-            miu = P->miu; lmbd = P->lmbd; aConst = P->a;
-        }
-        float fx = 0.f, fy = 0.f, fz = 0.f, s1 = 0.f, g00 = 0.f, g01 = 0.f, g02 = 0.f, g11 = 0.f, g12 = 0.f, g22 = 0.f;
-        const float3 x = f3(xs);
-        const int e = va.x + (active ? (va.z & 0xFFFF) : 0), nb0 = va.y;
-        const int nnbAll = active ? (va.z >> 16) : 0;
-
-        // ---- level 1: first incidence records and the neighbour ids (both only depend on va)
-        int j = va.x + lane;
-        float4 W = make_float4(0.f, 0.f, 0.f, 0.f), W1 = W, W2 = W;
-        uint32_t I = 0, I1 = 0, I2 = 0;
-        if (j < e) { W = ld_stream(incW + j); I = ld_stream(incIdx + j); }
-        if (PF >= 1 && j + L < e) { W1 = ld_stream(incW + j + L); I1 = ld_stream(incIdx + j + L); }
-        if (PF >= 2 && j + 2 * L < e) { W2 = ld_stream(incW + j + 2 * L); I2 = ld_stream(incIdx + j + 2 * L); }
-        {
-            const int nnb = min(nnbAll, kNbMax);
-            int idx[kNbMax / L];
-#pragma unroll
-            for (int q = 0; q < kNbMax / L; q++) { const int i = lane + q * L; idx[q] = (i < nnb) ? (int)ld_stream((const uint32_t*)nbList + nb0 + i) : -1; }
-            // ---- level 2: stage the distinct neighbour positions once (each is used by ~5 incident tets); L2 hits
-            if (GHOST) {
-                if (!waited) {
-                    if (threadIdx.x == 0 && !(hv.debug & 1)) halo_wait(hv.tab, *(volatile const uint32_t*)hv.ctl + (uint32_t)hv.epochOffset, hv.nPeers, errFlags);
-                    __syncthreads();
-                    waited = true;
-                }
-#pragma unroll
-                for (int q = 0; q < kNbMax / L; q++)
-                    if (idx[q] >= 0) {
-                        const float4 p = __ldcg(posRO + idx[q]);
-                        myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
-                    }
-            } else {
-#pragma unroll
-                for (int q = 0; q < kNbMax / L; q++)
-                    if (idx[q] >= 0) {
-                        const float4 p = __ldg(posRO + idx[q]);
-                        myNb[lane + q * L] = make_float4(p.x - x.x, p.y - x.y, p.z - x.z, 0.f);
-                    }
-            }
-        }
-        __syncwarp();
-        const float lm6 = lmbd * (-1.f / 6.f);
-        for (; j < e; j += L) {
-            // software pipeline: the record PF+1 iterations ahead is requested before this one is consumed
-            float4 Wn = W; uint32_t In = 0;
-            const int jn = j + (PF + 1) * L;
-            if (jn < e) { Wn = ld_stream(incW + jn); In = ld_stream(incIdx + jn); }
-            float3 pa, pb, pc;
-            if (nnbAll <= kNbMax) {
-                pa = f3(lds128(rowAddr + ((I & 0xFFu) << 4)));
-                pb = f3(lds128(rowAddr + ((I >> 4) & 0xFF0u)));
-                pc = f3(lds128(rowAddr + ((I >> 12) & 0xFF0u)));
-            } else {
-                pa = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + (I & 255)))) - x;
-                pb = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + ((I >> 8) & 255)))) - x;
-                pc = f3(ld_nb<GHOST>(posRO + __ldg(nbList + nb0 + ((I >> 16) & 255)))) - x;
-            }
-            // n = cof(Ds')(1,1,1) = b x c + c x a + a x b = (b-a) x (c-a);  det(Ds') = a . n;  A*g = -n/6
-            // (explicit _rn intrinsics: the contraction pattern is fixed, so every instantiation of this body - any L, PF,
-            // ROUNDS, with or without the ghost path - produces the same bits)
-            const float3 u = pb - pa, v = pc - pa;
-            float3 n;
-            n.x = __fmaf_rn(u.y, v.z, -__fmul_rn(u.z, v.y));
-            n.y = __fmaf_rn(u.z, v.x, -__fmul_rn(u.x, v.z));
-            n.z = __fmaf_rn(u.x, v.y, -__fmul_rn(u.y, v.x));
-            const float detDs = __fmaf_rn(pa.z, n.z, __fmaf_rn(pa.y, n.y, __fmul_rn(pa.x, n.x)));
-            const float k = __fmaf_rn(detDs, W.w, -aConst);            // det F - a,  det F = det(Ds') det(B')
-            const float c6 = __fmul_rn(lm6, k);
-            // A*(mu F m0 + lmbd k g)
-            fx = __fmaf_rn(c6, n.x, __fmaf_rn(miu, __fmaf_rn(W.z, pc.x, __fmaf_rn(W.y, pb.x, __fmul_rn(W.x, pa.x))), fx));
-            fy = __fmaf_rn(c6, n.y, __fmaf_rn(miu, __fmaf_rn(W.z, pc.y, __fmaf_rn(W.y, pb.y, __fmul_rn(W.x, pa.y))), fy));
-            fz = __fmaf_rn(c6, n.z, __fmaf_rn(miu, __fmaf_rn(W.z, pc.z, __fmaf_rn(W.y, pb.z, __fmul_rn(W.x, pa.z))), fz));
-            s1 = __fsub_rn(s1, __fadd_rn(__fadd_rn(W.x, W.y), W.z));   // A*|m0|^2
-            const float nx = __fmul_rn(W.w, n.x), ny = __fmul_rn(W.w, n.y), nz = __fmul_rn(W.w, n.z);   // 6 A g g^T = det(B') n n^T
-            g00 = __fmaf_rn(nx, n.x, g00); g01 = __fmaf_rn(nx, n.y, g01); g02 = __fmaf_rn(nx, n.z, g02);
-            g11 = __fmaf_rn(ny, n.y, g11); g12 = __fmaf_rn(ny, n.z, g12); g22 = __fmaf_rn(nz, n.z, g22);
-            if (PF == 0) { W = Wn; I = In; }
-            else if (PF == 1) { W = W1; I = I1; W1 = Wn; I1 = In; }
-            else { W = W1; I = I1; W1 = W2; I1 = I2; W2 = Wn; I2 = In; }
-        }
-#pragma unroll
-        for (int o = L / 2; o > 0; o >>= 1) {
-            fx += __shfl_xor_sync(0xffffffffu, fx, o); fy += __shfl_xor_sync(0xffffffffu, fy, o); fz += __shfl_xor_sync(0xffffffffu, fz, o);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-            g00 += __shfl_xor_sync(0xffffffffu, g00, o); g01 += __shfl_xor_sync(0xffffffffu, g01, o); g02 += __shfl_xor_sync(0xffffffffu, g02, o);
-            g11 += __shfl_xor_sync(0xffffffffu, g11, o); g12 += __shfl_xor_sync(0xffffffffu, g12, o); g22 += __shfl_xor_sync(0xffffffffu, g22, o);
-        }
-        if (lane == 0) {
-            acc[0 * VPB + slot] = fx; acc[1 * VPB + slot] = fy; acc[2 * VPB + slot] = fz; acc[3 * VPB + slot] = s1;
-            acc[4 * VPB + slot] = g00; acc[5 * VPB + slot] = g01; acc[6 * VPB + slot] = g02;
-            acc[7 * VPB + slot] = g11; acc[8 * VPB + slot] = g12; acc[9 * VPB + slot] = g22;
-        }
-        __syncwarp();      // the row of smNb is rewritten by the next round
-    }
-}
-
-template <int L, bool HAS_CONTACTS, int PF, int ROUNDS, bool HALO>
-__global__ void __launch_bounds__(kBlock, 4)
-k_solve_colour(int vBegin, int vEnd, float4* pos, const float4* __restrict__ prev, const float4* __restrict__ inertia,
-               const int4* __restrict__ vtx, const float4* __restrict__ incW, const uint32_t* __restrict__ incIdx,
-               const int32_t* __restrict__ nbList, const MeshParamsDev* __restrict__ mp,
-               StepParamsDev sp, int applyFriction, ContactView cv, int32_t* errFlags, HaloView hv) {
-    constexpr int VPR = kBlock / L;
-    constexpr int VPB = VPR * ROUNDS;
-    extern __shared__ float4 smem4[];
-    float* acc = (float*)(smem4 + VPR * kNbStride);         // [10][VPB] incident-tet sums
-    const int blockBase = vBegin + blockIdx.x * VPB;
-    bool ghostBlock = false;
-    if (HALO) {
-        if (blockIdx.x == 0 && threadIdx.x < hv.nPeers) {
-            const uint32_t done = *(volatile const uint32_t*)hv.ctl + (uint32_t)hv.epochOffset;
-            __threadfence_system();
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(hv.tab->peerFlag[threadIdx.x]), "r"(done) : "memory");
-        }
-        // a block that holds boundary vertices takes the ghost-safe copy of the accumulation (wait + gathers past L1);
-        // all other blocks run exactly the single-GPU code. Both copies use the same pinned arithmetic.
-        ghostBlock = __ldg(hv.boundaryPrefix + min(blockBase + VPB, vEnd)) != __ldg(hv.boundaryPrefix + min(blockBase, vEnd));
-    }
-    if (HALO && ghostBlock) accumulate_block<L, HAS_CONTACTS, PF, ROUNDS, true>(vBegin, vEnd, pos, prev, inertia, vtx, incW, incIdx, nbList, mp, sp, applyFriction, cv, errFlags, hv);
-    else accumulate_block<L, HAS_CONTACTS, PF, ROUNDS, false>(vBegin, vEnd, pos, prev, inertia, vtx, incW, incIdx, nbList, mp, sp, applyFriction, cv, errFlags, hv);
-    bool pushed = false;         // HALO: this thread stored into a neighbour's memory
-    __syncthreads();
-    // ---- transposed tail: thread t finishes vertex blockBase + t
-    for (int slot = threadIdx.x; slot < VPB; slot += kBlock) {
-        const int s = blockBase + slot;
-        if (s >= vEnd) continue;
-        const int4 va = __ldg(vtx + s);
-        if (va.w < 0) continue;
-        const MeshParamsDev* P = mp + (va.w & 0x00FFFFFF);
-        if (!P->activeSolve) continue;
-        const float4 xs = pos[s];
-        const float4 ys = __ldg(inertia + s);
-        float4 xNew;
-        const bool wrote = solve_tail<HAS_CONTACTS>(s, f3(xs), ys, P->miu, P->lmbd, P->dampH, P->dampD,
-                                 acc[0 * VPB + slot], acc[1 * VPB + slot], acc[2 * VPB + slot], acc[3 * VPB + slot],
-                                 acc[4 * VPB + slot] * (1.f / 6.f), acc[5 * VPB + slot] * (1.f / 6.f), acc[6 * VPB + slot] * (1.f / 6.f),
-                                 acc[7 * VPB + slot] * (1.f / 6.f), acc[8 * VPB + slot] * (1.f / 6.f), acc[9 * VPB + slot] * (1.f / 6.f),
-                                 pos, prev, sp, applyFriction, cv, errFlags, xNew);
-        if (HALO && wrote && (va.w & kHaloBoundaryBit) && !(hv.debug & 2)) {
-            const int si = __ldg(hv.sendIdx + s);
-            for (int q = 0; q < (si & 15); q++) {
-                const int2 en = __ldg(hv.sendEnt + (si >> 4) + q);
-                hv.tab->peerPos[en.x][en.y] = xNew;
-            }
-            pushed = true;
-        }
-    }
-    // the next launch of the stream publishes the epoch; the stores must be performed system-wide before it does
-    if (HALO && pushed) __threadfence_system();
-}
-
 
 // End of a batch of fused colour launches: publish the last epoch and advance the base.
 __global__ void k_halo_advance(HaloView hv, int n) {
@@ -606,14 +225,15 @@ static MeshParamsDev make_mesh_params(const HostMesh& m) {
     return p;
 }
 
-void sync_mesh_params(Scene& s) {
-    if (!s.meshParamsDirty) return;
+cudaError_t sync_mesh_params(Scene& s) {
+    if (!s.meshParamsDirty) return cudaSuccess;
     s.h_meshParams.resize(s.meshes.size());
     for (size_t i = 0; i < s.meshes.size(); i++) s.h_meshParams[i] = make_mesh_params(s.meshes[i]);
-    cudaMemcpyAsync(s.meshParams.p, s.h_meshParams.data(), s.h_meshParams.size() * sizeof(MeshParamsDev), cudaMemcpyHostToDevice, s.stream);
-    cudaStreamSynchronize(s.stream);
+    CK(cudaMemcpyAsync(s.meshParams.p, s.h_meshParams.data(), s.h_meshParams.size() * sizeof(MeshParamsDev), cudaMemcpyHostToDevice, s.stream));
+    CK(cudaStreamSynchronize(s.stream));
     s.meshParamsDirty = false;
     if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }   // per-iteration accounting changed
+    return cudaSuccess;
 }
 
 cudaError_t device_upload(Scene& s) {
@@ -621,8 +241,7 @@ cudaError_t device_upload(Scene& s) {
     CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&s.evA)); CK(cudaEventCreate(&s.evB)); CK(cudaEventCreate(&s.evP0)); CK(cudaEventCreate(&s.evP1));
     CK(s.pos.alloc(N + 1)); CK(s.prev.alloc(N + 1)); CK(s.inertia.alloc(N + 1)); CK(s.vel.alloc(N + 1));
-    CK(s.mass.alloc(N)); CK(s.info.alloc(N)); CK(s.incOff.alloc(N + 1));
-    CK(s.incW.alloc(s.nInc)); CK(s.incIdx.alloc(s.nInc)); CK(s.nbOff.alloc(N + 1)); CK(s.nbList.alloc(s.nNb)); CK(s.vtx.alloc(N));
+    CK(s.mass.alloc(N)); CK(s.info.alloc(N));
     CK(s.sorted2orig.alloc(N)); CK(s.orig2sorted.alloc(N));
     CK(s.meshParams.alloc(s.meshes.size())); CK(s.errFlags.alloc(8));
     CK(s.ioStage.alloc((size_t)(3 * N + 3) / 4 + 1));
@@ -660,15 +279,6 @@ cudaError_t device_upload(Scene& s) {
     if (needAccel) CK(cudaMemsetAsync(s.accel.p, 0, (N + 1) * sizeof(float4), s.stream));
     CK(cudaMemcpyAsync(s.mass.p, hmass.data(), N * sizeof(float), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.info.p, hinfo.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.incOff.p, s.h_incOff.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.incW.p, s.h_incW.data(), s.nInc * sizeof(float4), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.incIdx.p, s.h_incIdx.data(), s.nInc * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
-    std::vector<int4> hvtx(N);
-    for (int64_t i = 0; i < N; i++)
-        hvtx[i] = make_int4(s.h_incOff[i], s.h_nbOff[i], (s.h_incOff[i + 1] - s.h_incOff[i]) | ((s.h_nbOff[i + 1] - s.h_nbOff[i]) << 16), hinfo[i]);
-    CK(cudaMemcpyAsync(s.vtx.p, hvtx.data(), N * sizeof(int4), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.nbOff.p, s.h_nbOff.data(), (N + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
-    CK(cudaMemcpyAsync(s.nbList.p, s.h_nbList.data(), s.nNb * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.sorted2orig.p, s.sortedToOrig.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.orig2sorted.p, o2s.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream));
     CK(cudaStreamSynchronize(s.stream));
@@ -678,11 +288,9 @@ cudaError_t device_upload(Scene& s) {
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0) s.numSMs = sms;
         int64_t largest = 0;
         for (size_t g = 0; g + 1 < s.groupStart.size(); g++) largest = std::max<int64_t>(largest, s.groupStart[g + 1] - s.groupStart[g]);
-        if (const char* e = getenv("GAIA_B200_LEGACY_SWEEP")) s.legacySweep = atoi(e) != 0;      // (validation of the tile sweep only)
-        if (const char* e = getenv("GAIA_B200_TILE_V")) s.tileVOverride = atoi(e);
         int tileV = kTileV;
         while (tileV > 8 && largest < (int64_t)s.numSMs * 3 * tileV) tileV >>= 1;
-        if (!build_tile_streams(s, s.tileVOverride > 0 ? s.tileVOverride : tileV)) return cudaErrorInvalidValue;
+        if (!build_tile_streams(s, tileV)) return cudaErrorInvalidValue;
         CK(sweep_upload(s));
     }
     std::vector<uint32_t>().swap(s.h_incIdx);
@@ -698,77 +306,19 @@ cudaError_t device_upload(Scene& s) {
     s.pinnedIOBytes = (size_t)(3 * N + 16) * sizeof(float);
     CK(cudaMallocHost((void**)&s.pinnedIO, s.pinnedIOBytes));
     s.meshParamsDirty = true;
-    sync_mesh_params(s);
-    return cudaSuccess;
+    return sync_mesh_params(s);
 }
 
-
-static int g_lanes = 4;     // sub-warp width of the colour solve (GAIA_B200_LANES = 2|4|8)
-static int g_variant = 1;   // prefetch depth of the incidence stream (GAIA_B200_VARIANT = 0|1|2)
-
-template <int L, bool HC, int PF, int ROUNDS, bool HALO = false>
-static void launch_one(Scene& s, int vb, int ve, int applyFriction, const ContactView& cv, const HaloView* hvp = nullptr) {
-    HaloView hv;
-    if (hvp) hv = *hvp; else std::memset(&hv, 0, sizeof(hv));
-    const int n = ve - vb;
-    const int vpb = (kBlock / L) * ROUNDS;
-    const size_t smem = (size_t)(kBlock / L) * kNbStride * sizeof(float4) + (size_t)10 * vpb * sizeof(float);
-    static bool attrSet = false;
-    if (!attrSet) { cudaFuncSetAttribute(k_solve_colour<L, HC, PF, ROUNDS, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attrSet = true; }
-    k_solve_colour<L, HC, PF, ROUNDS, HALO><<<nblk(n, vpb), kBlock, smem, s.stream>>>(
-        vb, ve, s.pos.p, s.prev.p, s.inertia.p, s.vtx.p, s.incW.p, s.incIdx.p, s.nbList.p,
-        s.meshParams.p, s.stepParams, applyFriction, cv, s.errFlags.p, hv);
-}
-
-template <bool HC>
-static void launch_solve(Scene& s, int L, int variant, int vb, int ve, int applyFriction, const ContactView& cv, const HaloView* hv = nullptr) {
-    // rounds per block: big colours walk L rounds per block (full-width tail); smaller ones fewer rounds, so that the grid
-    // still fills the 148 SMs x 4 resident blocks for a few waves
-    const int64_t n = ve - vb;
-    const int rounds = n >= (int64_t)148 * 8 * kBlock ? L : (n >= (int64_t)148 * 4 * kBlock ? 2 : 1);
-    if (hv) {   // fused halo exchange: the default shape only (4 lanes, prefetch depth 1)
-        const int r4 = n >= (int64_t)148 * 8 * kBlock ? 4 : (n >= (int64_t)148 * 4 * kBlock ? 2 : 1);
-        if (r4 == 4) launch_one<4, HC, 1, 4, true>(s, vb, ve, applyFriction, cv, hv);
-        else if (r4 == 2) launch_one<4, HC, 1, 2, true>(s, vb, ve, applyFriction, cv, hv);
-        else launch_one<4, HC, 1, 1, true>(s, vb, ve, applyFriction, cv, hv);
-        return;
-    }
-#define BYVAR(LL) if (rounds == LL) { if (variant == 0) launch_one<LL, HC, 0, LL>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, LL>(s, vb, ve, applyFriction, cv); } \
-                  else if (rounds == 2) { if (variant == 0) launch_one<LL, HC, 0, 2>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 2>(s, vb, ve, applyFriction, cv); } \
-                  else { if (variant == 0) launch_one<LL, HC, 0, 1>(s, vb, ve, applyFriction, cv); else launch_one<LL, HC, 1, 1>(s, vb, ve, applyFriction, cv); }
-    switch (L) {
-        case 8: BYVAR(8); break;
-        default: BYVAR(4); break;
-    }
-#undef BYVAR
-}
 
 static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD, bool captured = false) {
-    static bool envRead = false, lanesFromEnv = false;
-    if (!envRead) {
-        const char* e = getenv("GAIA_B200_LANES"); if (e) { g_lanes = atoi(e); lanesFromEnv = true; }
-        e = getenv("GAIA_B200_VARIANT"); if (e) g_variant = atoi(e);
-        envRead = true;
-    }
     const int G = (int)s.groupStart.size() - 1;
     const int N = (int)s.nVerts;
     const bool halo = halo_active(s);
-    static int fusedHalo = -1;
-    if (fusedHalo < 0) { const char* e = getenv("GAIA_B200_HALO_FUSED"); fusedHalo = e ? atoi(e) : 1; }
     HaloView hv;
+    std::memset(&hv, 0, sizeof(hv));
     // (the accelerator needs full refreshes; with contacts the per-colour pre-pass reads ghost positions BEFORE the sweep,
     //  so the exchange of the previous colour must be complete when it starts: the separate push + wait launch is used)
-    const bool fused = halo && fusedHalo && !s.phys.useAccelerator && !s.cs && halo_view(s, hv);
-    static int haloDebug = -1;      // timing experiments only: 1 = do not wait, 2 = do not store to peers (results are wrong)
-    if (haloDebug < 0) { const char* e = getenv("GAIA_B200_HALO_DEBUG"); haloDebug = e ? atoi(e) : 0; }
-    if (fused) hv.debug = haloDebug;
-    static uint32_t* dbgCtl = nullptr;
-    bool forceHalo = false;
-    if (!halo && getenv("GAIA_B200_FORCE_HALO_KERNEL")) {      // single-GPU timing of the HALO kernel variant (no peers)
-        static int32_t* dbgPrefix = nullptr;
-        if (!dbgCtl) { cudaMalloc((void**)&dbgCtl, 16); cudaMemset(dbgCtl, 0, 16); cudaMalloc((void**)&dbgPrefix, (N + 1) * 4); cudaMemset(dbgPrefix, 0, (N + 1) * 4); }
-        std::memset(&hv, 0, sizeof(hv)); hv.ctl = dbgCtl; hv.boundaryPrefix = dbgPrefix; forceHalo = true;
-    }
+    const bool fused = halo && !s.phys.useAccelerator && !s.cs && halo_view(s, hv);
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
     // (captured: the contact variant runs every substep, with device-sized pre-passes; empty tables when nothing touches)
@@ -807,13 +357,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
                 cudaEventRecord(pe0, s.stream);
             }
             hv.epochOffset = it * G + g;
-            if (ve > vb && !s.legacySweep) {
-                CK(sweep_launch(s, g, s.solveLanes == 8 ? 8 : 4, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
-            } else if (ve > vb) {
-                const int lanes = (s.solveLanes && !lanesFromEnv) ? s.solveLanes : g_lanes;
-                if (hasContacts) launch_solve<true>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
-                else launch_solve<false>(s, lanes, g_variant, vb, ve, applyFriction, cv, (fused || forceHalo) ? &hv : nullptr);
-            }
+            if (ve > vb) CK(sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
             if (s.profiling) cudaEventRecord(pe1, s.stream);
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
@@ -856,12 +400,10 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
 // graph and replayed. With the collision pipeline on, the contact pre-passes are launched over the capacity of the contact
 // list and read this substep's counts on the device (collision_graphable: small scenes only).
 static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediateCD) {
-    static int useGraphs = -1;
-    if (useGraphs < 0) { const char* e = getenv("GAIA_B200_GRAPH"); useGraphs = e ? atoi(e) : 1; }
     const bool withContacts = s.cs != nullptr;
     const bool contactsOk = !withContacts || (collision_graphable(s) && !halo_active(s) && !s.phys.useAccelerator &&
                                               !(allowIntermediateCD && s.phys.intermediateCollisionIterations > 0));
-    const bool graphable = useGraphs && !s.profiling && contactsOk && s.iterCalls > 0 && nIters > 0;
+    const bool graphable = !s.profiling && contactsOk && s.iterCalls > 0 && nIters > 0;
     s.iterCalls++;
     if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD);
     if (!s.iterGraphExec || s.iterGraphIters != nIters) {
@@ -973,7 +515,7 @@ static cudaError_t timed_phase(Scene& s, double& acc, F&& fn) {
 }
 
 cudaError_t run_substeps(Scene& s, int nSubsteps) {
-    sync_mesh_params(s);
+    CK(sync_mesh_params(s));
     const int N = (int)s.nVerts;
     for (s.substep = 0; s.substep < nSubsteps; s.substep++) {
         s.curTime += s.dt;
@@ -999,7 +541,7 @@ cudaError_t run_substeps(Scene& s, int nSubsteps) {
 }
 
 cudaError_t run_iterations_only(Scene& s, int nIters) {
-    sync_mesh_params(s);
+    CK(sync_mesh_params(s));
     s.substep = 0;
     s.curTime += s.dt;
     CK(collision_dcd(s, false));

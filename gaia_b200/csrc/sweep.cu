@@ -576,7 +576,7 @@ static cudaError_t launch_tiles(Scene& s, const SweepArgs& a) {
     return cudaGetLastError();
 }
 
-cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv) {
+cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv) {
     SweepArgs a;
     std::memset(&a, 0, sizeof(a));
     a.tileBegin = s.groupTileStart[group]; a.tileEnd = s.groupTileStart[group + 1];
@@ -588,7 +588,6 @@ cudaError_t sweep_launch(Scene& s, int group, int lanes, int applyFriction, bool
     a.allActive = 1;
     for (auto& m : s.meshes) if (!m.activeForMaterialSolve) a.allActive = 0;
     if (hv) a.hv = *hv;
-    (void)lanes;      // the record order is laid out for kSweepLanes lanes per vertex
     if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true>(s, a) : launch_tiles<kSweepLanes, false, true>(s, a);
     return hasContacts ? launch_tiles<kSweepLanes, true, false>(s, a) : launch_tiles<kSweepLanes, false, false>(s, a);
 }

@@ -28,7 +28,8 @@ def workload_twist_beam(nx=472, ny=60, nz=60, h=0.02, collisions=False):
     cy, cz = 1.0 + 0.5 * ny * h, 0.5 * nz * h
     deformers = [("rotator", left, (0.0, cy, cz), (1.0, 0.0, 0.0), np.pi / 4, -1.0),
                  ("rotator", right, (0.0, cy, cz), (1.0, 0.0, 0.0), -np.pi / 4, -1.0)]
-    name = f"twist_beam {nx}x{ny}x{nz} cells ({len(tets)} tets, {len(verts)} verts), 5 substeps x 20 iters, 4 colours"
+    name = (f"twist_beam {nx}x{ny}x{nz} cells ({len(tets)} tets, {len(verts)} verts), 5 substeps x 20 iters, 4 colours, "
+            + ("DCD on (every substep + every 5 iterations), CCD off" if collisions else "collision detection off"))
     return dict(name=name, meshes=[(verts, tets, obj, colors, np.zeros(0, np.int32))], phys=phys, col=col, deformers=deformers)
 
 
@@ -120,8 +121,11 @@ def build_scene(cls, wl, **kw):
 
 
 WORKLOADS = {
-    "twist_beam_10m": lambda: workload_twist_beam(472, 60, 60),
-    "twist_beam_1m": lambda: workload_twist_beam(59, 60, 60),
+    # SURVEY.md §8(d) cfg 4 as written: DCD on, CCD off, intermediateCollisionIterations 5 (the *_nodcd variants: detection off)
+    "twist_beam_10m": lambda: workload_twist_beam(472, 60, 60, collisions=True),
+    "twist_beam_10m_nodcd": lambda: workload_twist_beam(472, 60, 60),
+    "twist_beam_1m": lambda: workload_twist_beam(59, 60, 60, collisions=True),
+    "twist_beam_1m_nodcd": lambda: workload_twist_beam(59, 60, 60),
     "twist_beam_small": lambda: workload_twist_beam(24, 12, 12),
     "drop_pile_32": lambda: workload_drop_pile(32),
     "drop_pile_8": lambda: workload_drop_pile(8, grid=(2, 2), preroll=30),

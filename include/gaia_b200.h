@@ -301,11 +301,15 @@ int gaia_b200_reset_stats(gaia_handle* h);
  * events on the launching stream when profiling is enabled */
 int gaia_b200_set_profiling(gaia_handle* h, int enabled);
 void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that time with their own events */
-/* Tuning: sub-warp lanes per vertex of the colour sweep (0 = default 4; 8 shortens the per-vertex chain and wins ~8 % when
- * colours are small, < ~64 k vertices). The lane count fixes the association of the per-vertex sums: runs that must be
- * bit-identical to each other (a sharded run and its single-GPU reference) have to use the same value, which is why the
- * library never picks it from a rank's local sizes. The fused-halo sweep of a partitioned mesh always uses 4. */
+/* Kept for round-1 callers: the colour sweep always runs 4 lanes per vertex (the lane count fixes the record order and the
+ * association of the per-vertex sums, so it is a property of the layout built at finalize, not a run-time switch).
+ * Accepts 0, 4 or 8 and has no effect. */
 int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
+/* Bytes of the solver's HBM layout, for the bench's "inputs vs L2" note and for capacity planning:
+ * out[0] per-tet record stream, out[1] per-neighbour entry stream, out[2] per-vertex state read or written by one iteration
+ * (headers, positions, inertia, previous positions), out[3] tile table; out[4] = shared-memory position reads per
+ * iteration (3 per strip restart, 1 per strip step), out[5] = incidences (vertex, tet) per iteration. */
+int gaia_b200_get_layout_bytes(gaia_handle* h, int64_t out[6]);
 
 /* Vertex graph colouring (host code; no device needed) -------------------------
  * The reference colours its meshes with an offline tool (S/GraphColoring/GraphColoring.cpp: `-v -a greedy -b -r ratio`;

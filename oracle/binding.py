@@ -14,12 +14,35 @@ _lib = None
 _ref = None
 
 
+FAST_LIB = os.path.join(_HERE, "liboracle_fast.so")
+_use_fast = False
+
+
+def use_speed_build():
+    """bench.py's CPU arm: load the -O3 / AVX2 / FMA build of the same sources (oracle/Makefile: liboracle_fast.so) instead of
+    the parity build. Must be called before the first scene is created; returns False when that build is absent or the host
+    CPU lacks AVX2 + FMA (the parity build is used then)."""
+    global _use_fast
+    if _lib is not None:
+        return _use_fast
+    ok = os.path.exists(FAST_LIB)
+    try:
+        with open("/proc/cpuinfo") as f:
+            flags = f.read()
+        ok = ok and (" avx2" in flags and " fma" in flags)
+    except OSError:
+        ok = False
+    _use_fast = ok
+    return ok
+
+
 def load_oracle():
     global _lib
     if _lib is None:
-        if not os.path.exists(ORACLE_LIB):
-            raise RuntimeError(f"{ORACLE_LIB} not built (make -C oracle)")
-        lib = C.CDLL(ORACLE_LIB)
+        path = FAST_LIB if _use_fast else ORACLE_LIB
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} not built (make -C oracle)")
+        lib = C.CDLL(path)
         lib.oracle_create.argtypes = [C.POINTER(PhysicsParams), C.POINTER(CollisionParams), C.c_int]
         lib.oracle_create.restype = C.c_void_p
         lib.oracle_destroy.argtypes = [C.c_void_p]; lib.oracle_destroy.restype = None

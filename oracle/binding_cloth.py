@@ -6,7 +6,7 @@ import numpy as np
 
 from gaia_b200.capi import _f32, _fp
 from gaia_b200.cloth import ClothPhysicsParams, ClothSceneBase, bind_cloth_api, default_cloth_physics_params
-from .binding import load_oracle
+from .binding import load_oracle, use_speed_build  # noqa: F401
 
 _bound = False
 

@@ -166,30 +166,41 @@ def test_config2_miniature_integer_surfaces_and_trajectory():
     """teapot + bunny + octopus + armadillo (S01 scales, shipped colourings, S01 material / friction / contact stiffness)
     stacked with a small overlap: DCD + CCD contact sets, LBVH leaf orders, per-group active lists and face-side relations
     bit-exact on identical states, at the start and on the GPU's own state after 20, 30 and 40 frames (the pile toppling,
-    ~150 contacts). Trajectory: the stack is chaotic once the bodies start to topple - perturbing the ORACLE's initial
-    positions by 1e-7 moves its own trajectory by 1.7e-5 at frame 10, 4.8e-5 at frame 20 and 6e-2 at frame 30 - so the
-    free-running comparison covers the first 20 frames (stated tolerance 1e-3 absolute, 0.03 % of the ~3-unit models) and
-    each later 10-frame segment restarts from the GPU's state (same tolerance per segment)."""
+    60-160 contacts), and ONE iteration from each of those states within the 1e-5 per-vertex bar (contact forces, friction
+    and relations live). Trajectory: the free-running comparison covers the first 20 frames (stated tolerance 1e-3 absolute,
+    0.03 % of the ~3-unit models). Beyond that the pile is chaotic - measured on the ORACLE alone (CPU): a 1e-6 perturbation of
+    its frame-20 state grows to 8e-5 in one frame, 2.5e-3 in six and 6e-2 in ten; from its frame-30 state to 3.5e-3 in ONE
+    frame - so later frames are checked from identical states, not as a free-running trajectory."""
     from gaia_b200.workloads import workload_ref_stack
     wl = workload_ref_stack()
     g, o = _both(wl, threads=8)
 
-    def integer_check():
+    def integer_check(one_iteration):
         state = [(g.positions(m), g.velocities(m)) for m in range(4)]
+
+        def put(scenes):
+            for s in scenes:
+                for m, (p, v) in enumerate(state):
+                    s.set_state(m, p, v)
+        put((g, o))
         for s in (g, o):
-            for m, (p, v) in enumerate(state):
-                s.set_state(m, p, v)
             s.run_iterations(0)          # DCD on the state, initial step, CCD, prepare
         for m in range(4):
             assert np.array_equal(g.positions(m), o.positions(m)) and np.array_equal(g.prev_positions(m), o.prev_positions(m))
         out = _assert_integer_surfaces_equal(g, o, 4, 8)
+        if one_iteration:
+            put((g, o))
+            for s in (g, o):
+                s.run_iterations(1)
+            scale = float(np.linalg.norm(_all(o).max(0) - _all(o).min(0)))
+            for m in range(4):
+                assert per_vertex_rel(g.positions(m), o.positions(m), scale=scale) < 1e-5, m
         # LBVH leaf orders: the product keeps the order of its last (re)build, so they are compared on a fresh pair whose
         # trees are built on exactly this state (tet / surface scenes at the detection before the initial step, the swept
         # scene after it)
         g2, o2 = _both(wl, threads=8)
+        put((g2, o2))
         for s in (g2, o2):
-            for m, (p, v) in enumerate(state):
-                s.set_state(m, p, v)
             s.detect_collisions(True, False)
         for which in (0, 1):
             assert np.array_equal(g2.bvh_leaf_order(which), o2.bvh_leaf_order(which)), which
@@ -197,25 +208,26 @@ def test_config2_miniature_integer_surfaces_and_trajectory():
             s.run_iterations(0)
         assert np.array_equal(g2.bvh_leaf_order(2), o2.bvh_leaf_order(2))
         g2.close()
-        for s in (g, o):
-            for m, (p, v) in enumerate(state):
-                s.set_state(m, p, v)
+        put((g, o))
         return out
 
-    n_contacts, n_active, n_rel = integer_check()
+    n_contacts, n_active, n_rel = integer_check(False)
     found = int((o.contacts()["shortestPathFound"] == 1).sum())
     assert n_contacts > 10 and found > 10
     assert n_rel == 3 * found and found <= n_active <= 4 * found
-    worst, most = [], 0
-    for chunk in range(4):
+    worst = []
+    for chunk in range(2):
         for s in (g, o):
             s.run_frames(10)
         worst.append(max(float(np.abs(g.positions(m) - o.positions(m)).max()) for m in range(4)))
-        if chunk >= 1:
-            n_contacts, _, _ = integer_check()           # also puts the oracle on the GPU's state
-            most = max(most, n_contacts)
-    assert most > 60, most
     assert max(worst) < 1e-3, worst
+    most = 0
+    for chunk in range(3):               # the GPU's own states at frames 20, 30, 40
+        n_contacts, _, _ = integer_check(True)
+        most = max(most, n_contacts)
+        if chunk < 2:
+            g.run_frames(10)
+    assert most > 60, most
 
 
 def test_self_collision_relations_bit_exact():
