@@ -254,8 +254,11 @@ bool host_finalize(Scene& s) {
     s.nInc = nInc;
     s.h_incIdx.resize((size_t)nInc);
     s.h_incW.resize(4 * (size_t)nInc);
-    // distinct neighbours of every vertex (sorted ids, ascending) -> local slots referenced by the incidence records
+    // distinct neighbours of every vertex -> local slots referenced by the incidence records. The list is ordered by the
+    // neighbours' ORIGINAL vertex ids (all of them live in the vertex's own mesh): slot order decides which lane sums which
+    // neighbour in the sweep, and original ids keep their relative order when a mesh is partitioned, sorted ids do not.
     s.h_nbOff.assign(vb + 1, 0);
+    std::vector<int32_t> nbOrig;      // parallel to h_nbList: original (mesh-local) ids
     {
         // incidence CSR (mesh-local tet id, local vertex k) filled in ascending tet order
         std::vector<int32_t> incTet((size_t)nInc);
@@ -264,7 +267,7 @@ bool host_finalize(Scene& s) {
             for (int t = 0; t < m.nT; t++)
                 for (int k = 0; k < 4; k++) incTet[fillAt[m.sortedId[m.tets[4 * (size_t)t + k]]]++] = 4 * t + k;
         std::vector<int32_t> tmp;
-        s.h_nbList.reserve((size_t)nInc);
+        s.h_nbList.reserve((size_t)nInc); nbOrig.reserve((size_t)nInc);
         // vertices are visited in sorted order so nbList is laid out exactly like the device reads it
         for (int64_t sid = 0; sid < vb; sid++) {
             const int64_t orig = s.sortedToOrig[sid];
@@ -275,21 +278,22 @@ bool host_finalize(Scene& s) {
             tmp.clear();
             for (int32_t j = s.h_incOff[sid]; j < s.h_incOff[sid + 1]; j++) {
                 const int t = incTet[j] >> 2, k = incTet[j] & 3;
-                for (int q = 0; q < 4; q++) if (q != k) tmp.push_back(m.sortedId[m.tets[4 * (size_t)t + q]]);
+                for (int q = 0; q < 4; q++) if (q != k) tmp.push_back(m.tets[4 * (size_t)t + q]);
             }
             std::sort(tmp.begin(), tmp.end());
             tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
             if (s.h_incOff[sid + 1] - s.h_incOff[sid] > 65535) { s.err = "a vertex has more than 65535 incident tets"; return false; }
             if (tmp.size() > 255) { s.err = "a vertex has more than 255 distinct neighbours"; return false; }
             s.h_nbOff[sid + 1] = s.h_nbOff[sid] + (int32_t)tmp.size();
-            s.h_nbList.insert(s.h_nbList.end(), tmp.begin(), tmp.end());
+            nbOrig.insert(nbOrig.end(), tmp.begin(), tmp.end());
+            for (int32_t o : tmp) s.h_nbList.push_back(m.sortedId[o]);
         }
     }
     s.nNb = s.h_nbOff[vb];
-    auto local_slot = [&](int32_t owner, int32_t nb) {
-        const int32_t* b0 = &s.h_nbList[s.h_nbOff[owner]];
-        const int32_t* e0 = &s.h_nbList[s.h_nbOff[owner + 1]];
-        return (uint32_t)(std::lower_bound(b0, e0, nb) - b0);
+    auto local_slot = [&](int32_t owner, int32_t nbOriginal) {
+        const int32_t* b0 = nbOrig.data() + s.h_nbOff[owner];
+        const int32_t* e0 = nbOrig.data() + s.h_nbOff[owner + 1];
+        return (uint32_t)(std::lower_bound(b0, e0, nbOriginal) - b0);
     };
     std::vector<int32_t> cursor(s.h_incOff.begin(), s.h_incOff.end() - 1);
     for (auto& m : M) {
@@ -321,7 +325,7 @@ bool host_finalize(Scene& s) {
                 const int32_t at = cursor[sOwn]++;
                 float* rw = &s.h_incW[4 * (size_t)at];
                 rw[0] = (float)(vol * w[0]); rw[1] = (float)(vol * w[1]); rw[2] = (float)(vol * w[2]); rw[3] = (float)(1.0 / (6.0 * vol));
-                s.h_incIdx[at] = local_slot(sOwn, m.sortedId[ia]) | (local_slot(sOwn, m.sortedId[ib]) << 8) | (local_slot(sOwn, m.sortedId[ic]) << 16);
+                s.h_incIdx[at] = local_slot(sOwn, ia) | (local_slot(sOwn, ib) << 8) | (local_slot(sOwn, ic) << 16);
             }
         }
         for (int v = 0; v < m.nV; v++)
