@@ -490,21 +490,38 @@ def _categories(fn, n, *args):
     return [nodes[off[c]:off[c + 1]].copy() for c in range(nc)]
 
 
-def color_graph(num_nodes, edges, balance=True, goal_max_min_ratio=1.05):
+def _color_flags(balance, algorithm):
+    if algorithm not in ("greedy", "mcs"):
+        raise ValueError("algorithm: 'greedy' or 'mcs'")
+    return (1 if balance else 0) | (2 if algorithm == "mcs" else 0)
+
+
+def color_graph_nodes(num_nodes, edges, balance=True, goal_max_min_ratio=1.05, algorithm="greedy"):
+    """colour id per node (the array the reference tool's GraphColor::get_coloring returns)"""
+    e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
+    col = np.zeros(max(int(num_nodes), 1), np.int32)
+    rc = load_library().gaia_b200_color_graph(int(num_nodes), len(e), _ip(e), _color_flags(balance, algorithm), float(goal_max_min_ratio),
+                                              _ip(col), None, None)
+    if rc < 0:
+        raise GaiaError(f"gaia_b200_color_graph failed: {rc}")
+    return col[:int(num_nodes)]
+
+
+def color_graph(num_nodes, edges, balance=True, goal_max_min_ratio=1.05, algorithm="greedy"):
     """The reference tool's `greedy` colouring (+ balancing) of an undirected graph given as an [nE, 2] edge list; returns the
     colour categories in the tool's order (what it writes to *.vertexColoring.json)."""
     e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
-    return _categories(load_library().gaia_b200_color_graph, int(num_nodes), int(num_nodes), len(e), _ip(e), 1 if balance else 0,
+    return _categories(load_library().gaia_b200_color_graph, int(num_nodes), int(num_nodes), len(e), _ip(e), _color_flags(balance, algorithm),
                        float(goal_max_min_ratio))
 
 
-def color_tet_mesh(n_verts, tets, balance=True, goal_max_min_ratio=1.05):
+def color_tet_mesh(n_verts, tets, balance=True, goal_max_min_ratio=1.05, algorithm="greedy"):
     t = _i32(np.asarray(tets, np.int32).reshape(-1, 4))
-    return _categories(load_library().gaia_b200_color_tet_mesh, int(n_verts), int(n_verts), len(t), _ip(t), 1 if balance else 0,
+    return _categories(load_library().gaia_b200_color_tet_mesh, int(n_verts), int(n_verts), len(t), _ip(t), _color_flags(balance, algorithm),
                        float(goal_max_min_ratio))
 
 
-def color_tri_mesh(n_verts, faces, edge_energy=True, balance=True, goal_max_min_ratio=1.05):
+def color_tri_mesh(n_verts, faces, edge_energy=True, balance=True, goal_max_min_ratio=1.05, algorithm="greedy"):
     f = _i32(np.asarray(faces, np.int32).reshape(-1, 3))
     return _categories(load_library().gaia_b200_color_tri_mesh, int(n_verts), int(n_verts), len(f), _ip(f), 1 if edge_energy else 0,
-                       1 if balance else 0, float(goal_max_min_ratio))
+                       _color_flags(balance, algorithm), float(goal_max_min_ratio))

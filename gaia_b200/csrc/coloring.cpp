@@ -59,6 +59,52 @@ int greedy_color(const Adj& graph, std::vector<int32_t>& colors) {
     return maxColor + 1;
 }
 
+// Mcs::color (M/GraphColoring/mcs.cpp:14-168): maximum cardinality search order - repeatedly the remaining node with the
+// most already-ordered neighbours, lowest id on ties (the tool scans its node list front to back and keeps the first
+// maximum) - then every node, in that order, takes the smallest colour none of its coloured neighbours holds. The tool
+// rescans all remaining nodes per step (O(V^2)); here bucket[w] is a min-heap of the node ids that reached weight w.
+int mcs_color(const Adj& graph, std::vector<int32_t>& colors) {
+    const int32_t n = (int32_t)graph.size();
+    colors.assign(n, -1);
+    std::vector<int32_t> weight(n, 0), order;
+    std::vector<uint8_t> taken(n, 0);
+    order.reserve(n);
+    using Heap = std::priority_queue<int32_t, std::vector<int32_t>, std::greater<int32_t>>;
+    std::vector<Heap> bucket(1);
+    for (int32_t i = 0; i < n; i++) bucket[0].push(i);
+    int32_t cur = 0;
+    for (int32_t done = 0; done < n; done++) {
+        int32_t node = -1;
+        for (;;) {
+            while (bucket[cur].empty()) cur--;
+            const int32_t c = bucket[cur].top();
+            bucket[cur].pop();
+            if (!taken[c] && weight[c] == cur) { node = c; break; }
+        }
+        taken[node] = 1;
+        order.push_back(node);
+        for (int32_t nb : graph[node]) {
+            // (the tool also raises the weight of nodes that are already ordered; they are never looked at again)
+            weight[nb]++;
+            if (taken[nb]) continue;
+            if ((size_t)weight[nb] >= bucket.size()) bucket.resize((size_t)weight[nb] + 1);
+            bucket[weight[nb]].push(nb);
+            if (weight[nb] > cur) cur = weight[nb];
+        }
+    }
+    int32_t maxColor = -1;
+    std::vector<uint8_t> used;
+    for (int32_t node : order) {
+        used.assign((size_t)maxColor + 2, 0);
+        for (int32_t nb : graph[node]) if (colors[nb] >= 0) used[colors[nb]] = 1;
+        int32_t pick = 0;
+        while (pick <= maxColor && used[pick]) pick++;
+        if (pick > maxColor) maxColor = pick;
+        colors[node] = pick;
+    }
+    return maxColor + 1;
+}
+
 void balance(const Adj& graph, std::vector<int32_t>& colors, std::vector<std::vector<int32_t>>& cat, float goalMaxMinRatio) {
     if (cat.empty()) return;
     auto changable = [&](int32_t node, int32_t dst) {
@@ -98,9 +144,11 @@ void balance(const Adj& graph, std::vector<int32_t>& colors, std::vector<std::ve
     } while (ratio > goalMaxMinRatio);
 }
 
-int color_adj(const Adj& graph, int balanceOn, float ratio, int32_t* colors, int32_t* catOff, int32_t* catNodes) {
+// flags: GAIA_COLOR_BALANCE | GAIA_COLOR_MCS
+int color_adj(const Adj& graph, int flags, float ratio, int32_t* colors, int32_t* catOff, int32_t* catNodes) {
+    const int balanceOn = flags & GAIA_COLOR_BALANCE;
     std::vector<int32_t> col;
-    int nc = greedy_color(graph, col);
+    int nc = (flags & GAIA_COLOR_MCS) ? mcs_color(graph, col) : greedy_color(graph, col);
     std::vector<std::vector<int32_t>> cat(nc);
     for (int32_t v = 0; v < (int32_t)graph.size(); v++) cat[col[v]].push_back(v);
     if (balanceOn) balance(graph, col, cat, ratio);

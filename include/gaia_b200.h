@@ -29,6 +29,8 @@ extern "C" {
 #endif
 
 #define GAIA_B200_ABI_VERSION 1
+#define GAIA_COLOR_BALANCE 1
+#define GAIA_COLOR_MCS 2
 
 typedef enum gaia_status {
     GAIA_OK = 0,
@@ -314,9 +316,16 @@ int gaia_b200_get_layout_bytes(gaia_handle* h, int64_t out[6]);
 /* Vertex graph colouring (host code; no device needed) -------------------------
  * The reference colours its meshes with an offline tool (S/GraphColoring/GraphColoring.cpp: `-v -a greedy -b -r ratio`;
  * OrderedGreedy, M/GraphColoring/gready.cpp:16-117; balanceColoredCategories, M/GraphColoring/ColoringAlgorithms.cpp:82-198)
- * whose output is the `*.vertexColoring.json` that add_tet_mesh / add_tri_mesh take. These calls restate it (same node
- * order, colour choice and balancing moves; O(E log V) instead of the tool's O(V^2) scan; balancing moves are capped, the
- * tool's loop is unbounded). Parity with the tool's own output is UNPINNED this round: tests check validity and balance.
+ * whose output is the `*.vertexColoring.json` that add_tet_mesh / add_tri_mesh take. These calls restate both of the tool's
+ * algorithms - `-a greedy` (OrderedGreedy) and `-a mcs` (Mcs::color, M/GraphColoring/mcs.cpp:14-168, the one the colourings
+ * shipped under Data/mesh_models were made with: 8 colours) - with the same node order, colour choice and balancing moves,
+ * in O(E log V) instead of the tool's O(V^2) scans. Pinned: colours[] are identical to the tool's own code (compiled into
+ * oracle/_ref) on random graphs and on the vertex graphs of reference meshes, before and after balancing
+ * (tests/test_coloring.py, fixtures tests/golden/ref_coloring.npz). One documented difference: the tool's balancing loop is
+ * unbounded and can shuttle a node between two colours for ever; here it stops after 4 V + 16 moves (a colouring is valid
+ * after every move).
+ * `balance` is a flag word: GAIA_COLOR_BALANCE (1) balances the categories towards goalMaxMinRatio, GAIA_COLOR_MCS (2)
+ * orders the nodes by maximum cardinality search instead of smallest remaining degree.
  * colors: numNodes colour ids (may be NULL); categoryOffsets (numColours + 1, sized numNodes + 1 by the caller) and
  * categoryNodes (numNodes): the colour categories in the tool's order (both NULL to skip). Return the number of colours.
  * color_graph takes the undirected edge list as given; the mesh variants build the vertex graph of TetMeshVertexGraph

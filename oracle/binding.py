@@ -89,6 +89,9 @@ def load_ref():
         lib.ref_damp_velocity.argtypes = [FP, C.c_float, C.c_float, C.c_float]; lib.ref_damp_velocity.restype = None
         lib.ref_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]
         lib.ref_cubic_roots.argtypes = [FP, C.c_float, C.c_float, FP]
+        lib.ref_point_in_tet.argtypes = [FP] * 5
+        lib.ref_closest_point_triangle.argtypes = [FP] * 6
+        lib.ref_closest_points_segments.argtypes = [FP] * 5; lib.ref_closest_points_segments.restype = None
         _ref = lib
     return _ref
 

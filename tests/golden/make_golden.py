@@ -21,7 +21,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases)  # noqa: E402
+from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+                           point_in_tet_cases, closest_point_triangle_cases, segment_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
 FP = C.POINTER(C.c_float)
@@ -96,6 +97,24 @@ def main():
         ref.ref_boundary(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bounds6), bc["kB"], bc["muB"], bc["epsVB"], bc["dt"], fp(f), fp(h))
         Fb[i] = f; Hb[i] = h
     out["boundary_force"] = Fb; out["boundary_hessian"] = Hb
+    # ---- collision predicates (GAIA::pointInTet, closestPointTriangle, get_closest_points_between_segments,
+    #      M/CollisionDetector/CollisionGeometry.h:56-267, compiled with the vendored M/common Embree math)
+    p, tets = point_in_tet_cases()
+    out["pit_inside"] = np.array([ref.ref_point_in_tet(fp(p[i]), fp(tets[i, 0]), fp(tets[i, 1]), fp(tets[i, 2]), fp(tets[i, 3])) for i in range(len(p))], np.int32)
+    p, tri = closest_point_triangle_cases()
+    cpt = np.zeros((len(p), 3), np.float32); cpb = np.zeros((len(p), 3), np.float32); cpk = np.zeros(len(p), np.int32)
+    for i in range(len(p)):
+        c3 = np.zeros(3, np.float32); b3 = np.zeros(3, np.float32)
+        cpk[i] = ref.ref_closest_point_triangle(fp(p[i]), fp(tri[i, 0]), fp(tri[i, 1]), fp(tri[i, 2]), fp(c3), fp(b3))
+        cpt[i] = c3; cpb[i] = b3
+    out["cpt_point"] = cpt; out["cpt_bary"] = cpb; out["cpt_type"] = cpk
+    seg = segment_cases()
+    so = np.zeros((len(seg), 8), np.float32)
+    for i in range(len(seg)):
+        o8 = np.zeros(8, np.float32)
+        ref.ref_closest_points_segments(fp(seg[i, 0]), fp(seg[i, 1]), fp(seg[i, 2]), fp(seg[i, 3]), fp(o8))
+        so[i] = o8
+    out["seg_out"] = so
     path = os.path.join(ROOT, "tests", "golden", "ref_vectors.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, {k: v.shape for k, v in out.items()})

@@ -120,3 +120,73 @@ def boundary_cases(n=48, seed=33):
     scale = np.where(np.arange(n)[:, None] % 4 == 0, 1e-4, 0.03)   # displacements below and above epsU = epsV*dt
     pPrev = (p + rng.normal(0, 1, p.shape) * scale).astype(np.float32)
     return dict(p=np.ascontiguousarray(p), pPrev=np.ascontiguousarray(pPrev), mn=mn, mx=mx, kB=1e5, muB=0.3, epsVB=1.0, dt=1.0 / 240)
+
+
+def point_in_tet_cases(n=400, seed=41):
+    """tets of mixed size (some nearly flat: |6V| around the reference's 1e-5 rejection bound) with query points inside,
+    outside, on faces / edges / vertices and just off them"""
+    rng = np.random.RandomState(seed)
+    tets = rng.uniform(-1, 1, (n, 4, 3)).astype(np.float32)
+    tets[::7] *= 0.02                                         # small tets: volume near CMP_EPSILON
+    tets[3::11, 3] = tets[3::11, 0] + 0.3 * (tets[3::11, 1] - tets[3::11, 0]) + 0.3 * (tets[3::11, 2] - tets[3::11, 0]) + \
+        rng.uniform(-2e-5, 2e-5, (len(tets[3::11]), 3)).astype(np.float32)     # nearly coplanar
+    w = rng.dirichlet(np.ones(4), n).astype(np.float32)
+    kind = rng.randint(0, 6, n)
+    w[kind == 1] = rng.uniform(-0.3, 1.3, (int((kind == 1).sum()), 4)).astype(np.float32)      # mostly outside
+    w[kind == 2, 0] = 0.0                                                                       # on a face
+    w[kind == 3, :2] = 0.0                                                                      # on an edge
+    w[kind == 4] = np.eye(4, dtype=np.float32)[rng.randint(0, 4, int((kind == 4).sum()))]       # at a vertex
+    w /= np.where(np.abs(w.sum(1, keepdims=True)) > 1e-6, w.sum(1, keepdims=True), 1.0)
+    p = np.einsum("nk,nkd->nd", w, tets).astype(np.float32)
+    p[kind == 5] += rng.uniform(-1e-6, 1e-6, (int((kind == 5).sum()), 3)).astype(np.float32)
+    return np.ascontiguousarray(p), np.ascontiguousarray(tets)
+
+
+def closest_point_triangle_cases(n=400, seed=43):
+    """random triangles (some slivers) and query points over all seven Voronoi regions (vertex / edge / interior)"""
+    rng = np.random.RandomState(seed)
+    tri = rng.uniform(-1, 1, (n, 3, 3)).astype(np.float32)
+    tri[::9, 2] = tri[::9, 0] + 0.5 * (tri[::9, 1] - tri[::9, 0]) + rng.uniform(-1e-3, 1e-3, (len(tri[::9]), 3)).astype(np.float32)
+    w = rng.uniform(-0.8, 1.8, (n, 3)).astype(np.float32)
+    w /= w.sum(1, keepdims=True) + 1e-3
+    nrm = np.cross(tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0])
+    p = np.einsum("nk,nkd->nd", w, tri) + rng.uniform(-0.5, 0.5, (n, 1)) * nrm
+    p[::13] = tri[::13, 1]                                    # exactly at a vertex
+    return np.ascontiguousarray(p, np.float32), np.ascontiguousarray(tri)
+
+
+def segment_cases(n=400, seed=47):
+    """segment pairs: general position, parallel, sharing an end point, degenerate (zero length)"""
+    rng = np.random.RandomState(seed)
+    s = rng.uniform(-1, 1, (n, 4, 3)).astype(np.float32)      # p0, p1, q0, q1
+    s[::5, 3] = s[::5, 2] + (s[::5, 1] - s[::5, 0])           # parallel
+    s[1::17, 2] = s[1::17, 0]                                 # shared end point
+    s[2::19, 1] = s[2::19, 0]                                 # zero-length first segment
+    s[4::23, 3] = s[4::23, 2]                                 # zero-length second segment
+    return np.ascontiguousarray(s)
+
+
+def coloring_graphs():
+    """name -> (numNodes, unique undirected edges [nE,2] with a < b): seeded random graphs and the vertex graphs of two
+    reference meshes (tests/golden/ref_root), as M/GraphColoring/TetMeshVertexGraph.h builds them"""
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    from gaia_b200 import meshio
+    from gaia_b200.workloads import ref_mesh
+    g = {}
+    rng = np.random.RandomState(77)
+    for n, deg in ((60, 4), (300, 7), (1000, 12)):
+        e = rng.randint(0, n, (n * deg // 2, 2))
+        e = e[e[:, 0] != e[:, 1]]
+        e = np.unique(np.sort(e, axis=1), axis=0)
+        g[f"rand{n}"] = (n, e.astype(np.int32))
+    for m in ("teapot", "beam_1k"):
+        v, t, _ = ref_mesh(m)
+        offs, dst = meshio.vertex_adjacency(len(v), t)
+        src = np.repeat(np.arange(len(v)), np.diff(offs))
+        keep = src < dst
+        g[m] = (len(v), np.stack([src[keep], dst[keep]], 1).astype(np.int32))
+    return g

@@ -1,6 +1,7 @@
-"""Vertex colouring: gaia_b200_color_* (a restatement of the reference tool's OrderedGreedy +
-balanceColoredCategories, M/GraphColoring) against the properties a colouring must have. Parity with the tool's own output
-is unpinned: its balancing loop does not terminate on some graphs, so it was not used as a checker this round."""
+"""Vertex colouring: gaia_b200_color_* (a restatement of the reference tool's OrderedGreedy, Mcs and
+balanceColoredCategories, M/GraphColoring). Pinned three ways: colours[] identical to the tool's own code compiled into
+oracle/_ref (fixture tests/golden/ref_coloring.npz), MCS output identical to the *.vertexColoring.json files the reference
+ships, and the properties any colouring must have."""
 import numpy as np
 import pytest
 
@@ -37,3 +38,34 @@ def test_colouring_a_large_mesh_takes_seconds():
     cat = capi.color_tet_mesh(len(v), t, balance=False)
     dt = time.time() - t0
     assert meshio.check_coloring(len(v), t, cat) and dt < 20, dt
+
+
+# ------------------------------------------------------------------------------------------ pinned to the reference's own code
+GOLD = np.load(__import__("os").path.join(__import__("os").path.dirname(__file__), "golden", "ref_coloring.npz"))
+
+
+@pytest.mark.parametrize("algorithm", ["greedy", "mcs"])
+def test_colours_are_identical_to_the_reference_tool(algorithm):
+    """colours[] of gaia_b200_color_graph against OrderedGreedy::color / Mcs::color (+ balanceColoredCategories at ratio 1.05)
+    compiled from the reference (tests/golden/make_coloring_golden.py): node by node identical, on seeded random graphs and on
+    the vertex graphs of teapot.t and Beam_1k.t, before and after balancing."""
+    from golden_inputs import coloring_graphs
+    for name, (n, edges) in coloring_graphs().items():
+        got = capi.color_graph_nodes(n, edges, balance=False, algorithm=algorithm)
+        assert np.array_equal(got, GOLD[f"{name}_{algorithm}"]), (name, algorithm)
+        if GOLD[f"{name}_{algorithm}_balance_ok"][0]:
+            got = capi.color_graph_nodes(n, edges, balance=True, goal_max_min_ratio=1.05, algorithm=algorithm)
+            assert np.array_equal(got, GOLD[f"{name}_{algorithm}_balanced"]), (name, algorithm, "balanced")
+
+
+@pytest.mark.parametrize("model", ["teapot", "beam_1k", "bunny_small", "octopus_5k", "armadillo_lowres"])
+def test_mcs_reproduces_the_shipped_colouring_files(model):
+    """`gaia_b200_color_tet_mesh(..., GAIA_COLOR_MCS)` without balancing writes exactly the *.vertexColoring.json the reference
+    ships beside its meshes (tests/golden/ref_root mirrors them): same categories, same node order inside every category."""
+    from gaia_b200.workloads import ref_mesh
+    v, t, shipped = ref_mesh(model)
+    cat = capi.color_tet_mesh(len(v), t, balance=False, algorithm="mcs")
+    assert len(cat) == len(shipped) == 8
+    for a, b in zip(cat, shipped):
+        assert np.array_equal(np.asarray(a), np.asarray(b))
+    assert meshio.check_coloring(len(v), t, cat)

@@ -12,7 +12,8 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases
+from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+                           point_in_tet_cases, closest_point_triangle_cases, segment_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
 GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vectors.npz"))
@@ -127,6 +128,41 @@ def test_boundary_force_hessian():
         else:
             assert np.abs(f).max() == 0
     assert nz >= 30
+
+
+def test_point_in_tet_bit_exact():
+    """oracle point_in_tet == GAIA::pointInTet (CollisionGeometry.h:56-88) compiled from the reference: same accept / reject
+    decision on every case, including nearly flat tets around the 1e-5 volume bound and points on faces, edges and vertices"""
+    lib = load_oracle()
+    p, tets = point_in_tet_cases()
+    got = np.array([lib.oracle_point_in_tet(fp(p[i]), fp(tets[i, 0]), fp(tets[i, 1]), fp(tets[i, 2]), fp(tets[i, 3])) for i in range(len(p))], np.int32)
+    assert np.array_equal(got, GOLD["pit_inside"])
+    assert 40 < int(GOLD["pit_inside"].sum()) < len(p) - 40          # both answers are well represented
+
+
+def test_closest_point_triangle_bit_exact():
+    """oracle closest_point_triangle == GAIA::closestPointTriangle (CollisionGeometry.h:90-157): region type, closest point
+    and barycentrics bit for bit over all seven regions"""
+    lib = load_oracle()
+    p, tri = closest_point_triangle_cases()
+    for i in range(len(p)):
+        c3 = np.zeros(3, np.float32); b3 = np.zeros(3, np.float32)
+        k = lib.oracle_closest_point_triangle(fp(p[i]), fp(tri[i, 0]), fp(tri[i, 1]), fp(tri[i, 2]), fp(c3), fp(b3))
+        assert k == GOLD["cpt_type"][i], i
+        assert np.array_equal(c3, GOLD["cpt_point"][i]) and np.array_equal(b3, GOLD["cpt_bary"][i]), i
+    assert len(set(GOLD["cpt_type"].tolist())) == 7
+
+
+def test_closest_points_between_segments_bit_exact():
+    """oracle closest_points_segments (cloth edge-edge contacts) == GAIA::get_closest_points_between_segments
+    (CollisionGeometry.h:160-267), incl. parallel, touching and zero-length segments"""
+    from oracle.binding_cloth import _lib as cloth_lib
+    lib = cloth_lib()
+    seg = segment_cases()
+    for i in range(len(seg)):
+        o8 = np.zeros(8, np.float32)
+        lib.oracle_cloth_closest_points_segments(fp(seg[i, 0]), fp(seg[i, 1]), fp(seg[i, 2]), fp(seg[i, 3]), fp(o8))
+        assert np.array_equal(o8, GOLD["seg_out"][i], equal_nan=True), (i, o8, GOLD["seg_out"][i])
 
 
 @pytest.mark.skipif(not ref_available(), reason="oracle/_ref/libgaia_ref.so is only built where /root/reference exists")
