@@ -92,6 +92,7 @@ def load_ref():
         lib.ref_point_in_tet.argtypes = [FP] * 5
         lib.ref_closest_point_triangle.argtypes = [FP] * 6
         lib.ref_closest_points_segments.argtypes = [FP] * 5; lib.ref_closest_points_segments.restype = None
+        lib.ref_cloth_contact_repulsion.argtypes = [C.c_float] * 4 + [C.c_int, FP, FP]; lib.ref_cloth_contact_repulsion.restype = None
         _ref = lib
     return _ref
 

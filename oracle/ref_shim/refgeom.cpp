@@ -11,6 +11,7 @@
 #include "common/math/vec3fa.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 
 typedef float FloatingType;
 #define CMP_EPSILON 0.00001f
@@ -40,4 +41,26 @@ void ref_closest_points_segments(const float* p0, const float* p1, const float* 
     GAIA::get_closest_points_between_segments(V(p0), V(p1), V(q0), V(q1), ps, qt, s, t);
     out8[0] = ps.x; out8[1] = ps.y; out8[2] = ps.z; out8[3] = qt.x; out8[4] = qt.y; out8[5] = qt.z; out8[6] = s; out8[7] = t;
 }
+}
+
+// ---- the cloth contact energy derivative, VBDClothSimulationFramework::computeContactRepulsiveForce
+// (Simulator/Modules/VBDCloth/VBDClothPhysics.cpp:1533-1579): the member function's own lines, extracted by oracle/Makefile,
+// compiled against a stand-in class that only offers the three physicsParams() fields the function reads.
+typedef const float CFloatingType;
+#define SQR(x) ((x) * (x))
+namespace GAIA {
+struct RefClothContactParams { float contactRadius, contactStiffness; int contactEnergyTypes; };
+struct VBDClothSimulationFramework {
+    RefClothContactParams p;
+    RefClothContactParams& physicsParams() { return p; }
+    void computeContactRepulsiveForce(CFloatingType dis_, CFloatingType thickness, FloatingType& dEdD, FloatingType& d2E_dDdD);
+};
+}  // namespace GAIA
+#include "ref_contact_repulsive_1533_1579.inc"
+
+extern "C" void ref_cloth_contact_repulsion(float dis, float thickness, float contactRadius, float contactStiffness, int energyType, float* dEdD, float* d2E) {
+    GAIA::VBDClothSimulationFramework f;
+    f.p.contactRadius = contactRadius; f.p.contactStiffness = contactStiffness; f.p.contactEnergyTypes = energyType;
+    *dEdD = 0.f; *d2E = 0.f;
+    f.computeContactRepulsiveForce(dis, thickness, *dEdD, *d2E);
 }

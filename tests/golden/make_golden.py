@@ -22,7 +22,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
-                           point_in_tet_cases, closest_point_triangle_cases, segment_cases)  # noqa: E402
+                           point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
 FP = C.POINTER(C.c_float)
@@ -115,6 +115,15 @@ def main():
         ref.ref_closest_points_segments(fp(seg[i, 0]), fp(seg[i, 1]), fp(seg[i, 2]), fp(seg[i, 3]), fp(o8))
         so[i] = o8
     out["seg_out"] = so
+    # ---- cloth contact energy derivatives (VBDClothSimulationFramework::computeContactRepulsiveForce, VBDClothPhysics.cpp:1533-1579)
+    dis, th, r, k = cloth_repulsion_cases()
+    rep = np.zeros((3, len(dis), 2), np.float32)
+    for et in range(3):
+        for i in range(len(dis)):
+            a, b = C.c_float(0), C.c_float(0)
+            ref.ref_cloth_contact_repulsion(float(dis[i]), float(th[i]), float(r[i]), float(k[i]), et, C.byref(a), C.byref(b))
+            rep[et, i] = (a.value, b.value)
+    out["cloth_repulsion"] = rep
     path = os.path.join(ROOT, "tests", "golden", "ref_vectors.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, {k: v.shape for k, v in out.items()})

@@ -190,3 +190,16 @@ def coloring_graphs():
         keep = src < dst
         g[m] = (len(v), np.stack([src[keep], dst[keep]], 1).astype(np.int32))
     return g
+
+
+def cloth_repulsion_cases(n=300, seed=51):
+    """(dis, thickness, contactRadius, contactStiffness) rows for the three contact energy types: distances on both sides of
+    tau = r/2 and of the CMP_EPSILON cut, and beyond the radius"""
+    rng = np.random.RandomState(seed)
+    r = rng.uniform(0.05, 0.5, n).astype(np.float32)
+    th = (rng.uniform(0, 0.02, n) * (rng.rand(n) < 0.7)).astype(np.float32)
+    dis = (th + r * rng.uniform(-0.05, 1.3, n)).astype(np.float32)
+    dis[::11] = th[::11] + np.float32(1e-5) * rng.uniform(0.5, 1.5, len(dis[::11])).astype(np.float32)
+    dis[1::13] = th[1::13] + r[1::13] * 0.5
+    k = rng.uniform(1e3, 1e6, n).astype(np.float32)
+    return dis, th, r, k

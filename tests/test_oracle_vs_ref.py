@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 
 from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
-                           point_in_tet_cases, closest_point_triangle_cases, segment_cases)
+                           point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
 GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vectors.npz"))
@@ -163,6 +163,26 @@ def test_closest_points_between_segments_bit_exact():
         o8 = np.zeros(8, np.float32)
         lib.oracle_cloth_closest_points_segments(fp(seg[i, 0]), fp(seg[i, 1]), fp(seg[i, 2]), fp(seg[i, 3]), fp(o8))
         assert np.array_equal(o8, GOLD["seg_out"][i], equal_nan=True), (i, o8, GOLD["seg_out"][i])
+
+
+def test_cloth_contact_repulsion_bit_exact():
+    """oracle cloth_contact_repulsion == VBDClothSimulationFramework::computeContactRepulsiveForce (VBDClothPhysics.cpp:1533-1579)
+    compiled from the reference: dE/dd and d2E/dd2 for the quadratic and the two-stage quadratic / logarithmic energies bit for
+    bit; the pure logarithmic type (2) calls log(): identical to 2 ulp (libm vs the build's vectorised log)."""
+    from gaia_b200.cloth import default_cloth_physics_params
+    from oracle.binding_cloth import OracleClothScene
+    dis, th, r, k = cloth_repulsion_cases()
+    for et in range(3):
+        for i in range(0, len(dis)):
+            o = OracleClothScene(default_cloth_physics_params(thickness=float(th[i]), contactRadius=float(r[i]), contactStiffness=float(k[i]),
+                                                              contactEnergyTypes=et), threads=1)
+            a, b = o.contact_repulsion(float(dis[i]))
+            o.close()
+            g = GOLD["cloth_repulsion"][et, i]
+            if et < 2:
+                assert np.float32(a) == g[0] and np.float32(b) == g[1], (et, i, a, b, g)
+            else:
+                assert np.allclose([a, b], g, rtol=3e-7, atol=0, equal_nan=True), (et, i, a, b, g)
 
 
 @pytest.mark.skipif(not ref_available(), reason="oracle/_ref/libgaia_ref.so is only built where /root/reference exists")
