@@ -131,7 +131,9 @@ def cpu_baseline(wl_name, max_seconds=25.0, threads=0):
         full = WORKLOADS[wl_name]()
         sample_wl = workload_drop_pile(min(32, len(full["meshes"])), substeps=full["phys"].numSubsteps, iterations=full["phys"].iterations, preroll=0)
     elif wl_name == "s01":
-        sample_wl = WORKLOADS["s01"]()          # the scene itself; the CPU is timed on its first frames (models 0, 1, ... in free fall and first contacts)
+        from gaia_b200.workloads import workload_s01
+        sample_wl = workload_s01(first_frame=1, n_models=4)      # the scene's first four models (appearing at frames 1, 7, 13, 19), timed from frame 0
+        sample_wl["preroll"] = 0
     else:
         sample_wl = WORKLOADS[wl_name]()
     t0 = time.time()

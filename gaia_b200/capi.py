@@ -370,6 +370,9 @@ def load_library(path=None):
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
     lib.gaia_b200_get_layout_bytes.argtypes = [P, C.POINTER(C.c_int64)]
+    lib.gaia_b200_total_surface_vertices.argtypes = [P]; lib.gaia_b200_total_surface_vertices.restype = C.c_int64
+    lib.gaia_b200_surface_snapshot_begin.argtypes = [P, C.c_int]
+    lib.gaia_b200_surface_snapshot_wait.argtypes = [P, C.c_int, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int64)]
     lib.gaia_b200_color_graph.argtypes = [C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
@@ -466,6 +469,16 @@ class Scene(SceneBase):
 
     def set_profiling(self, on=True):
         self._call("set_profiling", int(on))
+
+    def surface_snapshot_begin(self, slot):
+        self._call("surface_snapshot_begin", int(slot))
+
+    def surface_snapshot_wait(self, slot):
+        """[nSurfaceVertices, 3] view-copy of ring slot `slot` (all meshes concatenated, writeAllToBinary order)"""
+        ptr = C.POINTER(C.c_float)()
+        n = C.c_int64()
+        self._call("surface_snapshot_wait", int(slot), C.byref(ptr), C.byref(n))
+        return np.ctypeslib.as_array(ptr, shape=(n.value,)).reshape(-1, 3).copy()
 
     def layout_bytes(self):
         a = (C.c_int64 * 6)()

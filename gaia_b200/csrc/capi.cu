@@ -224,15 +224,75 @@ int gaia_b200_set_state(gaia_handle* h, int mesh, const float* pos, const float*
     return GAIA_OK;
 }
 
+// ---- surface output: gathered on the device (M/IO/FileIO.cpp:52-83 writes surface vertices in ascending tet-vertex id)
+static __global__ void k_gather_surface(int64_t n, const float4* __restrict__ pos, const int32_t* __restrict__ surfSid, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = pos[surfSid[i]];
+    out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+}
+static cudaError_t surface_io_init(Scene& s) {
+    if (s.ioStream) return cudaSuccess;
+    const int64_t nS = s.nSurfVerts;
+    cudaError_t e;
+    if ((e = cudaStreamCreateWithFlags(&s.ioStream, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    std::vector<int32_t> sid((size_t)std::max<int64_t>(nS, 1));
+    for (auto& m : s.meshes) for (int i = 0; i < m.nSurfV(); i++) sid[m.surfVBase + i] = m.sortedId[m.surfaceVIds[i]];
+    if ((e = s.surfSidAll.alloc(sid.size())) != cudaSuccess) return e;
+    if ((e = cudaMemcpy(s.surfSidAll.p, sid.data(), sid.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+    for (int k = 0; k < 2; k++) {
+        if ((e = s.surfStage[k].alloc(3 * sid.size())) != cudaSuccess) return e;
+        if ((e = cudaMallocHost((void**)&s.surfPinned[k], 3 * sid.size() * sizeof(float))) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&s.surfGathered[k], cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&s.surfCopied[k], cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+static cudaError_t surface_snapshot(Scene& s, int slot, int64_t first, int64_t count) {
+    cudaError_t e = surface_io_init(s);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(s.stream, s.surfCopied[slot], 0)) != cudaSuccess) return e;      // the slot's previous copy has left the staging buffer
+    if (count > 0) {
+        k_gather_surface<<<(unsigned)((count + 255) / 256), 256, 0, s.stream>>>(count, s.pos.p, s.surfSidAll.p + first, s.surfStage[slot].p + 3 * first);
+        s.stats.kernelLaunches++;
+    }
+    if ((e = cudaEventRecord(s.surfGathered[slot], s.stream)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(s.ioStream, s.surfGathered[slot], 0)) != cudaSuccess) return e;
+    if (count > 0 && (e = cudaMemcpyAsync(s.surfPinned[slot] + 3 * first, s.surfStage[slot].p + 3 * first, 3 * (size_t)count * sizeof(float),
+                                          cudaMemcpyDeviceToHost, s.ioStream)) != cudaSuccess) return e;
+    return cudaEventRecord(s.surfCopied[slot], s.ioStream);
+}
+
 int gaia_b200_get_surface_positions(gaia_handle* h, int mesh, float* xyz) {
     REQUIRE(h); FINALIZED(h);
     Scene& s = h->s;
     if (mesh < 0 || mesh >= (int)s.meshes.size() || !xyz) return fail(s, GAIA_ERR_INVALID_ARG, "bad mesh id / null output");
+    cudaSetDevice(s.device);
     const HostMesh& m = s.meshes[mesh];
-    std::vector<float> all(3 * (size_t)m.nV);
-    int rc = gaia_b200_get_positions(h, mesh, all.data());
-    if (rc < 0) return rc;
-    for (int i = 0; i < m.nSurfV(); i++) std::memcpy(xyz + 3 * (size_t)i, &all[3 * (size_t)m.surfaceVIds[i]], 12);
+    cudaError_t e = surface_snapshot(s, 0, m.surfVBase, m.nSurfV());
+    if (e == cudaSuccess) e = cudaEventSynchronize(s.surfCopied[0]);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    std::memcpy(xyz, s.surfPinned[0] + 3 * m.surfVBase, 3 * (size_t)m.nSurfV() * sizeof(float));
+    return GAIA_OK;
+}
+int64_t gaia_b200_total_surface_vertices(const gaia_handle* h) { return h ? h->s.nSurfVerts : GAIA_ERR_INVALID_ARG; }
+int gaia_b200_surface_snapshot_begin(gaia_handle* h, int slot) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (slot < 0 || slot > 1) return fail(s, GAIA_ERR_INVALID_ARG, "snapshot slot: 0 or 1");
+    cudaSetDevice(s.device);
+    const cudaError_t e = surface_snapshot(s, slot, 0, s.nSurfVerts);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
+}
+int gaia_b200_surface_snapshot_wait(gaia_handle* h, int slot, const float** xyz, int64_t* nFloats) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (slot < 0 || slot > 1 || !xyz || !s.ioStream) return fail(s, GAIA_ERR_INVALID_ARG, "snapshot slot not begun / null output");
+    cudaSetDevice(s.device);      // (may be a writer thread: the current device is per thread)
+    const cudaError_t e = cudaEventSynchronize(s.surfCopied[slot]);
+    if (e != cudaSuccess) return cuda_fail(s, e);
+    *xyz = s.surfPinned[slot];
+    if (nFloats) *nFloats = 3 * s.nSurfVerts;
     return GAIA_OK;
 }
 

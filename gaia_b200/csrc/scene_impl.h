@@ -99,6 +99,12 @@ struct Scene {
 
     // ---- device state (sorted order)
     cudaStream_t stream = nullptr;
+    // frame output (capi.cu: surface snapshots): second stream, device staging and page-locked ring, two slots
+    cudaStream_t ioStream = nullptr;
+    DevBuf<int32_t> surfSidAll;        // sorted id of every surface vertex, meshes concatenated (writeAllToBinary order)
+    DevBuf<float> surfStage[2];
+    float* surfPinned[2] = {nullptr, nullptr};
+    cudaEvent_t surfGathered[2] = {nullptr, nullptr}, surfCopied[2] = {nullptr, nullptr};
     DevBuf<float4> pos, prev, inertia, vel, velPrev, accel, accPrevPrev, accPrevIter;
     DevBuf<float> mass;
     DevBuf<int32_t> info;          // meshId | fixed<<31

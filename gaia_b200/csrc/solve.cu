@@ -204,6 +204,12 @@ Scene::~Scene() {
     if (pinnedIO) cudaFreeHost(pinnedIO);
     if (iterGraphExec) cudaGraphExecDestroy(iterGraphExec);
     for (cudaEvent_t e : profEv) if (e) cudaEventDestroy(e);
+    for (int k = 0; k < 2; k++) {
+        if (surfPinned[k]) cudaFreeHost(surfPinned[k]);
+        if (surfGathered[k]) cudaEventDestroy(surfGathered[k]);
+        if (surfCopied[k]) cudaEventDestroy(surfCopied[k]);
+    }
+    if (ioStream) cudaStreamDestroy(ioStream);
     if (evA) cudaEventDestroy(evA);
     if (evP0) cudaEventDestroy(evP0);
     if (evP1) cudaEventDestroy(evP1);

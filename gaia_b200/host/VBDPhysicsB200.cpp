@@ -18,7 +18,10 @@ namespace gaia_b200 {
 
 using jsonmin::Value;
 
-VBDPhysicsB200::~VBDPhysicsB200() { gaia_b200_destroy(h_); }
+VBDPhysicsB200::~VBDPhysicsB200() {
+    try { finishWriter(); } catch (...) {}
+    gaia_b200_destroy(h_);
+}
 
 void VBDPhysicsB200::check(int rc, const char* what) {
     if (rc < 0) throw std::runtime_error(std::string(what) + " failed (" + std::to_string(rc) + "): " + gaia_b200_last_error(h_));
@@ -241,12 +244,79 @@ void VBDPhysicsB200::simulate() {
     while (frameId_ < run_.numFrames) {
         const auto t0 = std::chrono::high_resolution_clock::now();
         runStep();
-        check(gaia_b200_synchronize(h_), "gaia_b200_synchronize");
-        const double ms = std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now() - t0).count();
-        if (run_.saveOutputs) writeOutputs(outputFolder_, frameId_);
-        if (run_.debugVerboseLvl >= 1) std::cout << "Frame " << frameId_ << " completed, Time consumption: " << ms << "\n";
+        if (run_.saveOutputs) {
+            submitFrame(frameId_);       // surface gather + copy enqueued behind the step; the writer thread takes it from there
+            if (run_.outputRecoveryState && !(frameId_ % run_.outputRecoveryStateStep)) {
+                createFolder(outputFolder_ + "/RecoveryStates");
+                saveRecoveryState(outputFolder_ + "/RecoveryStates/" + numbered("A", frameId_, ".json"), run_.outputRecoveryStateBinary);
+            }
+        }
+        if (run_.debugVerboseLvl >= 1) {
+            check(gaia_b200_synchronize(h_), "gaia_b200_synchronize");
+            const double ms = std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now() - t0).count();
+            std::cout << "Frame " << frameId_ << " completed, Time consumption: " << ms << "\n";
+        }
         if (run_.saveOutputs && run_.outputStatistics) writeStatistics(outputFolder_, frameId_);
     }
+    finishWriter();
+    check(gaia_b200_synchronize(h_), "gaia_b200_synchronize");
+}
+
+// ---- asynchronous frame output
+void VBDPhysicsB200::submitFrame(int frameId) {
+    const int slot = frameId & 1;
+    {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return !slotBusy_[slot] || !writerError_.empty(); });      // the writer is done with this ring slot
+        if (!writerError_.empty()) throw std::runtime_error("frame writer: " + writerError_);
+        slotBusy_[slot] = true;
+    }
+    check(gaia_b200_surface_snapshot_begin(h_, slot), "gaia_b200_surface_snapshot_begin");
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        jobs_.emplace_back(slot, frameId);
+        if (!writer_.joinable()) writer_ = std::thread([this] { writerLoop(); });
+    }
+    cv_.notify_all();
+}
+
+void VBDPhysicsB200::writerLoop() {
+    for (;;) {
+        std::pair<int, int> job;
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stopWriter_ || !jobs_.empty(); });
+            if (jobs_.empty()) return;
+            job = jobs_.front();
+            jobs_.pop_front();
+        }
+        try {
+            const float* surf = nullptr;
+            int64_t n = 0;
+            const int rc = gaia_b200_surface_snapshot_wait(h_, job.first, &surf, &n);
+            if (rc < 0) throw std::runtime_error(std::string("gaia_b200_surface_snapshot_wait: ") + gaia_b200_last_error(h_));
+            writeFrameFiles(outputFolder_, job.second, surf);
+        } catch (const std::exception& e) {
+            std::lock_guard<std::mutex> lk(mu_);
+            writerError_ = e.what();
+        }
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            slotBusy_[job.first] = false;
+        }
+        cv_.notify_all();
+    }
+}
+
+void VBDPhysicsB200::finishWriter() {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        stopWriter_ = true;
+    }
+    cv_.notify_all();
+    if (writer_.joinable()) writer_.join();
+    stopWriter_ = false;
+    if (!writerError_.empty()) { const std::string e = writerError_; writerError_.clear(); throw std::runtime_error("frame writer: " + e); }
 }
 
 void saveAsPly(const std::string& filePath, const std::vector<float>& verts, const std::vector<int32_t>& faces) {
@@ -262,37 +332,42 @@ void saveAsPly(const std::string& filePath, const std::vector<float>& verts, con
 }
 
 void VBDPhysicsB200::writeOutputs(const std::string& outFolder, int frameId) {
-    const int nM = gaia_b200_num_meshes(h_);
-    struct Surf { std::vector<float> v; std::vector<int32_t> f; };
-    std::vector<Surf> surf(nM);
-    for (int m = 0; m < nM; m++) {
-        int32_t nV, nT, nSV, nSF;
-        check(gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF), "gaia_b200_mesh_sizes");
-        surf[m].v.resize(3 * (size_t)nSV);
-        check(gaia_b200_get_surface_positions(h_, m, surf[m].v.data()), "gaia_b200_get_surface_positions");
+    // synchronous form (frame 0, callers that write by hand): same snapshot path, waited for here
+    finishWriter();
+    check(gaia_b200_surface_snapshot_begin(h_, 0), "gaia_b200_surface_snapshot_begin");
+    const float* surf = nullptr;
+    int64_t n = 0;
+    check(gaia_b200_surface_snapshot_wait(h_, 0, &surf, &n), "gaia_b200_surface_snapshot_wait");
+    writeFrameFiles(outFolder, frameId, surf);
+    if (run_.outputRecoveryState && !(frameId % run_.outputRecoveryStateStep)) {
+        createFolder(outFolder + "/RecoveryStates");
+        saveRecoveryState(outFolder + "/RecoveryStates/" + numbered("A", frameId, ".json"), run_.outputRecoveryStateBinary);
     }
-    auto loadFaces = [&]() {   // surfaceFacesSurfaceMeshVIds: face vertices as indices into the surface vertex list
+}
+
+// writeAllToBinary / writeAllToPLY (M/IO/FileIO.cpp:52-185) from one snapshot: surface vertices of all meshes, concatenated
+void VBDPhysicsB200::writeFrameFiles(const std::string& outFolder, int frameId, const float* surfAll) {
+    const int nM = gaia_b200_num_meshes(h_);
+    if ((int)surfFaces_.size() != nM) {      // static topology, fetched once: faces as indices into the surface vertex list
+        surfFaces_.assign(nM, {}); surfOffset_.assign(nM + 1, 0);
         for (int m = 0; m < nM; m++) {
             int32_t nV, nT, nSV, nSF;
-            gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF);
+            check(gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF), "gaia_b200_mesh_sizes");
             std::vector<int32_t> ids(nSV), faces(3 * (size_t)nSF), toSurf(nV, -1);
             check(gaia_b200_get_surface_vertex_ids(h_, m, ids.data()), "gaia_b200_get_surface_vertex_ids");
             check(gaia_b200_get_surface_faces(h_, m, faces.data()), "gaia_b200_get_surface_faces");
             for (int i = 0; i < nSV; i++) toSurf[ids[i]] = i;
-            surf[m].f.resize(faces.size());
-            for (size_t i = 0; i < faces.size(); i++) surf[m].f[i] = toSurf[faces[i]];
+            surfFaces_[m].resize(faces.size());
+            for (size_t i = 0; i < faces.size(); i++) surfFaces_[m][i] = toSurf[faces[i]];
+            surfOffset_[m + 1] = surfOffset_[m] + nSV;
         }
-    };
+    }
+    auto verts = [&](int m) { return std::vector<float>(surfAll + 3 * surfOffset_[m], surfAll + 3 * surfOffset_[m + 1]); };
     auto writePly = [&](const std::string& file, bool together, bool addModelName) {
-        loadFaces();
         if (together) {
-            std::vector<float> v; std::vector<int32_t> f;
-            int base = 0;
-            for (int m = 0; m < nM; m++) {
-                v.insert(v.end(), surf[m].v.begin(), surf[m].v.end());
-                for (int32_t id : surf[m].f) f.push_back(id + base);
-                base += (int)(surf[m].v.size() / 3);
-            }
+            std::vector<float> v(surfAll, surfAll + 3 * surfOffset_[nM]);
+            std::vector<int32_t> f;
+            for (int m = 0; m < nM; m++) for (int32_t id : surfFaces_[m]) f.push_back(id + (int32_t)surfOffset_[m]);
             saveAsPly(file, v, f);
         } else {
             const size_t dot = file.find_last_of('.');
@@ -300,7 +375,7 @@ void VBDPhysicsB200::writeOutputs(const std::string& outFolder, int frameId) {
             for (int m = 0; m < nM; m++) {
                 std::string name = stem + numbered("_Model_", m, "", 6);
                 if (addModelName) name += "_" + baseName(models_[m].path);
-                saveAsPly(name + ext, surf[m].v, surf[m].f);
+                saveAsPly(name + ext, verts(m), surfFaces_[m]);
             }
         }
     };
@@ -311,18 +386,13 @@ void VBDPhysicsB200::writeOutputs(const std::string& outFolder, int frameId) {
             writePly(outFolder + "/TemplateMesh/TemplateMesh.ply", false, true);
         }
         std::ofstream out(outFile, std::ios::out | std::ios::binary);
-        for (int m = 0; m < nM; m++) out.write(reinterpret_cast<const char*>(surf[m].v.data()), (std::streamsize)(surf[m].v.size() * sizeof(float)));
+        out.write(reinterpret_cast<const char*>(surfAll), (std::streamsize)(3 * surfOffset_[nM] * sizeof(float)));
         out.close();
         if (!(frameId % run_.binaryModeVisualizationSteps)) writePly(outFolder + "/" + numbered("A", frameId, ".ply"), run_.saveAllModelsTogether, run_.saveAllModelsTogether);
     } else if (run_.outputExt == "ply") {
         writePly(outFile, run_.saveAllModelsTogether, run_.saveAllModelsTogether);
     } else {
         std::cout << "[Error] Unsupported output EXT name: " << run_.outputExt << std::endl;
-        return;
-    }
-    if (run_.outputRecoveryState && !(frameId % run_.outputRecoveryStateStep)) {
-        createFolder(outFolder + "/RecoveryStates");
-        saveRecoveryState(outFolder + "/RecoveryStates/" + numbered("A", frameId, ".json"), run_.outputRecoveryStateBinary);
     }
 }
 

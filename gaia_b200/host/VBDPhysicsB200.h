@@ -17,6 +17,10 @@
 //   ${REPO_ROOT} substitution                                              M/Parser/InputHandler.h:139-183
 // The viewer (polyscope / OpenGL) is not part of the path: unavailable on this box.
 #pragma once
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
 #include <cstdint>
 #include <map>
 #include <string>
@@ -86,6 +90,21 @@ public:
 
 private:
     void check(int rc, const char* what);
+    // frame files are written by a second thread from the library's page-locked snapshot ring (two slots): the step of frame
+    // f+1 is enqueued while frame f is still being copied and written (FileIO.cpp's writers run inside the frame loop)
+    void writeFrameFiles(const std::string& outFolder, int frameId, const float* surfAll);
+    void submitFrame(int frameId);
+    void writerLoop();
+    void finishWriter();
+    std::thread writer_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<std::pair<int, int>> jobs_;      // (slot, frame id)
+    bool slotBusy_[2] = {false, false};
+    bool stopWriter_ = false;
+    std::string writerError_;
+    std::vector<std::vector<int32_t>> surfFaces_;   // per mesh: surface faces as indices into the surface vertex list (static)
+    std::vector<int64_t> surfOffset_;                // per mesh: first surface vertex in the concatenated snapshot
     void loadTetMesh(const std::string& path, HostMeshData& out);
     std::string resolve(const std::string& p) const;
 

@@ -131,8 +131,8 @@ WORKLOADS = {
     "drop_pile_8": lambda: workload_drop_pile(8, grid=(2, 2), preroll=30),
     # SURVEY.md §8(d) cfg 5 shape: many replicated models on a jittered lattice, 2 substeps x 20 iterations, DCD + CCD
     "drop_pile_512": lambda: workload_drop_pile(512, grid=(8, 8), substeps=2, iterations=20, preroll=20),
-    "drop_pile_4096": lambda: workload_drop_pile(4096, grid=(16, 16), substeps=2, iterations=20, preroll=10),
-    "cloth_1m": lambda: workload_cloth_drape(1000),
+    "drop_pile_4096": lambda: workload_drop_pile(4096, grid=(16, 16), substeps=2, iterations=20, preroll=60),
+    "cloth_1m": lambda: workload_cloth_drape(1000, preroll=12),
     "cloth_250k": lambda: workload_cloth_drape(500, width=50.0, sphere_level=4),
     "cloth_small": lambda: workload_cloth_drape(120, width=12.0, substeps=4, iterations=6, sphere_level=2),
 }

@@ -230,8 +230,17 @@ int gaia_b200_get_prev_positions(gaia_handle* h, int mesh, float* xyz);
 int gaia_b200_get_velocities(gaia_handle* h, int mesh, float* xyz);
 int gaia_b200_get_inertia(gaia_handle* h, int mesh, float* xyz);
 int gaia_b200_set_state(gaia_handle* h, int mesh, const float* pos, const float* vel);
-/* surface positions in writeAllToBinary order (M/IO/FileIO.cpp:52-83) */
+/* surface positions in writeAllToBinary order (M/IO/FileIO.cpp:52-83): gathered on the device, only the surface crosses PCIe */
 int gaia_b200_get_surface_positions(gaia_handle* h, int mesh, float* xyz);
+/* Frame output without stalling the step (writeAllToBinary / writeAllToPLY, M/IO/FileIO.cpp:52-185, feed on exactly this
+ * data). snapshot_begin enqueues, behind everything already enqueued, a device-side gather of ALL meshes' surface positions
+ * (meshes concatenated, the file order) and its copy into page-locked ring slot `slot` (0 or 1) on a second stream, and
+ * returns at once: the next frame can be enqueued while the copy runs. snapshot_wait blocks until that slot has landed and
+ * returns the ring buffer (valid until the slot's next snapshot_begin) - it may be called from another host thread, e.g. a
+ * writer thread. total_surface_vertices sizes the files. */
+int64_t gaia_b200_total_surface_vertices(const gaia_handle* h);
+int gaia_b200_surface_snapshot_begin(gaia_handle* h, int slot);
+int gaia_b200_surface_snapshot_wait(gaia_handle* h, int slot, const float** xyz, int64_t* nFloats);
 /* whole-scene transfers: all meshes concatenated in mesh order (one D2H / H2D) */
 int64_t gaia_b200_total_vertices(const gaia_handle* h);
 int gaia_b200_get_all_positions(gaia_handle* h, float* xyz);

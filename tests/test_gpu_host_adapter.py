@@ -91,3 +91,23 @@ def test_ply_output_and_text_recovery_state(tmp_path):
     txt = np.array(st["meshesState"][0]["position"] + st["meshesState"][1]["position"], np.float32)
     assert np.allclose(txt, allpos, rtol=0, atol=1e-6)
     scene.close()
+
+
+@pytest.mark.gpu
+def test_surface_snapshots_are_ordered_behind_the_step_and_match_the_per_mesh_getter():
+    """row f4: gaia_b200_surface_snapshot_begin / _wait - the device-side surface gather into the page-locked two-slot ring.
+    A snapshot taken before a frame keeps showing that state after the next frame was enqueued and snapshotted into the other
+    slot; its contents are the per-mesh surface positions concatenated (writeAllToBinary order)."""
+    from gaia_b200 import capi, meshio
+    from conftest import make_contact_scene
+    g = make_contact_scene(capi.Scene, n_objects=3)
+    g.run_frames(2)
+    before = np.concatenate([g.surface_positions(m) for m in range(3)])
+    g.surface_snapshot_begin(0)
+    g.run_frames(1)                       # enqueued behind the snapshot
+    g.surface_snapshot_begin(1)
+    s0, s1 = g.surface_snapshot_wait(0), g.surface_snapshot_wait(1)
+    after = np.concatenate([g.surface_positions(m) for m in range(3)])
+    assert np.array_equal(s0, before) and np.array_equal(s1, after) and not np.array_equal(s0, s1)
+    for m in range(3):                    # the per-mesh getter picks the surface out of all positions the same way
+        assert np.array_equal(g.surface_positions(m), g.positions(m)[g.surface_vertex_ids(m)])
