@@ -376,6 +376,7 @@ def load_library(path=None):
     lib.gaia_b200_color_graph.argtypes = [C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
+    lib.gaia_b200_color_graph_device.argtypes = [C.c_int, C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
         getattr(lib, "gaia_b200_" + f).restype = None
@@ -526,6 +527,22 @@ def color_graph(num_nodes, edges, balance=True, goal_max_min_ratio=1.05, algorit
     e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
     return _categories(load_library().gaia_b200_color_graph, int(num_nodes), int(num_nodes), len(e), _ip(e), _color_flags(balance, algorithm),
                        float(goal_max_min_ratio))
+
+
+def color_graph_device(num_nodes, edges, balance=True, goal_max_min_ratio=1.05, device=0):
+    """colour categories computed on the GPU (gaia_b200_color_graph_device): valid, few, balanced colours - not the tool's"""
+    e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
+    fn = load_library().gaia_b200_color_graph_device
+    return _categories(lambda *a: fn(int(device), *a), int(num_nodes), int(num_nodes), len(e), _ip(e), 1 if balance else 0, float(goal_max_min_ratio))
+
+
+def tet_mesh_edges(n_verts, tets):
+    """unique undirected edges of the tet-mesh vertex graph (M/GraphColoring/TetMeshVertexGraph.h)"""
+    t = np.asarray(tets, np.int64).reshape(-1, 4)
+    e = np.concatenate([t[:, [a, b]] for a in range(4) for b in range(a + 1, 4)])
+    e = np.sort(e, axis=1)
+    key = np.unique(e[:, 0] * int(n_verts) + e[:, 1])
+    return np.stack([key // int(n_verts), key % int(n_verts)], 1).astype(np.int32)
 
 
 def color_tet_mesh(n_verts, tets, balance=True, goal_max_min_ratio=1.05, algorithm="greedy"):

@@ -346,6 +346,12 @@ int gaia_b200_color_tet_mesh(int32_t nV, int32_t nT, const int32_t* tets, int32_
                              int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
 int gaia_b200_color_tri_mesh(int32_t nV, int32_t nF, const int32_t* faces, int32_t edgeEnergy, int32_t balance, float goalMaxMinRatio,
                              int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
+/* The same contract computed ON THE DEVICE `device` (csrc/coloring_gpu.cu): deterministic speculative greedy (largest degree
+ * first) + batched largest-to-smallest balancing; for graphs too large for an offline pass and for re-colouring generated or
+ * partitioned meshes. A valid colouring with few, balanced colours - NOT the tool's colours (use the host calls above where
+ * the tool's exact output matters). flags: GAIA_COLOR_BALANCE. At most 64 colours (GAIA_ERR_UNSUPPORTED beyond). */
+int gaia_b200_color_graph_device(int device, int32_t numNodes, int64_t nEdges, const int32_t* edges, int32_t flags, float goalMaxMinRatio,
+                                 int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
 
 #ifdef __cplusplus
 }
