@@ -29,6 +29,7 @@ namespace gb {
 
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 static const int kB = 128;
+static const int kCand = 64;        // DCD candidate cache: tets kept per surface vertex between refits (k_dcd_phase1)
 static inline int nblk(int64_t n, int per = kB) { return (int)((n + per - 1) / per); }
 // grid of a grid-stride kernel: at most one full wave of 148 SMs x 16 blocks (a launch that decides on the device to do nothing costs one wave)
 static inline int capped(int64_t n, int per = kB) { return (int)std::min<int64_t>((n + per - 1) / per, 148 * 16); }
@@ -276,6 +277,7 @@ struct CollisionState {
     Lbvh tetBvh, surfBvh, ccdBvh;
     DevBuf<float4> refPos;        // lazy refit of the DCD trees: positions their boxes were computed at
     DevBuf<int32_t> needRefit;    // device flag: some vertex left its margin (or a rebuild forces the refit)
+    DevBuf<int32_t> candCount, cand;   // per surface vertex: tets it can enter before the next refit (k_dcd_phase1), -1 = too many
     float lazyMargin = 0.f;
     DevBuf<int32_t> boundsOrd;    // 6 * (nMeshes + 1)
     DevBuf<float> normBox;        // 6 * (nMeshes + 1)
@@ -358,11 +360,13 @@ cudaError_t collision_init(Scene& s) {
     if (s.col.allowDCD) {
         CK(c->tetBvh.alloc((int)nT, oneSegT)); CK(c->surfBvh.alloc((int)nF, faceSegs));
         CK(c->refPos.alloc(N + 1)); CK(c->needRefit.alloc(1));
-        // margin = a tenth of the typical tet edge (cube root of 6 x the mean rest volume): refits become rare for slowly
-        // deforming bodies while the boxes - and with them the number of nodes a query visits - grow by a few per cent only
+        CK(c->candCount.alloc(std::max<int64_t>(nS, 1))); CK(c->cand.alloc((size_t)std::max<int64_t>(nS, 1) * kCand));
+        CK(cudaMemset(c->candCount.p, 0xff, std::max<int64_t>(nS, 1) * sizeof(int32_t)));
+        // margin = a fifth of the typical tet edge (cube root of 6 x the mean rest volume): refits become rare for slowly
+        // deforming bodies; the larger boxes cost little because between refits queries run from the candidate cache
         double vol = 0.0; int64_t cnt = 0;
         for (auto& m : s.meshes) for (float v : m.restVol) { vol += std::fabs((double)v); cnt++; }
-        c->lazyMargin = cnt ? 0.1f * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
+        c->lazyMargin = cnt ? 0.2f * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
     }
     if (s.col.allowCCD) CK(c->ccdBvh.alloc((int)nF, oneSegF));
     const size_t nM = s.meshes.size();
@@ -459,11 +463,18 @@ static const int kStack = 64;
 // the smallest containing tet id is warp-reduced at the end. A point on the surface of a regular mesh sits in the boxes of
 // ~50 tets and of their ancestors, ~250 node visits that one thread would walk one dependent load after the other.
 static const int kFrontier = 384;          // frontier capacity per warp (overflow -> errFlags[3], like the traversal stacks)
+// Candidate cache (goes with the lazy refit): when the trees are refitted (*need == 1) every surface vertex keeps the ids of
+// the tets it could possibly enter before the next refit - the non-incident tets whose lazy box, inflated by the margin once
+// more, holds the vertex: both the vertex and the tet stay within `margin` of where they are now for as long as the refit is
+// skipped. Between refits a detection only tests those ~30 tets per vertex instead of walking the 10 M-leaf tree; the set is
+// a superset of the tets a fresh traversal would test, and the tests themselves are the same, so results do not change.
+// A vertex whose candidates do not fit (kCand) keeps walking the tree.
 __global__ void __launch_bounds__(kB)
 k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const int32_t* __restrict__ surfSid, const int32_t* __restrict__ surfMesh,
              const MeshParamsDev* __restrict__ mp, const float4* __restrict__ pos, const int4* __restrict__ tetSid,
              const int32_t* __restrict__ tetMesh, uint8_t* penetrated, int32_t* cNum, int32_t* cHitTet, int32_t* cFace, int32_t* cFlags,
-             int32_t* hitList, int32_t* nHits, int32_t* errFlags) {
+             int32_t* hitList, int32_t* nHits, int32_t* errFlags, const int32_t* __restrict__ need, float margin, int32_t* candCount,
+             int32_t* cand) {
     __shared__ int32_t frontierAll[(kB / 32) * kFrontier];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* frontier = frontierAll + warp * kFrontier;
@@ -473,17 +484,30 @@ k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const in
     if (!mp[mesh].activeCollide) return;
     const int s = surfSid[slot];
     const V3 p = v3(pos[s]);
-    if (intermediate) {
-        if (!(penetrated[slot] || !cp.allowCCD)) return;
-    } else {
+    const bool collect = *need != 0;             // the trees were refitted for this detection: rebuild this vertex's candidates
+    bool queried = true;
+    if (intermediate) queried = penetrated[slot] || !cp.allowCCD;
+    else {
         if (lane == 0) penetrated[slot] = 0;
-        if (!(p.y < cp.offHeight)) return;
+        queried = p.y < cp.offHeight;
     }
+    if (!queried && !collect) return;
     int best = 0x7FFFFFFF;
-    if (bv.n > 0) {
-        // the frontier only ever holds nodes whose box contains the point: children are tested before they are queued
+    const int cached = collect ? -1 : candCount[slot];
+    if (cached >= 0) {
+        for (int i = lane; i < cached; i += 32) {
+            const int t = cand[(size_t)slot * kCand + i];
+            const int4 tv = __ldg(tetSid + t);
+            if (t < best && point_in_tet(p, v3(pos[tv.x]), v3(pos[tv.y]), v3(pos[tv.z]), v3(pos[tv.w]))) best = t;
+        }
+    } else if (bv.n > 0) {
+        // the frontier only ever holds nodes whose box (inflated by m2) contains the point: children are tested before they are queued
+        const float m2 = collect ? margin : 0.f;
+        const V3 pLo = v3(p.x - m2, p.y - m2, p.z - m2), pHi = v3(p.x + m2, p.y + m2, p.z + m2);
+        auto holds = [&](float4 lo, float4 hi) { return pHi.x >= lo.x && pLo.x <= hi.x && pHi.y >= lo.y && pLo.y <= hi.y && pHi.z >= lo.z && pLo.z <= hi.z; };
         const int root = bv.n > 1 ? 0 : bv.n;               // single-leaf scene: the leaf itself
-        int qn = box_contains(bv.box[2 * root], bv.box[2 * root + 1], p) ? 1 : 0;
+        int qn = holds(bv.box[2 * root], bv.box[2 * root + 1]) ? 1 : 0;
+        int nCand = 0;
         if (lane == 0) frontier[0] = root;
         __syncwarp();
         while (qn > 0) {
@@ -492,33 +516,41 @@ k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const in
             if (lane < m) node = frontier[qn - 1 - lane];
             qn -= m;
             __syncwarp();
-            int c0 = -1, c1 = -1;
+            int c0 = -1, c1 = -1, keep = -1;
             if (node >= bv.n) {
                 const int t = bv.order[node - bv.n];
                 const int g = tetMesh[t];
-                if (t < best && (cp.handleSelfCollision || g != mesh)) {
+                if (cp.handleSelfCollision || g != mesh) {
                     const int4 tv = __ldg(tetSid + t);
-                    if (!(g == mesh && (tv.x == s || tv.y == s || tv.z == s || tv.w == s)) &&
-                        point_in_tet(p, v3(pos[tv.x]), v3(pos[tv.y]), v3(pos[tv.z]), v3(pos[tv.w]))) best = t;
+                    if (!(g == mesh && (tv.x == s || tv.y == s || tv.z == s || tv.w == s))) {
+                        keep = t;
+                        if (queried && t < best && point_in_tet(p, v3(pos[tv.x]), v3(pos[tv.y]), v3(pos[tv.z]), v3(pos[tv.w]))) best = t;
+                    }
                 }
             } else if (node >= 0) {
                 const int2 ch = bv.child[node];
-                const float4 l0 = bv.box[2 * ch.x], h0 = bv.box[2 * ch.x + 1], l1 = bv.box[2 * ch.y], h1 = bv.box[2 * ch.y + 1];
-                if (box_contains(l0, h0, p)) c0 = ch.x;
-                if (box_contains(l1, h1, p)) c1 = ch.y;
+                if (holds(bv.box[2 * ch.x], bv.box[2 * ch.x + 1])) c0 = ch.x;
+                if (holds(bv.box[2 * ch.y], bv.box[2 * ch.y + 1])) c1 = ch.y;
+            }
+            if (collect) {
+                const unsigned km = __ballot_sync(0xffffffffu, keep >= 0);
+                if (keep >= 0) { const int at = nCand + __popc(km & ((1u << lane) - 1u)); if (at < kCand) cand[(size_t)slot * kCand + at] = keep; }
+                nCand += __popc(km);
             }
             const int mine = (c0 >= 0) + (c1 >= 0);
             int incl = mine;                                 // inclusive prefix sum of the pushes over the warp
             for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
             const int nPush = __shfl_sync(0xffffffffu, incl, 31);
-            if (qn + nPush > kFrontier) { if (lane == 0) atomicAdd(errFlags + 3, 1); break; }
+            if (qn + nPush > kFrontier) { if (lane == 0) atomicAdd(errFlags + 3, 1); nCand = kCand + 1; break; }
             int at = qn + incl - mine;
             if (c0 >= 0) frontier[at++] = c0;
             if (c1 >= 0) frontier[at] = c1;
             qn += nPush;
             __syncwarp();
         }
+        if (collect && lane == 0) candCount[slot] = nCand <= kCand ? nCand : -1;
     }
+    if (!queried) return;
     for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
     if (lane) return;
     // CollisionDetectionResult::clear() + the new result
@@ -836,7 +868,7 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
         TopoView tp{c->tetSid.p, c->tetNbr.p, c->faceSid.p, c->faceInfo.p, c->faceNbr.p, c->surfNbrOff.p, c->surfNbr.p, c->slotOfSorted.p};
         k_dcd_phase1<<<nblk((int64_t)nS * 32), kB, 0, s.stream>>>(nS, intermediate ? 1 : 0, c->cp, view_of(c->tetBvh), c->surfSid.p, c->surfMesh.p, s.meshParams.p,
                                                   s.pos.p, c->tetSid.p, c->tetMesh.p, c->penetrated.p, c->cNum.p, c->cHitTet.p, c->cFace.p,
-                                                  c->cFlags.p, c->hitList.p, nHits, s.errFlags.p);
+                                                  c->cFlags.p, c->hitList.p, nHits, s.errFlags.p, c->needRefit.p, c->lazyMargin, c->candCount.p, c->cand.p);
         // phase 2 runs over the compacted hit list; its length stays on the device (grid sized for the worst case, early exit)
         int32_t hits = 0;
         CK(cudaMemcpyAsync(&hits, nHits, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
