@@ -377,6 +377,20 @@ def load_library(path=None):
     lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_graph_device.argtypes = [C.c_int, C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
+    I64P, U8P = C.POINTER(C.c_int64), C.POINTER(C.c_uint8)
+    lib.gaia_b200_partition_slab_owner.argtypes = [C.c_int32, FP, C.c_int32, C.c_int32, IP]
+    lib.gaia_b200_partition_create.argtypes = [C.c_int32, C.c_int64, IP, IP, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]
+    lib.gaia_b200_partition_destroy.argtypes = [C.c_void_p]; lib.gaia_b200_partition_destroy.restype = None
+    lib.gaia_b200_partition_sizes.argtypes = [C.c_void_p, IP, I64P, IP]
+    lib.gaia_b200_partition_local_verts.argtypes = [C.c_void_p, IP, U8P]
+    lib.gaia_b200_partition_local_tets.argtypes = [C.c_void_p, IP, I64P]
+    lib.gaia_b200_partition_peer.argtypes = [C.c_void_p, C.c_int32, IP, IP, IP]
+    lib.gaia_b200_partition_peer_lists.argtypes = [C.c_void_p, C.c_int32, IP, IP]
+    lib.gaia_b200_partition_restrict_ids.argtypes = [C.c_void_p, C.c_int32, IP, IP]
+    lib.gaia_b200_partition_restrict_colors.argtypes = [C.c_void_p, C.c_int32, IP, IP, IP, IP]
+    lib.gaia_b200_tet_surface.argtypes = [C.c_int32, C.c_int32, IP, IP, IP, IP, IP]
+    lib.gaia_b200_halo_local_pointers.argtypes = [P, C.c_void_p]
+    lib.gaia_b200_halo_add_peer_pointers.argtypes = [P, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, IP, IP]
     lib.gaia_b200_cuda_stream.argtypes = [P]; lib.gaia_b200_cuda_stream.restype = C.c_void_p
     for f in ("default_physics_params", "default_collision_params", "default_object_params"):
         getattr(lib, "gaia_b200_" + f).restype = None
@@ -555,3 +569,85 @@ def color_tri_mesh(n_verts, faces, edge_energy=True, balance=True, goal_max_min_
     f = _i32(np.asarray(faces, np.int32).reshape(-1, 3))
     return _categories(load_library().gaia_b200_color_tri_mesh, int(n_verts), int(n_verts), len(f), _ip(f), 1 if edge_energy else 0,
                        _color_flags(balance, algorithm), float(goal_max_min_ratio))
+
+
+# --------------------------------------------------------------------------------------------- slab partitioning (csrc/partition.cpp)
+def partition_slab_owner(verts, world, axis=-1):
+    v = _f32(np.asarray(verts, np.float32).reshape(-1, 3))
+    owner = np.zeros(len(v), np.int32)
+    rc = load_library().gaia_b200_partition_slab_owner(len(v), _fp(v), int(world), int(axis), _ip(owner))
+    if rc < 0:
+        raise GaiaError(f"gaia_b200_partition_slab_owner failed: {rc}")
+    return owner
+
+
+class SlabPartition:
+    """What rank `rank` holds of one global tet mesh: binding of gaia_b200_partition_* (see include/gaia_b200.h)."""
+
+    def __init__(self, n_verts, tets, owner, rank, world):
+        lib = load_library()
+        t = _i32(np.asarray(tets, np.int32).reshape(-1, 4)); o = _i32(np.asarray(owner, np.int32))
+        self._p = C.c_void_p()
+        rc = lib.gaia_b200_partition_create(int(n_verts), len(t), _ip(t), _ip(o), int(rank), int(world), C.byref(self._p))
+        if rc < 0:
+            raise GaiaError(f"gaia_b200_partition_create failed: {rc}")
+        self._lib, self.rank, self.world = lib, rank, world
+        nv, nt, npeer = C.c_int32(), C.c_int64(), C.c_int32()
+        lib.gaia_b200_partition_sizes(self._p, C.byref(nv), C.byref(nt), C.byref(npeer))
+        self.local_verts = np.zeros(nv.value, np.int32); owned = np.zeros(nv.value, np.uint8)
+        lib.gaia_b200_partition_local_verts(self._p, _ip(self.local_verts), owned.ctypes.data_as(C.POINTER(C.c_uint8)))
+        self.owned = owned.astype(bool)
+        self.tets = np.zeros((nt.value, 4), np.int32); self.local_tets = np.zeros(nt.value, np.int64)
+        lib.gaia_b200_partition_local_tets(self._p, _ip(self.tets), self.local_tets.ctypes.data_as(C.POINTER(C.c_int64)))
+        self.send, self.recv = {}, {}
+        for i in range(npeer.value):
+            q, ns, nr = C.c_int32(), C.c_int32(), C.c_int32()
+            lib.gaia_b200_partition_peer(self._p, i, C.byref(q), C.byref(ns), C.byref(nr))
+            s_, r_ = np.zeros(max(ns.value, 1), np.int32), np.zeros(max(nr.value, 1), np.int32)
+            lib.gaia_b200_partition_peer_lists(self._p, i, _ip(s_), _ip(r_))
+            if ns.value:
+                self.send[q.value] = s_[:ns.value]
+            if nr.value:
+                self.recv[q.value] = r_[:nr.value]
+
+    def restrict_ids(self, ids):
+        g = _i32(np.asarray(ids, np.int32))
+        out = np.zeros(max(len(g), 1), np.int32)
+        k = self._lib.gaia_b200_partition_restrict_ids(self._p, len(g), _ip(g), _ip(out))
+        if k < 0:
+            raise GaiaError(f"gaia_b200_partition_restrict_ids failed: {k}")
+        return out[:k]
+
+    def restrict_colors(self, colors):
+        offs = np.zeros(len(colors) + 1, np.int32)
+        offs[1:] = np.cumsum([len(c) for c in colors])
+        flat = _i32(np.concatenate([np.asarray(c, np.int32) for c in colors]) if len(colors) else np.zeros(0, np.int32))
+        oo = np.zeros(len(colors) + 1, np.int32); ov = np.zeros(max(len(self.local_verts), 1), np.int32)
+        rc = self._lib.gaia_b200_partition_restrict_colors(self._p, len(colors), _ip(offs), _ip(flat), _ip(oo), _ip(ov))
+        if rc < 0:
+            raise GaiaError(f"gaia_b200_partition_restrict_colors failed: {rc}")
+        return [ov[oo[c]:oo[c + 1]].copy() for c in range(len(colors))]
+
+    def close(self):
+        if self._p:
+            self._lib.gaia_b200_partition_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def tet_surface(n_verts, tets):
+    """(surfaceVIds, surfaceFaces[nF,3]) of a tet mesh in the reference's orderings, no device needed"""
+    lib = load_library()
+    t = _i32(np.asarray(tets, np.int32).reshape(-1, 4))
+    nv, nf = C.c_int32(), C.c_int32()
+    rc = lib.gaia_b200_tet_surface(int(n_verts), len(t), _ip(t), C.byref(nv), None, C.byref(nf), None)
+    if rc < 0:
+        raise GaiaError(f"gaia_b200_tet_surface failed: {rc}")
+    ids = np.zeros(nv.value, np.int32); faces = np.zeros((nf.value, 3), np.int32)
+    lib.gaia_b200_tet_surface(int(n_verts), len(t), _ip(t), C.byref(nv), _ip(ids), C.byref(nf), _ip(faces))
+    return ids, faces

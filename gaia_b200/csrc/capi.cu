@@ -474,10 +474,48 @@ int gaia_b200_halo_add_peer(gaia_handle* h, int32_t peerRank, const void* peerHa
     cudaError_t e = halo_add_peer(s, peerRank, peerHandles128, nSend, sendMeshVerts, remoteSlots);
     return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
 }
+int gaia_b200_halo_local_pointers(gaia_handle* h, void* out16) {
+    REQUIRE(h); FINALIZED(h);
+    if (!out16) return GAIA_ERR_INVALID_ARG;
+    cudaSetDevice(h->s.device);
+    const cudaError_t e = halo_local_pointers(h->s, out16);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(h->s, e);
+}
+int gaia_b200_halo_add_peer_pointers(gaia_handle* h, int32_t peerRank, int32_t peerDevice, const void* peerPointers16, int32_t nSend,
+                                     const int32_t* sendMeshVerts, const int32_t* remoteSlots) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (!peerPointers16 || nSend < 0 || (nSend && (!sendMeshVerts || !remoteSlots)) || peerRank < 0 || peerRank >= s.worldSize || peerRank == s.myRank)
+        return fail(s, GAIA_ERR_INVALID_ARG, "bad halo peer argument");
+    for (int i = 0; i < nSend; i++) {
+        const int mm = sendMeshVerts[2 * i], v = sendMeshVerts[2 * i + 1];
+        if (mm < 0 || mm >= (int)s.meshes.size() || v < 0 || v >= s.meshes[mm].nV) return fail(s, GAIA_ERR_INVALID_ARG, "halo send vertex out of range");
+    }
+    cudaSetDevice(s.device);
+    const cudaError_t e = halo_add_peer(s, peerRank, nullptr, nSend, sendMeshVerts, remoteSlots, peerPointers16, peerDevice);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
+}
 int gaia_b200_halo_finalize(gaia_handle* h) {
     REQUIRE(h); FINALIZED(h);
     cudaError_t e = halo_finalize(h->s);
     return e == cudaSuccess ? GAIA_OK : cuda_fail(h->s, e);
+}
+
+int gaia_b200_tet_surface(int32_t nV, int32_t nT, const int32_t* tets, int32_t* nSurfV, int32_t* surfaceVIds, int32_t* nSurfF, int32_t* surfaceFaces) {
+    if (nV <= 0 || nT <= 0 || !tets) return GAIA_ERR_INVALID_ARG;
+    for (int64_t i = 0; i < 4 * (int64_t)nT; i++) if (tets[i] < 0 || tets[i] >= nV) return GAIA_ERR_INVALID_ARG;
+    HostMesh m;
+    std::vector<float> zeros(3 * (size_t)nV, 0.f);
+    for (int v = 0; v < nV; v++) { zeros[3 * (size_t)v] = (float)v; }      // positions do not matter for the topology
+    gaia_object_params obj;
+    gaia_b200_default_object_params(&obj);
+    const int32_t offs[2] = {0, 0};
+    host_mesh_init(m, nV, nT, zeros.data(), tets, obj, 0, offs, nullptr, 0, nullptr, true);
+    if (nSurfV) *nSurfV = m.nSurfV();
+    if (nSurfF) *nSurfF = m.nSurfF();
+    if (surfaceVIds) std::copy(m.surfaceVIds.begin(), m.surfaceVIds.end(), surfaceVIds);
+    if (surfaceFaces) std::copy(m.surfFaces.begin(), m.surfFaces.end(), surfaceFaces);
+    return GAIA_OK;
 }
 
 int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out) {

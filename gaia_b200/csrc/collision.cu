@@ -436,7 +436,8 @@ static cudaError_t update_bvh(Scene& s, Lbvh& b, bool rebuild, bool segmented, f
         b.built = true;
         CK(cudaMemsetAsync(b.flags.p, 0, (size_t)b.n * sizeof(int32_t), s.stream));     // (refits leave the counters at zero)
     }
-    k_refit<<<nblk(b.n), kB, 0, s.stream>>>(b.n, b.order.p, b.primLo.p, b.primHi.p, b.child.p, b.parent.p, b.box.p, b.flags.p, need);
+    // (512-thread blocks: a refit the device decides to skip costs one look at the flag per block)
+    k_refit<<<nblk(b.n, 512), 512, 0, s.stream>>>(b.n, b.order.p, b.primLo.p, b.primHi.p, b.child.p, b.parent.p, b.box.p, b.flags.p, need);
     s.stats.kernelLaunches++;
     return cudaGetLastError();
 }

@@ -183,7 +183,9 @@ int check_device_errors(Scene& s);
 
 // halo.cu
 cudaError_t halo_ipc_handles(Scene& s, void* out128);
-cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nSend, const int32_t* sendMeshVerts, const int32_t* remoteSlots);
+cudaError_t halo_local_pointers(Scene& s, void* out16);
+cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nSend, const int32_t* sendMeshVerts, const int32_t* remoteSlots,
+                          const void* pointers16 = nullptr, int peerDevice = -1);
 cudaError_t halo_finalize(Scene& s);
 void halo_destroy(Scene& s);
 bool halo_active(const Scene& s);

@@ -345,23 +345,26 @@ void VBDPhysicsB200::writeOutputs(const std::string& outFolder, int frameId) {
     }
 }
 
+void VBDPhysicsB200::fetchSurfaceTopology() {      // faces as indices into the surface vertex list, per mesh
+    const int nM = gaia_b200_num_meshes(h_);
+    surfFaces_.assign(nM, {}); surfOffset_.assign(nM + 1, 0);
+    for (int m = 0; m < nM; m++) {
+        int32_t nV, nT, nSV, nSF;
+        check(gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF), "gaia_b200_mesh_sizes");
+        std::vector<int32_t> ids(nSV), faces(3 * (size_t)nSF), toSurf(nV, -1);
+        check(gaia_b200_get_surface_vertex_ids(h_, m, ids.data()), "gaia_b200_get_surface_vertex_ids");
+        check(gaia_b200_get_surface_faces(h_, m, faces.data()), "gaia_b200_get_surface_faces");
+        for (int i = 0; i < nSV; i++) toSurf[ids[i]] = i;
+        surfFaces_[m].resize(faces.size());
+        for (size_t i = 0; i < faces.size(); i++) surfFaces_[m][i] = toSurf[faces[i]];
+        surfOffset_[m + 1] = surfOffset_[m] + nSV;
+    }
+}
+
 // writeAllToBinary / writeAllToPLY (M/IO/FileIO.cpp:52-185) from one snapshot: surface vertices of all meshes, concatenated
 void VBDPhysicsB200::writeFrameFiles(const std::string& outFolder, int frameId, const float* surfAll) {
-    const int nM = gaia_b200_num_meshes(h_);
-    if ((int)surfFaces_.size() != nM) {      // static topology, fetched once: faces as indices into the surface vertex list
-        surfFaces_.assign(nM, {}); surfOffset_.assign(nM + 1, 0);
-        for (int m = 0; m < nM; m++) {
-            int32_t nV, nT, nSV, nSF;
-            check(gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF), "gaia_b200_mesh_sizes");
-            std::vector<int32_t> ids(nSV), faces(3 * (size_t)nSF), toSurf(nV, -1);
-            check(gaia_b200_get_surface_vertex_ids(h_, m, ids.data()), "gaia_b200_get_surface_vertex_ids");
-            check(gaia_b200_get_surface_faces(h_, m, faces.data()), "gaia_b200_get_surface_faces");
-            for (int i = 0; i < nSV; i++) toSurf[ids[i]] = i;
-            surfFaces_[m].resize(faces.size());
-            for (size_t i = 0; i < faces.size(); i++) surfFaces_[m][i] = toSurf[faces[i]];
-            surfOffset_[m + 1] = surfOffset_[m] + nSV;
-        }
-    }
+    const int nM = (int)models_.size();
+    if ((int)surfFaces_.size() != nM) fetchSurfaceTopology();      // static topology, fetched once
     auto verts = [&](int m) { return std::vector<float>(surfAll + 3 * surfOffset_[m], surfAll + 3 * surfOffset_[m + 1]); };
     auto writePly = [&](const std::string& file, bool together, bool addModelName) {
         if (together) {

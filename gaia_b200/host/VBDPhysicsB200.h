@@ -62,7 +62,7 @@ struct HostRunParams {
 class VBDPhysicsB200 {
 public:
     VBDPhysicsB200() = default;
-    ~VBDPhysicsB200();
+    virtual ~VBDPhysicsB200();
     VBDPhysicsB200(const VBDPhysicsB200&) = delete;
     VBDPhysicsB200& operator=(const VBDPhysicsB200&) = delete;
 
@@ -76,7 +76,7 @@ public:
     void recoverFromState(const std::string& stateFile);
     void runStep();                       // one frame: enableModels + numSubsteps x (collision detection, iterations, velocities)
     void simulate();                      // writeOutputs(0); while frameId < numFrames: runStep, ++frameId, writeOutputs
-    void writeOutputs(const std::string& outFolder, int frameId);
+    virtual void writeOutputs(const std::string& outFolder, int frameId);
     void saveRecoveryState(const std::string& file, bool binary);
     void writeStatistics(const std::string& outFolder, int frameId);
 
@@ -88,8 +88,9 @@ public:
     int frameId() const { return frameId_; }
     const std::string& outputFolder() const { return outputFolder_; }
 
-private:
+protected:
     void check(int rc, const char* what);
+    virtual void fetchSurfaceTopology();          // fills surfFaces_ / surfOffset_ (single GPU: from the handle)
     // frame files are written by a second thread from the library's page-locked snapshot ring (two slots): the step of frame
     // f+1 is enqueued while frame f is still being copied and written (FileIO.cpp's writers run inside the frame loop)
     void writeFrameFiles(const std::string& outFolder, int frameId, const float* surfAll);

@@ -1,6 +1,7 @@
 // gaia_vbd_b200 — command-line driver with the reference's VBDDynamics calling convention (S/VBDDynamics/main.cpp:8-34,
 // M/Parser/Parser.h:7-45):
-//     gaia_vbd_b200 <Models.json> <Parameters.json> <outFolder|noOutput> [-R|--repoRoot DIR] [-r|--recoveryState FILE] [--device N]
+//     gaia_vbd_b200 <Models.json> <Parameters.json> <outFolder|noOutput> [-R|--repoRoot DIR] [-r|--recoveryState FILE] [--device N] [--gpus N]
+// --gpus N (N > 1): the scene's single tet mesh is cut into N slabs, one per GPU of this box (VBDPhysicsB200MultiGPU).
 // --gui is accepted and ignored (no graphics stack on this box); --CPU is refused (this implementation has no CPU path).
 #include <cstdlib>
 #include <cstring>
@@ -8,12 +9,12 @@
 #include <string>
 #include <vector>
 
-#include "VBDPhysicsB200.h"
+#include "VBDPhysicsB200MultiGPU.h"
 
 int main(int argc, char** argv) {
     std::vector<std::string> pos;
     std::string repoRoot, recoveryStateFile;
-    int device = 0;
+    int device = 0, gpus = 1;
     bool dryRun = false;   // parse the inputs and load the meshes, print the scene size, do not touch the GPU
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
@@ -24,6 +25,7 @@ int main(int argc, char** argv) {
         if (a == "-R" || a == "--repoRoot") repoRoot = next("--repoRoot");
         else if (a == "-r" || a == "--recoveryState") recoveryStateFile = next("--recoveryState");
         else if (a == "--device") device = std::atoi(next("--device").c_str());
+        else if (a == "--gpus") gpus = std::atoi(next("--gpus").c_str());
         else if (a == "-g" || a == "--gui") std::cerr << "[gaia_b200] --gui ignored: the viewer needs a graphics stack, unavailable on this box\n";
         else if (a == "--CPU") { std::cerr << "[gaia_b200] --CPU refused: this implementation of the VBD step has no CPU path\n"; return 2; }
         else if (a == "--git") {}
@@ -36,6 +38,17 @@ int main(int argc, char** argv) {
         return -1;
     }
     try {
+        if (gpus > 1) {
+            if (!recoveryStateFile.empty()) { std::cerr << "[gaia_b200] --recoveryState is not supported together with --gpus\n"; return 2; }
+            gaia_b200::VBDPhysicsB200MultiGPU physics(gpus);
+            physics.setRepoRoot(repoRoot);
+            physics.loadRunningparameters(pos[0], pos[1], pos[2]);
+            if (pos[2] == "noOutput") physics.runParams().saveOutputs = false;
+            physics.initialize();
+            std::cout << "----------------------------------------------------\nOutput folder is: " << physics.outputFolder() << " (" << gpus << " GPUs)" << std::endl;
+            physics.simulate();
+            return 0;
+        }
         gaia_b200::VBDPhysicsB200 physics;
         physics.setRepoRoot(repoRoot);
         physics.setDevice(device);

@@ -114,8 +114,11 @@ def build_partitioned_scene(wl, rank, world, local_rank):
     from . import capi
     assert len(wl["meshes"]) == 1, "slab partitioning handles one mesh per scene (many-object scenes shard by object)"
     verts, tets, obj, colors, fixed = wl["meshes"][0]
-    owner = slab_owner(verts, world)
-    part = Partition(verts, tets, owner, rank, world)
+    # partitioning is the library's (csrc/partition.cpp, the same calls the C++ host's --gpus path makes); the numpy
+    # `Partition` above states the same rules independently and is what the CPU tests compare it with
+    owner = capi.partition_slab_owner(verts, world)
+    part = capi.SlabPartition(len(verts), tets, owner, rank, world)
+    part.verts = np.asarray(verts, np.float32)[part.local_verts]
     s = capi.Scene(wl["phys"], wl["col"], device=local_rank)
     add_partition_mesh(s, part, obj, colors, fixed, rank, world)
     for d in wl["deformers"]:

@@ -304,6 +304,32 @@ int gaia_b200_halo_ipc_handles(gaia_handle* h, void* out128);
 int gaia_b200_halo_add_peer(gaia_handle* h, int32_t peerRank, const void* peerHandles128, int32_t nSend,
                             const int32_t* sendMeshVerts, const int32_t* remoteSlots);
 int gaia_b200_halo_finalize(gaia_handle* h);
+/* The same for partitions that live in ONE process (one host thread per GPU, e.g. gaia_vbd_b200 --gpus N): CUDA IPC handles
+ * cannot be opened by the process that made them, so the neighbours' arrays are addressed directly (unified addressing +
+ * cudaDeviceEnablePeerAccess). local_pointers: 16 bytes = the device pointers of the position array and of the flag array. */
+int gaia_b200_halo_local_pointers(gaia_handle* h, void* out16);
+int gaia_b200_halo_add_peer_pointers(gaia_handle* h, int32_t peerRank, int32_t peerDevice, const void* peerPointers16, int32_t nSend,
+                                     const int32_t* sendMeshVerts, const int32_t* remoteSlots);
+
+/* Slab partitioning of one tet mesh (csrc/partition.cpp; host code, no device needed): owner of every vertex, and for one
+ * rank its local mesh (tets with an owned vertex: owned vertices + a one-ring ghost layer, global order kept), the per-peer
+ * send / recv vertex lists (ascending global id on both sides) and the restriction of the global colouring (colour order
+ * kept, the vertices a rank sends first inside every colour). The reference has no counterpart (one device). */
+typedef struct gaia_partition gaia_partition;
+int gaia_b200_partition_slab_owner(int32_t nV, const float* xyz, int32_t world, int32_t axis /* -1: longest */, int32_t* owner);
+int gaia_b200_partition_create(int32_t nV, int64_t nT, const int32_t* tets, const int32_t* owner, int32_t rank, int32_t world, gaia_partition** out);
+void gaia_b200_partition_destroy(gaia_partition* p);
+int gaia_b200_partition_sizes(const gaia_partition* p, int32_t* nLocalV, int64_t* nLocalT, int32_t* nPeers);
+int gaia_b200_partition_local_verts(const gaia_partition* p, int32_t* globalIds, uint8_t* owned);
+int gaia_b200_partition_local_tets(const gaia_partition* p, int32_t* tetsLocalIds, int64_t* globalTetIds);
+int gaia_b200_partition_peer(const gaia_partition* p, int32_t i, int32_t* peerRank, int32_t* nSend, int32_t* nRecv);
+int gaia_b200_partition_peer_lists(const gaia_partition* p, int32_t i, int32_t* sendLocal, int32_t* recvLocal);
+int gaia_b200_partition_restrict_ids(const gaia_partition* p, int32_t n, const int32_t* globalIds, int32_t* localOut);
+int gaia_b200_partition_restrict_colors(const gaia_partition* p, int32_t nColors, const int32_t* offsets, const int32_t* verts,
+                                        int32_t* outOffsets, int32_t* outVerts);
+/* Surface of a tet mesh without a device (the orderings writeAllToBinary / writeAllToPLY use): call with NULL outputs for the
+ * counts. surfaceVIds ascending; surfaceFaces: 3 tet-mesh vertex ids per face, in the reference's face order. */
+int gaia_b200_tet_surface(int32_t nV, int32_t nT, const int32_t* tets, int32_t* nSurfV, int32_t* surfaceVIds, int32_t* nSurfF, int32_t* surfaceFaces);
 
 /* statistics */
 int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out);

@@ -22,7 +22,8 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    wl = bench.workload_twist_beam(40, 6, 6)
+    dims = [int(x) for x in os.environ.get("GAIA_CHECK_DIMS", "40,6,6").split(",")]
+    wl = bench.workload_twist_beam(*dims)
     s = multigpu.build_partitioned_scene(wl, rank, world, local)
     frames = 3
     s.run_frames(frames)

@@ -266,3 +266,42 @@ def test_object_sharded_oracle_equals_single_bit_exact(tmp_path, world):
             assert np.array_equal(p, o.positions(k)), (r, k, np.abs(p - o.positions(k)).max())
             seen.add(k)
     assert seen == set(range(6))
+
+
+def test_cpp_partitioner_matches_the_python_one():
+    """gaia_b200_partition_* (csrc/partition.cpp, what the C++ multi-GPU host and multigpu.py use) against the numpy statement
+    in multigpu.Partition: owners, local meshes, owned masks, send / recv lists and restricted colourings identical."""
+    from gaia_b200 import capi, meshio, multigpu
+    for (nx, ny, nz), world in (((24, 4, 4), 2), ((40, 3, 5), 4), ((9, 7, 3), 3)):
+        v, t = meshio.kuhn_beam(nx, ny, nz, h=0.1)
+        colors = meshio.kuhn_coloring(nx, ny, nz)
+        owner_py = multigpu.slab_owner(v, world)
+        owner_c = capi.partition_slab_owner(v, world)
+        assert np.array_equal(owner_py, owner_c)
+        for rank in range(world):
+            a = multigpu.Partition(v, t, owner_py, rank, world)
+            b = capi.SlabPartition(len(v), t, owner_c, rank, world)
+            assert np.array_equal(a.local_verts, b.local_verts) and np.array_equal(a.local_tets, b.local_tets)
+            assert np.array_equal(a.tets, b.tets) and np.array_equal(a.owned, b.owned)
+            assert sorted(a.send) == sorted(b.send) and sorted(a.recv) == sorted(b.recv)
+            for q in a.send:
+                assert np.array_equal(a.send[q], b.send[q])
+            for q in a.recv:
+                assert np.array_equal(a.recv[q], b.recv[q])
+            ca, cb = a.restrict_colors(colors), b.restrict_colors(colors)
+            assert len(ca) == len(cb) and all(np.array_equal(x, y) for x, y in zip(ca, cb))
+            fixed = np.arange(0, len(v), 7, dtype=np.int32)
+            assert np.array_equal(a.restrict_ids(fixed), b.restrict_ids(fixed))
+            b.close()
+
+
+def test_tet_surface_without_a_device_matches_the_oracle():
+    from gaia_b200 import capi, meshio
+    from gaia_b200.workloads import ref_mesh
+    from oracle.binding import OracleScene
+    for v, t in (meshio.kuhn_beam(5, 3, 2, h=0.2), ref_mesh("teapot")[:2]):
+        ids, faces = capi.tet_surface(len(v), t)
+        o = OracleScene(capi.default_physics_params(), capi.default_collision_params(allowDCD=0, allowCCD=0), threads=1)
+        o.add_tet_mesh(v, t, capi.default_object_params(), [np.arange(len(v), dtype=np.int32)])
+        o.finalize()
+        assert np.array_equal(ids, o.surface_vertex_ids(0)) and np.array_equal(faces, o.surface_faces(0))
