@@ -531,7 +531,7 @@ int gaia_b200_reset_stats(gaia_handle* h) {
     h->s.solveKernelMs = 0.0; h->s.solveKernelLaunches = 0;
     return GAIA_OK;
 }
-int gaia_b200_set_profiling(gaia_handle* h, int enabled) { REQUIRE(h); h->s.profiling = enabled != 0; return GAIA_OK; }
+int gaia_b200_set_profiling(gaia_handle* h, int enabled) { REQUIRE(h); h->s.profiling = enabled < 0 ? 0 : (enabled > 2 ? 1 : enabled); return GAIA_OK; }
 int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
     REQUIRE(h);
     if (lanes != 0 && lanes != 4 && lanes != 8) return fail(h->s, GAIA_ERR_INVALID_ARG, "solver lanes: 0 (default), 4 or 8");

@@ -149,7 +149,7 @@ struct Scene {
 
     // statistics / profiling
     gaia_stats stats;
-    bool profiling = false;
+    int profiling = 0;             // 0 off; 1 per-phase timers + an event pair around every colour-solve launch; 2 per-phase timers only (the colour loop stays a CUDA graph)
     cudaEvent_t evA = nullptr, evB = nullptr, evP0 = nullptr, evP1 = nullptr;
     std::vector<cudaEvent_t> profEv;   // event pairs around the colour-solve launches of one iteration loop (profiling only)
     size_t profUsed = 0;

@@ -356,7 +356,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             if (ve <= vb && !halo) continue;
             if (hasContacts) { CK(collision_update_infos(s, g, captured)); }
             cudaEvent_t pe0 = nullptr, pe1 = nullptr;
-            if (s.profiling) {      // a pair of events per launch, read back at the end of the loop: no host sync between launches
+            if (s.profiling == 1) {      // a pair of events per launch, read back at the end of the loop: no host sync between launches
                 if (s.profUsed + 2 > s.profEv.size()) { s.profEv.resize(s.profUsed + 2, nullptr); }
                 for (size_t q = s.profUsed; q < s.profUsed + 2; q++) if (!s.profEv[q]) CK(cudaEventCreate(&s.profEv[q]));
                 pe0 = s.profEv[s.profUsed]; pe1 = s.profEv[s.profUsed + 1]; s.profUsed += 2;
@@ -364,7 +364,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             }
             hv.epochOffset = it * G + g;
             if (ve > vb) CK(sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
-            if (s.profiling) cudaEventRecord(pe1, s.stream);
+            if (s.profiling == 1) cudaEventRecord(pe1, s.stream);
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
             else if (halo) {
@@ -390,7 +390,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
         }
     }
     if (fused) { k_halo_advance<<<1, 32, 0, s.stream>>>(hv, nIters * G); s.stats.kernelLaunches++; }
-    if (s.profiling && s.profUsed) {
+    if (s.profiling == 1 && s.profUsed) {
         CK(cudaStreamSynchronize(s.stream));
         for (size_t q = 0; q + 1 < s.profUsed; q += 2) {
             float ms = 0.f;
@@ -409,7 +409,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
     const bool withContacts = s.cs != nullptr;
     const bool contactsOk = !withContacts || (collision_graphable(s) && !halo_active(s) && !s.phys.useAccelerator &&
                                               !(allowIntermediateCD && s.phys.intermediateCollisionIterations > 0));
-    const bool graphable = !s.profiling && contactsOk && s.iterCalls > 0 && nIters > 0;
+    const bool graphable = s.profiling != 1 && contactsOk && s.iterCalls > 0 && nIters > 0;
     s.iterCalls++;
     if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD);
     if (!s.iterGraphExec || s.iterGraphIters != nIters) {

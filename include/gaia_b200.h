@@ -336,7 +336,7 @@ int gaia_b200_get_stats(gaia_handle* h, gaia_stats* out);
 int gaia_b200_reset_stats(gaia_handle* h);
 /* average device time (ms) of the colour-solve kernels since the last reset, measured with CUDA
  * events on the launching stream when profiling is enabled */
-int gaia_b200_set_profiling(gaia_handle* h, int enabled);
+int gaia_b200_set_profiling(gaia_handle* h, int enabled);   /* 0 off; 1 phase timers + per-launch events; 2 phase timers only (the colour loop stays a CUDA graph) */
 void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that time with their own events */
 /* Kept for round-1 callers: the colour sweep always runs 4 lanes per vertex (the lane count fixes the record order and the
  * association of the per-vertex sums, so it is a property of the layout built at finalize, not a run-time switch).
