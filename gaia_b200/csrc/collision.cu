@@ -29,6 +29,7 @@ namespace gb {
 
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return _e; } while (0)
 static const int kB = 128;
+static const int kRejCap = 1536;   // DCD phase 2: rejected-face distances kept per query (rule R2')
 static const int kCand = 64;        // DCD candidate cache: tets kept per surface vertex between refits (k_dcd_phase1)
 static inline int nblk(int64_t n, int per = kB) { return (int)((n + per - 1) / per); }
 // grid of a grid-stride kernel: at most one full wave of 148 SMs x 16 blocks (a launch that decides on the device to do nothing costs one wave)
@@ -36,6 +37,7 @@ static inline int capped(int64_t n, int per = kB) { return (int)std::min<int64_t
 
 struct ColParamsDev {
     int32_t allowCCD, checkFeasibleRegion, checkTetTraverse, handleSelfCollision, stopAfterPassing, traverseNonSelf, shiftQueryToCenter;
+    int32_t maxBVHQuery;
     float centerShiftLevel, feasibleEps, rayEps, maxSearchMult, offHeight, kCollision, dt;
 };
 
@@ -305,6 +307,7 @@ static ColParamsDev make_col_params(const Scene& s) {
     c.allowCCD = s.col.allowCCD; c.checkFeasibleRegion = s.col.checkFeasibleRegion; c.checkTetTraverse = s.col.checkTetTraverse;
     c.handleSelfCollision = s.col.handleSelfCollision; c.stopAfterPassing = s.col.stopTraversingAfterPassingQueryPoint;
     c.traverseNonSelf = s.col.tetrahedralTraverseForNonSelfIntersection; c.shiftQueryToCenter = s.col.shiftQueryPointToCenter;
+    c.maxBVHQuery = s.col.maxNumberOfBVHQuery;
     c.centerShiftLevel = s.col.centerShiftLevel; c.feasibleEps = s.col.feasibleRegionEpsilon; c.rayEps = s.col.rayTriIntersectionEPSILON;
     c.maxSearchMult = s.col.maxSearchDistanceMultiplier; c.offHeight = s.phys.collisionOffHeight; c.kCollision = s.phys.collisionStiffness;
     c.dt = s.dt;
@@ -692,6 +695,15 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
              const float4* __restrict__ pos, const int32_t* __restrict__ cHitTet, int32_t* cFace, int32_t* cFlags, int32_t* errFlags) {
     __shared__ int sStack[kB / 32][kStack];
     __shared__ int sCand[kB / 32][32];
+    // rule R2' (the order-independent form of maxNumberOfBVHQuery): an acceptable face at distance d is a valid answer only
+    // while fewer than `cap` faces are strictly nearer. So the `cap` smallest distances of the evaluated, not accepted faces
+    // are kept (sRej, thinned to the cap smallest whenever it fills up); once there are cap of them their largest, `bound`,
+    // limits the search like a found face does: nothing beyond it can be a valid answer, and a query whose surroundings hold
+    // no acceptable face ends after the nearest few hundred faces instead of scanning the whole mesh.
+    __shared__ float sRej[kB / 32][kRejCap];
+    int nRej = 0;
+    const int cap = (cp.maxBVHQuery > 0 && 2 * cp.maxBVHQuery <= kRejCap) ? cp.maxBVHQuery : 0;      // 0: no cap
+    float bound = __int_as_float(0x7f800000);
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (i >= *nHits) return;                       // whole warps leave together
@@ -721,7 +733,8 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
             int nCand = 0;
             while (sp > 0 && nCand < 32) {
                 const int node = sStack[w][--sp];
-                const float r2 = radius == kInf ? 1e30f : radius * radius * 1.0001f + 1e-12f;
+                const float reach = fminf(radius, bound);
+                const float r2 = reach == kInf ? 1e30f : reach * reach * 1.0001f + 1e-12f;
                 if (box_dist2(bv.box[2 * node], bv.box[2 * node + 1], q) > r2) continue;
                 if (node >= bv.n) { sCand[w][nCand++] = bv.order[node - bv.n]; continue; }
                 const int2 ch = bv.child[node];
@@ -736,6 +749,7 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
             if (nCand == 0) break;
             // ---- one candidate per lane
             float myD = kInf; int myFace = 0x7FFFFFFF, myType = NotFound;
+            float myRej = -1.f;
             if (lane < nCand) {
                 const int face = sCand[w][lane];
                 const int4 fv = __ldg(tp.faceSid + face);
@@ -750,6 +764,8 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
                     if (cpId != -1 && cpId == sQ) ok = false;
                 }
                 if (ok && !(d < radius || (d == radius && bestFace >= 0 && face < bestFace))) ok = false;
+                const bool inReach = d <= bound;          // beyond the cap-th nearest rejected face nothing is a valid answer
+                if (!inReach) ok = false;
                 if (ok && cp.checkFeasibleRegion && !feasible_region(q, pos, tp, face, fv, type, cp.feasibleEps)) ok = false;
                 if (ok && cp.checkTetTraverse && (g == meshQ || cp.traverseNonSelf)) {
                     V3 tracing;
@@ -763,6 +779,38 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
                     if (!tet_traverse(pos, tp, tracing, dir, maxDis, fi.x, fi.y, embraceTet, cp.rayEps, errFlags)) ok = false;
                 }
                 if (ok) { myD = d; myFace = face; myType = type; }
+                else if (inReach && d < radius) myRej = d;
+            }
+            if (cap) {      // log the rejected distances (warp-aggregated append) ...
+                const unsigned rm = __ballot_sync(full, myRej >= 0.f);
+                if (myRej >= 0.f) sRej[w][nRej + __popc(rm & ((1u << lane) - 1u))] = myRej;      // (room for 32 is kept below)
+                nRej += __popc(rm);
+                __syncwarp();
+                // ... and keep only the cap smallest: the first time cap of them are known, and whenever the log has doubled
+                if (nRej >= cap && (bound == kInf || nRej >= 2 * cap || nRej + 32 > kRejCap)) {
+                    // value of the cap-th smallest entry: bisection on the bit patterns (distances are non-negative floats)
+                    uint32_t lo = 0u, hi = 0x7f800000u;
+                    while (lo < hi) {
+                        const uint32_t mid = lo + ((hi - lo) >> 1);
+                        int c = 0;
+                        for (int i = lane; i < nRej; i += 32) c += __float_as_uint(sRej[w][i]) <= mid;
+                        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(full, c, o);
+                        if (c >= cap) hi = mid; else lo = mid + 1;
+                    }
+                    bound = fminf(bound, __uint_as_float(lo));
+                    int kept = 0;
+                    for (int base = 0; base < nRej; base += 32) {
+                        const float e = base + lane < nRej ? sRej[w][base + lane] : kInf;
+                        const bool keep = e <= bound;
+                        const unsigned km = __ballot_sync(full, keep);
+                        __syncwarp();
+                        if (keep) sRej[w][kept + __popc(km & ((1u << lane) - 1u))] = e;
+                        kept += __popc(km);
+                        __syncwarp();
+                    }
+                    nRej = kept;
+                    if (nRej + 32 > kRejCap) { if (lane == 0) atomicAdd(errFlags + 3, 1); nRej = kRejCap - 32; }      // > 1000 equal distances
+                }
             }
             __syncwarp();
 #pragma unroll
@@ -772,6 +820,12 @@ k_dcd_phase2(const int32_t* __restrict__ nHits, const int32_t* __restrict__ hitL
                 if (od < myD || (od == myD && of < myFace)) { myD = od; myFace = of; myType = ot; }
             }
             if (myFace != 0x7FFFFFFF) { radius = myD; bestFace = myFace; bestType = myType; }
+        }
+        if (cap && bestFace >= 0) {      // faces strictly nearer than the answer and not acceptable: cap of them void it
+            int cnt = 0;
+            for (int i = lane; i < nRej; i += 32) cnt += sRej[w][i] < radius;
+            for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(full, cnt, o);
+            if (cnt >= cap) { bestFace = -1; bestType = NotFound; }
         }
     }
     if (lane == 0) {

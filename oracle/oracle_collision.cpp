@@ -17,7 +17,8 @@
 //   R1  DCD phase 1 ("first tet found", maxNumberOfCollisions = 1): the containing tet with the smallest
 //       (meshId, tetId).
 //   R2  closest surface point: smallest distance d among the faces that pass the feasibility + traversal tests;
-//       ties -> smallest face id.  maxNumberOfBVHQuery (an Embree-order-dependent early-out) is not applied.
+//       ties -> smallest face id.  maxNumberOfBVHQuery (an Embree-order-dependent early-out) is applied in its order-independent
+//       form R2': the query fails when at least that many faces are strictly nearer than the nearest acceptable one.
 //   R3  CCD: smallest penetrationDepth = t*|p1-p0| over ALL faces of active meshes; ties -> smallest
 //       (meshId, faceId).  (Any true hit lies inside the query sphere, so the sphere only culls.)
 //   R4  tetrahedral traversal uses unbounded stacks (= static version when it does not overflow, = the
@@ -478,6 +479,20 @@ static void closest_point_query(Scene& s, ColResult& r) {
     };
     if (acc->bruteForce) { for (int f = 0; f < ms.nSurfF(); f++) visit(f); }
     else acc->surf.trees[g].query(q, [&] { return radius == std::numeric_limits<float>::infinity() ? 1e30f : radius * radius * 1.0001f + 1e-12f; }, visit);
+    // rule R2' (stand-in for maxNumberOfBVHQuery, DiscreteCollisionDetector.cpp:104-110: the reference gives up - found = false -
+    // once its callback has run more than maxNumberOfBVHQuery times; which faces those are depends on Embree's order). The
+    // order-independent statement: the query fails when at least maxNumberOfBVHQuery faces of the mesh are strictly nearer
+    // (exact closest-point distance) than the nearest acceptable one - a nearest-first search would have spent its budget on them.
+    if (bestFace >= 0 && s.col.maxNumberOfBVHQuery > 0 && ms.nSurfF() >= s.col.maxNumberOfBVHQuery) {
+        int nearer = 0;
+        for (int f = 0; f < ms.nSurfF() && nearer < s.col.maxNumberOfBVHQuery; f++) {
+            const int* fv = &ms.surfFaces[3 * f];
+            int type; V3 bary;
+            const V3 cp = closest_point_triangle(q, ms.pos[fv[0]], ms.pos[fv[1]], ms.pos[fv[2]], bary, type);
+            if (norm(q - cp) < radius) nearer++;
+        }
+        if (nearer >= s.col.maxNumberOfBVHQuery) bestFace = -1;
+    }
     if (bestFace >= 0) {
         r.shortestPathFound = true; r.closestSurfacePtBarycentrics = bestBary; r.closestSurfacePt = bestCp;
         r.closestSurfaceFaceId = bestFace; r.closestPointType = bestType; r.closestPointNormal = V3();
