@@ -198,6 +198,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="twist_beam_10m", choices=sorted(WORKLOADS))
+    ap.add_argument("--layout", default="ring", choices=["ring", "replicated"],
+                    help="N > 1, one mesh: 'ring' = slabs with a one-ring ghost layer (contacts seen inside a slab and its ring), "
+                         "'replicated' = solve partitioned, whole mesh on every rank as collision geometry (contacts between any two ranks)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=1, help="extra untimed steps with per-kernel CUDA events for the roofline")
     args = ap.parse_args()
@@ -231,7 +234,7 @@ def main():
         if len(wl["meshes"]) > 1:      # many objects: shard by object with ghost objects (config 5)
             scene = multigpu.build_object_sharded_scene(wl, rank, world, local_rank)
         else:                          # one big mesh: x-slab partition with a one-ring ghost layer (config 4)
-            scene = multigpu.build_partitioned_scene(wl, rank, world, local_rank)
+            scene = (multigpu.build_replicated_scene if args.layout == "replicated" else multigpu.build_partitioned_scene)(wl, rank, world, local_rank)
     else:
         scene = build_scene(cloth.ClothScene if is_cloth(wl) else capi.Scene, wl, device=local_rank)
     log(f"[bench] rank {rank}: scene '{wl['name']}' built in {time.time() - t0:.1f}s")
@@ -392,7 +395,7 @@ def main():
         out = {"metric": "VBD vertex-solves/sec", "value": value, "unit": "vertex-solves/s", "n_gpus": world, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": wl["name"], "parallelism": (f"{'objects sharded' if len(wl['meshes']) > 1 else 'x-slab partition'} over {world} GPU(s)") if world > 1 else "1 GPU",
+               "config": {"workload": wl["name"], "parallelism": (f"{'objects sharded' if len(wl['meshes']) > 1 else ('x-slab partition, ' + ('whole mesh replicated as collision geometry' if args.layout == 'replicated' else 'one-ring ghosts'))} over {world} GPU(s)") if world > 1 else "1 GPU",
                           "l2": l2_note,
                           "sim_steps_per_s": st["substeps"] / (ms * 1e-3), "frames_per_s": args.steps / (ms * 1e-3)},
                "clocks": clk, "e2e": e2e, "gpu_launches": int(st["kernelLaunches"]), "roofline": roof, "cpu_baseline": cpu}

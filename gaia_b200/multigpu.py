@@ -145,6 +145,59 @@ def build_partitioned_scene(wl, rank, world, local_rank):
     return s
 
 
+class ReplicatedPartition:
+    """Ownership record of the replicated layout (every rank holds the whole mesh): what `gather_owned_positions` needs."""
+
+    def __init__(self, owner, rank):
+        self.local_verts = np.arange(len(owner), dtype=np.int32)
+        self.owned = np.asarray(owner) == rank
+
+
+def add_replicated_mesh(scene, verts, tets, obj, colors, fixed, owner, rank, world):
+    """The whole mesh on this rank, every vertex another rank owns as a ghost: solved nowhere but on its owner, overwritten
+    by the owner's pushes. Colour order = the global one, so every rank numbers the vertices identically."""
+    scene.set_partition_mode(rank, world)
+    mesh = scene.add_tet_mesh(verts, tets, obj, global_color_order(colors), fixed)
+    scene.set_ghosts(mesh, np.nonzero(np.asarray(owner) != rank)[0].astype(np.int32))
+    return mesh
+
+
+def build_replicated_scene(wl, rank, world, local_rank):
+    """Cross-partition contacts for ONE mesh cut into slabs (SURVEY.md §8(e) "ghost BVH regions", taken to its simplest exact
+    form): the SOLVE is partitioned - a rank keeps records only for the vertices of its slab - but every rank holds the whole
+    mesh as collision geometry, and after every colour each rank pushes ALL its vertices of that colour to ALL ranks (not
+    just a one-ring boundary to its neighbours). Positions are therefore identical everywhere at every point where the
+    single-GPU step reads them, every rank finds every contact by itself (detection is deterministic), applies the ones
+    that touch its own vertices - own contacts and face-side relations alike - and nothing but positions is ever exchanged.
+    Bit-identical to the single-GPU run, far ends of a folded beam touching across ranks included. Cost: detection is not
+    partitioned and the exchange moves a colour's worth of positions per step (6 MB per rank and colour on the 10 M-tet beam)."""
+    import torch.distributed as dist
+    from . import capi
+    assert len(wl["meshes"]) == 1
+    verts, tets, obj, colors, fixed = wl["meshes"][0]
+    owner = capi.partition_slab_owner(wl.get("flat", verts), world)      # "flat": coordinates to cut along, if not the mesh's own
+    s = capi.Scene(wl["phys"], wl["col"], device=local_rank)
+    add_replicated_mesh(s, verts, tets, obj, colors, fixed, owner, rank, world)
+    for d in wl["deformers"]:
+        if d[0] == "rotator":
+            s.add_rotator(0, d[1], d[2], d[3], d[4], d[5])
+        else:
+            s.add_translator(0, d[1], d[2], d[3])
+    s.finalize()
+    s.partition = ReplicatedPartition(owner, rank)
+    mine = np.nonzero(owner == rank)[0].astype(np.int32)
+    slots = s.sorted_ids(0, mine)                       # the same numbering on every rank: my slot IS the remote slot
+    everyone = [None] * world
+    dist.all_gather_object(everyone, s.halo_ipc_handles())
+    mv = np.stack([np.zeros(len(mine), np.int32), mine], 1)
+    for q in range(world):
+        if q != rank:
+            s.halo_add_peer(q, everyone[q], mv, slots)
+    s.halo_finalize()
+    dist.barrier()
+    return s
+
+
 def gather_owned_positions(scene, part, n_global):
     """All ranks' owned positions assembled in global vertex order on every rank (tests / output)."""
     import torch

@@ -95,6 +95,45 @@ def workload_cloth_drape(n=1000, width=100.0, substeps=20, iterations=15, prerol
     return dict(kind="cloth", name=name, meshes=meshes, phys=phys, col=None, deformers=[], preroll=preroll)
 
 
+def workload_folded_beam(nx=16, ny=2, nz=2, h=0.2, gap=0.03, press=0.6, substeps=2, iterations=5):
+    """One beam bent into a U (the bent shape IS the rest shape), lower arm on the ground and clamped at its free end, the
+    upper arm's end pressed down onto the lower arm by a translator: self-contact between the two ENDS of one mesh. With
+    `owner` (slabs along the unbent beam) every one of those contacts joins vertices of the first and the last rank - the
+    case a one-ring ghost layer cannot see (cross-partition contacts)."""
+    from . import meshio
+    flat, tets = meshio.kuhn_beam(nx, ny, nz, h=h)
+    thick, L = ny * h, nx * h
+    R = 0.5 * (thick + gap)                         # radius of the centre line in the bend
+    arc = np.pi * R
+    arm = 0.5 * (L - arc)
+    s_, off, z = flat[:, 0].astype(np.float64), flat[:, 1].astype(np.float64) - 0.5 * thick, flat[:, 2].astype(np.float64)
+    x = np.empty_like(s_); y = np.empty_like(s_)
+    lo, hi = s_ <= arm, s_ >= arm + arc
+    mid = ~(lo | hi)
+    y0 = 0.5 * thick + 0.02
+    x[lo], y[lo] = s_[lo], y0 - off[lo]             # lower arm runs +x, its "up" is -off so that the upper arm keeps orientation
+    th = (s_[mid] - arm) / R                        # 0..pi around the centre (arm, y0 + R)
+    x[mid] = arm + (R + off[mid]) * np.sin(th)
+    y[mid] = y0 + R - (R + off[mid]) * np.cos(th)
+    x[hi], y[hi] = arm - (s_[hi] - arm - arc), y0 + 2 * R + off[hi]
+    verts = np.stack([x, y, z], 1).astype(np.float32)
+    p = verts[tets].astype(np.float64)
+    det = np.einsum("ij,ij->i", p[:, 1] - p[:, 0], np.cross(p[:, 2] - p[:, 0], p[:, 3] - p[:, 0]))
+    tets = tets.copy()
+    tets[det < 0] = tets[det < 0][:, [0, 2, 1, 3]]
+    colors = meshio.kuhn_coloring(nx, ny, nz)
+    fixed = np.nonzero(flat[:, 0] < 1e-6)[0].astype(np.int32)
+    tip = np.nonzero(flat[:, 0] > L - 1e-6)[0].astype(np.int32)
+    from . import capi
+    phys = capi.default_physics_params(numSubsteps=substeps, iterations=iterations, worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10],
+                                       collisionStiffness=1e5)
+    col = capi.default_collision_params(allowDCD=1, allowCCD=1)
+    obj = capi.default_object_params(miu=5e4, lmbd=5e5, density=100, dampingHydrostatic=1e-5, dampingDeviatoric=1e-5, frictionDynamic=0.2)
+    return dict(name=f"folded_beam {nx}x{ny}x{nz} cells ({len(tets)} tets, {len(verts)} verts), DCD+CCD, self-contact between the two ends",
+                meshes=[(verts, tets, obj, colors, fixed)], phys=phys, col=col, deformers=[("translator", tip, [0.0, -press, 0.0], -1.0)],
+                flat=flat)
+
+
 def is_cloth(wl):
     return wl.get("kind") == "cloth"
 

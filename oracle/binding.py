@@ -49,7 +49,7 @@ def load_oracle():
         bind_scene_api(lib, "oracle_")
         P, FP, IP = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
         lib.oracle_num_threads.argtypes = [P]
-        for f in ("phase_begin_substep", "phase_prepare", "phase_end_substep"):
+        for f in ("phase_begin_substep", "phase_prepare", "phase_intermediate_cd", "phase_end_substep"):
             getattr(lib, "oracle_" + f).argtypes = [P]
         lib.oracle_phase_solve_group.argtypes = [P, C.c_int, C.c_int]
         lib.oracle_set_prev_positions.argtypes = [P, C.c_int, FP]
@@ -128,6 +128,9 @@ class OracleScene(SceneBase):
 
     def phase_solve_group(self, g, apply_friction=True):
         self._call("phase_solve_group", int(g), int(apply_friction))
+
+    def phase_intermediate_cd(self):
+        self._call("phase_intermediate_cd")
 
     def phase_end_substep(self):
         self._call("phase_end_substep")

@@ -86,6 +86,7 @@ int oracle_set_ghosts(void* h, int mesh, const int32_t* verts, int32_t n) {
 int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_solve_group(void* h, int g, int applyFriction) { phase_solve_group(*(Scene*)h, g, applyFriction != 0); return GAIA_OK; }
+int oracle_phase_intermediate_cd(void* h) { phase_intermediate_cd(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_end_substep(void* h) { phase_end_substep(*(Scene*)h); return GAIA_OK; }
 
 int oracle_finalize(void* h) { scene_finalize(*(Scene*)h); return GAIA_OK; }

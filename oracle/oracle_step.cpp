@@ -413,6 +413,7 @@ void phase_begin_substep(Scene& s) {
     apply_deformers(s);
 }
 void phase_prepare(Scene& s) { ccd(s); prepare_collision_data(s); }
+void phase_intermediate_cd(Scene& s) { dcd(s, true); ccd(s); prepare_collision_data(s); }   // the block at the end of an iteration above
 void phase_end_substep(Scene& s) { update_velocities(s); s.stats.substeps++; }
 
 void run_step(Scene& s) {

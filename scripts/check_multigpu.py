@@ -22,10 +22,17 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    dims = [int(x) for x in os.environ.get("GAIA_CHECK_DIMS", "40,6,6").split(",")]
-    wl = bench.workload_twist_beam(*dims)
-    s = multigpu.build_partitioned_scene(wl, rank, world, local)
-    frames = 3
+    dims = [float(x) if "." in x else int(x) for x in os.environ.get("GAIA_CHECK_DIMS", "40,6,6").split(",")]
+    what = os.environ.get("GAIA_CHECK_WORKLOAD", "twist")
+    layout = os.environ.get("GAIA_CHECK_LAYOUT", "ring")          # ring: one-ring ghosts; replicated: whole mesh on every rank
+    frames = int(os.environ.get("GAIA_CHECK_FRAMES", "3"))
+    if what == "folded":          # self-contact between the two ends of one mesh = contacts between the first and last rank
+        from gaia_b200 import workloads
+        wl = workloads.workload_folded_beam(*dims)
+    else:
+        wl = bench.workload_twist_beam(*dims, collisions=os.environ.get("GAIA_CHECK_DCD", "0") == "1")
+    build = multigpu.build_replicated_scene if layout == "replicated" else multigpu.build_partitioned_scene
+    s = build(wl, rank, world, local)
     s.run_frames(frames)
     s.synchronize()
     nV = len(wl["meshes"][0][0])
@@ -40,8 +47,10 @@ def main():
         ref = single.positions(0)
         moved = float(np.abs(ref - wl["meshes"][0][0]).max())
         same = np.array_equal(got, ref)
-        print(f"[check_multigpu] world={world} moved={moved:.4f} bit_exact={same} maxdiff={float(np.abs(got - ref).max()):.3e} "
-              f"solves {int(solves.item())} vs {single.stats()['vertexSolves']}", flush=True)
+        con = single.contacts()
+        print(f"[check_multigpu] {wl['name']} | layout={layout} world={world} frames={frames} moved={moved:.4f} bit_exact={same} "
+              f"maxdiff={float(np.abs(got - ref).max()):.3e} solves {int(solves.item())} vs {single.stats()['vertexSolves']} "
+              f"contacts(single, last detection)={len(con)}", flush=True)
         ok = same and moved > 1e-3 and int(solves.item()) == single.stats()["vertexSolves"]
         single.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")

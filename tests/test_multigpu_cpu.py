@@ -123,6 +123,91 @@ def test_partitioned_oracle_equals_single_bit_exact(tmp_path, world):
     assert np.array_equal(got, ref)
 
 
+# ------------------------------------------------------------------------------ cross-partition contacts (replicated layout)
+def _folded_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from gaia_b200 import workloads
+    from oracle.binding import OracleScene
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    wl = workloads.workload_folded_beam()
+    verts, tets, obj, colors, fixed = wl["meshes"][0]
+    owner = multigpu.slab_owner(wl["flat"], world)          # slabs along the UNBENT beam: the two arms' ends are far-apart ranks
+    o = OracleScene(wl["phys"], wl["col"], threads=1)
+    multigpu.add_replicated_mesh(o, verts, tets, obj, colors, fixed, owner, rank, world)
+    for d in wl["deformers"]:
+        o.add_translator(0, d[1], d[2], d[3])
+    o.finalize()
+    groups = o.parallel_groups()
+    mine = owner == rank
+
+    def exchange(g):
+        """every rank's owned vertices of colour g (all for g < 0) to every other rank"""
+        pos = o.positions(0)
+        ids = np.nonzero(mine)[0] if g < 0 else groups[g][:, 1][mine[groups[g][:, 1]]]
+        everyone = [None] * world
+        dist.all_gather_object(everyone, (ids, pos[ids]))
+        for src, (i, p) in enumerate(everyone):
+            if src != rank:
+                pos[i] = p
+        o.set_state(0, pos, None)
+
+    phys = wl["phys"]
+    cross = 0
+    for frame in range(6):
+        for sub in range(phys.numSubsteps):
+            o.phase_begin_substep()
+            exchange(-1)
+            o.phase_prepare()
+            for it in range(phys.iterations):
+                for g in range(len(groups)):
+                    o.phase_solve_group(g, it >= phys.frictionStartIter)
+                    exchange(g)
+                ici = phys.intermediateCollisionIterations
+                if ici > 0 and it % ici == ici - 1:
+                    o.phase_intermediate_cd()
+            o.phase_end_substep()
+    pos = o.positions(0)
+    np.save(os.path.join(out_dir, f"fold_rank{rank}.npy"), np.concatenate([np.nonzero(mine)[0][:, None].astype(np.float64), pos[mine]], 1))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_cross_partition_contacts_replicated_layout_bit_exact(tmp_path, world):
+    """A beam folded onto itself, cut into slabs along its length: every contact joins the first and the last rank. Solve
+    partitioned, whole mesh replicated as collision geometry, a colour's owned vertices pushed to every rank
+    (multigpu.build_replicated_scene is the device statement) - identical to the single run, contacts and friction included."""
+    import torch.multiprocessing as mp
+    from gaia_b200 import workloads
+    from oracle.binding import OracleScene
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    mp.spawn(_folded_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    wl = workloads.workload_folded_beam()
+    o = workloads.build_scene(OracleScene, wl, threads=1)
+    o.run_frames(6)
+    con = o.contacts()
+    assert len(con) > 10
+    owner = multigpu.slab_owner(wl["flat"], world)
+    ref = o.positions(0)
+    got = np.zeros_like(ref)
+    seen = np.zeros(len(ref), bool)
+    for r in range(world):
+        a = np.load(tmp_path / f"fold_rank{r}.npy")
+        ids = a[:, 0].astype(np.int64)
+        got[ids] = a[:, 1:].astype(np.float32); seen[ids] = True
+    assert seen.all()
+    assert np.array_equal(got, ref)
+    # and the contacts really cross the cut: query vertex and hit face belong to different ranks, none of them neighbours
+    faces = o.surface_faces(0)
+    q_owner = owner[con["queryVertex"]]
+    f_owner = owner[faces[con["hitFace"]]]
+    crossing = (f_owner != q_owner[:, None]).all(1)
+    assert crossing.sum() > 10
+    assert (np.abs(f_owner[crossing] - q_owner[crossing, None]).min(1) == world - 1).any()
+
+
 # ------------------------------------------------------------------------------------------------ many-object sharding
 def _pile_workload():
     """Six blocks in three columns (two stacked per column, columns overlapping sideways): contacts inside a column and
