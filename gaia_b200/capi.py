@@ -365,10 +365,12 @@ def load_library(path=None):
     lib.gaia_b200_halo_ipc_handles.argtypes = [P, C.c_void_p]
     lib.gaia_b200_halo_add_peer.argtypes = [P, C.c_int32, C.c_void_p, C.c_int32, IP, IP]
     lib.gaia_b200_halo_finalize.argtypes = [P]
+    lib.gaia_b200_halo_set_world.argtypes = [P, C.c_int32, C.c_void_p]
     lib.gaia_b200_set_time.argtypes = [P, C.c_int32, C.c_double]
     lib.gaia_b200_cur_time.argtypes = [P]; lib.gaia_b200_cur_time.restype = C.c_double
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
+    lib.gaia_b200_set_multi_colour_launch.argtypes = [P, C.c_int]
     lib.gaia_b200_get_layout_bytes.argtypes = [P, C.POINTER(C.c_int64)]
     lib.gaia_b200_total_surface_vertices.argtypes = [P]; lib.gaia_b200_total_surface_vertices.restype = C.c_int64
     lib.gaia_b200_surface_snapshot_begin.argtypes = [P, C.c_int]
@@ -472,6 +474,12 @@ class Scene(SceneBase):
         assert len(mv) == len(rs)
         self._call("halo_add_peer", int(peer_rank), C.create_string_buffer(handles, 128), len(rs), _ip(mv), _ip(rs))
 
+    def halo_set_world(self, handles_by_rank):
+        """handles of ALL ranks (rank 0 first): lets the ranks agree, after every detection, whether anyone holds a contact"""
+        blob = b"".join(bytes(h) for h in handles_by_rank)
+        assert len(blob) == 128 * len(handles_by_rank)
+        self._call("halo_set_world", len(handles_by_rank), C.create_string_buffer(blob, len(blob)))
+
     def halo_finalize(self):
         self._call("halo_finalize")
 
@@ -499,6 +507,10 @@ class Scene(SceneBase):
         a = (C.c_int64 * 6)()
         self._call("get_layout_bytes", a)
         return dict(zip(("records", "neighbours", "vertex_state", "tiles", "pos_reads", "incidences"), [int(x) for x in a]))
+
+    def set_multi_colour_launch(self, enabled):
+        """contact-free stretches of the colour loop as one cooperative launch (default on); results do not change"""
+        self._call("set_multi_colour_launch", int(bool(enabled)))
 
     def set_solver_lanes(self, lanes):
         """0 (default 4), 4 or 8 lanes per vertex; runs compared bit for bit must use the same value"""

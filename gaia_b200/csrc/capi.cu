@@ -495,6 +495,14 @@ int gaia_b200_halo_add_peer_pointers(gaia_handle* h, int32_t peerRank, int32_t p
     const cudaError_t e = halo_add_peer(s, peerRank, nullptr, nSend, sendMeshVerts, remoteSlots, peerPointers16, peerDevice);
     return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
 }
+int gaia_b200_halo_set_world(gaia_handle* h, int32_t worldSize, const void* handles) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (!handles || worldSize != s.worldSize) return fail(s, GAIA_ERR_INVALID_ARG, "halo_set_world: one 128-byte record per rank of the partition mode");
+    cudaSetDevice(s.device);
+    const cudaError_t e = halo_set_world(s, worldSize, handles);
+    return e == cudaSuccess ? GAIA_OK : cuda_fail(s, e);
+}
 int gaia_b200_halo_finalize(gaia_handle* h) {
     REQUIRE(h); FINALIZED(h);
     cudaError_t e = halo_finalize(h->s);
@@ -537,6 +545,12 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
     if (lanes != 0 && lanes != 4 && lanes != 8) return fail(h->s, GAIA_ERR_INVALID_ARG, "solver lanes: 0 (default), 4 or 8");
     if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }
     h->s.solveLanes = lanes;
+    return GAIA_OK;
+}
+int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled) {
+    REQUIRE(h);
+    if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }
+    h->s.multiStepAllowed = enabled != 0;
     return GAIA_OK;
 }
 int gaia_b200_get_layout_bytes(gaia_handle* h, int64_t out[6]) {

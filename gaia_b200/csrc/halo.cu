@@ -40,6 +40,13 @@ struct HaloState {
     DevBuf<int2> sendEnt;               // (peer index, remote slot)
     DevBuf<HaloPeerTable> tab;
     DevBuf<int32_t> boundaryPrefix;     // [N+1]
+    // agreement among ALL ranks of the scene (halo_set_world): flag arrays of every rank, a vote counter, the result word
+    int nWorld = 0;
+    uint32_t* worldFlags[kMaxPeers + 1] = {};
+    bool worldOpened[kMaxPeers + 1] = {};
+    uint32_t voteEpoch = 0;
+    int32_t* voteHost = nullptr;        // pinned + mapped
+    int32_t* voteDev = nullptr;
 };
 
 struct PushArgs {
@@ -94,6 +101,69 @@ __global__ void k_halo_push_sync(PushArgs a, const float4* __restrict__ pos, uin
     }
     __syncthreads();
     if (threadIdx.x == 0) { ctl[0] = epoch; ctl[1] = 0; }
+}
+
+// Agreement among all ranks: "does ANY rank hold an active contact?" Every rank stores (epoch << 1 | mine) into slot
+// [32 + 8 * (epoch & 1) + myRank] of every rank's flag array and waits for the others' words of this epoch; two slot sets
+// alternate, and no rank can be two votes ahead of another (it needs that rank's word for the vote in between).
+struct VoteArgs { uint32_t* flags[kMaxPeers + 1]; };
+__global__ void k_halo_vote(VoteArgs a, int world, int myRank, uint32_t epoch, int mine, int32_t* result, int32_t* errFlags) {
+    const int p = threadIdx.x;
+    const int base = 32 + 8 * (int)(epoch & 1u);
+    int theirs = 0;
+    if (p < world && p != myRank) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.flags[p] + base + myRank), "r"((epoch << 1) | (uint32_t)mine) : "memory");
+        const unsigned long long t0 = globaltimer_ns();
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags[myRank] + base + p) : "memory");
+            if ((v >> 1) == epoch) { theirs = (int)(v & 1u); break; }
+            if (globaltimer_ns() - t0 > 5000000000ull) { atomicAdd(errFlags + 4, 1); theirs = 1; break; }
+            __nanosleep(100);
+        }
+    }
+    const int any = __any_sync(0xffffffffu, theirs | (p == myRank ? mine : 0));
+    if (p == 0) { *result = any; __threadfence_system(); }
+}
+
+// handles: 128 bytes per rank (halo_ipc_handles of rank 0 .. world-1); opens the flag arrays of the ranks that are not peers yet
+cudaError_t halo_set_world(Scene& s, int world, const void* handles) {
+    HaloState* h = s.halo;
+    if (!h || world < 1 || world > kMaxPeers + 1 || s.myRank >= world) return cudaErrorInvalidValue;
+    for (int r = 0; r < world; r++) {
+        if (r == s.myRank) { h->worldFlags[r] = h->flags.p; continue; }
+        uint32_t* f = nullptr;
+        for (auto& p : h->peers) if (p.rank == r) { if (!p.viaIpc) return cudaErrorInvalidValue; f = p.peerFlags; }
+        if (!f) {
+            cudaIpcMemHandle_t hf;
+            std::memcpy(&hf, (const char*)handles + 128 * (size_t)r + 64, 64);
+            CK(cudaIpcOpenMemHandle((void**)&f, hf, cudaIpcMemLazyEnablePeerAccess));
+            h->worldOpened[r] = true;
+        }
+        h->worldFlags[r] = f;
+    }
+    if (!h->voteHost) {
+        CK(cudaHostAlloc((void**)&h->voteHost, sizeof(int32_t), cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer((void**)&h->voteDev, h->voteHost, 0));
+    }
+    h->nWorld = world;
+    return cudaSuccess;
+}
+
+bool halo_can_vote(const Scene& s) { return s.halo && s.halo->nWorld > 1; }
+
+// blocks the host until every rank has voted (one tiny launch + a stream synchronisation)
+cudaError_t halo_vote(Scene& s, bool mine, bool* any) {
+    HaloState* h = s.halo;
+    VoteArgs a;
+    for (int r = 0; r <= kMaxPeers; r++) a.flags[r] = h->worldFlags[r];
+    *h->voteHost = 1;
+    k_halo_vote<<<1, 32, 0, s.stream>>>(a, h->nWorld, s.myRank, ++h->voteEpoch, mine ? 1 : 0, h->voteDev, s.errFlags.p);
+    s.stats.kernelLaunches++;
+    CK(cudaStreamSynchronize(s.stream));
+    *any = *(volatile int32_t*)h->voteHost != 0;
+    return cudaSuccess;
 }
 
 cudaError_t halo_ipc_handles(Scene& s, void* out128) {
@@ -243,6 +313,8 @@ void halo_destroy(Scene& s) {
         if (p.peerPos) cudaIpcCloseMemHandle(p.peerPos);
         if (p.peerFlags) cudaIpcCloseMemHandle(p.peerFlags);
     }
+    for (int r = 0; r <= kMaxPeers; r++) if (s.halo->worldOpened[r]) cudaIpcCloseMemHandle(s.halo->worldFlags[r]);
+    if (s.halo->voteHost) cudaFreeHost(s.halo->voteHost);
     delete s.halo;
     s.halo = nullptr;
 }

@@ -115,6 +115,10 @@ struct Scene {
     std::vector<int2> h_nbw;           // per (vertex, distinct neighbour): {sorted id, bits(sum of A*w' over the shared tets)}
     std::vector<TileDesc> h_tiles;
     std::vector<int32_t> groupTileStart;   // [G + 1]
+    DevBuf<int2> groupTilesDev;            // [G] {first tile, end tile}: what the multi-colour launch steps through
+    DevBuf<uint32_t> gridBar;              // its grid barrier: [0] arrivals, [1] exits
+    int multiStep = -1;                    // -1 not probed yet, 0 unavailable, 1 available
+    bool multiStepAllowed = true;          // gaia_b200_set_multi_colour_launch
     int64_t sweepPosReads = 0;             // shared-memory position reads per sweep over all vertices (3 per restart, 1 per strip step)
     DevBuf<int4> vtx2;
     DevBuf<uint2> rec;
@@ -168,6 +172,8 @@ bool build_tile_streams(Scene& s, int tileV);
 
 // sweep.cu: the per-colour vertex solve over tiles (TMA-fed persistent blocks)
 cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv);
+bool sweep_multi_available(Scene& s);
+cudaError_t sweep_launch_multi(Scene& s, int firstGroup, int nSteps, int frictionFromStep, const HaloView* hv);
 cudaError_t sweep_upload(Scene& s);
 cudaError_t sweep_mark_halo_tiles(Scene& s, const int32_t* boundaryPrefixDev);
 
@@ -187,6 +193,9 @@ cudaError_t halo_local_pointers(Scene& s, void* out16);
 cudaError_t halo_add_peer(Scene& s, int peerRank, const void* handles128, int nSend, const int32_t* sendMeshVerts, const int32_t* remoteSlots,
                           const void* pointers16 = nullptr, int peerDevice = -1);
 cudaError_t halo_finalize(Scene& s);
+cudaError_t halo_set_world(Scene& s, int world, const void* handles);   // flag arrays of ALL ranks: agreement votes
+bool halo_can_vote(const Scene& s);
+cudaError_t halo_vote(Scene& s, bool mine, bool* any);                 // "does any rank say yes?" (host-blocking)
 void halo_destroy(Scene& s);
 bool halo_active(const Scene& s);
 cudaError_t halo_push(Scene& s, int group);

@@ -316,19 +316,39 @@ cudaError_t device_upload(Scene& s) {
 }
 
 
-static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD, bool captured = false) {
+static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermediateCD, bool captured = false, bool graphShape = false) {
     const int G = (int)s.groupStart.size() - 1;
     const int N = (int)s.nVerts;
     const bool halo = halo_active(s);
     HaloView hv;
     std::memset(&hv, 0, sizeof(hv));
     // (the accelerator needs full refreshes; with contacts the per-colour pre-pass reads ghost positions BEFORE the sweep,
-    //  so the exchange of the previous colour must be complete when it starts: the separate push + wait launch is used)
-    const bool fused = halo && !s.phys.useAccelerator && !s.cs && halo_view(s, hv);
+    //  so the exchange of the previous colour must be complete when it starts: the separate push + wait launch is used.
+    //  A scene WITH a collision pipeline may still use the fused exchange while no rank holds an active contact - there
+    //  is no pre-pass then - which the ranks agree on after every detection: halo_vote)
+    const bool canFuse = halo && !s.phys.useAccelerator && halo_view(s, hv);
+    bool fused = canFuse && !s.cs;
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
     // (captured: the contact variant runs every substep, with device-sized pre-passes; empty tables when nothing touches)
     bool hasContacts = collision_contact_view(s, cv, &colliding, captured);
+    auto agree = [&]() -> cudaError_t {
+        if (!canFuse || !s.cs) return cudaSuccess;
+        bool any = true;
+        if (halo_can_vote(s)) CK(halo_vote(s, hasContacts, &any));
+        fused = !any;
+        return cudaSuccess;
+    };
+    CK(agree());
+    int batch = 0;        // colour steps of the running fused batch (the epoch base on the device advances when it is closed)
+    auto close_batch = [&]() -> cudaError_t {
+        if (!batch) return cudaSuccess;
+        k_halo_advance<<<1, 32, 0, s.stream>>>(hv, batch); s.stats.kernelLaunches++;
+        batch = 0;
+        // a detection (or the next substep's) reads ghost positions: the neighbours' last pushes must have landed
+        if (s.cs) CK(halo_sync(s));
+        return cudaGetLastError();
+    };
     // per-iteration accounting (active, non-fixed vertices)
     int64_t solvedPerIter = 0, bytesPerIter = 0;
     for (auto& m : s.meshes) {
@@ -342,8 +362,49 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
         k_accelerate<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.accPrevPrev.p, s.accPrevIter.p, s.info.p, s.meshParams.p, nullptr, 1.f, 1);
         s.stats.kernelLaunches++;
     }
+    std::vector<int> pairSteps;      // profiling level 1: colour steps covered by each event pair
+    auto prof_begin = [&](int steps) -> cudaError_t {      // a pair of events per launch, read back at the end of the loop: no host sync between launches
+        if (s.profiling != 1) return cudaSuccess;
+        if (s.profUsed + 2 > s.profEv.size()) { s.profEv.resize(s.profUsed + 2, nullptr); }
+        for (size_t q = s.profUsed; q < s.profUsed + 2; q++) if (!s.profEv[q]) CK(cudaEventCreate(&s.profEv[q]));
+        pairSteps.push_back(steps);
+        return cudaEventRecord(s.profEv[s.profUsed], s.stream);
+    };
+    auto prof_end = [&]() { if (s.profiling == 1) { cudaEventRecord(s.profEv[s.profUsed + 1], s.stream); s.profUsed += 2; } };
+    const int ici = s.phys.intermediateCollisionIterations;
+    // (measured on the 10 M-tet beam, whole and cut in two: a replayed graph of per-colour launches is 1.5 - 6 % faster than the
+    //  multi-colour launch, which in turn is 3 % faster than per-colour launches issued by the host. So: loops that replay
+    //  from a graph keep one launch per colour; loops the host has to issue - intermediate detection cuts them into
+    //  stretches - use one multi-colour launch per stretch)
+    const bool useMulti = s.multiStepAllowed && !s.phys.useAccelerator && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
     for (int it = 0; it < nIters; it++) {
         const int applyFriction = it >= s.phys.frictionStartIter;
+        // Contact-free stretch of iterations (up to the next intermediate detection): ONE launch sweeps all its colours, with
+        // a grid barrier between colours instead of a launch boundary (sweep.cu, MULTI)
+        if (useMulti && !hasContacts && (!halo || fused)) {
+            int nIt = nIters - it;
+            if (allowIntermediateCD && ici > 0) nIt = std::min(nIt, ici - (it % ici));
+            const int nSteps = nIt * G;
+            CK(prof_begin(nSteps));
+            hv.epochOffset = batch;
+            if (fused) batch += nSteps;
+            CK(sweep_launch_multi(s, 0, nSteps, std::max(0, s.phys.frictionStartIter - it) * G, fused ? &hv : nullptr));
+            prof_end();
+            s.stats.kernelLaunches++; s.stats.colourSweeps += nSteps;
+            if (fused) for (int q = 0; q < nIt; q++) for (int g = 0; g < G; g++) if (s.groupStart[g + 1] > s.groupStart[g]) halo_count_fused(s, g);
+            s.stats.vertexSolves += solvedPerIter * nIt;
+            s.stats.algorithmicBytes += bytesPerIter * nIt;
+            it += nIt - 1;
+            if (allowIntermediateCD && ici > 0 && it % ici == ici - 1) {
+                CK(close_batch());
+                CK(collision_dcd(s, true));
+                CK(collision_ccd(s));
+                CK(collision_prepare(s));
+                hasContacts = collision_contact_view(s, cv, &colliding);
+                CK(agree());
+            }
+            continue;
+        }
         if (s.phys.useAccelerator) {
             const int order = it + 1;
             const float rho = s.phys.acceleratorRho;
@@ -355,16 +416,11 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             const int vb = s.groupStart[g], ve = s.groupStart[g + 1];
             if (ve <= vb && !halo) continue;
             if (hasContacts) { CK(collision_update_infos(s, g, captured)); }
-            cudaEvent_t pe0 = nullptr, pe1 = nullptr;
-            if (s.profiling == 1) {      // a pair of events per launch, read back at the end of the loop: no host sync between launches
-                if (s.profUsed + 2 > s.profEv.size()) { s.profEv.resize(s.profUsed + 2, nullptr); }
-                for (size_t q = s.profUsed; q < s.profUsed + 2; q++) if (!s.profEv[q]) CK(cudaEventCreate(&s.profEv[q]));
-                pe0 = s.profEv[s.profUsed]; pe1 = s.profEv[s.profUsed + 1]; s.profUsed += 2;
-                cudaEventRecord(pe0, s.stream);
-            }
-            hv.epochOffset = it * G + g;
+            CK(prof_begin(1));
+            hv.epochOffset = batch;
+            if (fused) batch++;
             if (ve > vb) CK(sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
-            if (s.profiling == 1) cudaEventRecord(pe1, s.stream);
+            prof_end();
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
             else if (halo) {
@@ -381,20 +437,21 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             s.stats.kernelLaunches++;
             if (halo) { CK(halo_sync(s)); CK(halo_push(s, -1)); }    // the extrapolated positions replace the ghosts' copies
         }
-        const int ici = s.phys.intermediateCollisionIterations;
         if (allowIntermediateCD && ici > 0 && it % ici == ici - 1) {
+            CK(close_batch());
             CK(collision_dcd(s, true));
             CK(collision_ccd(s));
             CK(collision_prepare(s));
             hasContacts = collision_contact_view(s, cv, &colliding);
+            CK(agree());
         }
     }
-    if (fused) { k_halo_advance<<<1, 32, 0, s.stream>>>(hv, nIters * G); s.stats.kernelLaunches++; }
+    CK(close_batch());
     if (s.profiling == 1 && s.profUsed) {
         CK(cudaStreamSynchronize(s.stream));
         for (size_t q = 0; q + 1 < s.profUsed; q += 2) {
             float ms = 0.f;
-            if (cudaEventElapsedTime(&ms, s.profEv[q], s.profEv[q + 1]) == cudaSuccess) { s.solveKernelMs += ms; s.solveKernelLaunches++; }
+            if (cudaEventElapsedTime(&ms, s.profEv[q], s.profEv[q + 1]) == cudaSuccess) { s.solveKernelMs += ms; s.solveKernelLaunches += pairSteps[q / 2]; }
         }
         s.profUsed = 0;
     }
@@ -411,12 +468,14 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
                                               !(allowIntermediateCD && s.phys.intermediateCollisionIterations > 0));
     const bool graphable = s.profiling != 1 && contactsOk && s.iterCalls > 0 && nIters > 0;
     s.iterCalls++;
-    if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD);
+    // (graphShape: this loop is replayed from a graph whenever profiling / the first call do not prevent it - those calls take
+    //  the same launch shape, so that what the profiling pass times is what the timed pass runs)
+    if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD, false, contactsOk && nIters > 0);
     if (!s.iterGraphExec || s.iterGraphIters != nIters) {
         if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }
         const gaia_stats before = s.stats;
         CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
-        cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD, withContacts);
+        cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD, withContacts, true);
         cudaGraph_t g = nullptr;
         cudaError_t e2 = cudaStreamEndCapture(s.stream, &g);
         if (e != cudaSuccess) return e;

@@ -72,6 +72,26 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+__device__ __forceinline__ void mbar_inval(uint32_t bar) { asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar) : "memory"); }
+// coherent (L1-cached, invalidated by the acquire fence of the grid barrier) 16-byte load: the multi-colour launch reads
+// positions other blocks wrote earlier in the SAME launch, which ld.global.nc must not be used for
+__device__ __forceinline__ float4 ldca128(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.ca.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+// ghost positions are written by ANOTHER GPU while this kernel runs: a strong load at system scope (served by the point of
+// coherence, never by a line some cache picked up before the neighbour's store landed)
+__device__ __forceinline__ float4 ldsys128(const float4* p) {
+    float4 r;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 r;
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
@@ -125,6 +145,12 @@ struct SweepArgs {
     ContactView cv;
     int32_t* errFlags;
     HaloView hv;
+    // MULTI: one launch sweeps nSteps colours in turn (colour of step j = (firstGroup + j) % nGroups), a grid-wide barrier
+    // between them
+    const int2* stepTiles;               // [nGroups] {tileBegin, tileEnd}
+    int nSteps, firstGroup, nGroups;
+    int frictionFromStep;                // steps >= this apply friction
+    uint32_t* gridBar;                   // [0] arrivals, [1] exits (both 0 between launches)
 };
 
 // IPC-style mollified friction (computeVertexFriction, VBDPhysics.cpp:2563-2592) for an axis-aligned tangent basis
@@ -264,16 +290,24 @@ struct Prefetch {
     int hdrY;          // nbLocal | nNb << 16 of the vertex (0 when the lane has no vertex)
 };
 
-template <int L, bool HAS_CONTACTS, bool HALO>
+template <int L, bool HAS_CONTACTS, bool HALO, bool MULTI>
 __global__ void __launch_bounds__(kSweepThreads, kSweepBlocksPerSM)
 k_sweep_tiles(const SweepArgs a) {
+    static_assert(!(MULTI && HAS_CONTACTS), "the contact pre-pass of a colour is a separate launch: one colour per launch");
     constexpr int VPR = kSweepThreads / L;          // vertices per round
     constexpr int NQ = 16 / L;                      // gathers held in registers per lane (16 neighbours per vertex)
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t sb = smem_u32(smem);             // every shared-memory access below goes through 32-bit shared addresses
     const int tid = threadIdx.x, lane = tid & (L - 1), sub = tid / L;
-    const int nMine = (a.tileEnd - a.tileBegin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // tiles of this block
-    const float4* posRO = a.pos;      // gathers only touch other colours: read-only for this launch
+    int tileBegin = a.tileBegin, tileEnd = a.tileEnd, applyFriction = a.applyFriction;
+    if (MULTI) {
+        const int2 t = __ldg(a.stepTiles + a.firstGroup);
+        tileBegin = t.x; tileEnd = t.y; applyFriction = a.frictionFromStep <= 0;
+    }
+    int nMine = (tileEnd - tileBegin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // tiles of this block
+    if (nMine < 0) nMine = 0;
+    int step = 0;                     // MULTI: colour step inside this launch
+    const float4* posRO = a.pos;      // gathers only touch other colours: read-only for this colour
 
     if (HALO && blockIdx.x == 0 && tid < a.hv.nPeers) {
         // everything this stream launched before is complete (stream order): publish it to the neighbours
@@ -281,7 +315,7 @@ k_sweep_tiles(const SweepArgs a) {
         __threadfence_system();
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.hv.tab->peerFlag[tid]), "r"(done) : "memory");
     }
-    if (nMine <= 0) return;
+    if (!MULTI && nMine <= 0) return;
     if (tid == 0) {
         for (int i = 0; i < 5; i++) mbar_init(sb + kSmBarRec + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -291,7 +325,7 @@ k_sweep_tiles(const SweepArgs a) {
     // ---- producer (thread 0). Tile k: neighbour entries, headers and own positions -> slot k % 3 (one barrier: the data the
     // gathers need first); records -> slot k & 1 (their own barrier, needed half a tile later). info ring: slot k & 3.
     auto issue_nb = [&](int k) {
-        const int4* dp = (const int4*)(a.tiles + a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x);
+        const int4* dp = (const int4*)(a.tiles + tileBegin + (int)blockIdx.x + k * (int)gridDim.x);
         const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);       // {vBegin, nV, recBegin, recCount}, {nbBegin, nbCount, flags, -}
         const int s3 = k % 3;
         sts128i(sb + kSmInfo + (k & 3) * 32, d0); sts128i(sb + kSmInfo + (k & 3) * 32 + 16, d1);
@@ -303,17 +337,18 @@ k_sweep_tiles(const SweepArgs a) {
         bulk_g2s(sb + kSmPos + s3 * kVtxStage, a.pos + d0.x, bV, bar);
     };
     auto issue_rec = [&](int k) {
-        const int4 d0 = __ldg((const int4*)(a.tiles + a.tileBegin + (int)blockIdx.x + k * (int)gridDim.x));
+        const int4 d0 = __ldg((const int4*)(a.tiles + tileBegin + (int)blockIdx.x + k * (int)gridDim.x));
         const uint32_t bar = sb + kSmBarRec + 8 * (k & 1);
         const uint32_t bRec = (uint32_t)d0.w * 8u;
         mbar_expect_tx(bar, bRec);
         if (bRec) bulk_g2s(sb + kSmRec + (k & 1) * kRecStage, a.rec + d0.z, bRec, bar);
     };
-    if (tid == 0) {
-        issue_nb(0); issue_rec(0);
+    auto prologue = [&]() {
+        if (nMine > 0) { issue_nb(0); issue_rec(0); }
         if (nMine > 1) { issue_nb(1); issue_rec(1); }
         if (nMine > 2) issue_nb(2);
-    }
+    };
+    if (tid == 0) prologue();
     // (returns false when the copies never arrived - a watchdog for a sick device: the block leaves instead of spinning)
     auto wait_bar = [&](uint32_t bar, uint32_t parity) -> bool {
         if (mbar_try_wait(bar, parity)) return true;
@@ -334,7 +369,7 @@ k_sweep_tiles(const SweepArgs a) {
             // partitions' previous colour before gathering, and gather past L1
             ghost = (lds32(sb + kSmInfo + s4 * 32 + 24) & 1u) != 0;
             if (ghost && !haloWaited) {
-                if (tid == 0 && !(a.hv.debug & 1)) sweep_halo_wait(a.hv.tab, *(volatile const uint32_t*)a.hv.ctl + (uint32_t)a.hv.epochOffset, a.hv.nPeers, a.errFlags);
+                if (tid == 0 && !(a.hv.debug & 1)) sweep_halo_wait(a.hv.tab, *(volatile const uint32_t*)a.hv.ctl + (uint32_t)(a.hv.epochOffset + step), a.hv.nPeers, a.errFlags);
                 __syncthreads();
                 haloWaited = true;
             }
@@ -354,14 +389,16 @@ k_sweep_tiles(const SweepArgs a) {
             if (lane + q * L < nNb) {
                 const uint2 e = lds64(nbAddr + q * (L * 8));
                 pf.w[q] = __uint_as_float(e.y);
-                pf.p[q] = (HALO && ghost) ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
+                pf.p[q] = (HALO && ghost) ? __ldcg(posRO + e.x) : (MULTI ? ldca128(posRO + e.x) : __ldg(posRO + e.x));
             }
         }
         return true;
     };
 
     Prefetch<NQ> pf;
-    if (!prefetch(0, 0, 0u, 0, pf)) return;
+#pragma unroll 1
+    for (;;) {      // (one pass unless MULTI)
+    if (nMine > 0 && !prefetch(0, 0, 0u, 0, pf)) return;
 
     int s3 = 0;                 // k % 3
     uint32_t parNb = 0;         // (k / 3) & 1
@@ -411,7 +448,7 @@ k_sweep_tiles(const SweepArgs a) {
                 const uint32_t nbAddr = sb + kSmNbw + s3 * kNbwStage + nbLocal * 8;
                 for (int i = lane + NQ * L; i < nNb; i += L) {
                     const uint2 e = lds64(nbAddr + i * 8);
-                    const float4 p = ghostTile ? __ldcg(posRO + e.x) : __ldg(posRO + e.x);
+                    const float4 p = ghostTile ? __ldcg(posRO + e.x) : (MULTI ? ldca128(posRO + e.x) : __ldg(posRO + e.x));
                     const float w = __uint_as_float(e.y);
                     const float rx = __fsub_rn(p.x, x.x), ry = __fsub_rn(p.y, x.y), rz = __fsub_rn(p.z, x.z);
                     sts128_if(true, relAddr + i * 16, rx, ry, rz, p.w);
@@ -514,7 +551,7 @@ k_sweep_tiles(const SweepArgs a) {
                     const bool wrote = vertex_tail<HAS_CONTACTS>(s, x, ys, f3(xpv), P, lds32f(ac + 0 * kTileV * 4), lds32f(ac + 1 * kTileV * 4), lds32f(ac + 2 * kTileV * 4),
                                            __int_as_float(h.z), lds32f(ac + 3 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 4 * kTileV * 4) * (1.f / 6.f),
                                            lds32f(ac + 5 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 6 * kTileV * 4) * (1.f / 6.f), lds32f(ac + 7 * kTileV * 4) * (1.f / 6.f),
-                                           lds32f(ac + 8 * kTileV * 4) * (1.f / 6.f), a.pos, a.sp, a.applyFriction, a.cv, a.errFlags, xNew);
+                                           lds32f(ac + 8 * kTileV * 4) * (1.f / 6.f), a.pos, a.sp, applyFriction, a.cv, a.errFlags, xNew);
                     if (HALO && wrote && (h.w & kHaloBoundaryBit) && !(a.hv.debug & 2)) {
                         const int si = __ldg(a.hv.sendIdx + s);
                         for (int q = 0; q < (si & 15); q++) {
@@ -531,6 +568,52 @@ k_sweep_tiles(const SweepArgs a) {
         }
         s3 = s3n; parNb = parNbN;
     }
+    if (!MULTI) break;
+    if (++step == a.nSteps) break;
+    // ---- end of a colour: every block arrives at the grid barrier, re-arms its pipeline for the next colour and starts that
+    // colour's stream copies (records, neighbour entries, headers and OWN positions do not depend on the colour just swept)
+    // before it waits for the other blocks; only the neighbour gathers need the barrier
+    {
+        const int2 t = __ldg(a.stepTiles + (a.firstGroup + step) % a.nGroups);
+        tileBegin = t.x; tileEnd = t.y; applyFriction = step >= a.frictionFromStep;
+        nMine = (tileEnd - tileBegin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+        if (nMine < 0) nMine = 0;
+    }
+    __syncthreads();      // (all tails of this block are done, nobody waits on an mbarrier any more)
+    __shared__ int dead;
+    if (tid == 0) {
+        dead = 0;
+        __threadfence();
+        asm volatile("fence.proxy.async;" ::: "memory");      // the positions written here are read by other blocks' bulk copies
+        const uint32_t arrived = atomicAdd(a.gridBar, 1u) + 1u;
+        const uint32_t target = (uint32_t)step * gridDim.x;
+        if (HALO && arrived == target) {      // last block of the colour: publish it to the neighbour partitions
+            const uint32_t done = *(volatile const uint32_t*)a.hv.ctl + (uint32_t)(a.hv.epochOffset + step);
+            __threadfence_system();
+            for (int p = 0; p < a.hv.nPeers; p++)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.hv.tab->peerFlag[p]), "r"(done) : "memory");
+        }
+        for (int i = 0; i < 5; i++) { mbar_inval(sb + kSmBarRec + 8 * i); mbar_init(sb + kSmBarRec + 8 * i, 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        prologue();
+        if (arrived != target) {
+            const unsigned long long t0 = gtimer();
+            uint32_t spins = 0;
+            while ((int32_t)(ld_acquire_gpu(a.gridBar) - target) < 0) {
+                if ((++spins & 1023u) == 0 && gtimer() - t0 > 4000000000ull) { atomicAdd(a.errFlags + 5, 1); dead = 1; break; }
+            }
+        }
+        __threadfence();      // acquire: the other blocks' positions are visible, stale L1 lines are dropped
+        asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    __syncthreads();
+    if (dead) return;
+    haloWaited = false;
+    }
+    if (MULTI && tid == 0) {      // last block out re-arms the barrier for the next launch
+        __syncwarp();
+        if (atomicAdd(a.gridBar + 1, 1u) == gridDim.x - 1) { a.gridBar[0] = 0u; a.gridBar[1] = 0u; __threadfence(); }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------- host
@@ -540,6 +623,15 @@ cudaError_t sweep_upload(Scene& s) {
     if (!s.h_rec.empty()) CK(cudaMemcpyAsync(s.rec.p, s.h_rec.data(), s.h_rec.size() * sizeof(uint2), cudaMemcpyHostToDevice, s.stream));
     if (!s.h_nbw.empty()) CK(cudaMemcpyAsync(s.nbw.p, s.h_nbw.data(), s.h_nbw.size() * sizeof(int2), cudaMemcpyHostToDevice, s.stream));
     if (!s.h_tiles.empty()) CK(cudaMemcpyAsync(s.tiles.p, s.h_tiles.data(), s.h_tiles.size() * sizeof(TileDesc), cudaMemcpyHostToDevice, s.stream));
+    {   // colour -> tile range, and the grid barrier of the multi-colour launch
+        const int G = (int)s.groupTileStart.size() - 1;
+        std::vector<int2> gt(std::max(G, 1), make_int2(0, 0));
+        for (int g = 0; g < G; g++) gt[g] = make_int2(s.groupTileStart[g], s.groupTileStart[g + 1]);
+        CK(s.groupTilesDev.alloc(gt.size()));
+        CK(cudaMemcpyAsync(s.groupTilesDev.p, gt.data(), gt.size() * sizeof(int2), cudaMemcpyHostToDevice, s.stream));
+        CK(s.gridBar.alloc(2));
+        CK(cudaMemsetAsync(s.gridBar.p, 0, 2 * sizeof(uint32_t), s.stream));
+    }
     CK(cudaStreamSynchronize(s.stream));
     std::vector<uint2>().swap(s.h_rec);
     std::vector<int2>().swap(s.h_nbw);
@@ -561,35 +653,74 @@ cudaError_t sweep_mark_halo_tiles(Scene& s, const int32_t* boundaryPrefixDev) {
     return cudaStreamSynchronize(s.stream);
 }
 
-template <int L, bool HC, bool HALO>
-static cudaError_t launch_tiles(Scene& s, const SweepArgs& a) {
-    const int nTiles = a.tileEnd - a.tileBegin;
+template <int L, bool HC, bool HALO, bool MULTI>
+static cudaError_t launch_tiles(Scene& s, const SweepArgs& a, int nTiles) {
     if (nTiles <= 0) return cudaSuccess;
-    const uint32_t variant = 1u << ((L == 8 ? 4 : 0) + (HC ? 2 : 0) + (HALO ? 1 : 0));
+    const uint32_t variant = 1u << ((MULTI ? 4 : 0) + (HC ? 2 : 0) + (HALO ? 1 : 0));
     if (!(s.sweepAttrSet & variant)) {      // per scene = per device (a second scene on another GPU sets its own)
-        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmTotal));
-        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmTotal));
+        CK(cudaFuncSetAttribute(k_sweep_tiles<L, HC, HALO, MULTI>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         s.sweepAttrSet |= variant;
     }
     const int grid = std::min(nTiles, s.numSMs * kSweepBlocksPerSM);
-    k_sweep_tiles<L, HC, HALO><<<grid, kSweepThreads, kSmTotal, s.stream>>>(a);
+    if (MULTI) {
+        // the blocks wait for one another between colours: a cooperative launch, so that all of them are resident
+        void* params[] = {(void*)&a};
+        return cudaLaunchCooperativeKernel((const void*)k_sweep_tiles<L, HC, HALO, MULTI>, dim3(grid), dim3(kSweepThreads), params, kSmTotal, s.stream);
+    }
+    k_sweep_tiles<L, HC, HALO, MULTI><<<grid, kSweepThreads, kSmTotal, s.stream>>>(a);
     return cudaGetLastError();
+}
+
+static void fill_common(Scene& s, SweepArgs& a) {
+    a.pos = s.pos.p; a.prev = s.prev.p; a.inertia = s.inertia.p; a.vtx2 = s.vtx2.p; a.rec = s.rec.p; a.nbw = s.nbw.p; a.tiles = s.tiles.p;
+    a.mp = s.meshParams.p; a.sp = s.stepParams; a.errFlags = s.errFlags.p;
+    a.needPrev = 0;
+    for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
+    if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
+    a.allActive = 1;
+    for (auto& m : s.meshes) if (!m.activeForMaterialSolve) a.allActive = 0;
+}
+
+// Can `nSteps` colours run as ONE launch? (contact-free colours only; all blocks must be resident at once)
+bool sweep_multi_available(Scene& s) {
+    if (s.multiStep < 0) {
+        int perSM = 0;
+        const bool ok = cudaFuncSetAttribute(k_sweep_tiles<kSweepLanes, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmTotal) == cudaSuccess &&
+                        cudaFuncSetAttribute(k_sweep_tiles<kSweepLanes, false, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) == cudaSuccess &&
+                        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_sweep_tiles<kSweepLanes, false, false, true>, kSweepThreads, kSmTotal) == cudaSuccess;
+        int coop = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, s.device);
+        s.multiStep = (ok && coop && perSM >= kSweepBlocksPerSM) ? 1 : 0;
+        cudaGetLastError();
+    }
+    return s.multiStep == 1;
+}
+
+// colours firstGroup, firstGroup+1, ... (cyclically) for nSteps steps in one launch; friction from step frictionFromStep on
+cudaError_t sweep_launch_multi(Scene& s, int firstGroup, int nSteps, int frictionFromStep, const HaloView* hv) {
+    SweepArgs a;
+    std::memset(&a, 0, sizeof(a));
+    fill_common(s, a);
+    const int G = (int)s.groupTileStart.size() - 1;
+    a.stepTiles = s.groupTilesDev.p; a.nSteps = nSteps; a.firstGroup = firstGroup; a.nGroups = G; a.frictionFromStep = frictionFromStep;
+    a.gridBar = s.gridBar.p;
+    int maxTiles = 0;
+    for (int g = 0; g < G; g++) maxTiles = std::max(maxTiles, s.groupTileStart[g + 1] - s.groupTileStart[g]);
+    if (hv) { a.hv = *hv; return launch_tiles<kSweepLanes, false, true, true>(s, a, maxTiles); }
+    return launch_tiles<kSweepLanes, false, false, true>(s, a, maxTiles);
 }
 
 cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv) {
     SweepArgs a;
     std::memset(&a, 0, sizeof(a));
     a.tileBegin = s.groupTileStart[group]; a.tileEnd = s.groupTileStart[group + 1];
-    a.pos = s.pos.p; a.prev = s.prev.p; a.inertia = s.inertia.p; a.vtx2 = s.vtx2.p; a.rec = s.rec.p; a.nbw = s.nbw.p; a.tiles = s.tiles.p;
-    a.mp = s.meshParams.p; a.sp = s.stepParams; a.applyFriction = applyFriction; a.cv = cv; a.errFlags = s.errFlags.p;
-    a.needPrev = 0;
-    for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
-    if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
-    a.allActive = 1;
-    for (auto& m : s.meshes) if (!m.activeForMaterialSolve) a.allActive = 0;
+    fill_common(s, a);
+    a.applyFriction = applyFriction; a.cv = cv;
+    const int nTiles = a.tileEnd - a.tileBegin;
     if (hv) a.hv = *hv;
-    if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true>(s, a) : launch_tiles<kSweepLanes, false, true>(s, a);
-    return hasContacts ? launch_tiles<kSweepLanes, true, false>(s, a) : launch_tiles<kSweepLanes, false, false>(s, a);
+    if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true, false>(s, a, nTiles) : launch_tiles<kSweepLanes, false, true, false>(s, a, nTiles);
+    return hasContacts ? launch_tiles<kSweepLanes, true, false, false>(s, a, nTiles) : launch_tiles<kSweepLanes, false, false, false>(s, a, nTiles);
 }
 
 }  // namespace gb

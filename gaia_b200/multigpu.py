@@ -140,6 +140,7 @@ def build_partitioned_scene(wl, rank, world, local_rank):
         assert len(remote) == len(ids), (rank, q, len(remote), len(ids))
         mv = np.stack([np.zeros(len(ids), np.int32), ids], 1)
         s.halo_add_peer(q, everyone[q]["handles"], mv, remote)
+    s.halo_set_world([e["handles"] for e in everyone])      # all ranks: agreement on "no contacts anywhere" (fused exchange)
     s.halo_finalize()
     dist.barrier()
     return s
@@ -193,6 +194,7 @@ def build_replicated_scene(wl, rank, world, local_rank):
     for q in range(world):
         if q != rank:
             s.halo_add_peer(q, everyone[q], mv, slots)
+    s.halo_set_world(everyone)
     s.halo_finalize()
     dist.barrier()
     return s

@@ -296,6 +296,12 @@ int gaia_b200_enable_mesh(gaia_handle* h, int mesh, int activeForCollision, int 
  *   halo_ipc_handles:   128 bytes: cudaIpcMemHandle_t of the position array, then of the flag array.
  *   halo_add_peer:      neighbour `peerRank`; send list = nSend vertices of mesh 0.. given as (mesh, vertex) pairs in
  *                       `sendMeshVerts` [2*nSend] and the neighbour's slots `remoteSlots` [nSend] they are stored to.
+ *   halo_set_world:     (optional, processes only) the 128-byte handle records of ALL ranks, rank 0 first. With a collision
+ *                       pipeline in the scene the exchange fused into the colour sweep is valid only while NO rank holds an
+ *                       active contact (the contact pre-pass of a colour reads ghost positions before the sweep); with the
+ *                       world known the ranks agree on that after every detection (one tiny launch over the peers' flag
+ *                       arrays) and fall back to the separate barrier + push launches otherwise. Without it: always the
+ *                       separate launches when a collision pipeline exists.
  *   halo_finalize:      after all peers were added and every process has opened its handles. */
 int gaia_b200_set_partition_mode(gaia_handle* h, int32_t myRank, int32_t worldSize);
 int gaia_b200_set_ghosts(gaia_handle* h, int mesh, const int32_t* verts, int32_t n);
@@ -303,6 +309,7 @@ int gaia_b200_get_sorted_ids(gaia_handle* h, int mesh, const int32_t* verts, int
 int gaia_b200_halo_ipc_handles(gaia_handle* h, void* out128);
 int gaia_b200_halo_add_peer(gaia_handle* h, int32_t peerRank, const void* peerHandles128, int32_t nSend,
                             const int32_t* sendMeshVerts, const int32_t* remoteSlots);
+int gaia_b200_halo_set_world(gaia_handle* h, int32_t worldSize, const void* handles /* 128 * worldSize bytes */);
 int gaia_b200_halo_finalize(gaia_handle* h);
 /* The same for partitions that live in ONE process (one host thread per GPU, e.g. gaia_vbd_b200 --gpus N): CUDA IPC handles
  * cannot be opened by the process that made them, so the neighbours' arrays are addressed directly (unified addressing +
@@ -342,6 +349,11 @@ void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that
  * association of the per-vertex sums, so it is a property of the layout built at finalize, not a run-time switch).
  * Accepts 0, 4 or 8 and has no effect. */
 int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
+/* Contact-free stretches of the colour loop (all colours of the iterations up to the next intermediate detection) run as ONE
+ * cooperative launch with a grid-wide barrier between colours (csrc/sweep.cu, MULTI) - the device-side form of the loop
+ * M/VBD/VBDPhysics.cpp:1659-1702. Results are bit-identical to one launch per colour; 0 switches back to that (default 1).
+ * Colours with active contacts always use one launch per colour (their contact pre-pass is a separate launch). */
+int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled);
 /* Bytes of the solver's HBM layout, for the bench's "inputs vs L2" note and for capacity planning:
  * out[0] per-tet record stream, out[1] per-neighbour entry stream, out[2] per-vertex state read or written by one iteration
  * (headers, positions, inertia, previous positions), out[3] tile table; out[4] = shared-memory position reads per

@@ -33,6 +33,8 @@ def main():
         wl = bench.workload_twist_beam(*dims, collisions=os.environ.get("GAIA_CHECK_DCD", "0") == "1")
     build = multigpu.build_replicated_scene if layout == "replicated" else multigpu.build_partitioned_scene
     s = build(wl, rank, world, local)
+    if os.environ.get("GAIA_CHECK_MULTI_PART", "1") == "0":
+        s.set_multi_colour_launch(False)
     s.run_frames(frames)
     s.synchronize()
     nV = len(wl["meshes"][0][0])
@@ -43,6 +45,8 @@ def main():
     ok = True
     if rank == 0:
         single = bench.build_scene(capi.Scene, wl, device=local)
+        if os.environ.get("GAIA_CHECK_MULTI_SINGLE", "1") == "0":
+            single.set_multi_colour_launch(False)
         single.run_frames(frames)
         ref = single.positions(0)
         moved = float(np.abs(ref - wl["meshes"][0][0]).max())
@@ -50,7 +54,7 @@ def main():
         con = single.contacts()
         print(f"[check_multigpu] {wl['name']} | layout={layout} world={world} frames={frames} moved={moved:.4f} bit_exact={same} "
               f"maxdiff={float(np.abs(got - ref).max()):.3e} solves {int(solves.item())} vs {single.stats()['vertexSolves']} "
-              f"contacts(single, last detection)={len(con)}", flush=True)
+              f"contacts(single, last detection)={len(con)} multi(part,single)={os.environ.get('GAIA_CHECK_MULTI_PART', '1')},{os.environ.get('GAIA_CHECK_MULTI_SINGLE', '1')}", flush=True)
         ok = same and moved > 1e-3 and int(solves.item()) == single.stats()["vertexSolves"]
         single.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
