@@ -293,7 +293,8 @@ bool halo_view(Scene& s, HaloView& hv) {
     HaloState* h = s.halo;
     // Partitions of one process (directly addressed peers) use the separate push + wait launches: with the exchange fused
     // into the sweep they lost bit-identity with the single-GPU run at the cut (14 vertices, 4e-9, after two iterations on
-    // a 2-GPU beam; between processes over CUDA IPC the fused exchange is bit-identical). Cause not found yet.
+    // a 2-GPU beam; between processes over CUDA IPC the fused exchange is bit-identical). Cause not found yet (re-tried after
+    // the sweep was compiled without FMA contraction: still different, so it is not an arithmetic difference between variants).
     for (auto& p : h->peers) if (!p.viaIpc) return false;
     std::memset(&hv, 0, sizeof(hv));
     hv.nPeers = (int)h->peers.size();

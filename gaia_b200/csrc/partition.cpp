@@ -152,21 +152,27 @@ int gaia_b200_partition_restrict_ids(const gaia_partition* p, int32_t n, const i
     return k;
 }
 // global colouring -> local colouring, colour order kept (every partition sweeps the same colour together); inside a colour
-// the vertices this rank SENDS come first, so their tiles run in the first wave of the colour's launch and the halo stores
-// overlap the interior. outOffsets: nColors + 1; outVerts: sized for all local vertices.
+// the vertices this rank SENDS sit behind the first 2/5 of the interior vertices: when their tiles come up the neighbours have
+// long finished the previous colour (no stall on the epoch flag), and the halo stores still overlap the rest of the interior.
+// outOffsets: nColors + 1; outVerts: sized for all local vertices.
 int gaia_b200_partition_restrict_colors(const gaia_partition* p, int32_t nColors, const int32_t* offsets, const int32_t* verts,
                                         int32_t* outOffsets, int32_t* outVerts) {
     if (!p || nColors < 0 || !offsets || !outOffsets || !outVerts) return GAIA_ERR_INVALID_ARG;
     int32_t run = 0;
+    std::vector<int32_t> inner, edge;
     for (int32_t c = 0; c < nColors; c++) {
         outOffsets[c] = run;
-        for (int pass = 0; pass < 2; pass++)
-            for (int32_t i = offsets[c]; i < offsets[c + 1]; i++) {
-                const int32_t g = verts[i];
-                if (g < 0 || g >= (int32_t)p->g2l.size()) return GAIA_ERR_INVALID_ARG;
-                const int32_t l = p->g2l[g];
-                if (l >= 0 && (p->boundary[l] != 0) == (pass == 0)) outVerts[run++] = l;
-            }
+        inner.clear(); edge.clear();
+        for (int32_t i = offsets[c]; i < offsets[c + 1]; i++) {
+            const int32_t g = verts[i];
+            if (g < 0 || g >= (int32_t)p->g2l.size()) return GAIA_ERR_INVALID_ARG;
+            const int32_t l = p->g2l[g];
+            if (l >= 0) (p->boundary[l] ? edge : inner).push_back(l);
+        }
+        const size_t k = (2 * inner.size()) / 5;
+        for (size_t i = 0; i < k; i++) outVerts[run++] = inner[i];
+        for (int32_t l : edge) outVerts[run++] = l;
+        for (size_t i = k; i < inner.size(); i++) outVerts[run++] = inner[i];
     }
     outOffsets[nColors] = run;
     return GAIA_OK;

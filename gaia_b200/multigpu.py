@@ -75,16 +75,19 @@ class Partition:
 
     def restrict_colors(self, colors):
         """Global colouring -> local colouring, colour order kept (every partition sweeps the same colour together).
-        Inside a colour the vertices this rank SENDS come first: their blocks then run in the first wave of the colour's
-        launch, so the wait for the neighbours' epoch, the peer stores and the system-scope fence overlap with the interior
-        blocks instead of trailing the launch (a vertex update does not depend on the order inside a colour)."""
+        Inside a colour the vertices this rank SENDS sit behind the first 2/5 of the interior vertices: when their tiles come up
+        the neighbours have long finished the previous colour (no stall on the epoch flag, which a boundary-first order paid at
+        the start of every colour), and the peer stores and the system-scope fence still overlap with the remaining interior
+        tiles instead of trailing the launch (a vertex update does not depend on the order inside a colour)."""
         boundary = np.zeros(len(self.local_verts), bool)
         for ids in self.send.values():
             boundary[ids] = True
         out = []
         for c in (np.asarray(c) for c in colors):
             l = self.g2l[c[self.g2l[c] >= 0]]
-            out.append(np.concatenate([l[boundary[l]], l[~boundary[l]]]).astype(np.int32))
+            inner, edge = l[~boundary[l]], l[boundary[l]]
+            k = (2 * len(inner)) // 5
+            out.append(np.concatenate([inner[:k], edge, inner[k:]]).astype(np.int32))
         return out
 
     def restrict_ids(self, ids):
