@@ -509,8 +509,9 @@ class Scene(SceneBase):
         return dict(zip(("records", "neighbours", "vertex_state", "tiles", "pos_reads", "incidences"), [int(x) for x in a]))
 
     def set_multi_colour_launch(self, enabled):
-        """contact-free stretches of the colour loop as one cooperative launch (default on); results do not change"""
-        self._call("set_multi_colour_launch", int(bool(enabled)))
+        """contact-free stretches of the colour loop as one cooperative launch: False / 0 never, True / 1 (default) where the
+        host issues the loop, 2 everywhere (no graph replay of per-colour launches); results do not change"""
+        self._call("set_multi_colour_launch", int(enabled))
 
     def set_solver_lanes(self, lanes):
         """0 (default 4), 4 or 8 lanes per vertex; runs compared bit for bit must use the same value"""

@@ -550,7 +550,8 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
 int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled) {
     REQUIRE(h);
     if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }
-    h->s.multiStepAllowed = enabled != 0;
+    if (enabled < 0 || enabled > 2) return fail(h->s, GAIA_ERR_INVALID_ARG, "multi-colour launch: 0 (off), 1 (default) or 2 (always)");
+    h->s.multiStepMode = enabled;
     return GAIA_OK;
 }
 int gaia_b200_get_layout_bytes(gaia_handle* h, int64_t out[6]) {

@@ -118,7 +118,7 @@ struct Scene {
     DevBuf<int2> groupTilesDev;            // [G] {first tile, end tile}: what the multi-colour launch steps through
     DevBuf<uint32_t> gridBar;              // its grid barrier: [0] arrivals, [1] exits
     int multiStep = -1;                    // -1 not probed yet, 0 unavailable, 1 available
-    bool multiStepAllowed = true;          // gaia_b200_set_multi_colour_launch
+    int multiStepMode = 1;                 // gaia_b200_set_multi_colour_launch: 0 never, 1 where the host issues the loop, 2 always
     int64_t sweepPosReads = 0;             // shared-memory position reads per sweep over all vertices (3 per restart, 1 per strip step)
     DevBuf<int4> vtx2;
     DevBuf<uint2> rec;

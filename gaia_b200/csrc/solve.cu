@@ -376,7 +376,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     //  multi-colour launch, which in turn is 3 % faster than per-colour launches issued by the host. So: loops that replay
     //  from a graph keep one launch per colour; loops the host has to issue - intermediate detection cuts them into
     //  stretches - use one multi-colour launch per stretch)
-    const bool useMulti = s.multiStepAllowed && !s.phys.useAccelerator && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
+    const bool useMulti = s.multiStepMode != 0 && !s.phys.useAccelerator && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
     for (int it = 0; it < nIters; it++) {
         const int applyFriction = it >= s.phys.frictionStartIter;
         // Contact-free stretch of iterations (up to the next intermediate detection): ONE launch sweeps all its colours, with
@@ -466,11 +466,12 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
     const bool withContacts = s.cs != nullptr;
     const bool contactsOk = !withContacts || (collision_graphable(s) && !halo_active(s) && !s.phys.useAccelerator &&
                                               !(allowIntermediateCD && s.phys.intermediateCollisionIterations > 0));
-    const bool graphable = s.profiling != 1 && contactsOk && s.iterCalls > 0 && nIters > 0;
+    // (mode 2 of gaia_b200_set_multi_colour_launch: never replay a graph of per-colour launches, always issue multi-colour launches)
+    const bool graphable = s.profiling != 1 && contactsOk && s.iterCalls > 0 && nIters > 0 && s.multiStepMode != 2;
     s.iterCalls++;
     // (graphShape: this loop is replayed from a graph whenever profiling / the first call do not prevent it - those calls take
     //  the same launch shape, so that what the profiling pass times is what the timed pass runs)
-    if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD, false, contactsOk && nIters > 0);
+    if (!graphable) return enqueue_iterations(s, nIters, allowIntermediateCD, false, contactsOk && nIters > 0 && s.multiStepMode != 2);
     if (!s.iterGraphExec || s.iterGraphIters != nIters) {
         if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }
         const gaia_stats before = s.stats;

@@ -351,8 +351,11 @@ void* gaia_b200_cuda_stream(gaia_handle* h);   /* cudaStream_t, for callers that
 int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
 /* Contact-free stretches of the colour loop (all colours of the iterations up to the next intermediate detection) run as ONE
  * cooperative launch with a grid-wide barrier between colours (csrc/sweep.cu, MULTI) - the device-side form of the loop
- * M/VBD/VBDPhysics.cpp:1659-1702. Results are bit-identical to one launch per colour; 0 switches back to that (default 1).
- * Colours with active contacts always use one launch per colour (their contact pre-pass is a separate launch). */
+ * M/VBD/VBDPhysics.cpp:1659-1702. Results are bit-identical to one launch per colour. enabled: 0 = one launch per colour
+ * everywhere; 1 (default) = multi-colour launches where the host issues the loop (intermediate detection cuts it into
+ * stretches), while loops that replay from a CUDA graph keep one launch per colour (measured faster on large colours);
+ * 2 = multi-colour launches everywhere (no graph replay). Colours with active contacts always use one launch per colour
+ * (their contact pre-pass is a separate launch). */
 int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled);
 /* Bytes of the solver's HBM layout, for the bench's "inputs vs L2" note and for capacity planning:
  * out[0] per-tet record stream, out[1] per-neighbour entry stream, out[2] per-vertex state read or written by one iteration

@@ -221,6 +221,7 @@ def test_multi_colour_launch_is_bit_identical_to_one_launch_per_colour(case):
             return make_beam_scene(capi.Scene, v0=(1.0, -5.0, 0.5), substeps=4, iterations=10, phys_kw=dict(frictionStartIter=3))
         return workloads.build_scene(capi.Scene, wl)
     a, b = build(), build()
+    a.set_multi_colour_launch(2)          # everywhere, also where the default would replay a graph of per-colour launches
     b.set_multi_colour_launch(False)
     frames = 12 if case != "pile_before_impact" else 6
     for s in (a, b):
@@ -232,5 +233,4 @@ def test_multi_colour_launch_is_bit_identical_to_one_launch_per_colour(case):
         assert np.array_equal(a.velocities(m), b.velocities(m)), (case, m)
     sa, sb = a.stats(), b.stats()
     assert sa["vertexSolves"] == sb["vertexSolves"] and sa["colourSweeps"] == sb["colourSweeps"]
-    if case != "pile_before_impact":      # (a small scene with a collision pipeline may replay a captured per-colour graph)
-        assert sa["kernelLaunches"] < sb["kernelLaunches"]        # the stretches really were single launches
+    assert sa["kernelLaunches"] < sb["kernelLaunches"]            # the stretches really were single launches
