@@ -379,6 +379,7 @@ def load_library(path=None):
     lib.gaia_b200_color_tet_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_tri_mesh.argtypes = [C.c_int32, C.c_int32, IP, C.c_int32, C.c_int32, C.c_float, IP, IP, IP]
     lib.gaia_b200_color_graph_device.argtypes = [C.c_int, C.c_int32, C.c_int64, IP, C.c_int32, C.c_float, IP, IP, IP]
+    lib.gaia_b200_color_graph_device_noalloc.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
     I64P, U8P = C.POINTER(C.c_int64), C.POINTER(C.c_uint8)
     lib.gaia_b200_partition_slab_owner.argtypes = [C.c_int32, FP, C.c_int32, C.c_int32, IP]
     lib.gaia_b200_partition_create.argtypes = [C.c_int32, C.c_int64, IP, IP, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]
@@ -561,6 +562,22 @@ def color_graph_device(num_nodes, edges, balance=True, goal_max_min_ratio=1.05, 
     e = _i32(np.asarray(edges, np.int32).reshape(-1, 2))
     fn = load_library().gaia_b200_color_graph_device
     return _categories(lambda *a: fn(int(device), *a), int(num_nodes), int(num_nodes), len(e), _ip(e), 1 if balance else 0, float(goal_max_min_ratio))
+
+
+NOALLOC_COLOR_MAX_NODES = 1 << 20
+
+
+def color_graph_device_noalloc(num_nodes, d_offsets, d_adjacency, d_colors, device=0):
+    """gaia_b200_color_graph_device_noalloc: d_* are DEVICE addresses (ints) of the caller's CSR graph and colour output; returns
+    the number of colours. Allocates nothing on the device (fixed scratch inside the library, NOALLOC_COLOR_MAX_NODES nodes)."""
+    msg = C.create_string_buffer(256)
+    rc = load_library().gaia_b200_color_graph_device_noalloc(int(device), int(num_nodes), C.c_void_p(int(d_offsets)), C.c_void_p(int(d_adjacency)),
+                                                            C.c_void_p(int(d_colors)), msg, 256)
+    if rc < 0:
+        e = GaiaError(f"gaia_b200_color_graph_device_noalloc failed: {rc} {msg.value.decode()}")
+        e.code = rc
+        raise e
+    return rc
 
 
 def tet_mesh_edges(n_verts, tets):

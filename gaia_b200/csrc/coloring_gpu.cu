@@ -12,6 +12,8 @@
 //     ranks from a device prefix sum - deterministic as well.
 #include <algorithm>
 #include <cstdint>
+#include <cstdio>
+#include <mutex>
 #include <vector>
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
@@ -167,5 +169,114 @@ extern "C" int gaia_b200_color_graph_device(int device, int32_t numNodes, int64_
         std::vector<int32_t> at(cnt.begin(), cnt.end() - 1);
         for (int v = 0; v < n; v++) categoryNodes[at[col[v]]++] = v;
     }
+    return nc;
+}
+
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+// gaia_b200_color_graph_device_noalloc: the speculative greedy above for callers that may not allocate (CUDA graph capture
+// around them, serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// Its scratch - the two committed-colour arrays the rounds ping-pong between, the tentative colours, the
+// round counters and the colour histogram - lives in ONE file-scope device array of fixed size, which every GPU that loads
+// this library holds until the process exits: 3 * GAIA_NOALLOC_COLOR_MAX_NODES * 4 B + 512 B = 12 MB + 512 B.
+// All calls share that array (it keeps the last call's contents; what must start clean is cleared per call), so two calls
+// that overlap on one GPU race: serialise them.
+namespace {
+
+constexpr int64_t kNoAllocMaxNodes = GAIA_NOALLOC_COLOR_MAX_NODES;
+constexpr int64_t kNoAllocCounterWords = 128;      // [0] nodes left, [1] overflow, [2] bad input, [64..127] histogram
+constexpr int64_t kNoAllocWords = 3 * kNoAllocMaxNodes + kNoAllocCounterWords;
+static __device__ __align__(256) int32_t g_noalloc_scratch[kNoAllocWords];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noallocMutex;
+int32_t* g_noallocPtr[kNoAllocMaxDevices] = {};      // device address of g_noalloc_scratch on each device (resolved once)
+
+// host code cannot use the array's name as an address: ask the runtime, once per device, with that device current
+int noalloc_scratch(int device, int32_t** out) {
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocPtr[device]) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_noalloc_scratch) != cudaSuccess || !p) { cudaGetLastError(); return GAIA_ERR_CUDA; }
+        g_noallocPtr[device] = (int32_t*)p;
+    }
+    *out = g_noallocPtr[device];
+    return GAIA_OK;
+}
+
+// the CSR arrays come from the caller's device memory: offsets must start at 0 and ascend, neighbours must be other nodes
+__global__ void k_check_csr(int n, const int32_t* __restrict__ off, const int32_t* __restrict__ adj, int32_t* bad) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const int b = off[v], e = off[v + 1];
+    if ((v == 0 && b != 0) || e < b) { *bad = 1; return; }
+    for (int q = b; q < e; q++) { const int u = adj[q]; if (u < 0 || u >= n || u == v) { *bad = 1; return; } }
+}
+
+void noalloc_message(char* msg, int32_t cap, const char* text) {
+    if (msg && cap > 0) std::snprintf(msg, (size_t)cap, "%s", text);
+}
+
+}  // namespace
+
+extern "C" int gaia_b200_color_graph_device_noalloc(int device, int32_t numNodes, const int32_t* dOffsets, const int32_t* dAdjacency,
+                                                    int32_t* dColors, char* errMsg, int32_t errMsgCap) {
+    noalloc_message(errMsg, errMsgCap, "");
+    if (numNodes < 0 || (numNodes > 0 && (!dOffsets || !dAdjacency || !dColors))) {
+        noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: null pointer or negative node count");
+        return GAIA_ERR_INVALID_ARG;
+    }
+    if ((int64_t)numNodes > kNoAllocMaxNodes) {
+        char text[200];
+        std::snprintf(text, sizeof(text), "color_graph_device_noalloc: %d nodes exceed the fixed scratch of GAIA_NOALLOC_COLOR_MAX_NODES = %lld "
+                      "(use gaia_b200_color_graph_device, which allocates)", (int)numNodes, (long long)kNoAllocMaxNodes);
+        noalloc_message(errMsg, errMsgCap, text);
+        return GAIA_ERR_OVERFLOW;
+    }
+    if (numNodes == 0) return 0;
+    int nDev = 0;
+    if (cudaGetDeviceCount(&nDev) != cudaSuccess || device < 0 || device >= nDev || device >= kNoAllocMaxDevices) {
+        noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: no such CUDA device");
+        return GAIA_ERR_NO_DEVICE;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) { noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: cudaSetDevice failed"); return GAIA_ERR_CUDA; }
+    int32_t* scratch = nullptr;
+    if (noalloc_scratch(device, &scratch) != GAIA_OK) {
+        noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: cudaGetSymbolAddress of the scratch array failed");
+        return GAIA_ERR_CUDA;
+    }
+#define CKN(x) do { if ((x) != cudaSuccess) { cudaGetLastError(); noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: CUDA error in " #x); return GAIA_ERR_CUDA; } } while (0)
+    const int n = numNodes;
+    int32_t* dA = scratch;
+    int32_t* dB = scratch + kNoAllocMaxNodes;
+    int32_t* dT = scratch + 2 * kNoAllocMaxNodes;
+    int32_t* dCnt = scratch + 3 * kNoAllocMaxNodes;        // [0] left, [1] overflow, [2] bad input
+    int32_t* dSizes = dCnt + 64;
+    const int B = 256, G = (n + B - 1) / B;
+    // the array still holds the previous call's colours: nothing is committed yet, all counters zero
+    CKN(cudaMemsetAsync(dA, 0xff, (size_t)n * sizeof(int32_t), 0));
+    CKN(cudaMemsetAsync(dCnt, 0, kNoAllocCounterWords * sizeof(int32_t), 0));
+    k_check_csr<<<G, B>>>(n, dOffsets, dAdjacency, dCnt + 2);
+    int32_t h[3] = {0, 0, 0};
+    CKN(cudaMemcpy(h, dCnt, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    if (h[2]) { noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: offsets do not ascend from 0, or a neighbour is out of range / the node itself"); return GAIA_ERR_INVALID_ARG; }
+    int32_t *cur = dA, *nxt = dB;
+    for (int round = 0; round < 10000; round++) {
+        CKN(cudaMemsetAsync(dCnt, 0, 2 * sizeof(int32_t), 0));
+        k_speculate<<<G, B>>>(n, dOffsets, dAdjacency, cur, dT, dCnt + 1);
+        k_resolve<<<G, B>>>(n, dOffsets, dAdjacency, cur, dT, nxt, dCnt);
+        CKN(cudaMemcpy(h, dCnt, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        std::swap(cur, nxt);
+        if (h[1]) { noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: more than 64 colours needed"); return GAIA_ERR_UNSUPPORTED; }
+        if (!h[0]) break;
+    }
+    k_histogram<<<G, B>>>(n, cur, dSizes);
+    CKN(cudaMemcpyAsync(dColors, cur, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToDevice, 0));
+    int32_t sizes[64];
+    CKN(cudaMemcpy(sizes, dSizes, 64 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    CKN(cudaGetLastError());
+#undef CKN
+    int nc = 0;
+    for (int c = 0; c < 64; c++) if (sizes[c]) nc = c + 1;
     return nc;
 }

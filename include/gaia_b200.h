@@ -393,6 +393,19 @@ int gaia_b200_color_tri_mesh(int32_t nV, int32_t nF, const int32_t* faces, int32
  * the tool's exact output matters). flags: GAIA_COLOR_BALANCE. At most 64 colours (GAIA_ERR_UNSUPPORTED beyond). */
 int gaia_b200_color_graph_device(int device, int32_t numNodes, int64_t nEdges, const int32_t* edges, int32_t flags, float goalMaxMinRatio,
                                  int32_t* colors, int32_t* categoryOffsets, int32_t* categoryNodes);
+/* Allocation-free variant of the call above. It has NO counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). It runs the same deterministic speculative greedy (no balancing pass) and calls no cudaMalloc / cudaFree / allocating
+ * library routine: its scratch is a file-scope device array in csrc/coloring_gpu.cu sized for GAIA_NOALLOC_COLOR_MAX_NODES
+ * nodes (12 MB + 512 B, held by every GPU that loads the library until the process exits); more nodes -> GAIA_ERR_OVERFLOW.
+ * Inputs and output are the CALLER's device memory on `device`: the undirected graph in CSR form (dOffsets [numNodes + 1],
+ * dAdjacency [dOffsets[numNodes]], every edge listed from both ends, no self loops) and dColors [numNodes]. Returns the
+ * number of colours (same colours as gaia_b200_color_graph_device with flags = 0) or a negative gaia_status; errMsg
+ * (optional, errMsgCap bytes) receives the reason. Work is issued on the legacy default stream and complete on return.
+ * All calls share the one scratch array: calls that overlap on the same GPU race - serialise them. */
+#define GAIA_NOALLOC_COLOR_MAX_NODES (1 << 20)
+int gaia_b200_color_graph_device_noalloc(int device, int32_t numNodes, const int32_t* dOffsets, const int32_t* dAdjacency,
+                                         int32_t* dColors, char* errMsg, int32_t errMsgCap);
 
 #ifdef __cplusplus
 }
