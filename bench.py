@@ -201,6 +201,7 @@ def main():
     ap.add_argument("--layout", default="ring", choices=["ring", "replicated"],
                     help="N > 1, one mesh: 'ring' = slabs with a one-ring ghost layer (contacts seen inside a slab and its ring), "
                          "'replicated' = solve partitioned, whole mesh on every rank as collision geometry (contacts between any two ranks)")
+    ap.add_argument("--refit-margin", type=float, default=None, help="lazy-refit margin of the DCD trees in typical tet edges (library default 0.2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=1, help="extra untimed steps with per-kernel CUDA events for the roofline")
     args = ap.parse_args()
@@ -227,6 +228,9 @@ def main():
 
     t0 = time.time()
     wl = WORKLOADS[args.workload]()
+    if args.refit_margin is not None:
+        wl["refit_margin"] = args.refit_margin
+        wl["name"] += f", refit margin {args.refit_margin} edges"
     if world > 1:
         if is_cloth(wl):
             raise SystemExit("the cloth workloads run on one GPU (north_star partitions configs 4 and 5 only)")

@@ -164,6 +164,7 @@ def bind_scene_api(lib, prefix):
         "get_active_list": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
         "get_relations": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
         "set_partition_mode": ([P, C.c_int32, C.c_int32], C.c_int), "set_ghosts": ([P, C.c_int, IP, C.c_int32], C.c_int),
+        "set_line_search": ([P, C.c_int32, C.c_float, C.c_float, C.c_int32], C.c_int), "line_search_shrinks": ([P], C.c_int64),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, prefix + name)
@@ -215,6 +216,14 @@ class SceneBase:
 
     def run_frames(self, n=1):
         self._call("run_frames", n)
+
+    def set_line_search(self, enabled=True, tau=0.5, tau_gd=0.1, max_iters=16):
+        """backtracking line search on the vertex merit energy (APPLY_LOCAL_LINE_SEARCH, M/VBD/VBDPhysics.cpp:25, 2467-2474)"""
+        self._call("set_line_search", int(bool(enabled)), float(tau), float(tau_gd), int(max_iters))
+
+    def line_search_shrinks(self):
+        """trial steps the line search rejected so far (each one shrank alpha by tau)"""
+        return int(getattr(self._lib, self._prefix + "line_search_shrinks")(self.h))
 
     def run_iterations(self, n=1):
         self._call("run_iterations", n)
@@ -371,6 +380,7 @@ def load_library(path=None):
     lib.gaia_b200_set_profiling.argtypes = [P, C.c_int]
     lib.gaia_b200_set_solver_lanes.argtypes = [P, C.c_int]
     lib.gaia_b200_set_multi_colour_launch.argtypes = [P, C.c_int]
+    lib.gaia_b200_set_lazy_refit_margin.argtypes = [P, C.c_float]
     lib.gaia_b200_get_layout_bytes.argtypes = [P, C.POINTER(C.c_int64)]
     lib.gaia_b200_total_surface_vertices.argtypes = [P]; lib.gaia_b200_total_surface_vertices.restype = C.c_int64
     lib.gaia_b200_surface_snapshot_begin.argtypes = [P, C.c_int]
@@ -508,6 +518,10 @@ class Scene(SceneBase):
         a = (C.c_int64 * 6)()
         self._call("get_layout_bytes", a)
         return dict(zip(("records", "neighbours", "vertex_state", "tiles", "pos_reads", "incidences"), [int(x) for x in a]))
+
+    def set_lazy_refit_margin(self, edges):
+        """margin of the DCD trees' boxes in typical tet edges (default 0.2; 0 = refit at every detection); before finalize"""
+        self._call("set_lazy_refit_margin", float(edges))
 
     def set_multi_colour_launch(self, enabled):
         """contact-free stretches of the colour loop as one cooperative launch: False / 0 never, True / 1 (default) where the

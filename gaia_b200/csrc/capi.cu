@@ -547,6 +547,35 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
     h->s.solveLanes = lanes;
     return GAIA_OK;
 }
+int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float tauGD, int32_t maxIters) {
+    REQUIRE(h); FINALIZED(h);
+    Scene& s = h->s;
+    if (enabled && (!(tau > 0.f && tau < 1.f) || !(tauGD > 0.f && tauGD < 1.f) || maxIters < 0 || maxIters > 64))
+        return fail(s, GAIA_ERR_INVALID_ARG, "line search: 0 < tau, tauGD < 1 and 0 <= maxIters <= 64");
+    cudaSetDevice(s.device);
+    if (s.iterGraphExec) { cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }
+    if (enabled) {
+        const cudaError_t e = linesearch_upload(s);
+        if (e != cudaSuccess) return cuda_fail(s, e);
+        s.lineSearch.tau = tau; s.lineSearch.tauGD = tauGD; s.lineSearch.maxIters = maxIters;
+    }
+    s.lineSearch.enabled = enabled != 0;
+    return GAIA_OK;
+}
+int64_t gaia_b200_line_search_shrinks(gaia_handle* h) {
+    if (!h || !h->s.lsShrinks.p) return 0;
+    unsigned long long v = 0;
+    cudaSetDevice(h->s.device);
+    if (cudaStreamSynchronize(h->s.stream) != cudaSuccess || cudaMemcpy(&v, h->s.lsShrinks.p, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int64_t)v;
+}
+int gaia_b200_set_lazy_refit_margin(gaia_handle* h, float edges) {
+    REQUIRE(h);
+    if (h->s.finalized) return fail(h->s, GAIA_ERR_STATE, "set_lazy_refit_margin after finalize");
+    if (!(edges >= 0.f && edges <= 4.f)) return fail(h->s, GAIA_ERR_INVALID_ARG, "lazy refit margin: 0 .. 4 typical tet edges");
+    h->s.lazyRefitMargin = edges;
+    return GAIA_OK;
+}
 int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled) {
     REQUIRE(h);
     if (h->s.iterGraphExec) { cudaGraphExecDestroy(h->s.iterGraphExec); h->s.iterGraphExec = nullptr; }

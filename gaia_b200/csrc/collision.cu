@@ -369,7 +369,7 @@ cudaError_t collision_init(Scene& s) {
         // deforming bodies; the larger boxes cost little because between refits queries run from the candidate cache
         double vol = 0.0; int64_t cnt = 0;
         for (auto& m : s.meshes) for (float v : m.restVol) { vol += std::fabs((double)v); cnt++; }
-        c->lazyMargin = cnt ? 0.2f * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
+        c->lazyMargin = cnt ? s.lazyRefitMargin * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
     }
     if (s.col.allowCCD) CK(c->ccdBvh.alloc((int)nF, oneSegF));
     const size_t nM = s.meshes.size();

@@ -326,7 +326,8 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     //  so the exchange of the previous colour must be complete when it starts: the separate push + wait launch is used.
     //  A scene WITH a collision pipeline may still use the fused exchange while no rank holds an active contact - there
     //  is no pre-pass then - which the ranks agree on after every detection: halo_vote)
-    const bool canFuse = halo && !s.phys.useAccelerator && halo_view(s, hv);
+    const bool lineSearch = s.lineSearch.enabled;      // (its kernel does not push: separate halo launches)
+    const bool canFuse = halo && !s.phys.useAccelerator && !lineSearch && halo_view(s, hv);
     bool fused = canFuse && !s.cs;
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
@@ -376,7 +377,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     //  multi-colour launch, which in turn is 3 % faster than per-colour launches issued by the host. So: loops that replay
     //  from a graph keep one launch per colour; loops the host has to issue - intermediate detection cuts them into
     //  stretches - use one multi-colour launch per stretch)
-    const bool useMulti = s.multiStepMode != 0 && !s.phys.useAccelerator && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
+    const bool useMulti = s.multiStepMode != 0 && !s.phys.useAccelerator && !lineSearch && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
     for (int it = 0; it < nIters; it++) {
         const int applyFriction = it >= s.phys.frictionStartIter;
         // Contact-free stretch of iterations (up to the next intermediate detection): ONE launch sweeps all its colours, with
@@ -419,7 +420,8 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             CK(prof_begin(1));
             hv.epochOffset = batch;
             if (fused) batch++;
-            if (ve > vb) CK(sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
+            if (ve > vb) CK(lineSearch ? sweep_launch_linesearch(s, g, applyFriction, hasContacts, cv)
+                                       : sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
             prof_end();
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one

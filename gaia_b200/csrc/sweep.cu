@@ -167,7 +167,9 @@ __device__ __forceinline__ void box_friction(float mu, float lambda, float ua, f
 
 // The vertex-level part of VBDStepWithCollision once the incident-tet sums are known. (fx,fy,fz) = -f_elastic,
 // s1 = A sum|m0|^2, g = sum A g g^T (already / 6). Returns true when a new position was written.
-template <bool HAS_CONTACTS>
+// LS: do not move the vertex; hand the descent direction back instead (xNew = {dx, +-step}: negative step = the 3x3 solve
+// failed and dx is the force) - the line-search variant decides the step length itself.
+template <bool HAS_CONTACTS, bool LS = false>
 __device__ __forceinline__ bool vertex_tail(int s, float3 x, float4 ys, float3 xp, const MeshParamsDev* __restrict__ P,
                                             float fx, float fy, float fz, float s1, float g00, float g01, float g02, float g11, float g12, float g22,
                                             float4* pos, const StepParamsDev& sp, int applyFriction, const ContactView& cv, int32_t* errFlags, float4& xNew) {
@@ -245,8 +247,9 @@ __device__ __forceinline__ bool vertex_tail(int s, float3 x, float4 ys, float3 x
         const float i13 = h12 * h01 - h11 * h02;
         const float det = h00 * i11 + h01 * i12 + h02 * i13;
         float dx0, dx1, dx2, step;
+        bool failed = false;
         if (fabsf(det) < 1e-5f * (fabsf(h00 * i11) + fabsf(h01 * i12) + fabsf(h02 * i13))) {
-            dx0 = F0; dx1 = F1; dx2 = F2; step = sp.stepSizeGD;
+            dx0 = F0; dx1 = F1; dx2 = F2; step = sp.stepSizeGD; failed = true;
             atomicAdd(errFlags + 1, 1);
         } else {
             const float deti = 1.f / det;
@@ -259,6 +262,7 @@ __device__ __forceinline__ bool vertex_tail(int s, float3 x, float4 ys, float3 x
             step = sp.stepSize;
         }
         if (isnan(dx0) || isnan(dx1) || isnan(dx2)) { atomicAdd(errFlags + 0, 1); return false; }
+        if (LS) { xNew = make_float4(dx0, dx1, dx2, failed ? -step : step); return true; }
         xNew = make_float4(x.x + step * dx0, x.y + step * dx1, x.z + step * dx2, 0.f);
         pos[s] = xNew;
         return true;
@@ -721,6 +725,207 @@ cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContact
     if (hv) a.hv = *hv;
     if (hv) return hasContacts ? launch_tiles<kSweepLanes, true, true, false>(s, a, nTiles) : launch_tiles<kSweepLanes, false, true, false>(s, a, nTiles);
     return hasContacts ? launch_tiles<kSweepLanes, true, false, false>(s, a, nTiles) : launch_tiles<kSweepLanes, false, false, false>(s, a, nTiles);
+}
+
+
+// ------------------------------------------------------------------------------------------------ line-search variant
+// APPLY_LOCAL_LINE_SEARCH (M/VBD/VBDPhysics.cpp:25, 2467-2474; compiled OUT in the reference, named by north_star): after the
+// 3x3 solve the step length is found by backtracking on the vertex merit energy - inertia + Neo-Hookean energy of the
+// incident tets (evaluateVertexMeritEnergy, M/VBD/VBD_NeoHookean.cpp:90-124; backTracingLineSearchVBD, VBD_NeoHookean.h:115-153).
+// The energy needs |F|^2 and det F of every incident tet at up to maxIters trial positions, which the tile records (det B',
+// slots, summed weights) do not hold, so this variant is a kernel of its own over plain per-tet tables (Dm^-1, rest volume,
+// vertex ids; uploaded when the option is switched on): one thread per vertex, incident tets in the reference's order
+// (ascending tet id), F = Ds Dm^-1 as the reference forms it. It is a feature switch, not a fast path.
+struct LsArgs {
+    int vBegin, vEnd;
+    float4* pos;
+    const float4* prev;
+    const float4* inertia;
+    const int4* vtx2;
+    const int32_t* off;       // [N + 1] over sorted ids
+    const int2* ent;          // {global tet, order of the vertex in it}
+    const int4* tetSid;       // sorted ids of the tet's vertices
+    const float4* tetDm;      // 3 per tet: Dm^-1 column-major [0..8], rest volume
+    const MeshParamsDev* mp;
+    StepParamsDev sp;
+    int applyFriction, needPrev;
+    ContactView cv;
+    int32_t* errFlags;
+    float tau, tauGD;
+    int maxIters;
+    unsigned long long* shrinks;
+};
+
+// energy of the incident tets with the vertex at x; DERIV: also dE/dx, s1 = sum A |m|^2, G = sum A g g^T
+template <bool DERIV>
+__device__ __forceinline__ float ls_elastic(const LsArgs& a, int s, int b, int e, float miu, float lmbd, float aConst, float3 x,
+                                            float3& dEdx, float& s1, float (&G)[6]) {
+    float E = 0.f;
+    for (int q = b; q < e; q++) {
+        const int2 en = __ldg(a.ent + q);
+        const int4 tv = __ldg(a.tetSid + en.x);
+        const float4 d0 = __ldg(a.tetDm + 3 * (size_t)en.x), d1 = __ldg(a.tetDm + 3 * (size_t)en.x + 1), d2 = __ldg(a.tetDm + 3 * (size_t)en.x + 2);
+        const float Dm[9] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x};
+        const float A = d2.y;
+        const int ids[4] = {tv.x, tv.y, tv.z, tv.w};
+        float3 p[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) p[k] = (ids[k] == s) ? x : f3(a.pos[ids[k]]);
+        float Ds[9];
+#pragma unroll
+        for (int c = 0; c < 3; c++) { const float3 d = p[c + 1] - p[0]; Ds[3 * c] = d.x; Ds[3 * c + 1] = d.y; Ds[3 * c + 2] = d.z; }
+        float F[9];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int r = 0; r < 3; r++) F[r + 3 * c] = Ds[r] * Dm[3 * c] + Ds[r + 3] * Dm[3 * c + 1] + Ds[r + 6] * Dm[3 * c + 2];
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; k++) sum += F[k] * F[k];
+        const float PhiD = 0.5f * (sum - 3.f);
+        const float detF = F[0] * (F[4] * F[8] - F[7] * F[5]) - F[3] * (F[1] * F[8] - F[7] * F[2]) + F[6] * (F[1] * F[5] - F[4] * F[2]);
+        const float k_ = detF - aConst;
+        E += A * (miu * PhiD + lmbd * (0.5f * (k_ * k_)));
+        if (DERIV) {
+            const float dd[9] = {F[4] * F[8] - F[7] * F[5], F[6] * F[5] - F[3] * F[8], F[3] * F[7] - F[6] * F[4],
+                                 F[7] * F[2] - F[1] * F[8], F[0] * F[8] - F[6] * F[2], F[6] * F[1] - F[0] * F[7],
+                                 F[1] * F[5] - F[4] * F[2], F[3] * F[2] - F[0] * F[5], F[0] * F[4] - F[3] * F[1]};
+            float m1, m2, m3;
+            switch (en.y) {
+                case 0: m1 = -Dm[0] - Dm[1] - Dm[2]; m2 = -Dm[3] - Dm[4] - Dm[5]; m3 = -Dm[6] - Dm[7] - Dm[8]; break;
+                case 1: m1 = Dm[0]; m2 = Dm[3]; m3 = Dm[6]; break;
+                case 2: m1 = Dm[1]; m2 = Dm[4]; m3 = Dm[7]; break;
+                default: m1 = Dm[2]; m2 = Dm[5]; m3 = Dm[8]; break;
+            }
+            const float lk = lmbd * k_;
+            float dEdF[9];
+#pragma unroll
+            for (int k = 0; k < 9; k++) dEdF[k] = A * (miu * F[k] + lk * dd[k]);
+            dEdx.x += dEdF[0] * m1 + dEdF[3] * m2 + dEdF[6] * m3;
+            dEdx.y += dEdF[1] * m1 + dEdF[4] * m2 + dEdF[7] * m3;
+            dEdx.z += dEdF[2] * m1 + dEdF[5] * m2 + dEdF[8] * m3;
+            // the vertex block of the tet Hessian: A (mu |m|^2 I + lmbd g g^T), g = cof(F) m (det F is affine in one vertex)
+            const float gx = dd[0] * m1 + dd[3] * m2 + dd[6] * m3, gy = dd[1] * m1 + dd[4] * m2 + dd[7] * m3, gz = dd[2] * m1 + dd[5] * m2 + dd[8] * m3;
+            s1 += A * (m1 * m1 + m2 * m2 + m3 * m3);
+            G[0] += A * gx * gx; G[1] += A * gx * gy; G[2] += A * gx * gz; G[3] += A * gy * gy; G[4] += A * gy * gz; G[5] += A * gz * gz;
+        }
+    }
+    return E;
+}
+
+template <bool HAS_CONTACTS>
+__global__ void __launch_bounds__(128)
+k_sweep_linesearch(const LsArgs a) {
+    const int s = a.vBegin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= a.vEnd) return;
+    const int4 h = __ldg(a.vtx2 + s);
+    if (h.w < 0) return;
+    const MeshParamsDev* P = a.mp + (h.w & 0x00FFFFFF);
+    if (!P->activeSolve) return;
+    const float3 x = f3(a.pos[s]);
+    const float4 ys = __ldg(a.inertia + s);
+    float4 xpv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.needPrev) xpv = __ldg(a.prev + s);
+    const int b = __ldg(a.off + s), e = __ldg(a.off + s + 1);
+    const float miu = P->miu, lmbd = P->lmbd, aConst = P->a;
+    float3 dEdx = make_float3(0.f, 0.f, 0.f);
+    float s1 = 0.f, G[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const float Eel0 = ls_elastic<true>(a, s, b, e, miu, lmbd, aConst, x, dEdx, s1, G);
+    float4 dir;
+    if (!vertex_tail<HAS_CONTACTS, true>(s, x, ys, f3(xpv), P, dEdx.x, dEdx.y, dEdx.z, s1, G[0], G[1], G[2], G[3], G[4], G[5], a.pos, a.sp, a.applyFriction,
+                                        a.cv, a.errFlags, dir)) return;
+    // merit energy = inertia (0.5 * m * |x - y|^2 / dt^2, the product formed in double as the reference's literal makes it) + elastic
+    auto inertiaE = [&](float3 q) {
+        const float dx = q.x - ys.x, dy = q.y - ys.y, dz = q.z - ys.z;
+        const float sq = dx * dx + dy * dy + dz * dz;
+        return (float)(0.5 * (double)ys.w * (double)sq * (double)a.sp.dtSqrReciprocal);
+    };
+    const float E0 = inertiaE(x) + Eel0;
+    float alpha = fabsf(dir.w);
+    const float shrink = dir.w < 0.f ? a.tauGD : a.tau;
+    float3 xt = x;
+    float3 dummy3 = make_float3(0.f, 0.f, 0.f); float dummy1 = 0.f, dummy6[6];
+    int rejected = 0;
+    for (int it = 0; it < a.maxIters; it++) {
+        xt = make_float3(alpha * dir.x + x.x, alpha * dir.y + x.y, alpha * dir.z + x.z);
+        const float en = inertiaE(xt) + ls_elastic<false>(a, s, b, e, miu, lmbd, aConst, xt, dummy3, dummy1, dummy6);
+        if (en < E0) break;          // first Wolfe condition with c = 0 (the call site passes 0)
+        alpha = alpha * shrink;
+        rejected++;
+    }
+    if (a.maxIters > 0) a.pos[s] = make_float4(xt.x, xt.y, xt.z, 0.f);      // the LAST trial position stays, accepted or not, as in the reference
+    if (rejected) atomicAdd(a.shrinks, (unsigned long long)rejected);
+}
+
+// Eigen's 3x3 inverse (cofactors * 1/det) in float, as TetMeshFEM computes DmInv (M/TetMesh/TetMeshFEM.cpp:390-413)
+static void ls_inv3(const float m[9] /*column-major*/, float r[9]) {
+    auto M = [&](int i, int j) { return m[i + 3 * j]; };
+    auto cof = [&](int i, int j) {
+        const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+        return M(i1, j1) * M(i2, j2) - M(i1, j2) * M(i2, j1);
+    };
+    const float c00 = cof(0, 0), c10 = cof(1, 0), c20 = cof(2, 0);
+    const float det = c00 * M(0, 0) + c10 * M(1, 0) + c20 * M(2, 0);
+    const float invdet = 1.f / det;
+    r[0 + 3 * 0] = c00 * invdet; r[0 + 3 * 1] = c10 * invdet; r[0 + 3 * 2] = c20 * invdet;
+    r[1 + 3 * 0] = cof(0, 1) * invdet; r[1 + 3 * 1] = cof(1, 1) * invdet; r[1 + 3 * 2] = cof(2, 1) * invdet;
+    r[2 + 3 * 0] = cof(0, 2) * invdet; r[2 + 3 * 1] = cof(1, 2) * invdet; r[2 + 3 * 2] = cof(2, 2) * invdet;
+}
+
+cudaError_t linesearch_upload(Scene& s) {
+    if (s.lsOff.p) return cudaSuccess;
+    const int64_t N = s.nVerts;
+    int64_t nT = 0;
+    for (auto& m : s.meshes) nT += m.nT;
+    std::vector<int32_t> off(N + 1, 0);
+    std::vector<int4> tetSid(std::max<int64_t>(nT, 1));
+    std::vector<float4> dm(3 * std::max<int64_t>(nT, 1));
+    for (auto& m : s.meshes)
+        for (int t = 0; t < m.nT; t++) {
+            const int32_t* tv = &m.tets[4 * (size_t)t];
+            tetSid[m.tetBase + t] = make_int4(m.sortedId[tv[0]], m.sortedId[tv[1]], m.sortedId[tv[2]], m.sortedId[tv[3]]);
+            float Dm[9], Di[9];
+            const float* x0 = &m.pos0[3 * (size_t)tv[0]];
+            for (int c = 0; c < 3; c++) for (int d = 0; d < 3; d++) Dm[d + 3 * c] = m.pos0[3 * (size_t)tv[c + 1] + d] - x0[d];
+            ls_inv3(Dm, Di);
+            float4* o = &dm[3 * (size_t)(m.tetBase + t)];
+            o[0] = make_float4(Di[0], Di[1], Di[2], Di[3]); o[1] = make_float4(Di[4], Di[5], Di[6], Di[7]);
+            o[2] = make_float4(Di[8], m.restVol[t], 0.f, 0.f);
+            for (int k = 0; k < 4; k++) off[m.sortedId[tv[k]] + 1]++;
+        }
+    for (int64_t v = 0; v < N; v++) off[v + 1] += off[v];
+    std::vector<int2> ent(std::max<int64_t>(off[N], 1));
+    {
+        std::vector<int32_t> at(off.begin(), off.end() - 1);
+        for (auto& m : s.meshes)                    // tets ascending inside a mesh: the reference's incident-tet order
+            for (int t = 0; t < m.nT; t++)
+                for (int k = 0; k < 4; k++) ent[at[m.sortedId[m.tets[4 * (size_t)t + k]]]++] = make_int2((int)(m.tetBase + t), k);
+    }
+    CK(s.lsOff.alloc(off.size())); CK(s.lsEnt.alloc(ent.size())); CK(s.lsTetSid.alloc(tetSid.size())); CK(s.lsTetDm.alloc(dm.size())); CK(s.lsShrinks.alloc(1));
+    CK(cudaMemcpy(s.lsOff.p, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s.lsEnt.p, ent.data(), ent.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s.lsTetSid.p, tetSid.data(), tetSid.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s.lsTetDm.p, dm.data(), dm.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    CK(cudaMemset(s.lsShrinks.p, 0, sizeof(unsigned long long)));
+    return cudaSuccess;
+}
+
+cudaError_t sweep_launch_linesearch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv) {
+    const int vb = s.groupStart[group], ve = s.groupStart[group + 1];
+    if (ve <= vb) return cudaSuccess;
+    SweepArgs c;
+    std::memset(&c, 0, sizeof(c));
+    fill_common(s, c);
+    LsArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.vBegin = vb; a.vEnd = ve; a.pos = s.pos.p; a.prev = s.prev.p; a.inertia = s.inertia.p; a.vtx2 = s.vtx2.p;
+    a.off = s.lsOff.p; a.ent = s.lsEnt.p; a.tetSid = s.lsTetSid.p; a.tetDm = s.lsTetDm.p; a.mp = s.meshParams.p; a.sp = s.stepParams;
+    a.applyFriction = applyFriction; a.needPrev = c.needPrev; a.cv = cv; a.errFlags = s.errFlags.p;
+    a.tau = s.lineSearch.tau; a.tauGD = s.lineSearch.tauGD; a.maxIters = s.lineSearch.maxIters; a.shrinks = s.lsShrinks.p;
+    const int B = 128, G = (ve - vb + B - 1) / B;
+    if (hasContacts) k_sweep_linesearch<true><<<G, B, 0, s.stream>>>(a);
+    else k_sweep_linesearch<false><<<G, B, 0, s.stream>>>(a);
+    return cudaGetLastError();
 }
 
 }  // namespace gb

@@ -146,6 +146,8 @@ def build_scene(cls, wl, **kw):
         s.finalize()
         return s
     s = cls(wl["phys"], wl["col"], **kw)
+    if cls is capi.Scene and wl.get("refit_margin") is not None:
+        s.set_lazy_refit_margin(wl["refit_margin"])
     if cls is capi.Scene and len(wl["meshes"]) > 1:      # many-object scenes: the rule the sharded builder applies too
         from gaia_b200.multigpu import scene_solver_lanes
         s.set_solver_lanes(scene_solver_lanes([m[3] for m in wl["meshes"]]))

@@ -357,6 +357,23 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes);
  * 2 = multi-colour launches everywhere (no graph replay). Colours with active contacts always use one launch per colour
  * (their contact pre-pass is a separate launch). */
 int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled);
+/* Backtracking line search on the vertex merit energy after the 3x3 solve: the reference's APPLY_LOCAL_LINE_SEARCH
+ * (M/VBD/VBDPhysics.cpp:25 - compiled out there -, call site :2467-2474; backTracingLineSearchVBD, M/VBD/VBD_NeoHookean.h:115-153;
+ * evaluateVertexMeritEnergy, M/VBD/VBD_NeoHookean.cpp:90-124). Merit energy = inertia + Neo-Hookean energy of the incident
+ * tets (no boundary / contact / damping terms, as in the reference); first trial alpha = stepSize, c = 0, alpha *= tau after
+ * a rejected trial (tauGD when the 3x3 solve failed and the direction is the force), at most maxIters trials, the vertex stays
+ * at the LAST trial. tau / tauGD / maxIters = PhysicsParams tau (0.5), tau_GD (0.1), backtracingLineSearchMaxIters (16).
+ * A feature switch (csrc/sweep.cu: k_sweep_linesearch, one thread per vertex over plain per-tet tables uploaded on first use,
+ * ~100 B per tet), not a fast path; with it the colour loop uses neither the multi-colour launch nor the fused halo exchange.
+ * After finalize. line_search_shrinks: rejected trials so far (diagnostic). */
+int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float tauGD, int32_t maxIters);
+int64_t gaia_b200_line_search_shrinks(gaia_handle* h);
+/* Lazy refit of the DCD trees (csrc/collision.cu): boxes are inflated by a margin and refitted only when some vertex has moved
+ * further than that from where the boxes were computed. `edges` = the margin in typical tet edges (cube root of 6 x the mean
+ * rest volume), default 0.2, 0 = refit at every detection. A tuning knob without a reference counterpart (Embree refits at
+ * every detection, M/CollisionDetector/DiscreteCollisionDetector.cpp): contact sets do not depend on it, queries test the
+ * primitives themselves. Before finalize. */
+int gaia_b200_set_lazy_refit_margin(gaia_handle* h, float edges);
 /* Bytes of the solver's HBM layout, for the bench's "inputs vs L2" note and for capacity planning:
  * out[0] per-tet record stream, out[1] per-neighbour entry stream, out[2] per-vertex state read or written by one iteration
  * (headers, positions, inertia, previous positions), out[3] tile table; out[4] = shared-memory position reads per

@@ -83,6 +83,12 @@ int oracle_set_ghosts(void* h, int mesh, const int32_t* verts, int32_t n) {
     for (int i = 0; i < n; i++) if (!m.fixedMask[verts[i]]) { m.fixedMask[verts[i]] = 1; m.fixedPoints.push_back(verts[i]); }
     return GAIA_OK;
 }
+int oracle_set_line_search(void* h, int32_t enabled, float tau, float tauGD, int32_t maxIters) {
+    Scene* s = (Scene*)h;
+    s->lineSearch.enabled = enabled != 0; s->lineSearch.tau = tau; s->lineSearch.tauGD = tauGD; s->lineSearch.maxIters = maxIters;
+    return GAIA_OK;
+}
+int64_t oracle_line_search_shrinks(void* h) { return ((Scene*)h)->lineSearchShrinks; }
 int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_solve_group(void* h, int g, int applyFriction) { phase_solve_group(*(Scene*)h, g, applyFriction != 0); return GAIA_OK; }

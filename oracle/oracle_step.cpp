@@ -206,6 +206,56 @@ static void collision_force_hessian(Scene& s, Mesh& m, int iV, V3& force, M3& he
     }
 }
 
+// evaluateVertexMeritEnergy (M/VBD/VBD_NeoHookean.cpp:90-124): inertia + Neo-Hookean energy of the incident tets, with the
+// vertex at `x` (the reference writes the trial position into the mesh and evaluates; here it is passed in)
+static float vertex_merit_energy(const Scene& s, const Mesh& m, int iV, const V3& x) {
+    // 0.5 * vertexMass * squaredNorm * dtSqrReciprocal: the literal is a double, so the product is formed in double
+    const V3 d = x - m.inertia[iV];
+    const float meInertia = (float)(0.5 * (double)m.mass[iV] * (double)sqnorm(d) * (double)s.dtSqrReciprocal);
+    float meElastic = 0.f;
+    const int start = m.vNbrInfos[2 * iV], num = m.vNbrInfos[2 * iV + 1];
+    const float miu = m.obj.miu, lmbd = m.obj.lmbd;
+    const float a = 1 + miu / lmbd;
+    for (int iNei = 0; iNei < num; iNei++) {
+        const int tetId = m.vNbrTets[start + iNei];
+        const float A = m.restVol[tetId];
+        const float* Dm = &m.DmInv[9 * (size_t)tetId];
+        const int* tv = &m.tets[4 * (size_t)tetId];
+        V3 p[4];
+        for (int k = 0; k < 4; k++) p[k] = tv[k] == iV ? x : m.pos[tv[k]];
+        float Ds[9];
+        for (int c = 0; c < 3; c++) { V3 e = p[c + 1] - p[0]; Ds[3 * c] = e.x; Ds[3 * c + 1] = e.y; Ds[3 * c + 2] = e.z; }
+        float F[9];
+        for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++)
+            F[r + 3 * c] = Ds[r] * Dm[3 * c] + Ds[r + 3] * Dm[3 * c + 1] + Ds[r + 6] * Dm[3 * c + 2];
+        float sum = 0.f;
+        for (int q = 0; q < 9; q++) sum += F[q] * F[q];
+        const float PhiD = 0.5f * (sum - 3.f);
+        const float detF = F[0] * (F[4] * F[8] - F[7] * F[5]) - F[3] * (F[1] * F[8] - F[7] * F[2]) + F[6] * (F[1] * F[5] - F[4] * F[2]);
+        const float PhiH = 0.5f * ((detF - a) * (detF - a));
+        meElastic += A * (miu * PhiD + lmbd * PhiH);
+    }
+    return meInertia + meElastic;
+}
+
+// backTracingLineSearchVBD (M/VBD/VBD_NeoHookean.h:115-153) as called from VBDStepWithCollision (M/VBD/VBDPhysics.cpp:2467-2474):
+// c = 0, first trial alpha = stepSize; the vertex is left at the LAST trial position (accepted or not), as in the reference
+static int line_search(Scene& s, Mesh& m, int iV, const V3& dx, float alpha, float tau) {
+    const V3 org = m.pos[iV];
+    const float E0 = vertex_merit_energy(s, m, iV, org);
+    const float c = 0.f, mm = sqnorm(dx);
+    int shrinks = 0;
+    for (int it = 0; it < s.lineSearch.maxIters; it++) {
+        const V3 x = alpha * dx + org;
+        m.pos[iV] = x;
+        const float e = vertex_merit_energy(s, m, iV, x);
+        if (e < E0 - alpha * c * mm) break;
+        alpha = alpha * tau;
+        shrinks++;
+    }
+    return shrinks;
+}
+
 static void vbd_step_with_collision(Scene& s, Mesh& m, int iV, bool apply_friction) {
     M3 h; V3 force;
     neohookean_force_hessian(s, m, iV, force, h);
@@ -227,7 +277,11 @@ static void vbd_step_with_collision(Scene& s, Mesh& m, int iV, bool apply_fricti
         bool ok = solve3x3_psd_stable(h.m, f, dir);
         if (!ok) { stepSize = s.phys.stepSizeGD; dir[0] = f[0]; dir[1] = f[1]; dir[2] = f[2]; }
         if (std::isnan(dir[0]) || std::isnan(dir[1]) || std::isnan(dir[2])) { s.err = "descentDirection has NaN"; return; }
-        m.pos[iV] += stepSize * V3(dir[0], dir[1], dir[2]);
+        if (s.lineSearch.enabled) {
+            const int k = line_search(s, m, iV, V3(dir[0], dir[1], dir[2]), stepSize, ok ? s.lineSearch.tau : s.lineSearch.tauGD);
+            if (k) __atomic_fetch_add(&s.lineSearchShrinks, (int64_t)k, __ATOMIC_RELAXED);
+        } else
+            m.pos[iV] += stepSize * V3(dir[0], dir[1], dir[2]);
     }
 }
 

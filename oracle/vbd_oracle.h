@@ -82,6 +82,9 @@ struct Scene {
     std::vector<std::vector<int>> activeCollisionsEachGroup;
     bool finalized = false;
     bool keepColourOrder = false;   // partition of a multi-GPU scene: colours stay in the given (global) order
+    // APPLY_LOCAL_LINE_SEARCH (M/VBD/VBDPhysics.cpp:25, compiled out in the reference): backtracking on the vertex merit energy
+    struct { bool enabled = false; float tau = 0.5f, tauGD = 0.1f; int maxIters = 16; } lineSearch;   // VBDPhysicsParameters.h:24-29
+    int64_t lineSearchShrinks = 0;  // trial steps rejected so far (diagnostic)
     int frameId = 0, substep = 0, iIter = 0;
     float curTime = 0.f;
     std::vector<Deformer> deformers;
