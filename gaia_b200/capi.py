@@ -520,7 +520,7 @@ class Scene(SceneBase):
         return dict(zip(("records", "neighbours", "vertex_state", "tiles", "pos_reads", "incidences"), [int(x) for x in a]))
 
     def set_lazy_refit_margin(self, edges):
-        """margin of the DCD trees' boxes in typical tet edges (default 0.2; 0 = refit at every detection); before finalize"""
+        """margin of the DCD trees' boxes in typical tet edges (0 = refit at every detection; negative = the adaptive default); before finalize"""
         self._call("set_lazy_refit_margin", float(edges))
 
     def set_multi_colour_launch(self, enabled):

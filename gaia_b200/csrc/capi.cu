@@ -572,7 +572,7 @@ int64_t gaia_b200_line_search_shrinks(gaia_handle* h) {
 int gaia_b200_set_lazy_refit_margin(gaia_handle* h, float edges) {
     REQUIRE(h);
     if (h->s.finalized) return fail(h->s, GAIA_ERR_STATE, "set_lazy_refit_margin after finalize");
-    if (!(edges >= 0.f && edges <= 4.f)) return fail(h->s, GAIA_ERR_INVALID_ARG, "lazy refit margin: 0 .. 4 typical tet edges");
+    if (!(edges <= 4.f)) return fail(h->s, GAIA_ERR_INVALID_ARG, "lazy refit margin: 0 .. 4 typical tet edges, or negative for the adaptive default");
     h->s.lazyRefitMargin = edges;
     return GAIA_OK;
 }

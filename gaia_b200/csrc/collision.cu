@@ -280,7 +280,13 @@ struct CollisionState {
     DevBuf<float4> refPos;        // lazy refit of the DCD trees: positions their boxes were computed at
     DevBuf<int32_t> needRefit;    // device flag: some vertex left its margin (or a rebuild forces the refit)
     DevBuf<int32_t> candCount, cand;   // per surface vertex: tets it can enter before the next refit (k_dcd_phase1), -1 = too many
-    float lazyMargin = 0.f;
+    float lazyMargin = 0.f;       // margin the NEXT refit will use
+    // adaptive margin (Scene::lazyRefitMargin < 0): grown while refits come more often than every 6 detections, up to just under
+    // half an edge (beyond it the one-ring of candidate tets doubles and the candidate cache overflows), taken back for good when
+    // it does not help (bodies that move further than any margin between two detections) or when the cache overflows
+    float marginBuilt = 0.f, marginBase = 0.f, marginCap = 0.f;   // margin of the CURRENT boxes; start value; upper bound
+    int detSinceRefit = 0, shortAtCap = 0;
+    bool adaptive = false, adaptFrozen = false;
     DevBuf<int32_t> boundsOrd;    // 6 * (nMeshes + 1)
     DevBuf<float> normBox;        // 6 * (nMeshes + 1)
     // dense results per surface-vertex slot
@@ -362,14 +368,18 @@ cudaError_t collision_init(Scene& s) {
     CK(up(c->groupStart, s.groupStart));
     if (s.col.allowDCD) {
         CK(c->tetBvh.alloc((int)nT, oneSegT)); CK(c->surfBvh.alloc((int)nF, faceSegs));
-        CK(c->refPos.alloc(N + 1)); CK(c->needRefit.alloc(1));
+        CK(c->refPos.alloc(N + 1)); CK(c->needRefit.alloc(2));      // [0] refit needed, [1] vertices whose candidate list overflowed
         CK(c->candCount.alloc(std::max<int64_t>(nS, 1))); CK(c->cand.alloc((size_t)std::max<int64_t>(nS, 1) * kCand));
         CK(cudaMemset(c->candCount.p, 0xff, std::max<int64_t>(nS, 1) * sizeof(int32_t)));
         // margin = a fifth of the typical tet edge (cube root of 6 x the mean rest volume): refits become rare for slowly
         // deforming bodies; the larger boxes cost little because between refits queries run from the candidate cache
         double vol = 0.0; int64_t cnt = 0;
         for (auto& m : s.meshes) for (float v : m.restVol) { vol += std::fabs((double)v); cnt++; }
-        c->lazyMargin = cnt ? s.lazyRefitMargin * (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
+        const float edge = cnt ? (float)std::cbrt(6.0 * vol / (double)cnt) : 0.f;
+        c->adaptive = s.lazyRefitMargin < 0.f;
+        c->marginBase = (c->adaptive ? 0.2f : s.lazyRefitMargin) * edge;
+        c->marginCap = 0.48f * edge;
+        c->lazyMargin = c->marginBuilt = c->marginBase;
     }
     if (s.col.allowCCD) CK(c->ccdBvh.alloc((int)nF, oneSegF));
     const size_t nM = s.meshes.size();
@@ -478,7 +488,7 @@ k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const in
              const MeshParamsDev* __restrict__ mp, const float4* __restrict__ pos, const int4* __restrict__ tetSid,
              const int32_t* __restrict__ tetMesh, uint8_t* penetrated, int32_t* cNum, int32_t* cHitTet, int32_t* cFace, int32_t* cFlags,
              int32_t* hitList, int32_t* nHits, int32_t* errFlags, const int32_t* __restrict__ need, float margin, int32_t* candCount,
-             int32_t* cand) {
+             int32_t* cand, int32_t* overflowed) {
     __shared__ int32_t frontierAll[(kB / 32) * kFrontier];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* frontier = frontierAll + warp * kFrontier;
@@ -552,7 +562,7 @@ k_dcd_phase1(int nSlots, int intermediate, ColParamsDev cp, BvhView bv, const in
             qn += nPush;
             __syncwarp();
         }
-        if (collect && lane == 0) candCount[slot] = nCand <= kCand ? nCand : -1;
+        if (collect && lane == 0) { candCount[slot] = nCand <= kCand ? nCand : -1; if (nCand > kCand) atomicAdd(overflowed, 1); }
     }
     if (!queried) return;
     for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
@@ -899,7 +909,7 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
     const int nS = (int)s.nSurfVerts;
     c->prepared = false;
     if (s.col.allowDCD) {
-        bool rebuildTet = false, rebuildSurf = false;
+        bool rebuildTet = false, rebuildSurf = false, forced = false;
         if (!intermediate) {
             rebuildTet = (s.substep == 0) && !(s.frameId % s.phys.dcdTetMeshSceneBVHRebuildSteps) && s.frameId;
             rebuildSurf = (s.substep == 0) && !(s.frameId % s.phys.dcdSurfaceSceneBVHRebuildSteps) && s.frameId;
@@ -908,11 +918,11 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
             const int N = (int)s.nVerts;
             const bool force = rebuildTet || rebuildSurf || !c->tetBvh.built || !c->surfBvh.built ||
                                activity_differs(s, c->tetBvh.activeAtBuild) || activity_differs(s, c->surfBvh.activeAtBuild);
+            forced = force;
+            CK(cudaMemsetAsync(c->needRefit.p, 0, 2 * sizeof(int32_t), s.stream));
             if (force) CK(cudaMemsetAsync(c->needRefit.p, 0x01, sizeof(int32_t), s.stream));
-            else {
-                CK(cudaMemsetAsync(c->needRefit.p, 0, sizeof(int32_t), s.stream));
-                k_disp_check<<<nblk(N), kB, 0, s.stream>>>(N, s.pos.p, c->refPos.p, c->lazyMargin * c->lazyMargin, c->needRefit.p);
-            }
+            else      // (the boxes in use were inflated by marginBuilt; a refit in this detection inflates by lazyMargin)
+                k_disp_check<<<nblk(N), kB, 0, s.stream>>>(N, s.pos.p, c->refPos.p, c->marginBuilt * c->marginBuilt, c->needRefit.p);
             CK(update_bvh<0>(s, c->tetBvh, rebuildTet, false, c->lazyMargin, c->needRefit.p));
             CK(update_bvh<1>(s, c->surfBvh, rebuildSurf, true, c->lazyMargin, c->needRefit.p));
             k_copy_ref<<<capped(N), kB, 0, s.stream>>>(N, s.pos.p, c->refPos.p, c->needRefit.p);
@@ -923,11 +933,24 @@ cudaError_t collision_dcd(Scene& s, bool intermediate) {
         TopoView tp{c->tetSid.p, c->tetNbr.p, c->faceSid.p, c->faceInfo.p, c->faceNbr.p, c->surfNbrOff.p, c->surfNbr.p, c->slotOfSorted.p};
         k_dcd_phase1<<<nblk((int64_t)nS * 32), kB, 0, s.stream>>>(nS, intermediate ? 1 : 0, c->cp, view_of(c->tetBvh), c->surfSid.p, c->surfMesh.p, s.meshParams.p,
                                                   s.pos.p, c->tetSid.p, c->tetMesh.p, c->penetrated.p, c->cNum.p, c->cHitTet.p, c->cFace.p,
-                                                  c->cFlags.p, c->hitList.p, nHits, s.errFlags.p, c->needRefit.p, c->lazyMargin, c->candCount.p, c->cand.p);
+                                                  c->cFlags.p, c->hitList.p, nHits, s.errFlags.p, c->needRefit.p, c->lazyMargin, c->candCount.p, c->cand.p, c->needRefit.p + 1);
         // phase 2 runs over the compacted hit list; its length stays on the device (grid sized for the worst case, early exit)
-        int32_t hits = 0;
+        int32_t hits = 0, refit[2] = {0, 0};
         CK(cudaMemcpyAsync(&hits, nHits, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaMemcpyAsync(refit, c->needRefit.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CK(cudaStreamSynchronize(s.stream));
+        if (refit[0]) {      // the trees were refitted with lazyMargin in this detection
+            const int interval = c->detSinceRefit;
+            c->detSinceRefit = 0;
+            c->marginBuilt = c->lazyMargin;
+            if (c->adaptive && !c->adaptFrozen && !forced) {
+                if (refit[1] > nS / 50) { c->lazyMargin = std::max(c->marginBase, c->marginBuilt / 1.3f); c->marginCap = c->lazyMargin; }
+                else if (c->marginBuilt < 0.999f * c->marginCap) { if (interval < 6) c->lazyMargin = std::min(c->marginCap, c->marginBuilt * 1.3f); }
+                else if (interval < 3) { if (++c->shortAtCap >= 4) { c->lazyMargin = c->marginBase; c->adaptFrozen = true; } }
+                else c->shortAtCap = 0;
+            }
+        }
+        c->detSinceRefit++;
         if (hits > 0)
             k_dcd_phase2<<<nblk((int64_t)hits * 32), kB, 0, s.stream>>>(nHits, c->hitList.p, c->cp, view_of(c->surfBvh), c->surfBvh.segRange.p, tp,
                                                                       c->surfSid.p, c->surfMesh.p, c->tetMesh.p, s.pos.p, c->cHitTet.p, c->cFace.p,

@@ -156,7 +156,7 @@ struct Scene {
     // gaia_b200_set_line_search (sweep.cu: k_sweep_linesearch): plain per-tet tables, uploaded when the option is first switched on
     struct { bool enabled = false; float tau = 0.5f, tauGD = 0.1f; int maxIters = 16; } lineSearch;
     DevBuf<int32_t> lsOff; DevBuf<int2> lsEnt; DevBuf<int4> lsTetSid; DevBuf<float4> lsTetDm; DevBuf<unsigned long long> lsShrinks;
-    float lazyRefitMargin = 0.2f;  // gaia_b200_set_lazy_refit_margin: margin of the DCD trees' boxes, in typical tet edges
+    float lazyRefitMargin = -1.f;  // gaia_b200_set_lazy_refit_margin: margin of the DCD trees' boxes in typical tet edges; < 0: adaptive, from 0.2
     int profiling = 0;             // 0 off; 1 per-phase timers + an event pair around every colour-solve launch; 2 per-phase timers only (the colour loop stays a CUDA graph)
     cudaEvent_t evA = nullptr, evB = nullptr, evP0 = nullptr, evP1 = nullptr;
     std::vector<cudaEvent_t> profEv;   // event pairs around the colour-solve launches of one iteration loop (profiling only)

@@ -370,7 +370,10 @@ int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float 
 int64_t gaia_b200_line_search_shrinks(gaia_handle* h);
 /* Lazy refit of the DCD trees (csrc/collision.cu): boxes are inflated by a margin and refitted only when some vertex has moved
  * further than that from where the boxes were computed. `edges` = the margin in typical tet edges (cube root of 6 x the mean
- * rest volume), default 0.2, 0 = refit at every detection. A tuning knob without a reference counterpart (Embree refits at
+ * rest volume); 0 = refit at every detection; negative (the default) = adaptive: starts at 0.2, grows by 1.3x per refit while
+ * refits come more often than every 6 detections, stays below 0.48 (at half an edge the candidate neighbourhood of a vertex
+ * doubles), and goes back to 0.2 for good when growing did not space the refits out (fast-moving bodies) or when more than
+ * 2 % of the candidate lists overflow. A tuning knob without a reference counterpart (Embree refits at
  * every detection, M/CollisionDetector/DiscreteCollisionDetector.cpp): contact sets do not depend on it, queries test the
  * primitives themselves. Before finalize. */
 int gaia_b200_set_lazy_refit_margin(gaia_handle* h, float edges);
