@@ -368,7 +368,8 @@ def main():
             roof["kernel_share_of_step"] = loop_ms / (ms / args.steps)
             roof["timing"] = "colour loop timed as replayed in the step (CUDA events around the loop) / launches"
         else:
-            roof["timing"] = "CUDA event pair around every sweep launch"
+            roof["timing"] = ("CUDA event pair around every sweep launch; a multi-colour launch (one per contact-free stretch of the loop) counts as "
+                              "the colour steps it covers, so avg_launch_us, algorithmic bytes and traffic are all per COLOUR STEP")
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath) and world == 1:
             try:
