@@ -112,6 +112,8 @@ void VBDPhysicsB200::loadRunningparameters(std::string inModelInputFile, std::st
         p->get("outputRecoveryState", run_.outputRecoveryState); p->get("outputRecoveryStateStep", run_.outputRecoveryStateStep);
         p->get("outputRecoveryStateBinary", run_.outputRecoveryStateBinary); p->get("outputStatistics", run_.outputStatistics);
         p->get("debugVerboseLvl", run_.debugVerboseLvl);
+        p->get("applyLocalLineSearch", run_.applyLocalLineSearch); p->get("tau", run_.tau); p->get("tau_GD", run_.tauGD);
+        p->get("backtracingLineSearchMaxIters", run_.backtracingLineSearchMaxIters);
         int solType = 1; bool useNewton = false, useGD = false;
         p->get("collisionSolutionType", solType); p->get("useNewton", useNewton); p->get("useGDSolver", useGD);
         if (useNewton || useGD) throw std::runtime_error("useNewton / useGDSolver select comparison solvers outside the VBD hot path");
@@ -216,6 +218,8 @@ void VBDPhysicsB200::initialize() {
             else check(gaia_b200_add_translator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.speed, d.endTime), "gaia_b200_add_translator");
         }
     check(gaia_b200_finalize(h_), "gaia_b200_finalize");
+    if (run_.applyLocalLineSearch)
+        check(gaia_b200_set_line_search(h_, 1, run_.tau, run_.tauGD, run_.backtracingLineSearchMaxIters), "gaia_b200_set_line_search");
     // single-GPU driver: 8 lanes per vertex when every parallel group is small (see gaia_b200_set_solver_lanes)
     if (models_.size() > 1) {
         int32_t largest = 0;
@@ -461,10 +465,12 @@ void VBDPhysicsB200::recoverFromState(const std::string& stateFileIn) {
         for (int m = 0; m < nMeshes && m < nM; m++) {
             int32_t nV, nT, nSV, nSF;
             gaia_b200_mesh_sizes(h_, m, &nV, &nT, &nSV, &nSF);
-            if (nVerts[m] != nV) throw std::runtime_error("recovery state vertex count mismatch");
+            if ((int)nVerts.size() <= m || nVerts[m] != nV) throw std::runtime_error("recovery state vertex count mismatch");
             std::vector<float> p(3 * (size_t)nV), v(3 * (size_t)nV);
             velFile.read(reinterpret_cast<char*>(v.data()), (std::streamsize)(v.size() * 4));
             posFile.read(reinterpret_cast<char*>(p.data()), (std::streamsize)(p.size() * 4));
+            if (velFile.gcount() != (std::streamsize)(v.size() * 4) || posFile.gcount() != (std::streamsize)(p.size() * 4))
+                throw std::runtime_error("recovery state: the .pos / .vel file of " + stateFile + " is shorter than its meshes");
             check(gaia_b200_set_state(h_, m, p.data(), v.data()), "gaia_b200_set_state");
         }
     } else {
@@ -476,6 +482,11 @@ void VBDPhysicsB200::recoverFromState(const std::string& stateFileIn) {
                 return out;
             };
             std::vector<float> p = flat("position"), v = flat("velocities");
+            int32_t nV, nT, nSV, nSF;
+            gaia_b200_mesh_sizes(h_, (int)m, &nV, &nT, &nSV, &nSF);
+            if (p.size() != 3 * (size_t)nV || v.size() != 3 * (size_t)nV)      // set_state reads 3 * nV floats from each
+                throw std::runtime_error("recovery state vertex count mismatch (mesh " + std::to_string(m) + ": " + std::to_string(p.size() / 3) +
+                                         " positions, " + std::to_string(v.size() / 3) + " velocities, " + std::to_string(nV) + " vertices)");
             check(gaia_b200_set_state(h_, (int)m, p.data(), v.data()), "gaia_b200_set_state");
         }
     }

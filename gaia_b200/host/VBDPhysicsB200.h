@@ -49,6 +49,11 @@ struct HostMeshData {
 struct HostRunParams {
     int numFrames = 5000;
     bool saveOutputs = true;
+    // PhysicsParams "applyLocalLineSearch" (an addition of this host: the reference selects it at compile time with
+    // APPLY_LOCAL_LINE_SEARCH, M/VBD/VBDPhysics.cpp:25) + the reference's own tau / tau_GD / backtracingLineSearchMaxIters
+    bool applyLocalLineSearch = false;
+    float tau = 0.5f, tauGD = 0.1f;
+    int backtracingLineSearchMaxIters = 16;
     bool saveAllModelsTogether = true;
     std::string outputExt = "ply";
     int binaryModeVisualizationSteps = 100;

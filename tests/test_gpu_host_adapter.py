@@ -93,6 +93,41 @@ def test_ply_output_and_text_recovery_state(tmp_path):
     scene.close()
 
 
+def test_line_search_key_and_short_recovery_state(tmp_path):
+    """PhysicsParams.applyLocalLineSearch (+ tau, tau_GD, backtracingLineSearchMaxIters) switches the host's scene to the
+    line-search sweep: frames identical to the Python binding with set_line_search, different from the plain run. And a
+    text recovery state whose arrays are shorter than the mesh is refused instead of being read past its end."""
+    m, p = write_scene(str(tmp_path), n_frames=3, ext="bin")
+    par = json.load(open(p))
+    par["PhysicsParams"].update({"applyLocalLineSearch": True, "tau": 0.5, "tau_GD": 0.1, "backtracingLineSearchMaxIters": 8, "stepSize": 2.5})
+    json.dump(par, open(p, "w"))
+    out = tmp_path / "out"
+    r = subprocess.run([HOST_BIN, m, p, str(out), "-R", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    phys, col, meshes = meshio.load_scene_json(m, p, str(tmp_path))
+    assert abs(phys.stepSize - 2.5) < 1e-7
+    runs = {}
+    for ls in (True, False):
+        s = capi.Scene(phys, col)
+        meshio.add_scene_meshes(s, meshes)
+        s.set_solver_lanes(8)
+        if ls:
+            s.set_line_search(True, 0.5, 0.1, 8)
+        s.run_frames(3)
+        runs[ls] = np.concatenate([s.surface_positions(i) for i in range(len(meshes))])
+        if ls:
+            assert s.line_search_shrinks() > 0
+        s.close()
+    a = np.fromfile(out / "A00000003.bin", np.float32).reshape(-1, 3)
+    assert np.array_equal(a, runs[True]) and not np.array_equal(a, runs[False])
+    # short text recovery state
+    st = {"frameId": 1, "curTime": 0.0166666, "format": "text",
+          "meshesState": [{"position": [[0, 0, 0]] * 5, "velocities": [[0, 0, 0]] * 5}, {"position": [], "velocities": []}]}
+    json.dump(st, open(tmp_path / "short.json", "w"))
+    r = subprocess.run([HOST_BIN, m, p, str(tmp_path / "out2"), "-R", str(tmp_path), "-r", str(tmp_path / "short.json")], capture_output=True, text=True)
+    assert r.returncode == 3 and "vertex count mismatch" in r.stderr
+
+
 @pytest.mark.gpu
 def test_surface_snapshots_are_ordered_behind_the_step_and_match_the_per_mesh_getter():
     """row f4: gaia_b200_surface_snapshot_begin / _wait - the device-side surface gather into the page-locked two-slot ring.
