@@ -201,6 +201,8 @@ def main():
     ap.add_argument("--layout", default="ring", choices=["ring", "replicated"],
                     help="N > 1, one mesh: 'ring' = slabs with a one-ring ghost layer (contacts seen inside a slab and its ring), "
                          "'replicated' = solve partitioned, whole mesh on every rank as collision geometry (contacts between any two ranks)")
+    ap.add_argument("--multi-colour-launch", type=int, default=None, choices=[0, 1, 2],
+                    help="gaia_b200_set_multi_colour_launch mode (library default 1)")
     ap.add_argument("--refit-margin", type=float, default=None, help="lazy-refit margin of the DCD trees in typical tet edges (library default 0.2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=1, help="extra untimed steps with per-kernel CUDA events for the roofline")
@@ -241,6 +243,9 @@ def main():
             scene = (multigpu.build_replicated_scene if args.layout == "replicated" else multigpu.build_partitioned_scene)(wl, rank, world, local_rank)
     else:
         scene = build_scene(cloth.ClothScene if is_cloth(wl) else capi.Scene, wl, device=local_rank)
+    if args.multi_colour_launch is not None and not is_cloth(wl):
+        scene.set_multi_colour_launch(args.multi_colour_launch)
+        wl["name"] += f", multi-colour launch mode {args.multi_colour_launch}"
     log(f"[bench] rank {rank}: scene '{wl['name']}' built in {time.time() - t0:.1f}s")
     stream = torch.cuda.ExternalStream(scene.cuda_stream, device=torch.device("cuda", local_rank))
 
