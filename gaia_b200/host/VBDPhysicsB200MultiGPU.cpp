@@ -42,6 +42,13 @@ void VBDPhysicsB200MultiGPU::initialize() {
     std::vector<int32_t> owner(nV);
     check(gaia_b200_partition_slab_owner(nV, hm.verts.data(), nGpus_, -1, owner.data()), "gaia_b200_partition_slab_owner");
     parts_.assign(nGpus_, Part());
+    if (replicated_) {
+        if (nGpus_ > 8) throw std::runtime_error("--layout replicated: at most 8 GPUs (every GPU is every other GPU's peer)");
+        initializeReplicated(owner, cOffs, cFlat, (int)colours.size());
+        global_.assign(3 * (size_t)nV, 0.f);
+        frameId_ = 0;
+        return;
+    }
     forAllParts([&](int r) {
         Part& pt = parts_[r];
         pt.device = r;
@@ -115,6 +122,53 @@ void VBDPhysicsB200MultiGPU::initialize() {
     for (auto& pt : parts_) if (gaia_b200_halo_finalize(pt.h) < 0) throw std::runtime_error(gaia_b200_last_error(pt.h));
     global_.assign(3 * (size_t)nV, 0.f);
     frameId_ = 0;
+}
+
+// Replicated layout: full mesh on every GPU (global ids = local ids, global colour order), foreign vertices as ghosts, peers =
+// all other GPUs, send list = my owned vertices, remote slot = the peer's slot of the same vertex.
+void VBDPhysicsB200MultiGPU::initializeReplicated(const std::vector<int32_t>& owner, const std::vector<int32_t>& cOffs, const std::vector<int32_t>& cFlat,
+                                                  int nColours) {
+    const ModelInput& m = models_[0];
+    const HostMeshData& hm = meshCache_[m.meshCacheId];
+    const int32_t nV = (int32_t)(hm.verts.size() / 3);
+    const int64_t nT = (int64_t)(hm.tets.size() / 4);
+    forAllParts([&](int r) {
+        Part& pt = parts_[r];
+        pt.device = r;
+        pt.localVerts.resize(nV); pt.owned.resize(nV);
+        std::vector<int32_t> ghosts;
+        for (int32_t v = 0; v < nV; v++) { pt.localVerts[v] = v; pt.owned[v] = owner[v] == r; if (owner[v] != r) ghosts.push_back(v); }
+        auto ck = [&](int rc, const char* what) { if (rc < 0) throw std::runtime_error(std::string(what) + ": " + gaia_b200_last_error(pt.h)); };
+        ck(gaia_b200_create(&phys_, &col_, pt.device, &pt.h), "gaia_b200_create");
+        ck(gaia_b200_set_partition_mode(pt.h, r, nGpus_), "gaia_b200_set_partition_mode");
+        ck(gaia_b200_add_tet_mesh(pt.h, nV, (int32_t)nT, hm.verts.data(), hm.tets.data(), &m.obj, nColours, cOffs.data(), cFlat.data(),
+                                  (int32_t)m.fixedPoints.size(), m.fixedPoints.empty() ? nullptr : m.fixedPoints.data()), "gaia_b200_add_tet_mesh");
+        ck(gaia_b200_set_ghosts(pt.h, 0, ghosts.data(), (int32_t)ghosts.size()), "gaia_b200_set_ghosts");
+        for (auto& d : deformers_)
+            for (size_t i = 0; i < d.selectedMeshes.size(); i++) {
+                std::vector<int32_t> g(d.selectedVertices[i].begin(), d.selectedVertices[i].end());
+                if (g.empty()) continue;
+                if (d.type == 0) ck(gaia_b200_add_rotator(pt.h, 0, g.data(), (int32_t)g.size(), d.center, d.axis, d.angularVelocity, d.endTime), "gaia_b200_add_rotator");
+                else ck(gaia_b200_add_translator(pt.h, 0, g.data(), (int32_t)g.size(), d.speed, d.endTime), "gaia_b200_add_translator");
+            }
+        ck(gaia_b200_finalize(pt.h), "gaia_b200_finalize");
+    });
+    std::vector<std::array<unsigned char, 16>> ptrs(nGpus_);
+    for (int r = 0; r < nGpus_; r++) if (gaia_b200_halo_local_pointers(parts_[r].h, ptrs[r].data()) < 0) throw std::runtime_error(gaia_b200_last_error(parts_[r].h));
+    for (int r = 0; r < nGpus_; r++) {
+        Part& pt = parts_[r];
+        std::vector<int32_t> mine;
+        for (int32_t v = 0; v < nV; v++) if (owner[v] == r) mine.push_back(v);
+        std::vector<int32_t> mv(2 * mine.size(), 0), remote(std::max<size_t>(mine.size(), 1));
+        for (size_t k = 0; k < mine.size(); k++) mv[2 * k + 1] = mine[k];
+        for (int q = 0; q < nGpus_; q++) {
+            if (q == r) continue;
+            if (gaia_b200_get_sorted_ids(parts_[q].h, 0, mine.data(), (int32_t)mine.size(), remote.data()) < 0) throw std::runtime_error(gaia_b200_last_error(parts_[q].h));
+            if (gaia_b200_halo_add_peer_pointers(pt.h, q, parts_[q].device, ptrs[q].data(), (int32_t)mine.size(), mv.data(), remote.data()) < 0)
+                throw std::runtime_error(gaia_b200_last_error(pt.h));
+        }
+    }
+    for (auto& pt : parts_) if (gaia_b200_halo_finalize(pt.h) < 0) throw std::runtime_error(gaia_b200_last_error(pt.h));
 }
 
 void VBDPhysicsB200MultiGPU::runStep() {

@@ -20,6 +20,9 @@ public:
     void simulate();
     void writeOutputs(const std::string& outFolder, int frameId) override;
     int numGpus() const { return nGpus_; }
+    // --layout replicated: the solve stays partitioned, but every GPU holds the WHOLE mesh as collision geometry and receives
+    // every colour's new positions from every other GPU - contacts between any two slabs are seen
+    void setReplicatedLayout(bool on) { replicated_ = on; }
 
 protected:
     void fetchSurfaceTopology() override;
@@ -33,7 +36,9 @@ private:
         std::vector<uint8_t> owned;
     };
     void forAllParts(const std::function<void(int)>& fn);      // one host thread per partition, joined before returning
+    void initializeReplicated(const std::vector<int32_t>& owner, const std::vector<int32_t>& cOffs, const std::vector<int32_t>& cFlat, int nColours);
     int nGpus_ = 1;
+    bool replicated_ = false;
     std::vector<Part> parts_;
     std::vector<int32_t> surfIds_;            // global surface vertex ids of the mesh (ascending)
     std::vector<float> global_, surface_;     // assembled positions

@@ -1,7 +1,8 @@
 // gaia_vbd_b200 — command-line driver with the reference's VBDDynamics calling convention (S/VBDDynamics/main.cpp:8-34,
 // M/Parser/Parser.h:7-45):
-//     gaia_vbd_b200 <Models.json> <Parameters.json> <outFolder|noOutput> [-R|--repoRoot DIR] [-r|--recoveryState FILE] [--device N] [--gpus N]
-// --gpus N (N > 1): the scene's single tet mesh is cut into N slabs, one per GPU of this box (VBDPhysicsB200MultiGPU).
+//     gaia_vbd_b200 <Models.json> <Parameters.json> <outFolder|noOutput> [-R|--repoRoot DIR] [-r|--recoveryState FILE] [--device N] [--gpus N [--layout ring|replicated]]
+// --gpus N (N > 1): the scene's single tet mesh is cut into N slabs, one per GPU of this box (VBDPhysicsB200MultiGPU);
+// --layout replicated: every GPU also holds the whole mesh as collision geometry, so contacts between any two slabs are seen.
 // --gui is accepted and ignored (no graphics stack on this box); --CPU is refused (this implementation has no CPU path).
 #include <cstdlib>
 #include <cstring>
@@ -15,6 +16,7 @@ int main(int argc, char** argv) {
     std::vector<std::string> pos;
     std::string repoRoot, recoveryStateFile;
     int device = 0, gpus = 1;
+    std::string layout = "ring";
     bool dryRun = false;   // parse the inputs and load the meshes, print the scene size, do not touch the GPU
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
@@ -26,6 +28,7 @@ int main(int argc, char** argv) {
         else if (a == "-r" || a == "--recoveryState") recoveryStateFile = next("--recoveryState");
         else if (a == "--device") device = std::atoi(next("--device").c_str());
         else if (a == "--gpus") gpus = std::atoi(next("--gpus").c_str());
+        else if (a == "--layout") { layout = next("--layout"); if (layout != "ring" && layout != "replicated") { std::cerr << "--layout ring | replicated\n"; return 1; } }
         else if (a == "-g" || a == "--gui") std::cerr << "[gaia_b200] --gui ignored: the viewer needs a graphics stack, unavailable on this box\n";
         else if (a == "--CPU") { std::cerr << "[gaia_b200] --CPU refused: this implementation of the VBD step has no CPU path\n"; return 2; }
         else if (a == "--git") {}
@@ -41,6 +44,7 @@ int main(int argc, char** argv) {
         if (gpus > 1) {
             if (!recoveryStateFile.empty()) { std::cerr << "[gaia_b200] --recoveryState is not supported together with --gpus\n"; return 2; }
             gaia_b200::VBDPhysicsB200MultiGPU physics(gpus);
+            physics.setReplicatedLayout(layout == "replicated");
             physics.setRepoRoot(repoRoot);
             physics.loadRunningparameters(pos[0], pos[1], pos[2]);
             if (pos[2] == "noOutput") physics.runParams().saveOutputs = false;

@@ -40,6 +40,23 @@ def main():
                                 "iterations": int(os.environ.get("GAIA_CHECK_ITERS", "20")), "timeStep": 0.0166666, "outputExt": "bin", "outputRecoveryState": False, "binaryModeVisualizationSteps": 1000,
                                 "useGPU": True, "debugVerboseLvl": 1},
               "CollisionParams": {"allowDCD": bool(int(os.environ.get("GAIA_CHECK_DCD", "0"))), "allowCCD": False}, "ViewerParams": {"enableViewer": False}, "Deformers": deformers}
+    layout = os.environ.get("GAIA_CHECK_LAYOUT", "ring")
+    if os.environ.get("GAIA_CHECK_FOLDED", "0") == "1":
+        # a beam folded onto itself, the upper arm's end pressed onto the lower arm: self-contact between far-apart parts of the mesh
+        from gaia_b200 import workloads
+        wl = workloads.workload_folded_beam(96, 8, 8, 0.05, 0.03, 0.6, 2, 10)
+        fv, ft, fobj, fcol, ffixed = wl["meshes"][0]
+        meshio.save_t(os.path.join(tmp, "beam.t"), fv, ft)
+        with open(os.path.join(tmp, "beam.t.vertexColoring.json"), "w") as f:
+            json.dump([c.tolist() for c in fcol], f)
+        models[0].update({"density": 100, "miu": 5e4, "lmbd": 5e5, "dampingHydrostatic": 1e-5, "dampingDeviatoric": 1e-5, "frictionDynamic": 0.2,
+                          "fixedPoints": [int(x) for x in ffixed]})
+        tip = wl["deformers"][0][1]
+        params["Deformers"] = [{"DeformerName": "Translator", "speed": [0.0, -0.6, 0.0], "deformationEndTime": -1, "selectedMeshes": [0],
+                                "selectedVertices": [[int(x) for x in tip]]}]
+        params["PhysicsParams"].update({"gravity": [0, -10, 0], "worldBounds": [[-10, 0, -10], [10, 20, 10]], "numSubsteps": 2, "iterations": 10,
+                                        "collisionStiffness": 1e5})
+        params["CollisionParams"] = {"allowDCD": True, "allowCCD": True}
     with open(os.path.join(tmp, "Models.json"), "w") as f:
         json.dump({"Models": models}, f)
     with open(os.path.join(tmp, "Parameters.json"), "w") as f:
@@ -47,7 +64,7 @@ def main():
     outs = []
     for g in (1, n):
         out = os.path.join(tmp, f"out{g}")
-        r = subprocess.run([HOST, os.path.join(tmp, "Models.json"), os.path.join(tmp, "Parameters.json"), out, "-R", tmp, "--gpus", str(g)],
+        r = subprocess.run([HOST, os.path.join(tmp, "Models.json"), os.path.join(tmp, "Parameters.json"), out, "-R", tmp, "--gpus", str(g), "--layout", layout],
                            capture_output=True, text=True, timeout=600)
         print(f"--gpus {g}: rc={r.returncode}", r.stdout.strip().splitlines()[-1:] , r.stderr.strip()[-300:])
         if r.returncode:
@@ -71,7 +88,7 @@ def main():
                 for lo in np.arange(0.0, x0.max() + 1e-6, x0.max() / 8):
                     sel = (x0 >= lo) & (x0 < lo + x0.max() / 8 + 1e-9)
                     print(f"    x in [{lo:.2f}, {lo + x0.max() / 8:.2f}): {int((d[sel] > 0).sum())} of {int(sel.sum())} differ, max {d[sel].max():.2e}")
-    print(f"[check_cpp_multigpu] gpus={n} frames={frames} byte_identical={same} max_displacement={moved:.4f}")
+    print(f"[check_cpp_multigpu] gpus={n} layout={layout} folded={os.environ.get('GAIA_CHECK_FOLDED', '0')} frames={frames} byte_identical={same} max_displacement={moved:.4f}")
     sys.exit(0 if same and moved > 1e-3 else 1)
 
 
