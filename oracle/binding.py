@@ -53,6 +53,7 @@ def load_oracle():
             getattr(lib, "oracle_" + f).argtypes = [P]
         lib.oracle_phase_solve_group.argtypes = [P, C.c_int, C.c_int]
         lib.oracle_set_prev_positions.argtypes = [P, C.c_int, FP]
+        lib.oracle_vertex_merit_energy.argtypes = [P, C.c_int, C.c_int, FP, FP, FP]
         lib.oracle_get_dminv.argtypes = [P, C.c_int, FP]
         lib.oracle_get_rest_volumes.argtypes = [P, C.c_int, FP]
         lib.oracle_get_vertex_tet_csr.argtypes = [P, C.c_int, IP, IP, IP]
@@ -87,6 +88,8 @@ def load_ref():
         lib.ref_boundary.restype = None
         lib.ref_solve3x3.argtypes = [FP, FP, FP]
         lib.ref_damp_velocity.argtypes = [FP, C.c_float, C.c_float, C.c_float]; lib.ref_damp_velocity.restype = None
+        if hasattr(lib, "ref_neohookean_tet_energy"):
+            lib.ref_neohookean_tet_energy.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int, IP, FP, FP]; lib.ref_neohookean_tet_energy.restype = C.c_float
         lib.ref_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]
         lib.ref_cubic_roots.argtypes = [FP, C.c_float, C.c_float, FP]
         lib.ref_point_in_tet.argtypes = [FP] * 5
@@ -141,6 +144,12 @@ class OracleScene(SceneBase):
 
     def set_brute_force(self, on=True):
         self._call("set_brute_force", int(on))
+
+    def vertex_merit_energy(self, mesh, v, x):
+        """(inertia, elastic) parts of evaluateVertexMeritEnergy with vertex v at x"""
+        x = _f32(x); a = C.c_float(); b = C.c_float()
+        self._call("vertex_merit_energy", mesh, int(v), _fp(x), C.byref(a), C.byref(b))
+        return a.value, b.value
 
     def dminv(self, mesh):
         a = np.empty((self.mesh_sizes(mesh)[1], 9), np.float32)

@@ -88,6 +88,15 @@ int oracle_set_line_search(void* h, int32_t enabled, float tau, float tauGD, int
     s->lineSearch.enabled = enabled != 0; s->lineSearch.tau = tau; s->lineSearch.tauGD = tauGD; s->lineSearch.maxIters = maxIters;
     return GAIA_OK;
 }
+// parity surface of the line search's merit energy: inertia and elastic part with vertex v of `mesh` at x
+int oracle_vertex_merit_energy(void* h, int mesh, int v, const float* x3, float* inertiaOut, float* elasticOut) {
+    Scene* s = (Scene*)h;
+    if (mesh < 0 || mesh >= (int)s->meshes.size() || v < 0 || v >= s->meshes[mesh].nV) return GAIA_ERR_INVALID_ARG;
+    float in = 0.f, el = 0.f;
+    vertex_merit_energy_parts(*s, s->meshes[mesh], v, V3(x3[0], x3[1], x3[2]), in, el);
+    *inertiaOut = in; *elasticOut = el;
+    return GAIA_OK;
+}
 int64_t oracle_line_search_shrinks(void* h) { return ((Scene*)h)->lineSearchShrinks; }
 int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }

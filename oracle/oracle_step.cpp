@@ -208,7 +208,13 @@ static void collision_force_hessian(Scene& s, Mesh& m, int iV, V3& force, M3& he
 
 // evaluateVertexMeritEnergy (M/VBD/VBD_NeoHookean.cpp:90-124): inertia + Neo-Hookean energy of the incident tets, with the
 // vertex at `x` (the reference writes the trial position into the mesh and evaluates; here it is passed in)
+void vertex_merit_energy_parts(const Scene& s, const Mesh& m, int iV, const V3& x, float& meInertiaOut, float& meElasticOut);
 static float vertex_merit_energy(const Scene& s, const Mesh& m, int iV, const V3& x) {
+    float a, b;
+    vertex_merit_energy_parts(s, m, iV, x, a, b);
+    return a + b;
+}
+void vertex_merit_energy_parts(const Scene& s, const Mesh& m, int iV, const V3& x, float& meInertiaOut, float& meElasticOut) {
     // 0.5 * vertexMass * squaredNorm * dtSqrReciprocal: the literal is a double, so the product is formed in double
     const V3 d = x - m.inertia[iV];
     const float meInertia = (float)(0.5 * (double)m.mass[iV] * (double)sqnorm(d) * (double)s.dtSqrReciprocal);
@@ -235,7 +241,7 @@ static float vertex_merit_energy(const Scene& s, const Mesh& m, int iV, const V3
         const float PhiH = 0.5f * ((detF - a) * (detF - a));
         meElastic += A * (miu * PhiD + lmbd * PhiH);
     }
-    return meInertia + meElastic;
+    meInertiaOut = meInertia; meElasticOut = meElastic;
 }
 
 // backTracingLineSearchVBD (M/VBD/VBD_NeoHookean.h:115-153) as called from VBDStepWithCollision (M/VBD/VBDPhysics.cpp:2467-2474):

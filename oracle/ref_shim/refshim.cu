@@ -68,5 +68,11 @@ int ref_solve3x3(const float* m9, const float* b3, float* out3) { return CuMatri
 // GAIA::dampVelocity (VBDPhysicsCompute.cu:1397-1413); GPU-variant clamp rule
 void ref_damp_velocity(float* v3, float maxV, float expD, float constD) { dampVelocity(v3, maxV, expD, constD); }
 
+// GAIA::evaluateNeoHookeanEnergy (VBDPhysicsCompute.cu:1775-1808): the per-tet elastic energy (minus its rest value) behind
+// evaluateElasticEnergy_kernel - the same A (mu Phi_D + lmbd Phi_H) that evaluateVertexMeritEnergy sums over a vertex's tets
+float ref_neohookean_tet_energy(float miu, float lmbd, float A, int tetId, const int* tetVIds4, float* vs, const float* DmInvs) {
+    return evaluateNeoHookeanEnergy(miu, lmbd, A, tetId, tetVIds4, vs, DmInvs);
+}
+
 int refshim_ok() { return 1; }
 }

@@ -109,6 +109,7 @@ void run_iterations(Scene& s, int nIters); // initial step + nIters colour sweep
 void phase_begin_substep(Scene& s);       // curTime += dt, dcd, initial step, deformers
 void phase_prepare(Scene& s);             // ccd + prepareCollisionData
 void phase_solve_group(Scene& s, int g, bool applyFriction);
+void vertex_merit_energy_parts(const Scene& s, const Mesh& m, int iV, const V3& x, float& inertia, float& elastic);   // evaluateVertexMeritEnergy
 void phase_intermediate_cd(Scene& s);    // dcd (intermediate) + ccd + prepareCollisionData, every intermediateCollisionIterations
 void phase_end_substep(Scene& s);         // velocities
 void enable_models(Scene& s);

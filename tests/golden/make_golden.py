@@ -55,6 +55,14 @@ def main():
                                       c["dt"], v, fp(f), fp(h))
             F[v] = f; H[v] = h
         out[tag + "_force"] = F; out[tag + "_hessian"] = H
+    # ---- per-tet Neo-Hookean energy (GAIA::evaluateNeoHookeanEnergy, minus its rest value): what the line search's merit energy sums
+    c = neohookean_case(seed=11, dampH=0.0, dampD=0.0)
+    nT = len(c["tets"])
+    E = np.zeros(nT, np.float32)
+    pos = np.ascontiguousarray(c["pos"]); dm = np.ascontiguousarray(c["DmInv"]); tets = np.ascontiguousarray(c["tets"], np.int32)
+    for t in range(nT):
+        E[t] = ref.ref_neohookean_tet_energy(c["miu"], c["lmbd"], float(c["restVol"][t]), t, ip(tets[t]), fp(pos), fp(dm))
+    out["nh_tet_energy"] = E
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

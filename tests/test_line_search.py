@@ -1,7 +1,8 @@
 """Backtracking line search on the vertex merit energy (the reference's APPLY_LOCAL_LINE_SEARCH, M/VBD/VBDPhysics.cpp:25,
 2467-2474 - compiled out there; backTracingLineSearchVBD M/VBD/VBD_NeoHookean.h:115-153; evaluateVertexMeritEnergy
-M/VBD/VBD_NeoHookean.cpp:90-124). The oracle's restatement is UNPINNED (the reference's mesh class needs Eigen + MeshFrame and
-is not buildable here), so the CPU tests check it against an independent float64 statement of the merit energy: a colour sweep
+M/VBD/VBD_NeoHookean.cpp:90-124). The elastic part of the oracle's merit energy is pinned to the reference's own compiled per-tet
+energy (tests/test_oracle_vs_ref.py::test_vertex_merit_energy_elastic_part); the search loop itself restates CPU members that
+need Eigen + MeshFrame and are not buildable here, so these tests check it against an independent float64 statement: a colour sweep
 with the line search on never raises the total merit energy. With the stable Neo-Hookean energy the merit energy of ONE vertex is
 exactly quadratic in its position (|F|^2 is quadratic, det F affine), so a full Newton step is never rejected except by
 rounding at convergence - which is why the reference can compile the search out; the tests therefore drive it with

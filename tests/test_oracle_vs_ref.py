@@ -61,6 +61,32 @@ def test_neohookean_force_hessian_damped():
             assert tmp * c["dampD"] / c["dt"] > 1e-3 * np.abs(H).max()
 
 
+def test_vertex_merit_energy_elastic_part():
+    """The line search's merit energy (oracle: vertex_merit_energy_parts, restating evaluateVertexMeritEnergy,
+    M/VBD/VBD_NeoHookean.cpp:90-124) against the reference's own compiled per-tet energy evaluateNeoHookeanEnergy
+    (VBDPhysicsCompute.cu:1775-1808 = A (mu Phi_D + lmbd Phi_H) minus its rest value 0.5 A lmbd (1 - a)^2): the elastic part of
+    a vertex is the sum over its incident tets. 1e-5 relative (different float association; the rest value is added back)."""
+    c = neohookean_case(seed=11, dampH=0.0, dampD=0.0)
+    o = c["scene"]
+    o.set_state(0, c["pos"], None)
+    a = 1.0 + c["miu"] / c["lmbd"]
+    rest = 0.5 * c["restVol"].astype(np.float64) * c["lmbd"] * (1.0 - a) ** 2
+    per_tet = GOLD["nh_tet_energy"].astype(np.float64) + rest
+    assert per_tet.min() > 0 and (np.abs(GOLD["nh_tet_energy"]) > 1e-3 * rest).any()          # deformed: not just the rest value
+    infos, nbr, _ = c["infos"], c["nbrTets"], c["nbrOrder"]
+    for v in range(len(c["pos"])):
+        want = per_tet[nbr[infos[2 * v]: infos[2 * v] + infos[2 * v + 1]]].sum()
+        inertia, elastic = o.vertex_merit_energy(0, v, c["pos"][v])
+        assert abs(elastic - want) <= 1e-5 * want, (v, elastic, want)
+        # moving the vertex changes the energy the way the per-vertex force says (first order), so the two are consistent
+    v = 5
+    F, _ = o.vertex_material_force_hessian(0, v)
+    d = np.array([1e-3, -2e-3, 1.5e-3], np.float32)
+    e0 = o.vertex_merit_energy(0, v, c["pos"][v])[1]; e1 = o.vertex_merit_energy(0, v, c["pos"][v] + d)[1]; e2 = o.vertex_merit_energy(0, v, c["pos"][v] - d)[1]
+    fd = float(F.astype(np.float64) @ d)
+    assert abs((e1 - e2) / 2 + fd) < 2e-2 * abs(fd) + 1e-6 * abs(e0)
+
+
 def test_solve3x3_bit_exact():
     lib = load_oracle()
     Ms, Bs = solve3x3_cases()
