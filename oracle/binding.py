@@ -88,6 +88,11 @@ def load_ref():
         lib.ref_boundary.restype = None
         lib.ref_solve3x3.argtypes = [FP, FP, FP]
         lib.ref_damp_velocity.argtypes = [FP, C.c_float, C.c_float, C.c_float]; lib.ref_damp_velocity.restype = None
+        if hasattr(lib, "ref_cloth_material_vertex"):
+            lib.ref_cloth_bending_forms.argtypes = [C.c_int, FP, C.c_int, IP, C.c_int, IP, FP]; lib.ref_cloth_bending_forms.restype = None
+            lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
+                [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
+            lib.ref_cloth_material_vertex.restype = None
         if hasattr(lib, "ref_neohookean_tet_energy"):
             lib.ref_neohookean_tet_energy.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int, IP, FP, FP]; lib.ref_neohookean_tet_energy.restype = C.c_float
         lib.ref_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]

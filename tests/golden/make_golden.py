@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -63,6 +63,22 @@ def main():
     for t in range(nT):
         E[t] = ref.ref_neohookean_tet_energy(c["miu"], c["lmbd"], float(c["restVol"][t]), t, ip(tets[t]), fp(pos), fp(dm))
     out["nh_tet_energy"] = E
+    # ---- cloth material: VBDTriMeshStVk::intializeEdgeQuadraticForms + ::accumlateMaterialForceAndHessian (membrane + bending)
+    c = cloth_material_case()
+    nV, nF, nE = len(c["pos"]), len(c["faces"]), len(c["edges"])
+    Q = np.zeros((nE, 16), np.float32)
+    ref.ref_cloth_bending_forms(nV, fp(c["rest"]), nF, ip(c["faces"]), nE, ip(c["edges"]), fp(Q))
+    out["cloth_Q"] = Q
+    for which, tag in ((0, "cloth_material"), (1, "cloth_stvk"), (2, "cloth_bending")):
+        F = np.zeros((nV, 3), np.float32); H = np.zeros((nV, 9), np.float32)
+        for v in range(nV):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            ref.ref_cloth_material_vertex(nV, fp(c["pos"]), fp(c["prev"]), nF, ip(c["faces"]), fp(c["dminv"]), fp(c["area"]),
+                                          ip(c["vf"][0]), ip(c["vf"][1]), ip(c["vf"][2]), nE, ip(c["edges"]), fp(Q),
+                                          ip(c["vb"][0]), ip(c["vb"][1]), ip(c["vb"][2]), c["miu"], c["lmbd"], c["dampS"], c["bend"], c["dampB"],
+                                          c["dt"], c["thres"], v, which, fp(f), fp(h))
+            F[v] = f; H[v] = h
+        out[tag + "_force"] = F; out[tag + "_hessian"] = H
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

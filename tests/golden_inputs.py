@@ -203,3 +203,47 @@ def cloth_repulsion_cases(n=300, seed=51):
     dis[1::13] = th[1::13] + r[1::13] * 0.5
     k = rng.uniform(1e3, 1e6, n).astype(np.float32)
     return dis, th, r, k
+
+
+def cloth_material_case(n=7, seed=61):
+    """A small square cloth, bent and stretched at random (with a random previous position, so that both damping terms act):
+    everything the reference's per-vertex cloth material routine reads. Mesh set-up (DmInv, rest areas, edge infos) is the
+    cloth oracle's; the vertex -> face and vertex -> hinge tables are rebuilt here in ascending order."""
+    from gaia_b200 import cloth
+    from oracle.binding_cloth import OracleClothScene
+    rng = np.random.default_rng(seed)
+    verts, faces = cloth.grid_cloth(n, size=1.0, origin=(0.0, 1.0, 0.0))
+    phys = cloth.default_cloth_physics_params(numSubsteps=4, iterations=1, handleCollision=0)
+    obj = cloth.default_cloth_object_params(miu=1.2e4, lambda_=2.1e4, bendingStiffness=6.0, dampingStVK=1.5e-3, dampingBending=2.5e-3, density=0.3)
+    o = OracleClothScene(phys, threads=1)
+    o.add_tri_mesh(verts, faces, obj, cloth.grid_cloth_coloring(n))
+    o.finalize()
+    rest = o.positions(0)
+    h = 1.0 / (n - 1)
+    pos = (rest + rng.normal(0, 0.08 * h, rest.shape)).astype(np.float32)
+    prev = (pos + rng.normal(0, 0.02 * h, rest.shape)).astype(np.float32)
+    o.set_state(0, pos, None); o.set_prev_positions(0, prev)
+    faces = np.ascontiguousarray(faces, np.int32)
+    edges = o.edges(0)
+    nV = len(rest)
+    vf = [[] for _ in range(nV)]
+    for f, tri in enumerate(faces):
+        for k in range(3):
+            vf[tri[k]].append((f, k))
+    vb = [[] for _ in range(nV)]
+    for e, E in enumerate(edges):
+        if E[5] < 0:
+            continue                                    # boundary edge: no hinge
+        for k in range(4):
+            vb[E[k]].append((e, k))
+
+    def csr(lists):
+        off = np.zeros(nV + 1, np.int32); a = []; b = []
+        for v, l in enumerate(lists):
+            off[v + 1] = off[v] + len(l); a += [x[0] for x in l]; b += [x[1] for x in l]
+        return off, np.asarray(a, np.int32), np.asarray(b, np.int32)
+    dminv, area = o.dminv(0)
+    return dict(scene=o, rest=np.ascontiguousarray(rest), pos=pos, prev=prev, faces=faces, edges=np.ascontiguousarray(edges, np.int32),
+                dminv=np.ascontiguousarray(dminv), area=np.ascontiguousarray(area), vf=csr(vf), vb=csr(vb),
+                miu=1.2e4, lmbd=2.1e4, bend=6.0, dampS=1.5e-3, dampB=2.5e-3, dt=float(np.float32(phys.timeStep) / np.float32(4)),
+                thres=float(phys.degenerateTriangleThres))

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -212,6 +212,27 @@ def test_cloth_contact_repulsion_bit_exact():
 
 
 @pytest.mark.skipif(not ref_available(), reason="oracle/_ref/libgaia_ref.so is only built where /root/reference exists")
+def test_cloth_material_force_hessian_and_bending_forms():
+    """The cloth oracle's membrane (StVK) + bending force / Hessian per vertex, with both damping terms, and its quadratic
+    bending forms, against the reference's own lines compiled into oracle/_ref (VBDTriMeshStVk::accumlateMaterialForceAndHessian
+    = ::accumlateStVKForceAndHessian + ::accumlateBendingForceAndHessian, VBDTriMeshStVK.cpp:715-982; ::intializeEdgeQuadraticForms,
+    :49-88; assembleMembraneHessian, VBDBaseTriMesh.h:149-160 - compiled against a stand-in <Eigen/Dense>, oracle/ref_shim/refcloth.cpp).
+    Forms: bit-exact. Force / Hessian: 2e-6 relative to the largest entry (sums over 6 faces and up to 12 hinges in another order)."""
+    c = cloth_material_case()
+    o = c["scene"]
+    assert np.array_equal(o.bending_forms(0).reshape(-1, 16), GOLD["cloth_Q"]) and np.abs(GOLD["cloth_Q"]).max() > 10
+    n = len(c["pos"])
+    F = np.zeros((n, 3), np.float32); H = np.zeros((n, 9), np.float32)
+    for v in range(n):
+        f, h = o.material_force_hessian(0, v)
+        F[v] = f; H[v] = h.T.reshape(9)
+    assert relmax(F, GOLD["cloth_material_force"]) < 2e-6
+    assert relmax(H, GOLD["cloth_material_hessian"]) < 2e-6
+    # both parts and both damping terms are live in this fixture
+    assert np.abs(GOLD["cloth_bending_force"]).max() > 0.05 * np.abs(GOLD["cloth_stvk_force"]).max()
+    assert np.abs(GOLD["cloth_stvk_force"] + GOLD["cloth_bending_force"] - GOLD["cloth_material_force"]).max() < 1e-5 * np.abs(GOLD["cloth_material_force"]).max()
+
+
 def test_golden_file_matches_a_fresh_run_of_the_reference():
     """The committed fixture is what the reference's code produces today (guards against a stale .npz)."""
     ref = load_ref()
