@@ -93,6 +93,13 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_cloth_vf_contact"):
+            lib.ref_cloth_vf_contact.argtypes = [FP, FP, FP, FP, C.c_int, FP, FP, IP, C.c_int, FP, FP, C.c_int, C.c_int, FP, FP]
+            lib.ref_cloth_vf_contact.restype = C.c_float
+            lib.ref_cloth_ee_contact.argtypes = [FP, FP, FP, FP, C.c_int, IP, C.c_int, FP, FP, C.c_int, IP, C.c_int, FP, FP, C.c_float, C.c_float,
+                                                 C.c_int, C.c_int, FP, FP]
+            lib.ref_cloth_ee_contact.restype = C.c_float
+            lib.ref_cloth_boundary.argtypes = [FP, FP, FP, FP, FP, C.c_int, FP, FP]; lib.ref_cloth_boundary.restype = None
         if hasattr(lib, "ref_neohookean_tet_energy"):
             lib.ref_neohookean_tet_energy.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int, IP, FP, FP]; lib.ref_neohookean_tet_energy.restype = C.c_float
         lib.ref_ccd_tri_point.argtypes = [FP, FP, FP, FP, FP, FP]

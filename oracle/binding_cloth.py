@@ -22,6 +22,9 @@ def _lib():
         lib.oracle_cloth_num_threads.argtypes = [P]
         lib.oracle_cloth_set_brute_force.argtypes = [P, C.c_int]; lib.oracle_cloth_set_brute_force.restype = None
         lib.oracle_cloth_set_prev_positions.argtypes = [P, C.c_int, FP]
+        lib.oracle_cloth_probe_vf.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_vf.restype = C.c_float
+        lib.oracle_cloth_probe_ee.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_ee.restype = C.c_float
+        lib.oracle_cloth_probe_boundary.argtypes = [P, C.c_int, C.c_int, FP, FP]; lib.oracle_cloth_probe_boundary.restype = None
         lib.oracle_cloth_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
         lib.oracle_cloth_vertex_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
         lib.oracle_cloth_elastic_energy.argtypes = [P, C.c_int]; lib.oracle_cloth_elastic_energy.restype = C.c_float
@@ -62,6 +65,25 @@ class OracleClothScene(ClothSceneBase):
         f = np.empty(3, np.float32); h = np.empty(9, np.float32)
         self._lib.oracle_cloth_vertex_force_hessian(self.h, mesh, v, _fp(f), _fp(h))
         return f, h.reshape(3, 3).T.copy()
+
+    def probe_vf(self, v_mesh, v, f_mesh, f, order):
+        """one vertex-face contact in isolation (closest point recomputed, friction on): (distance, force, H[r, c])"""
+        fo = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        fn = self._lib.oracle_cloth_probe_vf; fn.restype = C.c_float
+        d = fn(self.h, int(v_mesh), int(v), int(f_mesh), int(f), int(order), _fp(fo), _fp(h))
+        return float(d), fo, h.reshape(3, 3).T.copy()
+
+    def probe_ee(self, m1, e1, m2, e2, order):
+        fo = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        fn = self._lib.oracle_cloth_probe_ee; fn.restype = C.c_float
+        d = fn(self.h, int(m1), int(e1), int(m2), int(e2), int(order), _fp(fo), _fp(h))
+        return float(d), fo, h.reshape(3, 3).T.copy()
+
+    def probe_boundary(self, mesh, v):
+        fo = np.empty(3, np.float32); h = np.empty(9, np.float32)
+        fn = self._lib.oracle_cloth_probe_boundary; fn.restype = None
+        fn(self.h, int(mesh), int(v), _fp(fo), _fp(h))
+        return fo, h.reshape(3, 3).T.copy()
 
     def elastic_energy(self, mesh):
         return float(self._lib.oracle_cloth_elastic_energy(self.h, mesh))

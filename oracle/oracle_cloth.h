@@ -1,9 +1,10 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
 // State of the CPU restatement of the reference VBD *cloth* step (M/VBDCloth, M/TriMesh,
-// M/CollisionDetector/ClothContactDetector.*). Parity status: UNPINNED beyond this restatement — the reference cloth code
-// needs Eigen/oneTBB/Embree (absent here) and ships no golden vectors; the restatement is checked against closed-form
-// properties (finite differences of the StVK / bending / contact energies, brute-force contact sets) in
-// tests/test_oracle_cloth.py.
+// M/CollisionDetector/ClothContactDetector.*). Parity status: the per-vertex arithmetic (membrane + bending force / Hessian,
+// bending forms, VF / EE contact force / Hessian with friction, world box, contact energy derivatives, segment distances) is
+// PINNED to the reference's own lines compiled into oracle/_ref (tests/test_oracle_vs_ref.py; ref_shim/refcloth*.cpp);
+// mesh set-up, contact detection and the step loop are UNPINNED - their reference code needs Embree / MeshFrame2 (absent here)
+// and ships no golden vectors - and are checked against closed-form properties and brute force in tests/test_oracle_cloth.py.
 #pragma once
 #include "oracle_common.h"
 #include "../include/gaia_b200_cloth.h"
@@ -121,6 +122,9 @@ void cloth_material_force_hessian(const ClothScene& s, const TriMesh& m, int v, 
 void cloth_vertex_force_hessian(ClothScene& s, int mesh, int v, V3& force, M3& hessian);
 float cloth_elastic_energy(const ClothScene& s, const TriMesh& m);
 void cloth_contact_repulsion(const ClothScene& s, float dis, float& dEdD, float& d2E);
+float cloth_probe_vf(const ClothScene& s, int vMesh, int v, int fMesh, int f, int vertexOrder, V3& force, M3& hessian);
+float cloth_probe_ee(const ClothScene& s, int m1, int e1, int m2, int e2, int vertexOrder, V3& force, M3& hessian);
+void cloth_probe_boundary(const ClothScene& s, int mesh, int v, V3& force, M3& hessian);
 V3 closest_point_triangle(V3 p, V3 a, V3 b, V3 c, V3& bary, int& type);   // oracle_collision.cpp
 void closest_points_segments(V3 p0, V3 p1, V3 q0, V3 q1, V3& ps, V3& qt, float& s, float& t);   // oracle_cloth_contact.cpp
 bool solve3x3_psd_stable(const float* m, const float* b, float* out);      // oracle_step.cpp

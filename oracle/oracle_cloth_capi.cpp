@@ -174,6 +174,16 @@ int oracle_cloth_vertex_force_hessian(void* h, int mesh, int v, float* f3, float
     std::memcpy(h9, H.m, sizeof(H.m));
     return GAIA_OK;
 }
+static void out_fh(const V3& f, const M3& H, float* f3, float* h9) { f3[0] = f.x; f3[1] = f.y; f3[2] = f.z; std::memcpy(h9, H.m, sizeof(H.m)); }
+float oracle_cloth_probe_vf(void* h, int vMesh, int v, int fMesh, int f, int order, float* f3, float* h9) {
+    V3 F; M3 H; const float d = cloth_probe_vf(*(ClothScene*)h, vMesh, v, fMesh, f, order, F, H); out_fh(F, H, f3, h9); return d;
+}
+float oracle_cloth_probe_ee(void* h, int m1, int e1, int m2, int e2, int order, float* f3, float* h9) {
+    V3 F; M3 H; const float d = cloth_probe_ee(*(ClothScene*)h, m1, e1, m2, e2, order, F, H); out_fh(F, H, f3, h9); return d;
+}
+void oracle_cloth_probe_boundary(void* h, int mesh, int v, float* f3, float* h9) {
+    V3 F; M3 H; cloth_probe_boundary(*(ClothScene*)h, mesh, v, F, H); out_fh(F, H, f3, h9);
+}
 float oracle_cloth_elastic_energy(void* h, int mesh) { ClothScene* s = (ClothScene*)h; return cloth_elastic_energy(*s, s->meshes[mesh]); }
 void oracle_cloth_contact_repulsion(void* h, float dis, float* dEdD, float* d2E) { cloth_contact_repulsion(*(ClothScene*)h, dis, *dEdD, *d2E); }
 int oracle_cloth_get_dminv(void* h, int mesh, float* out4, float* area) {

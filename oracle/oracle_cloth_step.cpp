@@ -247,6 +247,22 @@ static void boundary_force_hessian(const ClothScene& s, const TriMesh& m, int vI
     }
 }
 
+// parity probes (tests/test_oracle_vs_ref.py): one contact / the world box of one vertex in isolation
+float cloth_probe_vf(const ClothScene& s, int vMesh, int v, int fMesh, int f, int vertexOrder, V3& force, M3& hessian) {
+    VFContact c{}; c.vMesh = vMesh; c.v = v; c.fMesh = fMesh; c.f = f;
+    force = V3(); hessian = M3();
+    return vf_contact_force_hessian(s, c, vertexOrder, force, hessian);
+}
+float cloth_probe_ee(const ClothScene& s, int m1, int e1, int m2, int e2, int vertexOrder, V3& force, M3& hessian) {
+    EEContact c{}; c.m1 = m1; c.e1 = e1; c.m2 = m2; c.e2 = e2;
+    force = V3(); hessian = M3();
+    return ee_contact_force_hessian(s, c, vertexOrder, force, hessian);
+}
+void cloth_probe_boundary(const ClothScene& s, int mesh, int v, V3& force, M3& hessian) {
+    force = V3(); hessian = M3();
+    boundary_force_hessian(s, s.meshes[mesh], v, force, hessian);
+}
+
 // evaluateVertexForceAndHessian / the first part of VBDStepWithExistingCollisions (:1026-1104, 1156-1221)
 void cloth_vertex_force_hessian(ClothScene& s, int iMesh, int vId, V3& force, M3& hessian) {
     TriMesh& m = s.meshes[iMesh];

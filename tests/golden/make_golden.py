@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -79,6 +79,45 @@ def main():
                                           c["dt"], c["thres"], v, which, fp(f), fp(h))
             F[v] = f; H[v] = h
         out[tag + "_force"] = F; out[tag + "_hessian"] = H
+    # ---- cloth contacts, boundary and friction: VBDClothSimulationFramework::accumulateVF/EEContactForceAndHessian,
+    #      ::accumlateBoundaryForceAndHessian (with ::computeFriction, ::computeContactRepulsiveForce), three contact energies
+    for et in (0, 1, 2):
+        c = cloth_contact_case(et)
+        M = c["meshes"]
+        VF = np.zeros((len(c["vf"]), 4, 13), np.float32)
+        for i, (a, v, b, f) in enumerate(c["vf"]):
+            tri = M[b]["pos"][M[b]["faces"][f]]
+            cp = np.zeros(3, np.float32); bary = np.zeros(3, np.float32)
+            ref.ref_closest_point_triangle(fp(M[a]["pos"][v]), fp(tri[0]), fp(tri[1]), fp(tri[2]), fp(cp), fp(bary))
+            fr4 = np.array([M[a]["mu"], M[a]["eps"], M[b]["mu"], M[b]["eps"]], np.float32)
+            for order in range(4):
+                fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+                d = ref.ref_cloth_vf_contact(fp(c["params8"]), fp(fr4), fp(M[a]["pos"]), fp(M[a]["prev"]), v, fp(M[b]["pos"]), fp(M[b]["prev"]),
+                                             ip(M[b]["faces"]), f, fp(cp), fp(bary), order, 1, fp(fo), fp(h))
+                VF[i, order] = np.concatenate([[d], fo, h])
+        out[f"cloth_vf_e{et}"] = VF
+        EE = np.zeros((len(c["ee"]), 4, 13), np.float32)
+        for i, (a, e1, b, e2) in enumerate(c["ee"]):
+            E1, E2 = M[a]["edges"][e1], M[b]["edges"][e2]
+            o8 = np.zeros(8, np.float32)
+            ref.ref_closest_points_segments(fp(M[a]["pos"][E1[0]]), fp(M[a]["pos"][E1[1]]), fp(M[b]["pos"][E2[0]]), fp(M[b]["pos"][E2[1]]), fp(o8))
+            fr4 = np.array([M[a]["mu"], M[a]["eps"], M[b]["mu"], M[b]["eps"]], np.float32)
+            c1 = np.ascontiguousarray(o8[0:3]); c2 = np.ascontiguousarray(o8[3:6])
+            for order in range(4):
+                fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+                d = ref.ref_cloth_ee_contact(fp(c["params8"]), fp(fr4), fp(M[a]["pos"]), fp(M[a]["prev"]), len(M[a]["edges"]), ip(M[a]["edges"]), e1,
+                                             fp(M[b]["pos"]), fp(M[b]["prev"]), len(M[b]["edges"]), ip(M[b]["edges"]), e2, fp(c1), fp(c2),
+                                             float(o8[6]), float(o8[7]), order, 1, fp(fo), fp(h))
+                EE[i, order] = np.concatenate([[d], fo, h])
+        out[f"cloth_ee_e{et}"] = EE
+        if et == 1:
+            B = []
+            for mi, m in enumerate(M):
+                for v in range(len(m["pos"])):
+                    fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+                    ref.ref_cloth_boundary(fp(c["params8"]), fp(c["bmin"]), fp(c["bmax"]), fp(m["pos"]), fp(m["prev"]), v, fp(fo), fp(h))
+                    B.append(np.concatenate([fo, h]))
+            out["cloth_boundary"] = np.asarray(B, np.float32)
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

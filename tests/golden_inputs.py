@@ -247,3 +247,43 @@ def cloth_material_case(n=7, seed=61):
                 dminv=np.ascontiguousarray(dminv), area=np.ascontiguousarray(area), vf=csr(vf), vb=csr(vb),
                 miu=1.2e4, lmbd=2.1e4, bend=6.0, dampS=1.5e-3, dampB=2.5e-3, dt=float(np.float32(phys.timeStep) / np.float32(4)),
                 thres=float(phys.degenerateTriangleThres))
+
+
+def cloth_contact_case(energy_type=1, seed=71):
+    """Two small cloths a few centimetres apart (different friction parameters), both wrinkled at random with random previous
+    positions, inside a world box that cuts through them: vertex-face pairs in both directions, edge-edge pairs, and vertices
+    outside the box on several axes - the inputs of the reference's per-contact and boundary routines."""
+    from gaia_b200 import cloth
+    from oracle.binding_cloth import OracleClothScene
+    rng = np.random.default_rng(seed)
+    phys = cloth.default_cloth_physics_params(numSubsteps=4, iterations=1, handleCollision=1, contactRadius=0.12, thickness=0.01,
+                                              contactStiffness=2e4, contactEnergyTypes=energy_type, boundaryContactStiffness=3e4,
+                                              boundaryFrictionDynamic=0.4, boundaryFrictionEpsValue=0.05,
+                                              worldBoundsMin=[0.2, 0.005, -10.0], worldBoundsMax=[0.9, 10.0, 0.7])
+    o = OracleClothScene(phys, threads=1)
+    meshes = []
+    for n, size, org, mu, eps in ((5, 1.0, (0.0, 0.0, 0.0), 0.3, 0.05), (4, 0.8, (0.1, 0.06, 0.12), 0.5, 0.2)):
+        v, f = cloth.grid_cloth(n, size=size, origin=org)
+        obj = cloth.default_cloth_object_params(frictionDynamic=mu, frictionEpsV=eps, bendingStiffness=1.0)
+        o.add_tri_mesh(v, f, obj, cloth.grid_cloth_coloring(n))
+        meshes.append([np.ascontiguousarray(f, np.int32), mu, eps])
+    o.finalize()
+    out = []
+    for i, (f, mu, eps) in enumerate(meshes):
+        rest = o.positions(i)
+        pos = (rest + rng.normal(0, 0.02, rest.shape)).astype(np.float32)
+        prev = (pos + rng.normal(0, 0.01, rest.shape)).astype(np.float32)
+        o.set_state(i, pos, None); o.set_prev_positions(i, prev)
+        out.append(dict(pos=np.ascontiguousarray(pos), prev=np.ascontiguousarray(prev), faces=f, edges=np.ascontiguousarray(o.edges(i), np.int32), mu=mu, eps=eps))
+    vf = []           # (vertex mesh, vertex, face mesh, face): the face with the nearest centroid, both directions
+    for a, b in ((0, 1), (1, 0)):
+        cen = out[b]["pos"][out[b]["faces"]].mean(1)
+        for v in range(len(out[a]["pos"])):
+            vf.append((a, v, b, int(np.argmin(((cen - out[a]["pos"][v]) ** 2).sum(1)))))
+    ee = []           # (mesh 1, edge, mesh 2, edge): nearest midpoints
+    mid = [m["pos"][m["edges"][:, :2]].mean(1) for m in out]
+    for e1 in range(len(out[0]["edges"])):
+        ee.append((0, e1, 1, int(np.argmin(((mid[1] - mid[0][e1]) ** 2).sum(1)))))
+    dt = float(np.float32(phys.timeStep) / np.float32(4))
+    params8 = np.array([2e4, 0.12, 0.01, dt, 3e4, 0.4, 0.05, float(energy_type)], np.float32)
+    return dict(scene=o, meshes=out, vf=vf, ee=ee, params8=params8, bmin=np.array([0.2, 0.005, -10.0], np.float32), bmax=np.array([0.9, 10.0, 0.7], np.float32))

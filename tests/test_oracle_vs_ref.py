@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -231,6 +231,48 @@ def test_cloth_material_force_hessian_and_bending_forms():
     # both parts and both damping terms are live in this fixture
     assert np.abs(GOLD["cloth_bending_force"]).max() > 0.05 * np.abs(GOLD["cloth_stvk_force"]).max()
     assert np.abs(GOLD["cloth_stvk_force"] + GOLD["cloth_bending_force"] - GOLD["cloth_material_force"]).max() < 1e-5 * np.abs(GOLD["cloth_material_force"]).max()
+
+
+@pytest.mark.parametrize("energy_type", [0, 1, 2])
+def test_cloth_contact_force_hessian(energy_type):
+    """One vertex-face / edge-edge contact at a time, all four vertex orders, friction on, against the reference's own lines
+    compiled into oracle/_ref (VBDClothSimulationFramework::accumulateVFContactForceAndHessian, ::accumulateEEContactForceAndHessian
+    with ::computeFriction and ::computeContactRepulsiveForce, VBDClothPhysics.cpp:1248-1399, 1500-1579; oracle/ref_shim/
+    refclothcontact.cpp; closest points from the reference's own closestPointTriangle / get_closest_points_between_segments).
+    Distances bit-exact; force / Hessian 1e-6 relative to the largest entry; NaNs (log energy inside the thickness) in the same
+    places."""
+    c = cloth_contact_case(energy_type)
+    o = c["scene"]
+    for key, pairs, probe in (("cloth_vf", c["vf"], o.probe_vf), ("cloth_ee", c["ee"], o.probe_ee)):
+        G = GOLD[f"{key}_e{energy_type}"]
+        got = np.zeros_like(G)
+        for i, pr in enumerate(pairs):
+            for order in range(4):
+                d, f, h = probe(*pr, order)
+                got[i, order] = np.concatenate([[d], f, h.T.reshape(9)])
+        assert np.array_equal(got[:, :, 0], G[:, :, 0])
+        assert np.array_equal(np.isnan(got), np.isnan(G))
+        ok = ~np.isnan(G)
+        active = (np.abs(np.nan_to_num(G[:, :, 1:4])).max((1, 2)) > 0).sum()
+        assert active >= 25, active                                         # most pairs are inside the contact radius
+        for sl in (slice(1, 4), slice(4, 13)):
+            a, b = np.where(ok, got, 0)[:, :, sl], np.where(ok, G, 0)[:, :, sl]
+            assert relmax(a, b) < 1e-6
+
+
+def test_cloth_boundary_force_hessian():
+    """::accumlateBoundaryForceAndHessian (VBDClothPhysics.cpp:1401-1463): vertices outside the world box on up to two axes."""
+    c = cloth_contact_case(1)
+    o = c["scene"]
+    G = GOLD["cloth_boundary"]
+    got = []
+    for mi, m in enumerate(c["meshes"]):
+        for v in range(len(m["pos"])):
+            f, h = o.probe_boundary(mi, v)
+            got.append(np.concatenate([f, h.T.reshape(9)]))
+    got = np.asarray(got, np.float32)
+    assert (np.abs(G[:, :3]).max(1) > 0).sum() > 20
+    assert relmax(got[:, :3], G[:, :3]) < 1e-6 and relmax(got[:, 3:], G[:, 3:]) < 1e-6
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
