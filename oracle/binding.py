@@ -57,6 +57,8 @@ def load_oracle():
         lib.oracle_get_dminv.argtypes = [P, C.c_int, FP]
         lib.oracle_get_rest_volumes.argtypes = [P, C.c_int, FP]
         lib.oracle_get_vertex_tet_csr.argtypes = [P, C.c_int, IP, IP, IP]
+        lib.oracle_get_tet_topology.argtypes = [P, C.c_int, IP, IP, IP]
+        lib.oracle_tet_traverse.argtypes = [P, C.c_int, FP, FP, C.c_float, C.c_int, C.c_int, C.c_int, C.c_float, IP]
         lib.oracle_set_brute_force.argtypes = [P, C.c_int]
         lib.oracle_vertex_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
         lib.oracle_contact_force_hessian.argtypes = [FP, FP, FP, FP, C.c_int] + [C.c_float] * 6 + [FP, FP, FP]
@@ -93,6 +95,8 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_tet_traverse"):
+            lib.ref_tet_traverse.argtypes = [C.c_int, FP, C.c_int, IP, IP, IP, FP, FP, C.c_float, C.c_int, C.c_int, C.c_int, C.c_float, IP, IP]
         if hasattr(lib, "ref_cloth_vf_contact"):
             lib.ref_cloth_vf_contact.argtypes = [FP, FP, FP, FP, C.c_int, FP, FP, IP, C.c_int, FP, FP, C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_vf_contact.restype = C.c_float
@@ -176,6 +180,19 @@ class OracleScene(SceneBase):
         infos = np.empty(2 * nV, np.int32); t = np.empty(4 * nT, np.int32); o = np.empty(4 * nT, np.int32)
         self._call("get_vertex_tet_csr", mesh, _ip(infos), _ip(t), _ip(o))
         return infos, t, o
+
+    def tet_topology(self, mesh):
+        """(tets [nT,4], neighbour tet across face i [nT,4], xor of each tet's vertex ids [nT])"""
+        nT = self.mesh_sizes(mesh)[1]
+        t = np.empty((nT, 4), np.int32); nb = np.empty((nT, 4), np.int32); x = np.empty(nT, np.int32)
+        self._call("get_tet_topology", mesh, _ip(t), _ip(nb), _ip(x))
+        return t, nb, x
+
+    def tet_traverse(self, mesh, origin, direction, max_dis, start_tet, start_face, target_tet, eps):
+        """tetrahedralTraverseTo: (reached, tets traversed)"""
+        o = _f32(origin); d = _f32(direction); n = np.zeros(1, np.int32)
+        r = self._call("tet_traverse", mesh, _fp(o), _fp(d), float(max_dis), int(start_tet), int(start_face), int(target_tet), float(eps), _ip(n))
+        return bool(r), int(n[0])
 
     def vertex_material_force_hessian(self, mesh, v):
         f = np.empty(3, np.float32); h = np.empty(9, np.float32)

@@ -186,6 +186,22 @@ int oracle_get_vertex_tet_csr(void* h, int mesh, int32_t* infos, int32_t* tets, 
     std::memcpy(orders, m.vNbrOrder.data(), m.vNbrOrder.size() * 4);
     return GAIA_OK;
 }
+// parity probes of the tetrahedral traversal (tests/test_oracle_vs_ref.py): the topology it walks, and one walk
+int oracle_get_tet_topology(void* h, int mesh, int32_t* tets, int32_t* nbrTets, int32_t* xorSums) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    if (tets) std::memcpy(tets, m.tets.data(), m.tets.size() * 4);
+    if (nbrTets) std::memcpy(nbrTets, m.tetNbrTets.data(), m.tetNbrTets.size() * 4);
+    if (xorSums) std::memcpy(xorSums, m.tetXorSums.data(), m.tetXorSums.size() * 4);
+    return GAIA_OK;
+}
+int oracle_tet_traverse(void* h, int mesh, const float* origin3, const float* dir3, float maxDis, int startTet, int startFace, int targetTet, float eps,
+                        int32_t* numTraversed) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    int n = 0;
+    const bool ok = tetrahedral_traverse_to(m, V3(origin3[0], origin3[1], origin3[2]), V3(dir3[0], dir3[1], dir3[2]), maxDis, startTet, startFace, targetTet, eps, &n);
+    if (numTraversed) *numTraversed = n;
+    return ok ? 1 : 0;
+}
 int oracle_enable_mesh(void* h, int mesh, int col, int solve) {
     Mesh& m = ((Scene*)h)->meshes[mesh];
     m.activeForCollision = col != 0; m.activeForMaterialSolve = solve != 0;

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -118,6 +118,15 @@ def main():
                     ref.ref_cloth_boundary(fp(c["params8"]), fp(c["bmin"]), fp(c["bmax"]), fp(m["pos"]), fp(m["prev"]), v, fp(fo), fp(h))
                     B.append(np.concatenate([fo, h]))
             out["cloth_boundary"] = np.asarray(B, np.float32)
+    # ---- TetMeshFEM::tetrahedralTraverseTo (static-stack variant): reached?, tets traversed, stop reason
+    for c in traverse_cases():
+        R = np.zeros((len(c["rays"]), 3), np.int32)
+        for i, (org, d, md, st, sf, tg) in enumerate(c["rays"]):
+            n = np.zeros(1, np.int32); why = np.zeros(1, np.int32)
+            ok = ref.ref_tet_traverse(len(c["pos"]), fp(c["pos"]), len(c["tets"]), ip(c["tets"]), ip(c["nbr"]), ip(c["xor"]), fp(org), fp(d), float(md),
+                                      st, sf, tg, c["eps"], ip(n), ip(why))
+            R[i] = (ok, n[0], why[0])
+        out["traverse_" + c["name"]] = R
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

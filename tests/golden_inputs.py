@@ -287,3 +287,53 @@ def cloth_contact_case(energy_type=1, seed=71):
     dt = float(np.float32(phys.timeStep) / np.float32(4))
     params8 = np.array([2e4, 0.12, 0.01, dt, 3e4, 0.4, 0.05, float(energy_type)], np.float32)
     return dict(scene=o, meshes=out, vf=vf, ee=ee, params8=params8, bmin=np.array([0.2, 0.005, -10.0], np.float32), bmax=np.array([0.9, 10.0, 0.7], np.float32))
+
+
+def traverse_cases(seed=81, n_rays=400):
+    """Rays for TetMeshFEM::tetrahedralTraverseTo on two meshes - the reference's teapot (irregular valence, thin parts) and a
+    Kuhn beam -, both deformed at random: from a point on a surface face towards the centroid of a random tet (the way DCD
+    uses it: start = the tet behind that face, target = the tet holding the query point), with and without a distance limit,
+    plus rays aimed away from their target (stopped by the boundary, the empty stack or the distance check)."""
+    from gaia_b200.workloads import ref_mesh
+    from oracle.binding import OracleScene
+    rng = np.random.default_rng(seed)
+    out = []
+    for name in ("teapot", "kuhn"):
+        if name == "teapot":
+            verts, tets, colors = ref_mesh("teapot")
+        else:
+            verts, tets = meshio.kuhn_beam(6, 3, 3, h=0.25)
+            colors = meshio.kuhn_coloring(6, 3, 3)
+        o = OracleScene(capi.default_physics_params(), capi.default_collision_params(allowDCD=0, allowCCD=0), threads=1)
+        o.add_tet_mesh(verts, tets, capi.default_object_params(), colors)
+        o.finalize()
+        rest = o.positions(0)
+        scale = float(np.linalg.norm(rest.max(0) - rest.min(0)))
+        pos = (rest + rng.normal(0, 0.002 * scale, rest.shape)).astype(np.float32)
+        o.set_state(0, pos, None)
+        t, nb, xs = o.tet_topology(0)
+        faces = o.surface_faces(0)
+        # the tet behind a surface face and the face's id in it (= the index of the tet vertex the face does not hold)
+        key = {}
+        for ti in range(len(t)):
+            for i in range(4):
+                if nb[ti, i] < 0:
+                    key[tuple(sorted(int(x) for x in np.delete(t[ti], i)))] = (ti, i)
+        rays = []
+        for k in range(n_rays):
+            f = int(rng.integers(len(faces)))
+            st, sf = key[tuple(sorted(int(x) for x in faces[f]))]
+            w = rng.dirichlet([2.0, 2.0, 2.0]).astype(np.float32)
+            origin = (w[:, None] * pos[faces[f]]).sum(0).astype(np.float32)
+            target = int(rng.integers(len(t)))
+            cen = pos[t[target]].mean(0)
+            d = cen - origin
+            if k % 5 == 4:
+                d = d + rng.normal(0, 0.6 * np.linalg.norm(d), 3)            # off target
+            dist = float(np.linalg.norm(d))
+            d = (d / max(dist, 1e-20)).astype(np.float32)
+            max_dis = 0.0 if k % 3 == 0 else dist * float(rng.uniform(0.5, 1.6))
+            rays.append((origin, d, np.float32(max_dis), st, sf, target))
+        out.append(dict(name=name, scene=o, pos=np.ascontiguousarray(pos), tets=np.ascontiguousarray(t), nbr=np.ascontiguousarray(nb),
+                        xor=np.ascontiguousarray(xs), rays=rays, eps=1e-10))
+    return out

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -273,6 +273,21 @@ def test_cloth_boundary_force_hessian():
     got = np.asarray(got, np.float32)
     assert (np.abs(G[:, :3]).max(1) > 0).sum() > 20
     assert relmax(got[:, :3], G[:, :3]) < 1e-6 and relmax(got[:, 3:], G[:, 3:]) < 1e-6
+
+
+def test_tetrahedral_traversal_integer_exact():
+    """The oracle's tetrahedral_traverse_to against the reference's own TetMeshFEM::tetrahedralTraverseTo (TetMeshFEM.cpp:503-742 with
+    exitFaceSelection / projectTo2DCoordinates / originBarycentric2DTriangle from TetMeshFEM.h, MeshFrame2's CPArrayStatic / CircularArray
+    and CuMatrix::buildOrthonormalBasis, compiled into oracle/_ref: oracle/ref_shim/reftraverse.cu) on 800 rays through the
+    reference's teapot and a Kuhn beam: same answer (target reached or not) and the same number of tets traversed, ray by ray."""
+    for c in traverse_cases():
+        G = GOLD["traverse_" + c["name"]]
+        o = c["scene"]
+        assert G[:, 0].sum() > 100 and (G[:, 2] == 3).sum() > 50 and (G[:, 2] == 2).sum() > 20 and G[:, 1].max() > 20
+        assert (G[:, 2] != 1).all()                   # no static-stack overflow among the fixtures (the oracle's stack is unbounded)
+        for i, (org, d, md, st, sf, tg) in enumerate(c["rays"]):
+            ok, n = o.tet_traverse(0, org, d, md, st, sf, tg, c["eps"])
+            assert ok == bool(G[i, 0]) and n == G[i, 1], (c["name"], i, ok, n, G[i])
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
