@@ -58,6 +58,8 @@ def load_oracle():
         lib.oracle_get_rest_volumes.argtypes = [P, C.c_int, FP]
         lib.oracle_get_vertex_tet_csr.argtypes = [P, C.c_int, IP, IP, IP]
         lib.oracle_get_tet_topology.argtypes = [P, C.c_int, IP, IP, IP]
+        lib.oracle_get_surface_topology.argtypes = [P, C.c_int, IP, IP, IP, IP, C.POINTER(C.c_int64)]
+        lib.oracle_check_feasible_region.argtypes = [P, C.c_int, FP, C.c_int, C.c_int, C.c_float]
         lib.oracle_tet_traverse.argtypes = [P, C.c_int, FP, FP, C.c_float, C.c_int, C.c_int, C.c_int, C.c_float, IP]
         lib.oracle_set_brute_force.argtypes = [P, C.c_int]
         lib.oracle_vertex_material_force_hessian.argtypes = [P, C.c_int, C.c_int, FP, FP]
@@ -95,6 +97,8 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_check_feasible_region"):
+            lib.ref_check_feasible_region.argtypes = [C.c_int, FP, C.c_int, IP, IP, IP, C.c_int, IP, IP, FP, C.c_int, C.c_int, C.c_float]
         if hasattr(lib, "ref_tet_traverse"):
             lib.ref_tet_traverse.argtypes = [C.c_int, FP, C.c_int, IP, IP, IP, FP, FP, C.c_float, C.c_int, C.c_int, C.c_int, C.c_float, IP, IP]
         if hasattr(lib, "ref_cloth_vf_contact"):
@@ -187,6 +191,19 @@ class OracleScene(SceneBase):
         t = np.empty((nT, 4), np.int32); nb = np.empty((nT, 4), np.int32); x = np.empty(nT, np.int32)
         self._call("get_tet_topology", mesh, _ip(t), _ip(nb), _ip(x))
         return t, nb, x
+
+    def surface_topology(self, mesh):
+        """(neighbour face across each edge [nF,3], tet vertex -> surface vertex [nV], CSR offsets [nSV+1], neighbour tet-mesh vertex ids)"""
+        nV, nT, nSV, nSF = self.mesh_sizes(mesh)
+        n = C.c_int64()
+        self._call("get_surface_topology", mesh, None, None, None, None, C.byref(n))
+        f3 = np.empty((nSF, 3), np.int32); t2s = np.empty(nV, np.int32); off = np.empty(nSV + 1, np.int32); nb = np.empty(max(n.value, 1), np.int32)
+        self._call("get_surface_topology", mesh, _ip(f3), _ip(t2s), _ip(off), _ip(nb), C.byref(n))
+        return f3, t2s, off, nb[: n.value]
+
+    def check_feasible_region(self, mesh, p, face, point_type, eps):
+        q = _f32(p)
+        return bool(self._call("check_feasible_region", mesh, _fp(q), int(face), int(point_type), float(eps)))
 
     def tet_traverse(self, mesh, origin, direction, max_dis, start_tet, start_face, target_tet, eps):
         """tetrahedralTraverseTo: (reached, tets traversed)"""

@@ -202,6 +202,24 @@ int oracle_tet_traverse(void* h, int mesh, const float* origin3, const float* di
     if (numTraversed) *numTraversed = n;
     return ok ? 1 : 0;
 }
+// surface topology the feasible-region test reads: neighbour face across each edge [3 nF], tet vertex -> surface vertex [nV],
+// CSR of the neighbouring surface vertices (tet-mesh ids) of each surface vertex. nbrVerts == nullptr: only *nNbr is written
+int oracle_get_surface_topology(void* h, int mesh, int32_t* face3Nbr, int32_t* tetVertToSurf, int32_t* nbrOff, int32_t* nbrVerts, int64_t* nNbr) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    if (face3Nbr) std::memcpy(face3Nbr, m.surfFace3Nbr.data(), m.surfFace3Nbr.size() * 4);
+    if (tetVertToSurf) std::memcpy(tetVertToSurf, m.tetVertToSurf.data(), m.tetVertToSurf.size() * 4);
+    int64_t run = 0;
+    for (size_t sv = 0; sv < m.surfVertNbrSurfVerts.size(); sv++) {
+        if (nbrOff) nbrOff[sv] = (int32_t)run;
+        for (int v : m.surfVertNbrSurfVerts[sv]) { if (nbrVerts) nbrVerts[run] = v; run++; }
+    }
+    if (nbrOff) nbrOff[m.surfVertNbrSurfVerts.size()] = (int32_t)run;
+    if (nNbr) *nNbr = run;
+    return GAIA_OK;
+}
+int oracle_check_feasible_region(void* h, int mesh, const float* p3, int faceId, int type, float eps) {
+    return probe_feasible_region(((Scene*)h)->meshes[mesh], V3(p3[0], p3[1], p3[2]), faceId, type, eps) ? 1 : 0;
+}
 int oracle_enable_mesh(void* h, int mesh, int col, int solve) {
     Mesh& m = ((Scene*)h)->meshes[mesh];
     m.activeForCollision = col != 0; m.activeForMaterialSolve = solve != 0;

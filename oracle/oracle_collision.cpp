@@ -131,6 +131,8 @@ static bool check_feasible_region(V3 p, const Mesh& m, int faceId, int type, flo
     }
 }
 
+bool probe_feasible_region(const Mesh& m, V3 p, int faceId, int type, float eps) { return check_feasible_region(p, m, faceId, type, eps); }   // parity probe
+
 // ---------------------------------------------------------------- tetrahedral traversal
 static void build_orthonormal_basis(V3 n, V3& b1, V3& b2) {   // CuMatrix Geometry.h:183-206
     if (n.z < 0.f) {

@@ -112,6 +112,7 @@ void phase_solve_group(Scene& s, int g, bool applyFriction);
 void vertex_merit_energy_parts(const Scene& s, const Mesh& m, int iV, const V3& x, float& inertia, float& elastic);   // evaluateVertexMeritEnergy
 bool tetrahedral_traverse_to(const Mesh& m, V3 rayOrigin, V3 rayDir, float maxDis, int startTet, int startFace, int targetTet, float eps,
                              int* numTraversed);      // TetMeshFEM::tetrahedralTraverseTo (oracle_collision.cpp)
+bool probe_feasible_region(const Mesh& m, V3 p, int faceId, int type, float eps);   // DiscreteCollisionDetector::checkFeasibleRegion
 void phase_intermediate_cd(Scene& s);    // dcd (intermediate) + ccd + prepareCollisionData, every intermediateCollisionIterations
 void phase_end_substep(Scene& s);         // velocities
 void enable_models(Scene& s);

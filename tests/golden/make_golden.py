@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -127,6 +127,17 @@ def main():
                                       st, sf, tg, c["eps"], ip(n), ip(why))
             R[i] = (ok, n[0], why[0])
         out["traverse_" + c["name"]] = R
+    # ---- DiscreteCollisionDetector::checkFeasibleRegion (+ checkEdge / checkVertexFeasibleRegion): closest-point type, verdict
+    for c in feasible_region_cases():
+        R = np.zeros((len(c["pts"]), 2), np.int32)
+        for i, (f, q) in enumerate(c["pts"]):
+            tri = c["pos"][c["faces"][f]]
+            cp = np.zeros(3, np.float32); bary = np.zeros(3, np.float32)
+            typ = ref.ref_closest_point_triangle(fp(q), fp(tri[0]), fp(tri[1]), fp(tri[2]), fp(cp), fp(bary))
+            ok = ref.ref_check_feasible_region(len(c["pos"]), fp(c["pos"]), len(c["faces"]), ip(c["faces"]), ip(c["f3"]), ip(c["t2s"]), len(c["off"]) - 1,
+                                               ip(c["off"]), ip(c["nb"]), fp(q), f, typ, c["eps"])
+            R[i] = (typ, ok)
+        out["feasible_" + c["name"]] = R
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

@@ -337,3 +337,30 @@ def traverse_cases(seed=81, n_rays=400):
         out.append(dict(name=name, scene=o, pos=np.ascontiguousarray(pos), tets=np.ascontiguousarray(t), nbr=np.ascontiguousarray(nb),
                         xor=np.ascontiguousarray(xs), rays=rays, eps=1e-10))
     return out
+
+
+def feasible_region_cases(seed=91, n_pts=1500):
+    """Query points around the surfaces of the reference's teapot and a Kuhn beam (both deformed at random): near face
+    interiors, edges and corners, inside and outside, close and far - with the surface face they are tested against. The
+    closest-point type that selects the branch is computed by the caller with closestPointTriangle."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for c in traverse_cases(seed=seed + 1, n_rays=1):
+        o, pos = c["scene"], c["pos"]
+        faces = np.ascontiguousarray(o.surface_faces(0), np.int32)
+        f3, t2s, off, nb = o.surface_topology(0)
+        scale = float(np.linalg.norm(pos.max(0) - pos.min(0)))
+        pts = []
+        for k in range(n_pts):
+            f = int(rng.integers(len(faces)))
+            a, b, cc = pos[faces[f]]
+            mode = k % 3
+            w = rng.dirichlet([1.0, 1.0, 1.0]) if mode == 0 else (np.array([*rng.dirichlet([1.0, 1.0]), 0.0])[rng.permutation(3)] if mode == 1 else np.eye(3)[rng.integers(3)])
+            q = w[0] * a + w[1] * b + w[2] * cc
+            n = np.cross(b - a, cc - a); n /= max(np.linalg.norm(n), 1e-20)
+            edge = float(np.linalg.norm(b - a))
+            q = q + n * rng.normal(0, 0.7 * edge) + rng.normal(0, 0.35 * edge, 3)
+            pts.append((f, q.astype(np.float32)))
+        out.append(dict(name=c["name"], scene=o, pos=pos, faces=faces, f3=np.ascontiguousarray(f3), t2s=np.ascontiguousarray(t2s), off=np.ascontiguousarray(off),
+                        nb=np.ascontiguousarray(nb), pts=pts, eps=1e-2))
+    return out

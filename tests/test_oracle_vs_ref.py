@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -288,6 +288,21 @@ def test_tetrahedral_traversal_integer_exact():
         for i, (org, d, md, st, sf, tg) in enumerate(c["rays"]):
             ok, n = o.tet_traverse(0, org, d, md, st, sf, tg, c["eps"])
             assert ok == bool(G[i, 0]) and n == G[i, 1], (c["name"], i, ok, n, G[i])
+
+
+def test_feasible_region_verdicts_exact():
+    """The oracle's check_feasible_region against the reference's own DiscreteCollisionDetector::checkFeasibleRegion with
+    checkEdgeFeasibleRegion / checkVertexFeasibleRegion (DiscreteCollisionDetector.cpp:664-700, 709-815, compiled with the
+    vendored Embree math headers: oracle/ref_shim/reffeasible.cpp) on 3000 points around the reference's teapot and a Kuhn beam:
+    every closest-point type, both verdicts, identical point by point."""
+    for c in feasible_region_cases():
+        G = GOLD["feasible_" + c["name"]]
+        o = c["scene"]
+        for t in range(7):
+            assert (G[:, 0] == t).sum() > 50 and 0 < G[G[:, 0] == t, 1].sum()
+        assert (G[G[:, 0] != 6, 1] == 0).sum() > 500                      # many rejections outside the interior type
+        for i, (f, q) in enumerate(c["pts"]):
+            assert o.check_feasible_region(0, q, f, int(G[i, 0]), c["eps"]) == bool(G[i, 1]), (c["name"], i)
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
