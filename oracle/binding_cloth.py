@@ -4,6 +4,8 @@ import ctypes as C
 
 import numpy as np
 
+IPT = C.POINTER(C.c_int32)
+
 from gaia_b200.capi import _f32, _fp
 from gaia_b200.cloth import ClothPhysicsParams, ClothSceneBase, bind_cloth_api, default_cloth_physics_params
 from .binding import load_oracle, use_speed_build  # noqa: F401
@@ -15,13 +17,15 @@ def _lib():
     global _bound
     lib = load_oracle()
     if not _bound:
-        P, FP = C.c_void_p, C.POINTER(C.c_float)
+        P, FP, IP = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
         lib.oracle_cloth_create.argtypes = [C.POINTER(ClothPhysicsParams), C.c_int]
         lib.oracle_cloth_create.restype = C.c_void_p
         lib.oracle_cloth_destroy.argtypes = [P]; lib.oracle_cloth_destroy.restype = None
         lib.oracle_cloth_num_threads.argtypes = [P]
         lib.oracle_cloth_set_brute_force.argtypes = [P, C.c_int]; lib.oracle_cloth_set_brute_force.restype = None
         lib.oracle_cloth_set_prev_positions.argtypes = [P, C.c_int, FP]
+        lib.oracle_cloth_get_topology.argtypes = [P, C.c_int, IP, IP, IP, C.POINTER(C.c_int64)]
+        lib.oracle_cloth_check_feasible_region.argtypes = [P, C.c_int, FP, C.c_int, C.c_int, C.c_float]
         lib.oracle_cloth_probe_vf.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_vf.restype = C.c_float
         lib.oracle_cloth_probe_ee.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_ee.restype = C.c_float
         lib.oracle_cloth_probe_boundary.argtypes = [P, C.c_int, C.c_int, FP, FP]; lib.oracle_cloth_probe_boundary.restype = None
@@ -65,6 +69,19 @@ class OracleClothScene(ClothSceneBase):
         f = np.empty(3, np.float32); h = np.empty(9, np.float32)
         self._lib.oracle_cloth_vertex_force_hessian(self.h, mesh, v, _fp(f), _fp(h))
         return f, h.reshape(3, 3).T.copy()
+
+    def topology(self, mesh):
+        """(edge id of each face edge [nF,3], CSR offsets [nV+1], neighbour vertices)"""
+        nV, nF, nE = self.mesh_sizes(mesh)
+        n = C.c_int64()
+        self._lib.oracle_cloth_get_topology(self.h, mesh, None, None, None, C.byref(n))
+        f3 = np.empty((nF, 3), np.int32); off = np.empty(nV + 1, np.int32); nb = np.empty(max(n.value, 1), np.int32)
+        self._lib.oracle_cloth_get_topology(self.h, mesh, f3.ctypes.data_as(IPT), off.ctypes.data_as(IPT), nb.ctypes.data_as(IPT), C.byref(n))
+        return f3, off, nb[: n.value]
+
+    def check_feasible_region(self, mesh, p, face, point_type, eps):
+        q = _f32(p)
+        return bool(self._lib.oracle_cloth_check_feasible_region(self.h, mesh, _fp(q), int(face), int(point_type), float(eps)))
 
     def probe_vf(self, v_mesh, v, f_mesh, f, order):
         """one vertex-face contact in isolation (closest point recomputed, friction on): (distance, force, H[r, c])"""

@@ -184,6 +184,18 @@ float oracle_cloth_probe_ee(void* h, int m1, int e1, int m2, int e2, int order, 
 void oracle_cloth_probe_boundary(void* h, int mesh, int v, float* f3, float* h9) {
     V3 F; M3 H; cloth_probe_boundary(*(ClothScene*)h, mesh, v, F, H); out_fh(F, H, f3, h9);
 }
+// topology the cloth feasible-region test reads: edge id of each face edge [3 nF], CSR of each vertex's neighbour vertices
+int oracle_cloth_get_topology(void* h, int mesh, int32_t* face3Edges, int32_t* vNbrOff, int32_t* vNbrV, int64_t* nNbr) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    if (face3Edges) std::memcpy(face3Edges, m.face3Edges.data(), m.face3Edges.size() * 4);
+    if (vNbrOff) std::memcpy(vNbrOff, m.vNbrVOff.data(), m.vNbrVOff.size() * 4);
+    if (vNbrV) std::memcpy(vNbrV, m.vNbrV.data(), m.vNbrV.size() * 4);
+    if (nNbr) *nNbr = (int64_t)m.vNbrV.size();
+    return GAIA_OK;
+}
+int oracle_cloth_check_feasible_region(void* h, int mesh, const float* p3, int faceId, int type, float eps) {
+    return cloth_probe_feasible_region(((ClothScene*)h)->meshes[mesh], V3(p3[0], p3[1], p3[2]), faceId, type, eps) ? 1 : 0;
+}
 float oracle_cloth_elastic_energy(void* h, int mesh) { ClothScene* s = (ClothScene*)h; return cloth_elastic_energy(*s, s->meshes[mesh]); }
 void oracle_cloth_contact_repulsion(void* h, float dis, float* dEdD, float* d2E) { cloth_contact_repulsion(*(ClothScene*)h, dis, *dEdD, *d2E); }
 int oracle_cloth_get_dminv(void* h, int mesh, float* out4, float* area) {

@@ -60,6 +60,8 @@ static bool feasible_region(V3 p, const TriMesh& m, int faceId, int type, float 
     }
 }
 
+bool cloth_probe_feasible_region(const TriMesh& m, V3 p, int faceId, int type, float eps) { return feasible_region(p, m, faceId, type, eps); }   // parity probe
+
 // get_closest_points_between_segments (M/CollisionDetector/CollisionGeometry.h:160-267; Eberly / Godot)
 void closest_points_segments(V3 p0, V3 p1, V3 q0, V3 q1, V3& ps, V3& qt, float& s, float& t) {
     const V3 p = p1 - p0, q = q1 - q0, r = p0 - q0;

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -138,6 +138,17 @@ def main():
                                                ip(c["off"]), ip(c["nb"]), fp(q), f, typ, c["eps"])
             R[i] = (typ, ok)
         out["feasible_" + c["name"]] = R
+    # ---- cloth: checkFeasibleRegion (TriMeshFEM) + checkEdge / checkVertexFeasibleRegion
+    c = cloth_feasible_region_cases()
+    R = np.zeros((len(c["pts"]), 2), np.int32)
+    for i, (f, q) in enumerate(c["pts"]):
+        tri = c["pos"][c["faces"][f]]
+        cp = np.zeros(3, np.float32); bary = np.zeros(3, np.float32)
+        typ = ref.ref_closest_point_triangle(fp(q), fp(tri[0]), fp(tri[1]), fp(tri[2]), fp(cp), fp(bary))
+        ok = ref.ref_cloth_check_feasible_region(len(c["pos"]), fp(c["pos"]), len(c["faces"]), ip(c["faces"]), ip(c["f3"]), len(c["edges"]), ip(c["edges"]),
+                                                 ip(c["off"]), ip(c["nb"]), fp(q), f, typ, c["eps"])
+        R[i] = (typ, ok)
+    out["cloth_feasible"] = R
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

@@ -364,3 +364,26 @@ def feasible_region_cases(seed=91, n_pts=1500):
         out.append(dict(name=c["name"], scene=o, pos=pos, faces=faces, f3=np.ascontiguousarray(f3), t2s=np.ascontiguousarray(t2s), off=np.ascontiguousarray(off),
                         nb=np.ascontiguousarray(nb), pts=pts, eps=1e-2))
     return out
+
+
+def cloth_feasible_region_cases(seed=95, n_pts=1500):
+    """Query points around a wrinkled cloth (open boundary: boundary edges and corners included), with the face they are
+    tested against; the closest-point type comes from closestPointTriangle."""
+    rng = np.random.default_rng(seed)
+    c = cloth_material_case(n=9, seed=seed + 1)
+    o, pos = c["scene"], c["pos"]
+    faces = c["faces"]
+    f3, off, nb = o.topology(0)
+    pts = []
+    for k in range(n_pts):
+        f = int(rng.integers(len(faces)))
+        a, b, cc = pos[faces[f]]
+        mode = k % 3
+        w = rng.dirichlet([1.0, 1.0, 1.0]) if mode == 0 else (np.array([*rng.dirichlet([1.0, 1.0]), 0.0])[rng.permutation(3)] if mode == 1 else np.eye(3)[rng.integers(3)])
+        q = w[0] * a + w[1] * b + w[2] * cc
+        n = np.cross(b - a, cc - a); n /= max(np.linalg.norm(n), 1e-20)
+        edge = float(np.linalg.norm(b - a))
+        q = q + n * rng.normal(0, 0.5 * edge) + rng.normal(0, 0.3 * edge, 3)
+        pts.append((f, q.astype(np.float32)))
+    return dict(scene=o, pos=pos, faces=faces, f3=np.ascontiguousarray(f3), edges=c["edges"], off=np.ascontiguousarray(off), nb=np.ascontiguousarray(nb),
+                pts=pts, eps=1e-3)

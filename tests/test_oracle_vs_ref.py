@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -303,6 +303,20 @@ def test_feasible_region_verdicts_exact():
         assert (G[G[:, 0] != 6, 1] == 0).sum() > 500                      # many rejections outside the interior type
         for i, (f, q) in enumerate(c["pts"]):
             assert o.check_feasible_region(0, q, f, int(G[i, 0]), c["eps"]) == bool(G[i, 1]), (c["name"], i)
+
+
+def test_cloth_feasible_region_verdicts_exact():
+    """The cloth oracle's feasible_region against the reference's own checkFeasibleRegion (TriMeshFEM) with checkEdgeFeasibleRegion /
+    checkVertexFeasibleRegion (TriMeshCollisionGeometry.cpp:7-42, 91-186; oracle/ref_shim/refclothfeasible.cpp) on 1500 points
+    around a wrinkled open cloth: every closest-point type incl. boundary edges and corners, verdicts identical."""
+    c = cloth_feasible_region_cases()
+    G = GOLD["cloth_feasible"]
+    o = c["scene"]
+    for t in range(7):
+        assert (G[:, 0] == t).sum() > 50 and 0 < G[G[:, 0] == t, 1].sum()
+    assert (G[G[:, 0] != 6, 1] == 0).sum() > 500
+    for i, (f, q) in enumerate(c["pts"]):
+        assert o.check_feasible_region(0, q, f, int(G[i, 0]), c["eps"]) == bool(G[i, 1]), i
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
