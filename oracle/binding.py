@@ -97,6 +97,8 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_step_sequence"):
+            lib.ref_step_sequence.argtypes = [C.c_int, FP, FP, FP, C.c_int, IP, C.c_int, FP, FP, FP, FP]; lib.ref_step_sequence.restype = None
         if hasattr(lib, "ref_cloth_check_feasible_region"):
             lib.ref_cloth_check_feasible_region.argtypes = [C.c_int, FP, C.c_int, IP, IP, C.c_int, IP, IP, IP, FP, C.c_int, C.c_int, C.c_float]
         if hasattr(lib, "ref_check_feasible_region"):

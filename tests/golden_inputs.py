@@ -387,3 +387,54 @@ def cloth_feasible_region_cases(seed=95, n_pts=1500):
         pts.append((f, q.astype(np.float32)))
     return dict(scene=o, pos=pos, faces=faces, f3=np.ascontiguousarray(f3), edges=c["edges"], off=np.ascontiguousarray(off), nb=np.ascontiguousarray(nb),
                 pts=pts, eps=1e-3)
+
+
+def step_sequence_cases(seed=101, n_steps=4):
+    """Initial step + velocity update over four substeps for every initial-guess type the path supports, with velocity damping,
+    a velocity cap inside / outside a no-gravity zone and fixed points; the positions "after the iterations" of each substep
+    are given (the initial guess moved at random), so that the velocity history - which types 2, 4 and 6 read - evolves."""
+    import ctypes
+    powf = ctypes.CDLL("libm.so.6").powf
+    powf.restype = ctypes.c_float; powf.argtypes = [ctypes.c_float, ctypes.c_float]
+    rng = np.random.default_rng(seed)
+    verts, tets = meshio.kuhn_beam(3, 2, 2, h=0.3, origin=(0, 1.0, 0))
+    colors = meshio.kuhn_coloring(3, 2, 2)
+    fixed = np.array([0, 5, 11], np.int32)
+    cases = []
+    for init_type, kw in ((0, {}), (1, dict(exponentialVelDamping=0.5, constantVelDamping=0.3)), (2, dict(maxVelocityMagnitude=1.5, hasNoGravZone=1, noGravZoneThreshold=1.3)),
+                          (3, dict(constantVelDamping=4.0)), (4, dict(initRatio_g=0.6, exponentialVelDamping=0.8)), (6, dict(maxVelocityMagnitude=2.0, hasNoGravZone=1, noGravZoneThreshold=0.5))):
+        cases.append((init_type, kw))
+
+    def make(init_type, kw):
+        from oracle.binding import OracleScene
+        phys = capi.default_physics_params(numSubsteps=3, iterations=1, gravity=[0.4, -9.0, 0.2], worldBoundsMin=[-50, -50, -50], worldBoundsMax=[50, 50, 50])
+        obj = capi.default_object_params(initializationType=init_type, density=40, **kw)
+        o = OracleScene(phys, capi.default_collision_params(allowDCD=0, allowCCD=0), threads=1)
+        o.add_tet_mesh(verts, tets, obj, colors, fixed)
+        o.finalize()
+        dt = np.float32(phys.timeStep) / np.float32(3)
+        ed = float(powf(float(np.float32(kw.get("exponentialVelDamping", 1.0))), float(dt)))
+        cd = float(np.float32(kw.get("constantVelDamping", 0.0)) * dt)
+        params12 = np.array([dt, 0.4, -9.0, 0.2, 1.0, init_type, kw.get("initRatio_g", obj.initRatio_g), kw.get("maxVelocityMagnitude", obj.maxVelocityMagnitude),
+                             kw.get("hasNoGravZone", 0), kw.get("noGravZoneThreshold", 0.0), ed, cd], np.float32)
+        return o, params12
+    n = len(verts)
+    pos0 = (verts + rng.normal(0, 0.01, verts.shape)).astype(np.float32)
+    vel0 = rng.normal(0, 1.0, verts.shape).astype(np.float32)
+    noise = rng.normal(0, 0.01, (n_steps, n, 3)).astype(np.float32)
+    return dict(cases=cases, make=make, pos0=pos0, vel0=vel0, noise=noise, fixed=fixed, n_steps=n_steps)
+
+
+def run_oracle_step_sequence(o, c):
+    """the oracle through the same sequence: (positions after the initial step, inertia, velocities after the update, solved) per substep"""
+    o.set_state(0, c["pos0"], c["vel0"])
+    init, inert, vel, solved = [], [], [], []
+    for s in range(c["n_steps"]):
+        o.phase_begin_substep()
+        init.append(o.positions(0)); inert.append(o.inertia(0))
+        sol = (init[-1] + c["noise"][s]).astype(np.float32)
+        sol[c["fixed"]] = init[-1][c["fixed"]]
+        o.set_state(0, sol, None)
+        o.phase_end_substep()
+        vel.append(o.velocities(0)); solved.append(sol)
+    return np.array(init), np.array(inert), np.array(vel), np.array(solved)

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -317,6 +317,24 @@ def test_cloth_feasible_region_verdicts_exact():
     assert (G[G[:, 0] != 6, 1] == 0).sum() > 500
     for i, (f, q) in enumerate(c["pts"]):
         assert o.check_feasible_region(0, q, f, int(G[i, 0]), c["eps"]) == bool(G[i, 1]), i
+
+
+def test_initial_step_and_velocity_update_bit_exact():
+    """apply_initial_step / update_velocities of the oracle against the reference's own VBDBaseTetMesh::applyInitialStep
+    (computeInertia + forwardStep, VBD_BaseMaterial.h:201-221, 244-259; .cpp:7-132) and VBDPhysics::updateVelocities with
+    dampVelocities (VBDPhysics.cpp:2486-2561), compiled into oracle/_ref (oracle/ref_shim/refstep.cpp): four substeps for each
+    initial-guess type 0-4 and 6, with exponential / constant damping, the velocity cap in and out of the no-gravity zone and
+    fixed points. Elementwise float arithmetic: bit-exact (initial guess, inertia, velocities)."""
+    c = step_sequence_cases()
+    for init_type, kw in c["cases"]:
+        o, _ = c["make"](init_type, kw)
+        init, inert, vel, solved = run_oracle_step_sequence(o, c)
+        G = GOLD[f"step_init{init_type}"]
+        assert np.array_equal(solved, GOLD[f"step_solved{init_type}"])
+        assert np.array_equal(init, G[0]) and np.array_equal(inert, G[1]) and np.array_equal(vel, G[2]), (init_type, kw)
+        assert np.abs(G[2]).max() > 1.0 and np.abs(G[0][-1] - c["pos0"]).max() > 1e-3
+    # the guesses really differ between the types (the history-dependent ones from the second substep on)
+    assert not np.array_equal(GOLD["step_init0"][0][1], GOLD["step_init2"][0][1]) and not np.array_equal(GOLD["step_init4"][0][1], GOLD["step_init6"][0][1])
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
