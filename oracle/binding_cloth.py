@@ -26,6 +26,10 @@ def _lib():
         lib.oracle_cloth_set_prev_positions.argtypes = [P, C.c_int, FP]
         lib.oracle_cloth_get_topology.argtypes = [P, C.c_int, IP, IP, IP, C.POINTER(C.c_int64)]
         lib.oracle_cloth_check_feasible_region.argtypes = [P, C.c_int, FP, C.c_int, C.c_int, C.c_float]
+        lib.oracle_cloth_probe_initial_step.argtypes = [P]; lib.oracle_cloth_probe_update_velocity.argtypes = [P]
+        lib.oracle_cloth_probe_truncate.argtypes = [P, C.c_int, C.c_int, FP]
+        lib.oracle_cloth_get_inertia.argtypes = [P, C.c_int, FP]
+        lib.oracle_cloth_set_bounds.argtypes = [P, C.c_int, FP, FP]
         lib.oracle_cloth_probe_vf.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_vf.restype = C.c_float
         lib.oracle_cloth_probe_ee.argtypes = [P] + [C.c_int] * 5 + [FP, FP]; lib.oracle_cloth_probe_ee.restype = C.c_float
         lib.oracle_cloth_probe_boundary.argtypes = [P, C.c_int, C.c_int, FP, FP]; lib.oracle_cloth_probe_boundary.restype = None
@@ -82,6 +86,26 @@ class OracleClothScene(ClothSceneBase):
     def check_feasible_region(self, mesh, p, face, point_type, eps):
         q = _f32(p)
         return bool(self._lib.oracle_cloth_check_feasible_region(self.h, mesh, _fp(q), int(face), int(point_type), float(eps)))
+
+    def probe_initial_step(self):
+        self._lib.oracle_cloth_probe_initial_step(self.h)
+
+    def probe_update_velocity(self):
+        self._lib.oracle_cloth_probe_update_velocity(self.h)
+
+    def probe_truncate(self, mesh, v, new_pos):
+        p = _f32(new_pos).copy()
+        t = self._lib.oracle_cloth_probe_truncate(self.h, int(mesh), int(v), _fp(p))
+        return bool(t), p
+
+    def inertia(self, mesh):
+        a = np.empty((self.mesh_sizes(mesh)[0], 3), np.float32)
+        self._lib.oracle_cloth_get_inertia(self.h, int(mesh), _fp(a))
+        return a
+
+    def set_bounds(self, mesh, bounds, pos_at_cd):
+        b = _f32(bounds); p = _f32(pos_at_cd)
+        self._lib.oracle_cloth_set_bounds(self.h, int(mesh), _fp(b), _fp(p))
 
     def probe_vf(self, v_mesh, v, f_mesh, f, order):
         """one vertex-face contact in isolation (closest point recomputed, friction on): (distance, force, H[r, c])"""

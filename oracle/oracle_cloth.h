@@ -125,6 +125,9 @@ void cloth_contact_repulsion(const ClothScene& s, float dis, float& dEdD, float&
 float cloth_probe_vf(const ClothScene& s, int vMesh, int v, int fMesh, int f, int vertexOrder, V3& force, M3& hessian);
 float cloth_probe_ee(const ClothScene& s, int m1, int e1, int m2, int e2, int vertexOrder, V3& force, M3& hessian);
 bool cloth_probe_feasible_region(const TriMesh& m, V3 p, int faceId, int type, float eps);
+void cloth_probe_initial_step(ClothScene& s);
+void cloth_probe_update_velocity(ClothScene& s);
+bool cloth_probe_truncate(const ClothScene& s, int mesh, int v, V3& newPos);
 void cloth_probe_boundary(const ClothScene& s, int mesh, int v, V3& force, M3& hessian);
 V3 closest_point_triangle(V3 p, V3 a, V3 b, V3 c, V3& bary, int& type);   // oracle_collision.cpp
 void closest_points_segments(V3 p0, V3 p1, V3 q0, V3 q1, V3& ps, V3& qt, float& s, float& t);   // oracle_cloth_contact.cpp

@@ -196,6 +196,22 @@ int oracle_cloth_get_topology(void* h, int mesh, int32_t* face3Edges, int32_t* v
 int oracle_cloth_check_feasible_region(void* h, int mesh, const float* p3, int faceId, int type, float eps) {
     return cloth_probe_feasible_region(((ClothScene*)h)->meshes[mesh], V3(p3[0], p3[1], p3[2]), faceId, type, eps) ? 1 : 0;
 }
+int oracle_cloth_probe_initial_step(void* h) { cloth_probe_initial_step(*(ClothScene*)h); return GAIA_OK; }
+int oracle_cloth_probe_update_velocity(void* h) { cloth_probe_update_velocity(*(ClothScene*)h); return GAIA_OK; }
+int oracle_cloth_probe_truncate(void* h, int mesh, int v, float* newPos3) {
+    V3 p(newPos3[0], newPos3[1], newPos3[2]);
+    const bool t = cloth_probe_truncate(*(ClothScene*)h, mesh, v, p);
+    newPos3[0] = p.x; newPos3[1] = p.y; newPos3[2] = p.z;
+    return t ? 1 : 0;
+}
+int oracle_cloth_get_inertia(void* h, int mesh, float* xyz) { copy_out(((ClothScene*)h)->meshes[mesh].inertia, xyz); return GAIA_OK; }
+// (tests) conservative bounds and the positions of the last detection, as a detection would have left them
+int oracle_cloth_set_bounds(void* h, int mesh, const float* bounds, const float* posAtCD) {
+    TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    if (bounds) { m.bounds.resize(m.nV); std::memcpy(m.bounds.data(), bounds, m.nV * sizeof(float)); }
+    if (posAtCD) { m.posAtCD.resize(m.nV); std::memcpy(m.posAtCD.data(), posAtCD, m.nV * sizeof(V3)); }
+    return GAIA_OK;
+}
 float oracle_cloth_elastic_energy(void* h, int mesh) { ClothScene* s = (ClothScene*)h; return cloth_elastic_energy(*s, s->meshes[mesh]); }
 void oracle_cloth_contact_repulsion(void* h, float dis, float* dEdD, float* d2E) { cloth_contact_repulsion(*(ClothScene*)h, dis, *dEdD, *d2E); }
 int oracle_cloth_get_dminv(void* h, int mesh, float* out4, float* area) {

@@ -531,6 +531,11 @@ static void update_velocity(ClothScene& s) {
     }
 }
 
+// parity probes (tests/test_oracle_vs_ref.py): the pieces of a substep around the solver, one at a time
+void cloth_probe_initial_step(ClothScene& s) { for (int i = 0; i < s.numSim; i++) apply_initial_step(s, s.meshes[i]); }
+void cloth_probe_update_velocity(ClothScene& s) { update_velocity(s); }
+bool cloth_probe_truncate(const ClothScene& s, int mesh, int v, V3& newPos) { return truncate_to_bound(s.meshes[mesh], v, newPos); }
+
 void cloth_run_substeps(ClothScene& s, int nSubsteps) {
     for (s.substep = 0; s.substep < nSubsteps; s.substep++) {
         s.curTime += s.dt;

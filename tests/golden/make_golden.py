@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -158,6 +158,19 @@ def main():
         a = np.zeros((c["n_steps"], n, 3), np.float32); b = np.zeros_like(a); v = np.zeros_like(a)
         ref.ref_step_sequence(n, fp(c["pos0"]), fp(c["vel0"]), fp(params12), len(c["fixed"]), ip(c["fixed"]), c["n_steps"], fp(solved), fp(a), fp(b), fp(v))
         out[f"step_init{init_type}"] = np.stack([a, b, v]); out[f"step_solved{init_type}"] = solved
+    # ---- cloth: VBDBaseTriMesh::applyInitialStep (forwardStep_intertia), VBDClothSimulationFramework::updateVelocity, ::applyConservativeBoundTruncation
+    c = cloth_step_sequence_cases()
+    for init_type, kw in c["cases"]:
+        o, params12 = c["make"](init_type, kw)
+        solved = np.ascontiguousarray(run_cloth_oracle_step_sequence(o, c)[3])
+        n = len(c["pos0"])
+        a = np.zeros((c["n_steps"], n, 3), np.float32); b = np.zeros_like(a); v = np.zeros_like(a)
+        ref.ref_cloth_step_sequence(n, fp(c["pos0"]), fp(c["vel0"]), fp(params12), len(c["fixed"]), ip(c["fixed"]), fp(c["bounds"]), c["n_steps"], fp(solved),
+                                    fp(a), fp(b), fp(v))
+        out[f"cloth_step_init{init_type}"] = np.stack([a, b, v]); out[f"cloth_step_solved{init_type}"] = solved
+    tp = np.ascontiguousarray(c["trunc_pos"].copy()); tf = np.zeros(len(tp), np.int32)
+    ref.ref_cloth_truncate(len(c["pos0"]), fp(c["pos0"]), fp(c["bounds"]), len(tp), ip(c["trunc_verts"]), fp(tp), ip(tf))
+    out["cloth_truncate_pos"] = tp; out["cloth_truncate_flag"] = tf
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

@@ -438,3 +438,51 @@ def run_oracle_step_sequence(o, c):
         o.phase_end_substep()
         vel.append(o.velocities(0)); solved.append(sol)
     return np.array(init), np.array(inert), np.array(vel), np.array(solved)
+
+
+def cloth_step_sequence_cases(seed=111, n_steps=4):
+    """Cloth initial step + velocity update over four substeps for every initial-guess type (0 inertia, 1 adaptive, 2 previous
+    position, 3 inertia clipped to the conservative bound), with damping, the velocity cap / no-gravity zone and fixed points,
+    plus candidate positions for the conservative-bound truncation."""
+    from gaia_b200 import cloth
+    rng = np.random.default_rng(seed)
+    n = 5
+    verts, faces = cloth.grid_cloth(n, size=1.0, origin=(0.0, 1.0, 0.0))
+    fixed = np.array([0, 4], np.int32)
+    cases = [(0, {}), (1, dict(exponentialVelDamping=0.9, constantVelDamping=0.05)), (2, dict(maxVelocityMagnitude=1.0, hasNoGravZone=1, noGravZoneThreshold=-0.3)),
+             (3, dict(constantVelDamping=0.2))]
+
+    def make(init_type, kw):
+        from oracle.binding_cloth import OracleClothScene
+        phys = cloth.default_cloth_physics_params(numSubsteps=3, iterations=1, handleCollision=1, gravity=[0.3, -9.0, 0.1])
+        obj = cloth.default_cloth_object_params(initializationType=init_type, **kw)
+        o = OracleClothScene(phys, threads=1)
+        o.add_tri_mesh(verts, faces, obj, cloth.grid_cloth_coloring(n), fixed=fixed)
+        o.finalize()
+        dt = np.float32(phys.timeStep) / np.float32(3)
+        params12 = np.array([dt, 0.3, -9.0, 0.1, 1.0, 1.0, init_type, kw.get("maxVelocityMagnitude", obj.maxVelocityMagnitude), kw.get("hasNoGravZone", 0),
+                             kw.get("noGravZoneThreshold", 0.0), kw.get("exponentialVelDamping", 1.0), kw.get("constantVelDamping", 0.0)], np.float32)
+        return o, params12
+    nV = len(verts)
+    pos0 = (verts + rng.normal(0, 0.01, verts.shape)).astype(np.float32)
+    vel0 = rng.normal(0, 0.8, verts.shape).astype(np.float32)
+    noise = rng.normal(0, 0.01, (n_steps, nV, 3)).astype(np.float32)
+    bounds = rng.uniform(0.002, 0.08, nV).astype(np.float32)          # some smaller than a substep's inertia step, some larger
+    trunc_verts = rng.integers(0, nV, 200).astype(np.int32)
+    trunc_pos = (pos0[trunc_verts] + rng.normal(0, 0.04, (200, 3))).astype(np.float32)
+    return dict(cases=cases, make=make, pos0=pos0, vel0=vel0, noise=noise, fixed=fixed, n_steps=n_steps, bounds=bounds, trunc_verts=trunc_verts, trunc_pos=trunc_pos)
+
+
+def run_cloth_oracle_step_sequence(o, c):
+    o.set_state(0, c["pos0"], c["vel0"])
+    o.set_bounds(0, c["bounds"], c["pos0"])
+    init, inert, vel, solved = [], [], [], []
+    for s in range(c["n_steps"]):
+        o.probe_initial_step()
+        init.append(o.positions(0)); inert.append(o.inertia(0))
+        sol = (init[-1] + c["noise"][s]).astype(np.float32)
+        sol[c["fixed"]] = init[-1][c["fixed"]]
+        o.set_state(0, sol, None)
+        o.probe_update_velocity()
+        vel.append(o.velocities(0)); solved.append(sol)
+    return np.array(init), np.array(inert), np.array(vel), np.array(solved)

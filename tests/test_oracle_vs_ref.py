@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -335,6 +335,29 @@ def test_initial_step_and_velocity_update_bit_exact():
         assert np.abs(G[2]).max() > 1.0 and np.abs(G[0][-1] - c["pos0"]).max() > 1e-3
     # the guesses really differ between the types (the history-dependent ones from the second substep on)
     assert not np.array_equal(GOLD["step_init0"][0][1], GOLD["step_init2"][0][1]) and not np.array_equal(GOLD["step_init4"][0][1], GOLD["step_init6"][0][1])
+
+
+def test_cloth_initial_step_velocity_update_and_truncation_bit_exact():
+    """The cloth oracle's apply_initial_step / update_velocity / truncate_to_bound against the reference's own
+    VBDBaseTriMesh::applyInitialStep + ::forwardStep_intertia (VBDBaseTriMesh.cpp:58-178), VBDClothSimulationFramework::updateVelocity
+    (VBDClothPhysics.cpp:2318-2359) and ::applyConservativeBoundTruncation (:1223-1246), compiled into oracle/_ref
+    (oracle/ref_shim/refclothstep.cpp): four substeps per initial-guess type 0-3 with damping, velocity cap, fixed points and
+    conservative bounds, and 200 truncation candidates. Elementwise float arithmetic: bit-exact."""
+    c = cloth_step_sequence_cases()
+    for init_type, kw in c["cases"]:
+        o, _ = c["make"](init_type, kw)
+        init, inert, vel, solved = run_cloth_oracle_step_sequence(o, c)
+        G = GOLD[f"cloth_step_init{init_type}"]
+        assert np.array_equal(solved, GOLD[f"cloth_step_solved{init_type}"])
+        assert np.array_equal(init, G[0]) and np.array_equal(inert, G[1]) and np.array_equal(vel, G[2]), (init_type, kw)
+    assert not np.array_equal(GOLD["cloth_step_init0"][0][1], GOLD["cloth_step_init3"][0][1])      # the bound clips type 3's guess
+    o, _ = c["make"](0, {})
+    o.set_state(0, c["pos0"], None); o.set_bounds(0, c["bounds"], c["pos0"])
+    flags = GOLD["cloth_truncate_flag"]
+    assert 50 < flags.sum() < 190
+    for i, (v, p) in enumerate(zip(c["trunc_verts"], c["trunc_pos"])):
+        t, q = o.probe_truncate(0, int(v), p)
+        assert t == bool(flags[i]) and np.array_equal(q, GOLD["cloth_truncate_pos"][i]), i
 
 
 def test_golden_file_matches_a_fresh_run_of_the_reference():
