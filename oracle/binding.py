@@ -97,6 +97,8 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_boundary_cpu"):
+            lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
         if hasattr(lib, "ref_cloth_step_sequence"):
             lib.ref_cloth_step_sequence.argtypes = [C.c_int, FP, FP, FP, C.c_int, IP, FP, C.c_int, FP, FP, FP, FP]; lib.ref_cloth_step_sequence.restype = None
             lib.ref_cloth_truncate.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, IP]; lib.ref_cloth_truncate.restype = None

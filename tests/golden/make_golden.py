@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -171,6 +171,15 @@ def main():
     tp = np.ascontiguousarray(c["trunc_pos"].copy()); tf = np.zeros(len(tp), np.int32)
     ref.ref_cloth_truncate(len(c["pos0"]), fp(c["pos0"]), fp(c["bounds"]), len(tp), ip(c["trunc_verts"]), fp(tp), ip(tf))
     out["cloth_truncate_pos"] = tp; out["cloth_truncate_flag"] = tf
+    # ---- VBDPhysics::accumlateBoundaryForceAndHessian, CPU semantics (friction per violated axis), with and without friction
+    bc = boundary_cases_cpu()
+    B = np.zeros((2, len(bc["p"]), 12), np.float32)
+    for fr in (0, 1):
+        for i in range(len(bc["p"])):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            ref.ref_boundary_cpu(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bc["mn"]), fp(bc["mx"]), bc["kB"], bc["muB"], bc["epsVB"], bc["dt"], fr, fp(f), fp(h))
+            B[fr, i] = np.concatenate([f, h])
+    out["boundary_cpu"] = B
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

@@ -486,3 +486,18 @@ def run_cloth_oracle_step_sequence(o, c):
         o.probe_update_velocity()
         vel.append(o.velocities(0)); solved.append(sol)
     return np.array(init), np.array(inert), np.array(vel), np.array(solved)
+
+
+def boundary_cases_cpu(n=120, seed=35):
+    """World-box cases for the CPU rule (penalty + friction per violated axis): none, one, two and all three axes violated, on
+    either side, with displacements below and above epsU."""
+    rng = np.random.default_rng(seed)
+    mn = np.array([-2.0, 0.0, -3.0], np.float32); mx = np.array([2.0, 5.0, 3.0], np.float32)
+    p = rng.uniform(mn + 0.1, mx - 0.1, (n, 3)).astype(np.float32)
+    for i in range(n):
+        for d in range(3):
+            if (i >> d) & 1:
+                p[i, d] = (mn[d] - rng.uniform(1e-3, 0.2)) if rng.integers(2) else (mx[d] + rng.uniform(1e-3, 0.2))
+    scale = np.where(np.arange(n)[:, None] % 4 == 0, 1e-4, 0.03)
+    pPrev = (p + rng.normal(0, 1, p.shape) * scale).astype(np.float32)
+    return dict(p=np.ascontiguousarray(p), pPrev=np.ascontiguousarray(pPrev), mn=mn, mx=mx, kB=1e5, muB=0.3, epsVB=1.0, dt=1.0 / 240)

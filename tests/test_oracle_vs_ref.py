@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from golden_inputs import (cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)
 from oracle.binding import load_oracle, load_ref, ref_available
 
@@ -154,6 +154,27 @@ def test_boundary_force_hessian():
         else:
             assert np.abs(f).max() == 0
     assert nz >= 30
+
+
+def test_boundary_force_hessian_cpu_semantics():
+    """The rule the product implements - penalty AND friction for every violated axis - against the reference's own CPU function
+    VBDPhysics::accumlateBoundaryForceAndHessian with computeVertexFriction (VBDPhysics.cpp:2821-2954, 2563-2592; oracle/ref_shim/
+    refboundarycpu.cpp): 120 points with 0-3 violated axes, friction off and on. 1e-6 relative to the largest entry."""
+    lib = load_oracle()
+    bc = boundary_cases_cpu()
+    G = GOLD["boundary_cpu"]
+    multi = 0
+    for fr in (0, 1):
+        got = np.zeros_like(G[fr])
+        for i in range(len(bc["p"])):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            lib.oracle_boundary_force_hessian(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bc["mn"]), fp(bc["mx"]), bc["kB"], bc["muB"], bc["epsVB"],
+                                              bc["dt"], fr, fp(f), fp(h))
+            got[i] = np.concatenate([f, h])
+            multi += int((np.abs(G[fr, i, :3]) > 0).sum() >= 2)
+        assert relmax(got[:, :3], G[fr][:, :3]) < 1e-6 and relmax(got[:, 3:], G[fr][:, 3:]) < 1e-6
+        assert np.array_equal(got == 0, G[fr] == 0)
+    assert multi > 60 and not np.array_equal(G[0], G[1])
 
 
 def test_point_in_tet_bit_exact():
