@@ -180,6 +180,16 @@ def main():
             ref.ref_boundary_cpu(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bc["mn"]), fp(bc["mx"]), bc["kB"], bc["muB"], bc["epsVB"], bc["dt"], fr, fp(f), fp(h))
             B[fr, i] = np.concatenate([f, h])
     out["boundary_cpu"] = B
+    # ---- VBDPhysics::updateCollisionInfo + ::accumlateCollisionForceAndHessianPerCollision (the CPU contact term): [case][order][depth, f3, h9]
+    cc = contact_cases()
+    CC = np.zeros((len(cc["p"]), 4, 13), np.float32)
+    for i in range(len(cc["p"])):
+        for order in range(4):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+            d = ref.ref_contact_cpu(fp(cc["p"][i]), fp(cc["pPrev"][i]), fp(cc["tri"][i]), fp(cc["triPrev"][i]), order, cc["k"], cc["mu0"], cc["mu1"],
+                                    cc["eps0"], cc["eps1"], cc["dt"], fp(f), fp(h))
+            CC[i, order] = np.concatenate([[d], f, h])
+    out["contact_cpu"] = CC
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

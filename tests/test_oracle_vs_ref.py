@@ -139,6 +139,31 @@ def test_contact_force_hessian():
     assert nz > 100
 
 
+def test_contact_force_hessian_cpu_path():
+    """The same probe against the reference's own CPU contact path - VBDPhysics::updateCollisionInfo and
+    ::accumlateCollisionForceAndHessianPerCollision with computeVertexFriction, closestPointTriangle and computeFaceNormal
+    (VBDPhysics.cpp:2205-2311, 3005-3047, 2563-2592; oracle/ref_shim/refcontactcpu.cpp). Penetration depth, force and Hessian of all
+    four vertex orders; which cases carry a force must agree exactly, the depth bit for bit, force / Hessian to 1e-6 of the largest entry."""
+    lib = load_oracle()
+    cc = contact_cases()
+    G = GOLD["contact_cpu"]
+    got = np.zeros_like(G)
+    for i in range(len(cc["p"])):
+        for order in range(4):
+            f = np.zeros(3, np.float32); h = np.zeros(9, np.float32); d = C.c_float()
+            lib.oracle_contact_force_hessian(fp(cc["p"][i]), fp(cc["pPrev"][i]), fp(cc["tri"][i]), fp(cc["triPrev"][i]), order, cc["k"],
+                                             cc["mu0"], cc["mu1"], cc["eps0"], cc["eps1"], cc["dt"], fp(f), fp(h), C.byref(d))
+            got[i, order] = np.concatenate([[d.value], f, h])
+    assert np.array_equal(np.abs(got[..., 1:4]).max(-1) > 0, np.abs(G[..., 1:4]).max(-1) > 0)
+    assert (np.abs(G[..., 1:4]).max(-1) > 0).sum() > 100 and (G[:, 3, 0] <= 0).sum() >= 10
+    print("contact cpu:", relmax(got[..., 0], G[..., 0]), relmax(got[..., 1:4], G[..., 1:4]), relmax(got[..., 4:], G[..., 4:]))
+    assert np.array_equal(got[..., 0], G[..., 0])                     # penetration depth: bit for bit
+    for i in range(len(cc["p"])):
+        for order in range(4):
+            if np.abs(G[i, order, 1:4]).max() > 0:
+                assert relmax(got[i, order, 1:4], G[i, order, 1:4]) < 1e-6 and relmax(got[i, order, 4:], G[i, order, 4:]) < 1e-6
+
+
 def test_boundary_force_hessian():
     lib = load_oracle()
     bc = boundary_cases()
