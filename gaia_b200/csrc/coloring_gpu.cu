@@ -209,7 +209,7 @@ __global__ void k_check_csr(int n, const int32_t* __restrict__ off, const int32_
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
     const int b = off[v], e = off[v + 1];
-    if ((v == 0 && b != 0) || e < b) { *bad = 1; return; }
+    if ((v == 0 && b != 0) || b < 0 || e < b) { *bad = 1; return; }
     for (int q = b; q < e; q++) { const int u = adj[q]; if (u < 0 || u >= n || u == v) { *bad = 1; return; } }
 }
 
@@ -270,6 +270,7 @@ extern "C" int gaia_b200_color_graph_device_noalloc(int device, int32_t numNodes
         if (h[1]) { noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: more than 64 colours needed"); return GAIA_ERR_UNSUPPORTED; }
         if (!h[0]) break;
     }
+    if (h[0]) { noalloc_message(errMsg, errMsgCap, "color_graph_device_noalloc: the speculative rounds did not finish"); return GAIA_ERR_CUDA; }
     k_histogram<<<G, B>>>(n, cur, dSizes);
     CKN(cudaMemcpyAsync(dColors, cur, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToDevice, 0));
     int32_t sizes[64];

@@ -104,12 +104,12 @@ __global__ void k_halo_push_sync(PushArgs a, const float4* __restrict__ pos, uin
 }
 
 // Agreement among all ranks: "does ANY rank hold an active contact?" Every rank stores (epoch << 1 | mine) into slot
-// [32 + 8 * (epoch & 1) + myRank] of every rank's flag array and waits for the others' words of this epoch; two slot sets
+// [32 + 16 * (epoch & 1) + myRank] of every rank's flag array (64 words; ranks 0 .. kMaxPeers) and waits for the others' words of this epoch; two slot sets
 // alternate, and no rank can be two votes ahead of another (it needs that rank's word for the vote in between).
 struct VoteArgs { uint32_t* flags[kMaxPeers + 1]; };
 __global__ void k_halo_vote(VoteArgs a, int world, int myRank, uint32_t epoch, int mine, int32_t* result, int32_t* errFlags) {
     const int p = threadIdx.x;
-    const int base = 32 + 8 * (int)(epoch & 1u);
+    const int base = 32 + 16 * (int)(epoch & 1u);
     int theirs = 0;
     if (p < world && p != myRank) {
         __threadfence_system();

@@ -481,7 +481,7 @@ static cudaError_t solve_iterations(Scene& s, int nIters, bool allowIntermediate
         cudaError_t e = enqueue_iterations(s, nIters, allowIntermediateCD, withContacts, true);
         cudaGraph_t g = nullptr;
         cudaError_t e2 = cudaStreamEndCapture(s.stream, &g);
-        if (e != cudaSuccess) return e;
+        if (e != cudaSuccess) { if (g) cudaGraphDestroy(g); return e; }
         CK(e2);
         CK(cudaGraphInstantiate(&s.iterGraphExec, g, 0));
         cudaGraphDestroy(g);
@@ -591,11 +591,9 @@ cudaError_t run_substeps(Scene& s, int nSubsteps) {
         CK(timed_phase(s, s.stats.timeCsmpInitialStep, [&] { cudaError_t e = initial_step(s); if (e == cudaSuccess) e = apply_deformers(s); if (e == cudaSuccess) e = halo_refresh(s); return e; }));
         CK(timed_phase(s, s.stats.timeCsmpColDetectCCD, [&] { cudaError_t e = collision_ccd(s); if (e == cudaSuccess) e = collision_prepare(s); return e; }));
         {
-            const double solveBefore = s.solveKernelMs;
             double whole = 0.0;
             CK(timed_phase(s, whole, [&] { return solve_iterations(s, s.phys.iterations, true); }));
             s.stats.timeCsmpMaterialSolve += whole;      // colour loop incl. contact pre-passes (and intermediate detection)
-            (void)solveBefore;
         }
         CK(timed_phase(s, s.stats.timeCsmpUpdateVelocity, [&] {
             k_update_velocity<<<nblk(N), kBlock, 0, s.stream>>>(N, s.pos.p, s.prev.p, s.vel.p, s.info.p, s.meshParams.p, s.stepParams);
@@ -683,7 +681,7 @@ int check_device_errors(Scene& s) {
     if (h[2]) { s.err = "contact list overflow"; return GAIA_ERR_OVERFLOW; }
     if (h[3]) { s.err = "tetrahedral traversal stack overflow"; return GAIA_ERR_OVERFLOW; }
     if (h[4]) { s.err = "halo exchange timed out waiting for a neighbour partition"; return GAIA_ERR_TIMEOUT; }
-    if (h[5]) { s.err = "colour sweep: a bulk copy never completed"; return GAIA_ERR_TIMEOUT; }
+    if (h[5]) { s.err = "colour sweep: a bulk copy or the barrier between colours never completed"; return GAIA_ERR_TIMEOUT; }
     return GAIA_OK;
 }
 
