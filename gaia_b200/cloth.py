@@ -87,6 +87,8 @@ def bind_cloth_api(lib, prefix):
         "add_rotator": ([P, C.c_int, IP, C.c_int32, FP, FP, C.c_double, C.c_double], C.c_int),
         "add_translator": ([P, C.c_int, IP, C.c_int32, FP, C.c_float, C.c_float], C.c_int),
         "set_collider_sequence": ([P, C.c_int, C.c_int32, IP, FP, C.c_int32, C.c_int32], C.c_int),
+        "set_sewing": ([P, C.c_int, C.c_int32, IP, FP, C.c_float], C.c_int),
+        "add_attachment": ([P, C.c_int, C.c_int32, C.c_int, IP, FP, C.c_float], C.c_int),
         "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
         "frame_id": ([P], C.c_int), "cur_time": ([P], C.c_double), "set_time": ([P, C.c_int32, C.c_double], C.c_int),
         "synchronize": ([P], C.c_int), "num_meshes": ([P], C.c_int), "mesh_sizes": ([P, C.c_int, IP, IP, IP], C.c_int),
@@ -146,6 +148,20 @@ class ClothSceneBase:
         kf = _i32(np.asarray(key_frames, np.int32)) if key_frames is not None else None
         return self._call("set_collider_sequence", mesh, kp.shape[0], _ip(kf) if kf is not None else None, _fp(kp),
                           1 if interpolate_substep else 0, int(interpolate_iter))
+
+    def set_sewing(self, mesh, seams, ratios, stiffness):
+        """Seams [[v0, v1, v2], ...] of simulated `mesh` with their ratios (the reference's sewingPath JSON) and
+        ObjectParams::sewingStiffness; before finalize."""
+        v = _i32(np.asarray(seams, np.int32).reshape(-1, 3)); r = _f32(np.asarray(ratios, np.float32).reshape(-1))
+        if len(v) != len(r):
+            raise ValueError("one ratio per seam")
+        return self._call("set_sewing", mesh, len(r), _ip(v), _fp(r), float(stiffness))
+
+    def add_attachment(self, mesh_v, vertex, mesh_f, face_verts, bary_or_pos, stiffness=1e4):
+        """One VertexFaceAttachmentConstraint: vertex of simulated mesh_v tied to bary . face_verts of mesh_f, or (mesh_f = -1)
+        to the fixed position bary_or_pos; before finalize."""
+        fv = _i32(np.asarray(face_verts if mesh_f >= 0 else [-1, -1, -1], np.int32)); b = _f32(np.asarray(bary_or_pos, np.float32))
+        return self._call("add_attachment", int(mesh_v), int(vertex), int(mesh_f), _ip(fv), _fp(b), float(stiffness))
 
     def finalize(self):
         self._call("finalize")

@@ -139,7 +139,40 @@ def load_collider_sequences(pj, repo_root):
     return out
 
 
-def build_scene(cls, phys, meshes, deformers=None, colliders=None, **kw):
+def load_cloth_constraints(models_json, params_json, repo_root):
+    """-> (sewing, attachments): sewing = [(mesh, seams [n, 3], ratios [n], sewingStiffness)] from the models' sewingPath files
+    (TriMeshFEM::initialize, M/TriMesh/TriMesh.cpp:95-110), attachments = [(meshV, vertex, meshF, faceVerts, barys, stiffness)]
+    from PhysicsParams.VertexFaceAttachmentConstraintParams (M/VBDCloth/VBDTriMeshConstraints.h:6-29)"""
+    with open(params_json) as f:
+        pj = json.load(f)
+    with open(models_json) as f:
+        mj = json.load(f)
+    sewing = []
+    for i, m in enumerate(mj["Models"]):
+        if m.get("filteredPairsPath"):
+            raise NotImplementedError("filteredPairsPath (contact pairs excluded by seams) is not supported")
+        if m.get("sewingPath"):
+            path = meshio.resolve_path(m["sewingPath"], repo_root)
+            if not path.endswith(".json"):
+                raise NotImplementedError(f"Unsupported file format: {path}")
+            with open(path) as f:
+                sj = json.load(f)
+            sewing.append((i, np.asarray(sj["vertices"], np.int32).reshape(-1, 3), np.asarray(sj["ratios"], np.float32), float(m.get("sewingStiffness", 0.0))))
+    a = pj.get("PhysicsParams", {}).get("VertexFaceAttachmentConstraintParams")
+    attachments = []
+    if a:
+        vi = np.asarray(a.get("vertexConstraintVertexInfos", []), np.int32).reshape(-1, 2)
+        fi = np.asarray(a.get("vertexConstraintTargetFacesInfos", []), np.int32).reshape(-1, 4)
+        ba = np.asarray(a.get("vertexConstraintBarys", []), np.float32).reshape(-1, 3)
+        ks = a.get("vertexConstraintStiffness") or []
+        if not (len(vi) == len(fi) == len(ba)) or (len(ks) and len(ks) != len(vi)):
+            raise ValueError("VertexFaceAttachmentConstraintParams: one (mesh, vertex), one (mesh, v, v, v), one barycentric triple per constraint")
+        for k in range(len(vi)):
+            attachments.append((int(vi[k, 0]), int(vi[k, 1]), int(fi[k, 0]), fi[k, 1:].copy(), ba[k].copy(), float(ks[k]) if len(ks) else 1e4))
+    return sewing, attachments
+
+
+def build_scene(cls, phys, meshes, deformers=None, colliders=None, constraints=None, **kw):
     s = cls(phys, **kw)
     for v, f, obj, colors, fixed, v0 in meshes:
         s.add_tri_mesh(v, f, obj, colors, fixed=fixed, simulated=True)
@@ -147,6 +180,11 @@ def build_scene(cls, phys, meshes, deformers=None, colliders=None, **kw):
         cid = s.add_tri_mesh(keys[0], faces, obj, simulated=False)
         s.set_collider_sequence(cid, keys, kf, sub, it)
     add_deformers(s, deformers)
+    sewing, attachments = constraints if constraints is not None else ([], [])
+    for mesh, seams, ratios, k in sewing:
+        s.set_sewing(mesh, seams, ratios, k)
+    for mv, v, mf, fv, b, k in attachments:
+        s.add_attachment(mv, v, mf, fv, b, k)
     s.finalize()
     for i, (v, f, obj, colors, fixed, v0) in enumerate(meshes):
         if np.any(v0 != 0):
@@ -175,7 +213,7 @@ def simulate(models_json, params_json, out_dir, repo_root=".", frames=None, devi
     ext = pp.get("outputExt", "ply")
     os.makedirs(out_dir, exist_ok=True)
     s = build_scene(cloth.ClothScene, phys, meshes, deformers=pj.get("Deformers"), colliders=load_collider_sequences(pj, repo_root),
-                    device=device)
+                    constraints=load_cloth_constraints(models_json, params_json, repo_root), device=device)
     write_frame(s, meshes, out_dir, 0, ext)
     for fr in range(1, n + 1):
         s.run_frames(1)

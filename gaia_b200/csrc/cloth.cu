@@ -919,6 +919,52 @@ k_contact_terms_fast(int gs, int n, DevView D, StepP P, const int32_t* __restric
     }
 }
 
+// ------------------------------------------------------------------------------------------------ sewing / attachments
+// VBDBaseTriMesh::accumlateSewingForceAndHessian (M/VBDCloth/VBDBaseTriMesh.cpp:320-344) and VBDClothSimulationFramework::
+// accumulateConstraintForceAndHessian (VBDClothPhysics.cpp:1464-1498) are both "a stiffness times a fixed linear combination
+// of up to four vertex positions (plus a constant)": entry e of vertex s holds r = sum_i w_i x(id_i) + c and contributes
+// force -= km r, Hessian += kmm I (km = m k, kmm = m^2 k with m the coefficient of s's own role in the seam / attachment).
+// They ride on the contact pre-pass slot (cTerm, hasContact) the colour sweep already reads, so the sweep kernels are
+// untouched and scenes without such constraints launch nothing extra: per colour, k_constraint_clear zeroes the slots of
+// the constrained vertices BEFORE the contact pre-pass (which only writes where it has contacts), k_constraint_terms adds
+// the terms AFTER it and raises bit 1 of hasContact (detection rewrites that byte; this kernel runs before every sweep).
+struct ConRec { int32_t id[4]; float w[4]; float c[3]; float km; float kmm; float pad[3]; };
+
+static __global__ void k_constraint_clear(int gs, int n, const int32_t* __restrict__ conOff, float4* __restrict__ cTerm) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int s = gs + t;
+    if (conOff[s + 1] == conOff[s]) return;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    cTerm[3 * (size_t)s + 0] = z; cTerm[3 * (size_t)s + 1] = z; cTerm[3 * (size_t)s + 2] = z;
+}
+
+static __global__ void k_constraint_terms(int gs, int n, const int32_t* __restrict__ conOff, const ConRec* __restrict__ con,
+                                          const float4* __restrict__ pos, const int32_t* __restrict__ info, float4* __restrict__ cTerm,
+                                          uint8_t* __restrict__ hasContact) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int s = gs + t;
+    const int b = conOff[s], e = conOff[s + 1];
+    if (e == b || info[s] < 0) return;
+    V3 force = v3(0, 0, 0);
+    float hd = 0.f;
+    for (int q = b; q < e; q++) {
+        const ConRec R = con[q];
+        V3 r = v3(0, 0, 0);
+#pragma unroll
+        for (int i = 0; i < 4; i++) if (R.id[i] >= 0) r += R.w[i] * ld3(pos, R.id[i]);
+        r += v3(R.c[0], R.c[1], R.c[2]);
+        force -= R.km * r;
+        hd += R.kmm;
+    }
+    float4 c0 = cTerm[3 * (size_t)s], c1 = cTerm[3 * (size_t)s + 1], c2 = cTerm[3 * (size_t)s + 2];
+    c0.x += force.x; c0.y += force.y; c0.z += force.z;
+    c0.w += hd; c1.w += hd; c2.w += hd;          // H[0], H[4], H[8]
+    cTerm[3 * (size_t)s] = c0; cTerm[3 * (size_t)s + 1] = c1; cTerm[3 * (size_t)s + 2] = c2;
+    hasContact[s] |= 2;
+}
+
 // Same update as k_solve_colour with LS lanes per vertex: lane j takes the incident faces / hinges j, j + LS, ... of the
 // per-colour ELL streams; the StVK Hessian is contracted in closed form,
 //   H = A [ a11 f1 f1^T + a22 f2 f2^T + a12 (f1 f2^T + f2 f1^T) + c I ],  f = -A [ f1 (S00 m1 + S01 m2) + f2 (S01 m1 + S11 m2) ],
@@ -1267,6 +1313,9 @@ struct ClothScene {
     DevBuf<int32_t> itemOff, itemCnt, itemCursor;
     DevBuf<int2> items;
     int64_t itemCap = 0;
+    DevBuf<int32_t> conOff;             // sewing / attachment entries per simulated sorted vertex (CSR); empty: none
+    DevBuf<ConRec> con;
+    bool hasConstraints = false;
     bool exactOrder = false;            // GAIA_B200_CLOTH_EXACT_ORDER: one thread per vertex, the CPU path's summation order
     int variant = 0;
     bool exactContact = false, exactSolve = false;   // (2 / 3 select one of the two kernels only: debugging aid)
@@ -1466,6 +1515,45 @@ static cudaError_t device_upload(ClothScene& s) {
     s.itemCap = std::min<int64_t>(32 * h.nSimV + 4096, (int64_t)1 << 30);
     CK(s.items.alloc(s.itemCap)); CK(s.itemOff.alloc(h.nSimV + 1)); CK(s.itemCnt.alloc(h.nSimV + 1)); CK(s.itemCursor.alloc(1));
     CK(cudaMemset(s.itemCnt.p, 0, (h.nSimV + 1) * 4)); CK(cudaMemset(s.itemOff.p, 0, (h.nSimV + 1) * 4));
+    // ---- sewing / attachment entries per simulated sorted vertex (ConRec; the order per vertex is the reference's: seams as
+    //      sewingVMap lists them, then attachments in the order the set-up loop appends them, VBDClothPhysics.cpp:161-219)
+    {
+        std::vector<std::vector<ConRec>> per(h.nSimV);
+        auto blank = [] { ConRec r; std::memset(&r, 0, sizeof(r)); for (int i = 0; i < 4; i++) r.id[i] = -1; return r; };
+        for (auto& m : h.meshes) {
+            const float k = m.sewStiffness;
+            for (size_t i = 0; i < m.sewRatios.size(); i++) {
+                const float lbda = m.sewRatios[i];
+                for (int o = 0; o < 3; o++) {
+                    ConRec r = blank();
+                    for (int q = 0; q < 3; q++) r.id[q] = m.sortedId[m.sewVerts[3 * i + q]];
+                    r.w[0] = 1.f; r.w[1] = -(1 - lbda); r.w[2] = -lbda;
+                    const float w = o == 0 ? 1.f : (o == 1 ? -(1 - lbda) : -lbda);
+                    r.km = w * k; r.kmm = w * w * k;
+                    per[m.sortedId[m.sewVerts[3 * i + o]]].push_back(r);
+                }
+            }
+        }
+        for (auto& a : h.attachments) {
+            const ClothMesh& mv = h.meshes[a.meshV];
+            auto entry = [&](int solvedMesh, int vId, float b) {
+                ConRec r = blank();
+                r.id[0] = mv.sortedId[vId]; r.w[0] = 1.f;          // x(meshV, vId): the V-side mesh read with the solved vertex's id (:1472)
+                if (a.meshF >= 0) for (int q = 0; q < 3; q++) { r.id[1 + q] = h.meshes[a.meshF].sortedId[a.face[q]]; r.w[1 + q] = -a.pos[q]; }
+                else for (int q = 0; q < 3; q++) r.c[q] = -a.pos[q];
+                r.km = a.stiffness * b; r.kmm = a.stiffness * b * b;
+                per[h.meshes[solvedMesh].sortedId[vId]].push_back(r);
+            };
+            entry(a.meshV, a.vertex, 1.f);
+            if (a.meshF >= 0 && h.meshes[a.meshF].simulated)
+                for (int q = 0; q < 3; q++) if (a.pos[q] != 0.f) entry(a.meshF, a.face[q], -a.pos[q]);
+        }
+        std::vector<int32_t> off(h.nSimV + 1, 0);
+        std::vector<ConRec> flat;
+        for (int64_t v = 0; v < h.nSimV; v++) { off[v + 1] = off[v] + (int32_t)per[v].size(); flat.insert(flat.end(), per[v].begin(), per[v].end()); }
+        s.hasConstraints = !flat.empty();
+        if (s.hasConstraints) { CK(upload(s.conOff, off)); CK(upload(s.con, flat)); }
+    }
     { const char* ex = getenv("GAIA_B200_CLOTH_EXACT_ORDER"); s.exactOrder = ex && ex[0] == '1'; s.exactContact = s.exactOrder || (ex && ex[0] == '2'); s.exactSolve = s.exactOrder || (ex && ex[0] == '3'); }
     { const char* va = getenv("GAIA_B200_CLOTH_VARIANT"); s.variant = va ? atoi(va) : 0; }
     CK(s.errFlags.alloc(N_FLAGS)); CK(cudaMemset(s.errFlags.p, 0, N_FLAGS * 4));
@@ -1664,12 +1752,17 @@ static int iteration(ClothScene& s, int iIter, float& omega) {
     for (int g = 0; g < s.G; g++) {
         const int gs = h.groupStart[g], n = h.groupStart[g + 1] - gs;
         if (!n) continue;
+        if (s.hasConstraints) { k_constraint_clear<<<nblk(n), kB, 0, s.stream>>>(gs, n, s.conOff.p, s.cTerm.p); s.stats.kernelLaunches++; }
         if (h.phys.handleCollision) {
             if (s.exactContact)
                 k_contact_terms<<<nblk(n), kB, 0, s.stream>>>(gs, n, D, s.P, s.hasContact.p, s.vfCount.p, s.vfList.p, s.linkOff.p, s.linkVal.p,
                                                               s.eeCount.p, s.eeList.p, s.cTerm.p);
             else
                 k_contact_terms_fast<<<nblk((int64_t)n * LC), kB, 0, s.stream>>>(gs, n, D, s.P, s.itemOff.p, s.itemCnt.p, s.items.p, s.cTerm.p);
+            s.stats.kernelLaunches++;
+        }
+        if (s.hasConstraints) {
+            k_constraint_terms<<<nblk(n), kB, 0, s.stream>>>(gs, n, s.conOff.p, s.con.p, s.pos.p, s.info.p, s.cTerm.p, s.hasContact.p);
             s.stats.kernelLaunches++;
         }
         if (s.profiling) cudaEventRecord(s.ev[2 * g], s.stream);
@@ -1914,6 +2007,47 @@ int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t
     return (int)h->s.h.deformers.size() - 1;
 }
 
+// ObjectParams::sewingPath / ::sewingStiffness (M/TriMesh/TriMesh.cpp:95-110, 458); the force is k_constraint_terms
+int gaia_b200_cloth_set_sewing(gaia_cloth_handle* h, int mesh, int32_t nSeams, const int32_t* verts3, const float* ratios, float sewingStiffness) {
+    CREQ(h);
+    ClothScene& s = h->s;
+    if (s.finalized) return cfail(s, GAIA_ERR_STATE, "sewing is set before finalize");
+    if (mesh < 0 || mesh >= (int)s.h.meshes.size()) return cfail(s, GAIA_ERR_INVALID_ARG, "mesh id out of range");
+    ClothMesh& m = s.h.meshes[mesh];
+    if (!m.simulated) return cfail(s, GAIA_ERR_INVALID_ARG, "sewing belongs to a simulated mesh");
+    if (nSeams < 0 || (nSeams > 0 && (!verts3 || !ratios))) return cfail(s, GAIA_ERR_INVALID_ARG, "bad seam list");
+    for (int i = 0; i < 3 * nSeams; i++) if (verts3[i] < 0 || verts3[i] >= m.nV) return cfail(s, GAIA_ERR_INVALID_ARG, "seam vertex out of range");
+    m.sewVerts.assign(verts3, verts3 + 3 * (size_t)nSeams);
+    m.sewRatios.assign(ratios, ratios + nSeams);
+    m.sewStiffness = sewingStiffness;
+    return GAIA_OK;
+}
+// one entry of PhysicsParams.VertexFaceAttachmentConstraintParams (set-up: VBDClothPhysics.cpp:152-220)
+int gaia_b200_cloth_add_attachment(gaia_cloth_handle* h, int meshV, int32_t vertex, int meshF, const int32_t faceVerts[3], const float baryOrPos[3],
+                                   float stiffness) {
+    CREQ(h);
+    ClothScene& s = h->s;
+    if (s.finalized) return cfail(s, GAIA_ERR_STATE, "attachments are added before finalize");
+    const int nM = (int)s.h.meshes.size();
+    if (meshV < 0 || meshV >= nM || !s.h.meshes[meshV].simulated) return cfail(s, GAIA_ERR_INVALID_ARG, "the vertex side of an attachment is a simulated mesh");
+    if (vertex < 0 || vertex >= s.h.meshes[meshV].nV) return cfail(s, GAIA_ERR_INVALID_ARG, "attached vertex out of range");
+    if (meshF < -1 || meshF >= nM || !baryOrPos) return cfail(s, GAIA_ERR_INVALID_ARG, "bad attachment target");
+    ClothAttachment a;
+    a.meshV = meshV; a.vertex = vertex; a.meshF = meshF; a.stiffness = stiffness;
+    for (int k = 0; k < 3; k++) a.pos[k] = baryOrPos[k];
+    if (meshF >= 0) {
+        if (!faceVerts) return cfail(s, GAIA_ERR_INVALID_ARG, "an attachment to a mesh names three face vertices");
+        for (int k = 0; k < 3; k++) {
+            if (faceVerts[k] < 0 || faceVerts[k] >= s.h.meshes[meshF].nV) return cfail(s, GAIA_ERR_INVALID_ARG, "attachment face vertex out of range");
+            // the reaction on a simulated face vertex is computed from x(meshV, that vertex's id) (the reference, :1472)
+            if (s.h.meshes[meshF].simulated && baryOrPos[k] != 0.f && faceVerts[k] >= s.h.meshes[meshV].nV)
+                return cfail(s, GAIA_ERR_INVALID_ARG, "attachment face vertex id does not exist in the vertex-side mesh (the reference reads it there)");
+            a.face[k] = faceVerts[k];
+        }
+    }
+    s.h.attachments.push_back(a);
+    return GAIA_OK;
+}
 int gaia_b200_cloth_run_frames(gaia_cloth_handle* h, int32_t nFrames) {
     CREQ(h); CFIN(h);
     CCUDA(h, cudaSetDevice(h->s.device));

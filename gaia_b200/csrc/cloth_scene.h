@@ -33,6 +33,10 @@ struct ClothMesh {
     std::vector<float> Q;                    // 16*nE: edgeLaplacianQuadraticForms, row-major 4x4
     std::vector<std::vector<int32_t>> colors;
     std::vector<int32_t> sortedId;           // original vertex -> sorted id
+    // sewing (M/TriMesh/TriMesh.h:226-227 + ObjectParams::sewingStiffness): seam i = (v0, v1, v2) with ratio i
+    std::vector<int32_t> sewVerts;           // 3 * nSeams
+    std::vector<float> sewRatios;
+    float sewStiffness = 0.f;
     int64_t vBase = 0, fBase = 0, eBase = 0; // offsets in "meshes concatenated" order
 };
 
@@ -59,8 +63,17 @@ struct ColliderSequence {
     bool firstTime = true;
 };
 
+// one entry of VertexFaceAttachmentConstraintParams (M/VBDCloth/VBDTriMeshConstraints.h:6-29)
+struct ClothAttachment {
+    int meshV = 0, vertex = 0, meshF = -1;
+    int32_t face[3] = {-1, -1, -1};
+    float pos[3] = {0, 0, 0};          // barycentrics (meshF >= 0) or the fixed position (meshF = -1)
+    float stiffness = 1e4f;
+};
+
 struct ClothHost {
     gaia_cloth_physics_params phys;
+    std::vector<ClothAttachment> attachments;
     std::vector<ClothDeformer> deformers;
     std::vector<ColliderSequence> colliderSeqs;
     float dt = 0.f, dtSqrReciprocal = 0.f;

@@ -135,6 +135,21 @@ void VBDClothPhysicsB200::loadRunningparameters(std::string inModelInputFile, st
         p->get("debugVerboseLvl", run_.debugVerboseLvl);
     }
     if (const Value* cd = params.find("ContactDetectorParams")) cd->get("maxQueryDis", phys_.maxQueryDis);
+    // VertexFaceAttachmentConstraintParams::fromJson (M/VBDCloth/VBDTriMeshConstraints.h:13-19), read at VBDClothPhysics.cpp:152-159
+    if (const Value* p = params.find("PhysicsParams"))
+        if (const Value* a = p->find("VertexFaceAttachmentConstraintParams")) {
+            a->get_ints("vertexConstraintVertexInfos", attachments_.vertexInfos);
+            a->get_ints("vertexConstraintTargetFacesInfos", attachments_.targetFacesInfos);
+            if (const Value* b = a->find("vertexConstraintBarys"))
+                if (b->is_array()) for (auto& t : b->arr) { if (!t.is_array() || t.arr.size() != 3) throw std::runtime_error("vertexConstraintBarys holds triples"); for (auto& x : t.arr) attachments_.barys.push_back((float)x.as_double()); }
+            if (const Value* k = a->find("vertexConstraintStiffness"))
+                if (k->is_array()) for (auto& x : k->arr) attachments_.stiffness.push_back((float)x.as_double());
+            const size_t n = attachments_.vertexInfos.size() / 2;
+            if (attachments_.vertexInfos.size() % 2 || attachments_.targetFacesInfos.size() != 4 * n || attachments_.barys.size() != 3 * n ||
+                (!attachments_.stiffness.empty() && attachments_.stiffness.size() != n))
+                throw std::runtime_error("VertexFaceAttachmentConstraintParams: (mesh, vertex) pairs, (mesh, v, v, v) quadruples, one barycentric triple "
+                                         "and (optionally) one stiffness per constraint");
+        }
     const Value* ml = modelsFile.find("Models");
     if (!ml || !ml->is_array()) throw std::runtime_error("Models.json has no \"Models\" list");
     for (auto& m : ml->arr) {
@@ -154,6 +169,9 @@ void VBDClothPhysicsB200::loadRunningparameters(std::string inModelInputFile, st
         m.get("initializationType", in.obj.initializationType);
         m.get("miu", in.obj.miu); m.get("lambda", in.obj.lambda);
         m.get("dampingStVK", in.obj.dampingStVK); m.get("dampingBending", in.obj.dampingBending);
+        m.get("sewingPath", in.sewingPath); m.get("filteredPairsPath", in.filteredPairsPath); m.get("sewingStiffness", in.sewingStiffness);
+        if (!in.sewingPath.empty()) in.sewingPath = resolve(in.sewingPath);
+        if (!in.filteredPairsPath.empty()) throw std::runtime_error("filteredPairsPath (contact pairs excluded by seams) is not supported");
         std::vector<int> fp;
         m.get_ints("fixedPoints", fp);
         in.fixedPoints.assign(fp.begin(), fp.end());
@@ -177,6 +195,14 @@ void VBDClothPhysicsB200::loadMeshes(int64_t* nVertsTotal, int64_t* nFacesTotal)
         if (!colourings_.count(m.verticesColoringCategoriesPath))
             colourings_.emplace(m.verticesColoringCategoriesPath, loadVertexColoring(m.verticesColoringCategoriesPath));
         nv += (int64_t)meshCache_[m.meshCacheId].verts.size() / 3; nf += (int64_t)meshCache_[m.meshCacheId].faces.size() / 3;
+        if (!m.sewingPath.empty() && m.sewingRatios.empty()) {       // TriMeshFEM::initialize, M/TriMesh/TriMesh.cpp:95-110 (".json" only, as there)
+            if (m.sewingPath.size() < 5 || m.sewingPath.substr(m.sewingPath.size() - 5) != ".json") throw std::runtime_error("Unsupported file format: " + m.sewingPath);
+            const Value sj = jsonmin::parse_file(m.sewingPath);
+            if (const Value* sv = sj.find("vertices"))
+                for (auto& t : sv->arr) { if (!t.is_array() || t.arr.size() != 3) throw std::runtime_error("sewing \"vertices\" holds triples"); for (auto& x : t.arr) m.sewingVertices.push_back((int32_t)x.as_double()); }
+            if (const Value* sr = sj.find("ratios")) for (auto& x : sr->arr) m.sewingRatios.push_back((float)x.as_double());
+            if (m.sewingVertices.size() != 3 * m.sewingRatios.size()) throw std::runtime_error("sewing file: one ratio per vertex triple");
+        }
     }
     if (nVertsTotal) *nVertsTotal = nv;
     if (nFacesTotal) *nFacesTotal = nf;
@@ -195,6 +221,9 @@ void VBDClothPhysicsB200::initialize() {
                                                     &m.obj, (int32_t)ct->second.size(), offs.data(), flat.data(), (int32_t)m.fixedPoints.size(),
                                                     m.fixedPoints.empty() ? nullptr : m.fixedPoints.data());
         check(rc, "gaia_b200_cloth_add_tri_mesh");
+        if (!m.sewingRatios.empty()) {
+            check(gaia_b200_cloth_set_sewing(h_, rc, (int32_t)m.sewingRatios.size(), m.sewingVertices.data(), m.sewingRatios.data(), m.sewingStiffness), "gaia_b200_cloth_set_sewing");
+        }
     }
     for (auto& c : colliders_) {       // colliderTriMeshes come after the simulated meshes (triMeshesAll)
         std::vector<float> keys;
@@ -219,6 +248,12 @@ void VBDClothPhysicsB200::initialize() {
             if (d.type == 0) check(gaia_b200_cloth_add_rotator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.center, d.axis, d.angularVelocity, d.rotationEndTime), "gaia_b200_cloth_add_rotator");
             else check(gaia_b200_cloth_add_translator(h_, d.selectedMeshes[i], v.data(), (int32_t)v.size(), d.speed, d.deformationStartTime, d.deformationEndTime), "gaia_b200_cloth_add_translator");
         }
+    for (size_t i = 0; i < attachments_.vertexInfos.size() / 2; i++) {      // the set-up loop of VBDClothPhysics.cpp:161-220
+        const int32_t fv[3] = {attachments_.targetFacesInfos[4 * i + 1], attachments_.targetFacesInfos[4 * i + 2], attachments_.targetFacesInfos[4 * i + 3]};
+        check(gaia_b200_cloth_add_attachment(h_, attachments_.vertexInfos[2 * i], attachments_.vertexInfos[2 * i + 1], attachments_.targetFacesInfos[4 * i], fv,
+                                             &attachments_.barys[3 * i], attachments_.stiffness.empty() ? 1e4f : attachments_.stiffness[i]),
+              "gaia_b200_cloth_add_attachment");
+    }
     check(gaia_b200_cloth_finalize(h_), "gaia_b200_cloth_finalize");
     for (size_t i = 0; i < models_.size(); i++) {
         const float* v0 = models_[i].initialVelocity;

@@ -33,6 +33,17 @@ struct ClothModelInput {
     std::vector<int32_t> fixedPoints;
     float initialVelocity[3] = {0, 0, 0};
     int meshCacheId = -1;
+    // ObjectParams::sewingPath / ::sewingStiffness (M/TriMesh/TriMesh.cpp:95-110, 458): {"vertices": [[v0, v1, v2], ...], "ratios": [...]}
+    std::string sewingPath, filteredPairsPath;
+    float sewingStiffness = 0.f;
+    std::vector<int32_t> sewingVertices;     // 3 per seam, read by loadMeshes()
+    std::vector<float> sewingRatios;
+};
+
+// PhysicsParams.VertexFaceAttachmentConstraintParams (M/VBDCloth/VBDTriMeshConstraints.h:6-29)
+struct ClothAttachmentInput {
+    std::vector<int> vertexInfos, targetFacesInfos;      // (mesh, vertex) * N, (mesh or -1, three face vertices) * N
+    std::vector<float> barys, stiffness;                 // 3 * N; N or empty (the reference's default 1e4)
 };
 
 struct ClothDeformerInput {
@@ -111,6 +122,7 @@ private:
     std::map<std::string, std::vector<std::vector<int32_t>>> colourings_;
     std::vector<ClothDeformerInput> deformers_;
     std::vector<ColliderInput> colliders_;
+    ClothAttachmentInput attachments_;
     gaia_cloth_handle* h_ = nullptr;
     int frameId_ = 0;
     double curTime_ = 0.0;

@@ -142,6 +142,25 @@ int gaia_b200_cloth_add_translator(gaia_cloth_handle* h, int mesh, const int32_t
  * and a moved collider triggers collision detection (VBDClothPhysics.cpp:413-418). Before finalize. */
 int gaia_b200_cloth_set_collider_sequence(gaia_cloth_handle* h, int mesh, int32_t nKeys, const int32_t* keyFrames, const float* xyz,
                                           int32_t interpolateSubstep, int32_t interpolateIter);
+/* Sewing of a simulated mesh (ObjectParams::sewingPath = {"vertices": [[v0, v1, v2], ...], "ratios": [...]} and
+ * ::sewingStiffness, M/TriMesh/TriMesh.cpp:95-110, 458; VBDBaseTriMesh::accumlateSewingForceAndHessian,
+ * M/VBDCloth/VBDBaseTriMesh.cpp:320-344, called from the vertex solve at VBDClothPhysics.cpp:1112-1114): seam i pulls vertex
+ * v0 onto the point (1 - ratio_i) x_v1 + ratio_i x_v2 of the SAME mesh; every vertex of the seam gets the force
+ * -m k (x_v0 - (1 - ratio) x_v1 - ratio x_v2) and the Hessian m^2 k I with m = 1, -(1 - ratio), -ratio for v0, v1, v2.
+ * Replaces the mesh's seams; before finalize. The colouring passed to add_tri_mesh must keep the three vertices of a seam in
+ * different colours (as for the reference, whose colour files are an input). ObjectParams::filteredPairsPath (contact pairs
+ * the seams exclude, TriMesh.h:603-621) is not supported: no pair is filtered. */
+int gaia_b200_cloth_set_sewing(gaia_cloth_handle* h, int mesh, int32_t nSeams, const int32_t* verts3, const float* ratios, float sewingStiffness);
+/* One vertex-face attachment (PhysicsParams.VertexFaceAttachmentConstraintParams: vertexConstraintVertexInfos,
+ * vertexConstraintTargetFacesInfos, vertexConstraintBarys, vertexConstraintStiffness; M/VBDCloth/VBDTriMeshConstraints.h:6-52,
+ * set-up VBDClothPhysics.cpp:152-220, force ::accumulateConstraintForceAndHessian :1464-1498): vertex `vertex` of the simulated
+ * mesh `meshV` is tied with `stiffness` (the reference's default: 1e4) to the point bary . (three vertices faceVerts of mesh
+ * `meshF`), or, with meshF = -1, to the fixed position baryOrPos. When meshF is simulated too, each face vertex whose bary is
+ * not 0 receives the reaction, computed exactly as the reference does: from x(meshV, THAT face vertex's id) - attached point
+ * (the reference reads the V-side mesh with the id of the vertex being solved, :1472), so such ids must exist in meshV.
+ * Before finalize; the vertices an attachment couples must have different colours. */
+int gaia_b200_cloth_add_attachment(gaia_cloth_handle* h, int meshV, int32_t vertex, int meshF, const int32_t faceVerts[3],
+                                   const float baryOrPos[3], float stiffness);
 /* finalize: VBDClothSimulationFramework::initialize (parallel groups :72-138, contact detector) */
 int gaia_b200_cloth_finalize(gaia_cloth_handle* h);
 

@@ -99,6 +99,9 @@ def load_ref():
             lib.ref_cloth_material_vertex.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_cloth_sewing"):
+            lib.ref_cloth_sewing.argtypes = [C.c_int, FP, C.c_int, IP, FP, C.c_float, C.c_int, FP, FP]; lib.ref_cloth_sewing.restype = None
+            lib.ref_cloth_attachments.argtypes = [C.c_int, C.c_int, IP, FP, C.c_int, IP, IP, FP, FP, FP, IP]; lib.ref_cloth_attachments.restype = None
         if hasattr(lib, "ref_contact_cpu"):
             lib.ref_contact_cpu.argtypes = [FP, FP, FP, FP, C.c_int] + [C.c_float] * 6 + [FP, FP]; lib.ref_contact_cpu.restype = C.c_float
         if hasattr(lib, "ref_cloth_step_sequence"):

@@ -126,6 +126,20 @@ class OracleClothScene(ClothSceneBase):
         fn(self.h, int(mesh), int(v), _fp(fo), _fp(h))
         return fo, h.reshape(3, 3).T.copy()
 
+    def sewing_force_hessian(self, mesh, v):
+        """VBDBaseTriMesh::accumlateSewingForceAndHessian alone: (force, H column-major 9)"""
+        fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+        fn = self._lib.oracle_cloth_sewing_force_hessian; fn.restype = None
+        fn(self.h, int(mesh), int(v), _fp(fo), _fp(h))
+        return fo, h
+
+    def constraint_force_hessian(self, mesh, v):
+        """accumulateConstraintForceAndHessian (attachments) alone: (force, H column-major 9)"""
+        fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+        fn = self._lib.oracle_cloth_constraint_force_hessian; fn.restype = None
+        fn(self.h, int(mesh), int(v), _fp(fo), _fp(h))
+        return fo, h
+
     def elastic_energy(self, mesh):
         return float(self._lib.oracle_cloth_elastic_energy(self.h, mesh))
 

@@ -34,6 +34,15 @@ struct EEContact {
 // FVContactInfo (:79-84)
 struct FVLink { int vMesh, v, contactId; };
 
+// VertexFaceAttachmentConstraint (M/VBDCloth/VBDTriMeshConstraints.h:31-45)
+struct Attachment {
+    float stiffness = 1e4f;
+    int vertexOrder = -1;                   // 0-2: face side, 3: vertex side
+    int vertexId = -1, meshV = -1, meshF = -1;
+    int face[3] = {-1, -1, -1};
+    V3 attachedPos;                         // barycentrics (meshF >= 0) or a fixed position (meshF = -1)
+};
+
 struct TriMesh {
     int id = 0, nV = 0, nF = 0, nE = 0;
     bool simulated = true;
@@ -64,6 +73,12 @@ struct TriMesh {
     std::vector<float> faceMinDis;          // per face
     std::vector<std::vector<FVLink>> faceLinks;
     bool hasVelocitiesPrev = false, hasApproxAcceleration = false;
+    // sewing (M/TriMesh/TriMesh.h:226-228; sewingVMap built as in generate_sewing_filters, :596-633) and attachment constraints
+    std::vector<std::array<int, 3>> sewingVertices;
+    std::vector<float> sewingRatio;
+    float sewingStiffness = 0.f;
+    std::vector<std::vector<std::pair<int, int>>> sewingVMap;      // per vertex: (seam, order)
+    std::vector<std::vector<Attachment>> attachments;              // per vertex (VertexConstraints::attachmentConstraints)
 };
 
 // ClothDeformerRotator / ClothDeformerTranslater (M/VBDCloth/VBDClothDeformer.h:43-200)
@@ -113,6 +128,10 @@ void cloth_add_rotator(ClothScene& s, int mesh, const int32_t* verts, int n, con
                        double angularVelocity, double rotationEnd);
 void cloth_add_translator(ClothScene& s, int mesh, const int32_t* verts, int n, const float speed[3], float tStart, float tEnd);
 void cloth_set_collider_sequence(ClothScene& s, int mesh, int nKeys, const int32_t* keyFrames, const float* xyz, bool interpolateSubstep, int interpolateIter);
+void cloth_set_sewing(ClothScene& s, int mesh, int nSeams, const int32_t* verts3, const float* ratios, float stiffness);
+int cloth_add_attachment(ClothScene& s, int meshV, int vertex, int meshF, const int32_t faceVerts[3], const float baryOrPos[3], float stiffness);
+void cloth_sewing_force_hessian(const TriMesh& m, int iV, V3& force, M3& hessian);
+void cloth_constraint_force_hessian(const ClothScene& s, int iMesh, int vId, V3& force, M3& hessian);
 void cloth_transform_points(const gaia_cloth_object_params& obj, std::vector<V3>& pos);
 void cloth_detect(ClothScene& s);
 void cloth_run_substeps(ClothScene& s, int nSubsteps);

@@ -53,6 +53,42 @@ int oracle_cloth_add_translator(void* h, int mesh, const int32_t* verts, int32_t
     cloth_add_translator(*s, mesh, verts, n, speed, tStart, tEnd);
     return (int)s->deformers.size() - 1;
 }
+int oracle_cloth_set_sewing(void* h, int mesh, int32_t nSeams, const int32_t* verts3, const float* ratios, float stiffness) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    if (mesh < 0 || mesh >= (int)s->meshes.size() || !s->meshes[mesh].simulated || nSeams < 0 || (nSeams && (!verts3 || !ratios))) return GAIA_ERR_INVALID_ARG;
+    for (int i = 0; i < 3 * nSeams; i++) if (verts3[i] < 0 || verts3[i] >= s->meshes[mesh].nV) return GAIA_ERR_INVALID_ARG;
+    cloth_set_sewing(*s, mesh, nSeams, verts3, ratios, stiffness);
+    return GAIA_OK;
+}
+int oracle_cloth_add_attachment(void* h, int meshV, int32_t vertex, int meshF, const int32_t* faceVerts, const float* baryOrPos, float stiffness) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    const int nM = (int)s->meshes.size();
+    if (meshV < 0 || meshV >= nM || !s->meshes[meshV].simulated || vertex < 0 || vertex >= s->meshes[meshV].nV || meshF < -1 || meshF >= nM || !baryOrPos)
+        return GAIA_ERR_INVALID_ARG;
+    if (meshF >= 0) {
+        if (!faceVerts) return GAIA_ERR_INVALID_ARG;
+        for (int k = 0; k < 3; k++) {
+            if (faceVerts[k] < 0 || faceVerts[k] >= s->meshes[meshF].nV) return GAIA_ERR_INVALID_ARG;
+            if (s->meshes[meshF].simulated && baryOrPos[k] != 0.f && faceVerts[k] >= s->meshes[meshV].nV) return GAIA_ERR_INVALID_ARG;   // read from meshV (:1472)
+        }
+    }
+    return cloth_add_attachment(*s, meshV, vertex, meshF, faceVerts, baryOrPos, stiffness);
+}
+// probes: the two terms alone, at the scene's current positions
+void oracle_cloth_sewing_force_hessian(void* h, int mesh, int v, float* f3, float* h9) {
+    ClothScene* s = (ClothScene*)h;
+    V3 f; M3 H;
+    cloth_sewing_force_hessian(s->meshes[mesh], v, f, H);
+    f3[0] = f.x; f3[1] = f.y; f3[2] = f.z; std::memcpy(h9, H.m, 36);
+}
+void oracle_cloth_constraint_force_hessian(void* h, int mesh, int v, float* f3, float* h9) {
+    ClothScene* s = (ClothScene*)h;
+    V3 f; M3 H;
+    cloth_constraint_force_hessian(*s, mesh, v, f, H);
+    f3[0] = f.x; f3[1] = f.y; f3[2] = f.z; std::memcpy(h9, H.m, 36);
+}
 int oracle_cloth_finalize(void* h) { cloth_finalize(*(ClothScene*)h); return GAIA_OK; }
 int oracle_cloth_run_frames(void* h, int32_t n) {
     ClothScene* s = (ClothScene*)h;

@@ -279,9 +279,82 @@ void cloth_vertex_force_hessian(ClothScene& s, int iMesh, int vId, V3& force, M3
     const float hi = m.mass[vId] * s.dtSqrReciprocal;
     hessian(0, 0) += hi; hessian(1, 1) += hi; hessian(2, 2) += hi;
     cloth_material_force_hessian(s, m, vId, force, hessian);
+    if (!m.sewingVertices.empty()) cloth_sewing_force_hessian(m, vId, force, hessian);      // :1112-1114
     boundary_force_hessian(s, m, vId, force, hessian);
-    // (attachment constraints, sewing and external forces are not part of the path: vertexExternalForces is zero,
-    //  M/VBDCloth/VBDBaseTriMesh.cpp:185-188)
+    cloth_constraint_force_hessian(s, iMesh, vId, force, hessian);                           // :1118
+    // (external forces are not part of the path: vertexExternalForces is zero, M/VBDCloth/VBDBaseTriMesh.cpp:185-188)
+}
+
+// VBDBaseTriMesh::accumlateSewingForceAndHessian (M/VBDCloth/VBDBaseTriMesh.cpp:320-344)
+void cloth_sewing_force_hessian(const TriMesh& m, int iV, V3& force, M3& hessian) {
+    if (m.sewingVMap.empty()) return;
+    const float k = m.sewingStiffness;
+    for (const auto& p : m.sewingVMap[iV]) {
+        const int sid = p.first, order = p.second;
+        float w = 1.f;
+        const float lbda = m.sewingRatio[sid];
+        if (order == 1) w = -(1 - lbda);
+        else if (order == 2) w = -lbda;
+        const V3 x0 = m.pos[m.sewingVertices[sid][0]], x1 = m.pos[m.sewingVertices[sid][1]], x2 = m.pos[m.sewingVertices[sid][2]];
+        const V3 x = x0 - (1 - lbda) * x1 - lbda * x2;
+        force -= (w * k) * x;
+        const float h = w * w * k;
+        hessian(0, 0) += h; hessian(1, 1) += h; hessian(2, 2) += h;
+    }
+}
+
+// VBDClothSimulationFramework::accumulateConstraintForceAndHessian (M/VBDCloth/VBDClothPhysics.cpp:1464-1498). Note :1472: the
+// position is read from the V-SIDE mesh with the id of the vertex being solved, also for the face-side entries.
+void cloth_constraint_force_hessian(const ClothScene& s, int iMesh, int vId, V3& force, M3& hessian) {
+    const TriMesh& m = s.meshes[iMesh];
+    if (m.attachments.empty()) return;
+    for (const Attachment& a : m.attachments[vId]) {
+        const V3 vertPos = s.meshes[a.meshV].pos[vId];
+        const float bs[4] = {-a.attachedPos[0], -a.attachedPos[1], -a.attachedPos[2], 1.f};
+        V3 attachedPos;
+        if (a.meshF != -1) {
+            const TriMesh& t = s.meshes[a.meshF];
+            attachedPos = a.attachedPos[0] * t.pos[a.face[0]] + a.attachedPos[1] * t.pos[a.face[1]] + a.attachedPos[2] * t.pos[a.face[2]];
+        } else attachedPos = a.attachedPos;
+        const V3 diff = vertPos - attachedPos;
+        const float b = bs[a.vertexOrder];
+        force -= (a.stiffness * b) * diff;
+        const float h = a.stiffness * b * b;
+        hessian(0, 0) += h; hessian(1, 1) += h; hessian(2, 2) += h;
+    }
+}
+
+// TriMeshFEM::generate_sewing_filters, the sewingVMap part (M/TriMesh/TriMesh.h:596-633)
+void cloth_set_sewing(ClothScene& s, int mesh, int nSeams, const int32_t* verts3, const float* ratios, float stiffness) {
+    TriMesh& m = s.meshes[mesh];
+    m.sewingVertices.clear(); m.sewingRatio.assign(ratios, ratios + nSeams); m.sewingStiffness = stiffness;
+    m.sewingVMap.assign(m.nV, {});
+    for (int i = 0; i < nSeams; i++) {
+        m.sewingVertices.push_back({verts3[3 * i], verts3[3 * i + 1], verts3[3 * i + 2]});
+        for (int o = 0; o < 3; o++) m.sewingVMap[verts3[3 * i + o]].push_back({i, o});
+    }
+}
+
+// the set-up loop of VBDClothSimulationFramework::initialize (M/VBDCloth/VBDClothPhysics.cpp:161-219)
+int cloth_add_attachment(ClothScene& s, int meshV, int vertex, int meshF, const int32_t faceVerts[3], const float baryOrPos[3], float stiffness) {
+    TriMesh& mv = s.meshes[meshV];
+    if (mv.attachments.empty()) mv.attachments.assign(mv.nV, {});
+    Attachment a;
+    a.vertexOrder = 3; a.meshF = meshF; a.meshV = meshV; a.vertexId = vertex; a.stiffness = stiffness;
+    for (int k = 0; k < 3; k++) a.face[k] = meshF >= 0 ? faceVerts[k] : -1;
+    a.attachedPos = V3(baryOrPos[0], baryOrPos[1], baryOrPos[2]);
+    mv.attachments[vertex].push_back(a);
+    if (meshF >= 0 && s.meshes[meshF].simulated) {      // (simulated meshes come first: meshF < numSimulationMeshes())
+        TriMesh& mf = s.meshes[meshF];
+        if (mf.attachments.empty()) mf.attachments.assign(mf.nV, {});
+        for (int iFV = 0; iFV < 3; iFV++) {
+            if (a.attachedPos[iFV] == 0.f) continue;
+            Attachment f = a;
+            f.vertexOrder = iFV;
+            mf.attachments[faceVerts[iFV]].push_back(f);
+        }
+    }
+    return GAIA_OK;
 }
 
 // applyConservativeBoundTruncation (:1223-1246)

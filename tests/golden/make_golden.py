@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -190,6 +190,24 @@ def main():
                                     cc["eps0"], cc["eps1"], cc["dt"], fp(f), fp(h))
             CC[i, order] = np.concatenate([[d], f, h])
     out["contact_cpu"] = CC
+    # ---- cloth sewing and attachments: VBDBaseTriMesh::accumlateSewingForceAndHessian, the attachment set-up loop of
+    #      VBDClothSimulationFramework::initialize and ::accumulateConstraintForceAndHessian
+    c = cloth_constraint_case()
+    pos0 = np.ascontiguousarray(c["meshes"][0][0])
+    SW = np.zeros((len(pos0), 12), np.float32)
+    for v in range(len(pos0)):
+        f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+        ref.ref_cloth_sewing(len(pos0), fp(pos0), len(c["ratios"]), ip(c["seams"]), fp(c["ratios"]), c["sew_k"], v, fp(f), fp(h))
+        SW[v] = np.concatenate([f, h])
+    out["cloth_sewing"] = SW
+    allpos = np.ascontiguousarray(np.concatenate([m[0] for m in c["meshes"]]))
+    voff = np.zeros(len(c["meshes"]) + 1, np.int32); voff[1:] = np.cumsum([len(m[0]) for m in c["meshes"]])
+    n_sim_v = int(voff[c["n_sim"]])
+    for tag, st in (("", c["stiff"]), ("_default_k", None)):
+        A = np.zeros((n_sim_v, 12), np.float32); cnt = np.zeros(n_sim_v, np.int32)
+        ref.ref_cloth_attachments(len(c["meshes"]), c["n_sim"], ip(voff), fp(allpos), len(c["v_infos"]), ip(c["v_infos"]), ip(c["f_infos"]), fp(c["barys"]),
+                                  fp(st) if st is not None else None, fp(A), ip(cnt))
+        out["cloth_attach" + tag] = A; out["cloth_attach_count" + tag] = cnt
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

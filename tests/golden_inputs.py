@@ -289,6 +289,43 @@ def cloth_contact_case(energy_type=1, seed=71):
     return dict(scene=o, meshes=out, vf=vf, ee=ee, params8=params8, bmin=np.array([0.2, 0.005, -10.0], np.float32), bmax=np.array([0.9, 10.0, 0.7], np.float32))
 
 
+def cloth_constraint_case(seed=91):
+    """Sewing and vertex-face attachments: two simulated 5 x 5 cloths and a collider sheet, all wrinkled at
+    random. Seams inside cloth 0 with ratios that include both ends (0 and 1) and a vertex that sits in three seams;
+    attachments of every kind the reference's set-up loop distinguishes: to a fixed point, to a face of the other simulated
+    cloth (one barycentric coordinate exactly 0: that face vertex gets no reaction entry), to a face of the collider, and to
+    a face of the vertex's own cloth; with and without per-constraint stiffness (None = the struct's default 1e4)."""
+    from gaia_b200 import cloth
+    rng = np.random.default_rng(seed)
+    meshes = []
+    for n, org in ((5, (0.0, 0.5, 0.0)), (5, (0.05, 0.56, 0.02)), (4, (0.0, 0.4, 0.0))):
+        v, f = cloth.grid_cloth(n, 1.0, origin=org)
+        meshes.append(((v + rng.normal(0, 0.02, v.shape)).astype(np.float32), np.ascontiguousarray(f, np.int32), n))
+    seams = np.array([[0, 6, 7], [12, 1, 2], [12, 20, 21], [24, 12, 13], [3, 18, 19], [9, 15, 16]], np.int32)
+    ratios = np.array([0.3, 0.0, 1.0, 0.65, 0.5, 0.125], np.float32)
+    # (mesh, vertex), (target mesh or -1, three face vertices), barycentrics or position
+    v_infos = np.array([[0, 4], [0, 10], [1, 7], [0, 22], [1, 0], [1, 7]], np.int32)
+    f_infos = np.array([[-1, 0, 0, 0], [1, 5, 6, 10], [2, 0, 1, 4], [0, 8, 13, 14], [0, 1, 2, 6], [-1, 0, 0, 0]], np.int32)
+    barys = np.array([[0.1, 0.9, -0.2], [0.25, 0.0, 0.75], [0.2, 0.3, 0.5], [0.6, 0.3, 0.1], [1.0 / 3, 1.0 / 3, 1.0 / 3], [0.3, 0.55, 0.1]], np.float32)
+    stiff = np.array([1e4, 3e3, 5e4, 8e3, 2e4, 1.5e3], np.float32)
+    return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
+
+
+def build_cloth_constraint_scene(cls, case, phys=None, with_stiffness=True, **kw):
+    """the scene of cloth_constraint_case on either implementation (colourings that keep coupled vertices apart are the
+    caller's business: the probes do not step)"""
+    from gaia_b200 import cloth
+    s = cls(phys if phys is not None else cloth.default_cloth_physics_params(handleCollision=0), **kw)
+    for i, (v, f, n) in enumerate(case["meshes"]):
+        s.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(n) if i < case["n_sim"] else (), simulated=i < case["n_sim"])
+    s.set_sewing(0, case["seams"], case["ratios"], case["sew_k"])
+    for i in range(len(case["v_infos"])):
+        s.add_attachment(case["v_infos"][i, 0], case["v_infos"][i, 1], case["f_infos"][i, 0], case["f_infos"][i, 1:], case["barys"][i],
+                         float(case["stiff"][i]) if with_stiffness else 1e4)
+    s.finalize()
+    return s
+
+
 def traverse_cases(seed=81, n_rays=400):
     """Rays for TetMeshFEM::tetrahedralTraverseTo on two meshes - the reference's teapot (irregular valence, thin parts) and a
     Kuhn beam -, both deformed at random: from a point on a surface face towards the centroid of a random tet (the way DCD

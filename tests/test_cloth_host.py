@@ -95,6 +95,48 @@ def test_collider_sequence_from_scene_files(tmp_path):
     assert r.returncode == 3 and "Unrecognized collider type" in r.stderr
 
 
+def add_constraints(tmp, m, p):
+    """sewingPath / sewingStiffness of a model and PhysicsParams.VertexFaceAttachmentConstraintParams, in the reference's schema
+    (M/TriMesh/TriMesh.cpp:95-110, 458; M/VBDCloth/VBDTriMeshConstraints.h:6-29); the seam keeps to the 10 x 10 sheet's colouring"""
+    with open(os.path.join(tmp, "seams.json"), "w") as fh:
+        json.dump({"vertices": [[44, 48, 59], [2, 22, 23]], "ratios": [0.4, 1.0]}, fh)
+    mj = json.load(open(m))
+    mj["Models"][0].update(sewingPath="${REPO_ROOT}\\seams.json", sewingStiffness=300.0)
+    json.dump(mj, open(m, "w"))
+    pj = json.load(open(p))
+    pj["PhysicsParams"]["VertexFaceAttachmentConstraintParams"] = {
+        "vertexConstraintVertexInfos": [0, 0, 0, 9, 0, 55], "vertexConstraintTargetFacesInfos": [-1, 0, 0, 0, 1, 0, 1, 2, 0, 33, 34, 43],
+        "vertexConstraintBarys": [[-0.5, 0.9, -0.5], [0.2, 0.3, 0.5], [0.5, 0.5, 0.0]], "vertexConstraintStiffness": [2e3, 1e3, 5e2]}
+    json.dump(pj, open(p, "w"))
+
+
+def test_sewing_and_attachments_from_scene_files(tmp_path):
+    m, p, (v, f, sv, sf) = write_scene(str(tmp_path))
+    add_constraints(str(tmp_path), m, p)
+    phys, meshes, pj = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    sewing, att = cloth_host.load_cloth_constraints(m, p, str(tmp_path))
+    assert len(sewing) == 1 and sewing[0][0] == 0 and sewing[0][1].tolist() == [[44, 48, 59], [2, 22, 23]] and sewing[0][3] == 300.0
+    assert [a[:3] for a in att] == [(0, 0, -1), (0, 9, 1), (0, 55, 0)] and att[1][3].tolist() == [0, 1, 2] and att[2][5] == 500.0
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, constraints=(sewing, att), threads=2)
+    plain = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)
+    o.run_frames(2); plain.run_frames(2)
+    x, xp = o.positions(0), plain.positions(0)
+    assert np.isfinite(x).all()
+    corner = np.float32([-0.5, 0.9, -0.5])
+    assert np.linalg.norm(x[0] - corner) < 0.5 * np.linalg.norm(xp[0] - corner)       # tied to a fixed point above its rest place
+    gap = lambda q: np.linalg.norm(q[44] - (0.6 * q[48] + 0.4 * q[59]))
+    assert gap(x) < 0.8 * gap(xp)                                                      # the seam closes
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    pj = json.load(open(p))
+    pj["PhysicsParams"]["VertexFaceAttachmentConstraintParams"]["vertexConstraintBarys"].pop()
+    json.dump(pj, open(p, "w"))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 3 and "VertexFaceAttachmentConstraintParams" in r.stderr
+    with pytest.raises(ValueError):
+        cloth_host.load_cloth_constraints(m, p, str(tmp_path))
+
+
 @pytest.mark.skipif(not meshio.reference_available(), reason="/root/reference only exists in the build container")
 def test_reference_cloth_experiment_files_parse():
     d = ("/root/reference/Simulator/VBDCloth/ParameterGen/Parameters/S01_Twisting/"
@@ -105,6 +147,31 @@ def test_reference_cloth_experiment_files_parse():
     assert v.shape == (10000, 3) and f.shape == (19602, 3) and abs(obj.bendingStiffness - 20) < 1e-6 and obj.initializationType == 2
     assert sum(len(c) for c in colors) == 10000 and cloth.check_cloth_coloring(10000, f, colors)
     assert len(pj["Deformers"]) == 2
+
+
+@pytest.mark.gpu
+def test_gpu_scene_with_sewing_and_attachments_from_files(tmp_path):
+    """gaia_vbdcloth_b200 reads the seams and attachments from the scene files: its frames equal the Python binding's (same
+    library underneath: bit-identical), and the binding's run matches the oracle"""
+    m, p, _ = write_scene(str(tmp_path))
+    add_constraints(str(tmp_path), m, p)
+    pj = json.load(open(p))
+    pj["PhysicsParams"].update(outputExt="bin")
+    json.dump(pj, open(p, "w"))
+    r = subprocess.run([CLOTH_HOST_BIN, m, p, str(tmp_path / "outc"), "-R", str(tmp_path), "--frames", "2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    phys, meshes, _ = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
+    con = cloth_host.load_cloth_constraints(m, p, str(tmp_path))
+    g = cloth_host.build_scene(cloth.ClothScene, phys, meshes, constraints=con)
+    o = cloth_host.build_scene(OracleClothScene, phys, meshes, constraints=con, threads=2)
+    plain = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)
+    # (oracle against itself with every coordinate moved by 1 / 8 ulp: 1e-6 / 3e-5 after one and two frames, chaotic from the third)
+    g.run_frames(1); o.run_frames(1); plain.run_frames(1)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 5e-4 < 0.01 < np.abs(plain.positions(0) - o.positions(0)).max()
+    g.run_frames(1); o.run_frames(1)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 2e-3
+    a = np.fromfile(tmp_path / "outc" / "A00000002.bin", np.float32).reshape(-1, 3)
+    assert np.array_equal(a, np.concatenate([g.positions(0), g.positions(1)]))
 
 
 @pytest.mark.gpu

@@ -419,3 +419,30 @@ def test_golden_file_matches_a_fresh_run_of_the_reference():
         t = C.c_float(-1); b = np.zeros(3, np.float32)
         hit = ref.ref_ccd_tri_point(fp(x0[i]), fp(x1[i]), fp(p0[i]), fp(p1[i]), C.byref(t), fp(b))
         assert hit == GOLD["ccd_hit"][i] and (not hit or t.value == GOLD["ccd_t"][i])
+
+
+def test_cloth_sewing_and_attachment_terms():
+    """Sewing and vertex-face attachments of the cloth path against the reference's own lines (VBDBaseTriMesh::
+    accumlateSewingForceAndHessian, VBDBaseTriMesh.cpp:320-344; the attachment set-up loop and ::accumulateConstraintForceAndHessian,
+    VBDClothPhysics.cpp:161-220, 1464-1498; oracle/ref_shim/refclothconstraint.cpp): every vertex of both simulated cloths, seams with
+    ratios 0 and 1, attachments to a fixed point / the other cloth / a collider / the own cloth, a zero barycentric coordinate,
+    given and default stiffness. Which vertices carry a term must agree exactly; force / Hessian 1e-6 of the largest entry."""
+    from golden_inputs import build_cloth_constraint_scene, cloth_constraint_case
+    from oracle.binding_cloth import OracleClothScene
+    c = cloth_constraint_case()
+    n0 = len(c["meshes"][0][0]); n1 = len(c["meshes"][1][0])
+    for tag, with_k in (("", True), ("_default_k", False)):
+        o = build_cloth_constraint_scene(OracleClothScene, c, with_stiffness=with_k, threads=1)
+        sw = np.stack([np.concatenate(o.sewing_force_hessian(0, v)) for v in range(n0)])
+        at = np.stack([np.concatenate(o.constraint_force_hessian(m, v)) for m, n in ((0, n0), (1, n1)) for v in range(n)])
+        G, A = GOLD["cloth_sewing"], GOLD["cloth_attach" + tag]
+        assert np.array_equal(np.abs(sw).max(1) > 0, np.abs(G).max(1) > 0) and (np.abs(G).max(1) > 0).sum() == 14
+        assert np.array_equal(np.abs(at).max(1) > 0, GOLD["cloth_attach_count" + tag] > 0) and (GOLD["cloth_attach_count" + tag] > 0).sum() == 13
+        assert relmax(sw[:, :3], G[:, :3]) < 1e-6 and relmax(sw[:, 3:], G[:, 3:]) < 1e-6
+        assert relmax(at[:, :3], A[:, :3]) < 1e-6 and relmax(at[:, 3:], A[:, 3:]) < 1e-6
+        # both terms are part of the vertex's total: the total moves by exactly these amounts when they are switched off
+        f_all = np.stack([np.concatenate([o.vertex_force_hessian(0, v)[0], o.vertex_force_hessian(0, v)[1].T.reshape(-1)]) for v in range(n0)])
+        plain = build_cloth_constraint_scene(OracleClothScene, dict(c, seams=np.zeros((0, 3), np.int32), ratios=np.zeros(0, np.float32),
+                                                                    v_infos=c["v_infos"][:0], f_infos=c["f_infos"][:0]), threads=1)
+        f_plain = np.stack([np.concatenate([plain.vertex_force_hessian(0, v)[0], plain.vertex_force_hessian(0, v)[1].T.reshape(-1)]) for v in range(n0)])
+        assert relmax(f_all - f_plain, sw + at[:n0]) < 1e-5
