@@ -89,6 +89,7 @@ def bind_cloth_api(lib, prefix):
         "set_collider_sequence": ([P, C.c_int, C.c_int32, IP, FP, C.c_int32, C.c_int32], C.c_int),
         "set_sewing": ([P, C.c_int, C.c_int32, IP, FP, C.c_float], C.c_int),
         "add_attachment": ([P, C.c_int, C.c_int32, C.c_int, IP, FP, C.c_float], C.c_int),
+        "set_filtered_pairs": ([P, C.c_int, C.c_int32, IP, C.c_int32, IP], C.c_int),
         "finalize": ([P], C.c_int), "run_frames": ([P, C.c_int32], C.c_int), "run_iterations": ([P, C.c_int32], C.c_int),
         "frame_id": ([P], C.c_int), "cur_time": ([P], C.c_double), "set_time": ([P, C.c_int32, C.c_double], C.c_int),
         "synchronize": ([P], C.c_int), "num_meshes": ([P], C.c_int), "mesh_sizes": ([P, C.c_int, IP, IP, IP], C.c_int),
@@ -156,6 +157,12 @@ class ClothSceneBase:
         if len(v) != len(r):
             raise ValueError("one ratio per seam")
         return self._call("set_sewing", mesh, len(r), _ip(v), _fp(r), float(stiffness))
+
+    def set_filtered_pairs(self, mesh, vf_pairs=(), ee_pairs=()):
+        """filteredPairsPath of the reference: (vertex, face) and (edge, edge) pairs of `mesh` that never form a contact; they take
+        effect only if the mesh also has seams; before finalize."""
+        vf = _i32(np.asarray(vf_pairs, np.int32).reshape(-1, 2)); ee = _i32(np.asarray(ee_pairs, np.int32).reshape(-1, 2))
+        return self._call("set_filtered_pairs", mesh, len(vf), _ip(vf), len(ee), _ip(ee))
 
     def add_attachment(self, mesh_v, vertex, mesh_f, face_verts, bary_or_pos, stiffness=1e4):
         """One VertexFaceAttachmentConstraint: vertex of simulated mesh_v tied to bary . face_verts of mesh_f, or (mesh_f = -1)

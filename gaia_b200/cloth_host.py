@@ -140,7 +140,7 @@ def load_collider_sequences(pj, repo_root):
 
 
 def load_cloth_constraints(models_json, params_json, repo_root):
-    """-> (sewing, attachments): sewing = [(mesh, seams [n, 3], ratios [n], sewingStiffness)] from the models' sewingPath files
+    """-> (sewing, attachments): sewing = [(mesh, seams [n, 3], ratios [n], sewingStiffness, filtered vf pairs, filtered ee pairs)] from the models' sewingPath / filteredPairsPath files
     (TriMeshFEM::initialize, M/TriMesh/TriMesh.cpp:95-110), attachments = [(meshV, vertex, meshF, faceVerts, barys, stiffness)]
     from PhysicsParams.VertexFaceAttachmentConstraintParams (M/VBDCloth/VBDTriMeshConstraints.h:6-29)"""
     with open(params_json) as f:
@@ -149,15 +149,18 @@ def load_cloth_constraints(models_json, params_json, repo_root):
         mj = json.load(f)
     sewing = []
     for i, m in enumerate(mj["Models"]):
-        if m.get("filteredPairsPath"):
-            raise NotImplementedError("filteredPairsPath (contact pairs excluded by seams) is not supported")
         if m.get("sewingPath"):
             path = meshio.resolve_path(m["sewingPath"], repo_root)
             if not path.endswith(".json"):
                 raise NotImplementedError(f"Unsupported file format: {path}")
             with open(path) as f:
                 sj = json.load(f)
-            sewing.append((i, np.asarray(sj["vertices"], np.int32).reshape(-1, 3), np.asarray(sj["ratios"], np.float32), float(m.get("sewingStiffness", 0.0))))
+            vf, ee = np.zeros((0, 2), np.int32), np.zeros((0, 2), np.int32)
+            if m.get("filteredPairsPath"):        # generate_sewing_filters reads it only beside a sewing file (M/TriMesh/TriMesh.h:603-621)
+                with open(meshio.resolve_path(m["filteredPairsPath"], repo_root)) as f:
+                    fj = json.load(f)
+                vf = np.asarray(fj.get("vf", []), np.int32).reshape(-1, 2); ee = np.asarray(fj.get("ee", []), np.int32).reshape(-1, 2)
+            sewing.append((i, np.asarray(sj["vertices"], np.int32).reshape(-1, 3), np.asarray(sj["ratios"], np.float32), float(m.get("sewingStiffness", 0.0)), vf, ee))
     a = pj.get("PhysicsParams", {}).get("VertexFaceAttachmentConstraintParams")
     attachments = []
     if a:
@@ -181,8 +184,10 @@ def build_scene(cls, phys, meshes, deformers=None, colliders=None, constraints=N
         s.set_collider_sequence(cid, keys, kf, sub, it)
     add_deformers(s, deformers)
     sewing, attachments = constraints if constraints is not None else ([], [])
-    for mesh, seams, ratios, k in sewing:
+    for mesh, seams, ratios, k, vf, ee in sewing:
         s.set_sewing(mesh, seams, ratios, k)
+        if len(vf) or len(ee):
+            s.set_filtered_pairs(mesh, vf, ee)
     for mv, v, mf, fv, b, k in attachments:
         s.add_attachment(mv, v, mf, fv, b, k)
     s.finalize()

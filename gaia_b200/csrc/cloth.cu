@@ -374,7 +374,7 @@ CDEV float box_dist2(float4 lo, float4 hi, V3 p) {
 // reference); per key the feasible face with the smallest global id is kept (rule R5), the list is sorted by face id.
 static __global__ void __launch_bounds__(kB)
 k_vf_query(DevView D, StepP P, BvhView bv, int32_t* __restrict__ vfCount, int2* __restrict__ vfList, float* __restrict__ vfMinDis,
-           int32_t* faceMinBits, int32_t* errFlags) {
+           int32_t* faceMinBits, int32_t* errFlags, const int32_t* __restrict__ filtOff, const int32_t* __restrict__ filt) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= D.N) return;
     const int qm = D.info[s] & 0x00FFFFFF;
@@ -390,7 +390,9 @@ k_vf_query(DevView D, StepP P, BvhView bv, int32_t* __restrict__ vfCount, int2* 
             const int f = bv.order[node - bv.n];
             const int4 fv = __ldg(D.faceSid + f);
             const int fm = fv.w;
-            const bool skip = (fm >= P.numSim && qm >= P.numSim) || (qm == fm && (fv.x == s || fv.y == s || fv.z == s));
+            bool skip = (fm >= P.numSim && qm >= P.numSim) || (qm == fm && (fv.x == s || fv.y == s || fv.z == s));
+            // the seams' filtered pairs (filtOff: NULL unless a mesh has them; the lists hold global face ids of the vertex's own mesh)
+            if (filtOff && !skip) for (int q = filtOff[s]; q < filtOff[s + 1]; q++) if (filt[q] == f) { skip = true; break; }
             if (!skip) {
                 V3 bary; int type;
                 const V3 cp = gb::closest_point_triangle(p, ld3(D.pos, fv.x), ld3(D.pos, fv.y), ld3(D.pos, fv.z), bary, type);
@@ -449,7 +451,7 @@ k_vf_query(DevView D, StepP P, BvhView bv, int32_t* __restrict__ vfCount, int2* 
 // contactQueryEE + triMeshEdgeContactQueryFunc: every edge of a simulated mesh against the edges within maxQueryDis
 static __global__ void __launch_bounds__(kB)
 k_ee_query(DevView D, StepP P, BvhView bv, int32_t* __restrict__ eeCount, int32_t* __restrict__ eeList, float* __restrict__ eeMinDis,
-           int32_t* errFlags) {
+           int32_t* errFlags, const int32_t* __restrict__ filtOff, const int32_t* __restrict__ filt) {
     const int qe = blockIdx.x * blockDim.x + threadIdx.x;
     if (qe >= D.nSimE) return;
     const int4 Q = __ldg(D.edgeSid + qe);
@@ -471,7 +473,8 @@ k_ee_query(DevView D, StepP P, BvhView bv, int32_t* __restrict__ eeCount, int32_
             const int te = bv.order[node - bv.n];
             const int4 T = __ldg(D.edgeSid + te);
             // sorted vertex ids are unique over the scene: sharing an id implies the same mesh
-            const bool skip = te == qe || Q.x == T.x || Q.x == T.y || Q.y == T.x || Q.y == T.y;
+            bool skip = te == qe || Q.x == T.x || Q.x == T.y || Q.y == T.x || Q.y == T.y;
+            if (filtOff && !skip) for (int q = filtOff[qe]; q < filtOff[qe + 1]; q++) if (filt[q] == te) { skip = true; break; }
             if (!skip) {
                 const V3 q1 = ld3(D.pos, T.x), q2 = ld3(D.pos, T.y);
                 V3 c1, c2; float mua, mub;
@@ -1313,6 +1316,7 @@ struct ClothScene {
     DevBuf<int32_t> itemOff, itemCnt, itemCursor;
     DevBuf<int2> items;
     int64_t itemCap = 0;
+    DevBuf<int32_t> vfFiltOff, vfFilt, eeFiltOff, eeFilt;   // filtered contact pairs of seams (CSR over sorted vertices / simulated edges); empty: none
     DevBuf<int32_t> conOff;             // sewing / attachment entries per simulated sorted vertex (CSR); empty: none
     DevBuf<ConRec> con;
     bool hasConstraints = false;
@@ -1515,6 +1519,32 @@ static cudaError_t device_upload(ClothScene& s) {
     s.itemCap = std::min<int64_t>(32 * h.nSimV + 4096, (int64_t)1 << 30);
     CK(s.items.alloc(s.itemCap)); CK(s.itemOff.alloc(h.nSimV + 1)); CK(s.itemCnt.alloc(h.nSimV + 1)); CK(s.itemCursor.alloc(1));
     CK(cudaMemset(s.itemCnt.p, 0, (h.nSimV + 1) * 4)); CK(cudaMemset(s.itemOff.p, 0, (h.nSimV + 1) * 4));
+    // ---- filtered contact pairs of seams (TriMeshFEM::generate_sewing_filters): per sorted vertex the global ids of the faces it
+    //      never pairs with, per global (simulated) edge the global ids of the edges it never pairs with. Only for meshes that
+    //      have seams, as the reference attaches its ...WithSewing callbacks (ClothContactDetector.cpp:969-974, 1011-1016).
+    {
+        std::vector<std::vector<int32_t>> vf(N), ee(h.nSimE);
+        bool any = false;
+        for (auto& m : h.meshes) {
+            if (!m.simulated || m.sewRatios.empty()) continue;
+            for (size_t i = 0; i + 1 < m.filtVF.size(); i += 2) { vf[m.sortedId[m.filtVF[i]]].push_back((int32_t)(m.fBase + m.filtVF[i + 1])); any = true; }
+            for (size_t i = 0; i + 1 < m.filtEE.size(); i += 2) {
+                ee[m.eBase + m.filtEE[i]].push_back((int32_t)(m.eBase + m.filtEE[i + 1]));
+                ee[m.eBase + m.filtEE[i + 1]].push_back((int32_t)(m.eBase + m.filtEE[i]));
+                any = true;
+            }
+        }
+        if (any) {
+            auto flatten = [](const std::vector<std::vector<int32_t>>& per, std::vector<int32_t>& off, std::vector<int32_t>& flat) {
+                off.assign(per.size() + 1, 0);
+                for (size_t i = 0; i < per.size(); i++) { off[i + 1] = off[i] + (int32_t)per[i].size(); flat.insert(flat.end(), per[i].begin(), per[i].end()); }
+                if (flat.empty()) flat.push_back(-1);
+            };
+            std::vector<int32_t> o1, f1, o2, f2;
+            flatten(vf, o1, f1); flatten(ee, o2, f2);
+            CK(upload(s.vfFiltOff, o1)); CK(upload(s.vfFilt, f1)); CK(upload(s.eeFiltOff, o2)); CK(upload(s.eeFilt, f2));
+        }
+    }
     // ---- sewing / attachment entries per simulated sorted vertex (ConRec; the order per vertex is the reference's: seams as
     //      sewingVMap lists them, then attachments in the order the set-up loop appends them, VBDClothPhysics.cpp:161-219)
     {
@@ -1609,8 +1639,10 @@ static cudaError_t detect(ClothScene& s) {
     k_fill_i32<<<nblk(h.nF + 1), kB, 0, s.stream>>>((int)h.nF + 1, s.faceMinBits.p, rBits);   // resetFaceContactInfo
     CK(cudaMemsetAsync(s.linkCnt.p, 0, (h.nF + 1) * sizeof(int32_t), s.stream));
     CK(cudaMemsetAsync(s.linkCur.p, 0, (h.nF + 1) * sizeof(int32_t), s.stream));
-    k_vf_query<<<nblk(N), kB, 0, s.stream>>>(D, s.P, view_of(s.faceBvh), s.vfCount.p, s.vfList.p, s.vfMinDis.p, s.faceMinBits.p, s.errFlags.p);
-    if (h.nSimE) k_ee_query<<<nblk(h.nSimE), kB, 0, s.stream>>>(D, s.P, view_of(s.edgeBvh), s.eeCount.p, s.eeList.p, s.eeMinDis.p, s.errFlags.p);
+    k_vf_query<<<nblk(N), kB, 0, s.stream>>>(D, s.P, view_of(s.faceBvh), s.vfCount.p, s.vfList.p, s.vfMinDis.p, s.faceMinBits.p, s.errFlags.p,
+                                             s.vfFiltOff.p, s.vfFilt.p);
+    if (h.nSimE) k_ee_query<<<nblk(h.nSimE), kB, 0, s.stream>>>(D, s.P, view_of(s.edgeBvh), s.eeCount.p, s.eeList.p, s.eeMinDis.p, s.errFlags.p,
+                                                                s.eeFiltOff.p, s.eeFilt.p);
     k_link_count<<<nblk(N), kB, 0, s.stream>>>(N, s.vfCount.p, s.vfList.p, s.linkCnt.p);
     CK(cub::DeviceScan::ExclusiveSum(s.scanTmp.p, s.scanTmpBytes, s.linkCnt.p, s.linkOff.p, (int)(h.nF + 1), s.stream));
     k_link_fill<<<nblk(N), kB, 0, s.stream>>>(N, s.linkCap, s.s2o.p, s.vfCount.p, s.vfList.p, s.linkOff.p, s.linkCur.p, s.linkVal.p, s.errFlags.p);
@@ -2020,6 +2052,22 @@ int gaia_b200_cloth_set_sewing(gaia_cloth_handle* h, int mesh, int32_t nSeams, c
     m.sewVerts.assign(verts3, verts3 + 3 * (size_t)nSeams);
     m.sewRatios.assign(ratios, ratios + nSeams);
     m.sewStiffness = sewingStiffness;
+    return GAIA_OK;
+}
+// ObjectParams::filteredPairsPath (TriMeshFEM::generate_sewing_filters, M/TriMesh/TriMesh.h:596-622); applied in k_vf_query / k_ee_query
+int gaia_b200_cloth_set_filtered_pairs(gaia_cloth_handle* h, int mesh, int32_t nVF, const int32_t* vfPairs, int32_t nEE, const int32_t* eePairs) {
+    CREQ(h);
+    ClothScene& s = h->s;
+    if (s.finalized) return cfail(s, GAIA_ERR_STATE, "filtered pairs are set before finalize");
+    if (mesh < 0 || mesh >= (int)s.h.meshes.size()) return cfail(s, GAIA_ERR_INVALID_ARG, "mesh id out of range");
+    ClothMesh& m = s.h.meshes[mesh];
+    if (!m.simulated) return cfail(s, GAIA_ERR_INVALID_ARG, "filtered pairs belong to a simulated mesh");
+    if (nVF < 0 || nEE < 0 || (nVF > 0 && !vfPairs) || (nEE > 0 && !eePairs)) return cfail(s, GAIA_ERR_INVALID_ARG, "bad pair list");
+    for (int i = 0; i < nVF; i++)
+        if (vfPairs[2 * i] < 0 || vfPairs[2 * i] >= m.nV || vfPairs[2 * i + 1] < 0 || vfPairs[2 * i + 1] >= m.nF) return cfail(s, GAIA_ERR_INVALID_ARG, "filtered (vertex, face) out of range");
+    for (int i = 0; i < 2 * nEE; i++) if (eePairs[i] < 0 || eePairs[i] >= m.nE) return cfail(s, GAIA_ERR_INVALID_ARG, "filtered edge out of range");
+    m.filtVF.assign(vfPairs, vfPairs + 2 * (size_t)nVF);
+    m.filtEE.assign(eePairs, eePairs + 2 * (size_t)nEE);
     return GAIA_OK;
 }
 // one entry of PhysicsParams.VertexFaceAttachmentConstraintParams (set-up: VBDClothPhysics.cpp:152-220)

@@ -37,6 +37,7 @@ struct ClothMesh {
     std::vector<int32_t> sewVerts;           // 3 * nSeams
     std::vector<float> sewRatios;
     float sewStiffness = 0.f;
+    std::vector<int32_t> filtVF, filtEE;     // filteredPairsPath: (vertex, face) and (edge, edge) pairs, 2 ints each
     int64_t vBase = 0, fBase = 0, eBase = 0; // offsets in "meshes concatenated" order
 };
 

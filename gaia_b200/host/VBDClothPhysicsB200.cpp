@@ -171,7 +171,7 @@ void VBDClothPhysicsB200::loadRunningparameters(std::string inModelInputFile, st
         m.get("dampingStVK", in.obj.dampingStVK); m.get("dampingBending", in.obj.dampingBending);
         m.get("sewingPath", in.sewingPath); m.get("filteredPairsPath", in.filteredPairsPath); m.get("sewingStiffness", in.sewingStiffness);
         if (!in.sewingPath.empty()) in.sewingPath = resolve(in.sewingPath);
-        if (!in.filteredPairsPath.empty()) throw std::runtime_error("filteredPairsPath (contact pairs excluded by seams) is not supported");
+        if (!in.filteredPairsPath.empty()) in.filteredPairsPath = resolve(in.filteredPairsPath);
         std::vector<int> fp;
         m.get_ints("fixedPoints", fp);
         in.fixedPoints.assign(fp.begin(), fp.end());
@@ -202,6 +202,14 @@ void VBDClothPhysicsB200::loadMeshes(int64_t* nVertsTotal, int64_t* nFacesTotal)
                 for (auto& t : sv->arr) { if (!t.is_array() || t.arr.size() != 3) throw std::runtime_error("sewing \"vertices\" holds triples"); for (auto& x : t.arr) m.sewingVertices.push_back((int32_t)x.as_double()); }
             if (const Value* sr = sj.find("ratios")) for (auto& x : sr->arr) m.sewingRatios.push_back((float)x.as_double());
             if (m.sewingVertices.size() != 3 * m.sewingRatios.size()) throw std::runtime_error("sewing file: one ratio per vertex triple");
+            if (!m.filteredPairsPath.empty()) {       // generate_sewing_filters (M/TriMesh/TriMesh.h:603-621): read only beside a sewing file
+                const Value fj = jsonmin::parse_file(m.filteredPairsPath);
+                auto pairs = [&](const char* key, std::vector<int32_t>& out) {
+                    if (const Value* a = fj.find(key))
+                        for (auto& t : a->arr) { if (!t.is_array() || t.arr.size() != 2) throw std::runtime_error(std::string("filtered pairs \"") + key + "\" holds pairs"); for (auto& x : t.arr) out.push_back((int32_t)x.as_double()); }
+                };
+                pairs("vf", m.filteredVF); pairs("ee", m.filteredEE);
+            }
         }
     }
     if (nVertsTotal) *nVertsTotal = nv;
@@ -223,6 +231,9 @@ void VBDClothPhysicsB200::initialize() {
         check(rc, "gaia_b200_cloth_add_tri_mesh");
         if (!m.sewingRatios.empty()) {
             check(gaia_b200_cloth_set_sewing(h_, rc, (int32_t)m.sewingRatios.size(), m.sewingVertices.data(), m.sewingRatios.data(), m.sewingStiffness), "gaia_b200_cloth_set_sewing");
+            if (!m.filteredVF.empty() || !m.filteredEE.empty())
+                check(gaia_b200_cloth_set_filtered_pairs(h_, rc, (int32_t)(m.filteredVF.size() / 2), m.filteredVF.data(), (int32_t)(m.filteredEE.size() / 2), m.filteredEE.data()),
+                      "gaia_b200_cloth_set_filtered_pairs");
         }
     }
     for (auto& c : colliders_) {       // colliderTriMeshes come after the simulated meshes (triMeshesAll)

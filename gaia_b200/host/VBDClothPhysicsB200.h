@@ -38,6 +38,7 @@ struct ClothModelInput {
     float sewingStiffness = 0.f;
     std::vector<int32_t> sewingVertices;     // 3 per seam, read by loadMeshes()
     std::vector<float> sewingRatios;
+    std::vector<int32_t> filteredVF, filteredEE;   // ObjectParams::filteredPairsPath {"vf": [[v, f], ...], "ee": [[e, e'], ...]}, 2 ints per pair
 };
 
 // PhysicsParams.VertexFaceAttachmentConstraintParams (M/VBDCloth/VBDTriMeshConstraints.h:6-29)

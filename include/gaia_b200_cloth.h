@@ -148,9 +148,15 @@ int gaia_b200_cloth_set_collider_sequence(gaia_cloth_handle* h, int mesh, int32_
  * v0 onto the point (1 - ratio_i) x_v1 + ratio_i x_v2 of the SAME mesh; every vertex of the seam gets the force
  * -m k (x_v0 - (1 - ratio) x_v1 - ratio x_v2) and the Hessian m^2 k I with m = 1, -(1 - ratio), -ratio for v0, v1, v2.
  * Replaces the mesh's seams; before finalize. The colouring passed to add_tri_mesh must keep the three vertices of a seam in
- * different colours (as for the reference, whose colour files are an input). ObjectParams::filteredPairsPath (contact pairs
- * the seams exclude, TriMesh.h:603-621) is not supported: no pair is filtered. */
+ * different colours (as for the reference, whose colour files are an input). */
 int gaia_b200_cloth_set_sewing(gaia_cloth_handle* h, int mesh, int32_t nSeams, const int32_t* verts3, const float* ratios, float sewingStiffness);
+/* Contact pairs the seams of a mesh exclude (ObjectParams::filteredPairsPath = {"vf": [[vertex, face], ...], "ee": [[edge, edge],
+ * ...]}, TriMeshFEM::generate_sewing_filters, M/TriMesh/TriMesh.h:596-622): a listed vertex never pairs with the listed face,
+ * a listed edge never with the listed edge (either way round), of the SAME mesh - neither as a contact nor in the minimum
+ * distances behind the conservative bounds (the ...WithSewing callbacks return before measuring, M/CollisionDetector/
+ * ClothContactDetector.cpp:290-320, 815-852). Edge ids are the reference's (gaia_b200_cloth_get_edges). As in the reference the
+ * lists only take effect for a mesh that also has seams (:969-974, 1011-1016). Replaces the mesh's lists; before finalize. */
+int gaia_b200_cloth_set_filtered_pairs(gaia_cloth_handle* h, int mesh, int32_t nVF, const int32_t* vfPairs, int32_t nEE, const int32_t* eePairs);
 /* One vertex-face attachment (PhysicsParams.VertexFaceAttachmentConstraintParams: vertexConstraintVertexInfos,
  * vertexConstraintTargetFacesInfos, vertexConstraintBarys, vertexConstraintStiffness; M/VBDCloth/VBDTriMeshConstraints.h:6-52,
  * set-up VBDClothPhysics.cpp:152-220, force ::accumulateConstraintForceAndHessian :1464-1498): vertex `vertex` of the simulated

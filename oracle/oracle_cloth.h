@@ -79,6 +79,7 @@ struct TriMesh {
     float sewingStiffness = 0.f;
     std::vector<std::vector<std::pair<int, int>>> sewingVMap;      // per vertex: (seam, order)
     std::vector<std::vector<Attachment>> attachments;              // per vertex (VertexConstraints::attachmentConstraints)
+    std::vector<std::vector<int>> sewingVF, sewingEE;              // filteredPairsPath: per vertex the faces, per edge the edges (sorted) not to be paired with
 };
 
 // ClothDeformerRotator / ClothDeformerTranslater (M/VBDCloth/VBDClothDeformer.h:43-200)
@@ -130,6 +131,7 @@ void cloth_add_translator(ClothScene& s, int mesh, const int32_t* verts, int n, 
 void cloth_set_collider_sequence(ClothScene& s, int mesh, int nKeys, const int32_t* keyFrames, const float* xyz, bool interpolateSubstep, int interpolateIter);
 void cloth_set_sewing(ClothScene& s, int mesh, int nSeams, const int32_t* verts3, const float* ratios, float stiffness);
 int cloth_add_attachment(ClothScene& s, int meshV, int vertex, int meshF, const int32_t faceVerts[3], const float baryOrPos[3], float stiffness);
+void cloth_set_filtered_pairs(ClothScene& s, int mesh, int nVF, const int32_t* vfPairs, int nEE, const int32_t* eePairs);
 void cloth_sewing_force_hessian(const TriMesh& m, int iV, V3& force, M3& hessian);
 void cloth_constraint_force_hessian(const ClothScene& s, int iMesh, int vId, V3& force, M3& hessian);
 void cloth_transform_points(const gaia_cloth_object_params& obj, std::vector<V3>& pos);

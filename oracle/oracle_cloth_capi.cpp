@@ -61,6 +61,16 @@ int oracle_cloth_set_sewing(void* h, int mesh, int32_t nSeams, const int32_t* ve
     cloth_set_sewing(*s, mesh, nSeams, verts3, ratios, stiffness);
     return GAIA_OK;
 }
+int oracle_cloth_set_filtered_pairs(void* h, int mesh, int32_t nVF, const int32_t* vfPairs, int32_t nEE, const int32_t* eePairs) {
+    ClothScene* s = (ClothScene*)h;
+    if (s->finalized) return GAIA_ERR_STATE;
+    if (mesh < 0 || mesh >= (int)s->meshes.size() || !s->meshes[mesh].simulated || nVF < 0 || nEE < 0 || (nVF && !vfPairs) || (nEE && !eePairs)) return GAIA_ERR_INVALID_ARG;
+    const TriMesh& m = s->meshes[mesh];
+    for (int i = 0; i < nVF; i++) if (vfPairs[2 * i] < 0 || vfPairs[2 * i] >= m.nV || vfPairs[2 * i + 1] < 0 || vfPairs[2 * i + 1] >= m.nF) return GAIA_ERR_INVALID_ARG;
+    for (int i = 0; i < 2 * nEE; i++) if (eePairs[i] < 0 || eePairs[i] >= m.nE) return GAIA_ERR_INVALID_ARG;
+    cloth_set_filtered_pairs(*s, mesh, nVF, vfPairs, nEE, eePairs);
+    return GAIA_OK;
+}
 int oracle_cloth_add_attachment(void* h, int meshV, int32_t vertex, int meshF, const int32_t* faceVerts, const float* baryOrPos, float stiffness) {
     ClothScene* s = (ClothScene*)h;
     if (s->finalized) return GAIA_ERR_STATE;

@@ -132,6 +132,8 @@ static void vf_candidate(const ClothScene& s, int qMesh, int qV, V3 queryPt, int
     if (fMesh >= s.numSim && qMesh >= s.numSim) return;                 // collider callback: only simulated meshes query colliders
     const int* fv = &tm.faces[3 * f];
     if (qMesh == fMesh && (fv[0] == qV || fv[1] == qV || fv[2] == qV)) return;
+    // ...WithSewing (:290-438), attached to meshes that have seams (:969-974): the filtered vertex-face pairs of that mesh are skipped
+    if (qMesh == fMesh && !tm.sewingVertices.empty() && !tm.sewingVF.empty() && std::binary_search(tm.sewingVF[qV].begin(), tm.sewingVF[qV].end(), f)) return;
     V3 bary; int type;
     const V3 cp = closest_point_triangle(queryPt, tm.pos[fv[0]], tm.pos[fv[1]], tm.pos[fv[2]], bary, type);
     const float d = norm(queryPt - cp);
@@ -168,6 +170,8 @@ static void ee_candidate(const ClothScene& s, int qMesh, int qE, int tMesh, int 
     if (qMesh == tMesh) {
         if (tE == qE) return;
         if (Q.eV1 == T.eV1 || Q.eV1 == T.eV2 || Q.eV2 == T.eV1 || Q.eV2 == T.eV2) return;
+        // triMeshEdgeContactQueryFuncWithSewing (:815-901, attached at :1011-1016): the filtered edge pairs
+        if (!tm.sewingVertices.empty() && !tm.sewingEE.empty() && std::binary_search(tm.sewingEE[qE].begin(), tm.sewingEE[qE].end(), tE)) return;
     }
     const V3 p1 = qm.pos[Q.eV1], p2 = qm.pos[Q.eV2], q1 = tm.pos[T.eV1], q2 = tm.pos[T.eV2];
     V3 c1, c2; float mua, mub;

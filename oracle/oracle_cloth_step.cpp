@@ -335,6 +335,17 @@ void cloth_set_sewing(ClothScene& s, int mesh, int nSeams, const int32_t* verts3
     }
 }
 
+// TriMeshFEM::generate_sewing_filters, the filteredPairsPath part (M/TriMesh/TriMesh.h:596-622): {"vf": [[v, f], ...], "ee": [[e, e'], ...]};
+// the vertex-face pairs go one way, the edge pairs both ways
+void cloth_set_filtered_pairs(ClothScene& s, int mesh, int nVF, const int32_t* vfPairs, int nEE, const int32_t* eePairs) {
+    TriMesh& m = s.meshes[mesh];
+    m.sewingVF.assign(m.nV, {}); m.sewingEE.assign(m.nE, {});
+    for (int i = 0; i < nVF; i++) m.sewingVF[vfPairs[2 * i]].push_back(vfPairs[2 * i + 1]);
+    for (int i = 0; i < nEE; i++) { m.sewingEE[eePairs[2 * i]].push_back(eePairs[2 * i + 1]); m.sewingEE[eePairs[2 * i + 1]].push_back(eePairs[2 * i]); }
+    for (auto& l : m.sewingVF) { std::sort(l.begin(), l.end()); l.erase(std::unique(l.begin(), l.end()), l.end()); }
+    for (auto& l : m.sewingEE) { std::sort(l.begin(), l.end()); l.erase(std::unique(l.begin(), l.end()), l.end()); }
+}
+
 // the set-up loop of VBDClothSimulationFramework::initialize (M/VBDCloth/VBDClothPhysics.cpp:161-219)
 int cloth_add_attachment(ClothScene& s, int meshV, int vertex, int meshF, const int32_t faceVerts[3], const float baryOrPos[3], float stiffness) {
     TriMesh& mv = s.meshes[meshV];

@@ -101,7 +101,9 @@ def add_constraints(tmp, m, p):
     with open(os.path.join(tmp, "seams.json"), "w") as fh:
         json.dump({"vertices": [[44, 48, 59], [2, 22, 23]], "ratios": [0.4, 1.0]}, fh)
     mj = json.load(open(m))
-    mj["Models"][0].update(sewingPath="${REPO_ROOT}\\seams.json", sewingStiffness=300.0)
+    with open(os.path.join(tmp, "pairs.json"), "w") as fh:
+        json.dump({"vf": [[44, 90], [45, 91]], "ee": [[10, 200]]}, fh)
+    mj["Models"][0].update(sewingPath="${REPO_ROOT}\\seams.json", sewingStiffness=300.0, filteredPairsPath="${REPO_ROOT}\\pairs.json")
     json.dump(mj, open(m, "w"))
     pj = json.load(open(p))
     pj["PhysicsParams"]["VertexFaceAttachmentConstraintParams"] = {
@@ -116,6 +118,7 @@ def test_sewing_and_attachments_from_scene_files(tmp_path):
     phys, meshes, pj = cloth_host.load_cloth_scene_json(m, p, str(tmp_path))
     sewing, att = cloth_host.load_cloth_constraints(m, p, str(tmp_path))
     assert len(sewing) == 1 and sewing[0][0] == 0 and sewing[0][1].tolist() == [[44, 48, 59], [2, 22, 23]] and sewing[0][3] == 300.0
+    assert sewing[0][4].tolist() == [[44, 90], [45, 91]] and sewing[0][5].tolist() == [[10, 200]]
     assert [a[:3] for a in att] == [(0, 0, -1), (0, 9, 1), (0, 55, 0)] and att[1][3].tolist() == [0, 1, 2] and att[2][5] == 500.0
     o = cloth_host.build_scene(OracleClothScene, phys, meshes, constraints=(sewing, att), threads=2)
     plain = cloth_host.build_scene(OracleClothScene, phys, meshes, threads=2)

@@ -133,6 +133,30 @@ def test_no_coupled_pair_shares_a_group():
                 assert gid[(mf, a)] != gid[(mv, a)]
 
 
+def test_seam_filtered_pairs_contact_sets_bit_exact():
+    """gaia_b200_cloth_set_filtered_pairs (the reference's filteredPairsPath): on a sheet folded onto itself every 7th detected
+    self contact is declared a filtered pair; contact sets and conservative bounds stay bit-identical to the oracle's, the pairs
+    are gone, and without seams the lists are inert (tests/test_oracle_cloth.py checks the oracle's side of this)."""
+    from cloth_filter_scene import build, pick_pairs
+    base = build(OracleClothScene, dict(threads=2))
+    base.detect_contacts()
+    vf0, ee0 = base.vf_contacts(), base.ee_contacts()
+    vf_pairs, ee_pairs = pick_pairs(vf0, ee0)
+    g = build(cloth.ClothScene, {}, vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    o = build(OracleClothScene, dict(threads=2), vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    g.detect_contacts(); o.detect_contacts()
+    vf1, ee1 = o.vf_contacts(), o.ee_contacts()
+    assert 50 < len(vf1) < len(vf0) and 50 < len(ee1) < len(ee0)
+    assert np.array_equal(g.vf_contacts(), vf1) and np.array_equal(g.ee_contacts(), ee1)
+    assert np.array_equal(g.conservative_bounds(0), o.conservative_bounds(0))
+    have = {(int(r[1]), int(r[3])) for r in g.vf_contacts()}
+    assert not any((int(v), int(f)) in have for v, f in vf_pairs)
+    g2 = build(cloth.ClothScene, {}, seams=False, vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    g2.detect_contacts()
+    assert np.array_equal(g2.vf_contacts(), vf0) and np.array_equal(g2.ee_contacts(), ee0)
+    assert np.array_equal(g2.conservative_bounds(0), base.conservative_bounds(0))
+
+
 def test_constraint_arguments_are_checked():
     v, f = cloth.grid_cloth(4, 1.0)
     for cls, kw in ((cloth.ClothScene, {}), (OracleClothScene, dict(threads=1))):
@@ -150,6 +174,13 @@ def test_constraint_arguments_are_checked():
             s.add_attachment(0, 16, -1, None, [0, 0, 0])              # vertex out of range
         with pytest.raises(GaiaError):
             s.add_attachment(0, 3, 1, [0, 1, 9], [0.3, 0.3, 0.4])     # face vertex out of range
+        with pytest.raises(GaiaError):
+            s.set_filtered_pairs(0, [[0, 18]], [])                    # the 4 x 4 sheet has 18 faces: 0 .. 17
+        with pytest.raises(GaiaError):
+            s.set_filtered_pairs(0, [], [[0, 33]])                    # ... and 33 edges
+        with pytest.raises(GaiaError):
+            s.set_filtered_pairs(1, [[0, 0]], [])                     # colliders have no seams
+        s.set_filtered_pairs(0, [[0, 17]], [[0, 32]])
         s.add_attachment(0, 3, 1, [0, 1, 2], [0.3, 0.3, 0.4])
         s.set_sewing(0, [[0, 5, 6]], [0.5], 1e3)
         s.finalize()

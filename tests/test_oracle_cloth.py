@@ -215,3 +215,37 @@ def test_accelerator_and_initialization_types_run():
         x = o.positions(0)
         assert np.isfinite(x).all() and np.allclose(x[[0, 5]], v[[0, 5]])
         assert x[:, 1].min() < 1.0 - 1e-3
+
+
+def test_seam_filtered_pairs_are_skipped_before_they_are_measured():
+    """ObjectParams::filteredPairsPath (TriMeshFEM::generate_sewing_filters, M/TriMesh/TriMesh.h:596-622; the ...WithSewing callbacks,
+    M/CollisionDetector/ClothContactDetector.cpp:290-320, 815-852 - Embree-bound, so a restatement): on a sheet folded onto
+    itself every 7th detected self contact is declared a filtered pair. Those pairs are gone (either way round for edges), the
+    lists of vertices / edges that are in no filtered pair are untouched, a filtered vertex's conservative bound can only grow,
+    the grid and brute force agree, and - as in the reference, which attaches the filtering callbacks only to meshes with seams -
+    the lists do nothing without seams."""
+    from cloth_filter_scene import build, pick_pairs
+    base = build(OracleClothScene, dict(threads=2))
+    base.detect_contacts()
+    vf0, ee0 = base.vf_contacts(), base.ee_contacts()
+    assert len(vf0) > 100 and len(ee0) > 100
+    vf_pairs, ee_pairs = pick_pairs(vf0, ee0)
+    o = build(OracleClothScene, dict(threads=2), vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    o.detect_contacts()
+    vf1, ee1 = o.vf_contacts(), o.ee_contacts()
+    have_vf = {(int(r[1]), int(r[3])) for r in vf1}
+    assert not any((int(v), int(f)) in have_vf for v, f in vf_pairs)
+    have_ee = {(int(r[1]), int(r[3])) for r in ee1}
+    assert not any((int(a), int(b)) in have_ee or (int(b), int(a)) in have_ee for a, b in ee_pairs)
+    assert len(vf1) < len(vf0) and len(ee1) < len(ee0)
+    touched_v = set(vf_pairs[:, 0].tolist()); touched_e = set(ee_pairs.ravel().tolist())
+    keep = lambda rows, touched: np.array([r for r in rows if int(r[1]) not in touched])
+    assert np.array_equal(keep(vf0, touched_v), keep(vf1, touched_v)) and np.array_equal(keep(ee0, touched_e), keep(ee1, touched_e))
+    b0, b1 = base.conservative_bounds(0), o.conservative_bounds(0)
+    assert (b1 >= b0).all() and (b1 > b0).any()
+    bf = build(OracleClothScene, dict(threads=2), vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    bf.set_brute_force(True); bf.detect_contacts()
+    assert np.array_equal(bf.vf_contacts(), vf1) and np.array_equal(bf.ee_contacts(), ee1) and np.array_equal(bf.conservative_bounds(0), b1)
+    ns = build(OracleClothScene, dict(threads=2), seams=False, vf_pairs=vf_pairs, ee_pairs=ee_pairs)
+    ns.detect_contacts()
+    assert np.array_equal(ns.vf_contacts(), vf0) and np.array_equal(ns.ee_contacts(), ee0)
