@@ -165,6 +165,7 @@ def bind_scene_api(lib, prefix):
         "get_relations": ([P, C.c_int, IP, C.c_int64, C.POINTER(C.c_int64)], C.c_int),
         "set_partition_mode": ([P, C.c_int32, C.c_int32], C.c_int), "set_ghosts": ([P, C.c_int, IP, C.c_int32], C.c_int),
         "set_line_search": ([P, C.c_int32, C.c_float, C.c_float, C.c_int32], C.c_int), "line_search_shrinks": ([P], C.c_int64),
+        "set_bowl_ground": ([P, FP, C.c_float, C.c_int32], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, prefix + name)
@@ -224,6 +225,11 @@ class SceneBase:
     def line_search_shrinks(self):
         """trial steps the line search rejected so far (each one shrank alpha by tau)"""
         return int(getattr(self._lib, self._prefix + "line_search_shrinks")(self.h))
+
+    def set_bowl_ground(self, center, radius, cap=False):
+        """centre, radius and cap of the bowl ground of a scene created with useBowlGround=1 (the reference's bowlCenter / bowlRadius / bowlCap)"""
+        c = _f32(np.asarray(center, np.float32))
+        self._call("set_bowl_ground", _fp(c), float(radius), int(bool(cap)))
 
     def run_iterations(self, n=1):
         self._call("run_iterations", n)

@@ -58,7 +58,6 @@ int gaia_b200_create(const gaia_physics_params* phys, const gaia_collision_param
         return GAIA_ERR_NO_DEVICE;
     }
     if (device < 0 || device >= nDev) { g_createErr = "device ordinal out of range"; return GAIA_ERR_INVALID_ARG; }
-    if (phys->useBowlGround) { g_createErr = "useBowlGround is outside the hot path (CPU-only feature of the reference)"; return GAIA_ERR_UNSUPPORTED; }
     if (phys->numSubsteps <= 0 || phys->iterations < 0 || !(phys->timeStep > 0)) { g_createErr = "bad step parameters"; return GAIA_ERR_INVALID_ARG; }
     if ((e = cudaSetDevice(device)) != cudaSuccess) { g_createErr = cudaGetErrorString(e); return GAIA_ERR_CUDA; }
     gaia_handle* h = new gaia_handle();
@@ -86,7 +85,6 @@ int gaia_b200_add_tet_mesh(gaia_handle* h, int32_t nV, int32_t nT, const float* 
     if (nV <= 0 || nT <= 0 || !xyz || !tets || !obj || nColors <= 0 || !color_offsets || !color_verts || nFixed < 0 || (nFixed && !fixedPoints))
         return fail(s, GAIA_ERR_INVALID_ARG, "add_tet_mesh: bad argument");
     if (s.meshes.size() >= (1u << 24) - 1) return fail(s, GAIA_ERR_INVALID_ARG, "too many meshes");
-    if (obj->initializationType == 5) return fail(s, GAIA_ERR_UNSUPPORTED, "initializationType 5 (symplectic Euler) is not on the hot path");
     for (int64_t i = 0; i < 4 * (int64_t)nT; i++) if (tets[i] < 0 || tets[i] >= nV) return fail(s, GAIA_ERR_INVALID_ARG, "tet index out of range");
     for (int i = 0; i < nFixed; i++) if (fixedPoints[i] < 0 || fixedPoints[i] >= nV) return fail(s, GAIA_ERR_INVALID_ARG, "fixed point out of range");
     s.meshes.emplace_back();
@@ -138,6 +136,12 @@ int gaia_b200_finalize(gaia_handle* h) {
     if (e != cudaSuccess) return cuda_fail(s, e);
     e = collision_init(s);
     if (e != cudaSuccess) return cuda_fail(s, e);
+    for (auto& m : s.meshes)
+        if (m.obj.initializationType == 5 && !s.symScratch.p) {      // symplectic-Euler initial guess: per-tet tables + a Jacobi target
+            e = linesearch_upload(s);
+            if (e == cudaSuccess) e = s.symScratch.alloc((size_t)s.nVerts);
+            if (e != cudaSuccess) return cuda_fail(s, e);
+        }
     s.finalized = true;
     return GAIA_OK;
 }
@@ -550,6 +554,7 @@ int gaia_b200_set_solver_lanes(gaia_handle* h, int lanes) {
 int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float tauGD, int32_t maxIters) {
     REQUIRE(h); FINALIZED(h);
     Scene& s = h->s;
+    if (enabled && s.phys.useBowlGround) return fail(s, GAIA_ERR_UNSUPPORTED, "line search with the bowl ground: its merit energy has no bowl term");
     if (enabled && (!(tau > 0.f && tau < 1.f) || !(tauGD > 0.f && tauGD < 1.f) || maxIters < 0 || maxIters > 64))
         return fail(s, GAIA_ERR_INVALID_ARG, "line search: 0 < tau, tauGD < 1 and 0 <= maxIters <= 64");
     cudaSetDevice(s.device);
@@ -560,6 +565,17 @@ int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float 
         s.lineSearch.tau = tau; s.lineSearch.tauGD = tauGD; s.lineSearch.maxIters = maxIters;
     }
     s.lineSearch.enabled = enabled != 0;
+    return GAIA_OK;
+}
+// BasePhysicsParams::bowlCenter / bowlRadius / bowlCap (M/Parameters/PhysicsParameters.h:18, 40-45) for a scene created with useBowlGround
+int gaia_b200_set_bowl_ground(gaia_handle* h, const float center[3], float radius, int32_t cap) {
+    REQUIRE(h);
+    Scene& s = h->s;
+    if (!center || !(radius > 0.f)) return fail(s, GAIA_ERR_INVALID_ARG, "bowl ground: a centre and a positive radius");
+    for (int d = 0; d < 3; d++) { s.bowl.center[d] = center[d]; s.stepParams.bowlCenter[d] = center[d]; }
+    s.bowl.radius = radius; s.bowl.cap = cap != 0;
+    s.stepParams.bowlRadius = radius; s.stepParams.bowlCap = cap != 0;
+    if (s.iterGraphExec) { cudaSetDevice(s.device); cudaGraphExecDestroy(s.iterGraphExec); s.iterGraphExec = nullptr; }   // the captured launches hold the old values
     return GAIA_OK;
 }
 int64_t gaia_b200_line_search_shrinks(gaia_handle* h) {

@@ -60,6 +60,8 @@ struct StepParamsDev {
     float stepSize, stepSizeGD;
     float kCollision;
     int32_t usePlaneGround, associateGravityWithInertia;
+    int32_t useBowlGround, bowlCap;      // BasePhysicsParams::useBowlGround / bowlCap / bowlCenter / bowlRadius (M/Parameters/PhysicsParameters.h:18, 40-45)
+    float bowlCenter[3], bowlRadius;
 };
 
 struct Scene;   // defined in scene_impl.h (needs CUDA types)

@@ -155,6 +155,9 @@ struct Scene {
     gaia_stats stats;
     // gaia_b200_set_line_search (sweep.cu: k_sweep_linesearch): plain per-tet tables, uploaded when the option is first switched on
     struct { bool enabled = false; float tau = 0.5f, tauGD = 0.1f; int maxIters = 16; } lineSearch;
+    struct { float center[3] = {0.f, 0.f, 0.f}; float radius = 1.f; int cap = 0; } bowl;      // used when phys.useBowlGround (gaia_b200_set_bowl_ground)
+    DevBuf<int32_t> bowlNoContact, bowlZeroOff;   // bowl ground without contacts: empty contact tables for the contact variant of the sweep ([N] = -1, [N + 1] = 0)
+    DevBuf<float4> symScratch;          // initializationType 5: the Jacobi target of the symplectic-Euler initial guess (N; only if some mesh asks for it)
     DevBuf<int32_t> lsOff; DevBuf<int2> lsEnt; DevBuf<int4> lsTetSid; DevBuf<float4> lsTetDm; DevBuf<unsigned long long> lsShrinks;
     float lazyRefitMargin = -1.f;  // gaia_b200_set_lazy_refit_margin: margin of the DCD trees' boxes in typical tet edges; < 0: adaptive, from 0.2
     int profiling = 0;             // 0 off; 1 per-phase timers + an event pair around every colour-solve launch; 2 per-phase timers only (the colour loop stays a CUDA graph)
@@ -177,6 +180,7 @@ bool build_tile_streams(Scene& s, int tileV);
 // sweep.cu: the per-colour vertex solve over tiles (TMA-fed persistent blocks)
 cudaError_t sweep_launch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv, const HaloView* hv);
 cudaError_t linesearch_upload(Scene& s);
+cudaError_t sweep_symplectic_guess(Scene& s);      // initializationType 5 (no-op unless symScratch was allocated at finalize)
 cudaError_t sweep_launch_linesearch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv);
 bool sweep_multi_available(Scene& s);
 cudaError_t sweep_launch_multi(Scene& s, int firstGroup, int nSteps, int frictionFromStep, const HaloView* hv);

@@ -309,6 +309,13 @@ cudaError_t device_upload(Scene& s) {
     sp.kBoundary = s.phys.boundaryCollisionStiffness; sp.muBoundary = s.phys.boundaryFrictionDynamic; sp.epsVBoundary = s.phys.boundaryFrictionEpsV;
     sp.stepSize = s.phys.stepSize; sp.stepSizeGD = s.phys.stepSizeGD; sp.kCollision = s.phys.collisionStiffness;
     sp.usePlaneGround = s.phys.usePlaneGround; sp.associateGravityWithInertia = s.phys.associateGravityWithInertia;
+    sp.useBowlGround = s.phys.useBowlGround; sp.bowlCap = s.bowl.cap; sp.bowlRadius = s.bowl.radius;
+    for (int d = 0; d < 3; d++) sp.bowlCenter[d] = s.bowl.center[d];
+    if (s.phys.useBowlGround) {      // the bowl term lives in the contact variant of the sweep only: it needs (empty) contact tables
+        std::vector<int32_t> none(N, -1);
+        CK(s.bowlNoContact.alloc(N)); CK(cudaMemcpy(s.bowlNoContact.p, none.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CK(s.bowlZeroOff.alloc(N + 1)); CK(cudaMemset(s.bowlZeroOff.p, 0, (N + 1) * sizeof(int32_t)));
+    }
     s.pinnedIOBytes = (size_t)(3 * N + 16) * sizeof(float);
     CK(cudaMallocHost((void**)&s.pinnedIO, s.pinnedIOBytes));
     s.meshParamsDirty = true;
@@ -327,12 +334,16 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     //  A scene WITH a collision pipeline may still use the fused exchange while no rank holds an active contact - there
     //  is no pre-pass then - which the ranks agree on after every detection: halo_vote)
     const bool lineSearch = s.lineSearch.enabled;      // (its kernel does not push: separate halo launches)
-    const bool canFuse = halo && !s.phys.useAccelerator && !lineSearch && halo_view(s, hv);
+    const bool bowl = s.phys.useBowlGround != 0;      // the bowl term is compiled into the contact variant of the sweep only (sweep.cu: vertex_tail)
+    const bool canFuse = halo && !s.phys.useAccelerator && !lineSearch && !bowl && halo_view(s, hv);
     bool fused = canFuse && !s.cs;
     ContactView cv; std::memset(&cv, 0, sizeof(cv));
     const uint8_t* colliding = nullptr;
     // (captured: the contact variant runs every substep, with device-sized pre-passes; empty tables when nothing touches)
     bool hasContacts = collision_contact_view(s, cv, &colliding, captured);
+    // the contact variant with empty tables when the bowl is on and nothing touches
+    auto bowl_tables = [&]() { if (bowl && !hasContacts) { std::memset(&cv, 0, sizeof(cv)); cv.contactOfVertex = s.bowlNoContact.p; cv.relOff = s.bowlZeroOff.p; } };
+    bowl_tables();
     auto agree = [&]() -> cudaError_t {
         if (!canFuse || !s.cs) return cudaSuccess;
         bool any = true;
@@ -377,7 +388,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
     //  multi-colour launch, which in turn is 3 % faster than per-colour launches issued by the host. So: loops that replay
     //  from a graph keep one launch per colour; loops the host has to issue - intermediate detection cuts them into
     //  stretches - use one multi-colour launch per stretch)
-    const bool useMulti = s.multiStepMode != 0 && !s.phys.useAccelerator && !lineSearch && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
+    const bool useMulti = s.multiStepMode != 0 && !s.phys.useAccelerator && !lineSearch && !bowl && G > 0 && !(captured || graphShape) && sweep_multi_available(s);
     for (int it = 0; it < nIters; it++) {
         const int applyFriction = it >= s.phys.frictionStartIter;
         // Contact-free stretch of iterations (up to the next intermediate detection): ONE launch sweeps all its colours, with
@@ -402,6 +413,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
                 CK(collision_ccd(s));
                 CK(collision_prepare(s));
                 hasContacts = collision_contact_view(s, cv, &colliding);
+                bowl_tables();
                 CK(agree());
             }
             continue;
@@ -420,8 +432,8 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             CK(prof_begin(1));
             hv.epochOffset = batch;
             if (fused) batch++;
-            if (ve > vb) CK(lineSearch ? sweep_launch_linesearch(s, g, applyFriction, hasContacts, cv)
-                                       : sweep_launch(s, g, applyFriction, hasContacts, cv, fused ? &hv : nullptr));
+            if (ve > vb) CK(lineSearch ? sweep_launch_linesearch(s, g, applyFriction, hasContacts || bowl, cv)
+                                       : sweep_launch(s, g, applyFriction, hasContacts || bowl, cv, fused ? &hv : nullptr));
             prof_end();
             s.stats.kernelLaunches++; s.stats.colourSweeps++;
             if (fused) { if (ve > vb) halo_count_fused(s, g); }    // pushed by the solve launch itself, published by the next one
@@ -445,6 +457,7 @@ static cudaError_t enqueue_iterations(Scene& s, int nIters, bool allowIntermedia
             CK(collision_ccd(s));
             CK(collision_prepare(s));
             hasContacts = collision_contact_view(s, cv, &colliding);
+            bowl_tables();
             CK(agree());
         }
     }
@@ -503,6 +516,7 @@ static cudaError_t initial_step(Scene& s) {
                                                    s.meshParams.p, s.meshSubsteps.p, s.stepParams);
     k_count_substeps<<<nblk((int64_t)s.meshes.size(), 128), 128, 0, s.stream>>>((int)s.meshes.size(), s.meshParams.p, s.meshSubsteps.p);
     s.stats.kernelLaunches += 2;
+    CK(sweep_symplectic_guess(s));      // initializationType 5: k_initial_step left those meshes where they were
     return cudaGetLastError();
 }
 

@@ -196,7 +196,42 @@ __device__ __forceinline__ bool vertex_tail(int s, float3 x, float4 ys, float3 x
         F2 += (m * (ys.z - x.z)) * sp.dtSqrReciprocal;
         h00 += w; h11 += w; h22 += w;
     }
-    if (sp.usePlaneGround) {   // world-box penalty + friction, per violated axis (CPU semantics)
+    if (HAS_CONTACTS && sp.useBowlGround) {
+        // the inside of a sphere as the ground (accumlateBoundaryForceAndHessian, VBDPhysics.cpp:2824-2864), as written there -
+        // including the sign of its Hessian. Compiled into the contact variant only (scenes with the bowl are routed to it with
+        // empty contact tables when nothing touches), so the contact-free sweep is the same code as without this feature.
+        const float3 rel = make_float3(x.x - sp.bowlCenter[0], x.y - sp.bowlCenter[1], x.z - sp.bowlCenter[2]);
+        const float dist = sqrtf(rel.x * rel.x + rel.y * rel.y + rel.z * rel.z);
+        if ((sp.bowlCap || !(rel.y > 0.f)) && !(dist < sp.bowlRadius)) {
+            const float3 dir = make_float3(rel.x / dist, rel.y / dist, rel.z / dist);
+            const float depth = dist - sp.bowlRadius;
+            const float fk = -depth * sp.kBoundary;
+            F0 += fk * dir.x; F1 += fk * dir.y; F2 += fk * dir.z;
+            const float rd = sp.bowlRadius / dist, kB = sp.kBoundary;
+            h00 += kB * ((-1.f + dir.x * dir.x) + rd * (1.f - dir.x * dir.x));
+            h11 += kB * ((-1.f + dir.y * dir.y) + rd * (1.f - dir.y * dir.y));
+            h22 += kB * ((-1.f + dir.z * dir.z) + rd * (1.f - dir.z * dir.z));
+            h01 += kB * (dir.x * dir.y + rd * (0.f - dir.x * dir.y));
+            h02 += kB * (dir.x * dir.z + rd * (0.f - dir.x * dir.z));
+            h12 += kB * (dir.y * dir.z + rd * (0.f - dir.y * dir.z));
+            if (applyFriction) {
+                // T = [normalize(dir x e_z), normalize(dir x T0)], u = T^T (x - x_prev); computeVertexFriction (:2563-2592)
+                float3 t0 = make_float3(dir.y, -dir.x, 0.f);
+                const float n0 = sqrtf(t0.x * t0.x + t0.y * t0.y + t0.z * t0.z);
+                t0 = make_float3(t0.x / n0, t0.y / n0, t0.z / n0);
+                float3 t1 = make_float3(dir.y * t0.z - dir.z * t0.y, dir.z * t0.x - dir.x * t0.z, dir.x * t0.y - dir.y * t0.x);
+                const float n1 = sqrtf(t1.x * t1.x + t1.y * t1.y + t1.z * t1.z);
+                t1 = make_float3(t1.x / n1, t1.y / n1, t1.z / n1);
+                const float3 dx = make_float3(x.x - xp.x, x.y - xp.y, x.z - xp.z);
+                const float u0 = t0.x * dx.x + t0.y * dx.y + t0.z * dx.z, u1 = t1.x * dx.x + t1.y * dx.y + t1.z * dx.z;
+                float fa, fb, haa;
+                box_friction(sp.muBoundary, depth * sp.kBoundary, u0, u1, sp.epsVBoundary * sp.dt, fa, fb, haa);
+                F0 += fa * t0.x + fb * t1.x; F1 += fa * t0.y + fb * t1.y; F2 += fa * t0.z + fb * t1.z;
+                h00 += haa * (t0.x * t0.x + t1.x * t1.x); h11 += haa * (t0.y * t0.y + t1.y * t1.y); h22 += haa * (t0.z * t0.z + t1.z * t1.z);
+                h01 += haa * (t0.x * t0.y + t1.x * t1.y); h02 += haa * (t0.x * t0.z + t1.x * t1.z); h12 += haa * (t0.y * t0.z + t1.y * t1.z);
+            }
+        }
+    } else if (sp.usePlaneGround) {   // world-box penalty + friction, per violated axis (CPU semantics)
         const float xs[3] = {x.x, x.y, x.z};
         float Fb[3] = {0.f, 0.f, 0.f}, Hb[3] = {0.f, 0.f, 0.f};
 #pragma unroll
@@ -681,7 +716,7 @@ static void fill_common(Scene& s, SweepArgs& a) {
     a.mp = s.meshParams.p; a.sp = s.stepParams; a.errFlags = s.errFlags.p;
     a.needPrev = 0;
     for (auto& m : s.meshes) if (m.obj.dampingHydrostatic != 0.f || m.obj.dampingDeviatoric != 0.f) a.needPrev = 1;
-    if (s.phys.usePlaneGround && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
+    if ((s.phys.usePlaneGround || s.phys.useBowlGround) && s.phys.boundaryFrictionDynamic != 0.f) a.needPrev = 1;
     a.allActive = 1;
     for (auto& m : s.meshes) if (!m.activeForMaterialSolve) a.allActive = 0;
 }
@@ -908,6 +943,51 @@ cudaError_t linesearch_upload(Scene& s) {
     CK(cudaMemcpy(s.lsTetDm.p, dm.data(), dm.size() * sizeof(float4), cudaMemcpyHostToDevice));
     CK(cudaMemset(s.lsShrinks.p, 0, sizeof(unsigned long long)));
     return cudaSuccess;
+}
+
+// ------------------------------------------------------------------------------------------------ initializationType 5
+// VBDBaseTetMesh::forwardStepSimplecticEuler (M/VBD/VBD_BaseMaterial.cpp:134-147, the initial guess of initializationType 5):
+// the elastic force of EVERY vertex at the positions the substep starts from (VBDTetMeshNeoHookean::evaluateInternalForce /
+// accumlateMaterialForce, VBD_NeoHookean.cpp:29-37, 781-870: no damping), then velocity = velocitiesPrev + dt f / mass and
+// position += velocity dt - fixed vertices included, as in the reference. Jacobi over the mesh: the new positions go to a
+// scratch array and are copied back by a second launch. Runs once per substep over the per-tet tables of the line search;
+// scenes without a type-5 mesh launch nothing.
+__global__ void __launch_bounds__(128)
+k_symplectic_guess(const LsArgs a, int n, float4* __restrict__ vel, const float* __restrict__ mass, float4* __restrict__ out) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const MeshParamsDev* P = a.mp + (__ldg(a.vtx2 + s).w & 0x00FFFFFF);
+    if (!P->activeSolve || P->initType != 5) return;
+    const float3 x = f3(a.pos[s]);
+    float3 dEdx = make_float3(0.f, 0.f, 0.f);
+    float s1 = 0.f, G[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    ls_elastic<true>(a, s, __ldg(a.off + s), __ldg(a.off + s + 1), P->miu, P->lmbd, P->a, x, dEdx, s1, G);
+    const float dt = a.sp.dt, invMass = 1.f / __ldg(mass + s);
+    const float4 vp = vel[s];
+    const float3 v = make_float3(__fadd_rn(vp.x, __fmul_rn(__fmul_rn(dt, -dEdx.x), invMass)), __fadd_rn(vp.y, __fmul_rn(__fmul_rn(dt, -dEdx.y), invMass)),
+                                 __fadd_rn(vp.z, __fmul_rn(__fmul_rn(dt, -dEdx.z), invMass)));
+    vel[s] = make_float4(v.x, v.y, v.z, 0.f);      // (the reference stores it too; updateVelocities overwrites it)
+    out[s] = make_float4(__fadd_rn(x.x, __fmul_rn(v.x, dt)), __fadd_rn(x.y, __fmul_rn(v.y, dt)), __fadd_rn(x.z, __fmul_rn(v.z, dt)), 0.f);
+}
+
+__global__ void k_symplectic_apply(int n, const int4* __restrict__ vtx2, const MeshParamsDev* __restrict__ mp, const float4* __restrict__ in, float4* __restrict__ pos) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const MeshParamsDev* P = mp + (__ldg(vtx2 + s).w & 0x00FFFFFF);
+    if (!P->activeSolve || P->initType != 5) return;
+    pos[s] = in[s];
+}
+
+cudaError_t sweep_symplectic_guess(Scene& s) {
+    if (!s.symScratch.p) return cudaSuccess;
+    const int N = (int)s.nVerts;
+    LsArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.pos = s.pos.p; a.vtx2 = s.vtx2.p; a.off = s.lsOff.p; a.ent = s.lsEnt.p; a.tetSid = s.lsTetSid.p; a.tetDm = s.lsTetDm.p; a.mp = s.meshParams.p; a.sp = s.stepParams;
+    k_symplectic_guess<<<(N + 127) / 128, 128, 0, s.stream>>>(a, N, s.vel.p, s.mass.p, s.symScratch.p);
+    k_symplectic_apply<<<(N + 255) / 256, 256, 0, s.stream>>>(N, s.vtx2.p, s.meshParams.p, s.symScratch.p, s.pos.p);
+    s.stats.kernelLaunches += 2;
+    return cudaGetLastError();
 }
 
 cudaError_t sweep_launch_linesearch(Scene& s, int group, int applyFriction, bool hasContacts, const ContactView& cv) {

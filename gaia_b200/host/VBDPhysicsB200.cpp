@@ -90,6 +90,7 @@ void VBDPhysicsB200::loadRunningparameters(std::string inModelInputFile, std::st
         bool b;
         if (p->get("usePlaneGround", b)) phys_.usePlaneGround = b;
         if (p->get("useBowlGround", b)) phys_.useBowlGround = b;
+        p->get_vec3("bowlCenter", bowlCenter_); p->get("bowlRadius", bowlRadius_); p->get("bowlCap", bowlCap_);
         if (p->get("checkAndUpdateWorldBounds", b)) phys_.checkAndUpdateWorldBounds = b;
         p->get("boundaryFrictionDynamic", phys_.boundaryFrictionDynamic);
         p->get("dcdTetMeshSceneBVHRebuildSteps", phys_.dcdTetMeshSceneBVHRebuildSteps);
@@ -200,6 +201,7 @@ void VBDPhysicsB200::loadMeshes(int64_t* nVertsTotal, int64_t* nTetsTotal) {
 void VBDPhysicsB200::initialize() {
     if (!loaded_) throw std::runtime_error("initialize() before loadRunningparameters()");
     check(gaia_b200_create(&phys_, &col_, device_, &h_), "gaia_b200_create");
+    if (phys_.useBowlGround) check(gaia_b200_set_bowl_ground(h_, bowlCenter_, bowlRadius_, bowlCap_ ? 1 : 0), "gaia_b200_set_bowl_ground");
     if (meshCache_.empty()) loadMeshes(nullptr, nullptr);
     for (auto& m : models_) {
         auto ct = colourings_.find(m.verticesColoringCategoriesPath);

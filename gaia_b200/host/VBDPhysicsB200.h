@@ -117,6 +117,8 @@ protected:
     std::string repoRoot_, outputFolder_;
     int device_ = 0;
     gaia_physics_params phys_;
+    float bowlCenter_[3] = {0.f, 0.f, 0.f}, bowlRadius_ = 1.f;      // BasePhysicsParams::bowlCenter / bowlRadius / bowlCap (used with useBowlGround)
+    bool bowlCap_ = false;
     gaia_collision_params col_;
     HostRunParams run_;
     std::vector<ModelInput> models_;

@@ -68,6 +68,7 @@ void VBDPhysicsB200MultiGPU::initialize() {
         const int nFixed = gaia_b200_partition_restrict_ids(pt.p, (int32_t)m.fixedPoints.size(), m.fixedPoints.data(), fixed.data());
         auto ck = [&](int rc, const char* what) { if (rc < 0) throw std::runtime_error(std::string(what) + ": " + gaia_b200_last_error(pt.h)); };
         ck(gaia_b200_create(&phys_, &col_, pt.device, &pt.h), "gaia_b200_create");
+        if (phys_.useBowlGround) ck(gaia_b200_set_bowl_ground(pt.h, bowlCenter_, bowlRadius_, bowlCap_ ? 1 : 0), "gaia_b200_set_bowl_ground");
         ck(gaia_b200_set_partition_mode(pt.h, r, nGpus_), "gaia_b200_set_partition_mode");
         ck(gaia_b200_add_tet_mesh(pt.h, nLV, (int32_t)nLT, xyz.data(), tets.data(), &m.obj, (int32_t)colours.size(), lo.data(), lv.data(), nFixed,
                                   nFixed ? fixed.data() : nullptr), "gaia_b200_add_tet_mesh");
@@ -140,6 +141,7 @@ void VBDPhysicsB200MultiGPU::initializeReplicated(const std::vector<int32_t>& ow
         for (int32_t v = 0; v < nV; v++) { pt.localVerts[v] = v; pt.owned[v] = owner[v] == r; if (owner[v] != r) ghosts.push_back(v); }
         auto ck = [&](int rc, const char* what) { if (rc < 0) throw std::runtime_error(std::string(what) + ": " + gaia_b200_last_error(pt.h)); };
         ck(gaia_b200_create(&phys_, &col_, pt.device, &pt.h), "gaia_b200_create");
+        if (phys_.useBowlGround) ck(gaia_b200_set_bowl_ground(pt.h, bowlCenter_, bowlRadius_, bowlCap_ ? 1 : 0), "gaia_b200_set_bowl_ground");
         ck(gaia_b200_set_partition_mode(pt.h, r, nGpus_), "gaia_b200_set_partition_mode");
         ck(gaia_b200_add_tet_mesh(pt.h, nV, (int32_t)nT, hm.verts.data(), hm.tets.data(), &m.obj, nColours, cOffs.data(), cFlat.data(),
                                   (int32_t)m.fixedPoints.size(), m.fixedPoints.empty() ? nullptr : m.fixedPoints.data()), "gaia_b200_add_tet_mesh");

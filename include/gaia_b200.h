@@ -38,7 +38,7 @@ typedef enum gaia_status {
     GAIA_ERR_NO_DEVICE = -2,     /* no CUDA device / driver: there is no CPU path */
     GAIA_ERR_CUDA = -3,
     GAIA_ERR_STATE = -4,         /* call order violated (e.g. step before finalize) */
-    GAIA_ERR_UNSUPPORTED = -5,   /* a reference feature outside the hot path (e.g. bowl ground) */
+    GAIA_ERR_UNSUPPORTED = -5,   /* a reference feature outside the hot path, or a combination of options that is not built */
     GAIA_ERR_OVERFLOW = -6,      /* a device-side list overflowed its capacity */
     GAIA_ERR_NAN = -7,           /* NaN met in the solve (reference: std::exit(-1), M/VBD/VBDPhysics.cpp:2460) */
     GAIA_ERR_TIMEOUT = -8        /* a neighbour partition stopped answering the halo exchange */
@@ -54,7 +54,7 @@ typedef struct gaia_physics_params {
     int32_t numSubsteps;                    /* 20 */
     int32_t iterations;                     /* 1 */
     int32_t usePlaneGround;                 /* 1 */
-    int32_t useBowlGround;                  /* 0; 1 -> GAIA_ERR_UNSUPPORTED */
+    int32_t useBowlGround;                  /* 0; 1: the inside of a sphere is the ground (gaia_b200_set_bowl_ground) instead of the world box */
     int32_t checkAndUpdateWorldBounds;      /* 0 */
     float worldBoundsMin[3];                /* -1e7 */
     float worldBoundsMax[3];                /* +1e7 */
@@ -115,7 +115,7 @@ typedef struct gaia_object_params {
     float frictionEpsV;             /* 0.01 */
     float exponentialVelDamping;    /* 1.0 (raised to dt at create, M/VBD/VBDPhysics.cpp:794-807) */
     float constantVelDamping;       /* 0.0 (multiplied by dt likewise) */
-    int32_t initializationType;     /* 0..6, M/VBD/VBD_BaseMaterial.cpp:16-131; 5 -> unsupported */
+    int32_t initializationType;     /* 0..6, M/VBD/VBD_BaseMaterial.cpp:16-131 (5: forwardStepSimplecticEuler, :134-147) */
     float initRatio_g;              /* 0.5 */
     /* NeoHookean */
     float miu;                      /* 1e4 */
@@ -367,6 +367,13 @@ int gaia_b200_set_multi_colour_launch(gaia_handle* h, int enabled);
  * ~100 B per tet), not a fast path; with it the colour loop uses neither the multi-colour launch nor the fused halo exchange.
  * After finalize. line_search_shrinks: rejected trials so far (diagnostic). */
 int gaia_b200_set_line_search(gaia_handle* h, int32_t enabled, float tau, float tauGD, int32_t maxIters);
+/* The bowl ground of a scene created with gaia_physics_params::useBowlGround = 1: BasePhysicsParams::bowlCenter (0, 0, 0),
+ * bowlRadius (1), bowlCap (false) (M/Parameters/PhysicsParameters.h:18, 40-45). The inside of the sphere is the ground: a vertex
+ * further than `radius` from `center` - below the centre only, unless `cap` - is pushed back with boundaryCollisionStiffness and
+ * rubbed with the boundary friction, exactly as VBDPhysics::accumlateBoundaryForceAndHessian writes it (M/VBD/VBDPhysics.cpp:
+ * 2824-2864; the world box is then not applied, :2865). The term is built into the contact variant of the colour sweep, to which
+ * such scenes are routed; not combined with the fused halo exchange, the multi-colour launch or the line search. Any time after create. */
+int gaia_b200_set_bowl_ground(gaia_handle* h, const float center[3], float radius, int32_t cap);
 int64_t gaia_b200_line_search_shrinks(gaia_handle* h);
 /* Lazy refit of the DCD trees (csrc/collision.cu): boxes are inflated by a margin and refitted only when some vertex has moved
  * further than that from where the boxes were computed. `edges` = the margin in typical tet edges (cube root of 6 x the mean

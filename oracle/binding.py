@@ -97,6 +97,8 @@ def load_ref():
             lib.ref_cloth_material_vertex.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, FP, IP, IP, IP, C.c_int, IP, FP, IP, IP, IP] + \
                 [C.c_float] * 7 + [C.c_int, C.c_int, FP, FP]
             lib.ref_cloth_material_vertex.restype = None
+        if hasattr(lib, "ref_boundary_bowl_cpu"):
+            lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
         if hasattr(lib, "ref_cloth_sewing"):
@@ -108,7 +110,7 @@ def load_ref():
             lib.ref_cloth_step_sequence.argtypes = [C.c_int, FP, FP, FP, C.c_int, IP, FP, C.c_int, FP, FP, FP, FP]; lib.ref_cloth_step_sequence.restype = None
             lib.ref_cloth_truncate.argtypes = [C.c_int, FP, FP, C.c_int, IP, FP, IP]; lib.ref_cloth_truncate.restype = None
         if hasattr(lib, "ref_step_sequence"):
-            lib.ref_step_sequence.argtypes = [C.c_int, FP, FP, FP, C.c_int, IP, C.c_int, FP, FP, FP, FP]; lib.ref_step_sequence.restype = None
+            lib.ref_step_sequence.argtypes = [C.c_int, FP, FP, FP, C.c_int, IP, C.c_int, FP, FP, FP, FP, FP, FP]; lib.ref_step_sequence.restype = None
         if hasattr(lib, "ref_cloth_check_feasible_region"):
             lib.ref_cloth_check_feasible_region.argtypes = [C.c_int, FP, C.c_int, IP, IP, C.c_int, IP, IP, IP, FP, C.c_int, C.c_int, C.c_float]
         if hasattr(lib, "ref_check_feasible_region"):
@@ -156,6 +158,13 @@ class OracleScene(SceneBase):
     @property
     def num_threads(self):
         return self._lib.oracle_num_threads(self.h)
+
+    def neohookean_forces(self, mesh):
+        """elastic force of every vertex at the current positions (accumlateMaterialForce: no damping)"""
+        out = np.zeros((self.mesh_sizes(mesh)[0], 3), np.float32)
+        fn = self._lib.oracle_neohookean_forces; fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]; fn.restype = C.c_int
+        fn(self.h, int(mesh), out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
 
     def phase_begin_substep(self):
         self._call("phase_begin_substep")

@@ -98,6 +98,12 @@ int oracle_vertex_merit_energy(void* h, int mesh, int v, const float* x3, float*
     return GAIA_OK;
 }
 int64_t oracle_line_search_shrinks(void* h) { return ((Scene*)h)->lineSearchShrinks; }
+// probe: VBDTetMeshNeoHookean::accumlateMaterialForce for every vertex of a mesh at the current positions ([nV][3])
+int oracle_neohookean_forces(void* h, int mesh, float* out) {
+    const Mesh& m = ((Scene*)h)->meshes[mesh];
+    for (int v = 0; v < m.nV; v++) { const V3 f = neohookean_force(m, v); out[3 * v] = f.x; out[3 * v + 1] = f.y; out[3 * v + 2] = f.z; }
+    return GAIA_OK;
+}
 int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_solve_group(void* h, int g, int applyFriction) { phase_solve_group(*(Scene*)h, g, applyFriction != 0); return GAIA_OK; }
@@ -336,6 +342,28 @@ int oracle_boundary_force_hessian(const float* p, const float* pPrev, const floa
     probe_boundary(s, m, 0, f, H, applyFriction != 0);
     force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
     std::memcpy(hessian9, H.m, 36);
+    return GAIA_OK;
+}
+// the bowl ground (useBowlGround) for one vertex
+int oracle_boundary_bowl_force_hessian(const float* p, const float* pPrev, const float* center, float radius, int cap, float kB, float muB,
+                                       float epsVB, float dt, int applyFriction, float* force3, float* hessian9) {
+    Scene s;
+    std::memset(&s.phys, 0, sizeof(s.phys));
+    s.phys.useBowlGround = 1; s.phys.usePlaneGround = 1; s.phys.boundaryCollisionStiffness = kB; s.phys.boundaryFrictionDynamic = muB; s.phys.boundaryFrictionEpsV = epsVB;
+    s.bowl.center = V3(center[0], center[1], center[2]); s.bowl.radius = radius; s.bowl.cap = cap != 0;
+    s.dt = dt;
+    Mesh m;
+    m.pos = {V3(p[0], p[1], p[2])}; m.prev = {V3(pPrev[0], pPrev[1], pPrev[2])};
+    V3 f; M3 H;
+    probe_boundary(s, m, 0, f, H, applyFriction != 0);
+    force3[0] = f.x; force3[1] = f.y; force3[2] = f.z;
+    std::memcpy(hessian9, H.m, 36);
+    return GAIA_OK;
+}
+int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t cap) {
+    Scene* s = (Scene*)h;
+    if (!center || !(radius > 0.f)) return GAIA_ERR_INVALID_ARG;
+    s->bowl.center = V3(center[0], center[1], center[2]); s->bowl.radius = radius; s->bowl.cap = cap != 0;
     return GAIA_OK;
 }
 int oracle_solve3x3(const float* m9, const float* b3, float* out3) { return solve3x3_psd_stable(m9, b3, out3) ? 1 : 0; }

@@ -69,6 +69,44 @@ void vertex_friction(float mu, float lambda, const float T[6], const float u[2],
     }
 }
 
+// VBDTetMeshNeoHookean::accumlateMaterialForce (M/VBD/VBD_NeoHookean.cpp:781-870): the elastic force alone, no damping; the same
+// F, det F, cofactors and vertex weights as the force half of accumlateMaterialForceAndHessian below
+V3 neohookean_force(const Mesh& m, int iV) {
+    const int start = m.vNbrInfos[2 * iV], num = m.vNbrInfos[2 * iV + 1];
+    const float miu = m.obj.miu, lmbd = m.obj.lmbd;
+    const float a = 1 + miu / lmbd;
+    V3 force;
+    for (int iNei = 0; iNei < num; iNei++) {
+        const int tetId = m.vNbrTets[start + iNei];
+        const float A = m.restVol[tetId];
+        const float* Dm = &m.DmInv[9 * (size_t)tetId];
+        const int* tv = &m.tets[4 * (size_t)tetId];
+        float Ds[9];
+        const V3 v0 = m.pos[tv[0]];
+        for (int c = 0; c < 3; c++) { const V3 d = m.pos[tv[c + 1]] - v0; Ds[3 * c] = d.x; Ds[3 * c + 1] = d.y; Ds[3 * c + 2] = d.z; }
+        float F[9];
+        for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++)
+            F[r + 3 * c] = Ds[r] * Dm[3 * c] + Ds[r + 3] * Dm[3 * c + 1] + Ds[r + 6] * Dm[3 * c + 2];
+        const float F1_1 = F[0], F2_1 = F[1], F3_1 = F[2], F1_2 = F[3], F2_2 = F[4], F3_2 = F[5], F1_3 = F[6], F2_3 = F[7], F3_3 = F[8];
+        const float detF = F1_1 * (F2_2 * F3_3 - F2_3 * F3_2) - F1_2 * (F2_1 * F3_3 - F2_3 * F3_1) + F1_3 * (F2_1 * F3_2 - F2_2 * F3_1);
+        const float dd[9] = {F2_2 * F3_3 - F2_3 * F3_2, F1_3 * F3_2 - F1_2 * F3_3, F1_2 * F2_3 - F1_3 * F2_2,
+                             F2_3 * F3_1 - F2_1 * F3_3, F1_1 * F3_3 - F1_3 * F3_1, F1_3 * F2_1 - F1_1 * F2_3,
+                             F2_1 * F3_2 - F2_2 * F3_1, F1_2 * F3_1 - F1_1 * F3_2, F1_1 * F2_2 - F1_2 * F2_1};
+        const float lk = lmbd * (detF - a);
+        float dE_dF[9];
+        for (int q = 0; q < 9; q++) dE_dF[q] = A * (miu * F[q] + lk * dd[q]);
+        float m1, m2, m3;
+        switch (m.vNbrOrder[start + iNei]) {
+            case 0: m1 = -Dm[0] - Dm[1] - Dm[2]; m2 = -Dm[3] - Dm[4] - Dm[5]; m3 = -Dm[6] - Dm[7] - Dm[8]; break;
+            case 1: m1 = Dm[0]; m2 = Dm[3]; m3 = Dm[6]; break;
+            case 2: m1 = Dm[1]; m2 = Dm[4]; m3 = Dm[7]; break;
+            default: m1 = Dm[2]; m2 = Dm[5]; m3 = Dm[8]; break;
+        }
+        force -= V3(dE_dF[0] * m1 + dE_dF[3] * m2 + dE_dF[6] * m3, dE_dF[1] * m1 + dE_dF[4] * m2 + dE_dF[7] * m3, dE_dF[2] * m1 + dE_dF[5] * m2 + dE_dF[8] * m3);
+    }
+    return force;
+}
+
 void neohookean_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, M3& hessian) {
     const int start = m.vNbrInfos[2 * iV], num = m.vNbrInfos[2 * iV + 1];
     const float miu = m.obj.miu, lmbd = m.obj.lmbd;
@@ -144,6 +182,38 @@ void neohookean_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, 
 
 static void boundary_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, M3& hessian, bool apply_friction) {
     const float kB = s.phys.boundaryCollisionStiffness;
+    if (s.phys.useBowlGround) {
+        // the inside of a sphere as ground (VBDPhysics.cpp:2824-2864), restated as written - including the Hessian's sign
+        const V3 center = s.bowl.center;
+        const float radius = s.bowl.radius;
+        const V3 pos = m.pos[iV];
+        if (!s.bowl.cap && (pos.y - center.y > 0)) return;
+        const float dist = norm(pos - center);
+        if (dist < radius) return;
+        const V3 dir = (pos - center) / dist;
+        const float penetrationDepth = dist - radius;
+        force += (-penetrationDepth * kB) * dir;
+        const float rd = radius / dist;
+        const float d[3] = {dir.x, dir.y, dir.z};
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) {
+            const float I = r == c ? 1.f : 0.f, dd = d[r] * d[c];
+            hessian(r, c) += kB * ((-I + dd) + rd * (I - dd));
+        }
+        if (apply_friction) {
+            const V3 dx = m.pos[iV] - m.prev[iV];
+            const V3 c0 = cross(dir, V3(0, 0, 1));
+            const V3 t0 = c0 / norm(c0);
+            const V3 c1 = cross(dir, t0);
+            const V3 t1 = c1 / norm(c1);
+            float T[6] = {t0.x, t0.y, t0.z, t1.x, t1.y, t1.z};
+            float u[2] = {T[0] * dx.x + T[1] * dx.y + T[2] * dx.z, T[3] * dx.x + T[4] * dx.y + T[5] * dx.z};
+            V3 ff; M3 fh;
+            vertex_friction(s.phys.boundaryFrictionDynamic, penetrationDepth * kB, T, u, s.phys.boundaryFrictionEpsV * s.dt, ff, fh);
+            force += ff;
+            for (int q = 0; q < 9; q++) hessian.m[q] += fh.m[q];
+        }
+        return;
+    }
     if (!s.phys.usePlaneGround) return;
     for (int iDim = 0; iDim < 3; iDim++) {
         const float dt = s.dt;
@@ -322,6 +392,18 @@ static void apply_initial_step(Scene& s, Mesh& m) {
                 m.pos[v] += (dt * dt * m.obj.initRatio_g) * g;
             }
             break;
+        case 5: {
+            // forwardStepSimplecticEuler (M/VBD/VBD_BaseMaterial.cpp:134-147): the internal forces of ALL vertices first, then
+            // velocity = velocitiesPrev + dt (external 0 + internal) / mass and position += velocity dt - for every vertex, the
+            // fixed ones included (the reference has no guard there). The velocity it stores is overwritten by updateVelocities.
+            std::vector<V3> f(nV);
+            for (int v = 0; v < nV; v++) f[v] = neohookean_force(m, v);
+            for (int v = 0; v < nV; v++) {
+                const V3 vel = m.velPrev[v] + (dt * (V3() + f[v])) * (1.f / m.mass[v]);
+                m.vel[v] = vel;
+                m.pos[v] += vel * dt;
+            }
+        } break;
         case 6:
             for (int v = 0; v < nV; v++) {
                 if (m.hasApproxAcceleration) {

@@ -69,3 +69,18 @@ extern "C" void ref_boundary_cpu(const float* p3, const float* pPrev3, const flo
     for (int k = 0; k < 3; k++) f3[k] = force.d[k];
     for (int k = 0; k < 9; k++) h9[k] = H.d[k];
 }
+
+// the same function with useBowlGround: the inside of a sphere (center, radius; cap: also above the centre) as the ground
+extern "C" void ref_boundary_bowl_cpu(const float* p3, const float* pPrev3, const float* center3, float radius, int cap, float kB, float muB, float epsVB,
+                                      float dt, int applyFriction, float* f3, float* h9) {
+    GAIA_BC::VBDPhysics ph;
+    ph.p.boundaryCollisionStiffness = kB; ph.p.boundaryFrictionDynamic = muB; ph.p.boundaryFrictionEpsV = epsVB; ph.p.dt = dt;
+    ph.p.useBowlGround = true; ph.p.bowlCap = cap != 0; ph.p.bowlRadius = radius; ph.p.bowlCenter = GAIA_BC::Vec3(center3[0], center3[1], center3[2]);
+    ph.boundaryCollisionForce.resize(1); ph.boundaryFrictionForce.resize(1);
+    GAIA_BC::TetMeshFEM m;
+    m.x = GAIA_BC::Vec3(p3[0], p3[1], p3[2]); m.xPrev = GAIA_BC::Vec3(pPrev3[0], pPrev3[1], pPrev3[2]);
+    GAIA_BC::Vec3 force; GAIA_BC::Mat3 H;
+    ph.accumlateBoundaryForceAndHessian(&m, 0, 0, force, H, applyFriction != 0);
+    for (int k = 0; k < 3; k++) f3[k] = force.d[k];
+    for (int k = 0; k < 9; k++) h9[k] = H.d[k];
+}

@@ -1,7 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.
 // extern "C" shim over the REFERENCE's own initial step and velocity update of the tet VBD path, compiled from where they lie
 // under /root/reference (Simulator/Modules/VBD):
-//   VBDBaseTetMesh::forwardStep                                          VBD_BaseMaterial.cpp:7-132
+//   VBDBaseTetMesh::forwardStep, ::forwardStepSimplecticEuler             VBD_BaseMaterial.cpp:7-132, 134-147
 //   VBDBaseTetMesh::computeInertia, ::applyInitialStep, ::handleVelocityConstraint      VBD_BaseMaterial.h:201-221, 244-259, 300-306
 //   VBDPhysics::updateVelocities, ::updateVelocity, ::dampVelocities     VBDPhysics.cpp:2486-2506, 2514-2518, 2520-2561
 // oracle/Makefile extracts those line ranges into the build directory (deleted after linking). The classes need Eigen,
@@ -57,7 +57,8 @@ struct RefObjectParams {
 template <class F> static void cpu_parallel_for(int b, int e, F&& fn) { for (int i = b; i < e; i++) fn(i); }
 
 struct VBDBaseTetMesh {
-    Mat3N mVertPos, mVertPrevPos, mVelocity, mVelocitiesPrev, inertia, acceletration, vertexExternalForces;
+    Mat3N mVertPos, mVertPrevPos, mVelocity, mVelocitiesPrev, inertia, acceletration, vertexExternalForces, vertexInternalForces;
+    const float* internalForcesNow = nullptr;       // the caller's elastic forces for this substep (evaluateInternalForce needs the mesh class)
     std::vector<float> invMass;
     RefPhysicsParams* pPhysicsParams = nullptr;
     RefObjectParams* pObjParamsVBD = nullptr;
@@ -73,7 +74,8 @@ struct VBDBaseTetMesh {
     Mat3N::Col velocity(size_t i) { return mVelocity.col((int)i); }
     float vertexInvMass(int i) const { return invMass[i]; }
     void evaluateExternalForce() {}                 // VBD_BaseMaterial.h:308-311: the external forces stay zero on this path
-    void forwardStepSimplecticEuler() {}            // initializationType 5: not on this path (GAIA_ERR_UNSUPPORTED in the product)
+    void evaluateInternalForce() { for (size_t i = 0; i < vertexInternalForces.d.size(); i++) vertexInternalForces.d[i] = internalForcesNow ? internalForcesNow[i] : 0.f; }
+    void forwardStepSimplecticEuler();              // initializationType 5: defined by the extracted lines
     // defined by the extracted lines
     void forwardStep();
     void computeInertia();
@@ -101,6 +103,7 @@ struct VBDPhysics {
 
 using namespace GAIA;
 #include "ref_basemat_cpp_7_132.inc"
+#include "ref_basemat_cpp_134_147.inc"
 #include "ref_vbdphysics_cpp_2486_2506.inc"
 #include "ref_vbdphysics_cpp_2514_2518.inc"
 #include "ref_vbdphysics_cpp_2520_2561.inc"
@@ -110,8 +113,10 @@ using namespace GAIA;
 // params12: dt, gravity xyz, associateGravityWithInertia, initializationType, initRatio_g, maxVelocityMagnitude, hasNoGravZone,
 // noGravZoneThreshold, exponentialVelDamping, constantVelDamping. solved: [nSteps][3 nV] positions "after the iterations".
 // Outputs per step: positions after the initial step, inertia, velocities after the update; each [nSteps][3 nV].
+// internalForces: [nSteps][3 nV] elastic forces at the positions each substep starts from (read by type 5 only), or NULL;
+// invMass: [nV] vertexInvMass (type 5 only), or NULL for 1.
 extern "C" void ref_step_sequence(int nV, const float* pos0, const float* vel0, const float* params12, int nFixed, const int32_t* fixed, int nSteps,
-                                  const float* solved, float* outInitPos, float* outInertia, float* outVel) {
+                                  const float* solved, float* outInitPos, float* outInertia, float* outVel, const float* internalForces, const float* invMass) {
     GAIA_ST::VBDPhysics ph;
     GAIA_ST::RefObjectParams obj;
     ph.phys.dt = params12[0]; ph.phys.gravity = GAIA_ST::Vec3(params12[1], params12[2], params12[3]); ph.phys.associateGravityWithInertia = params12[4] != 0.f;
@@ -120,13 +125,16 @@ extern "C" void ref_step_sequence(int nV, const float* pos0, const float* vel0, 
     obj.fixedPoints.assign(fixed, fixed + nFixed);
     auto m = std::make_shared<GAIA_ST::VBDBaseTetMesh>();
     m->pPhysicsParams = &ph.phys; m->pObjParamsVBD = &obj; m->pObjectParams = &obj;
-    for (GAIA_ST::Mat3N* a : {&m->mVertPos, &m->mVertPrevPos, &m->mVelocity, &m->mVelocitiesPrev, &m->inertia, &m->acceletration, &m->vertexExternalForces}) a->resize(nV);
+    for (GAIA_ST::Mat3N* a : {&m->mVertPos, &m->mVertPrevPos, &m->mVelocity, &m->mVelocitiesPrev, &m->inertia, &m->acceletration, &m->vertexExternalForces,
+                              &m->vertexInternalForces}) a->resize(nV);
     m->invMass.assign(nV, 1.f);
+    if (invMass) m->invMass.assign(invMass, invMass + nV);
     std::memcpy(m->mVertPos.d.data(), pos0, 3 * (size_t)nV * sizeof(float));
     std::memcpy(m->mVelocity.d.data(), vel0, 3 * (size_t)nV * sizeof(float));
     ph.tMeshes.push_back(m); ph.objParams.push_back(&obj);
     const size_t S = 3 * (size_t)nV;
     for (int s = 0; s < nSteps; s++) {
+        m->internalForcesNow = internalForces ? internalForces + s * S : nullptr;
         m->applyInitialStep();
         std::memcpy(outInitPos + s * S, m->mVertPos.d.data(), S * sizeof(float));
         std::memcpy(outInertia + s * S, m->inertia.d.data(), S * sizeof(float));

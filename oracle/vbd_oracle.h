@@ -85,6 +85,7 @@ struct Scene {
     // APPLY_LOCAL_LINE_SEARCH (M/VBD/VBDPhysics.cpp:25, compiled out in the reference): backtracking on the vertex merit energy
     struct { bool enabled = false; float tau = 0.5f, tauGD = 0.1f; int maxIters = 16; } lineSearch;   // VBDPhysicsParameters.h:24-29
     int64_t lineSearchShrinks = 0;  // trial steps rejected so far (diagnostic)
+    struct { V3 center; float radius = 1.f; bool cap = false; } bowl;   // BasePhysicsParams::bowlCenter / bowlRadius / bowlCap (M/Parameters/PhysicsParameters.h:18, 40-45), used when phys.useBowlGround
     int frameId = 0, substep = 0, iIter = 0;
     float curTime = 0.f;
     std::vector<Deformer> deformers;
@@ -117,6 +118,7 @@ void phase_intermediate_cd(Scene& s);    // dcd (intermediate) + ccd + prepareCo
 void phase_end_substep(Scene& s);         // velocities
 void enable_models(Scene& s);
 void neohookean_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, M3& h);
+V3 neohookean_force(const Mesh& m, int iV);      // accumlateMaterialForce: elastic force alone
 bool solve3x3_psd_stable(const float* m, const float* b, float* out);
 void vertex_friction(float mu, float lambda, const float T[6], const float u[2], float epsU, V3& force, M3& hessian);
 // oracle_collision.cpp

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -153,11 +153,17 @@ def main():
     c = step_sequence_cases()
     for init_type, kw in c["cases"]:
         o, params12 = c["make"](init_type, kw)
-        solved = np.ascontiguousarray(run_oracle_step_sequence(o, c)[3])          # the "solved" positions build on the oracle's initial guesses
+        forces = []
+        solved = np.ascontiguousarray(run_oracle_step_sequence(o, c, forces)[3])          # the "solved" positions build on the oracle's initial guesses
         n = len(c["pos0"])
         a = np.zeros((c["n_steps"], n, 3), np.float32); b = np.zeros_like(a); v = np.zeros_like(a)
-        ref.ref_step_sequence(n, fp(c["pos0"]), fp(c["vel0"]), fp(params12), len(c["fixed"]), ip(c["fixed"]), c["n_steps"], fp(solved), fp(a), fp(b), fp(v))
+        # type 5 (forwardStepSimplecticEuler) reads the elastic forces (the oracle's: its force routine is pinned separately) and 1 / mass
+        fo = np.ascontiguousarray(np.array(forces, np.float32)); inv = np.ascontiguousarray((np.float32(1.0) / o.vertex_masses(0)).astype(np.float32))
+        ref.ref_step_sequence(n, fp(c["pos0"]), fp(c["vel0"]), fp(params12), len(c["fixed"]), ip(c["fixed"]), c["n_steps"], fp(solved), fp(a), fp(b), fp(v),
+                              fp(fo) if init_type == 5 else None, fp(inv) if init_type == 5 else None)
         out[f"step_init{init_type}"] = np.stack([a, b, v]); out[f"step_solved{init_type}"] = solved
+        if init_type == 5:
+            out["step_forces5"] = fo
     # ---- cloth: VBDBaseTriMesh::applyInitialStep (forwardStep_intertia), VBDClothSimulationFramework::updateVelocity, ::applyConservativeBoundTruncation
     c = cloth_step_sequence_cases()
     for init_type, kw in c["cases"]:
@@ -180,6 +186,16 @@ def main():
             ref.ref_boundary_cpu(fp(bc["p"][i]), fp(bc["pPrev"][i]), fp(bc["mn"]), fp(bc["mx"]), bc["kB"], bc["muB"], bc["epsVB"], bc["dt"], fr, fp(f), fp(h))
             B[fr, i] = np.concatenate([f, h])
     out["boundary_cpu"] = B
+    # ---- the same function with useBowlGround: [cap][friction][case][f3, h9]
+    bw = bowl_cases()
+    BW = np.zeros((2, 2, len(bw["p"]), 12), np.float32)
+    for cap in (0, 1):
+        for fr in (0, 1):
+            for i in range(len(bw["p"])):
+                f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+                ref.ref_boundary_bowl_cpu(fp(bw["p"][i]), fp(bw["pPrev"][i]), fp(bw["center"]), bw["radius"], cap, bw["kB"], bw["muB"], bw["epsVB"], bw["dt"], fr, fp(f), fp(h))
+                BW[cap, fr, i] = np.concatenate([f, h])
+    out["boundary_bowl_cpu"] = BW
     # ---- VBDPhysics::updateCollisionInfo + ::accumlateCollisionForceAndHessianPerCollision (the CPU contact term): [case][order][depth, f3, h9]
     cc = contact_cases()
     CC = np.zeros((len(cc["p"]), 4, 13), np.float32)

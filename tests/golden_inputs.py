@@ -122,6 +122,19 @@ def boundary_cases(n=48, seed=33):
     return dict(p=np.ascontiguousarray(p), pPrev=np.ascontiguousarray(pPrev), mn=mn, mx=mx, kB=1e5, muB=0.3, epsVB=1.0, dt=1.0 / 240)
 
 
+def bowl_cases(n=160, seed=35):
+    """points around the bowl ground (the inside of a sphere): inside (no force), outside below / above the centre (above only
+    counts with the cap), just outside, far outside; displacements below and above epsU = epsV * dt"""
+    rng = np.random.default_rng(seed)
+    center = np.array([0.3, 1.0, -0.2], np.float32); radius = 2.0
+    d = rng.normal(0, 1, (n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = np.where(np.arange(n) % 4 == 0, rng.uniform(0.5, 1.99, n), np.where(np.arange(n) % 4 == 1, rng.uniform(2.0001, 2.01, n), rng.uniform(2.01, 2.6, n)))
+    p = (center + d * r[:, None]).astype(np.float32)
+    scale = np.where(np.arange(n)[:, None] % 3 == 0, 1e-4, 0.03)
+    pPrev = (p + rng.normal(0, 1, p.shape) * scale).astype(np.float32)
+    return dict(p=np.ascontiguousarray(p), pPrev=np.ascontiguousarray(pPrev), center=center, radius=radius, kB=1e5, muB=0.3, epsVB=1.0, dt=1.0 / 240)
+
+
 def point_in_tet_cases(n=400, seed=41):
     """tets of mixed size (some nearly flat: |6V| around the reference's 1e-5 rejection bound) with query points inside,
     outside, on faces / edges / vertices and just off them"""
@@ -439,7 +452,8 @@ def step_sequence_cases(seed=101, n_steps=4):
     fixed = np.array([0, 5, 11], np.int32)
     cases = []
     for init_type, kw in ((0, {}), (1, dict(exponentialVelDamping=0.5, constantVelDamping=0.3)), (2, dict(maxVelocityMagnitude=1.5, hasNoGravZone=1, noGravZoneThreshold=1.3)),
-                          (3, dict(constantVelDamping=4.0)), (4, dict(initRatio_g=0.6, exponentialVelDamping=0.8)), (6, dict(maxVelocityMagnitude=2.0, hasNoGravZone=1, noGravZoneThreshold=0.5))):
+                          (3, dict(constantVelDamping=4.0)), (4, dict(initRatio_g=0.6, exponentialVelDamping=0.8)), (5, dict(constantVelDamping=0.5)),
+                          (6, dict(maxVelocityMagnitude=2.0, hasNoGravZone=1, noGravZoneThreshold=0.5))):
         cases.append((init_type, kw))
 
     def make(init_type, kw):
@@ -462,11 +476,14 @@ def step_sequence_cases(seed=101, n_steps=4):
     return dict(cases=cases, make=make, pos0=pos0, vel0=vel0, noise=noise, fixed=fixed, n_steps=n_steps)
 
 
-def run_oracle_step_sequence(o, c):
-    """the oracle through the same sequence: (positions after the initial step, inertia, velocities after the update, solved) per substep"""
+def run_oracle_step_sequence(o, c, forces=None):
+    """the oracle through the same sequence: (positions after the initial step, inertia, velocities after the update, solved) per substep;
+    forces (a list) collects the elastic forces at the positions each substep starts from - what initial-guess type 5 reads"""
     o.set_state(0, c["pos0"], c["vel0"])
     init, inert, vel, solved = [], [], [], []
     for s in range(c["n_steps"]):
+        if forces is not None:
+            forces.append(o.neohookean_forces(0))
         o.phase_begin_substep()
         init.append(o.positions(0)); inert.append(o.inertia(0))
         sol = (init[-1] + c["noise"][s]).astype(np.float32)

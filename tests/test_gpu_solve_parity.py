@@ -37,6 +37,29 @@ def test_positions_after_one_iteration(init_type):
     assert rel_err(g.positions(0), o.positions(0)) < 1e-5
 
 
+def test_symplectic_euler_initial_guess_type_5():
+    """initializationType 5 (VBDBaseTetMesh::forwardStepSimplecticEuler, M/VBD/VBD_BaseMaterial.cpp:134-147): the elastic force of
+    every vertex first, then x += dt (v_prev + dt f / m). The oracle's version is bit-identical to those reference lines
+    (tests/test_oracle_vs_ref.py). A softer, heavier beam than the other types' test: the explicit guess is only tame for
+    dt^2 k / m << 1 - on the default beam it throws vertices 0.35 m and a 1-ulp change of the input moves the result by 5e-5;
+    here the guess moves them by up to 1.2 cm and 1 / 8 ulp move the result by 4e-7."""
+    kw = dict(obj_kw=dict(initializationType=5, miu=1e4, lmbd=1e5, density=200), substeps=4)
+    g, o = _pair(**kw)
+    for s in (g, o):
+        s.run_frames(1)
+        s.run_iterations(1)
+    assert rel_err(g.prev_positions(0), o.prev_positions(0)) < 1e-5
+    assert rel_err(g.inertia(0), o.inertia(0)) < 1e-5
+    assert rel_err(g.positions(0), o.positions(0)) < 1e-5
+    g.run_frames(3); o.run_frames(3)
+    assert np.abs(g.positions(0) - o.positions(0)).max() < 1e-4
+    # not the inertia guess in disguise
+    from oracle.binding import OracleScene
+    o0 = make_beam_scene(OracleScene, threads=2, obj_kw=dict(initializationType=0, miu=1e4, lmbd=1e5, density=200), substeps=4)
+    o0.run_frames(1); o0.run_iterations(1); o0.run_frames(3)
+    assert np.abs(o0.positions(0) - o.positions(0)).max() > 1e-3
+
+
 def test_first_iteration_from_rest_state():
     g, o = _pair()
     g.run_iterations(1); o.run_iterations(1)
@@ -53,6 +76,36 @@ def test_ground_contact_and_friction_trajectory():
     assert po[:, 1].min() < 0.05                              # it reached the ground
     assert np.abs(pg - po).max() < 1e-3 * 1.5
     assert rel_err(g.velocities(0), o.velocities(0)) < 5e-2
+
+
+@pytest.mark.parametrize("case", ["below", "cap", "no_cap"])
+def test_bowl_ground_trajectory(case):
+    """useBowlGround: the inside of a sphere is the ground (VBDPhysics::accumlateBoundaryForceAndHessian, VBDPhysics.cpp:2824-2864;
+    the oracle's term is pinned to those lines in tests/test_oracle_vs_ref.py). "below": the beam falls into the bowl and comes
+    back; "cap": thrown upwards against the upper half, which only exists with bowlCap; "no_cap": the same throw without it
+    (no force above the centre). The stiffness is low on purpose: the reference's bowl Hessian has no normal component, so the
+    penalty acts explicitly. Oracle against itself with the input moved by 1 / 8 ulp: <= 2e-5 over these runs."""
+    below = case == "below"
+    kw = dict(phys_kw=dict(useBowlGround=1, boundaryCollisionStiffness=2e4, boundaryFrictionDynamic=0.3), v0=(1.0, -5.0, 0.5) if below else (1.0, 4.0, 0.5),
+              substeps=4, iterations=10)
+    g, o = _pair(**kw)
+    centre, radius = ([0.75, 2.0, 0.375], 2.2) if below else ([0.75, -2.0, 0.375], 2.95)
+    for s in (g, o):
+        s.set_bowl_ground(centre, radius, case == "cap")
+        s.run_iterations(1)
+    assert rel_err(g.positions(0), o.positions(0)) < 1e-5
+    far = 0.0
+    for _ in range(4):
+        g.run_frames(5); o.run_frames(5)
+        pg, po = g.positions(0), o.positions(0)
+        assert np.isfinite(pg).all()
+        assert np.abs(pg - po).max() < 5e-4
+        far = max(far, np.linalg.norm(po - np.float32(centre), axis=1).max())
+    if case == "no_cap":
+        assert po[:, 1].max() > 1.2                                   # nothing held it back
+    else:
+        assert far > radius and np.linalg.norm(po - np.float32(centre), axis=1).max() < radius     # it went through the wall and was pushed back
+    assert g.stats()["vertexSolves"] == o.stats()["vertexSolves"]
 
 
 def test_damping_and_velocity_damping():

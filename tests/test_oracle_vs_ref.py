@@ -369,13 +369,20 @@ def test_initial_step_and_velocity_update_bit_exact():
     """apply_initial_step / update_velocities of the oracle against the reference's own VBDBaseTetMesh::applyInitialStep
     (computeInertia + forwardStep, VBD_BaseMaterial.h:201-221, 244-259; .cpp:7-132) and VBDPhysics::updateVelocities with
     dampVelocities (VBDPhysics.cpp:2486-2561), compiled into oracle/_ref (oracle/ref_shim/refstep.cpp): four substeps for each
-    initial-guess type 0-4 and 6, with exponential / constant damping, the velocity cap in and out of the no-gravity zone and
-    fixed points. Elementwise float arithmetic: bit-exact (initial guess, inertia, velocities)."""
+    initial-guess type 0-6 (5 = forwardStepSimplecticEuler, .cpp:134-147), with exponential / constant damping, the velocity cap in
+    and out of the no-gravity zone and fixed points. Elementwise float arithmetic: bit-exact (initial guess, inertia, velocities)."""
     c = step_sequence_cases()
+    assert [t for t, _ in c["cases"]] == [0, 1, 2, 3, 4, 5, 6]
     for init_type, kw in c["cases"]:
         o, _ = c["make"](init_type, kw)
-        init, inert, vel, solved = run_oracle_step_sequence(o, c)
+        forces = []
+        init, inert, vel, solved = run_oracle_step_sequence(o, c, forces)
         G = GOLD[f"step_init{init_type}"]
+        if init_type == 5:
+            # forwardStepSimplecticEuler (VBD_BaseMaterial.cpp:134-147) was given the oracle's elastic forces (pinned in
+            # test_elastic_force_alone_equals_the_force_half...) and 1 / mass: the same forces here, and a guess that they moved
+            assert np.array_equal(np.array(forces, np.float32), GOLD["step_forces5"])
+            assert np.abs(init[0] - c["pos0"]).max() > 1e-3 and not np.array_equal(init[0][c["fixed"]], c["pos0"][c["fixed"]])   # fixed vertices move too, as there
         assert np.array_equal(solved, GOLD[f"step_solved{init_type}"])
         assert np.array_equal(init, G[0]) and np.array_equal(inert, G[1]) and np.array_equal(vel, G[2]), (init_type, kw)
         assert np.abs(G[2]).max() > 1.0 and np.abs(G[0][-1] - c["pos0"]).max() > 1e-3
@@ -446,3 +453,42 @@ def test_cloth_sewing_and_attachment_terms():
                                                                     v_infos=c["v_infos"][:0], f_infos=c["f_infos"][:0]), threads=1)
         f_plain = np.stack([np.concatenate([plain.vertex_force_hessian(0, v)[0], plain.vertex_force_hessian(0, v)[1].T.reshape(-1)]) for v in range(n0)])
         assert relmax(f_all - f_plain, sw + at[:n0]) < 1e-5
+
+
+def test_elastic_force_alone_equals_the_force_half_of_the_pinned_routine():
+    """neohookean_force (VBDTetMeshNeoHookean::accumlateMaterialForce, VBD_NeoHookean.cpp:781-870: what initial-guess type 5 sums)
+    is the force half of neohookean_force_hessian with the damping off - the routine pinned to the reference's compiled code in
+    test_neohookean_force_hessian_plain: same F, cofactors and weights, summed in the same order, so bit for bit."""
+    c = neohookean_case(seed=11, dampH=0.0, dampD=0.0)
+    o = c["scene"]
+    o.set_state(0, c["pos"], None); o.set_prev_positions(0, c["prev"])
+    f = o.neohookean_forces(0)
+    ref = np.stack([o.vertex_material_force_hessian(0, v)[0] for v in range(len(c["pos"]))])
+    assert np.abs(f).max() > 1.0 and np.array_equal(f, ref)
+    assert relmax(f, GOLD["nh_plain_force"]) < 2e-5
+
+
+def test_bowl_ground_force_hessian():
+    """useBowlGround - the inside of a sphere as the ground - against the reference's own accumlateBoundaryForceAndHessian
+    (VBDPhysics.cpp:2824-2864 of the function compiled in oracle/ref_shim/refboundarycpu.cpp): 160 points inside, just outside and far
+    outside the sphere, below and above its centre, with and without the cap and friction. Zeros in the same places; 2e-6 of the
+    largest entry (the sphere normal goes through a square root and a division)."""
+    from golden_inputs import bowl_cases
+    lib = load_oracle()
+    lib.oracle_boundary_bowl_force_hessian.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]
+    bw = bowl_cases()
+    G = GOLD["boundary_bowl_cpu"]
+    for cap in (0, 1):
+        for fr in (0, 1):
+            got = np.zeros_like(G[cap, fr])
+            for i in range(len(bw["p"])):
+                f = np.zeros(3, np.float32); h = np.zeros(9, np.float32)
+                lib.oracle_boundary_bowl_force_hessian(fp(bw["p"][i]), fp(bw["pPrev"][i]), fp(bw["center"]), bw["radius"], cap, bw["kB"], bw["muB"], bw["epsVB"],
+                                                       bw["dt"], fr, fp(f), fp(h))
+                got[i] = np.concatenate([f, h])
+            hit = np.abs(G[cap, fr]).max(1) > 0
+            assert np.array_equal(np.abs(got).max(1) > 0, hit)
+            assert relmax(got[:, :3], G[cap, fr][:, :3]) < 2e-6 and relmax(got[:, 3:], G[cap, fr][:, 3:]) < 2e-6
+    n_open, n_cap = (np.abs(G[0, 1]).max(1) > 0).sum(), (np.abs(G[1, 1]).max(1) > 0).sum()
+    assert 30 < n_open < n_cap < len(bw["p"])                  # the cap adds the points above the centre
+    assert not np.array_equal(G[1, 0], G[1, 1])                 # friction matters
