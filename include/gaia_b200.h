@@ -211,7 +211,9 @@ int gaia_b200_finalize(gaia_handle* h);
  *           VBDPhysics::runStep_hybridCollisionHandling (M/VBD/VBDPhysics.cpp:1634-1707). */
 int gaia_b200_run_frames(gaia_handle* h, int32_t nFrames);
 /* run_iterations: debugging/parity entry: applyInitialStep once, then nIters colour sweeps of
- *           the material solve (no velocity update) — "positions after one iteration". */
+ *           the material solve (no velocity update) — "positions after one iteration". The stored velocities are left as
+ *           they were (the initial step's gravity kick lives in the inertia term only; the reference's computeInertia adds
+ *           it to mVelocity, where updateVelocities would overwrite it): do not continue a trajectory from this state. */
 int gaia_b200_run_iterations(gaia_handle* h, int32_t nIters);
 int gaia_b200_synchronize(gaia_handle* h);
 int gaia_b200_frame_id(const gaia_handle* h);
