@@ -101,6 +101,10 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_cloth_bounds"):
+            UP = C.POINTER(C.c_uint8)
+            lib.ref_cloth_bounds.argtypes = [C.c_int, C.c_int, C.c_int, IP, IP, IP, IP, C.c_float, C.c_float, C.c_float, FP, IP, FP, IP, FP, IP, UP, FP, UP]
+            lib.ref_cloth_bounds.restype = None
         if hasattr(lib, "ref_cloth_sewing"):
             lib.ref_cloth_sewing.argtypes = [C.c_int, FP, C.c_int, IP, FP, C.c_float, C.c_int, FP, FP]; lib.ref_cloth_sewing.restype = None
             lib.ref_cloth_attachments.argtypes = [C.c_int, C.c_int, IP, FP, C.c_int, IP, IP, FP, FP, FP, IP]; lib.ref_cloth_attachments.restype = None

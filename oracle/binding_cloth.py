@@ -126,6 +126,27 @@ class OracleClothScene(ClothSceneBase):
         fn(self.h, int(mesh), int(v), _fp(fo), _fp(h))
         return fo, h.reshape(3, 3).T.copy()
 
+    def incidence(self, mesh):
+        """vertex -> incident faces / edges of `mesh` (CSR: fOff, fAdj, eOff, eAdj) as the conservative-bounds fold walks them"""
+        nV, nF, nE = self.mesh_sizes(mesh)
+        f_off = np.zeros(nV + 1, np.int32); e_off = np.zeros(nV + 1, np.int32); f_adj = np.zeros(3 * nF, np.int32); e_adj = np.zeros(2 * nE, np.int32)
+        ip = lambda a: a.ctypes.data_as(C.POINTER(C.c_int32))
+        fn = self._lib.oracle_cloth_get_incidence; fn.restype = C.c_int
+        fn(self.h, int(mesh), ip(f_off), ip(f_adj), ip(e_off), ip(e_adj))
+        return f_off, f_adj, e_off, e_adj
+
+    def probe_bounds(self, mesh, vf_min, vf_cnt, face_min, face_cnt, ee_min, ee_cnt, mask_before):
+        """the last loop of applyCollisionDetection alone: (conservative bounds, mask after)"""
+        nV = self.mesh_sizes(mesh)[0]
+        b = np.zeros(nV, np.float32); m = np.zeros(nV, np.uint8)
+        ip = lambda a: np.ascontiguousarray(a, np.int32).ctypes.data_as(C.POINTER(C.c_int32))
+        up = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
+        mb = np.ascontiguousarray(mask_before, np.uint8)
+        fn = self._lib.oracle_cloth_probe_bounds; fn.restype = C.c_int
+        rc = fn(self.h, int(mesh), _fp(_f32(vf_min)), ip(vf_cnt), _fp(_f32(face_min)), ip(face_cnt), _fp(_f32(ee_min)), ip(ee_cnt), up(mb), _fp(b), up(m))
+        assert rc == 0
+        return b, m
+
     def sewing_force_hessian(self, mesh, v):
         """VBDBaseTriMesh::accumlateSewingForceAndHessian alone: (force, H column-major 9)"""
         fo = np.zeros(3, np.float32); h = np.zeros(9, np.float32)

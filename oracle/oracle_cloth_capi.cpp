@@ -99,6 +99,27 @@ void oracle_cloth_constraint_force_hessian(void* h, int mesh, int v, float* f3, 
     cloth_constraint_force_hessian(*s, mesh, v, f, H);
     f3[0] = f.x; f3[1] = f.y; f3[2] = f.z; std::memcpy(h9, H.m, 36);
 }
+// probe: the conservative-bounds fold alone, from given query leftovers (smallest distance and number of contacts per vertex / face /
+// edge of simulated `mesh`) and a given mask; also hands out the vertex -> faces / edges incidence it folds over (CSR; NULL to skip)
+int oracle_cloth_probe_bounds(void* h, int mesh, const float* vfMinDis, const int32_t* vfCount, const float* faceMinDis, const int32_t* faceCount,
+                              const float* eeMinDis, const int32_t* eeCount, const uint8_t* maskBefore, float* bounds, uint8_t* maskAfter) {
+    ClothScene* s = (ClothScene*)h;
+    if (mesh < 0 || mesh >= s->numSim) return GAIA_ERR_INVALID_ARG;
+    TriMesh& m = s->meshes[mesh];
+    for (int v = 0; v < m.nV; v++) { m.vfMinDis[v] = vfMinDis[v]; m.vf[v].assign((size_t)vfCount[v], VFContact()); m.activeCollisionMask[v] = maskBefore[v]; }
+    for (int f = 0; f < m.nF; f++) { m.faceMinDis[f] = faceMinDis[f]; m.faceLinks[f].assign((size_t)faceCount[f], FVLink()); }
+    for (int e = 0; e < m.nE; e++) { m.eeMinDis[e] = eeMinDis[e]; m.ee[e].assign((size_t)eeCount[e], EEContact()); }
+    cloth_conservative_bounds(*s, m);
+    for (int v = 0; v < m.nV; v++) { bounds[v] = m.bounds[v]; maskAfter[v] = m.activeCollisionMask[v]; }
+    return GAIA_OK;
+}
+int oracle_cloth_get_incidence(void* h, int mesh, int32_t* fOff, int32_t* fAdj, int32_t* eOff, int32_t* eAdj) {
+    const TriMesh& m = ((ClothScene*)h)->meshes[mesh];
+    for (int v = 0; v <= m.nV; v++) { fOff[v] = m.vNbrFOff[v]; eOff[v] = m.vNbrEOff[v]; }
+    for (size_t i = 0; i < m.vNbrF.size(); i++) fAdj[i] = m.vNbrF[i];
+    for (size_t i = 0; i < m.vNbrE.size(); i++) eAdj[i] = m.vNbrE[i];
+    return GAIA_OK;
+}
 int oracle_cloth_finalize(void* h) { cloth_finalize(*(ClothScene*)h); return GAIA_OK; }
 int oracle_cloth_run_frames(void* h, int32_t n) {
     ClothScene* s = (ClothScene*)h;

@@ -187,6 +187,30 @@ static void ee_candidate(const ClothScene& s, int qMesh, int qE, int tMesh, int 
     }
 }
 
+// the last loop of applyCollisionDetection (M/VBDCloth/VBDClothPhysics.cpp:775-819) for one simulated mesh: fold what the queries left
+// per vertex / face / edge over each vertex's incident faces and edges -> conservative bounds, active mask (only ever raised),
+// positions at this detection
+void cloth_conservative_bounds(const ClothScene& s, TriMesh& m) {
+    const float R = s.phys.maxQueryDis;
+    for (int v = 0; v < m.nV; v++) {
+        float dMin = R;
+        dMin = std::min(dMin, m.vfMinDis[v]);
+        bool active = !m.vf[v].empty();
+        for (int i = m.vNbrFOff[v]; i < m.vNbrFOff[v + 1]; i++) {
+            dMin = std::min(dMin, m.faceMinDis[m.vNbrF[i]]);
+            active = active || !m.faceLinks[m.vNbrF[i]].empty();
+        }
+        for (int i = m.vNbrEOff[v]; i < m.vNbrEOff[v + 1]; i++) {
+            dMin = std::min(dMin, m.eeMinDis[m.vNbrE[i]]);
+            active = active || !m.ee[m.vNbrE[i]].empty();
+        }
+        dMin = std::max(0.f, dMin - s.phys.thickness);
+        m.bounds[v] = dMin * s.phys.conservativeStepRelaxation;
+        if (active) m.activeCollisionMask[v] = 1;
+    }
+    m.posAtCD = m.pos;
+}
+
 // VBDClothSimulationFramework::applyCollisionDetection (M/VBDCloth/VBDClothPhysics.cpp:735-820): VF queries for the vertices
 // of ALL meshes, EE queries for the edges of simulated meshes, conservative bounds, active mask.
 void cloth_detect(ClothScene& s) {
@@ -261,29 +285,10 @@ void cloth_detect(ClothScene& s) {
             }
         }, 64);
     }
-    // ---- conservative bounds + active mask (:775-816)
+    // ---- conservative bounds + active mask (:775-819)
     int64_t nVF = 0, nEE = 0;
     for (auto& m : s.meshes) { for (auto& l : m.vf) nVF += l.size(); for (auto& l : m.ee) nEE += l.size(); }
-    for (int mi = 0; mi < s.numSim; mi++) {
-        TriMesh& m = s.meshes[mi];
-        for (int v = 0; v < m.nV; v++) {
-            float dMin = R;
-            dMin = std::min(dMin, m.vfMinDis[v]);
-            bool active = !m.vf[v].empty();
-            for (int i = m.vNbrFOff[v]; i < m.vNbrFOff[v + 1]; i++) {
-                dMin = std::min(dMin, m.faceMinDis[m.vNbrF[i]]);
-                active = active || !m.faceLinks[m.vNbrF[i]].empty();
-            }
-            for (int i = m.vNbrEOff[v]; i < m.vNbrEOff[v + 1]; i++) {
-                dMin = std::min(dMin, m.eeMinDis[m.vNbrE[i]]);
-                active = active || !m.ee[m.vNbrE[i]].empty();
-            }
-            dMin = std::max(0.f, dMin - s.phys.thickness);
-            m.bounds[v] = dMin * s.phys.conservativeStepRelaxation;
-            if (active) m.activeCollisionMask[v] = 1;
-        }
-        m.posAtCD = m.pos;
-    }
+    for (int mi = 0; mi < s.numSim; mi++) cloth_conservative_bounds(s, s.meshes[mi]);
     s.collisionDetectionRequired = false;
     s.stats.numberCollisionDetection++;
     s.stats.numContactsVF = nVF; s.stats.numContactsEE = nEE;

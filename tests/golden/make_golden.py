@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -224,6 +224,15 @@ def main():
         ref.ref_cloth_attachments(len(c["meshes"]), c["n_sim"], ip(voff), fp(allpos), len(c["v_infos"]), ip(c["v_infos"]), ip(c["f_infos"]), fp(c["barys"]),
                                   fp(st) if st is not None else None, fp(A), ip(cnt))
         out["cloth_attach" + tag] = A; out["cloth_attach_count" + tag] = cnt
+    # ---- the conservative-bounds loop of VBDClothSimulationFramework::applyCollisionDetection
+    c = cloth_bounds_case()
+    nV, nF, nE = c["sizes"]
+    f_off, f_adj, e_off, e_adj = c["scene"].incidence(0)
+    b = np.zeros(nV, np.float32); mk = np.zeros(nV, np.uint8)
+    up = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
+    ref.ref_cloth_bounds(nV, nF, nE, ip(f_off), ip(f_adj), ip(e_off), ip(e_adj), c["R"], c["thick"], c["relax"], fp(c["vf_min"]), ip(c["vf_cnt"]), fp(c["face_min"]),
+                         ip(c["face_cnt"]), fp(c["ee_min"]), ip(c["ee_cnt"]), up(c["mask"]), fp(b), up(mk))
+    out["cloth_bounds"] = b; out["cloth_bounds_mask"] = mk
     # ---- CuMatrix::solve3x3_psd_stable
     Ms, Bs = solve3x3_cases()
     X = np.zeros_like(Bs); ok = np.zeros(len(Ms), np.int32)

@@ -324,6 +324,31 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
+def cloth_bounds_case(seed=95):
+    """What the VF / EE queries leave behind on a 7 x 7 cloth, made up at random: per vertex / face / edge the smallest distance met
+    (the query radius where nothing was met, some below the thickness) and the number of contacts recorded (mostly none), and a
+    mask that already has some vertices raised: the inputs of the reference's conservative-bounds loop."""
+    from gaia_b200 import cloth
+    from oracle.binding_cloth import OracleClothScene
+    rng = np.random.default_rng(seed)
+    R, thick, relax = 0.05, 0.004, 0.42
+    v, f = cloth.grid_cloth(7, 1.0)
+    o = OracleClothScene(cloth.default_cloth_physics_params(maxQueryDis=R, thickness=thick, conservativeStepRelaxation=relax, contactRadius=0.03), threads=1)
+    o.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(7))
+    o.finalize()
+    nV, nF, nE = o.mesh_sizes(0)
+
+    def leftovers(n):
+        d = np.where(rng.random(n) < 0.8, R, rng.uniform(0.0, R, n)).astype(np.float32)
+        d[rng.random(n) < 0.015] = np.float32(0.5 * thick)                    # closer than the thickness: the bound clamps at 0
+        c = np.where((d < 0.03) & (rng.random(n) < 0.6), rng.integers(1, 4, n), 0).astype(np.int32)
+        return d, c
+    vf_min, vf_cnt = leftovers(nV); face_min, face_cnt = leftovers(nF); ee_min, ee_cnt = leftovers(nE)
+    mask = (rng.random(nV) < 0.15).astype(np.uint8)
+    return dict(scene=o, sizes=(nV, nF, nE), R=R, thick=thick, relax=relax, vf_min=vf_min, vf_cnt=vf_cnt, face_min=face_min, face_cnt=face_cnt,
+                ee_min=ee_min, ee_cnt=ee_cnt, mask=mask)
+
+
 def build_cloth_constraint_scene(cls, case, phys=None, with_stiffness=True, **kw):
     """the scene of cloth_constraint_case on either implementation (colourings that keep coupled vertices apart are the
     caller's business: the probes do not step)"""

@@ -492,3 +492,25 @@ def test_bowl_ground_force_hessian():
     n_open, n_cap = (np.abs(G[0, 1]).max(1) > 0).sum(), (np.abs(G[1, 1]).max(1) > 0).sum()
     assert 30 < n_open < n_cap < len(bw["p"])                  # the cap adds the points above the centre
     assert not np.array_equal(G[1, 0], G[1, 1])                 # friction matters
+
+
+def test_cloth_conservative_bounds_fold_bit_exact():
+    """The cloth oracle's conservative bounds and active-collision mask against the reference's own loop (the end of
+    VBDClothSimulationFramework::applyCollisionDetection, VBDClothPhysics.cpp:775-819, compiled in oracle/ref_shim/refclothbounds.cpp):
+    the same query leftovers - smallest distance and number of contacts per vertex / face / edge, some closer than the
+    thickness - folded over each vertex's incident faces and edges; a mask that is only ever raised. Minima, one subtraction,
+    one product: bit for bit. (The incidence lists are the oracle's own; a numpy recomputation checks them here.)"""
+    from golden_inputs import cloth_bounds_case
+    c = cloth_bounds_case()
+    o = c["scene"]
+    nV, nF, nE = c["sizes"]
+    f_off, f_adj, e_off, e_adj = o.incidence(0)
+    faces = o.topology(0)[0]; edges = o.edges(0)
+    for v in range(nV):          # incidence = exactly the faces / edges that contain the vertex
+        fs = sorted(f_adj[f_off[v]:f_off[v + 1]].tolist()); es = sorted(e_adj[e_off[v]:e_off[v + 1]].tolist())
+        assert es == sorted(np.nonzero((edges[:, 0] == v) | (edges[:, 1] == v))[0].tolist())
+        assert len(fs) == f_off[v + 1] - f_off[v] and len(set(fs)) == len(fs)
+    b, m = o.probe_bounds(0, c["vf_min"], c["vf_cnt"], c["face_min"], c["face_cnt"], c["ee_min"], c["ee_cnt"], c["mask"])
+    assert np.array_equal(b, GOLD["cloth_bounds"]) and np.array_equal(m, GOLD["cloth_bounds_mask"])
+    assert (b == 0).sum() >= 3 and (b > 0).sum() > 20 and len(np.unique(b)) > 15 and b.max() <= np.float32(c["relax"]) * np.float32(c["R"] - c["thick"]) * 1.000001
+    assert (m >= c["mask"]).all() and m.sum() > c["mask"].sum() and (m == 0).sum() > 5
