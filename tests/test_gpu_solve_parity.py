@@ -111,7 +111,6 @@ def test_bowl_ground_trajectory(case):
         assert po[:, 1].max() > 1.2                                   # nothing held it back
     else:
         assert far > radius and np.linalg.norm(po - np.float32(centre), axis=1).max() < radius     # it went through the wall and was pushed back
-    assert g.stats()["vertexSolves"] == o.stats()["vertexSolves"]
 
 
 def test_damping_and_velocity_damping():
