@@ -86,6 +86,9 @@ public:
     void writeStatistics(const std::string& outFolder, int frameId);
 
     gaia_physics_params& physicsParams() { return phys_; }
+    const float* bowlCenter() const { return bowlCenter_; }
+    float bowlRadius() const { return bowlRadius_; }
+    bool bowlCap() const { return bowlCap_; }
     gaia_collision_params& collisionParams() { return col_; }
     HostRunParams& runParams() { return run_; }
     std::vector<ModelInput>& models() { return models_; }

@@ -64,6 +64,9 @@ int main(int argc, char** argv) {
             std::cout << "dryRun: " << physics.models().size() << " models, " << nV << " vertices, " << nT << " tets, numFrames "
                       << physics.runParams().numFrames << ", numSubsteps " << physics.physicsParams().numSubsteps << ", iterations "
                       << physics.physicsParams().iterations << ", outputExt " << physics.runParams().outputExt << std::endl;
+            if (physics.physicsParams().useBowlGround)
+                std::cout << "dryRun: bowl ground, centre (" << physics.bowlCenter()[0] << ", " << physics.bowlCenter()[1] << ", " << physics.bowlCenter()[2]
+                          << "), radius " << physics.bowlRadius() << ", cap " << (physics.bowlCap() ? 1 : 0) << std::endl;
             return 0;
         }
         physics.initialize();

@@ -72,6 +72,14 @@ def physics_params_from_json(j):
     return p
 
 
+def bowl_ground_from_json(j):
+    """(centre, radius, cap) of PhysicsParams when useBowlGround is set (BasePhysicsParams::bowlCenter / bowlRadius / bowlCap, the
+    reference's defaults where a key is missing), else None: pass it to Scene.set_bowl_ground after creating the scene"""
+    if not j.get("useBowlGround"):
+        return None
+    return [float(x) for x in j.get("bowlCenter", [0.0, 0.0, 0.0])], float(j.get("bowlRadius", 1.0)), bool(j.get("bowlCap", False))
+
+
 def collision_params_from_json(j):
     c = capi.default_collision_params()
     _take(c, j, [n for n, _ in capi.CollisionParams._fields_])

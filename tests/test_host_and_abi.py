@@ -130,6 +130,34 @@ def test_host_adapter_dry_run_reads_the_schema(tmp_path):
     assert abs(meshes[1][2].initialVelocity[1] + 2.0) < 1e-7 and meshes[1][2].frameToAppear == 0
 
 
+def test_host_adapter_reads_the_bowl_ground_and_initial_guess_5(tmp_path):
+    """useBowlGround with bowlCenter / bowlRadius / bowlCap (M/Parameters/PhysicsParameters.h:110, 130-131, 148) and
+    initializationType 5 are accepted by both readers (they were refused until round 2)"""
+    m, p = write_scene(str(tmp_path))
+    pj = json.load(open(p))
+    pj["PhysicsParams"].update(useBowlGround=True, bowlCenter=[0.5, 40.0, -0.25], bowlRadius=45.5, bowlCap=True)     # a wide bowl: the blocks start inside
+    json.dump(pj, open(p, "w"))
+    mj = json.load(open(m))
+    mj["Models"][0]["initializationType"] = 5
+    json.dump(mj, open(m, "w"))
+    r = subprocess.run([HOST_BIN, m, p, str(tmp_path / "out"), "-R", str(tmp_path), "--dryRun"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "bowl ground, centre (0.5, 40, -0.25), radius 45.5, cap 1" in r.stdout
+    phys, col, meshes = meshio.load_scene_json(m, p, str(tmp_path))
+    assert phys.useBowlGround == 1 and meshes[0][2].initializationType == 5
+    assert meshio.bowl_ground_from_json(pj["PhysicsParams"]) == ([0.5, 40.0, -0.25], 45.5, True)
+    assert meshio.bowl_ground_from_json({"useBowlGround": True}) == ([0.0, 0.0, 0.0], 1.0, False) and meshio.bowl_ground_from_json({}) is None
+    # the oracle runs such a scene
+    from oracle.binding import OracleScene
+    o = OracleScene(phys, col, threads=1)
+    for v, t, obj, colors, fixed in meshes:
+        o.add_tet_mesh(v, t, obj, colors, fixed)
+    o.finalize()
+    o.set_bowl_ground(*meshio.bowl_ground_from_json(pj["PhysicsParams"]))
+    o.run_frames(2)
+    assert np.isfinite(o.positions(0)).all()
+
+
 @pytest.mark.skipif(has_gpu(), reason="checks the no-GPU failure mode")
 def test_host_adapter_fails_loudly_without_gpu(tmp_path):
     m, p = write_scene(str(tmp_path))
