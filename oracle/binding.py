@@ -101,6 +101,8 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_step_trace"):
+            lib.ref_step_trace.argtypes = [IP, C.c_int, IP, IP, C.POINTER(C.c_uint8), C.c_int, IP, IP, IP, C.c_int64, IP, C.c_int64]; lib.ref_step_trace.restype = C.c_int64
         if hasattr(lib, "ref_cloth_bounds"):
             UP = C.POINTER(C.c_uint8)
             lib.ref_cloth_bounds.argtypes = [C.c_int, C.c_int, C.c_int, IP, IP, IP, IP, C.c_float, C.c_float, C.c_float, FP, IP, FP, IP, FP, IP, UP, FP, UP]
@@ -162,6 +164,20 @@ class OracleScene(SceneBase):
     @property
     def num_threads(self):
         return self._lib.oracle_num_threads(self.h)
+
+    def trace_begin(self):
+        """start recording the schedule of run_step (threads=1 scenes only): see oracle/vbd_oracle.h, Scene::trace"""
+        rc = self._lib.oracle_trace_begin(self.h)
+        if rc != 0:
+            raise RuntimeError("oracle_trace_begin: the scene must be single-threaded")
+
+    def trace_read(self):
+        """the events recorded since trace_begin: int32 [n, 4] = (code, a, b, c)"""
+        fn = self._lib.oracle_trace_read; fn.restype = C.c_int64; fn.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
+        n = fn(self.h, None, 0)
+        out = np.zeros(max(n, 1), np.int32)
+        fn(self.h, out.ctypes.data_as(C.POINTER(C.c_int32)), n)
+        return out[:n].reshape(-1, 4)
 
     def neohookean_forces(self, mesh):
         """elastic force of every vertex at the current positions (accumlateMaterialForce: no damping)"""

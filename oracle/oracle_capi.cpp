@@ -104,6 +104,20 @@ int oracle_neohookean_forces(void* h, int mesh, float* out) {
     for (int v = 0; v < m.nV; v++) { const V3 f = neohookean_force(m, v); out[3 * v] = f.x; out[3 * v + 1] = f.y; out[3 * v + 2] = f.z; }
     return GAIA_OK;
 }
+// schedule trace of run_step (tests): start / stop recording; read the events back (4 ints each). Single-threaded scenes only.
+int oracle_trace_begin(void* h) {
+    Scene* s = (Scene*)h;
+    if (s->pool->size() != 1) return GAIA_ERR_STATE;
+    delete s->trace; s->trace = new std::vector<int32_t>();
+    return GAIA_OK;
+}
+int64_t oracle_trace_read(void* h, int32_t* out, int64_t capacity) {
+    Scene* s = (Scene*)h;
+    if (!s->trace) return 0;
+    const int64_t n = (int64_t)s->trace->size();
+    if (out && capacity >= n) std::memcpy(out, s->trace->data(), n * sizeof(int32_t));
+    return n;
+}
 int oracle_phase_begin_substep(void* h) { enable_models(*(Scene*)h); phase_begin_substep(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_prepare(void* h) { phase_prepare(*(Scene*)h); return GAIA_OK; }
 int oracle_phase_solve_group(void* h, int g, int applyFriction) { phase_solve_group(*(Scene*)h, g, applyFriction != 0); return GAIA_OK; }

@@ -244,6 +244,7 @@ void scene_finalize(Scene& s) {
 Scene::~Scene() {
     collision_free(*this);
     delete pool;
+    delete trace;
 }
 
 }  // namespace orc

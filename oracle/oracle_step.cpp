@@ -464,6 +464,7 @@ void phase_solve_group(Scene& s, int g, bool apply_friction) {
     s.pool->parallel_for(nAct, [&](int64_t b, int64_t e) {
         for (int64_t i = b; i < e; i++) {
             Mesh& m = s.meshes[act[2 * i]];
+            s.ev(6, act[2 * i], act[2 * i + 1]);
             update_collision_info(s, m.colResults[m.tetVertToSurf[act[2 * i + 1]]]);
         }
     }, 16);
@@ -474,12 +475,18 @@ void phase_solve_group(Scene& s, int g, bool apply_friction) {
         for (int64_t i = b; i < e; i++) {
             Mesh& m = s.meshes[grp[2 * i]];
             const int v = grp[2 * i + 1];
-            if (!m.fixedMask[v] && m.activeForMaterialSolve) { vbd_step_with_collision(s, m, v, apply_friction); cnt++; }
+            if (!m.fixedMask[v] && m.activeForMaterialSolve) { s.ev(7, grp[2 * i], v, apply_friction ? 1 : 0); vbd_step_with_collision(s, m, v, apply_friction); cnt++; }
         }
         solved += cnt;
     }, 64);
     s.stats.vertexSolves += solved.load();
     s.stats.colourSweeps++;
+}
+
+static void trace_active_lists(Scene& s) {
+    if (!s.trace) return;
+    for (size_t g = 0; g < s.activeCollisionsEachGroup.size(); g++)
+        for (size_t i = 0; i + 1 < s.activeCollisionsEachGroup[g].size(); i += 2) s.ev(11, (int)g, s.activeCollisionsEachGroup[g][i], s.activeCollisionsEachGroup[g][i + 1]);
 }
 
 static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
@@ -507,9 +514,11 @@ static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
         }
         const int ici = s.phys.intermediateCollisionIterations;
         if (withIntermediateCD && ici > 0 && s.iIter % ici == ici - 1) {
+            s.ev(8);
             dcd(s, true);
             ccd(s);
             prepare_collision_data(s);
+            trace_active_lists(s);
         }
     }
 }
@@ -561,12 +570,18 @@ void phase_end_substep(Scene& s) { update_velocities(s); s.stats.substeps++; }
 void run_step(Scene& s) {
     for (s.substep = 0; s.substep < s.phys.numSubsteps; s.substep++) {
         s.curTime += s.dt;
+        s.ev(1);
         dcd(s, false);
-        for (auto& m : s.meshes) if (m.activeForMaterialSolve) apply_initial_step(s, m);
+        for (size_t im = 0; im < s.meshes.size(); im++) if (s.meshes[im].activeForMaterialSolve) { s.ev(2, (int)im); apply_initial_step(s, s.meshes[im]); }
+        s.ev(3);
         apply_deformers(s);
+        s.ev(4);
         ccd(s);
+        s.ev(5);
         prepare_collision_data(s);
+        trace_active_lists(s);
         solve_iterations(s, s.phys.iterations, true);
+        s.ev(9);
         update_velocities(s);
         s.stats.substeps++;
     }

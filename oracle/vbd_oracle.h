@@ -90,6 +90,11 @@ struct Scene {
     float curTime = 0.f;
     std::vector<Deformer> deformers;
     Pool* pool = nullptr;
+    // optional schedule trace of run_step (tests; single-threaded scenes only): events of 4 ints {code, a, b, c} -
+    // 1 dcd, 2 initial step (mesh), 3 deformers, 4 ccd, 5 prepare, 6 update collision info (mesh, vertex), 7 vertex solve (mesh, vertex,
+    // friction), 8 intermediate detection, 9 velocity update, 11 active-list entry after a 5 / 8 (group, mesh, vertex)
+    std::vector<int32_t>* trace = nullptr;
+    void ev(int code, int a = 0, int b = 0, int c = 0) { if (trace) { trace->push_back(code); trace->push_back(a); trace->push_back(b); trace->push_back(c); } }
     gaia_stats stats;
     std::string err;
     // collision acceleration (oracle_collision.cpp)

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -224,6 +224,18 @@ def main():
         ref.ref_cloth_attachments(len(c["meshes"]), c["n_sim"], ip(voff), fp(allpos), len(c["v_infos"]), ip(c["v_infos"]), ip(c["f_infos"]), fp(c["barys"]),
                                   fp(st) if st is not None else None, fp(A), ip(cnt))
         out["cloth_attach" + tag] = A; out["cloth_attach_count" + tag] = cnt
+    # ---- the schedule of VBDPhysics::runStep_hybridCollisionHandling (stand-in members that record their calls), two frames
+    c = step_schedule_case()
+    up8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
+    for frame in range(2):
+        c["scene"].trace_begin(); c["scene"].run_frames(1)
+        rec = np.ascontiguousarray(c["scene"].trace_read())
+        n = ref.ref_step_trace(ip(c["params4"]), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
+                               ip(rec), len(rec), None, 0)
+        tr = np.zeros(n, np.int32)
+        ref.ref_step_trace(ip(c["params4"]), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
+                           ip(rec), len(rec), ip(tr), n)
+        out[f"step_trace_f{frame}"] = tr.reshape(-1, 4)
     # ---- the conservative-bounds loop of VBDClothSimulationFramework::applyCollisionDetection
     c = cloth_bounds_case()
     nV, nF, nE = c["sizes"]

@@ -324,6 +324,35 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
+def step_schedule_case():
+    """Three Kuhn blocks for the SCHEDULE of the step: block 0 with fixed vertices, block 1 dropped onto it (contacts from the first
+    detection on), block 2 appearing in frame 1 (frameToAppear); 2 substeps x 6 iterations, friction from iteration 2 on,
+    intermediate detection every 3 iterations. Single-threaded oracle (the trace is ordered)."""
+    from oracle.binding import OracleScene
+    phys = capi.default_physics_params(numSubsteps=2, iterations=6, frictionStartIter=2, intermediateCollisionIterations=3, collisionStiffness=1e5,
+                                       worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10])
+    o = OracleScene(phys, capi.default_collision_params(allowDCD=1, allowCCD=1), threads=1)
+    fixed = [np.array([0, 3, 7, 20], np.int32), np.zeros(0, np.int32), np.array([1], np.int32)]
+    shapes = [((3, 2, 2, 0.25), (0.0, 0.3, 0.0), 0), ((2, 2, 2, 0.22), (0.1, 0.72, 0.05), 0), ((2, 1, 2, 0.2), (0.3, 1.4, 0.1), 1)]
+    sizes = []
+    for i, ((nx, ny, nz, h), org, appear) in enumerate(shapes):
+        verts, tets = meshio.kuhn_beam(nx, ny, nz, h=h, origin=org)
+        colors = meshio.kuhn_coloring(nx, ny, nz) if i != 1 else meshio.greedy_coloring(len(verts), tets)
+        obj = capi.default_object_params(miu=1e5, lmbd=1e6, density=50 + 10 * i, frictionDynamic=0.2, initialVelocity=[0.0, -4.0 * i, 0.0], frameToAppear=appear)
+        o.add_tet_mesh(verts, tets, obj, colors, fixed[i])
+        sizes.append(len(verts))
+    o.finalize()
+    fixed_off = np.zeros(len(sizes) + 1, np.int32); fixed_off[1:] = np.cumsum(sizes)
+    mask = np.zeros(int(fixed_off[-1]), np.uint8)
+    for i, fx in enumerate(fixed):
+        mask[fixed_off[i] + fx] = 1
+    groups = o.parallel_groups()
+    group_off = np.zeros(len(groups) + 1, np.int32); group_off[1:] = np.cumsum([2 * len(g) for g in groups])
+    pairs = np.ascontiguousarray(np.concatenate([g.reshape(-1) for g in groups]), np.int32)
+    return dict(scene=o, params4=np.array([2, 6, 2, 3], np.int32), fixed_off=fixed_off, mask=mask, group_off=group_off, pairs=pairs, n_groups=len(groups),
+                active=[np.array([1, 1, 0], np.int32), np.array([1, 1, 1], np.int32)])
+
+
 def cloth_bounds_case(seed=95):
     """What the VF / EE queries leave behind on a 7 x 7 cloth, made up at random: per vertex / face / edge the smallest distance met
     (the query radius where nothing was met, some below the thickness) and the number of contacts recorded (mostly none), and a

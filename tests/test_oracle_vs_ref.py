@@ -514,3 +514,28 @@ def test_cloth_conservative_bounds_fold_bit_exact():
     assert np.array_equal(b, GOLD["cloth_bounds"]) and np.array_equal(m, GOLD["cloth_bounds_mask"])
     assert (b == 0).sum() >= 3 and (b > 0).sum() > 20 and len(np.unique(b)) > 15 and b.max() <= np.float32(c["relax"]) * np.float32(c["R"] - c["thick"]) * 1.000001
     assert (m >= c["mask"]).all() and m.sum() > c["mask"].sum() and (m == 0).sum() > 5
+
+
+def test_step_schedule_is_the_reference_loop():
+    """WHICH operations the step runs, in which order, on which (mesh, vertex), with which friction flag: the oracle's run_step
+    traced event by event against the reference's own loop - VBDPhysics::runStep_hybridCollisionHandling, VBDPhysics.cpp:1634-1707,
+    compiled against stand-in members that record their calls (oracle/ref_shim/refsteploop.cpp). Two frames of a three-block
+    scene with fixed vertices, contacts, a block that appears in frame 1, friction from iteration 2 on and intermediate detection
+    every 3 iterations. (The active collision lists are data the stand-in repeats from the oracle's recording; their content is
+    checked against the product bit for bit elsewhere.)"""
+    from golden_inputs import step_schedule_case
+    c = step_schedule_case()
+    o = c["scene"]
+    for frame in range(2):
+        o.trace_begin(); o.run_frames(1)
+        tr = o.trace_read()
+        G = GOLD[f"step_trace_f{frame}"]
+        assert tr.shape == G.shape and np.array_equal(tr, G), frame
+        codes = set(G[:, 0].tolist())
+        assert codes == {1, 2, 3, 4, 5, 6, 7, 8, 9, 11}
+        assert (G[:, 0] == 1).sum() == 2 and (G[:, 0] == 9).sum() == 2 and (G[:, 0] == 8).sum() == 2 * 2          # substeps; 6 // 3 intermediate detections each
+        assert (G[:, 0] == 2).sum() == 2 * int(c["active"][frame].sum())
+        solves = G[G[:, 0] == 7]
+        assert set(solves[:, 3].tolist()) == {0, 1} and (2 in solves[:, 1]) == (frame == 1)                        # friction switches on; block 2 only once it has appeared
+        n_free = sum(int((c["mask"][c["fixed_off"][m]:c["fixed_off"][m + 1]] == 0).sum()) for m in range(3) if c["active"][frame][m])
+        assert len(solves) == 2 * 6 * n_free                                                                       # every free vertex of every active mesh, every iteration
