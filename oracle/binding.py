@@ -101,6 +101,10 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_prepare_collision_data"):
+            UP8 = C.POINTER(C.c_uint8)
+            lib.ref_prepare_collision_data.argtypes = [C.c_int, IP, IP, IP, IP, IP, IP, UP8, UP8, UP8, IP, IP, C.c_int, IP, C.c_float, IP, IP, C.c_int64, IP, IP, C.c_int64, UP8]
+            lib.ref_prepare_collision_data.restype = C.c_int64
         if hasattr(lib, "ref_step_trace"):
             lib.ref_step_trace.argtypes = [IP, C.c_int, IP, IP, C.POINTER(C.c_uint8), C.c_int, IP, IP, IP, C.c_int64, IP, C.c_int64]; lib.ref_step_trace.restype = C.c_int64
         if hasattr(lib, "ref_cloth_bounds"):
@@ -164,6 +168,34 @@ class OracleScene(SceneBase):
     @property
     def num_threads(self):
         return self._lib.oracle_num_threads(self.h)
+
+    def prepared_raw(self):
+        """the prepared collision data in the order prepare_collision_data built it: (active pairs per group [list of [n, 2]],
+        per mesh (relOff [nV + 1], rows [n, 5], mask [nV], group of every vertex [nV]), per mesh the detection results of its
+        surface vertices (has, fromCCD, pathFound, hitMesh, hitFace))"""
+        L = self._lib
+        IPc = C.POINTER(C.c_int32); UPc = C.POINTER(C.c_uint8)
+        L.oracle_get_active_list_raw.restype = C.c_int64; L.oracle_get_active_list_raw.argtypes = [C.c_void_p, C.c_int, IPc, C.c_int64]
+        L.oracle_get_relations_raw.restype = C.c_int64; L.oracle_get_relations_raw.argtypes = [C.c_void_p, C.c_int, IPc, IPc, C.c_int64, UPc, IPc]
+        L.oracle_get_col_results.argtypes = [C.c_void_p, C.c_int, UPc, UPc, UPc, IPc, IPc]
+        ip = lambda a: a.ctypes.data_as(IPc); up = lambda a: a.ctypes.data_as(UPc)
+        active = []
+        for g in range(self._call("num_parallel_groups")):
+            n = L.oracle_get_active_list_raw(self.h, g, None, 0)
+            a = np.zeros(max(2 * n, 1), np.int32)
+            L.oracle_get_active_list_raw(self.h, g, ip(a), 2 * n)
+            active.append(a[: 2 * n].reshape(-1, 2))
+        rel, res = [], []
+        for m in range(self.num_meshes):
+            nV, nS = self.mesh_sizes(m)[0], self.mesh_sizes(m)[2]
+            n = L.oracle_get_relations_raw(self.h, m, None, None, 0, None, None)
+            off = np.zeros(nV + 1, np.int32); rows = np.zeros((max(n, 1), 5), np.int32); mask = np.zeros(nV, np.uint8); grp = np.zeros(nV, np.int32)
+            L.oracle_get_relations_raw(self.h, m, ip(off), ip(rows), n, up(mask), ip(grp))
+            rel.append((off, rows[:n], mask, grp))
+            r = [np.zeros(nS, np.uint8) for _ in range(3)] + [np.zeros(nS, np.int32) for _ in range(2)]
+            L.oracle_get_col_results(self.h, m, up(r[0]), up(r[1]), up(r[2]), ip(r[3]), ip(r[4]))
+            res.append(tuple(r))
+        return active, rel, res
 
     def trace_begin(self):
         """start recording the schedule of run_step (threads=1 scenes only): see oracle/vbd_oracle.h, Scene::trace"""

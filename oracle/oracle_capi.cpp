@@ -291,6 +291,41 @@ int oracle_get_active_list(void* h, int group, int32_t* out, int64_t capacity, i
     if (out) for (int64_t i = 0; i < *n && i < capacity; i++) { out[2 * i] = pairs[i].first; out[2 * i + 1] = pairs[i].second; }
     return GAIA_OK;
 }
+// raw views of the prepared collision data, in the order prepare_collision_data built them (the pin against the reference's own
+// prepareCollisionDataCPU / addToActiveCollisionList compares order and all): active pairs of a group; per vertex of a mesh its
+// relation rows (meshId, surfaceVertexId, collisionId, collisionType, collisionVertexOrder) behind relOff [nV + 1]; the mask;
+// the group of every vertex; the detection result of every surface vertex
+int64_t oracle_get_active_list_raw(void* h, int group, int32_t* out, int64_t capacity) {
+    Scene* s = (Scene*)h;
+    const std::vector<int>& g = s->activeCollisionsEachGroup[group];
+    if (out && capacity >= (int64_t)g.size()) for (size_t i = 0; i < g.size(); i++) out[i] = g[i];
+    return (int64_t)g.size() / 2;
+}
+int64_t oracle_get_relations_raw(void* h, int mesh, int32_t* relOff, int32_t* rows, int64_t capacityRows, uint8_t* mask, int32_t* vertexGroup) {
+    Scene* s = (Scene*)h;
+    Mesh& m = s->meshes[mesh];
+    int64_t n = 0;
+    for (int v = 0; v < m.nV; v++) {
+        if (relOff) relOff[v] = (int32_t)n;
+        for (auto& r : m.colRelations[v]) {
+            if (rows && n < capacityRows) { rows[5 * n] = r.meshId; rows[5 * n + 1] = r.surfaceVertexId; rows[5 * n + 2] = r.collisionId; rows[5 * n + 3] = r.collisionType; rows[5 * n + 4] = r.collisionVertexOrder; }
+            n++;
+        }
+        if (mask) mask[v] = m.activeCollisionMask[v];
+        if (vertexGroup) vertexGroup[v] = m.vertexParallelGroup[v];
+    }
+    if (relOff) relOff[m.nV] = (int32_t)n;
+    return n;
+}
+int oracle_get_col_results(void* h, int mesh, uint8_t* has, uint8_t* fromCCD, uint8_t* pathFound, int32_t* hitMesh, int32_t* hitFace) {
+    Mesh& m = ((Scene*)h)->meshes[mesh];
+    for (int sv = 0; sv < m.nSurfV(); sv++) {
+        const ColResult& r = m.colResults[sv];
+        has[sv] = r.numIntersections ? 1 : 0; fromCCD[sv] = r.fromCCD ? 1 : 0; pathFound[sv] = r.shortestPathFound ? 1 : 0;
+        hitMesh[sv] = r.intersectedMeshId; hitFace[sv] = r.closestSurfaceFaceId;
+    }
+    return GAIA_OK;
+}
 int oracle_get_relations(void* h, int mesh, int32_t* out, int64_t capacity, int64_t* n) {
     Scene* s = (Scene*)h;
     Mesh& m = s->meshes[mesh];

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -236,6 +236,20 @@ def main():
         ref.ref_step_trace(ip(c["params4"]), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
                            ip(rec), len(rec), ip(tr), n)
         out[f"step_trace_f{frame}"] = tr.reshape(-1, 4)
+    # ---- VBDPhysics::prepareCollisionDataCPU + ActiveCollisionList::addToActiveCollisionList on the oracle's detection results
+    for tag, o in prepared_collision_cases():
+        q = prepared_collision_inputs(o)
+        nG = len(q["group_sizes"]); nVt = int(q["v_off"][-1])
+        a_off = np.zeros(nG + 1, np.int32); a_pairs = np.zeros((4096, 2), np.int32); r_off = np.zeros(nVt + 1, np.int32); rows = np.zeros((8192, 5), np.int32)
+        mask = np.zeros(nVt, np.uint8)
+        nr = ref.ref_prepare_collision_data(q["nM"], ip(q["v_off"]), ip(q["sv_off"]), ip(q["f_off"]), ip(q["vertex_group"]), ip(q["svids"]), ip(q["faces"]),
+                                            up8(q["has"]), up8(q["ccd"]), up8(q["path"]), ip(q["hit_mesh"]), ip(q["hit_face"]), nG, ip(q["group_sizes"]), 8.0,
+                                            ip(a_off), ip(a_pairs), len(a_pairs), ip(r_off), ip(rows), len(rows), up8(mask))
+        # activeCollisionListPreAllocationRatio 8 (the reference's default 1 overflows on these small groups: it then drops contacts
+        # and, having counted before it checks - ActiveCollisionList.cpp:63-65 -, reads a slot it never wrote)
+        assert nr >= 0 and (np.diff(a_off) <= 8 * q["group_sizes"]).all()
+        out[f"prep_{tag}_aoff"] = a_off; out[f"prep_{tag}_apairs"] = a_pairs[: a_off[-1]].copy()
+        out[f"prep_{tag}_roff"] = r_off; out[f"prep_{tag}_rows"] = rows[:nr].copy(); out[f"prep_{tag}_mask"] = mask
     # ---- the conservative-bounds loop of VBDClothSimulationFramework::applyCollisionDetection
     c = cloth_bounds_case()
     nV, nF, nE = c["sizes"]

@@ -353,6 +353,37 @@ def step_schedule_case():
                 active=[np.array([1, 1, 0], np.int32), np.array([1, 1, 1], np.int32)])
 
 
+def prepared_collision_cases():
+    """Scene states whose detection results feed prepareCollisionDataCPU: the three-block schedule scene after one and two frames,
+    and a four-block stack (config 2 in miniature) after 3 and 6 frames - DCD and CCD contacts, on the order of a hundred of them"""
+    from conftest import make_contact_scene
+    from oracle.binding import OracleScene
+    o = step_schedule_case()["scene"]
+    for tag in ("blocks3_f1", "blocks3_f2"):
+        o.run_frames(1)
+        yield tag, o                      # (a generator: the caller looks at the scene before it moves on)
+    o = make_contact_scene(OracleScene, n_objects=4, threads=1)
+    for tag in ("stack4_f3", "stack4_f6"):
+        o.run_frames(3)
+        yield tag, o
+
+
+def prepared_collision_inputs(o):
+    """what ref_prepare_collision_data takes, from the oracle's current state"""
+    nM = o.num_meshes
+    sizes = [o.mesh_sizes(m) for m in range(nM)]
+    v_off = np.zeros(nM + 1, np.int32); sv_off = np.zeros(nM + 1, np.int32); f_off = np.zeros(nM + 1, np.int32)
+    v_off[1:] = np.cumsum([s[0] for s in sizes]); sv_off[1:] = np.cumsum([s[2] for s in sizes]); f_off[1:] = np.cumsum([s[3] for s in sizes])
+    active, rel, res = o.prepared_raw()
+    cat = lambda xs, dt: np.ascontiguousarray(np.concatenate(xs), dt)
+    groups = o.parallel_groups()
+    return dict(nM=nM, v_off=v_off, sv_off=sv_off, f_off=f_off, vertex_group=cat([r[3] for r in rel], np.int32),
+                svids=cat([o.surface_vertex_ids(m) for m in range(nM)], np.int32), faces=cat([o.surface_faces(m).reshape(-1) for m in range(nM)], np.int32),
+                has=cat([r[0] for r in res], np.uint8), ccd=cat([r[1] for r in res], np.uint8), path=cat([r[2] for r in res], np.uint8),
+                hit_mesh=cat([r[3] for r in res], np.int32), hit_face=cat([r[4] for r in res], np.int32),
+                group_sizes=np.array([len(g) for g in groups], np.int32), active=active, rel=rel)
+
+
 def cloth_bounds_case(seed=95):
     """What the VF / EE queries leave behind on a 7 x 7 cloth, made up at random: per vertex / face / edge the smallest distance met
     (the query radius where nothing was met, some below the thickness) and the number of contacts recorded (mostly none), and a

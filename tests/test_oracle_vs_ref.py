@@ -539,3 +539,36 @@ def test_step_schedule_is_the_reference_loop():
         assert set(solves[:, 3].tolist()) == {0, 1} and (2 in solves[:, 1]) == (frame == 1)                        # friction switches on; block 2 only once it has appeared
         n_free = sum(int((c["mask"][c["fixed_off"][m]:c["fixed_off"][m + 1]] == 0).sum()) for m in range(3) if c["active"][frame][m])
         assert len(solves) == 2 * 6 * n_free                                                                       # every free vertex of every active mesh, every iteration
+
+
+def test_active_lists_and_relations_are_the_reference_construction():
+    """Row a15 on the oracle's side: the active collision list of every parallel group, the face-side relations of every vertex
+    and the active-collision mask, built from the same detection results by the reference's own code - VBDPhysics::
+    prepareCollisionDataCPU (VBDPhysics.cpp:1709-1810) with ActiveCollisionList::clear / addToActiveCollisionList
+    (ActiveCollisionList.cpp:6-110, .h:9-53) and MeshFrame2's CPArray, compiled in oracle/ref_shim/refprepare.cpp. Four scene
+    states with DCD and CCD contacts; ORDER and all: entry for entry. (The product's lists are compared with the oracle's bit for
+    bit, after the canonical sort the ABI returns them in, in tests/test_gpu_collision_parity.py.)"""
+    from golden_inputs import prepared_collision_cases, prepared_collision_inputs
+    total = 0
+    for tag, o in prepared_collision_cases():
+        q = prepared_collision_inputs(o)
+        a_off, a_pairs = GOLD[f"prep_{tag}_aoff"], GOLD[f"prep_{tag}_apairs"]
+        for g, mine in enumerate(q["active"]):
+            assert np.array_equal(mine, a_pairs[a_off[g]:a_off[g + 1]]), (tag, g)
+        r_off, rows, mask = GOLD[f"prep_{tag}_roff"], GOLD[f"prep_{tag}_rows"], GOLD[f"prep_{tag}_mask"]
+        for m, (off, rw, mk, _) in enumerate(q["rel"]):
+            b = q["v_off"][m]
+            assert np.array_equal(off + r_off[b], r_off[b:b + len(off)]) and np.array_equal(rw, rows[r_off[b]:r_off[b] + len(rw)]), (tag, m)
+            # the mask: the oracle follows the rule of the reference's GPU step, where the accelerator reads it (own contact with a
+            # path, or any relation: VBDPhysicsCompute.cu:1740-1770). prepareCollisionDataCPU clears each mesh's mask when it COMES
+            # to that mesh (:1719), wiping what earlier meshes' contacts marked on it - its mask is a subset, read by nothing on
+            # this path. Both statements are checked against the reference's own output here.
+            ref_mask = mask[b:b + len(mk)]
+            own = np.zeros(len(mk), bool)
+            sv = slice(q["sv_off"][m], q["sv_off"][m + 1])
+            own[q["svids"][sv][(q["has"][sv] & q["path"][sv]) != 0]] = True
+            gpu_rule = own | (np.diff(r_off[b:b + len(off)]) > 0)
+            assert np.array_equal(mk != 0, gpu_rule) and not (ref_mask & ~mk.astype(bool)).any()
+        assert len(rows) == 3 * int((q["has"] & q["path"]).sum()) and a_off[-1] >= int(q["has"].sum())
+        total += int(q["has"].sum())
+    assert total > 60
