@@ -106,7 +106,7 @@ def load_ref():
             lib.ref_prepare_collision_data.argtypes = [C.c_int, IP, IP, IP, IP, IP, IP, UP8, UP8, UP8, IP, IP, C.c_int, IP, C.c_float, IP, IP, C.c_int64, IP, IP, C.c_int64, UP8]
             lib.ref_prepare_collision_data.restype = C.c_int64
         if hasattr(lib, "ref_step_trace"):
-            lib.ref_step_trace.argtypes = [IP, C.c_int, IP, IP, C.POINTER(C.c_uint8), C.c_int, IP, IP, IP, C.c_int64, IP, C.c_int64]; lib.ref_step_trace.restype = C.c_int64
+            lib.ref_step_trace.argtypes = [IP, C.c_int, IP, IP, C.POINTER(C.c_uint8), C.c_int, IP, IP, IP, C.c_int64, IP, C.c_int64, IP, IP, C.POINTER(C.c_uint8)]; lib.ref_step_trace.restype = C.c_int64
         if hasattr(lib, "ref_cloth_bounds"):
             UP = C.POINTER(C.c_uint8)
             lib.ref_cloth_bounds.argtypes = [C.c_int, C.c_int, C.c_int, IP, IP, IP, IP, C.c_float, C.c_float, C.c_float, FP, IP, FP, IP, FP, IP, UP, FP, UP]

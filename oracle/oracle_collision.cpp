@@ -554,11 +554,12 @@ void dcd(Scene& s, bool intermediate) {
             rebuildTet = (s.substep == 0) && !(s.frameId % s.phys.dcdTetMeshSceneBVHRebuildSteps) && s.frameId;
             rebuildSurf = (s.substep == 0) && !(s.frameId % s.phys.dcdSurfaceSceneBVHRebuildSteps) && s.frameId;
         }
+        s.ev(12, rebuildTet, rebuildSurf);
         update_dcd_bvh(s, rebuildTet, rebuildSurf);
         for (size_t im = 0; im < s.meshes.size(); im++) {
             Mesh& m = s.meshes[im];
             if (!m.activeForCollision) continue;
-            if (!intermediate) std::fill(m.penetratedMask.begin(), m.penetratedMask.end(), 0);
+            if (!intermediate) { s.ev(18, (int)im); std::fill(m.penetratedMask.begin(), m.penetratedMask.end(), 0); }
             s.pool->parallel_for(m.nSurfV(), [&](int64_t b, int64_t e) {
                 for (int64_t sv = b; sv < e; sv++) {
                     const int v = m.surfaceVIds[sv];
@@ -567,21 +568,25 @@ void dcd(Scene& s, bool intermediate) {
                     if (!doIt) continue;
                     ColResult& r = m.colResults[sv];
                     vertex_collision_detection(s, v, (int)im, r);
+                    s.ev(13, (int)im, v, r.numIntersections);
                     if (r.numIntersections) {
                         if (!intermediate) m.penetratedMask[v] = 1;
+                        s.ev(14, (int)im, v);
                         closest_point_query(s, r);
                     }
                 }
             }, 32);
         }
     } else if (s.col.allowCCD && !intermediate) {
-        for (auto& m : s.meshes) for (auto& r : m.colResults) r.clear();
+        for (size_t im = 0; im < s.meshes.size(); im++) for (size_t sv = 0; sv < s.meshes[im].colResults.size(); sv++) { s.ev(17, (int)im, (int)sv); s.meshes[im].colResults[sv].clear(); }
     }
 }
 
-void ccd(Scene& s) {
+// ccd() (M/VBD/VBDPhysics.cpp:2077-2115) and, with intermediate, intermediateCCD() (:2117-2156: the same loop, never a rebuild)
+void ccd(Scene& s, bool intermediate) {
     if (!s.col.allowCCD) return;
-    bool rebuild = (s.substep == 0) && !(s.frameId % s.phys.ccdBVHRebuildSteps) && s.frameId;
+    const bool rebuild = !intermediate && (s.substep == 0) && !(s.frameId % s.phys.ccdBVHRebuildSteps) && s.frameId;
+    s.ev(15, rebuild);
     update_ccd_bvh(s, rebuild);
     for (size_t im = 0; im < s.meshes.size(); im++) {
         Mesh& m = s.meshes[im];
@@ -589,8 +594,10 @@ void ccd(Scene& s) {
         s.pool->parallel_for(m.nSurfV(), [&](int64_t b, int64_t e) {
             for (int64_t sv = b; sv < e; sv++) {
                 const int v = m.surfaceVIds[sv];
-                if (m.pos[v][GRAVITY_AXIS] < s.phys.collisionOffHeight && !m.penetratedMask[v])
+                if (m.pos[v][GRAVITY_AXIS] < s.phys.collisionOffHeight && !m.penetratedMask[v]) {
+                    s.ev(16, (int)im, v);
                     vertex_ccd(s, v, (int)im, m.colResults[sv]);
+                }
             }
         }, 32);
     }

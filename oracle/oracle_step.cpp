@@ -516,7 +516,8 @@ static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
         if (withIntermediateCD && ici > 0 && s.iIter % ici == ici - 1) {
             s.ev(8);
             dcd(s, true);
-            ccd(s);
+            ccd(s, true);
+            s.ev(5);
             prepare_collision_data(s);
             trace_active_lists(s);
         }
@@ -564,7 +565,7 @@ void phase_begin_substep(Scene& s) {
     apply_deformers(s);
 }
 void phase_prepare(Scene& s) { ccd(s); prepare_collision_data(s); }
-void phase_intermediate_cd(Scene& s) { dcd(s, true); ccd(s); prepare_collision_data(s); }   // the block at the end of an iteration above
+void phase_intermediate_cd(Scene& s) { dcd(s, true); ccd(s, true); prepare_collision_data(s); }   // the block at the end of an iteration above
 void phase_end_substep(Scene& s) { update_velocities(s); s.stats.substeps++; }
 
 void run_step(Scene& s) {

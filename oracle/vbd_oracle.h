@@ -130,7 +130,7 @@ void vertex_friction(float mu, float lambda, const float T[6], const float u[2],
 void collision_initialize(Scene& s);
 void collision_free(Scene& s);
 void dcd(Scene& s, bool intermediate);
-void ccd(Scene& s);
+void ccd(Scene& s, bool intermediate = false);
 void prepare_collision_data(Scene& s);
 void update_collision_info(Scene& s, ColResult& r);
 

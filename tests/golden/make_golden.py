@@ -224,18 +224,21 @@ def main():
         ref.ref_cloth_attachments(len(c["meshes"]), c["n_sim"], ip(voff), fp(allpos), len(c["v_infos"]), ip(c["v_infos"]), ip(c["f_infos"]), fp(c["barys"]),
                                   fp(st) if st is not None else None, fp(A), ip(cnt))
         out["cloth_attach" + tag] = A; out["cloth_attach_count" + tag] = cnt
-    # ---- the schedule of VBDPhysics::runStep_hybridCollisionHandling (stand-in members that record their calls), two frames
-    c = step_schedule_case()
+    # ---- the schedule of VBDPhysics::runStep_hybridCollisionHandling with its own dcd / ccd / intermediate passes (stand-in members and
+    #      detectors that record their calls): three frames with both detectors, one frame with DCD alone, one with CCD alone
     up8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
-    for frame in range(2):
-        c["scene"].trace_begin(); c["scene"].run_frames(1)
-        rec = np.ascontiguousarray(c["scene"].trace_read())
-        n = ref.ref_step_trace(ip(c["params4"]), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
-                               ip(rec), len(rec), None, 0)
-        tr = np.zeros(n, np.int32)
-        ref.ref_step_trace(ip(c["params4"]), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
-                           ip(rec), len(rec), ip(tr), n)
-        out[f"step_trace_f{frame}"] = tr.reshape(-1, 4)
+    for tag, dcd, ccd, frames in (("", 1, 1, 3), ("_dcd", 1, 0, 1), ("_ccd", 0, 1, 1)):
+        c = step_schedule_case(dcd, ccd)
+        pen = np.zeros(c["n_verts"], np.uint8)
+        for frame in range(frames):
+            c["scene"].trace_begin(); c["scene"].run_frames(1)
+            rec = np.ascontiguousarray(c["scene"].trace_read())
+            args = lambda o_, cap: (ip(c["params"](frame)), 3, ip(c["active"][frame]), ip(c["fixed_off"]), up8(c["mask"]), c["n_groups"], ip(c["group_off"]), ip(c["pairs"]),
+                                    ip(rec), len(rec), o_, cap, ip(c["sv_off"]), ip(c["svids"]))
+            n = ref.ref_step_trace(*args(None, 0), up8(pen.copy()))
+            tr = np.zeros(n, np.int32)
+            ref.ref_step_trace(*args(ip(tr), n), up8(pen))          # (this call carries the penetrated mask on to the next frame)
+            out[f"step_trace{tag}_f{frame}"] = tr.reshape(-1, 4)
     # ---- VBDPhysics::prepareCollisionDataCPU + ActiveCollisionList::addToActiveCollisionList on the oracle's detection results
     for tag, o in prepared_collision_cases():
         q = prepared_collision_inputs(o)

@@ -324,14 +324,16 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
-def step_schedule_case():
+def step_schedule_case(dcd=1, ccd=1):
     """Three Kuhn blocks for the SCHEDULE of the step: block 0 with fixed vertices, block 1 dropped onto it (contacts from the first
     detection on), block 2 appearing in frame 1 (frameToAppear); 2 substeps x 6 iterations, friction from iteration 2 on,
-    intermediate detection every 3 iterations. Single-threaded oracle (the trace is ordered)."""
+    intermediate detection every 3 iterations, tree rebuilds every 2 / 1 / 2 frames (tets / surface / CCD). Single-threaded oracle
+    (the trace is ordered). dcd / ccd: which detectors run (both; DCD alone; CCD alone)."""
     from oracle.binding import OracleScene
     phys = capi.default_physics_params(numSubsteps=2, iterations=6, frictionStartIter=2, intermediateCollisionIterations=3, collisionStiffness=1e5,
-                                       worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10])
-    o = OracleScene(phys, capi.default_collision_params(allowDCD=1, allowCCD=1), threads=1)
+                                       worldBoundsMin=[-10, 0, -10], worldBoundsMax=[10, 20, 10], dcdTetMeshSceneBVHRebuildSteps=2,
+                                       dcdSurfaceSceneBVHRebuildSteps=1, ccdBVHRebuildSteps=2)
+    o = OracleScene(phys, capi.default_collision_params(allowDCD=dcd, allowCCD=ccd), threads=1)
     fixed = [np.array([0, 3, 7, 20], np.int32), np.zeros(0, np.int32), np.array([1], np.int32)]
     shapes = [((3, 2, 2, 0.25), (0.0, 0.3, 0.0), 0), ((2, 2, 2, 0.22), (0.1, 0.72, 0.05), 0), ((2, 1, 2, 0.2), (0.3, 1.4, 0.1), 1)]
     sizes = []
@@ -349,8 +351,14 @@ def step_schedule_case():
     groups = o.parallel_groups()
     group_off = np.zeros(len(groups) + 1, np.int32); group_off[1:] = np.cumsum([2 * len(g) for g in groups])
     pairs = np.ascontiguousarray(np.concatenate([g.reshape(-1) for g in groups]), np.int32)
-    return dict(scene=o, params4=np.array([2, 6, 2, 3], np.int32), fixed_off=fixed_off, mask=mask, group_off=group_off, pairs=pairs, n_groups=len(groups),
-                active=[np.array([1, 1, 0], np.int32), np.array([1, 1, 1], np.int32)])
+    svids = [o.surface_vertex_ids(m) for m in range(3)]
+    sv_off = np.zeros(4, np.int32); sv_off[1:] = np.cumsum([len(x) for x in svids])
+
+    def params(frame):      # ref_step_trace's params10
+        return np.array([2, 6, 2, 3, frame, dcd, ccd, 2, 1, 2], np.int32)
+    return dict(scene=o, params=params, fixed_off=fixed_off, mask=mask, group_off=group_off, pairs=pairs, n_groups=len(groups), sv_off=sv_off,
+                svids=np.ascontiguousarray(np.concatenate(svids), np.int32), n_verts=int(fixed_off[-1]),
+                active=[np.array([1, 1, 0], np.int32), np.array([1, 1, 1], np.int32), np.array([1, 1, 1], np.int32)])
 
 
 def prepared_collision_cases():

@@ -517,28 +517,44 @@ def test_cloth_conservative_bounds_fold_bit_exact():
 
 
 def test_step_schedule_is_the_reference_loop():
-    """WHICH operations the step runs, in which order, on which (mesh, vertex), with which friction flag: the oracle's run_step
-    traced event by event against the reference's own loop - VBDPhysics::runStep_hybridCollisionHandling, VBDPhysics.cpp:1634-1707,
-    compiled against stand-in members that record their calls (oracle/ref_shim/refsteploop.cpp). Two frames of a three-block
-    scene with fixed vertices, contacts, a block that appears in frame 1, friction from iteration 2 on and intermediate detection
-    every 3 iterations. (The active collision lists are data the stand-in repeats from the oracle's recording; their content is
-    checked against the product bit for bit elsewhere.)"""
+    """WHICH operations the step runs, in which order, on which (mesh, vertex), with which flags: the oracle's run_step traced
+    event by event against the reference's own loop and detection passes - VBDPhysics::runStep_hybridCollisionHandling
+    (VBDPhysics.cpp:1634-1707) with ::dcd, ::intermediateDCD, ::ccd, ::intermediateCCD, ::intermediateCollisionDetection (:1958-2172),
+    compiled against stand-in members and detectors that record their calls (oracle/ref_shim/refsteploop.cpp). Three frames of a
+    three-block scene with fixed vertices, contacts, a block that appears in frame 1, friction from iteration 2 on, intermediate
+    detection every 3 iterations and tree rebuilds every 2 / 1 / 2 frames; one frame each with DCD alone (the intermediate pass
+    then re-queries every vertex) and CCD alone (the results are cleared instead). Covered: when the trees are rebuilt, when the
+    penetrated mask is cleared, which surface vertices each pass queries (DCD: all; intermediate DCD: the penetrated ones; CCD: the
+    others), closest-point queries after hits only, contact updates before the solves of a group, every vertex solve with its
+    friction flag. The outcome of a DCD query and the active lists are data the stand-in repeats from the oracle's recording."""
     from golden_inputs import step_schedule_case
-    c = step_schedule_case()
-    o = c["scene"]
-    for frame in range(2):
-        o.trace_begin(); o.run_frames(1)
-        tr = o.trace_read()
-        G = GOLD[f"step_trace_f{frame}"]
-        assert tr.shape == G.shape and np.array_equal(tr, G), frame
-        codes = set(G[:, 0].tolist())
-        assert codes == {1, 2, 3, 4, 5, 6, 7, 8, 9, 11}
-        assert (G[:, 0] == 1).sum() == 2 and (G[:, 0] == 9).sum() == 2 and (G[:, 0] == 8).sum() == 2 * 2          # substeps; 6 // 3 intermediate detections each
-        assert (G[:, 0] == 2).sum() == 2 * int(c["active"][frame].sum())
-        solves = G[G[:, 0] == 7]
-        assert set(solves[:, 3].tolist()) == {0, 1} and (2 in solves[:, 1]) == (frame == 1)                        # friction switches on; block 2 only once it has appeared
-        n_free = sum(int((c["mask"][c["fixed_off"][m]:c["fixed_off"][m + 1]] == 0).sum()) for m in range(3) if c["active"][frame][m])
-        assert len(solves) == 2 * 6 * n_free                                                                       # every free vertex of every active mesh, every iteration
+    for tag, dcd, ccd, frames in (("", 1, 1, 3), ("_dcd", 1, 0, 1), ("_ccd", 0, 1, 1)):
+        c = step_schedule_case(dcd, ccd)
+        o = c["scene"]
+        seen = set()
+        for frame in range(frames):
+            o.trace_begin(); o.run_frames(1)
+            tr = o.trace_read()
+            G = GOLD[f"step_trace{tag}_f{frame}"]
+            assert tr.shape == G.shape and np.array_equal(tr, G), (tag, frame)
+            seen |= set(G[:, 0].tolist())
+            assert (G[:, 0] == 1).sum() == 2 and (G[:, 0] == 9).sum() == 2 and (G[:, 0] == 8).sum() == 2 * 2          # substeps; 6 // 3 intermediate detections each
+            assert (G[:, 0] == 2).sum() == 2 * int(c["active"][frame].sum())
+            solves = G[G[:, 0] == 7]
+            assert set(solves[:, 3].tolist()) == {0, 1} and (2 in solves[:, 1]) == (frame >= 1)                       # friction switches on; block 2 only once it has appeared
+            n_free = sum(int((c["mask"][c["fixed_off"][m]:c["fixed_off"][m + 1]] == 0).sum()) for m in range(3) if c["active"][frame][m])
+            assert len(solves) == 2 * 6 * n_free                                                                       # every free vertex of every active mesh, every iteration
+            if dcd and ccd:
+                rebuilds = G[G[:, 0] == 12][:, 1:3].tolist()
+                assert rebuilds[0] == [int(frame == 2), int(frame >= 1)] and all(r == [0, 0] for r in rebuilds[1:])     # first substep of a rebuild frame only
+                assert G[G[:, 0] == 15][:, 1].tolist()[0] == int(frame == 2) and G[G[:, 0] == 15][:, 1].sum() == int(frame == 2)
+        if dcd and ccd:
+            assert seen == {1, 2, 3, 4, 5, 6, 7, 8, 9, 11, 12, 13, 14, 15, 16, 18}
+        elif dcd:
+            assert seen == {1, 2, 3, 4, 5, 6, 7, 8, 9, 11, 12, 13, 14, 18}
+            assert (G[:, 0] == 13).sum() == 2 * 3 * int(np.diff(c["sv_off"])[:2].sum())       # the intermediate passes re-query every surface vertex of the active meshes
+        else:
+            assert 17 in seen and 13 not in seen and 16 in seen
 
 
 def test_active_lists_and_relations_are_the_reference_construction():
