@@ -415,6 +415,17 @@ int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t c
     s->bowl.center = V3(center[0], center[1], center[2]); s->bowl.radius = radius; s->bowl.cap = cap != 0;
     return GAIA_OK;
 }
+// probe: the tail of the vertex step on n (force, Hessian, position) triples; flags [n]: 0 no move, 1 Newton step, 2 gradient step
+int oracle_vertex_step_tail(int n, const float* f, const float* h, float* x, float stepSize, float stepSizeGD, int32_t* flags) {
+    for (int i = 0; i < n; i++) {
+        M3 H; std::memcpy(H.m, h + 9 * i, 36);
+        V3 dir; float st; bool ok;
+        const int rc = vertex_step_direction(stepSize, stepSizeGD, V3(f[3 * i], f[3 * i + 1], f[3 * i + 2]), H, dir, st, ok);
+        flags[i] = rc <= 0 ? rc : (ok ? 1 : 2);
+        if (rc > 0) { const V3 p = V3(x[3 * i], x[3 * i + 1], x[3 * i + 2]) + st * dir; x[3 * i] = p.x; x[3 * i + 1] = p.y; x[3 * i + 2] = p.z; }
+    }
+    return GAIA_OK;
+}
 int oracle_solve3x3(const float* m9, const float* b3, float* out3) { return solve3x3_psd_stable(m9, b3, out3) ? 1 : 0; }
 int oracle_get_stats(void* h, gaia_stats* out) { *out = ((Scene*)h)->stats; return GAIA_OK; }
 int oracle_reset_stats(void* h) { std::memset(&((Scene*)h)->stats, 0, sizeof(gaia_stats)); return GAIA_OK; }

@@ -332,6 +332,21 @@ static int line_search(Scene& s, Mesh& m, int iV, const V3& dx, float alpha, flo
     return shrinks;
 }
 
+// what VBDStepWithCollision does once the terms are summed (M/VBD/VBDPhysics.cpp:2430-2462; useDouble3x3 = false, the default): nothing
+// below the force threshold; else the 3x3 solve, or - when it fails - the force itself with stepSizeGD.
+// Returns 0 (no move), 1 (move by stepSize * dir), -1 (NaN direction: the reference exits).
+int vertex_step_direction(float stepSizeNewton, float stepSizeGD, V3 force, const M3& h, V3& dir, float& stepSize, bool& solverOk) {
+    solverOk = true; stepSize = stepSizeNewton; dir = V3();
+    if (!(sqnorm(force) > CMP_EPSILON2)) return 0;
+    float d[3];
+    const float f[3] = {force.x, force.y, force.z};
+    solverOk = solve3x3_psd_stable(h.m, f, d);
+    if (!solverOk) { stepSize = stepSizeGD; d[0] = f[0]; d[1] = f[1]; d[2] = f[2]; }
+    if (std::isnan(d[0]) || std::isnan(d[1]) || std::isnan(d[2])) return -1;
+    dir = V3(d[0], d[1], d[2]);
+    return 1;
+}
+
 static void vbd_step_with_collision(Scene& s, Mesh& m, int iV, bool apply_friction) {
     M3 h; V3 force;
     neohookean_force_hessian(s, m, iV, force, h);
@@ -346,18 +361,15 @@ static void vbd_step_with_collision(Scene& s, Mesh& m, int iV, bool apply_fricti
     boundary_force_hessian(s, m, iV, force, h, apply_friction);
     collision_force_hessian(s, m, iV, force, h);
     // external force: zero (VBDBaseTetMesh::evaluateExternalForce, VBD_BaseMaterial.h:308-311)
-    if (sqnorm(force) > CMP_EPSILON2) {
-        float dir[3];
-        float stepSize = s.phys.stepSize;
-        float f[3] = {force.x, force.y, force.z};
-        bool ok = solve3x3_psd_stable(h.m, f, dir);
-        if (!ok) { stepSize = s.phys.stepSizeGD; dir[0] = f[0]; dir[1] = f[1]; dir[2] = f[2]; }
-        if (std::isnan(dir[0]) || std::isnan(dir[1]) || std::isnan(dir[2])) { s.err = "descentDirection has NaN"; return; }
+    V3 dir; float stepSize; bool ok;
+    const int rc = vertex_step_direction(s.phys.stepSize, s.phys.stepSizeGD, force, h, dir, stepSize, ok);
+    if (rc < 0) { s.err = "descentDirection has NaN"; return; }
+    if (rc > 0) {
         if (s.lineSearch.enabled) {
-            const int k = line_search(s, m, iV, V3(dir[0], dir[1], dir[2]), stepSize, ok ? s.lineSearch.tau : s.lineSearch.tauGD);
+            const int k = line_search(s, m, iV, dir, stepSize, ok ? s.lineSearch.tau : s.lineSearch.tauGD);
             if (k) __atomic_fetch_add(&s.lineSearchShrinks, (int64_t)k, __ATOMIC_RELAXED);
         } else
-            m.pos[iV] += stepSize * V3(dir[0], dir[1], dir[2]);
+            m.pos[iV] += stepSize * dir;
     }
 }
 

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -224,6 +224,11 @@ def main():
         ref.ref_cloth_attachments(len(c["meshes"]), c["n_sim"], ip(voff), fp(allpos), len(c["v_infos"]), ip(c["v_infos"]), ip(c["f_infos"]), fp(c["barys"]),
                                   fp(st) if st is not None else None, fp(A), ip(cnt))
         out["cloth_attach" + tag] = A; out["cloth_attach_count" + tag] = cnt
+    # ---- the tail of VBDPhysics::VBDStepWithCollision (threshold, CuMatrix::solve3x3_psd_stable, gradient fall-back, update)
+    c = vertex_step_tail_cases()
+    xs = c["x"].copy(); order = np.zeros(4, np.int32)
+    ref.ref_vertex_step_tail(len(xs), fp(c["f"]), fp(c["h"]), fp(xs), c["step"], c["step_gd"], 0, ip(order))
+    out["vertex_step_tail_x"] = xs; out["vertex_step_order"] = order
     # ---- the schedule of VBDPhysics::runStep_hybridCollisionHandling with its own dcd / ccd / intermediate passes (stand-in members and
     #      detectors that record their calls): three frames with both detectors, one frame with DCD alone, one with CCD alone
     up8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))

@@ -324,6 +324,29 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
+def vertex_step_tail_cases(n=240, seed=131):
+    """(total force, total Hessian, position) triples for the tail of the vertex step: well-conditioned SPD Hessians of the size the
+    step meets (mass / dt^2 + stiffness), forces just below and above the threshold |f|^2 = 1e-10, Hessians that are singular or
+    nearly singular (the 3x3 solve fails: gradient step), tiny, indefinite"""
+    rng = np.random.default_rng(seed)
+    f = (rng.normal(0, 1, (n, 3)) * 10.0 ** rng.uniform(-2, 4, (n, 1))).astype(np.float32)
+    H = np.zeros((n, 3, 3), np.float32)
+    for i in range(n):
+        A = rng.normal(0, 1, (3, 3)); S = A @ A.T + 0.1 * np.eye(3)
+        kind = i % 8
+        if kind == 5:
+            S = np.outer(A[:, 0], A[:, 0]) + 1e-5 * np.eye(3)                 # rank 1 plus a whiff (an exactly singular Hessian whose cofactors vanish
+            # makes the reference divide 0 by 0 and exit: "descentDirection has NaN")
+        elif kind == 6:
+            S = S - 2.0 * np.linalg.eigvalsh(S)[1] * np.eye(3)                # indefinite
+        elif kind == 7:
+            S = (np.outer(A[:, 0], A[:, 0]) + np.outer(A[:, 1], A[:, 1]) + 1e-7 * np.eye(3)) if i % 16 == 7 else S * 1e-12      # rank 2 plus a whiff; tiny
+        H[i] = (S * 10.0 ** rng.uniform(2, 6)).astype(np.float32)
+    f[3::8] = (rng.normal(0, 1, (len(f[3::8]), 3)) * rng.choice([2e-6, 5e-6, 8e-6, 2e-5], (len(f[3::8]), 1))).astype(np.float32)      # around the threshold 1e-5
+    x = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+    return dict(f=np.ascontiguousarray(f), h=np.ascontiguousarray(H.transpose(0, 2, 1).reshape(n, 9)), x=np.ascontiguousarray(x), step=0.9, step_gd=2e-6)
+
+
 def step_schedule_case(dcd=1, ccd=1):
     """Three Kuhn blocks for the SCHEDULE of the step: block 0 with fixed vertices, block 1 dropped onto it (contacts from the first
     detection on), block 2 appearing in frame 1 (frameToAppear); 2 substeps x 6 iterations, friction from iteration 2 on,

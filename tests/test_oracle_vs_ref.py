@@ -588,3 +588,26 @@ def test_active_lists_and_relations_are_the_reference_construction():
         assert len(rows) == 3 * int((q["has"] & q["path"]).sum()) and a_off[-1] >= int(q["has"].sum())
         total += int(q["has"].sum())
     assert total > 60
+
+
+def test_vertex_step_tail_bit_exact():
+    """What the vertex step does once its terms are summed - the force threshold, the 3x3 solve, the gradient fall-back with
+    stepSizeGD when the solve fails, x += stepSize * direction - against the reference's own VBDPhysics::VBDStepWithCollision
+    (VBDPhysics.cpp:2402-2484) with its own CuMatrix::solve3x3_psd_stable, compiled in oracle/ref_shim/refvertexstep.cu: 240 (force,
+    Hessian, position) triples with forces around the threshold and singular / indefinite / zero Hessians. New positions bit for
+    bit; all three outcomes occur. The same compile records the order in which that function sums its terms - material, inertia,
+    world box, contacts - which is the order vbd_step_with_collision restates."""
+    from golden_inputs import vertex_step_tail_cases
+    lib = load_oracle()
+    lib.oracle_vertex_step_tail.argtypes = [C.c_int, FP, FP, FP, C.c_float, C.c_float, C.POINTER(C.c_int32)]
+    c = vertex_step_tail_cases()
+    x = c["x"].copy(); flags = np.zeros(len(x), np.int32)
+    lib.oracle_vertex_step_tail(len(x), fp(c["f"]), fp(c["h"]), fp(x), c["step"], c["step_gd"], flags.ctypes.data_as(C.POINTER(C.c_int32)))
+    G = GOLD["vertex_step_tail_x"]
+    assert np.array_equal(x, G)
+    moved = (G != c["x"]).any(1)
+    assert not moved[flags == 0].any() and moved[flags > 0].sum() > 150        # (a step below the ulp of the position leaves it unchanged)
+    assert (flags == 0).sum() >= 10 and (flags == 1).sum() >= 100 and (flags == 2).sum() >= 10
+    below = (c["f"].astype(np.float32) ** 2).sum(1, dtype=np.float32) <= np.float32(1e-5) * np.float32(1e-5)
+    assert below.sum() >= 10 and np.array_equal(flags == 0, below)                # the threshold is |f|^2 > CMP_EPSILON^2, nothing else stops a step
+    assert GOLD["vertex_step_order"].tolist() == [0, 1, 2, 3]
