@@ -415,6 +415,15 @@ int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t c
     s->bowl.center = V3(center[0], center[1], center[2]); s->bowl.radius = radius; s->bowl.cap = cap != 0;
     return GAIA_OK;
 }
+// probe: the inertia term for n vertices, added onto given force / Hessian accumulators (in / out)
+int oracle_inertia_terms(int n, const float* mass, const float* inertia, const float* x, float dtSqrReciprocal, float* f, float* h) {
+    for (int i = 0; i < n; i++) {
+        V3 force(f[3 * i], f[3 * i + 1], f[3 * i + 2]); M3 H; std::memcpy(H.m, h + 9 * i, 36);
+        inertia_force_hessian(mass[i], V3(inertia[3 * i], inertia[3 * i + 1], inertia[3 * i + 2]), V3(x[3 * i], x[3 * i + 1], x[3 * i + 2]), dtSqrReciprocal, force, H);
+        f[3 * i] = force.x; f[3 * i + 1] = force.y; f[3 * i + 2] = force.z; std::memcpy(h + 9 * i, H.m, 36);
+    }
+    return GAIA_OK;
+}
 // probe: the tail of the vertex step on n (force, Hessian, position) triples; flags [n]: 0 no move, 1 Newton step, 2 gradient step
 int oracle_vertex_step_tail(int n, const float* f, const float* h, float* x, float stepSize, float stepSizeGD, int32_t* flags) {
     for (int i = 0; i < n; i++) {

@@ -347,17 +347,17 @@ int vertex_step_direction(float stepSizeNewton, float stepSizeGD, V3 force, cons
     return 1;
 }
 
+// VBDBaseTetMesh::accumlateInertiaForceAndHessian (M/VBD/VBD_BaseMaterial.h:359-366)
+void inertia_force_hessian(float mass, V3 inertia, V3 x, float dtSqrReciprocal, V3& force, M3& h) {
+    force += (mass * (inertia - x)) * dtSqrReciprocal;
+    const float hh = 1.f * mass * dtSqrReciprocal;
+    h(0, 0) += hh; h(1, 1) += hh; h(2, 2) += hh;
+}
+
 static void vbd_step_with_collision(Scene& s, Mesh& m, int iV, bool apply_friction) {
     M3 h; V3 force;
     neohookean_force_hessian(s, m, iV, force, h);
-    // inertia
-    {
-        const float w = m.mass[iV];
-        V3 d = m.inertia[iV] - m.pos[iV];
-        force += (w * d) * s.dtSqrReciprocal;
-        const float hh = 1.f * w * s.dtSqrReciprocal;
-        h(0, 0) += hh; h(1, 1) += hh; h(2, 2) += hh;
-    }
+    inertia_force_hessian(m.mass[iV], m.inertia[iV], m.pos[iV], s.dtSqrReciprocal, force, h);
     boundary_force_hessian(s, m, iV, force, h, apply_friction);
     collision_force_hessian(s, m, iV, force, h);
     // external force: zero (VBDBaseTetMesh::evaluateExternalForce, VBD_BaseMaterial.h:308-311)

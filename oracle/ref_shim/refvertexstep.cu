@@ -5,7 +5,8 @@
 // force (CMP_EPSILON2), the 3x3 solve in float or double (useDouble3x3), the fall-back to a gradient step of stepSizeGD when the
 // solve fails, the update x += stepSize * direction. The terms themselves (material, inertia, world box, contacts) are pinned one by
 // one elsewhere; here the stand-in's material routine adds the caller's TOTAL force / Hessian and the other three add nothing, and
-// the order in which the function calls them is recorded. oracle/Makefile extracts the lines into the build directory (deleted
+// the order in which the function calls them is recorded. Also here: VBDBaseTetMesh::accumlateInertiaForceAndHessian
+// (VBD_BaseMaterial.h:359-366), compiled against a second stand-in mesh over the caller's masses / inertia / positions. oracle/Makefile extracts the lines into the build directory (deleted
 // after linking). Stand-in <Eigen/Dense> from ref_shim/stub. Everything lives in namespace GAIA_VS.
 #include <cstdint>
 #include <cstdlib>
@@ -57,7 +58,33 @@ struct VBDPhysics {
 
 using namespace GAIA;
 #include "ref_vbdphysics_cpp_2402_2484.inc"
+
+namespace GAIA {
+typedef const float CFloatingType;
+struct RefInertiaParams { FloatingType dtSqrReciprocal = 0.f; };
+struct Cols3 { const float* p = nullptr; Vec3 col(int i) const { return Vec3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); } };
+struct VBDBaseTetMesh {
+    const float* mass = nullptr; Cols3 inertia, pos;
+    RefInertiaParams par; RefInertiaParams* pPhysicsParams = &par;
+    FloatingType vertexMass(int i) const { return mass[i]; }
+    Vec3 vertex(int i) const { return pos.col(i); }
+    void accumlateInertiaForceAndHessian(int iV, Vec3& force, Mat3& hessian);
+};
+#include "ref_basemat_h_359_366.inc"
+}  // namespace GAIA
 #undef GAIA
+
+extern "C" void ref_inertia_terms(int n, const float* mass, const float* inertia, const float* x, float dtSqrReciprocal, float* f, float* h) {
+    GAIA_VS::VBDBaseTetMesh m;
+    m.mass = mass; m.inertia.p = inertia; m.pos.p = x; m.par.dtSqrReciprocal = dtSqrReciprocal;
+    for (int i = 0; i < n; i++) {
+        GAIA_VS::Vec3 force(f[3 * i], f[3 * i + 1], f[3 * i + 2]); GAIA_VS::Mat3 H;
+        for (int k = 0; k < 9; k++) H.d[k] = h[9 * i + k];
+        m.accumlateInertiaForceAndHessian(i, force, H);
+        for (int k = 0; k < 3; k++) f[3 * i + k] = force.d[k];
+        for (int k = 0; k < 9; k++) h[9 * i + k] = H.d[k];
+    }
+}
 
 // n cases: total force f [n][3], total Hessian h [n][9] (column-major), position x [n][3] in / out; order4 [4]: the order in which
 // the four accumulate routines were called in the last case (0 material, 1 inertia, 2 world box, 3 contacts)

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -229,6 +229,11 @@ def main():
     xs = c["x"].copy(); order = np.zeros(4, np.int32)
     ref.ref_vertex_step_tail(len(xs), fp(c["f"]), fp(c["h"]), fp(xs), c["step"], c["step_gd"], 0, ip(order))
     out["vertex_step_tail_x"] = xs; out["vertex_step_order"] = order
+    # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
+    c = inertia_cases()
+    f = c["f0"].copy(); h = c["h0"].copy()
+    ref.ref_inertia_terms(len(f), fp(c["mass"]), fp(c["inertia"]), fp(c["x"]), c["dtsq"], fp(f), fp(h))
+    out["inertia_f"] = f; out["inertia_h"] = h
     # ---- the schedule of VBDPhysics::runStep_hybridCollisionHandling with its own dcd / ccd / intermediate passes (stand-in members and
     #      detectors that record their calls): three frames with both detectors, one frame with DCD alone, one with CCD alone
     up8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))

@@ -324,6 +324,14 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
+def inertia_cases(n=200, seed=133):
+    """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
+    rng = np.random.default_rng(seed)
+    return dict(mass=(10.0 ** rng.uniform(-4, 1, n)).astype(np.float32), inertia=rng.uniform(-3, 3, (n, 3)).astype(np.float32),
+                x=rng.uniform(-3, 3, (n, 3)).astype(np.float32), dtsq=float(np.float32(240.0) * np.float32(240.0)),
+                f0=(rng.normal(0, 100, (n, 3))).astype(np.float32), h0=(rng.normal(0, 1e4, (n, 9))).astype(np.float32))
+
+
 def vertex_step_tail_cases(n=240, seed=131):
     """(total force, total Hessian, position) triples for the tail of the vertex step: well-conditioned SPD Hessians of the size the
     step meets (mass / dt^2 + stiffness), forces just below and above the threshold |f|^2 = 1e-10, Hessians that are singular or

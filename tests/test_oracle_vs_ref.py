@@ -611,3 +611,17 @@ def test_vertex_step_tail_bit_exact():
     below = (c["f"].astype(np.float32) ** 2).sum(1, dtype=np.float32) <= np.float32(1e-5) * np.float32(1e-5)
     assert below.sum() >= 10 and np.array_equal(flags == 0, below)                # the threshold is |f|^2 > CMP_EPSILON^2, nothing else stops a step
     assert GOLD["vertex_step_order"].tolist() == [0, 1, 2, 3]
+
+
+def test_inertia_term_bit_exact():
+    """Row a4: m (y - x) / dt^2 and (m / dt^2) I added onto accumulators that already hold the material term, against the reference's
+    own VBDBaseTetMesh::accumlateInertiaForceAndHessian (VBD_BaseMaterial.h:359-366, compiled in oracle/ref_shim/refvertexstep.cu):
+    200 vertices, masses over five decades. Bit for bit."""
+    from golden_inputs import inertia_cases
+    lib = load_oracle()
+    lib.oracle_inertia_terms.argtypes = [C.c_int, FP, FP, FP, C.c_float, FP, FP]
+    c = inertia_cases()
+    f = c["f0"].copy(); h = c["h0"].copy()
+    lib.oracle_inertia_terms(len(f), fp(c["mass"]), fp(c["inertia"]), fp(c["x"]), c["dtsq"], fp(f), fp(h))
+    assert np.array_equal(f, GOLD["inertia_f"]) and np.array_equal(h, GOLD["inertia_h"])
+    assert not np.array_equal(f, c["f0"]) and np.array_equal(h[:, [1, 2, 3, 5, 6, 7]], c["h0"][:, [1, 2, 3, 5, 6, 7]]) and (h[:, 0] != c["h0"][:, 0]).any()
