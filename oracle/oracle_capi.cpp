@@ -415,6 +415,8 @@ int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t c
     s->bowl.center = V3(center[0], center[1], center[2]); s->bowl.radius = radius; s->bowl.cap = cap != 0;
     return GAIA_OK;
 }
+// probe: the Chebyshev weights omega_1 .. omega_n of the tet step
+void oracle_accelerator_omegas(float rho, int n, float* out) { float w = 1.f; for (int k = 1; k <= n; k++) { w = accelerator_omega(k, rho, w); out[k - 1] = w; } }
 // probe: the inertia term for n vertices, added onto given force / Hessian accumulators (in / out)
 int oracle_inertia_terms(int n, const float* mass, const float* inertia, const float* x, float dtSqrReciprocal, float* f, float* h) {
     for (int i = 0; i < n; i++) {

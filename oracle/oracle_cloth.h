@@ -136,6 +136,7 @@ void cloth_sewing_force_hessian(const TriMesh& m, int iV, V3& force, M3& hessian
 void cloth_constraint_force_hessian(const ClothScene& s, int iMesh, int vId, V3& force, M3& hessian);
 void cloth_transform_points(const gaia_cloth_object_params& obj, std::vector<V3>& pos);
 void cloth_detect(ClothScene& s);
+float cloth_accelerator_omega(float rho, int order, float prevOmega);
 void cloth_conservative_bounds(const ClothScene& s, TriMesh& m);
 void cloth_run_substeps(ClothScene& s, int nSubsteps);
 void cloth_run_iterations(ClothScene& s, int nIters);

@@ -424,7 +424,7 @@ static void apply_initial_step(ClothScene& s, TriMesh& m) {
 }
 
 // ChebysevAccelerator::getAcceleratorOmega (same recurrence as M/VBD/VBDPhysics.cpp:3558-3574)
-static float accelerator_omega(float rho, int order, float prevOmega) {
+float cloth_accelerator_omega(float rho, int order, float prevOmega) {      // ChebysevAccelerator::getAcceleratorOmega (M/SolverUtils/ChebysevAccelerator.h:15-35)
     switch (order) {
         case 1: return 1.f;
         case 2: return 2.f / (2.f - rho * rho);
@@ -579,7 +579,7 @@ static void cloth_iteration(ClothScene& s, int iIter, float& omega) {
     for (int i = 0; i < s.numSim; i++) { const TriMesh& m = s.meshes[i]; for (int v = 0; v < m.nV; v++) if (!m.fixedMask[v]) s.stats.vertexSolves++; }
     if (truncated) s.collisionDetectionRequired = true;     // rule R6
     if (s.phys.applyAcceleration) {
-        omega = accelerator_omega(s.phys.acceleratorRho, iIter + 1, omega);
+        omega = cloth_accelerator_omega(s.phys.acceleratorRho, iIter + 1, omega);
         // applyAcceleration (:893-915)
         if (omega > 1.f)
             for (int i = 0; i < s.numSim; i++) {

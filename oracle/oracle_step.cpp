@@ -461,7 +461,7 @@ static void update_velocities(Scene& s) {
 
 // Chebyshev accelerator: a GPU-path feature of the reference (runStepGPU, VBDPhysics.cpp:869-907; omega
 // VBDPhysics.cpp:3558-3574; apply kernel VBDPhysicsCompute.cu:910-944), restated here so the oracle covers it.
-static float accelerator_omega(int order, float rho, float prevOmega) {
+float accelerator_omega(int order, float rho, float prevOmega) {      // VBDPhysics::getAcceleratorOmega (M/VBD/VBDPhysics.cpp:3558-3574)
     switch (order) {
         case 1: return 1;
         case 2: return 2 / (2 - rho * rho);

@@ -229,6 +229,13 @@ def main():
     xs = c["x"].copy(); order = np.zeros(4, np.int32)
     ref.ref_vertex_step_tail(len(xs), fp(c["f"]), fp(c["h"]), fp(xs), c["step"], c["step_gd"], 0, ip(order))
     out["vertex_step_tail_x"] = xs; out["vertex_step_order"] = order
+    # ---- the Chebyshev weights: VBDPhysics::getAcceleratorOmega (tet step) and ChebysevAccelerator (cloth step), 40 iterations per rho
+    rhos = np.array([0.0, 0.3, 0.8, 0.93, 0.95, 0.99], np.float32)
+    W = np.zeros((2, len(rhos), 40), np.float32)
+    for which in (0, 1):
+        for i, rho in enumerate(rhos):
+            ref.ref_accelerator_omegas(which, float(rho), 40, fp(W[which, i]))
+    out["accel_rhos"] = rhos; out["accel_omegas"] = W
     # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
     c = inertia_cases()
     f = c["f0"].copy(); h = c["h0"].copy()

@@ -625,3 +625,19 @@ def test_inertia_term_bit_exact():
     lib.oracle_inertia_terms(len(f), fp(c["mass"]), fp(c["inertia"]), fp(c["x"]), c["dtsq"], fp(f), fp(h))
     assert np.array_equal(f, GOLD["inertia_f"]) and np.array_equal(h, GOLD["inertia_h"])
     assert not np.array_equal(f, c["f0"]) and np.array_equal(h[:, [1, 2, 3, 5, 6, 7]], c["h0"][:, [1, 2, 3, 5, 6, 7]]) and (h[:, 0] != c["h0"][:, 0]).any()
+
+
+def test_chebyshev_weights_bit_exact():
+    """Row a10: the accelerator's weights omega_1 .. omega_40 of the tet oracle against VBDPhysics::getAcceleratorOmega
+    (VBDPhysics.cpp:3558-3574) and of the cloth oracle against ChebysevAccelerator::getAcceleratorOmega (M/SolverUtils/
+    ChebysevAccelerator.h:6-38), both compiled in oracle/ref_shim/refaccel.cpp, for six values of rho (0 included). Bit for bit."""
+    from oracle.binding_cloth import _lib as cloth_lib
+    lib = load_oracle(); cl = cloth_lib()
+    lib.oracle_accelerator_omegas.argtypes = [C.c_float, C.c_int, FP]; lib.oracle_accelerator_omegas.restype = None
+    cl.oracle_cloth_accelerator_omegas.argtypes = [C.c_float, C.c_int, FP]; cl.oracle_cloth_accelerator_omegas.restype = None
+    W = GOLD["accel_omegas"]
+    for i, rho in enumerate(GOLD["accel_rhos"]):
+        a = np.zeros(40, np.float32); b = np.zeros(40, np.float32)
+        lib.oracle_accelerator_omegas(float(rho), 40, fp(a)); cl.oracle_cloth_accelerator_omegas(float(rho), 40, fp(b))
+        assert np.array_equal(a, W[0, i]) and np.array_equal(b, W[1, i]), rho
+    assert W[0, 0].max() == 1.0 and W[0, -1, -1] > 1.5 and np.array_equal(W[0], W[1])      # rho 0: no acceleration; the two recurrences agree
