@@ -101,6 +101,8 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_accelerate"):
+            lib.ref_accelerate.argtypes = [C.c_int, FP, FP, C.c_float]; lib.ref_accelerate.restype = None
         if hasattr(lib, "ref_accelerator_omegas"):
             lib.ref_accelerator_omegas.argtypes = [C.c_int, C.c_float, C.c_int, FP]; lib.ref_accelerator_omegas.restype = None
         if hasattr(lib, "ref_inertia_terms"):

@@ -417,6 +417,10 @@ int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t c
 }
 // probe: the Chebyshev weights omega_1 .. omega_n of the tet step
 void oracle_accelerator_omegas(float rho, int n, float* out) { float w = 1.f; for (int k = 1; k <= n; k++) { w = accelerator_omega(k, rho, w); out[k - 1] = w; } }
+// probe: the accelerator's position update for n vertices (v in / out)
+void oracle_accelerate(int n, float* v, const float* ypp, float omega) {
+    for (int i = 0; i < n; i++) { const V3 r = accelerate_position(V3(v[3 * i], v[3 * i + 1], v[3 * i + 2]), V3(ypp[3 * i], ypp[3 * i + 1], ypp[3 * i + 2]), omega); v[3 * i] = r.x; v[3 * i + 1] = r.y; v[3 * i + 2] = r.z; }
+}
 // probe: the inertia term for n vertices, added onto given force / Hessian accumulators (in / out)
 int oracle_inertia_terms(int n, const float* mass, const float* inertia, const float* x, float dtSqrReciprocal, float* f, float* h) {
     for (int i = 0; i < n; i++) {

@@ -461,6 +461,8 @@ static void update_velocities(Scene& s) {
 
 // Chebyshev accelerator: a GPU-path feature of the reference (runStepGPU, VBDPhysics.cpp:869-907; omega
 // VBDPhysics.cpp:3558-3574; apply kernel VBDPhysicsCompute.cu:910-944), restated here so the oracle covers it.
+// the accelerator's position update (VBDSolveParallelGroup_applyAcceleration_kernel, M/VBD/VBDPhysicsCompute.cu:932-935)
+V3 accelerate_position(V3 y, V3 yPrevPrev, float omega) { return yPrevPrev + omega * (y - yPrevPrev); }
 float accelerator_omega(int order, float rho, float prevOmega) {      // VBDPhysics::getAcceleratorOmega (M/VBD/VBDPhysics.cpp:3558-3574)
     switch (order) {
         case 1: return 1;
@@ -519,7 +521,7 @@ static void solve_iterations(Scene& s, int nIters, bool withIntermediateCD) {
                 if (!m.activeForMaterialSolve) continue;
                 for (int v = 0; v < m.nV; v++) {
                     if (m.fixedMask[v]) continue;
-                    if (!m.activeCollisionMask[v]) m.pos[v] = pp[im][v] + omega * (m.pos[v] - pp[im][v]);
+                    if (!m.activeCollisionMask[v]) m.pos[v] = accelerate_position(m.pos[v], pp[im][v], omega);
                     pp[im][v] = pIter[im][v];
                 }
             }

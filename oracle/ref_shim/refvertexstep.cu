@@ -103,3 +103,14 @@ extern "C" void ref_vertex_step_tail(int n, const float* f, const float* h, floa
         if (i == n - 1) for (int k = 0; k < 4; k++) order4[k] = ph.order[k];
     }
 }
+
+// the position update of the accelerator, the body of VBDSolveParallelGroup_applyAcceleration_kernel for one vertex
+// (Simulator/Modules/VBD/VBDPhysicsCompute.cu:932-935: y = (y_k+1 - y_k-1) * omega + y_k-1, with CuMatrix's vec3 helpers)
+extern "C" void ref_accelerate(int n, float* vAll, const float* yPrevPrevAll, float acceleratorOmega) {
+    typedef float FloatingTypeGPU;
+    for (int i = 0; i < n; i++) {
+        float* v = vAll + 3 * i;
+        const float* y_prevprev = yPrevPrevAll + 3 * i;
+#include "ref_compute_cu_932_935.inc"
+    }
+}

@@ -126,6 +126,7 @@ void neohookean_force_hessian(const Scene& s, const Mesh& m, int iV, V3& force, 
 V3 neohookean_force(const Mesh& m, int iV);
 void inertia_force_hessian(float mass, V3 inertia, V3 x, float dtSqrReciprocal, V3& force, M3& h);
 float accelerator_omega(int order, float rho, float prevOmega);
+V3 accelerate_position(V3 y, V3 yPrevPrev, float omega);
 int vertex_step_direction(float stepSizeNewton, float stepSizeGD, V3 force, const M3& h, V3& dir, float& stepSize, bool& solverOk);      // accumlateMaterialForce: elastic force alone
 bool solve3x3_psd_stable(const float* m, const float* b, float* out);
 void vertex_friction(float mu, float lambda, const float T[6], const float u[2], float epsU, V3& force, M3& hessian);

@@ -236,6 +236,11 @@ def main():
         for i, rho in enumerate(rhos):
             ref.ref_accelerator_omegas(which, float(rho), 40, fp(W[which, i]))
     out["accel_rhos"] = rhos; out["accel_omegas"] = W
+    rng = np.random.default_rng(141)
+    yv = rng.uniform(-3, 3, (300, 3)).astype(np.float32); ypp = (yv + rng.normal(0, 0.01, yv.shape)).astype(np.float32)
+    acc = yv.copy()
+    ref.ref_accelerate(len(acc), fp(acc), fp(ypp), 1.7321)
+    out["accel_y"] = yv; out["accel_ypp"] = ypp; out["accel_out"] = acc
     # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
     c = inertia_cases()
     f = c["f0"].copy(); h = c["h0"].copy()

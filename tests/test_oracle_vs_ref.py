@@ -641,3 +641,8 @@ def test_chebyshev_weights_bit_exact():
         lib.oracle_accelerator_omegas(float(rho), 40, fp(a)); cl.oracle_cloth_accelerator_omegas(float(rho), 40, fp(b))
         assert np.array_equal(a, W[0, i]) and np.array_equal(b, W[1, i]), rho
     assert W[0, 0].max() == 1.0 and W[0, -1, -1] > 1.5 and np.array_equal(W[0], W[1])      # rho 0: no acceleration; the two recurrences agree
+    # the position update y_{k-1} + omega (y_{k+1} - y_{k-1}): the body of VBDSolveParallelGroup_applyAcceleration_kernel (VBDPhysicsCompute.cu:932-935)
+    lib.oracle_accelerate.argtypes = [C.c_int, FP, FP, C.c_float]; lib.oracle_accelerate.restype = None
+    v = GOLD["accel_y"].copy()
+    lib.oracle_accelerate(len(v), fp(v), fp(np.ascontiguousarray(GOLD["accel_ypp"])), 1.7321)
+    assert np.array_equal(v, GOLD["accel_out"]) and not np.array_equal(v, GOLD["accel_y"])
