@@ -101,6 +101,8 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_deformer"):
+            lib.ref_deformer.argtypes = [C.c_int, C.c_int, FP, C.c_int, IP, FP, FP, C.c_double, C.c_double, C.c_int, C.POINTER(C.c_double), FP]; lib.ref_deformer.restype = None
         if hasattr(lib, "ref_accelerate"):
             lib.ref_accelerate.argtypes = [C.c_int, FP, FP, C.c_float]; lib.ref_accelerate.restype = None
         if hasattr(lib, "ref_accelerator_omegas"):
@@ -204,6 +206,11 @@ class OracleScene(SceneBase):
             L.oracle_get_col_results(self.h, m, up(r[0]), up(r[1]), up(r[2]), ip(r[3]), ip(r[4]))
             res.append(tuple(r))
         return active, rel, res
+
+    @property
+    def cur_time(self):
+        fn = self._lib.oracle_cur_time; fn.restype = C.c_double; fn.argtypes = [C.c_void_p]
+        return float(fn(self.h))
 
     def trace_begin(self):
         """start recording the schedule of run_step (threads=1 scenes only): see oracle/vbd_oracle.h, Scene::trace"""

@@ -415,6 +415,7 @@ int oracle_set_bowl_ground(void* h, const float* center, float radius, int32_t c
     s->bowl.center = V3(center[0], center[1], center[2]); s->bowl.radius = radius; s->bowl.cap = cap != 0;
     return GAIA_OK;
 }
+double oracle_cur_time(void* h) { return (double)((Scene*)h)->curTime; }
 // probe: the Chebyshev weights omega_1 .. omega_n of the tet step
 void oracle_accelerator_omegas(float rho, int n, float* out) { float w = 1.f; for (int k = 1; k <= n; k++) { w = accelerator_omega(k, rho, w); out[k - 1] = w; } }
 // probe: the accelerator's position update for n vertices (v in / out)

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (deformer_cases, run_oracle_deformer, inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -241,6 +241,15 @@ def main():
     acc = yv.copy()
     ref.ref_accelerate(len(acc), fp(acc), fp(ypp), 1.7321)
     out["accel_y"] = yv; out["accel_ypp"] = ypp; out["accel_out"] = acc
+    # ---- DeformerRotator / DeformerTranslater at the oracle's own curTime after each frame
+    c = deformer_cases()
+    for i, case in enumerate(c["cases"]):
+        times, _, o = run_oracle_deformer(case, c)
+        kind, sel, centre, a, w, end = case
+        res = np.zeros((len(times), len(sel), 3), np.float32)
+        ref.ref_deformer(kind, len(c["verts"]), fp(np.ascontiguousarray(c["verts"])), len(sel), ip(sel), fp(np.array(centre, np.float32)), fp(np.array(a, np.float32)),
+                         w, end, len(times), times.ctypes.data_as(C.POINTER(C.c_double)), fp(res))
+        out[f"deformer{i}_times"] = times; out[f"deformer{i}_pos"] = res
     # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
     c = inertia_cases()
     f = c["f0"].copy(); h = c["h0"].copy()

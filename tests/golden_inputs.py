@@ -324,6 +324,36 @@ def cloth_constraint_case(seed=91):
     return dict(meshes=meshes, n_sim=2, seams=seams, ratios=ratios, sew_k=7.5e3, v_infos=v_infos, f_infos=f_infos, barys=barys, stiff=stiff)
 
 
+def deformer_cases():
+    """A Kuhn beam whose two end faces are driven: (kind, selected vertices, centre, axis or speed, angular velocity, end time). The
+    rotator's axis is not a unit vector and does not pass through the centre on purpose (the reference normalises nothing); end
+    times fall inside the run."""
+    verts, tets = meshio.kuhn_beam(4, 2, 2, h=0.25, origin=(0.1, 0.5, -0.2))
+    left = np.nonzero(verts[:, 0] < 0.11)[0].astype(np.int32); right = np.nonzero(verts[:, 0] > 1.09)[0].astype(np.int32)
+    return dict(verts=verts, tets=tets, colors=meshio.kuhn_coloring(4, 2, 2),
+                cases=[(0, left, [0.0, 0.7, 0.1], [1.0, 0.05, -0.02], 2.5, -1.0), (0, right, [1.1, 0.75, 0.0], [0.9, 0.0, 0.1], -4.0, 0.05),
+                       (1, right, [0.0, 0.0, 0.0], [0.3, -0.1, 0.05], 0.0, -1.0), (1, left, [0.0, 0.0, 0.0], [-0.2, 0.4, 0.0], 0.0, 0.06)])
+
+
+def run_oracle_deformer(case, c, frames=6):
+    """the oracle with one deformer: (curTime after each frame, positions of the selected vertices after each frame)"""
+    from oracle.binding import OracleScene
+    kind, sel, centre, a, w, end = case
+    phys = capi.default_physics_params(numSubsteps=3, iterations=2, worldBoundsMin=[-10, -10, -10], worldBoundsMax=[10, 10, 10])
+    o = OracleScene(phys, capi.default_collision_params(allowDCD=0, allowCCD=0), threads=1)
+    o.add_tet_mesh(c["verts"], c["tets"], capi.default_object_params(miu=1e4, lmbd=1e5, density=100), c["colors"])
+    if kind == 0:
+        o.add_rotator(0, sel, centre, a, w, end)
+    else:
+        o.add_translator(0, sel, a, end)
+    o.finalize()
+    times, pos = [], []
+    for _ in range(frames):
+        o.run_frames(1)
+        times.append(o.cur_time); pos.append(o.positions(0)[sel].copy())
+    return np.array(times, np.float64), np.array(pos, np.float32), o
+
+
 def inertia_cases(n=200, seed=133):
     """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
     rng = np.random.default_rng(seed)

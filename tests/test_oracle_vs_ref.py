@@ -646,3 +646,20 @@ def test_chebyshev_weights_bit_exact():
     v = GOLD["accel_y"].copy()
     lib.oracle_accelerate(len(v), fp(v), fp(np.ascontiguousarray(GOLD["accel_ypp"])), 1.7321)
     assert np.array_equal(v, GOLD["accel_out"]) and not np.array_equal(v, GOLD["accel_y"])
+
+
+def test_tet_deformers_bit_exact():
+    """Row f3: the oracle's Rotator and Translator against the reference's own DeformerRotator / DeformerTranslater (M/VBD/
+    VBDDeformer.h:45-179, compiled in oracle/ref_shim/refdeformer.cpp against the stand-in <Eigen/Dense>): the driven vertices of a
+    beam after each of six frames, at the oracle's own clock (float accumulation of dt) - axis not normalised and off the centre,
+    rotation and translation that stop inside the run. Bit for bit (double trigonometry from the same libm, cast as there)."""
+    from golden_inputs import deformer_cases, run_oracle_deformer
+    c = deformer_cases()
+    for i, case in enumerate(c["cases"]):
+        times, pos, _ = run_oracle_deformer(case, c)
+        assert np.array_equal(times, GOLD[f"deformer{i}_times"])
+        assert np.array_equal(pos, GOLD[f"deformer{i}_pos"]), i
+        moved = np.abs(pos[-1] - c["verts"][case[1]]).max()
+        assert moved > 0.005
+        if case[5] > 0:
+            assert np.array_equal(pos[-1], pos[-2]) and not np.array_equal(pos[0], pos[1])      # stopped at its end time
