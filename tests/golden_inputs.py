@@ -354,6 +354,40 @@ def run_oracle_deformer(case, c, frames=6):
     return np.array(times, np.float64), np.array(pos, np.float32), o
 
 
+def cloth_deformer_cases():
+    """a 6 x 6 cloth whose two edges are driven: (kind, selected vertices, centre, axis or speed, angular velocity, start, end)"""
+    from gaia_b200 import cloth
+    v, f = cloth.grid_cloth(6, 1.0, origin=(0.0, 1.0, 0.0))
+    left = np.arange(0, 6, dtype=np.int32); right = np.arange(30, 36, dtype=np.int32)
+    return dict(verts=v, faces=f, cases=[(0, left, [0.0, 1.0, 0.1], [0.0, 0.05, 1.0], 3.0, 0.0, -1.0), (0, right, [0.2, 1.1, 0.0], [0.1, 0.0, 0.9], -5.0, 0.0, 0.04),
+                                         (1, right, [0, 0, 0], [0.3, -0.2, 0.05], 0.0, 0.0, -1.0), (1, left, [0, 0, 0], [-0.2, 0.4, 0.0], 0.0, 0.02, 0.06)])
+
+
+def run_cloth_oracle_deformer(case, c, frames=5, substeps=4):
+    """the cloth oracle with one deformer: (curTime of every substep, dt, positions of the selected vertices after each frame)"""
+    from gaia_b200 import cloth
+    from oracle.binding_cloth import OracleClothScene
+    kind, sel, centre, a, w, t0, t1 = case
+    phys = cloth.default_cloth_physics_params(numSubsteps=substeps, iterations=2, handleCollision=0)
+    o = OracleClothScene(phys, threads=1)
+    o.add_tri_mesh(c["verts"], c["faces"], cloth.default_cloth_object_params(density=0.2, miu=1e3), cloth.grid_cloth_coloring(6))
+    if kind == 0:
+        o.add_rotator(0, sel, centre, a, w, t1)
+    else:
+        o.add_translator(0, sel, a, t0, t1)
+    o.finalize()
+    dt = np.float32(phys.timeStep) / np.float32(substeps)
+    t = np.float32(0.0)
+    times, pos = [], []
+    for _ in range(frames):
+        o.run_frames(1)
+        for _ in range(substeps):
+            t = np.float32(t + dt); times.append(t)
+        assert abs(o.cur_time - float(t)) < 1e-9
+        pos.append(o.positions(0)[sel].copy())
+    return np.array(times, np.float32), float(dt), np.array(pos, np.float32)
+
+
 def inertia_cases(n=200, seed=133):
     """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
     rng = np.random.default_rng(seed)

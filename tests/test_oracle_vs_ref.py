@@ -663,3 +663,18 @@ def test_tet_deformers_bit_exact():
         assert moved > 0.005
         if case[5] > 0:
             assert np.array_equal(pos[-1], pos[-2]) and not np.array_equal(pos[0], pos[1])      # stopped at its end time
+
+
+def test_cloth_deformers_bit_exact():
+    """The cloth oracle's Rotator and Translator against the reference's own ClothDeformerRotator / ClothDeformerTranslater
+    (M/VBDCloth/VBDClothDeformer.h:43-199, compiled in oracle/ref_shim/refclothdeformer.cpp), applied once per substep at the
+    oracle's own clock: the driven edge of a cloth after each of five frames; a rotation that stops, a translation that runs only
+    between its start and end times. Bit for bit."""
+    from golden_inputs import cloth_deformer_cases, run_cloth_oracle_deformer
+    c = cloth_deformer_cases()
+    for i, case in enumerate(c["cases"]):
+        _, _, pos = run_cloth_oracle_deformer(case, c)
+        assert np.array_equal(pos, GOLD[f"cloth_deformer{i}_pos"]), i
+        assert np.abs(pos[-1] - c["verts"][case[1]]).max() > 0.005
+        if case[6] > 0:
+            assert np.array_equal(pos[-1], pos[-2])      # stopped
