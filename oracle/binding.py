@@ -101,6 +101,8 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_collider_sequence"):
+            lib.ref_collider_sequence.argtypes = [C.c_int, C.c_int, IP, FP, C.c_int, C.c_int, C.c_int, IP, C.c_int, C.c_int, FP, IP]; lib.ref_collider_sequence.restype = None
         if hasattr(lib, "ref_cloth_deformer"):
             lib.ref_cloth_deformer.argtypes = [C.c_int, C.c_int, FP, C.c_int, IP, FP, FP, C.c_double, C.c_float, C.c_float, C.c_int, FP, C.c_float, FP]; lib.ref_cloth_deformer.restype = None
         if hasattr(lib, "ref_deformer"):

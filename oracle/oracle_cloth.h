@@ -149,6 +149,7 @@ float cloth_probe_vf(const ClothScene& s, int vMesh, int v, int fMesh, int f, in
 float cloth_probe_ee(const ClothScene& s, int m1, int e1, int m2, int e2, int vertexOrder, V3& force, M3& hessian);
 bool cloth_probe_feasible_region(const TriMesh& m, V3 p, int faceId, int type, float eps);
 void cloth_probe_initial_step(ClothScene& s);
+bool cloth_probe_update_colliders(ClothScene& s, int frameId, int substep, int iIter);
 void cloth_probe_update_velocity(ClothScene& s);
 bool cloth_probe_truncate(const ClothScene& s, int mesh, int v, V3& newPos);
 void cloth_probe_boundary(const ClothScene& s, int mesh, int v, V3& force, M3& hessian);

@@ -121,6 +121,7 @@ int oracle_cloth_get_incidence(void* h, int mesh, int32_t* fOff, int32_t* fAdj, 
     return GAIA_OK;
 }
 void oracle_cloth_accelerator_omegas(float rho, int n, float* out) { float w = 1.f; for (int k = 1; k <= n; k++) { w = cloth_accelerator_omega(rho, k, w); out[k - 1] = w; } }
+int oracle_cloth_probe_update_colliders(void* h, int frameId, int substep, int iIter) { return cloth_probe_update_colliders(*(ClothScene*)h, frameId, substep, iIter) ? 1 : 0; }
 int oracle_cloth_finalize(void* h) { cloth_finalize(*(ClothScene*)h); return GAIA_OK; }
 int oracle_cloth_run_frames(void* h, int32_t n) {
     ClothScene* s = (ClothScene*)h;

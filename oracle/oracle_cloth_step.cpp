@@ -538,6 +538,11 @@ static bool update_colliders(ClothScene& s) {
     return any;
 }
 
+bool cloth_probe_update_colliders(ClothScene& s, int frameId, int substep, int iIter) {      // parity probe: one call of updateCollider at the given place of the step
+    s.frameId = frameId; s.substep = substep; s.iIter = iIter;
+    return update_colliders(s);
+}
+
 static void cloth_iteration(ClothScene& s, int iIter, float& omega) {
     s.iIter = iIter;
     if (iIter == 0) apply_deformers(s);

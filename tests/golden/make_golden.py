@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (cloth_deformer_cases, run_cloth_oracle_deformer, deformer_cases, run_oracle_deformer, inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (collider_sequence_cases, cloth_deformer_cases, run_cloth_oracle_deformer, deformer_cases, run_oracle_deformer, inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -259,6 +259,13 @@ def main():
         ref.ref_cloth_deformer(kind, len(c["verts"]), fp(np.ascontiguousarray(c["verts"])), len(sel), ip(sel), fp(np.array(centre, np.float32)), fp(np.array(a, np.float32)),
                                w, t0, t1, len(times), fp(times), dt, fp(res))
         out[f"cloth_deformer{i}_pos"] = res[3::4].copy()          # after the last substep of each frame
+    # ---- ColliderTrimeshSequence::update / ::set_state
+    c = collider_sequence_cases()
+    nV = len(c["verts"])
+    for i, (isub, iit) in enumerate(c["settings"]):
+        res = np.zeros((len(c["calls"]), nV, 3), np.float32); upd = np.zeros(len(c["calls"]), np.int32)
+        ref.ref_collider_sequence(nV, len(c["key_frames"]), ip(c["key_frames"]), fp(c["keys"]), isub, iit, len(c["calls"]), ip(c["calls"]), c["substeps"], c["iters"], fp(res), ip(upd))
+        out[f"collider_seq{i}_pos"] = res; out[f"collider_seq{i}_upd"] = upd
     # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
     c = inertia_cases()
     f = c["f0"].copy(); h = c["h0"].copy()

@@ -388,6 +388,38 @@ def run_cloth_oracle_deformer(case, c, frames=5, substeps=4):
     return np.array(times, np.float32), float(dt), np.array(pos, np.float32)
 
 
+def collider_sequence_cases(seed=151):
+    """A collider with four key meshes at frames 1, 3, 4, 8 and the calls one step makes - every (frame 0..9, substep 0..2, iteration
+    0..3) in order - for three settings: per-iteration interpolation over the first 2 iterations, over the first iteration only,
+    and once per frame"""
+    from gaia_b200 import cloth
+    rng = np.random.default_rng(seed)
+    v, f = cloth.grid_cloth(4, 0.8, origin=(0.0, 0.3, 0.0))
+    keys = np.stack([v + rng.normal(0, 0.05, v.shape).astype(np.float32) + np.float32([0, 0.1 * k, 0]) for k in range(4)]).astype(np.float32)
+    calls = np.array([(fr, sub, it) for fr in range(10) for sub in range(3) for it in range(4)], np.int32)
+    return dict(verts=v, faces=f, keys=np.ascontiguousarray(keys), key_frames=np.array([1, 3, 4, 8], np.int32), calls=calls, substeps=3, iters=4,
+                settings=[(1, 2), (1, 1), (0, 1)])
+
+
+def run_cloth_oracle_collider(c, interp_substep, interp_iter):
+    """the cloth oracle's update of the collider at every call: (positions [nCalls, nV, 3], updated flags)"""
+    from gaia_b200 import cloth
+    from oracle.binding_cloth import OracleClothScene
+    phys = cloth.default_cloth_physics_params(numSubsteps=c["substeps"], iterations=c["iters"], handleCollision=0)
+    o = OracleClothScene(phys, threads=1)
+    sv, sf = cloth.grid_cloth(3, 0.5, origin=(0.0, 1.0, 0.0))
+    o.add_tri_mesh(sv, sf, cloth.default_cloth_object_params(), cloth.grid_cloth_coloring(3))
+    cid = o.add_tri_mesh(c["keys"][0], c["faces"], cloth.default_cloth_object_params(), simulated=False)
+    o.set_collider_sequence(cid, c["keys"], c["key_frames"], bool(interp_substep), interp_iter)
+    o.finalize()
+    fn = o._lib.oracle_cloth_probe_update_colliders
+    pos, upd = [], []
+    for fr, sub, it in c["calls"]:
+        upd.append(int(fn(o.h, int(fr), int(sub), int(it))))
+        pos.append(o.positions(cid).copy())
+    return np.array(pos, np.float32), np.array(upd, np.int32)
+
+
 def inertia_cases(n=200, seed=133):
     """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
     rng = np.random.default_rng(seed)

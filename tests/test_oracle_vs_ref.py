@@ -678,3 +678,17 @@ def test_cloth_deformers_bit_exact():
         assert np.abs(pos[-1] - c["verts"][case[1]]).max() > 0.005
         if case[6] > 0:
             assert np.array_equal(pos[-1], pos[-2])      # stopped
+
+
+def test_collider_key_frame_sequence_bit_exact():
+    """The cloth oracle's key-frame collider against the reference's own ColliderTrimeshSequence::update / ::set_state (M/SpatialQuery/
+    ColiiderTriMeshSequence.h:59-124, compiled in oracle/ref_shim/refcollider.cpp): every call of ten frames x 3 substeps x 4 iterations
+    for three interpolation settings - which calls move the collider (the flag that forces a re-detection) and where to. Bit for bit."""
+    from golden_inputs import collider_sequence_cases, run_cloth_oracle_collider
+    c = collider_sequence_cases()
+    for i, (isub, iit) in enumerate(c["settings"]):
+        pos, upd = run_cloth_oracle_collider(c, isub, iit)
+        assert np.array_equal(upd, GOLD[f"collider_seq{i}_upd"]), i
+        assert np.array_equal(pos, GOLD[f"collider_seq{i}_pos"]), i
+        assert upd[0] == 1 and 0 < upd.sum() < len(upd)
+    assert GOLD["collider_seq0_upd"].sum() > GOLD["collider_seq1_upd"].sum() > GOLD["collider_seq2_upd"].sum()
