@@ -420,6 +420,23 @@ def run_cloth_oracle_collider(c, interp_substep, interp_iter):
     return np.array(pos, np.float32), np.array(upd, np.int32)
 
 
+def group_merge_case(seed=161):
+    """Five meshes with different numbers of colour classes of different sizes (Kuhn colourings, greedy colourings, and colourings
+    with some classes merged) for the merge into global parallel groups: (meshes [(verts, tets, colours)], the colours as the oracle
+    holds them = sorted by size, large first, ties in file order)"""
+    rng = np.random.default_rng(seed)
+    meshes = []
+    for i, dims in enumerate(((3, 2, 2), (2, 2, 1), (4, 1, 1), (1, 1, 1), (2, 3, 2))):
+        verts, tets = meshio.kuhn_beam(*dims, h=0.2, origin=(0.5 * i, 0.1, 0.0))
+        colors = meshio.kuhn_coloring(*dims) if i % 2 == 0 else meshio.greedy_coloring(len(verts), tets)
+        colors = [np.asarray(c, np.int32) for c in colors if len(c)]
+        if i == 4:      # fewer, larger classes would not be a proper colouring; split instead: one class in two
+            k = int(np.argmax([len(c) for c in colors])); c = colors.pop(k); colors += [c[: len(c) // 3], c[len(c) // 3:]]
+        rng.shuffle(colors)
+        meshes.append((verts, tets, colors))
+    return meshes
+
+
 def inertia_cases(n=200, seed=133):
     """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
     rng = np.random.default_rng(seed)

@@ -692,3 +692,25 @@ def test_collider_key_frame_sequence_bit_exact():
         assert np.array_equal(pos, GOLD[f"collider_seq{i}_pos"]), i
         assert upd[0] == 1 and 0 < upd.sum() < len(upd)
     assert GOLD["collider_seq0_upd"].sum() > GOLD["collider_seq1_upd"].sum() > GOLD["collider_seq2_upd"].sum()
+
+
+def test_parallel_group_merge_is_the_reference_construction():
+    """Row a1: the merge of every mesh's colour classes into the global parallel groups - each class of a mesh joins the currently
+    smallest group that mesh has not used yet - against the reference's own findSmallestParallelGroup and the merge loop of
+    VBDPhysics::initialize (VBDPhysics.cpp:99-122, 236-274, compiled in oracle/ref_shim/refgroups.cpp): five meshes with 2 to 5 classes
+    of uneven sizes. Groups entry for entry, order included. (The size sort before it is the stated stable rule: the reference's
+    std::sort leaves ties to the library.)"""
+    from gaia_b200 import capi
+    from golden_inputs import group_merge_case
+    from oracle.binding import OracleScene
+    o = OracleScene(capi.default_physics_params(), capi.default_collision_params(allowDCD=0, allowCCD=0), threads=1)
+    for verts, tets, colors in group_merge_case():
+        o.add_tet_mesh(verts, tets, capi.default_object_params(), colors)
+    o.finalize()
+    groups = o.parallel_groups()
+    off, pairs = GOLD["group_merge_off"], GOLD["group_merge_pairs"]
+    assert len(groups) == len(off) - 1 == 5
+    for g, mine in enumerate(groups):
+        assert np.array_equal(mine, pairs[off[g] // 2:off[g + 1] // 2]), g          # (offsets count ints: two per pair)
+    sizes = np.diff(off)
+    assert sizes.min() > 0 and len(set(pairs[:off[1] // 2, 0].tolist())) >= 4      # the groups mix several meshes
