@@ -101,6 +101,8 @@ def load_ref():
             lib.ref_boundary_bowl_cpu.argtypes = [FP, FP, FP, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_bowl_cpu.restype = None
         if hasattr(lib, "ref_boundary_cpu"):
             lib.ref_boundary_cpu.argtypes = [FP, FP, FP, FP, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, FP, FP]; lib.ref_boundary_cpu.restype = None
+        if hasattr(lib, "ref_cloth_merge_groups"):
+            lib.ref_cloth_merge_groups.argtypes = [C.c_int, IP, IP, IP, IP, IP, IP, IP]; lib.ref_cloth_merge_groups.restype = C.c_int
         if hasattr(lib, "ref_merge_groups"):
             lib.ref_merge_groups.argtypes = [C.c_int, IP, IP, IP, IP, IP, IP]; lib.ref_merge_groups.restype = C.c_int
         if hasattr(lib, "ref_collider_sequence"):

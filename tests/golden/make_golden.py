@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from golden_inputs import (group_merge_case, collider_sequence_cases, cloth_deformer_cases, run_cloth_oracle_deformer, deformer_cases, run_oracle_deformer, inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
+from golden_inputs import (cloth_group_merge_case, group_merge_case, collider_sequence_cases, cloth_deformer_cases, run_cloth_oracle_deformer, deformer_cases, run_oracle_deformer, inertia_cases, vertex_step_tail_cases, prepared_collision_cases, prepared_collision_inputs, step_schedule_case, cloth_bounds_case, bowl_cases, cloth_constraint_case, boundary_cases_cpu, cloth_step_sequence_cases, run_cloth_oracle_step_sequence, step_sequence_cases, run_oracle_step_sequence, cloth_feasible_region_cases, feasible_region_cases, traverse_cases, cloth_contact_case, cloth_material_case, neohookean_case, single_tet_cases, solve3x3_cases, ccd_cases, cubic_cases, contact_cases, boundary_cases,
                            point_in_tet_cases, closest_point_triangle_cases, segment_cases, cloth_repulsion_cases)  # noqa: E402
 from oracle.binding import load_ref, ref_available  # noqa: E402
 
@@ -276,6 +276,17 @@ def main():
     g_off = np.zeros(int(n_colors.max()) + 1, np.int32); g_pairs = np.zeros(2 * int(n_verts.sum()), np.int32)
     nG = ref.ref_merge_groups(len(meshes), ip(n_verts), ip(n_colors), ip(class_off), ip(class_verts), ip(g_off), ip(g_pairs))
     out["group_merge_off"] = g_off[: nG + 1].copy(); out["group_merge_pairs"] = g_pairs[: g_off[nG]].reshape(-1, 2).copy()
+    # ---- VBDClothSimulationFramework::initializeParallelGroups + ::findSmallestParallelGroup (classes in file order)
+    meshes = cloth_group_merge_case()
+    n_colors = np.array([len(c) for _, _, c in meshes], np.int32); n_verts = np.array([len(v) for v, _, _ in meshes], np.int32)
+    # the mesh loader sorts the classes large to small before the merge sees them (TriMesh.cpp:747-750, needs the mesh class: done
+    # here, stable on ties as the oracle does)
+    flat = [c for _, _, cols in meshes for c in sorted(cols, key=lambda c: -len(c))]
+    class_off = np.zeros(len(flat) + 1, np.int32); class_off[1:] = np.cumsum([len(c) for c in flat])
+    class_verts = np.ascontiguousarray(np.concatenate(flat), np.int32)
+    g_off = np.zeros(int(n_colors.max()) + 1, np.int32); g_pairs = np.zeros(2 * int(n_verts.sum()), np.int32); g_col = np.zeros(int(n_verts.sum()), np.int32)
+    nG = ref.ref_cloth_merge_groups(len(meshes), ip(n_verts), ip(n_colors), ip(class_off), ip(class_verts), ip(g_off), ip(g_pairs), ip(g_col))
+    out["cloth_group_merge_off"] = g_off[: nG + 1].copy(); out["cloth_group_merge_pairs"] = g_pairs[: g_off[nG]].reshape(-1, 2).copy()
     # ---- VBDBaseTetMesh::accumlateInertiaForceAndHessian
     c = inertia_cases()
     f = c["f0"].copy(); h = c["h0"].copy()

@@ -437,6 +437,24 @@ def group_merge_case(seed=161):
     return meshes
 
 
+def cloth_group_merge_case(seed=163):
+    """four cloths with 9, 6, 9 and 4 colour classes of uneven sizes (grid colourings with classes merged or emptied, in shuffled
+    order): the cloth framework takes the classes in file order and does not retire a group once a mesh has used it"""
+    from gaia_b200 import cloth
+    rng = np.random.default_rng(seed)
+    meshes = []
+    for i, n in enumerate((7, 5, 6, 4)):
+        v, f = cloth.grid_cloth(n, 1.0, origin=(0.0, 1.0 + 0.2 * i, 0.0))
+        cols = [np.asarray(c, np.int32) for c in cloth.grid_cloth_coloring(n)]
+        if i == 1:
+            cols = [np.concatenate([cols[0], cols[4]]), np.concatenate([cols[1], cols[5]]), cols[2], cols[3], np.concatenate([cols[6], cols[7]]), cols[8]]   # (not proper: only the merge is under test)
+        if i == 3:
+            cols = [np.concatenate(cols[0:3]), np.concatenate(cols[3:5]), np.concatenate(cols[5:8]), cols[8]]
+        order = rng.permutation(len(cols))
+        meshes.append((v, f, [cols[k] for k in order]))
+    return meshes
+
+
 def inertia_cases(n=200, seed=133):
     """masses, inertia targets and positions for the inertia term, with force / Hessian accumulators that already hold something"""
     rng = np.random.default_rng(seed)

@@ -714,3 +714,22 @@ def test_parallel_group_merge_is_the_reference_construction():
         assert np.array_equal(mine, pairs[off[g] // 2:off[g + 1] // 2]), g          # (offsets count ints: two per pair)
     sizes = np.diff(off)
     assert sizes.min() > 0 and len(set(pairs[:off[1] // 2, 0].tolist())) >= 4      # the groups mix several meshes
+
+
+def test_cloth_parallel_group_merge_is_the_reference_construction():
+    """The cloth oracle's parallel groups against the reference's own VBDClothSimulationFramework::initializeParallelGroups and
+    ::findSmallestParallelGroup (VBDClothPhysics.cpp:72-138, compiled in oracle/ref_shim/refclothgroups.cpp): four cloths with 9, 6, 9
+    and 4 classes of uneven sizes, taken in file order, a used group not retired (two classes of one mesh may share a group). Groups
+    entry for entry, order included."""
+    from gaia_b200 import cloth
+    from golden_inputs import cloth_group_merge_case
+    from oracle.binding_cloth import OracleClothScene
+    o = OracleClothScene(cloth.default_cloth_physics_params(handleCollision=0), threads=1)
+    for v, f, cols in cloth_group_merge_case():
+        o.add_tri_mesh(v, f, cloth.default_cloth_object_params(), cols)
+    o.finalize()
+    groups = o.parallel_groups()
+    off, pairs = GOLD["cloth_group_merge_off"], GOLD["cloth_group_merge_pairs"]
+    assert len(groups) == len(off) - 1 == 9
+    for g, mine in enumerate(groups):
+        assert np.array_equal(np.asarray(mine).reshape(-1, 2), pairs[off[g] // 2:off[g + 1] // 2]), g
